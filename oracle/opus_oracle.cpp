@@ -1,0 +1,392 @@
+// ORACLE (test infrastructure only — never linked into the product library).
+// CPU restatement of the Opus decoder front-end:
+//   TOC helpers / packet parse    src/packet.rs:30-276, 316-498
+//   decode_native_with            src/opus_decoder.rs:1139-1367
+//   decode_frame (CELT-only arm)  src/opus_decoder.rs:453-1133
+//   opus_decode_float / opus_decode (i16: soft clip + float2int16)
+//                                 src/opus_decoder.rs:1632-1715, 1803-1826; src/opus.rs:16-140;
+//                                 src/celt/float_cast.rs:38-41
+// SILK-only / Hybrid frames return OPUS_UNIMPLEMENTED (-5) until the SILK oracle lands
+// (SURVEY.md §8 rows A16, C3/C4). Packet-loss concealment likewise (row F2).
+// Exposes a plain C API (orc_*) that tests/ drive through ctypes.
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <thread>
+#include <vector>
+
+#include "celt_oracle.h"
+
+namespace orc {
+
+enum { MODE_SILK_ONLY = 1000, MODE_HYBRID = 1001, MODE_CELT_ONLY = 1002 };
+enum { BW_NB = 1101, BW_MB = 1102, BW_WB = 1103, BW_SWB = 1104, BW_FB = 1105 };
+enum { OPUS_BAD_ARG = -1, OPUS_BUFFER_TOO_SMALL = -2, OPUS_INTERNAL_ERROR = -3, OPUS_INVALID_PACKET = -4, OPUS_UNIMPLEMENTED = -5 };
+
+static int packet_mode(uint8_t toc) { return (toc & 0x80) ? MODE_CELT_ONLY : ((toc & 0x60) == 0x60 ? MODE_HYBRID : MODE_SILK_ONLY); }
+static int packet_bandwidth(uint8_t toc) {  // packet.rs:177-204
+  if (toc & 0x80) { int b = (toc >> 5) & 3; return b == 0 ? BW_NB : b == 1 ? BW_WB : b == 2 ? BW_SWB : BW_FB; }
+  if ((toc & 0x60) == 0x60) return (toc & 0x10) ? BW_FB : BW_SWB;
+  int b = (toc >> 5) & 3;
+  return b == 0 ? BW_NB : b == 1 ? BW_MB : b == 2 ? BW_WB : BW_SWB;
+}
+static int packet_samples_per_frame(uint8_t toc, int fs) {  // packet.rs:212-236
+  if (toc & 0x80) return (fs << ((toc >> 3) & 3)) / 400;
+  if ((toc & 0x60) == 0x60) return (toc & 0x08) ? fs / 50 : fs / 100;
+  int sc = (toc >> 3) & 3;
+  return sc == 3 ? fs * 60 / 1000 : (fs << sc) / 100;
+}
+static int parse_size(const uint8_t* d, int len, int* size) {
+  if (len < 1) return -1;
+  if (d[0] < 252) { *size = d[0]; return 1; }
+  if (len < 2) return -1;
+  *size = 4 * d[1] + d[0];
+  return 2;
+}
+
+struct Parsed { int count; const uint8_t* frames[48]; int sizes[48]; int packet_offset; };
+
+// packet.rs:316-498
+static int packet_parse(const uint8_t* data, int len, int self_delimited, Parsed* out) {
+  if (len == 0) return OPUS_INVALID_PACKET;
+  int idx = 1, remaining = len - 1;
+  uint8_t toc = data[0];
+  int framesize = packet_samples_per_frame(toc, 48000);
+  int cbr = 0, count, last_size = remaining, pad = 0;
+  int* sz = out->sizes;
+  memset(sz, 0, sizeof(out->sizes));
+  switch (toc & 3) {
+    case 0: count = 1; break;
+    case 1:
+      count = 2; cbr = 1;
+      if (!self_delimited) {
+        if (remaining & 1) return OPUS_INVALID_PACKET;
+        last_size = remaining / 2;
+        sz[0] = last_size;
+      }
+      break;
+    case 2: {
+      count = 2;
+      int s, nb = parse_size(data + idx, len - idx, &s);
+      if (nb < 0) return OPUS_INVALID_PACKET;
+      if (s > (remaining >= nb ? remaining - nb : 0)) return OPUS_INVALID_PACKET;
+      idx += nb; remaining -= nb;
+      sz[0] = s;
+      last_size = remaining - s;
+      break;
+    }
+    default: {
+      if (remaining == 0) return OPUS_INVALID_PACKET;
+      uint8_t ch = data[idx++];
+      remaining--;
+      count = ch & 0x3F;
+      if (count == 0 || count > 48 || framesize * count > 5760) return OPUS_INVALID_PACKET;
+      if (ch & 0x40) {
+        for (;;) {
+          if (remaining == 0) return OPUS_INVALID_PACKET;
+          int p = data[idx++];
+          remaining--;
+          int tmp = p == 255 ? 254 : p;
+          pad += tmp;
+          if (remaining < tmp) return OPUS_INVALID_PACKET;
+          remaining -= tmp;
+          if (p != 255) break;
+        }
+      }
+      cbr = !(ch & 0x80);
+      if (!cbr) {
+        last_size = remaining;
+        for (int i = 0; i < count - 1; i++) {
+          int s, nb = parse_size(data + idx, len - idx, &s);
+          if (nb < 0) return OPUS_INVALID_PACKET;
+          if (s > (remaining >= nb ? remaining - nb : 0)) return OPUS_INVALID_PACKET;
+          idx += nb; remaining -= nb;
+          sz[i] = s;
+          last_size -= nb + s;
+          if (last_size < 0) return OPUS_INVALID_PACKET;
+        }
+      } else if (!self_delimited) {
+        int per = remaining / count;
+        if (per * count != remaining) return OPUS_INVALID_PACKET;
+        last_size = per;
+        for (int i = 0; i < count - 1; i++) sz[i] = per;
+      }
+    }
+  }
+  if (self_delimited) {
+    int s, nb = parse_size(data + idx, len - idx, &s);
+    if (nb < 0) return OPUS_INVALID_PACKET;
+    if (s > (remaining >= nb ? remaining - nb : 0)) return OPUS_INVALID_PACKET;
+    idx += nb; remaining -= nb;
+    sz[count - 1] = s;
+    if (cbr) {
+      if (s * count > remaining) return OPUS_INVALID_PACKET;
+      for (int i = 0; i < count - 1; i++) sz[i] = s;
+    } else if (nb + s > last_size) return OPUS_INVALID_PACKET;
+  } else {
+    if (last_size < 0 || last_size > 1275) return OPUS_INVALID_PACKET;
+    sz[count - 1] = last_size;
+  }
+  int cur = idx;
+  for (int i = 0; i < count; i++) {
+    if (cur + sz[i] > len) return OPUS_INVALID_PACKET;
+    out->frames[i] = data + cur;
+    cur += sz[i];
+  }
+  if (cur + pad > len) return OPUS_INVALID_PACKET;
+  out->count = count;
+  out->packet_offset = cur + pad;
+  return 0;
+}
+
+struct OpusDecoder {
+  int fs = 48000, channels = 2;
+  CeltDecoder celt;
+  int mode = 0, prev_mode = 0, bandwidth = 0, frame_size = 0, stream_channels = 0, prev_redundancy = 0;
+  int last_packet_duration = 0, decode_gain = 0;
+  uint32_t range_final = 0;
+  float softclip_mem[2] = {0, 0};
+  CeltTrace trace;
+
+  int init(int fs_, int ch) {
+    if (!(fs_ == 48000 || fs_ == 24000 || fs_ == 16000 || fs_ == 12000 || fs_ == 8000) || (ch != 1 && ch != 2)) return OPUS_BAD_ARG;
+    fs = fs_; channels = ch;
+    celt.init(ch, 48000 / fs_);
+    stream_channels = ch;
+    frame_size = fs_ / 400;
+    reset();
+    return 0;
+  }
+  void reset() {  // opus_decoder.rs:1451-1476
+    celt.reset();
+    stream_channels = channels;
+    bandwidth = 0; mode = 0; prev_mode = 0; frame_size = fs / 400; prev_redundancy = 0; last_packet_duration = 0;
+    range_final = 0; softclip_mem[0] = softclip_mem[1] = 0;
+  }
+
+  // opus_decoder.rs:453-1133, CELT-only arm.
+  int decode_frame(const uint8_t* data, int len, float* pcm, int fsz, int decode_fec) {
+    int F20 = fs / 50, F10 = F20 / 2, F5 = F10 / 2, F2_5 = F5 / 2;
+    if (fsz < F2_5) return OPUS_BUFFER_TOO_SMALL;
+    fsz = fsz < fs / 25 * 3 ? fsz : fs / 25 * 3;
+    if (data == nullptr || len <= 1) return OPUS_UNIMPLEMENTED;  // PLC row (F2)
+    int audiosize = frame_size;
+    int md = mode;
+    if (md != MODE_CELT_ONLY) return OPUS_UNIMPLEMENTED;        // SILK / hybrid rows
+    EcDec dec;
+    dec.init(data, (uint32_t)len);
+    if (prev_mode > 0 && prev_mode != MODE_CELT_ONLY && !prev_redundancy) return OPUS_UNIMPLEMENTED;  // transition needs PLC
+    if (audiosize > fsz) return OPUS_BAD_ARG;
+    int endband = 21;
+    switch (bandwidth) { case BW_NB: endband = 13; break; case BW_MB: case BW_WB: endband = 17; break; case BW_SWB: endband = 19; break; case BW_FB: endband = 21; break; }
+    celt.end_band = endband;
+    celt.stream_channels = stream_channels;
+    celt.start_band = 0;
+    if (md != prev_mode && prev_mode > 0 && !prev_redundancy) celt.reset();
+    int celt_frame = audiosize < F20 ? audiosize : F20;
+    if (decode_fec) return OPUS_UNIMPLEMENTED;
+    int ret = celt_decode_with_ec(&celt, data, len, pcm, celt_frame, &dec, 0);
+    if (ret < 0) return ret;
+    if (ret != celt_frame) return OPUS_INTERNAL_ERROR;
+    prev_mode = md;
+    prev_redundancy = 0;
+    range_final = len > 1 ? celt.rng : 0;
+    return audiosize;
+  }
+
+  // opus_decoder.rs:1139-1367 (no FEC / PLC arms yet)
+  int decode_native(const uint8_t* data, int len, float* pcm, int fsz, int decode_fec, int soft_clip) {
+    if (fsz <= 0) return OPUS_BAD_ARG;
+    if ((decode_fec || len == 0 || data == nullptr) && fsz % (fs / 400) != 0) return OPUS_BAD_ARG;
+    if (len == 0 || data == nullptr) return OPUS_UNIMPLEMENTED;
+    uint8_t toc = data[0];
+    int pmode = packet_mode(toc), pbw = packet_bandwidth(toc), pfs = packet_samples_per_frame(toc, fs);
+    int pch = (toc & 4) ? 2 : 1;
+    Parsed P;
+    int r = packet_parse(data, len, 0, &P);
+    if (r < 0) return r;
+    if (decode_fec) return OPUS_UNIMPLEMENTED;
+    if (P.count * pfs > fsz) return OPUS_BUFFER_TOO_SMALL;
+    mode = pmode; bandwidth = pbw; frame_size = pfs; stream_channels = pch;
+    int nb = 0;
+    for (int i = 0; i < P.count; i++) {
+      int ret = decode_frame(P.frames[i], P.sizes[i], pcm + nb * channels, fsz - nb, 0);
+      if (ret < 0) return ret;
+      nb += ret;
+    }
+    last_packet_duration = nb;
+    apply_gain_clip(pcm, nb, soft_clip);
+    return nb;
+  }
+
+  void apply_gain_clip(float* pcm, int n, int soft_clip) {  // opus_decoder.rs:1376-1418
+    if (decode_gain != 0) {
+      const float scale = 3.32192809488736234787f / 5120.0f;  // DECODE_GAIN_SCALE opus_decoder.rs:53
+      float g = (float)exp(0.6931471805599453094 * (double)(scale * (float)decode_gain));
+      for (int i = 0; i < n * channels; i++) pcm[i] *= g;
+    }
+    if (soft_clip) pcm_soft_clip(pcm, n, channels, softclip_mem);
+    else softclip_mem[0] = softclip_mem[1] = 0;
+  }
+
+  // src/opus.rs:16-140 (opus_pcm_soft_clip_impl)
+  static void pcm_soft_clip(float* x_, int N, int C, float* declip_mem) {
+    if (C < 1 || N < 1) return;
+    for (int i = 0; i < N * C; i++) x_[i] = x_[i] < -2.f ? -2.f : (x_[i] > 2.f ? 2.f : x_[i]);
+    for (int c = 0; c < C; c++) {
+      float* x = x_ + c;
+      float a = declip_mem[c];
+      for (int i = 0; i < N; i++) {
+        if (x[i * C] * a >= 0) break;
+        x[i * C] = x[i * C] + a * x[i * C] * x[i * C];
+      }
+      int curr = 0;
+      float x0 = x[0];
+      for (;;) {
+        int i;
+        for (i = curr; i < N; i++) if (!(x[i * C] >= -1.f && x[i * C] <= 1.f)) break;
+        if (i == N) { a = 0; break; }
+        int peak_pos = i, start = i, end = i;
+        float maxval = fabsf(x[i * C]);
+        while (start > 0 && x[i * C] * x[(start - 1) * C] >= 0) start--;
+        while (end < N && x[i * C] * x[end * C] >= 0) {
+          if (fabsf(x[end * C]) > maxval) { maxval = fabsf(x[end * C]); peak_pos = end; }
+          end++;
+        }
+        int special = (start == 0 && x[i * C] * x[0] >= 0);
+        a = (maxval - 1) / (maxval * maxval);
+        a += a * 2.4e-7f;
+        if (x[i * C] > 0) a = -a;
+        for (i = start; i < end; i++) x[i * C] = x[i * C] + a * x[i * C] * x[i * C];
+        if (special && peak_pos >= 2) {
+          float offset = x0 - x[0];
+          float delta = offset / (float)peak_pos;
+          for (i = curr; i < peak_pos; i++) {
+            offset -= delta;
+            x[i * C] += offset;
+            x[i * C] = x[i * C] < -1.f ? -1.f : (x[i * C] > 1.f ? 1.f : x[i * C]);
+          }
+        }
+        curr = end;
+        if (curr == N) break;
+      }
+      declip_mem[c] = a;
+    }
+  }
+};
+
+static inline int16_t float2int16(float v) {  // float_cast.rs:38-41
+  float s = v * 32768.0f;
+  s = s < -32768.0f ? -32768.0f : (s > 32767.0f ? 32767.0f : s);
+  return (int16_t)lrintf(s);
+}
+
+}  // namespace orc
+
+using namespace orc;
+
+extern "C" {
+
+void* orc_create(int fs, int channels, uint32_t quirks) {
+  OpusDecoder* d = new OpusDecoder();
+  if (d->init(fs, channels) < 0) { delete d; return nullptr; }
+  d->celt.quirks = quirks;
+  return d;
+}
+void orc_destroy(void* h) { delete (OpusDecoder*)h; }
+void orc_reset(void* h) { ((OpusDecoder*)h)->reset(); }
+void orc_set_gain(void* h, int gain_q8) { ((OpusDecoder*)h)->decode_gain = gain_q8; }
+uint32_t orc_final_range(void* h) { return ((OpusDecoder*)h)->range_final; }
+int orc_last_packet_duration(void* h) { return ((OpusDecoder*)h)->last_packet_duration; }
+
+// opus_decode_float (opus_decoder.rs:1803-1826)
+int orc_decode_float(void* h, const uint8_t* data, int len, float* pcm, int frame_size, int fec) {
+  return ((OpusDecoder*)h)->decode_native(data, len, pcm, frame_size, fec, 0);
+}
+// opus_decode (i16; opus_decoder.rs:1632-1715): decode to float scratch with soft clip, then float2int16.
+int orc_decode_i16(void* h, const uint8_t* data, int len, int16_t* pcm, int frame_size, int fec) {
+  OpusDecoder* d = (OpusDecoder*)h;
+  if (frame_size <= 0) return OPUS_BAD_ARG;
+  // (the reference limits frame_size to the packet's sample count when a packet is present)
+  if (data && len > 0 && !fec) {
+    int count = (data[0] & 3) == 0 ? 1 : ((data[0] & 3) != 3 ? 2 : (len < 2 ? -1 : (data[1] & 0x3F)));
+    if (count < 0) return OPUS_INVALID_PACKET;
+    int ns = count * packet_samples_per_frame(data[0], d->fs);
+    if (ns * 25 > d->fs * 3) return OPUS_INVALID_PACKET;
+    if (ns > 0 && ns < frame_size) frame_size = ns;
+  }
+  std::vector<float> tmp((size_t)frame_size * d->channels);
+  int ret = d->decode_native(data, len, tmp.data(), frame_size, fec, 1);
+  if (ret > 0) for (int i = 0; i < ret * d->channels; i++) pcm[i] = float2int16(tmp[i]);
+  return ret;
+}
+
+// Stage dump of the LAST decoded CELT frame (enable before decoding).
+void orc_trace_enable(void* h, int on) { OpusDecoder* d = (OpusDecoder*)h; d->celt.trace = on ? &d->trace : nullptr; }
+int orc_trace_info(void* h, int* out /*16 ints*/) {
+  CeltTrace& t = ((OpusDecoder*)h)->trace;
+  int v[16] = {t.lm, t.C, t.N, t.silence, t.transient, t.intra, t.spread, t.anti_collapse_on, t.intensity, t.dual_stereo,
+               t.coded_bands, t.pf_pitch, t.pf_tapset, (int)t.seed_out, 0, 0};
+  memcpy(out, v, sizeof(v));
+  memcpy(&out[14], &t.pf_gain, 4);
+  return 0;
+}
+int orc_trace_get(void* h, int what, void* dst, int max_elems) {
+  CeltTrace& t = ((OpusDecoder*)h)->trace;
+  const void* src = nullptr; size_t n = 0, es = 4;
+  switch (what) {
+    case 0: src = t.iy.data(); n = t.iy.size(); break;
+    case 1: src = t.X.data(); n = t.X.size(); break;
+    case 2: src = t.bandE.data(); n = t.bandE.size(); break;
+    case 3: src = t.syn.data(); n = t.syn.size(); break;
+    case 4: src = t.post.data(); n = t.post.size(); break;
+    case 5: src = t.tf_res; n = NB_EBANDS; break;
+    case 6: src = t.pulses; n = NB_EBANDS; break;
+    case 7: src = t.fine_quant; n = NB_EBANDS; break;
+    default: return -1;
+  }
+  if ((int)n > max_elems) n = max_elems;
+  memcpy(dst, src, n * es);
+  return (int)n;
+}
+
+// Batch helper used by tests and by bench.py's cpu_baseline leg: decodes a [n_ticks][n_lanes] packet grid
+// (packet p = t*n_lanes + j belongs to lane j) with one fresh decoder per lane, `threads` std::threads,
+// lanes statically partitioned. pcm layout: [p][frame_size*channels]. Returns 0.
+int orc_decode_grid(int fs, int channels, uint32_t quirks, const uint8_t* arena, const uint32_t* offsets, int n_lanes,
+                    int n_ticks, int frame_size, float* pcm /*nullable*/, int16_t* pcm16 /*nullable*/, int32_t* samples_out,
+                    uint32_t* final_range_out, int threads) {
+  if (threads < 1) threads = 1;
+  auto work = [&](int tid) {
+    std::vector<float> buf((size_t)frame_size * channels);
+    std::vector<int16_t> buf16((size_t)frame_size * channels);
+    for (int j = tid; j < n_lanes; j += threads) {
+      OpusDecoder d;
+      d.init(fs, channels);
+      d.celt.quirks = quirks;
+      for (int t = 0; t < n_ticks; t++) {
+        size_t p = (size_t)t * n_lanes + j;
+        const uint8_t* pkt = arena + offsets[p];
+        int len = (int)(offsets[p + 1] - offsets[p]);
+        int ret;
+        if (pcm16) {
+          int16_t* o = pcm16 + p * frame_size * channels;
+          ret = orc_decode_i16(&d, pkt, len, o, frame_size, 0);
+        } else {
+          float* o = pcm ? pcm + p * frame_size * channels : buf.data();
+          ret = d.decode_native(pkt, len, o, frame_size, 0, 0);
+        }
+        if (samples_out) samples_out[p] = ret;
+        if (final_range_out) final_range_out[p] = d.range_final;
+      }
+    }
+  };
+  std::vector<std::thread> th;
+  for (int i = 1; i < threads; i++) th.emplace_back(work, i);
+  work(0);
+  for (auto& t : th) t.join();
+  return 0;
+}
+
+}  // extern "C"
