@@ -1,0 +1,110 @@
+/* mousiki_b200 — C ABI of the B200 batched Opus decoder.
+ *
+ * This is the drop-in boundary for ONE path of cijiugechu/mousiki: Opus packet decode.
+ * Each entry point names the reference interface it replaces (paths relative to the
+ * reference tree). Signatures use plain pointers and sizes only; a Rust / C / Python
+ * host binds them directly (see INTEGRATION.md for the `extern "C"` block a mousiki
+ * maintainer would add).
+ *
+ * Semantics per stream are those of `mousiki::Decoder` (src/codec.rs:792-977) /
+ * `c_style_api::opus_decoder::opus_decode_float` (src/opus_decoder.rs:1803-1826):
+ * one decoder state per stream id, packets of a stream are decoded in the order they
+ * appear in the call, output is interleaved PCM, errors are reported per packet with
+ * libopus codes (src/opus_decoder.rs:275-286) and never abort the batch.
+ *
+ * There is no CPU fallback: every decode entry point runs CUDA kernels on the device
+ * chosen at bd_create and fails with BD_ERR_CUDA if that is impossible.
+ */
+#ifndef MOUSIKI_B200_H
+#define MOUSIKI_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* API-level return codes (per-packet results use the Opus codes below) */
+#define BD_OK 0
+#define BD_ERR_BAD_ARG (-1)        /* OpusDecoderInitError::BadArgument, src/opus_decoder.rs:1550-1556 */
+#define BD_ERR_CUDA (-100)         /* no usable device / kernel launch or copy failed (see bd_last_error) */
+#define BD_ERR_ALLOC (-101)
+#define BD_ERR_UNIMPLEMENTED (-5)
+
+/* per-packet codes written to samples_out[] when negative (OpusDecodeError::code, src/opus_decoder.rs:275-286) */
+#define BD_OPUS_BAD_ARG (-1)
+#define BD_OPUS_BUFFER_TOO_SMALL (-2)
+#define BD_OPUS_INTERNAL_ERROR (-3)
+#define BD_OPUS_INVALID_PACKET (-4)
+#define BD_OPUS_UNIMPLEMENTED (-5)
+
+/* Behaviour switches: bit set = mousiki's float decoder as written, clear = libopus (DESIGN.md "Quirks"). */
+#define BD_QUIRKS_MOUSIKI 0x7fu
+
+typedef struct bd_handle bd_handle;
+
+typedef struct bd_config {
+  uint32_t struct_size;              /* sizeof(bd_config), for forward compatibility */
+  uint32_t n_streams;                /* decoder states to allocate (stream ids are 0..n_streams-1) */
+  int32_t sample_rate_hz;            /* Decoder::new(sample_rate, ..): 48000 (8/12/16/24 kHz: BD_ERR_UNIMPLEMENTED) */
+  int32_t channels;                  /* Channels::Mono = 1 / Channels::Stereo = 2 */
+  int32_t gain_q8;                   /* DecoderBuilder::gain / OPUS_SET_GAIN, Q8 dB (src/codec.rs:411-463) */
+  int32_t disable_phase_inversion;   /* <0: decoder default (mono decoders disable it), 0/1 explicit */
+  uint32_t quirks;                   /* BD_QUIRKS_MOUSIKI */
+  int32_t device;                    /* CUDA device ordinal */
+  uint32_t max_frames_per_pass;      /* 0 = default; bounds the phase-1 scratch (14 KB per frame) */
+  uint32_t reserved;
+} bd_config;
+
+/* Decoder::new / DecoderBuilder::build for n_streams decoders (src/codec.rs:792-801, src/opus_decoder.rs:1536-1603). */
+int bd_create(const bd_config* cfg, bd_handle** out);
+void bd_destroy(bd_handle* h);
+/* Decoder::reset / OPUS_RESET_STATE (src/opus_decoder.rs:1451-1476). ids == NULL resets every stream. */
+int bd_reset_streams(bd_handle* h, const uint32_t* stream_ids, uint32_t n);
+const char* bd_last_error(const bd_handle* h);
+
+/* Decoder::decode_float / opus_decode_float for a batch (src/codec.rs:892-907, src/opus_decoder.rs:1803-1826).
+ * HOST buffers. Packet p is arena[offsets[p] .. offsets[p+1]) and belongs to stream_ids[p]; packets of one
+ * stream are decoded in array order. flags[p] bit0 = decode_fec, bit1 = packet lost (both: row F2, reported as
+ * BD_OPUS_UNIMPLEMENTED until built); flags may be NULL. pcm receives packet p's interleaved samples at
+ * pcm + p * pcm_stride (pcm_stride elements >= frame_size * channels; the per-channel capacity
+ * pcm_stride / channels plays the role of `frame_size`). samples_out[p] = samples per channel (>= 0) or an
+ * Opus error code; final_range_out[p] = Decoder::final_range() after that packet. Returns BD_OK or an API error. */
+int bd_decode_f32(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
+                  const uint8_t* flags, float* pcm, uint32_t pcm_stride, int32_t* samples_out, uint32_t* final_range_out);
+/* Decoder::decode / opus_decode (i16: soft clip + round; src/codec.rs:843-859, src/opus_decoder.rs:1632-1715). */
+int bd_decode_i16(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
+                  const uint8_t* flags, int16_t* pcm, uint32_t pcm_stride, int32_t* samples_out, uint32_t* final_range_out);
+
+/* Device-resident form of the same call for callers that already hold packets in HBM and keep PCM there.
+ * Regular grid: packet (t, j) = index t * n_lanes + j belongs to stream lane_stream[j] (NULL: stream j);
+ * a zero-length packet marks "nothing for this lane at this tick". All pointers are DEVICE pointers;
+ * cuda_stream is a cudaStream_t (NULL = default stream). The call returns after enqueueing; results are
+ * valid once the stream is synchronised. d_pcm_f32 or d_pcm_i16 may be NULL (but not both non-NULL). */
+int bd_decode_grid_dev(bd_handle* h, const uint8_t* d_arena, const uint32_t* d_offsets, uint32_t n_lanes, uint32_t n_ticks,
+                       const uint32_t* d_lane_stream, float* d_pcm_f32, int16_t* d_pcm_i16, uint32_t pcm_stride,
+                       int32_t* d_samples_out, uint32_t* d_final_range_out, void* cuda_stream);
+
+/* Decoder::{bandwidth,last_packet_duration,final_range} style queries (src/codec.rs:838-977); synchronises. */
+typedef struct bd_stream_info {
+  uint32_t final_range;
+  int32_t last_packet_duration;
+  int32_t prev_mode;      /* 0 none, 1000 SILK, 1001 hybrid, 1002 CELT */
+  int32_t celt_error;
+} bd_stream_info;
+int bd_get_stream_info(bd_handle* h, uint32_t stream_id, bd_stream_info* out);
+
+/* Pinned host memory helpers so that a host language can stage packets/PCM for full-rate PCIe copies. */
+void* bd_alloc_pinned(uint64_t bytes);
+void bd_free_pinned(void* p);
+
+/* Number of kernel launches issued by the last decode call (bench.py's gpu_launches). */
+uint32_t bd_last_launch_count(const bd_handle* h);
+
+/* Test hooks (parity suite): optional device-side capture of the decoded PVQ pulse vectors and normalised spectra
+ * of the next bd_decode_* call; layout [packet][2][960] int32 / float. Pass 0 to disable. Host buffers are
+ * filled when the call returns. */
+int bd_debug_capture(bd_handle* h, int32_t* pulses_host, float* spectrum_host, uint32_t max_packets);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

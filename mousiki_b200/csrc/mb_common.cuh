@@ -1,0 +1,166 @@
+// mousiki_b200 — shared definitions for the batched CELT decode kernels (sm_100a).
+//
+// The kernel bodies in mb_*.cuh are written as plain functions over an explicit
+// (thread id, team size) pair so that the very same source compiles
+//   * with nvcc as __device__ code called from the __global__ wrappers in mb_kernels.cu, and
+//   * with g++ (-DMB_EMUL) as a single-threaded host emulation used by the CPU test-suite
+//     (tests/emul/) to check the algorithm against the oracle where no GPU exists.
+// The emulation is test infrastructure only; the product library never runs it.
+#pragma once
+#include <stdint.h>
+#include <string.h>
+#include <math.h>
+
+#if defined(__CUDACC__) && !defined(MB_EMUL)
+#define MB_DEV __device__ __forceinline__
+#define MB_MEM __device__ __forceinline__
+#define MB_DEV_NOINLINE __device__ __noinline__
+#define MB_TBL static __device__ const
+#define MB_SYNC() __syncthreads()
+#define MB_ON_DEVICE 1
+#else
+#define MB_DEV static inline
+#define MB_MEM inline
+#define MB_DEV_NOINLINE static
+#define MB_TBL static const
+#define MB_SYNC() ((void)0)
+#define MB_ON_DEVICE 0
+#endif
+
+#include "celt_tables_data.h"
+
+namespace mb {
+
+// ---- fixed CELT mode parameters (48 kHz / 960 static mode; reference src/celt/modes.rs:84-105)
+enum {
+  NB_EBANDS = 21, OVERLAP = 120, SHORT_MDCT = 120, MAX_LM = 3, MAX_N = 960,
+  MAX_PERIOD = 1024, COMB_MINPERIOD = 15, BITRES = 3,
+  HIST = 1024,  // post-filtered history kept per channel (comb filter reaches back T+2 <= 1024)
+};
+
+// ---- quirk switches: bit set = mousiki's float decoder behaviour, clear = libopus
+enum : uint32_t {
+  Q1_DYNALLOC_BUDGET = 1u << 0, Q2_MDCT_ZERO_FILL = 1u << 1, Q5_FOLD_START = 1u << 2, Q6_HYBRID_LOWBAND = 1u << 3,
+  Q7_EBITS_BUST = 1u << 4, Q8_COARSE_CLAMP = 1u << 5, Q9_DUAL_STEREO_RSV = 1u << 6, QUIRKS_MOUSIKI = 0x7f,
+};
+
+// ---- Opus error codes (reference src/opus_decoder.rs:275-286)
+enum { MB_OK = 0, MB_BAD_ARG = -1, MB_BUFFER_TOO_SMALL = -2, MB_INTERNAL_ERROR = -3, MB_INVALID_PACKET = -4, MB_UNIMPLEMENTED = -5 };
+
+// ---- phase-1 -> phase-2 scratch ("records"): 32-bit words, structure-of-arrays in tiles of 32 frames:
+//      word(slot, f) = rec[((f >> 5) * slots + slot) * 32 + (f & 31)]
+// so the 32 lanes of a parse warp store 128 contiguous bytes per slot, and a reconstruction block
+// fetches one 32-byte sector per slot for 8 neighbouring frames.
+enum {
+  S_HDR0 = 0, S_HDR1 = 1, S_RANGE = 2, S_STATUS = 3,
+  S_ENERGY = 4,                 // 42 words, index c*21+band
+  S_BANDA = S_ENERGY + 42,      // 21 words
+  S_BANDB = S_BANDA + 21,       // 21 words
+  S_NODES = S_BANDB + 21,       // CAP_NODES words
+  CAP_NODES = 1344,             // 21 bands x (1 stereo split + 2 x (15 splits + 16 leaves)) rounded up
+  CAP_LEAVES = 704,             // 21 bands x 2 x 16 rounded up
+  S_LEAVES = S_NODES + CAP_NODES,  // 3 words per leaf: index, gain bits, packed geometry
+  REC_SLOTS = S_LEAVES + 3 * CAP_LEAVES,
+};
+
+// S_HDR0 fields
+#define MB_H0_LM(h) ((h) & 3u)
+#define MB_H0_C(h) ((((h) >> 2) & 1u) + 1u)
+#define MB_H0_SILENCE(h) (((h) >> 3) & 1u)
+#define MB_H0_TRANSIENT(h) (((h) >> 4) & 1u)
+#define MB_H0_INTRA(h) (((h) >> 5) & 1u)
+#define MB_H0_SPREAD(h) (((h) >> 6) & 3u)
+#define MB_H0_ACON(h) (((h) >> 8) & 1u)
+#define MB_H0_DUAL(h) (((h) >> 9) & 1u)
+#define MB_H0_INTENSITY(h) (((h) >> 10) & 31u)
+#define MB_H0_CODED(h) (((h) >> 15) & 31u)
+#define MB_H0_TAPSET(h) (((h) >> 20) & 3u)
+#define MB_H0_QG1(h) (((h) >> 22) & 15u)   // 0 = post-filter off, else qg+1
+#define MB_H0_START(h) (((h) >> 26) & 31u)
+// S_HDR1 fields
+#define MB_H1_PITCH(h) ((h) & 2047u)
+#define MB_H1_NNODES(h) (((h) >> 11) & 2047u)
+#define MB_H1_NLEAVES(h) (((h) >> 22) & 1023u)
+// S_STATUS: bits 0..7 signed return code (0 ok), 8..12 end band, 13 range-decoder error flag, 14 frame decoded, 15 empty cell
+#define MB_ST_CODE(s) ((int)(int8_t)((s) & 255u))
+#define MB_ST_END(s) (((s) >> 8) & 31u)
+#define MB_ST_DECODED(s) (((s) >> 14) & 1u)
+#define MB_ST_EMPTY(s) (((s) >> 15) & 1u)   // grid cell without a packet
+
+// node stream word: type[0..2] order[3] inv[4] sign[5..6] itheta[7..21]
+enum { ND_LEAF_EMPTY = 0, ND_LEAF_PULSE = 1, ND_SPLIT = 2, ND_STEREO = 3, ND_N1 = 4 };
+#define MB_ND_TYPE(w) ((w) & 7u)
+#define MB_ND_ORDER(w) (((w) >> 3) & 1u)
+#define MB_ND_INV(w) (((w) >> 4) & 1u)
+#define MB_ND_SIGN(w) (((w) >> 5) & 3u)
+#define MB_ND_ITHETA(w) (((w) >> 7) & 32767u)
+// leaf geometry word: x_off[0..10] n[11..18] k[19..26] B[27..31]
+#define MB_LF_XOFF(w) ((w) & 2047u)
+#define MB_LF_N(w) (((w) >> 11) & 255u)
+#define MB_LF_K(w) (((w) >> 19) & 255u)
+#define MB_LF_B(w) (((w) >> 27) & 31u)
+// band word A: in+1[0..10] fold_start[11..15] fold_end[16..20] tf+4[21..23] dual[24] out_valid[25] average[26] has_fold[27]
+#define MB_BA_IN1(w) ((w) & 2047u)
+#define MB_BA_FS(w) (((w) >> 11) & 31u)
+#define MB_BA_FE(w) (((w) >> 16) & 31u)
+#define MB_BA_TF(w) ((int)(((w) >> 21) & 7u) - 4)
+#define MB_BA_DUAL(w) (((w) >> 24) & 1u)
+#define MB_BA_OUT(w) (((w) >> 25) & 1u)
+#define MB_BA_AVG(w) (((w) >> 26) & 1u)
+#define MB_BA_HASFOLD(w) (((w) >> 27) & 1u)
+
+MB_DEV size_t rec_index(uint32_t f, uint32_t slot) { return ((size_t)(f >> 5) * REC_SLOTS + slot) * 32u + (f & 31u); }
+
+// ---- per-frame descriptor produced by the framing kernel (TOC parse; reference src/packet.rs:30-236)
+struct FrameDesc {
+  uint32_t byte_off;   // first payload byte of the frame inside the packet arena
+  uint16_t len;        // payload bytes
+  uint8_t cfg;         // lm[0..1] stream_channels-1[2] mode: 0 celt, 1 silk, 2 hybrid [3..4]
+  uint8_t end_band;    // 13/17/19/21 by bandwidth
+};
+
+// ---- small helpers
+MB_DEV int imin(int a, int b) { return a < b ? a : b; }
+MB_DEV int imax(int a, int b) { return a > b ? a : b; }
+MB_DEV float fmin32(float a, float b) { return a < b ? a : b; }
+MB_DEV float fmax32(float a, float b) { return a > b ? a : b; }
+MB_DEV int ilog32(uint32_t v) {
+#if MB_ON_DEVICE
+  return 32 - __clz((int)v);
+#else
+  return v ? 32 - __builtin_clz(v) : 0;
+#endif
+}
+MB_DEV float bits2f(uint32_t b) {
+#if MB_ON_DEVICE
+  return __uint_as_float(b);
+#else
+  float f; memcpy(&f, &b, 4); return f;
+#endif
+}
+MB_DEV uint32_t f2bits(float f) {
+#if MB_ON_DEVICE
+  return __float_as_uint(f);
+#else
+  uint32_t b; memcpy(&b, &f, 4); return b;
+#endif
+}
+// The reference (Rust) never contracts a*b+c; fused multiply-adds appear only where it calls fmaf
+// (src/celt/kiss_fft.rs:537-542, src/celt/celt.rs:164-166,414-419). Device code is built with
+// -fmad=false and uses this helper at exactly those sites.
+MB_DEV float fma32(float a, float b, float c) {
+#if MB_ON_DEVICE
+  return __fmaf_rn(a, b, c);
+#else
+  return fmaf(a, b, c);
+#endif
+}
+// f64-evaluate-then-round helpers (reference src/celt/math.rs:259-334 via crate libm)
+MB_DEV float celt_exp2(float x) { return (float)exp(0.6931471805599453094 * (double)x); }
+MB_DEV float celt_sqrt(float x) { return (float)sqrt((double)x); }
+MB_DEV float celt_rsqrt(float x) { return 1.0f / celt_sqrt(x); }
+MB_DEV float celt_cos_norm(float x) { return (float)cos((double)(0.5f * 3.14159265358979323846f * x)); }
+MB_DEV int eband(int i) { return kEBands5ms[i]; }
+MB_DEV uint32_t mask_from_bits(int b) { return b <= 0 ? 0u : (b >= 32 ? 0xffffffffu : (1u << b) - 1u); }
+
+}  // namespace mb

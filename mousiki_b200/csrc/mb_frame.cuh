@@ -1,0 +1,48 @@
+// Phase 0/1 entry for one grid cell: Opus TOC + framing, then the CELT entropy parse.
+//
+// Replaces the per-packet front end of the reference:
+//   opus_packet_get_mode / bandwidth / samples_per_frame / nb_channels   src/packet.rs:30-236
+//   opus_packet_parse_impl (code 0 framing)                              src/packet.rs:316-498
+//   decode_native_with / decode_frame argument and mode checks           src/opus_decoder.rs:453-600, 1139-1367
+// Frame kinds that are not built yet are reported per packet as BD_OPUS_UNIMPLEMENTED and leave the
+// stream state untouched: SILK-only and hybrid packets (row A16), packets with more than one frame
+// (codes 1-3, row F1), lost packets / FEC (row F2).
+#pragma once
+#include "mb_celt_parse.cuh"
+
+namespace mb {
+
+// cap_per_ch: PCM capacity per channel of the caller's buffer (the reference's `frame_size`).
+MB_DEV void parse_cell(const uint8_t* arena, const uint32_t* offsets, uint32_t pkt, uint32_t* rec_base, int CC, uint32_t quirks,
+                       int disable_inv, int cap_per_ch, const uint8_t* flags) {
+  if (pkt == 0xffffffffu) { rec_base[S_STATUS * 32] = 1u << 15; return; }
+  const uint32_t off = offsets[pkt];
+  const int len = (int)(offsets[pkt + 1] - off);
+  if (len == 0 && !flags) { rec_base[S_STATUS * 32] = 1u << 15; return; }
+  int code = MB_OK;
+  const uint8_t* data = arena + off;
+  if (len == 0 || (flags && (flags[pkt] & 3u))) code = MB_UNIMPLEMENTED;  // concealment / FEC (row F2)
+  uint32_t toc = 0;
+  if (code == MB_OK) {
+    toc = data[0];
+    if (!(toc & 0x80u)) code = MB_UNIMPLEMENTED;        // SILK-only / hybrid (row A16)
+    else if (toc & 3u) code = MB_UNIMPLEMENTED;         // multi-frame packets (row F1)
+  }
+  if (code == MB_OK) {
+    const int lm = (int)((toc >> 3) & 3u);
+    const int N = SHORT_MDCT << lm;
+    if (N > cap_per_ch) code = MB_BUFFER_TOO_SMALL;     // src/opus_decoder.rs:1318-1320
+    else if (len - 1 <= 1) code = MB_UNIMPLEMENTED;     // a <=1-byte frame is concealment (src/opus_decoder.rs:491)
+    else {
+      const int bw = (int)((toc >> 5) & 3u);
+      const int end = bw == 0 ? 13 : bw == 1 ? 17 : bw == 2 ? 19 : 21;
+      const int C = (toc & 4u) ? 2 : 1;
+      celt_parse_frame(data + 1, len - 1, lm, C, 0, end, quirks, disable_inv, rec_base);
+      (void)CC;
+      return;
+    }
+  }
+  rec_base[S_STATUS * 32] = (uint32_t)(uint8_t)(int8_t)code;
+}
+
+}  // namespace mb

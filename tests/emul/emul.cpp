@@ -1,0 +1,72 @@
+// TEST INFRASTRUCTURE ONLY. Single-threaded host build of the kernel bodies in
+// mousiki_b200/csrc/mb_*.cuh (compiled with -DMB_EMUL, team size 1) so that the CPU test-suite can
+// check the product's algorithmic logic against the oracle where no GPU exists. Nothing in the
+// product library links or calls this file; GPU parity proper is tests/test_gpu_parity.py.
+#define MB_EMUL 1
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <vector>
+
+#include "../../mousiki_b200/csrc/mb_celt_recon.cuh"
+#include "../../mousiki_b200/csrc/mb_celt_tail.cuh"
+#include "../../mousiki_b200/csrc/mb_frame.cuh"
+
+using namespace mb;
+
+extern "C" {
+
+// Decodes a regular [n_ticks][n_lanes] packet grid with one fresh decoder state per lane, phases in
+// the same order as the CUDA launcher. pcm: [packet][pcm_stride]. iy_dbg/x_dbg: optional [packet][2*960].
+int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_t* offsets, uint32_t n_lanes, uint32_t n_ticks,
+                    uint32_t pcm_stride, float* pcm, int16_t* pcm16, int32_t* samples_out, uint32_t* final_range_out, int32_t* iy_dbg,
+                    float* x_dbg) {
+  const uint32_t F = n_lanes * n_ticks;
+  const size_t tiles = (F + 31) / 32;
+  std::vector<uint32_t> rec(tiles * REC_SLOTS * 32, 0);
+  std::vector<StreamState> st(n_lanes);
+  for (auto& s : st) stream_state_reset(s);
+  std::vector<float> hist((size_t)n_lanes * CC * HIST, 0.f);
+  std::vector<float> en((size_t)F * EN_STRIDE, 0.f);
+  std::vector<FrameMeta> meta(F);
+  const uint32_t series_stride = HIST + n_ticks * MAX_N;
+  std::vector<float> series((size_t)n_lanes * CC * series_stride, 0.f);
+  const int disable_inv = CC == 1;
+  // phase 1
+  for (uint32_t f = 0; f < F; f++)
+    parse_cell(arena, offsets, f, rec.data() + rec_index(f, 0), CC, quirks, disable_inv, (int)(pcm_stride / CC), nullptr);
+  // phase 2a
+  for (uint32_t j = 0; j < n_lanes; j++)
+    celt_energy_lane(j, n_lanes, n_ticks, nullptr, rec.data(), st.data(), nullptr, en.data(), meta.data(), samples_out, final_range_out, quirks);
+  // phase 2b
+  ReconSmem* sm = new ReconSmem;
+  ReconParams rp;
+  rp.rec = rec.data(); rp.en = en.data(); rp.meta = meta.data(); rp.series = series.data(); rp.series_stride = series_stride;
+  rp.CC = CC; rp.quirks = quirks; rp.iy_dbg = iy_dbg; rp.x_dbg = x_dbg;
+  Team tm = {0, 1};
+  for (uint32_t f = 0; f < F; f++) celt_recon_frame(tm, sm, f, rp);
+  delete sm;
+  // phase 2c
+  std::vector<float> tmp;
+  float* out = pcm;
+  if (!out) { tmp.assign((size_t)F * pcm_stride, 0.f); out = tmp.data(); }
+  TailParams tp;
+  tp.rec = rec.data(); tp.meta = meta.data(); tp.pkt_map = nullptr; tp.lane_stream = nullptr; tp.st_all = st.data(); tp.hist = hist.data();
+  tp.series = series.data(); tp.series_stride = series_stride; tp.n_lanes = n_lanes; tp.n_ticks = n_ticks; tp.CC = CC;
+  tp.gain = 1.f; tp.apply_gain = 0; tp.pcm_f32 = out; tp.pcm_stride = pcm_stride;
+  for (uint32_t j = 0; j < n_lanes; j++)
+    for (int c = 0; c < CC; c++) celt_tail_lane(j, c, tp);
+  if (pcm16) {
+    for (uint32_t j = 0; j < n_lanes; j++)
+      for (uint32_t t = 0; t < n_ticks; t++) {
+        uint32_t p = t * n_lanes + j;
+        if (samples_out[p] <= 0) continue;
+        soft_clip_packet(out + (size_t)p * pcm_stride, samples_out[p], CC, st[j].softclip_mem);
+        for (int i = 0; i < samples_out[p] * CC; i++) pcm16[(size_t)p * pcm_stride + i] = float2int16(out[(size_t)p * pcm_stride + i]);
+      }
+  }
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,113 @@
+"""Shared test helpers: seeded packet corpora, ctypes bindings for the oracle (CPU restatement of the
+reference, the checker) and for the host emulation of the kernel bodies (CPU tests only)."""
+import ctypes as C
+import os
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent.parent
+QUIRKS_MOUSIKI = 0x7F
+
+
+def _make(dirpath: Path, target: str) -> Path:
+    subprocess.run(["make", "-C", str(dirpath), target], check=True, stdout=subprocess.DEVNULL)
+    return dirpath / target
+
+
+_ORACLE = None
+_EMUL = None
+
+
+def oracle_lib():
+    global _ORACLE
+    if _ORACLE is None:
+        lib = C.CDLL(str(_make(ROOT / "oracle", "_build/liboracle.so")))
+        lib.orc_create.restype = C.c_void_p
+        lib.orc_create.argtypes = [C.c_int, C.c_int, C.c_uint32]
+        lib.orc_destroy.argtypes = [C.c_void_p]
+        lib.orc_reset.argtypes = [C.c_void_p]
+        lib.orc_set_gain.argtypes = [C.c_void_p, C.c_int]
+        lib.orc_final_range.restype = C.c_uint32
+        lib.orc_final_range.argtypes = [C.c_void_p]
+        lib.orc_decode_float.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int]
+        lib.orc_decode_i16.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int]
+        lib.orc_trace_enable.argtypes = [C.c_void_p, C.c_int]
+        lib.orc_trace_info.argtypes = [C.c_void_p, C.c_void_p]
+        lib.orc_trace_get.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        lib.orc_decode_grid.argtypes = [C.c_int, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        _ORACLE = lib
+    return _ORACLE
+
+
+def emul_lib():
+    global _EMUL
+    if _EMUL is None:
+        lib = C.CDLL(str(_make(ROOT / "tests" / "emul", "_build/libemul.so")))
+        lib.emu_decode_grid.argtypes = [C.c_int, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
+                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        _EMUL = lib
+    return _EMUL
+
+
+def ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def lcg_bytes(seed: int, n: int) -> np.ndarray:
+    """Deterministic byte stream (numpy PCG is fine: the generator only has to be seeded and committed)."""
+    return np.random.default_rng(seed).integers(0, 256, size=n, dtype=np.uint8)
+
+
+def celt_toc(lm: int, stereo: bool, bandwidth: int = 3) -> int:
+    """CELT-only TOC, code 0: config = 16 + 4*bandwidth(0 NB,1 WB,2 SWB,3 FB) + lm."""
+    return ((16 + 4 * bandwidth + lm) << 3) | (4 if stereo else 0)
+
+
+def fuzz_grid(n_lanes: int, n_ticks: int, payload: int, toc_fn, seed: int = 1):
+    """[n_ticks][n_lanes] grid of `TOC || random bytes` packets (the construction of the reference's own
+    decode fuzz, tests/test_opus_decode.rs:372-407). toc_fn(t, j, rng) -> TOC byte; payload may be an int or
+    a (lo, hi) range. Returns (arena uint8, offsets uint32[n+1])."""
+    rng = np.random.default_rng(seed)
+    n = n_lanes * n_ticks
+    if isinstance(payload, tuple):
+        lens = rng.integers(payload[0], payload[1] + 1, size=n)
+    else:
+        lens = np.full(n, payload)
+    offsets = np.zeros(n + 1, dtype=np.uint32)
+    offsets[1:] = np.cumsum(lens + 1)
+    arena = rng.integers(0, 256, size=int(offsets[-1]), dtype=np.uint8)
+    for t in range(n_ticks):
+        for j in range(n_lanes):
+            p = t * n_lanes + j
+            arena[offsets[p]] = toc_fn(t, j, rng)
+    return arena, offsets
+
+
+def oracle_decode_grid(arena, offsets, n_lanes, n_ticks, channels, frame_size, i16=False, quirks=QUIRKS_MOUSIKI, threads=None):
+    lib = oracle_lib()
+    n = n_lanes * n_ticks
+    pcm = np.zeros((n, frame_size * channels), dtype=np.int16 if i16 else np.float32)
+    samples = np.zeros(n, dtype=np.int32)
+    rng = np.zeros(n, dtype=np.uint32)
+    lib.orc_decode_grid(48000, channels, quirks, ptr(arena), ptr(offsets), n_lanes, n_ticks, frame_size,
+                        None if i16 else ptr(pcm), ptr(pcm) if i16 else None, ptr(samples), ptr(rng),
+                        threads or os.cpu_count() or 1)
+    return pcm, samples, rng
+
+
+def emul_decode_grid(arena, offsets, n_lanes, n_ticks, channels, frame_size, i16=False, quirks=QUIRKS_MOUSIKI, debug=False):
+    lib = emul_lib()
+    n = n_lanes * n_ticks
+    stride = frame_size * channels
+    pcm = np.zeros((n, stride), dtype=np.float32)
+    pcm16 = np.zeros((n, stride), dtype=np.int16) if i16 else None
+    samples = np.zeros(n, dtype=np.int32)
+    rng = np.zeros(n, dtype=np.uint32)
+    iy = np.zeros((n, 2, 960), dtype=np.int32) if debug else None
+    xs = np.zeros((n, 2, 960), dtype=np.float32) if debug else None
+    lib.emu_decode_grid(channels, quirks, ptr(arena), ptr(offsets), n_lanes, n_ticks, stride, ptr(pcm), ptr(pcm16), ptr(samples),
+                        ptr(rng), ptr(iy), ptr(xs))
+    return (pcm16 if i16 else pcm), samples, rng, iy, xs

@@ -72,6 +72,35 @@ def emit_int(ctype, name, vals, per=16):
     return "\n".join(out)
 
 
+def derived_tables():
+    """PVQ codebook sizes U(n,k) (recurrence of src/celt/cwrs_pvq.rs:19-52, rows 0..14 packed) and
+    LCG jump-ahead coefficients for celt_lcg_rand (seed_j = A_j*seed + C_j mod 2^32)."""
+    row_len = [209, 208, 207, 206, 205, 204, 104, 54, 33, 21, 15, 10, 7, 4, 1]
+    t = [[0] * 209 for _ in range(15)]
+    t[0][0] = 1
+    for n in range(1, 15):
+        for k in range(1, 209):
+            t[n][k] = min(t[n - 1][k] + t[n][k - 1] + t[n - 1][k - 1], (1 << 64) - 1)
+    u = []
+    for row in range(15):
+        for col in range(row, row + row_len[row]):
+            u.append(t[row][col] & 0xFFFFFFFF)
+    assert len(u) == 1488
+    a, c = 1, 0
+    la, lc = [], []
+    for _ in range(257):
+        la.append(a); lc.append(c)
+        a, c = (a * 1664525) & 0xFFFFFFFF, (c * 1664525 + 1013904223) & 0xFFFFFFFF
+    def emit(name, vals, per=6):
+        out = [f"MB_TBL uint32_t {name}[{len(vals)}] = {{"]
+        for i in range(0, len(vals), per):
+            out.append("  " + ", ".join(f"0x{v:08x}u" for v in vals[i : i + per]) + ",")
+        out.append("};")
+        return "\n".join(out)
+    return ["// derived: U(n,k) rows 0..14 (cwrs_pvq.rs recurrence)", emit("kPvqU", u),
+            "// derived: LCG jump-ahead, seed after j steps = kLcgA[j]*seed + kLcgC[j]", emit("kLcgA", la), emit("kLcgC", lc)]
+
+
 def main():
     window = parse_floats(REF / "window_48000_960.rs")
     mdct_tw = parse_floats(REF / "mdct_twiddles_48000_960.rs")
@@ -126,10 +155,14 @@ def main():
         "",
     ]
     text = "\n".join(hdr)
-    for out in (ROOT / "oracle" / "celt_tables_data.h", ROOT / "mousiki_b200" / "csrc" / "celt_tables_data.h"):
+    # Product copy: same data behind the MB_TBL qualifier (device-resident arrays when compiled by
+    # nvcc, plain host arrays in the CPU emulation build) plus two derived, reference-free tables.
+    prod = text.replace("static const", "MB_TBL").replace("#include <stdint.h>", "#include <stdint.h>\n#ifndef MB_TBL\n#define MB_TBL static const\n#endif")
+    prod += "\n".join(derived_tables()) + "\n"
+    for out, t in ((ROOT / "oracle" / "celt_tables_data.h", text), (ROOT / "mousiki_b200" / "csrc" / "celt_tables_data.h", prod)):
         out.parent.mkdir(parents=True, exist_ok=True)
-        out.write_text(text)
-        print("wrote", out, len(text), "bytes")
+        out.write_text(t)
+        print("wrote", out, len(t), "bytes")
 
 
 if __name__ == "__main__":
