@@ -1,0 +1,432 @@
+// mousiki_b200 — CUDA kernels (sm_100a) and the C ABI declared in include/mousiki_b200.h.
+//
+// Launch sequence of one decode pass over a [ticks x lanes] grid of packets:
+//   k_parse    lane per packet          phase 1  (mb_frame.cuh / mb_celt_parse.cuh)
+//   k_energy   lane per stream          phase 2a (mb_celt_energy.cuh)
+//   k_recon    CTA per frame            phase 2b (mb_celt_recon.cuh)
+//   k_tail     lane per stream-channel  phase 2c (mb_celt_tail.cuh)
+//   k_softclip / k_to_i16               i16 output path only
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo (see __graft_entry__.build()).
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/mousiki_b200.h"
+#include "mb_celt_recon.cuh"
+#include "mb_celt_tail.cuh"
+#include "mb_frame.cuh"
+
+using namespace mb;
+
+// ------------------------------------------------------------------------------------------ kernels
+__global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ arena, const uint32_t* __restrict__ offsets,
+                                               const uint32_t* __restrict__ pkt_map, uint32_t n_cells, uint32_t* __restrict__ rec, int CC,
+                                               uint32_t quirks, int disable_inv, int cap_per_ch, const uint8_t* __restrict__ flags) {
+  uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= n_cells) return;
+  uint32_t pkt = pkt_map ? pkt_map[f] : f;
+  parse_cell(arena, offsets, pkt, rec + rec_index(f, 0), CC, quirks, disable_inv, cap_per_ch, flags);
+}
+
+__global__ void __launch_bounds__(64) k_energy(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
+                                               const uint32_t* __restrict__ rec, StreamState* st, const uint32_t* __restrict__ lane_stream,
+                                               float* __restrict__ en, FrameMeta* __restrict__ meta, int32_t* __restrict__ samples_out,
+                                               uint32_t* __restrict__ final_range_out, uint32_t quirks) {
+  uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
+  if (lane >= n_lanes) return;
+  celt_energy_lane(lane, n_lanes, n_ticks, pkt_map, rec, st, lane_stream, en, meta, samples_out, final_range_out, quirks);
+}
+
+constexpr int RECON_THREADS = 64;
+__global__ void __launch_bounds__(RECON_THREADS) k_recon(ReconParams P, uint32_t n_cells) {
+  __shared__ ReconSmem sm;
+  Team tm = {(int)threadIdx.x, (int)blockDim.x};
+  celt_recon_frame(tm, &sm, blockIdx.x, P);
+}
+
+__global__ void __launch_bounds__(64) k_tail(TailParams P) {
+  uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t lane = idx / (uint32_t)P.CC;
+  int c = (int)(idx - lane * (uint32_t)P.CC);
+  if (lane >= P.n_lanes) return;
+  celt_tail_lane(lane, c, P);
+}
+
+// opus_decode's soft clip (src/opus.rs:16-140): one lane per stream, its packets in tick order.
+__global__ void __launch_bounds__(64) k_softclip(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
+                                                 const uint32_t* __restrict__ lane_stream, const FrameMeta* __restrict__ meta,
+                                                 const int32_t* __restrict__ samples_out, StreamState* st, float* pcm, uint32_t pcm_stride,
+                                                 int CC) {
+  uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
+  if (lane >= n_lanes) return;
+  StreamState& s = st[lane_stream ? lane_stream[lane] : lane];
+  for (uint32_t t = 0; t < n_ticks; t++) {
+    uint32_t f = t * n_lanes + lane;
+    if (!(meta[f].flags & 1u)) continue;
+    uint32_t p = pkt_map ? pkt_map[f] : f;
+    int n = samples_out[p];
+    if (n <= 0) continue;
+    soft_clip_packet(pcm + (size_t)p * pcm_stride, n, CC, s.softclip_mem);
+  }
+}
+// decode_float leaves the clipper memory cleared (src/opus_decoder.rs:1411-1417)
+__global__ void k_clear_softclip(uint32_t n_lanes, const uint32_t* __restrict__ lane_stream, StreamState* st) {
+  uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
+  if (lane >= n_lanes) return;
+  StreamState& s = st[lane_stream ? lane_stream[lane] : lane];
+  s.softclip_mem[0] = s.softclip_mem[1] = 0.f;
+}
+__global__ void k_to_i16(const float* __restrict__ in, int16_t* __restrict__ out, const int32_t* __restrict__ samples_out,
+                         uint32_t n_packets, uint32_t pcm_stride, int CC) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t total = (size_t)n_packets * pcm_stride;
+  if (i >= total) return;
+  uint32_t p = (uint32_t)(i / pcm_stride), k = (uint32_t)(i - (size_t)p * pcm_stride);
+  int n = samples_out[p];
+  if (n > 0 && k < (uint32_t)(n * CC)) out[i] = float2int16(in[i]);
+}
+__global__ void k_reset(StreamState* st, float* hist, const uint32_t* __restrict__ ids, uint32_t n, int CC) {
+  uint32_t i = blockIdx.x;
+  if (i >= n) return;
+  uint32_t sid = ids ? ids[i] : i;
+  if (threadIdx.x == 0) stream_state_reset(st[sid]);
+  float* h = hist + (size_t)sid * CC * HIST;
+  for (int k = threadIdx.x; k < CC * HIST; k += blockDim.x) h[k] = 0.f;
+}
+
+// ------------------------------------------------------------------------------------------ host side
+namespace {
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <class T> T* as() { return (T*)p; }
+};
+
+}  // namespace
+
+struct bd_handle {
+  bd_config cfg;
+  int device = 0;
+  int CC = 2;
+  int disable_inv = 0;
+  float gain = 1.f;
+  uint32_t max_frames_per_pass = 0;
+  std::string err;
+  uint32_t launches = 0;
+  cudaStream_t own_stream = nullptr;
+  DevBuf states, hist, rec, en, meta, series;
+  // staging for the host-buffer entry points
+  DevBuf d_arena, d_offsets, d_pkt_map, d_lane_stream, d_flags, d_pcm, d_pcm16, d_samples, d_range, d_ids, d_dbg_iy, d_dbg_x;
+  std::vector<uint32_t> h_pkt_map, h_lane_stream, h_lane_of_stream, h_epoch, h_count;
+  uint32_t epoch = 0;
+  int32_t* dbg_iy_host = nullptr;
+  float* dbg_x_host = nullptr;
+  uint32_t dbg_max = 0;
+};
+
+#define CK(call)                                                                          \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess) {                                                              \
+      h->err = std::string(#call) + ": " + cudaGetErrorString(e_);                       \
+      return e_ == cudaErrorMemoryAllocation ? BD_ERR_ALLOC : BD_ERR_CUDA;                \
+    }                                                                                     \
+  } while (0)
+
+extern "C" {
+
+const char* bd_last_error(const bd_handle* h) { return h ? h->err.c_str() : "null handle"; }
+uint32_t bd_last_launch_count(const bd_handle* h) { return h ? h->launches : 0; }
+
+void* bd_alloc_pinned(uint64_t bytes) {
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, (size_t)bytes, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+  return p;
+}
+void bd_free_pinned(void* p) { if (p) cudaFreeHost(p); }
+
+int bd_create(const bd_config* cfg, bd_handle** out) {
+  if (!cfg || !out) return BD_ERR_BAD_ARG;
+  *out = nullptr;
+  if (cfg->struct_size != sizeof(bd_config)) return BD_ERR_BAD_ARG;
+  if (cfg->channels != 1 && cfg->channels != 2) return BD_ERR_BAD_ARG;
+  const int fs = cfg->sample_rate_hz;
+  if (!(fs == 48000 || fs == 24000 || fs == 16000 || fs == 12000 || fs == 8000)) return BD_ERR_BAD_ARG;
+  if (fs != 48000) return BD_ERR_UNIMPLEMENTED;                                   // row F4
+  if ((cfg->quirks & Q2_MDCT_ZERO_FILL) == 0) return BD_ERR_UNIMPLEMENTED;        // libopus overlap-add variant not built
+  if (cfg->n_streams == 0) return BD_ERR_BAD_ARG;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) return BD_ERR_CUDA;
+  bd_handle* h = new (std::nothrow) bd_handle();
+  if (!h) return BD_ERR_ALLOC;
+  h->cfg = *cfg;
+  h->device = cfg->device;
+  h->CC = cfg->channels;
+  h->disable_inv = cfg->disable_phase_inversion < 0 ? (cfg->channels == 1) : (cfg->disable_phase_inversion != 0);
+  h->gain = cfg->gain_q8 == 0 ? 1.f : (float)exp(0.6931471805599453094 * (double)((3.32192809488736234787f / 5120.0f) * (float)cfg->gain_q8));
+  h->max_frames_per_pass = cfg->max_frames_per_pass ? cfg->max_frames_per_pass : (1u << 18);
+  const char* env = getenv("MOUSIKI_B200_MAX_FRAMES_PER_PASS");
+  if (env && atoi(env) > 0) h->max_frames_per_pass = (uint32_t)atoi(env);
+  auto fail = [&](int code) { bd_destroy(h); return code; };
+  if (cudaSetDevice(h->device) != cudaSuccess) return fail(BD_ERR_CUDA);
+  if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) return fail(BD_ERR_CUDA);
+  if (h->states.ensure((size_t)cfg->n_streams * sizeof(StreamState)) != cudaSuccess) return fail(BD_ERR_ALLOC);
+  if (h->hist.ensure((size_t)cfg->n_streams * h->CC * HIST * sizeof(float)) != cudaSuccess) return fail(BD_ERR_ALLOC);
+  k_reset<<<cfg->n_streams, 128, 0, h->own_stream>>>(h->states.as<StreamState>(), h->hist.as<float>(), nullptr, cfg->n_streams, h->CC);
+  if (cudaStreamSynchronize(h->own_stream) != cudaSuccess || cudaGetLastError() != cudaSuccess) return fail(BD_ERR_CUDA);
+  *out = h;
+  return BD_OK;
+}
+
+void bd_destroy(bd_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  DevBuf* all[] = {&h->states, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->d_arena, &h->d_offsets, &h->d_pkt_map,
+                   &h->d_lane_stream, &h->d_flags, &h->d_pcm, &h->d_pcm16, &h->d_samples, &h->d_range, &h->d_ids, &h->d_dbg_iy, &h->d_dbg_x};
+  for (DevBuf* b : all) b->release();
+  if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  delete h;
+}
+
+int bd_reset_streams(bd_handle* h, const uint32_t* ids, uint32_t n) {
+  if (!h) return BD_ERR_BAD_ARG;
+  CK(cudaSetDevice(h->device));
+  const uint32_t* d_ids = nullptr;
+  if (ids) {
+    for (uint32_t i = 0; i < n; i++)
+      if (ids[i] >= h->cfg.n_streams) return BD_ERR_BAD_ARG;
+    CK(h->d_ids.ensure((size_t)n * 4));
+    CK(cudaMemcpyAsync(h->d_ids.p, ids, (size_t)n * 4, cudaMemcpyHostToDevice, h->own_stream));
+    d_ids = h->d_ids.as<uint32_t>();
+  } else n = h->cfg.n_streams;
+  if (n == 0) return BD_OK;
+  k_reset<<<n, 128, 0, h->own_stream>>>(h->states.as<StreamState>(), h->hist.as<float>(), d_ids, n, h->CC);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(h->own_stream));
+  return BD_OK;
+}
+
+int bd_get_stream_info(bd_handle* h, uint32_t sid, bd_stream_info* out) {
+  if (!h || !out || sid >= h->cfg.n_streams) return BD_ERR_BAD_ARG;
+  CK(cudaSetDevice(h->device));
+  StreamState s;
+  CK(cudaMemcpy(&s, h->states.as<StreamState>() + sid, sizeof(s), cudaMemcpyDeviceToHost));
+  out->final_range = s.range_final; out->last_packet_duration = s.last_packet_duration; out->prev_mode = s.prev_mode;
+  out->celt_error = s.celt_error;
+  return BD_OK;
+}
+
+int bd_debug_capture(bd_handle* h, int32_t* pulses_host, float* spectrum_host, uint32_t max_packets) {
+  if (!h) return BD_ERR_BAD_ARG;
+  h->dbg_iy_host = pulses_host; h->dbg_x_host = spectrum_host; h->dbg_max = (pulses_host || spectrum_host) ? max_packets : 0;
+  return BD_OK;
+}
+
+// One or more passes over the grid (ticks are split so that a pass holds at most max_frames_per_pass cells).
+// All pointers are device pointers. pkt_map == nullptr: cell f is packet f.
+static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32_t* d_offsets, const uint32_t* d_pkt_map,
+                              const uint8_t* d_flags, uint32_t n_lanes, uint32_t n_ticks, const uint32_t* d_lane_stream, float* d_pcm_f32,
+                              int16_t* d_pcm_i16, uint32_t pcm_stride, int32_t* d_samples, uint32_t* d_range, uint32_t n_packets,
+                              cudaStream_t s, int32_t* d_dbg_iy, float* d_dbg_x) {
+  if (n_lanes == 0 || n_ticks == 0) return BD_OK;
+  const int CC = h->CC;
+  if (pcm_stride < (uint32_t)(SHORT_MDCT * CC)) return BD_ERR_BAD_ARG;
+  if ((uint64_t)n_lanes > h->max_frames_per_pass) return BD_ERR_BAD_ARG;  // caller splits lanes (lanes are independent)
+  uint32_t ticks_per_pass = h->max_frames_per_pass / n_lanes;
+  if (ticks_per_pass > n_ticks) ticks_per_pass = n_ticks;
+  const uint32_t cells_max = ticks_per_pass * n_lanes;
+  const uint32_t series_stride = HIST + ticks_per_pass * MAX_N;
+  CK(h->rec.ensure((size_t)((cells_max + 31) / 32) * REC_SLOTS * 32 * sizeof(uint32_t)));
+  CK(h->en.ensure((size_t)cells_max * EN_STRIDE * sizeof(float)));
+  CK(h->meta.ensure((size_t)cells_max * sizeof(FrameMeta)));
+  CK(h->series.ensure((size_t)n_lanes * CC * series_stride * sizeof(float)));
+  float* pcm_f32 = d_pcm_f32;
+  if (d_pcm_i16) {  // the i16 path decodes to a float scratch, soft-clips, then rounds (src/opus_decoder.rs:1679-1712)
+    CK(h->d_pcm.ensure((size_t)n_packets * pcm_stride * sizeof(float)));
+    pcm_f32 = h->d_pcm.as<float>();
+  }
+  const int cap_per_ch = (int)(pcm_stride / (uint32_t)CC);
+  for (uint32_t t0 = 0; t0 < n_ticks; t0 += ticks_per_pass) {
+    const uint32_t nt = (n_ticks - t0 < ticks_per_pass) ? n_ticks - t0 : ticks_per_pass;
+    const uint32_t cells = nt * n_lanes;
+    const size_t cell0 = (size_t)t0 * n_lanes;
+    // identity mapping: shift the per-packet arrays so that cell index == local packet index
+    const uint32_t* map = d_pkt_map ? d_pkt_map + cell0 : nullptr;
+    const size_t shift = d_pkt_map ? 0 : cell0;
+    const uint32_t* offs = d_offsets + shift;
+    const uint8_t* flg = d_flags ? d_flags + shift : nullptr;
+    int32_t* samples = d_samples + shift;
+    uint32_t* range = d_range + shift;
+    float* pcm = pcm_f32 ? pcm_f32 + shift * pcm_stride : nullptr;
+    k_parse<<<(cells + 127) / 128, 128, 0, s>>>(d_arena, offs, map, cells, h->rec.as<uint32_t>(), CC, h->cfg.quirks, h->disable_inv,
+                                                cap_per_ch, flg);
+    k_energy<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, nt, map, h->rec.as<uint32_t>(), h->states.as<StreamState>(), d_lane_stream,
+                                                h->en.as<float>(), h->meta.as<FrameMeta>(), samples, range, h->cfg.quirks);
+    ReconParams rp;
+    rp.rec = h->rec.as<uint32_t>(); rp.en = h->en.as<float>(); rp.meta = h->meta.as<FrameMeta>(); rp.series = h->series.as<float>();
+    rp.series_stride = series_stride; rp.CC = CC; rp.quirks = h->cfg.quirks;
+    rp.iy_dbg = d_dbg_iy ? d_dbg_iy + cell0 * 2 * MAX_N : nullptr;
+    rp.x_dbg = d_dbg_x ? d_dbg_x + cell0 * 2 * MAX_N : nullptr;
+    k_recon<<<cells, RECON_THREADS, 0, s>>>(rp, cells);
+    TailParams tp;
+    tp.rec = h->rec.as<uint32_t>(); tp.meta = h->meta.as<FrameMeta>(); tp.pkt_map = map; tp.lane_stream = d_lane_stream;
+    tp.st_all = h->states.as<StreamState>(); tp.hist = h->hist.as<float>(); tp.series = h->series.as<float>();
+    tp.series_stride = series_stride; tp.n_lanes = n_lanes; tp.n_ticks = nt; tp.CC = CC; tp.gain = h->gain;
+    tp.apply_gain = h->cfg.gain_q8 != 0; tp.pcm_f32 = pcm; tp.pcm_stride = pcm_stride;
+    k_tail<<<(n_lanes * CC + 63) / 64, 64, 0, s>>>(tp);
+    h->launches += 4;
+    if (d_pcm_i16) {
+      k_softclip<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, nt, map, d_lane_stream, h->meta.as<FrameMeta>(), samples,
+                                                    h->states.as<StreamState>(), pcm, pcm_stride, CC);
+      h->launches += 1;
+    } else {
+      k_clear_softclip<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, d_lane_stream, h->states.as<StreamState>());
+      h->launches += 1;
+    }
+  }
+  if (d_pcm_i16) {
+    size_t total = (size_t)n_packets * pcm_stride;
+    k_to_i16<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(pcm_f32, d_pcm_i16, d_samples, n_packets, pcm_stride, CC);
+    h->launches += 1;
+  }
+  CK(cudaGetLastError());
+  return BD_OK;
+}
+
+int bd_decode_grid_dev(bd_handle* h, const uint8_t* d_arena, const uint32_t* d_offsets, uint32_t n_lanes, uint32_t n_ticks,
+                       const uint32_t* d_lane_stream, float* d_pcm_f32, int16_t* d_pcm_i16, uint32_t pcm_stride, int32_t* d_samples_out,
+                       uint32_t* d_final_range_out, void* cuda_stream) {
+  if (!h || !d_arena || !d_offsets || !d_samples_out || !d_final_range_out) return BD_ERR_BAD_ARG;
+  if (d_pcm_f32 && d_pcm_i16) return BD_ERR_BAD_ARG;
+  if (!d_lane_stream && n_lanes > h->cfg.n_streams) return BD_ERR_BAD_ARG;
+  CK(cudaSetDevice(h->device));
+  h->launches = 0;
+  return decode_grid_device(h, d_arena, d_offsets, nullptr, nullptr, n_lanes, n_ticks, d_lane_stream, d_pcm_f32, d_pcm_i16, pcm_stride,
+                            d_samples_out, d_final_range_out, n_lanes * n_ticks, (cudaStream_t)cuda_stream, nullptr, nullptr);
+}
+
+static int decode_host(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
+                       const uint8_t* flags, float* pcm_f32, int16_t* pcm_i16, uint32_t pcm_stride, int32_t* samples_out,
+                       uint32_t* final_range_out) {
+  if (!h || !arena || !offsets || !stream_ids || !samples_out || !final_range_out || (!pcm_f32 && !pcm_i16)) return BD_ERR_BAD_ARG;
+  if (n_packets == 0) return BD_OK;
+  CK(cudaSetDevice(h->device));
+  h->launches = 0;
+  cudaStream_t s = h->own_stream;
+  const uint32_t S = h->cfg.n_streams;
+  // ---- schedule: lane = order of first appearance of a stream in this call, tick = occurrence number
+  if (h->h_epoch.size() != S) { h->h_epoch.assign(S, 0); h->h_lane_of_stream.assign(S, 0); h->h_count.assign(S, 0); h->epoch = 0; }
+  h->epoch++;
+  if (h->epoch == 0) { std::fill(h->h_epoch.begin(), h->h_epoch.end(), 0u); h->epoch = 1; }
+  h->h_lane_stream.clear();
+  uint32_t n_ticks = 0;
+  for (uint32_t p = 0; p < n_packets; p++) {
+    uint32_t sid = stream_ids[p];
+    if (sid >= S) return BD_ERR_BAD_ARG;
+    if (h->h_epoch[sid] != h->epoch) {
+      h->h_epoch[sid] = h->epoch; h->h_count[sid] = 0;
+      h->h_lane_of_stream[sid] = (uint32_t)h->h_lane_stream.size();
+      h->h_lane_stream.push_back(sid);
+    }
+    if (++h->h_count[sid] > n_ticks) n_ticks = h->h_count[sid];
+  }
+  const uint32_t n_lanes = (uint32_t)h->h_lane_stream.size();
+  const bool identity = n_ticks == 1;  // every stream at most once: cell == packet
+  const uint32_t* d_map = nullptr;
+  if (!identity) {
+    h->h_pkt_map.assign((size_t)n_lanes * n_ticks, 0xffffffffu);
+    for (uint32_t sid : h->h_lane_stream) h->h_count[sid] = 0;
+    for (uint32_t p = 0; p < n_packets; p++) {
+      uint32_t sid = stream_ids[p];
+      uint32_t t = h->h_count[sid]++;
+      h->h_pkt_map[(size_t)t * n_lanes + h->h_lane_of_stream[sid]] = p;
+    }
+    CK(h->d_pkt_map.ensure(h->h_pkt_map.size() * 4));
+    CK(cudaMemcpyAsync(h->d_pkt_map.p, h->h_pkt_map.data(), h->h_pkt_map.size() * 4, cudaMemcpyHostToDevice, s));
+    d_map = h->d_pkt_map.as<uint32_t>();
+  }
+  const size_t arena_bytes = offsets[n_packets];
+  CK(h->d_arena.ensure(arena_bytes + 16));
+  CK(h->d_offsets.ensure((size_t)(n_packets + 1) * 4));
+  CK(h->d_lane_stream.ensure((size_t)n_lanes * 4));
+  CK(h->d_samples.ensure((size_t)n_packets * 4));
+  CK(h->d_range.ensure((size_t)n_packets * 4));
+  CK(cudaMemcpyAsync(h->d_arena.p, arena, arena_bytes, cudaMemcpyHostToDevice, s));
+  CK(cudaMemcpyAsync(h->d_offsets.p, offsets, (size_t)(n_packets + 1) * 4, cudaMemcpyHostToDevice, s));
+  CK(cudaMemcpyAsync(h->d_lane_stream.p, h->h_lane_stream.data(), (size_t)n_lanes * 4, cudaMemcpyHostToDevice, s));
+  const uint8_t* d_flags = nullptr;
+  // an all-ones flag array is still needed in identity mode to tell "lost packet" from "empty cell"
+  std::vector<uint8_t> zero_flags;
+  if (!flags) { zero_flags.assign(n_packets, 0); flags = zero_flags.data(); }
+  CK(h->d_flags.ensure(n_packets));
+  CK(cudaMemcpyAsync(h->d_flags.p, flags, n_packets, cudaMemcpyHostToDevice, s));
+  d_flags = h->d_flags.as<uint8_t>();
+  const size_t pcm_elems = (size_t)n_packets * pcm_stride;
+  float* d_f32 = nullptr;
+  int16_t* d_i16 = nullptr;
+  if (pcm_f32) {
+    // the float output reuses d_pcm; the i16 path uses d_pcm as its float scratch and d_pcm16 as the result
+    CK(h->d_pcm.ensure(pcm_elems * sizeof(float)));
+    d_f32 = h->d_pcm.as<float>();
+  } else {
+    CK(h->d_pcm16.ensure(pcm_elems * sizeof(int16_t)));
+    d_i16 = h->d_pcm16.as<int16_t>();
+  }
+  int32_t* d_dbg_iy = nullptr;
+  float* d_dbg_x = nullptr;
+  const size_t n_cells = (size_t)n_lanes * n_ticks;
+  if (h->dbg_max) {
+    if (h->dbg_iy_host) { CK(h->d_dbg_iy.ensure(n_cells * 2 * MAX_N * 4)); CK(cudaMemsetAsync(h->d_dbg_iy.p, 0, n_cells * 2 * MAX_N * 4, s)); d_dbg_iy = h->d_dbg_iy.as<int32_t>(); }
+    if (h->dbg_x_host) { CK(h->d_dbg_x.ensure(n_cells * 2 * MAX_N * 4)); CK(cudaMemsetAsync(h->d_dbg_x.p, 0, n_cells * 2 * MAX_N * 4, s)); d_dbg_x = h->d_dbg_x.as<float>(); }
+  }
+  CK(cudaMemsetAsync(h->d_samples.p, 0, (size_t)n_packets * 4, s));
+  int rc = decode_grid_device(h, h->d_arena.as<uint8_t>(), h->d_offsets.as<uint32_t>(), d_map, d_flags, n_lanes, n_ticks,
+                              h->d_lane_stream.as<uint32_t>(), d_f32, d_i16, pcm_stride, h->d_samples.as<int32_t>(),
+                              h->d_range.as<uint32_t>(), n_packets, s, d_dbg_iy, d_dbg_x);
+  if (rc != BD_OK) return rc;
+  if (pcm_f32) CK(cudaMemcpyAsync(pcm_f32, d_f32, pcm_elems * sizeof(float), cudaMemcpyDeviceToHost, s));
+  else CK(cudaMemcpyAsync(pcm_i16, d_i16, pcm_elems * sizeof(int16_t), cudaMemcpyDeviceToHost, s));
+  CK(cudaMemcpyAsync(samples_out, h->d_samples.p, (size_t)n_packets * 4, cudaMemcpyDeviceToHost, s));
+  CK(cudaMemcpyAsync(final_range_out, h->d_range.p, (size_t)n_packets * 4, cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  if (h->dbg_max) {
+    // debug captures are indexed by grid cell; scatter them back to packet order
+    std::vector<int32_t> iy;
+    std::vector<float> xs;
+    if (d_dbg_iy) { iy.resize(n_cells * 2 * MAX_N); CK(cudaMemcpy(iy.data(), d_dbg_iy, iy.size() * 4, cudaMemcpyDeviceToHost)); }
+    if (d_dbg_x) { xs.resize(n_cells * 2 * MAX_N); CK(cudaMemcpy(xs.data(), d_dbg_x, xs.size() * 4, cudaMemcpyDeviceToHost)); }
+    for (size_t cidx = 0; cidx < n_cells; cidx++) {
+      uint32_t p = identity ? (uint32_t)cidx : h->h_pkt_map[cidx];
+      if (p == 0xffffffffu || p >= h->dbg_max) continue;
+      if (d_dbg_iy) memcpy(h->dbg_iy_host + (size_t)p * 2 * MAX_N, iy.data() + cidx * 2 * MAX_N, 2 * MAX_N * 4);
+      if (d_dbg_x) memcpy(h->dbg_x_host + (size_t)p * 2 * MAX_N, xs.data() + cidx * 2 * MAX_N, 2 * MAX_N * 4);
+    }
+  }
+  return BD_OK;
+}
+
+int bd_decode_f32(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
+                  const uint8_t* flags, float* pcm, uint32_t pcm_stride, int32_t* samples_out, uint32_t* final_range_out) {
+  return decode_host(h, arena, offsets, stream_ids, n_packets, flags, pcm, nullptr, pcm_stride, samples_out, final_range_out);
+}
+int bd_decode_i16(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
+                  const uint8_t* flags, int16_t* pcm, uint32_t pcm_stride, int32_t* samples_out, uint32_t* final_range_out) {
+  return decode_host(h, arena, offsets, stream_ids, n_packets, flags, nullptr, pcm, pcm_stride, samples_out, final_range_out);
+}
+
+}  // extern "C"
