@@ -99,6 +99,13 @@ void bd_free_pinned(void* p);
 /* Number of kernel launches issued by the last decode call (bench.py's gpu_launches). */
 uint32_t bd_last_launch_count(const bd_handle* h);
 
+/* Per-kernel device timing for the roofline report: when enabled, every kernel launch of the decode calls is
+ * bracketed by CUDA events on the launching stream. bd_profile_read synchronises, returns the accumulated
+ * milliseconds and launch counts per kernel id (arrays of BD_K_COUNT) since the last read, and resets them. */
+enum { BD_K_PARSE = 0, BD_K_ENERGY = 1, BD_K_RECON = 2, BD_K_TAIL = 3, BD_K_SOFTCLIP = 4, BD_K_TO_I16 = 5, BD_K_COUNT = 6 };
+int bd_profile_enable(bd_handle* h, int on);
+int bd_profile_read(bd_handle* h, double* ms_out, uint32_t* launches_out);
+
 /* Test hooks (parity suite): optional device-side capture of the decoded PVQ pulse vectors and normalised spectra
  * of the next bd_decode_* call; layout [packet][2][960] int32 / float. Pass 0 to disable. Host buffers are
  * filled when the call returns. */

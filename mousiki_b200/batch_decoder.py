@@ -23,7 +23,7 @@ OPUS_BAD_ARG, OPUS_BUFFER_TOO_SMALL, OPUS_INTERNAL_ERROR, OPUS_INVALID_PACKET, O
 
 EXPORTS = [
     "bd_create", "bd_destroy", "bd_reset_streams", "bd_last_error", "bd_decode_f32", "bd_decode_i16", "bd_decode_grid_dev",
-    "bd_get_stream_info", "bd_alloc_pinned", "bd_free_pinned", "bd_last_launch_count", "bd_debug_capture",
+    "bd_get_stream_info", "bd_alloc_pinned", "bd_free_pinned", "bd_last_launch_count", "bd_debug_capture", "bd_profile_enable", "bd_profile_read",
 ]
 
 
@@ -71,6 +71,8 @@ def load_library():
     lib.bd_last_launch_count.argtypes = [vp]
     lib.bd_last_launch_count.restype = C.c_uint32
     lib.bd_debug_capture.argtypes = [vp, vp, vp, C.c_uint32]
+    lib.bd_profile_enable.argtypes = [vp, C.c_int]
+    lib.bd_profile_read.argtypes = [vp, vp, vp]
     _lib = lib
     return lib
 
@@ -180,6 +182,18 @@ class BatchDecoder:
                                           C.c_void_p(d_lane_stream or None), C.c_void_p(d_pcm_f32 or None), C.c_void_p(d_pcm_i16 or None),
                                           pcm_stride, C.c_void_p(d_samples), C.c_void_p(d_final_range), C.c_void_p(stream or None))
         self._check(rc, "bd_decode_grid_dev")
+
+    KERNELS = ("k_parse", "k_energy", "k_recon", "k_tail", "k_softclip", "k_to_i16")
+
+    def profile(self, on=True):
+        self._check(self._lib.bd_profile_enable(self._h, int(on)), "bd_profile_enable")
+
+    def profile_read(self):
+        """-> {kernel: (total_ms, launches)} accumulated since the last read (CUDA-event timed on the launch stream)."""
+        ms = np.zeros(len(self.KERNELS), dtype=np.float64)
+        cnt = np.zeros(len(self.KERNELS), dtype=np.uint32)
+        self._check(self._lib.bd_profile_read(self._h, _p(ms), _p(cnt)), "bd_profile_read")
+        return {k: (float(ms[i]), int(cnt[i])) for i, k in enumerate(self.KERNELS)}
 
     def launch_count(self):
         return int(self._lib.bd_last_launch_count(self._h))

@@ -137,6 +137,17 @@ struct bd_handle {
   int32_t* dbg_iy_host = nullptr;
   float* dbg_x_host = nullptr;
   uint32_t dbg_max = 0;
+  // optional per-kernel timing (CUDA events on the launching stream), see bd_profile_*
+  bool prof_on = false;
+  struct Span { int id; cudaEvent_t a, b; };
+  std::vector<Span> prof_spans;
+  std::vector<cudaEvent_t> prof_pool;
+  cudaEvent_t prof_event() {
+    if (!prof_pool.empty()) { cudaEvent_t e = prof_pool.back(); prof_pool.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+  }
+  void prof_begin(int id, cudaStream_t s) { if (prof_on) { Span sp{id, prof_event(), prof_event()}; cudaEventRecord(sp.a, s); prof_spans.push_back(sp); } }
+  void prof_end(cudaStream_t s) { if (prof_on) cudaEventRecord(prof_spans.back().b, s); }
 };
 
 #define CK(call)                                                                          \
@@ -199,6 +210,8 @@ void bd_destroy(bd_handle* h) {
   DevBuf* all[] = {&h->states, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->d_arena, &h->d_offsets, &h->d_pkt_map,
                    &h->d_lane_stream, &h->d_flags, &h->d_pcm, &h->d_pcm16, &h->d_samples, &h->d_range, &h->d_ids, &h->d_dbg_iy, &h->d_dbg_x};
   for (DevBuf* b : all) b->release();
+  for (auto& sp : h->prof_spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
+  for (auto e : h->prof_pool) cudaEventDestroy(e);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
 }
@@ -228,6 +241,24 @@ int bd_get_stream_info(bd_handle* h, uint32_t sid, bd_stream_info* out) {
   CK(cudaMemcpy(&s, h->states.as<StreamState>() + sid, sizeof(s), cudaMemcpyDeviceToHost));
   out->final_range = s.range_final; out->last_packet_duration = s.last_packet_duration; out->prev_mode = s.prev_mode;
   out->celt_error = s.celt_error;
+  return BD_OK;
+}
+
+int bd_profile_enable(bd_handle* h, int on) {
+  if (!h) return BD_ERR_BAD_ARG;
+  h->prof_on = on != 0;
+  return BD_OK;
+}
+int bd_profile_read(bd_handle* h, double* ms_out, uint32_t* launches_out) {
+  if (!h || !ms_out || !launches_out) return BD_ERR_BAD_ARG;
+  for (int i = 0; i < BD_K_COUNT; i++) { ms_out[i] = 0; launches_out[i] = 0; }
+  for (auto& sp : h->prof_spans) {
+    float ms = 0.f;
+    cudaEventSynchronize(sp.b);
+    if (cudaEventElapsedTime(&ms, sp.a, sp.b) == cudaSuccess && sp.id >= 0 && sp.id < BD_K_COUNT) { ms_out[sp.id] += ms; launches_out[sp.id]++; }
+    h->prof_pool.push_back(sp.a); h->prof_pool.push_back(sp.b);
+  }
+  h->prof_spans.clear();
   return BD_OK;
 }
 
@@ -273,26 +304,36 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     int32_t* samples = d_samples + shift;
     uint32_t* range = d_range + shift;
     float* pcm = pcm_f32 ? pcm_f32 + shift * pcm_stride : nullptr;
+    h->prof_begin(BD_K_PARSE, s);
     k_parse<<<(cells + 127) / 128, 128, 0, s>>>(d_arena, offs, map, cells, h->rec.as<uint32_t>(), CC, h->cfg.quirks, h->disable_inv,
                                                 cap_per_ch, flg);
+    h->prof_end(s);
+    h->prof_begin(BD_K_ENERGY, s);
     k_energy<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, nt, map, h->rec.as<uint32_t>(), h->states.as<StreamState>(), d_lane_stream,
                                                 h->en.as<float>(), h->meta.as<FrameMeta>(), samples, range, h->cfg.quirks);
+    h->prof_end(s);
     ReconParams rp;
     rp.rec = h->rec.as<uint32_t>(); rp.en = h->en.as<float>(); rp.meta = h->meta.as<FrameMeta>(); rp.series = h->series.as<float>();
     rp.series_stride = series_stride; rp.CC = CC; rp.quirks = h->cfg.quirks;
     rp.iy_dbg = d_dbg_iy ? d_dbg_iy + cell0 * 2 * MAX_N : nullptr;
     rp.x_dbg = d_dbg_x ? d_dbg_x + cell0 * 2 * MAX_N : nullptr;
+    h->prof_begin(BD_K_RECON, s);
     k_recon<<<cells, RECON_THREADS, 0, s>>>(rp, cells);
+    h->prof_end(s);
     TailParams tp;
     tp.rec = h->rec.as<uint32_t>(); tp.meta = h->meta.as<FrameMeta>(); tp.pkt_map = map; tp.lane_stream = d_lane_stream;
     tp.st_all = h->states.as<StreamState>(); tp.hist = h->hist.as<float>(); tp.series = h->series.as<float>();
     tp.series_stride = series_stride; tp.n_lanes = n_lanes; tp.n_ticks = nt; tp.CC = CC; tp.gain = h->gain;
     tp.apply_gain = h->cfg.gain_q8 != 0; tp.pcm_f32 = pcm; tp.pcm_stride = pcm_stride;
+    h->prof_begin(BD_K_TAIL, s);
     k_tail<<<(n_lanes * CC + 63) / 64, 64, 0, s>>>(tp);
+    h->prof_end(s);
     h->launches += 4;
     if (d_pcm_i16) {
+      h->prof_begin(BD_K_SOFTCLIP, s);
       k_softclip<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, nt, map, d_lane_stream, h->meta.as<FrameMeta>(), samples,
                                                     h->states.as<StreamState>(), pcm, pcm_stride, CC);
+      h->prof_end(s);
       h->launches += 1;
     } else {
       k_clear_softclip<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, d_lane_stream, h->states.as<StreamState>());
@@ -301,7 +342,9 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
   }
   if (d_pcm_i16) {
     size_t total = (size_t)n_packets * pcm_stride;
+    h->prof_begin(BD_K_TO_I16, s);
     k_to_i16<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(pcm_f32, d_pcm_i16, d_samples, n_packets, pcm_stride, CC);
+    h->prof_end(s);
     h->launches += 1;
   }
   CK(cudaGetLastError());
