@@ -163,6 +163,16 @@ class BatchDecoder:
         self._check(rc, "bd_decode")
         return (pcm, samples, rng, iy, xs) if capture else (pcm, samples, rng)
 
+    def decode_into(self, arena, offsets, stream_ids, pcm_out, samples_out, final_range_out, flags=None):
+        """Zero-allocation form of decode/decode_float: caller-owned (ideally pinned) numpy buffers.
+        pcm_out: [n, stride] float32 (decode_float) or int16 (decode); stride = frame_size * channels."""
+        n = len(stream_ids)
+        assert pcm_out.dtype in (np.float32, np.int16) and pcm_out.flags.c_contiguous and pcm_out.shape[0] == n
+        fn = self._lib.bd_decode_i16 if pcm_out.dtype == np.int16 else self._lib.bd_decode_f32
+        rc = fn(self._h, _p(arena), _p(offsets), _p(stream_ids), n, _p(flags), _p(pcm_out), pcm_out.shape[1], _p(samples_out),
+                _p(final_range_out))
+        self._check(rc, "bd_decode")
+
     def decode_float(self, arena, offsets, stream_ids, frame_size=960, flags=None, capture=False):
         """-> (pcm float32 [n, frame_size*channels], samples int32 [n], final_range uint32 [n])"""
         return self._decode(arena, offsets, stream_ids, frame_size, flags, False, capture)
