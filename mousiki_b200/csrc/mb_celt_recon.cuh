@@ -218,7 +218,7 @@ MB_DEV void team_renormalise(Walk& w, float* x, int n, float gain) {
 }
 
 // quant_partition, resynthesis side. Consumes the node stream in execution order.
-MB_DEV uint32_t recon_partition(Walk& w, float* x, int n, int B, float* lowband, int lm, float gain, uint32_t fill) {
+MB_DEV_NOINLINE uint32_t recon_partition(Walk& w, float* x, int n, int B, float* lowband, int lm, float gain, uint32_t fill) {
   struct Frame { float* x; float* lb; int n, B, B0, lm; float gmid, gside; uint32_t fill, cm; uint8_t order, st; };
   Frame st[6];
   int sp = 0;
@@ -301,7 +301,7 @@ MB_DEV uint32_t recon_partition(Walk& w, float* x, int n, int B, float* lowband,
 }
 
 // quant_band, resynthesis side (bands.rs:2133-2291)
-MB_DEV uint32_t recon_band(Walk& w, float* x, int n, int B, float* lowband, int lm, float* lowband_out, float gain,
+MB_DEV_NOINLINE uint32_t recon_band(Walk& w, float* x, int n, int B, float* lowband, int lm, float* lowband_out, float gain,
                            float* lowband_scratch, uint32_t fill) {
   const int n0 = n, long_blocks = B == 1;
   if (n == 1) {
