@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(64) k_energy(uint32_t n_lanes, uint32_t n_tick
   celt_energy_lane(lane, n_lanes, n_ticks, pkt_map, rec, st, lane_stream, en, meta, samples_out, final_range_out, quirks);
 }
 
-constexpr int RECON_THREADS = 64;
+constexpr int RECON_THREADS = 32;  // one warp per frame: team barriers are __syncwarp, uniform control flow runs once
 __global__ void __launch_bounds__(RECON_THREADS) k_recon(ReconParams P, uint32_t n_cells) {
   __shared__ ReconSmem sm;
   Team tm = {(int)threadIdx.x, (int)blockDim.x};

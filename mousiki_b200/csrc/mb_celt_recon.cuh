@@ -29,6 +29,11 @@ MB_TBL uint8_t kBitInterleave[16] = {0, 1, 1, 1, 2, 3, 3, 3, 2, 3, 3, 3, 2, 3, 3
 MB_TBL uint8_t kBitDeinterleave[16] = {0x00, 0x03, 0x0C, 0x0F, 0x30, 0x33, 0x3C, 0x3F, 0xC0, 0xC3, 0xCC, 0xCF, 0xF0, 0xF3, 0xFC, 0xFF};
 MB_TBL uint8_t kFftFactors[4][10] = {{5, 96, 3, 32, 4, 8, 2, 4, 4, 1}, {5, 48, 3, 16, 4, 4, 4, 1, 0, 0}, {5, 24, 3, 8, 2, 4, 4, 1, 0, 0}, {5, 12, 3, 4, 4, 1, 0, 0, 0, 0}};
 MB_TBL uint16_t kMdctTwOff[4] = {0, 960, 1440, 1680};
+// band of a 2.5 ms-resolution bin (bins 0..99; eBands5ms boundaries)
+MB_TBL uint8_t kBandOfBin[100] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 12, 12, 13, 13, 13, 13, 14, 14, 14, 14, 15, 15, 15, 15, 15, 15,
+                                  16, 16, 16, 16, 16, 16, 17, 17, 17, 17, 17, 17, 17, 17, 18, 18, 18, 18, 18, 18, 18, 18, 18, 18, 18, 18,
+                                  19, 19, 19, 19, 19, 19, 19, 19, 19, 19, 19, 19, 19, 19, 19, 19, 19, 19,
+                                  20, 20, 20, 20, 20, 20, 20, 20, 20, 20, 20, 20, 20, 20, 20, 20, 20, 20, 20, 20, 20, 20};
 
 // Shared-memory working set of one frame (floats unless noted). ~24 KB.
 struct ReconSmem {
@@ -36,9 +41,9 @@ struct ReconSmem {
   float W[2 * MAX_N];          // norm / norm2 fold buffers (2 x 800) during stage B, FFT work (2 x 480 complex) in stage C
   float tmp[208];              // hadamard / lowband scratch
   float lowband_scratch[176];
-  uint32_t nodes[CAP_NODES];
   uint16_t leaf_cm[CAP_LEAVES];
   float red[4];                // scalar broadcast slots
+  uint8_t collapse[2 * NB_EBANDS + 6];
 };
 
 struct Team { int tid, n; };
@@ -154,7 +159,34 @@ struct Walk {
   uint32_t seed;
   int node_pos, leaf_pos;
   int tf_change, spread;
+  const uint32_t* nodes;     // node stream of this frame in the record tile (word i at nodes[i * 32])
+  int n_nodes;
+  uint32_t cache0, cache1;   // device: lane l holds node (base + l) and (base + 32 + l) of the current window
 };
+
+// Next word of the node stream (consumed in execution order by every lane at once). On the device the warp keeps a
+// 64-node window in two registers per lane and broadcasts by shuffle; the next window is fetched one window ahead.
+MB_DEV uint32_t next_node(Walk& w) {
+  const int p = w.node_pos++;
+#if MB_ON_DEVICE
+  const int slot = p & 31;
+  if (slot == 0 && p != 0) {
+    w.cache0 = w.cache1;
+    const int q = p + 32 + w.tm.tid;
+    w.cache1 = q < w.n_nodes ? __ldg(w.nodes + (size_t)q * 32) : 0u;
+  }
+  return __shfl_sync(0xffffffffu, w.cache0, slot);
+#else
+  return w.nodes[(size_t)p * 32];
+#endif
+}
+MB_DEV void open_nodes(Walk& w, const uint32_t* nodes, int n_nodes) {
+  w.nodes = nodes; w.n_nodes = n_nodes; w.node_pos = 0; w.cache0 = w.cache1 = 0;
+#if MB_ON_DEVICE
+  if (w.tm.tid < n_nodes) w.cache0 = __ldg(nodes + (size_t)w.tm.tid * 32);
+  if (w.tm.tid + 32 < n_nodes) w.cache1 = __ldg(nodes + (size_t)(w.tm.tid + 32) * 32);
+#endif
+}
 
 MB_DEV uint32_t lcg_jump(uint32_t seed, int steps) { return kLcgA[steps] * seed + kLcgC[steps]; }
 
@@ -227,7 +259,7 @@ MB_DEV_NOINLINE uint32_t recon_partition(Walk& w, float* x, int n, int B, float*
   while (sp >= 0) {
     Frame& F = st[sp];
     if (F.st == 0) {
-      uint32_t node = w.sm->nodes[w.node_pos++];
+      uint32_t node = next_node(w);
       uint32_t type = MB_ND_TYPE(node);
       if (type == ND_SPLIT) {
         int half = F.n >> 1, itheta = (int)MB_ND_ITHETA(node);
@@ -305,7 +337,7 @@ MB_DEV_NOINLINE uint32_t recon_band(Walk& w, float* x, int n, int B, float* lowb
                            float* lowband_scratch, uint32_t fill) {
   const int n0 = n, long_blocks = B == 1;
   if (n == 1) {
-    uint32_t node = w.sm->nodes[w.node_pos++];
+    uint32_t node = next_node(w);
     if (w.tm.tid == 0) {
       x[0] = (MB_ND_SIGN(node) & 1u) ? -1.0f : 1.0f;
       if (lowband_out) lowband_out[0] = x[0];
@@ -365,7 +397,7 @@ MB_DEV_NOINLINE uint32_t recon_band(Walk& w, float* x, int n, int B, float* lowb
 MB_DEV uint32_t recon_band_stereo(Walk& w, float* x, float* y, int n, int B, float* lowband, int lm, float* lowband_out,
                                   float* lowband_scratch, uint32_t fill) {
   if (n == 1) {
-    uint32_t node = w.sm->nodes[w.node_pos++];
+    uint32_t node = next_node(w);
     if (w.tm.tid == 0) {
       x[0] = (MB_ND_SIGN(node) & 1u) ? -1.0f : 1.0f;
       y[0] = (MB_ND_SIGN(node) & 2u) ? -1.0f : 1.0f;
@@ -375,7 +407,7 @@ MB_DEV uint32_t recon_band_stereo(Walk& w, float* x, float* y, int n, int B, flo
     return 1;
   }
   const uint32_t orig_fill = fill;
-  uint32_t node = w.sm->nodes[w.node_pos++];
+  uint32_t node = next_node(w);
   const int itheta = (int)MB_ND_ITHETA(node), inv = (int)MB_ND_INV(node);
   int imid, iside;
   {
@@ -408,20 +440,28 @@ MB_DEV uint32_t recon_band_stereo(Walk& w, float* x, float* y, int n, int B, flo
       cm = recon_band(w, y, n, B, nullptr, lm, nullptr, side, nullptr, fill >> B);
       cm |= recon_band(w, x, n, B, lowband, lm, lowband_out, 1.0f, lowband_scratch, fill);
     }
-    // stereo_merge: the two inner products keep the reference's summation order (one thread each)
+    // stereo_merge: the two inner products keep the reference's summation order (one lane each)
     MB_SYNC();
-    if (w.tm.tid == 0) {
-      float xp = 0.f, sd = 0.f;
-      for (int j = 0; j < n; j++) { float a = y[j]; xp += a * x[j]; sd += a * y[j]; }
-      xp *= mid;
-      float mid2 = mid * mid;
-      float el = mid2 + sd - 2.0f * xp, er = mid2 + sd + 2.0f * xp;
-      if (er < 6e-4f || el < 6e-4f) { w.sm->red[0] = 0.f; w.sm->red[1] = 0.f; w.sm->red[2] = 1.f; }
-      else { w.sm->red[0] = celt_rsqrt(el); w.sm->red[1] = celt_rsqrt(er); w.sm->red[2] = 0.f; }
+    for (int q = w.tm.tid; q < 2; q += w.tm.n) {
+      const float* o = q ? y : x;
+      float acc = 0.f;
+      for (int j = 0; j < n; j++) acc += y[j] * o[j];
+      w.sm->red[q] = acc;
     }
     MB_SYNC();
-    float lgain = w.sm->red[0], rgain = w.sm->red[1];
-    int degenerate = w.sm->red[2] != 0.f;
+    float lgain_, rgain_;
+    int degenerate_;
+    {
+      float xp = w.sm->red[0] * mid, sd = w.sm->red[1];
+      float mid2 = mid * mid;
+      float el = mid2 + sd - 2.0f * xp, er = mid2 + sd + 2.0f * xp;
+      degenerate_ = er < 6e-4f || el < 6e-4f;
+      lgain_ = degenerate_ ? 0.f : celt_rsqrt(el);
+      rgain_ = degenerate_ ? 0.f : celt_rsqrt(er);
+    }
+    MB_SYNC();
+    const float lgain = lgain_, rgain = rgain_;
+    const int degenerate = degenerate_;
     for (int j = w.tm.tid; j < n; j += w.tm.n) {
       if (degenerate) y[j] = x[j];
       else {
@@ -558,7 +598,6 @@ MB_DEV void celt_recon_frame(Team tm, ReconSmem* sm, uint32_t f, const ReconPara
   float* Y = C == 2 ? X + N : nullptr;
 
   for (int i = tm.tid; i < C * N; i += tm.n) X[i] = 0.f;
-  for (int i = tm.tid; i < n_nodes; i += tm.n) sm->nodes[i] = r[(S_NODES + i) * 32];
   MB_SYNC();
   // ---- stage A: all PVQ leaves in parallel
   for (int l = tm.tid; l < n_leaves; l += tm.n) {
@@ -574,10 +613,11 @@ MB_DEV void celt_recon_frame(Team tm, ReconSmem* sm, uint32_t f, const ReconPara
   MB_SYNC();
   // ---- stage B: band walk
   uint32_t seed;
-  uint8_t collapse[2 * NB_EBANDS];
+  uint8_t* collapse = sm->collapse;   // every lane stores the same value: no ordering needed between lanes
   {
     Walk w;
-    w.tm = tm; w.sm = sm; w.seed = meta.seed_in; w.node_pos = 0; w.leaf_pos = 0; w.spread = spread; w.tf_change = 0;
+    w.tm = tm; w.sm = sm; w.seed = meta.seed_in; w.leaf_pos = 0; w.spread = spread; w.tf_change = 0;
+    open_nodes(w, r + S_NODES * 32, n_nodes);
     const int B = transient ? M : 1;
     const int norm_offset = M * eband(start);
     const int norm_len = imax(M * eband(NB_EBANDS - 1) - norm_offset, 0);
@@ -586,7 +626,7 @@ MB_DEV void celt_recon_frame(Team tm, ReconSmem* sm, uint32_t f, const ReconPara
     // (CELT-only frames start at band 0: every fold source is written earlier in the same frame, so
     //  the fold buffer needs no cross-frame persistence; hybrid frames will carry it in stream state)
     for (int i = tm.tid; i < 2 * norm_len; i += tm.n) norm[i] = 0.f;
-    for (int i = 0; i < 2 * NB_EBANDS; i++) collapse[i] = 0;
+    for (int i = tm.tid; i < 2 * NB_EBANDS; i += tm.n) collapse[i] = 0;
     MB_SYNC();
     for (int i = start; i < end; i++) {
       const uint32_t ba = r[(S_BANDA + i) * 32];
@@ -691,11 +731,7 @@ MB_DEV void celt_recon_frame(Team tm, ReconSmem* sm, uint32_t f, const ReconPara
     for (int idx = tm.tid; idx < C * N; idx += tm.n) {
       int c = idx >= N, j = idx - c * N;
       float v = 0.f;
-      if (j >= lo && j < hi) {
-        int b = start;
-        while (M * eband(b + 1) <= j) b++;
-        v = X[idx] * gains[c * NB_EBANDS + b];
-      }
+      if (j >= lo && j < hi) v = X[idx] * gains[c * NB_EBANDS + kBandOfBin[j >> lm]];
       X[idx] = v;
     }
     MB_SYNC();
@@ -728,8 +764,9 @@ MB_DEV void celt_recon_frame(Team tm, ReconSmem* sm, uint32_t f, const ReconPara
     }
     MB_SYNC();
     team_fft(tm, F, shift, nt);
-    // post-rotation, window fold against the zero-filled overlap, store to the lane's time series
-    const uint32_t lane = meta.lane;
+    // post-rotation and window fold against the zero-filled overlap into shared memory (X is free once the
+    // pre-rotation has consumed it), then one coalesced pass to the lane's time series
+    float* O = X;
     for (int idx = tm.tid; idx < nt * n4; idx += tm.n) {
       int t = idx / n4, i = idx - t * n4;
       int c = t / nbk, b = t - c * nbk;
@@ -738,29 +775,30 @@ MB_DEV void celt_recon_frame(Team tm, ReconSmem* sm, uint32_t f, const ReconPara
       float t0 = bits2f(twb[i]), t1 = bits2f(twb[n4 + i]);
       float yr = v.r * t0 + v.i * t1;     // temp[2i]
       float yi = v.r * t1 - v.i * t0;     // temp[n2-1-2i]
-      int k0 = 2 * i, k1 = n2 - 1 - 2 * i;
-      float vals[2] = {yr, yi};
-      int ks[2] = {k0, k1};
+      float* ob = O + c * N + b * n2;
+      const int lim = nbk > 1 ? 120 : N;
+#pragma unroll
       for (int q = 0; q < 2; q++) {
-        int k = ks[q];
-        float val = vals[q];
+        int k = q ? n2 - 1 - 2 * i : 2 * i;
+        float val = q ? yi : yr;
         // temp[k] lands at out[60 + k]; the fold rewrites out[0..120) from temp[0..60)
-        int pos0 = -1, pos1 = -1;
-        float o0 = 0.f, o1 = 0.f;
         if (k < 60) {
           float w1 = bits2f(kWindow120Bits[59 - k]), w2 = bits2f(kWindow120Bits[60 + k]);
-          pos0 = 59 - k; o0 = 0.f * w2 - val * w1;     // out[i] = x2*w2 - x1*w1 with x2 = 0
-          pos1 = 60 + k; o1 = 0.f * w1 + val * w2;     // out[119-i] = x2*w1 + x1*w2
-        } else if (60 + k < (nbk > 1 ? 120 : N)) {
-          pos0 = 60 + k; o0 = val;
+          ob[59 - k] = 0.f * w2 - val * w1;     // out[i] = x2*w2 - x1*w1 with x2 = 0
+          ob[60 + k] = 0.f * w1 + val * w2;     // out[119-i] = x2*w1 + x1*w2
+        } else if (60 + k < lim) {
+          ob[60 + k] = val;
         }
-        for (int cc = 0; cc < CC; cc++) {
-          if (nch == 2 && cc != c) continue;
-          float* out = P.series + ((size_t)lane * CC + cc) * P.series_stride + HIST + meta.sample_off + b * n2;
-          const float SIG_SAT = 536870911.0f;
-          if (pos0 >= 0) out[pos0] = o0 < -SIG_SAT ? -SIG_SAT : (o0 > SIG_SAT ? SIG_SAT : o0);
-          if (pos1 >= 0) out[pos1] = o1 < -SIG_SAT ? -SIG_SAT : (o1 > SIG_SAT ? SIG_SAT : o1);
-        }
+      }
+    }
+    MB_SYNC();
+    const float SIG_SAT = 536870911.0f;
+    for (int cc = 0; cc < CC; cc++) {
+      const float* src = O + (nch == 2 ? cc : 0) * N;
+      float* out = P.series + ((size_t)meta.lane * CC + cc) * P.series_stride + HIST + meta.sample_off;
+      for (int i = tm.tid; i < N; i += tm.n) {
+        float o = src[i];
+        out[i] = o < -SIG_SAT ? -SIG_SAT : (o > SIG_SAT ? SIG_SAT : o);
       }
     }
   }

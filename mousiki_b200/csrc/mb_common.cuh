@@ -16,7 +16,7 @@
 #define MB_MEM __device__ __forceinline__
 #define MB_DEV_NOINLINE __device__ __noinline__
 #define MB_TBL static __device__ const
-#define MB_SYNC() __syncthreads()
+#define MB_SYNC() __syncwarp()   /* a thread team is one warp (mb_celt_recon.cuh) */
 #define MB_ON_DEVICE 1
 #else
 #define MB_DEV static inline
@@ -157,8 +157,21 @@ MB_DEV float fma32(float a, float b, float c) {
 }
 // f64-evaluate-then-round helpers (reference src/celt/math.rs:259-334 via crate libm)
 MB_DEV float celt_exp2(float x) { return (float)exp(0.6931471805599453094 * (double)x); }
-MB_DEV float celt_sqrt(float x) { return (float)sqrt((double)x); }
-MB_DEV float celt_rsqrt(float x) { return 1.0f / celt_sqrt(x); }
+// (float)sqrt((double)x) == correctly rounded f32 sqrt (53 >= 2*24+2 bits: double rounding is innocuous for sqrt)
+MB_DEV float celt_sqrt(float x) {
+#if MB_ON_DEVICE
+  return __fsqrt_rn(x);
+#else
+  return (float)sqrt((double)x);
+#endif
+}
+MB_DEV float celt_rsqrt(float x) {
+#if MB_ON_DEVICE
+  return __fdiv_rn(1.0f, celt_sqrt(x));
+#else
+  return 1.0f / celt_sqrt(x);
+#endif
+}
 MB_DEV float celt_cos_norm(float x) { return (float)cos((double)(0.5f * 3.14159265358979323846f * x)); }
 MB_DEV int eband(int i) { return kEBands5ms[i]; }
 MB_DEV uint32_t mask_from_bits(int b) { return b <= 0 ? 0u : (b >= 32 ? 0xffffffffu : (1u << b) - 1u); }
