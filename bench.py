@@ -156,7 +156,10 @@ def run_reference(args):
 ALG_BYTES = {
     "k_parse": 161 + 8 + 1800,          # packet + offsets in, ~450 record words out
     "k_energy": 42 * 4 + 126 * 4 + 16,  # energy symbols in, band energies + frame meta out
-    "k_recon": 1800 + 504 + 7680,       # records + energies in, 2 x 960 f32 time-domain samples out
+    "k_pvq": 600 + 7680,                # leaf records in, spectrum row (pulse leaves) out
+    "k_plan": 1200 + 1200,              # node stream + leaf masks in, operation list out
+    "k_bands": 1200 + 504 + 7680 + 7680,  # operation list + energies + spectrum row in, freq row out (in place)
+    "k_imdct": 7680 + 7680,             # freq row in, 2 x 960 f32 time-domain samples out
     "k_tail": 7680 + 7680,              # time-domain samples in, interleaved f32 PCM out
 }
 PATH_BYTES = 30200

@@ -50,7 +50,7 @@ typedef struct bd_config {
   int32_t disable_phase_inversion;   /* <0: decoder default (mono decoders disable it), 0/1 explicit */
   uint32_t quirks;                   /* BD_QUIRKS_MOUSIKI */
   int32_t device;                    /* CUDA device ordinal */
-  uint32_t max_frames_per_pass;      /* 0 = default; bounds the phase-1 scratch (14 KB per frame) */
+  uint32_t max_frames_per_pass;      /* 0 = default; bounds the per-frame scratch (~30 KB per frame) */
   uint32_t reserved;
 } bd_config;
 
@@ -102,7 +102,8 @@ uint32_t bd_last_launch_count(const bd_handle* h);
 /* Per-kernel device timing for the roofline report: when enabled, every kernel launch of the decode calls is
  * bracketed by CUDA events on the launching stream. bd_profile_read synchronises, returns the accumulated
  * milliseconds and launch counts per kernel id (arrays of BD_K_COUNT) since the last read, and resets them. */
-enum { BD_K_PARSE = 0, BD_K_ENERGY = 1, BD_K_RECON = 2, BD_K_TAIL = 3, BD_K_SOFTCLIP = 4, BD_K_TO_I16 = 5, BD_K_COUNT = 6 };
+enum { BD_K_PARSE = 0, BD_K_ENERGY = 1, BD_K_PVQ = 2, BD_K_PLAN = 3, BD_K_BANDS = 4, BD_K_IMDCT = 5, BD_K_TAIL = 6, BD_K_SOFTCLIP = 7,
+       BD_K_TO_I16 = 8, BD_K_COUNT = 9 };
 int bd_profile_enable(bd_handle* h, int on);
 int bd_profile_read(bd_handle* h, double* ms_out, uint32_t* launches_out);
 

@@ -3,7 +3,10 @@
 // Launch sequence of one decode pass over a [ticks x lanes] grid of packets:
 //   k_parse    lane per packet          phase 1  (mb_frame.cuh / mb_celt_parse.cuh)
 //   k_energy   lane per stream          phase 2a (mb_celt_energy.cuh)
-//   k_recon    CTA per frame            phase 2b (mb_celt_recon.cuh)
+//   k_pvq      CTA per frame, thread per PVQ leaf   phase 2b(i)   (mb_celt_pvq.cuh)
+//   k_plan     lane per frame                       phase 2b(ii)  (mb_celt_plan.cuh)
+//   k_bands    warp per frame                       phase 2b(iii) (mb_celt_bands.cuh)
+//   k_imdct    warp per frame-channel               phase 2b(iv)  (mb_celt_imdct.cuh)
 //   k_tail     lane per stream-channel  phase 2c (mb_celt_tail.cuh)
 //   k_softclip / k_to_i16               i16 output path only
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo (see __graft_entry__.build()).
@@ -16,7 +19,7 @@
 #include <vector>
 
 #include "../../include/mousiki_b200.h"
-#include "mb_celt_recon.cuh"
+#include "mb_celt_imdct.cuh"
 #include "mb_celt_tail.cuh"
 #include "mb_frame.cuh"
 
@@ -41,11 +44,38 @@ __global__ void __launch_bounds__(64) k_energy(uint32_t n_lanes, uint32_t n_tick
   celt_energy_lane(lane, n_lanes, n_ticks, pkt_map, rec, st, lane_stream, en, meta, samples_out, final_range_out, quirks);
 }
 
-constexpr int RECON_THREADS = 32;  // one warp per frame: team barriers are __syncwarp, uniform control flow runs once
-__global__ void __launch_bounds__(RECON_THREADS) k_recon(ReconParams P, uint32_t n_cells) {
-  __shared__ ReconSmem sm;
+constexpr int PVQ_THREADS = 64;
+__global__ void __launch_bounds__(PVQ_THREADS) k_pvq(PvqParams P) {
+  __shared__ float X[2 * MAX_N];
   Team tm = {(int)threadIdx.x, (int)blockDim.x};
-  celt_recon_frame(tm, &sm, blockIdx.x, P);
+  celt_pvq_frame(tm, X, blockIdx.x, P);
+}
+
+__global__ void __launch_bounds__(128) k_plan(PlanParams P, uint32_t n_cells) {
+  uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= n_cells) return;
+  celt_plan_frame(f, P);
+}
+
+// one warp per frame; 4 frames per CTA
+constexpr int BANDS_WARPS = 4;
+__global__ void __launch_bounds__(32 * BANDS_WARPS) k_bands(BandsParams P, uint32_t n_cells) {
+  __shared__ BandsSmem sm[BANDS_WARPS];
+  const uint32_t f = blockIdx.x * BANDS_WARPS + (threadIdx.x >> 5);
+  if (f >= n_cells) return;
+  Team tm = {(int)(threadIdx.x & 31), 32};
+  celt_bands_frame(tm, &sm[threadIdx.x >> 5], f, P);
+}
+
+// one warp per (frame, channel); 4 units per CTA
+constexpr int IMDCT_WARPS = 4;
+__global__ void __launch_bounds__(32 * IMDCT_WARPS) k_imdct(ImdctParams P, uint32_t n_units) {
+  __shared__ ImdctSmem sm[IMDCT_WARPS];
+  const uint32_t unit = blockIdx.x * IMDCT_WARPS + (threadIdx.x >> 5);
+  if (unit >= n_units) return;
+  Team tm = {(int)(threadIdx.x & 31), 32};
+  const uint32_t nu = (uint32_t)P.CC;
+  celt_imdct_unit(tm, &sm[threadIdx.x >> 5], unit / nu, (int)(unit % nu), P);
 }
 
 __global__ void __launch_bounds__(64) k_tail(TailParams P) {
@@ -129,7 +159,7 @@ struct bd_handle {
   std::string err;
   uint32_t launches = 0;
   cudaStream_t own_stream = nullptr;
-  DevBuf states, hist, rec, en, meta, series;
+  DevBuf states, hist, rec, en, meta, series, xbuf;
   // staging for the host-buffer entry points
   DevBuf d_arena, d_offsets, d_pkt_map, d_lane_stream, d_flags, d_pcm, d_pcm16, d_samples, d_range, d_ids, d_dbg_iy, d_dbg_x;
   std::vector<uint32_t> h_pkt_map, h_lane_stream, h_lane_of_stream, h_epoch, h_count;
@@ -207,7 +237,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
 void bd_destroy(bd_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  DevBuf* all[] = {&h->states, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->d_arena, &h->d_offsets, &h->d_pkt_map,
+  DevBuf* all[] = {&h->states, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map,
                    &h->d_lane_stream, &h->d_flags, &h->d_pcm, &h->d_pcm16, &h->d_samples, &h->d_range, &h->d_ids, &h->d_dbg_iy, &h->d_dbg_x};
   for (DevBuf* b : all) b->release();
   for (auto& sp : h->prof_spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -286,6 +316,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
   CK(h->en.ensure((size_t)cells_max * EN_STRIDE * sizeof(float)));
   CK(h->meta.ensure((size_t)cells_max * sizeof(FrameMeta)));
   CK(h->series.ensure((size_t)n_lanes * CC * series_stride * sizeof(float)));
+  CK(h->xbuf.ensure((size_t)cells_max * XBUF_STRIDE * sizeof(float)));
   float* pcm_f32 = d_pcm_f32;
   if (d_pcm_i16) {  // the i16 path decodes to a float scratch, soft-clips, then rounds (src/opus_decoder.rs:1679-1712)
     CK(h->d_pcm.ensure((size_t)n_packets * pcm_stride * sizeof(float)));
@@ -312,13 +343,28 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     k_energy<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, nt, map, h->rec.as<uint32_t>(), h->states.as<StreamState>(), d_lane_stream,
                                                 h->en.as<float>(), h->meta.as<FrameMeta>(), samples, range, h->cfg.quirks);
     h->prof_end(s);
-    ReconParams rp;
-    rp.rec = h->rec.as<uint32_t>(); rp.en = h->en.as<float>(); rp.meta = h->meta.as<FrameMeta>(); rp.series = h->series.as<float>();
-    rp.series_stride = series_stride; rp.CC = CC; rp.quirks = h->cfg.quirks;
-    rp.iy_dbg = d_dbg_iy ? d_dbg_iy + cell0 * 2 * MAX_N : nullptr;
-    rp.x_dbg = d_dbg_x ? d_dbg_x + cell0 * 2 * MAX_N : nullptr;
-    h->prof_begin(BD_K_RECON, s);
-    k_recon<<<cells, RECON_THREADS, 0, s>>>(rp, cells);
+    PvqParams pq;
+    pq.rec = h->rec.as<uint32_t>(); pq.meta = h->meta.as<FrameMeta>(); pq.xbuf = h->xbuf.as<float>();
+    pq.iy_dbg = d_dbg_iy ? d_dbg_iy + cell0 * 2 * MAX_N : nullptr;
+    h->prof_begin(BD_K_PVQ, s);
+    k_pvq<<<cells, PVQ_THREADS, 0, s>>>(pq);
+    h->prof_end(s);
+    PlanParams pl;
+    pl.rec = h->rec.as<uint32_t>(); pl.en = h->en.as<float>(); pl.meta = h->meta.as<FrameMeta>();
+    h->prof_begin(BD_K_PLAN, s);
+    k_plan<<<(cells + 127) / 128, 128, 0, s>>>(pl, cells);
+    h->prof_end(s);
+    BandsParams bp;
+    bp.rec = h->rec.as<uint32_t>(); bp.en = h->en.as<float>(); bp.meta = h->meta.as<FrameMeta>(); bp.xbuf = h->xbuf.as<float>();
+    bp.x_dbg = d_dbg_x ? d_dbg_x + cell0 * 2 * MAX_N : nullptr;
+    h->prof_begin(BD_K_BANDS, s);
+    k_bands<<<(cells + BANDS_WARPS - 1) / BANDS_WARPS, 32 * BANDS_WARPS, 0, s>>>(bp, cells);
+    h->prof_end(s);
+    ImdctParams ip;
+    ip.rec = h->rec.as<uint32_t>(); ip.meta = h->meta.as<FrameMeta>(); ip.xbuf = h->xbuf.as<float>(); ip.series = h->series.as<float>();
+    ip.series_stride = series_stride; ip.CC = CC;
+    h->prof_begin(BD_K_IMDCT, s);
+    k_imdct<<<(cells * CC + IMDCT_WARPS - 1) / IMDCT_WARPS, 32 * IMDCT_WARPS, 0, s>>>(ip, cells * CC);
     h->prof_end(s);
     TailParams tp;
     tp.rec = h->rec.as<uint32_t>(); tp.meta = h->meta.as<FrameMeta>(); tp.pkt_map = map; tp.lane_stream = d_lane_stream;
@@ -328,7 +374,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     h->prof_begin(BD_K_TAIL, s);
     k_tail<<<(n_lanes * CC + 63) / 64, 64, 0, s>>>(tp);
     h->prof_end(s);
-    h->launches += 4;
+    h->launches += 7;
     if (d_pcm_i16) {
       h->prof_begin(BD_K_SOFTCLIP, s);
       k_softclip<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, nt, map, d_lane_stream, h->meta.as<FrameMeta>(), samples,

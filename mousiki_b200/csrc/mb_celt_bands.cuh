@@ -1,0 +1,305 @@
+// Phase 2b(iii) — band resynthesis: one warp per frame executes the frame's operation list (mb_celt_plan.cuh) band by
+// band on a small shared-memory window, then scales the band to its energy.
+//
+// Replaces the float half of
+//   quant_band / quant_band_stereo / quant_partition resynthesis (fold, noise fill, haar1, hadamard
+//   (de)interleave, stereo_merge)            src/celt/bands.rs:1917-3082, 3477-3505, 3708-3836
+//   renormalise_vector                       src/celt/vq.rs:1073-1088
+//   anti_collapse (noise injection)          src/celt/bands.rs:3220-3349
+//   denormalise_bands                        src/celt/bands.rs:4172-4234
+// Only the band being rebuilt (<= 176 bins per channel) and the fold buffer live on chip; the spectrum row itself
+// stays in the spectrum buffer, where the PVQ pass left the pulse leaves and this pass leaves `freq`, in place.
+#pragma once
+#include "mb_celt_plan.cuh"
+
+namespace mb {
+
+MB_TBL float kEMeans[25] = {6.4375f, 6.25f, 5.75f, 5.3125f, 5.0625f, 4.8125f, 4.5f, 4.375f, 4.875f, 4.6875f, 4.5625f, 4.4375f, 4.875f,
+                            4.625f, 4.3125f, 4.5f, 4.375f, 4.625f, 4.75f, 4.4375f, 3.75f, 3.75f, 3.75f, 3.75f, 3.75f};
+MB_TBL uint8_t kOrdery[30] = {1, 0, 3, 0, 2, 1, 7, 0, 4, 3, 6, 1, 5, 2, 15, 0, 8, 7, 12, 3, 11, 4, 14, 1, 9, 6, 13, 2, 10, 5};
+
+// Shared-memory working set of one frame: 9.4 KB.
+struct BandsSmem {
+  float win[2 * WIN_Y];        // x | y of the current band
+  float scratch[176];          // transformed copy of the fold source
+  float tmp[176];              // permutation scratch
+  float norm[2 * 800];         // fold buffers (norm | norm2), bands.rs:2614-2617
+  float gains[2 * NB_EBANDS];
+  float red[4];
+};
+
+// Window of operation words: lane l holds words (base + l) and (base + 32 + l); broadcast by shuffle.
+struct OpReader {
+  const uint32_t* ops;
+  int n_ops, pos, tid;
+  uint32_t c0, c1;
+  MB_MEM void open(const uint32_t* o, int n, int lane) {
+    ops = o; n_ops = n; pos = 0; tid = lane; c0 = c1 = 0;
+#if MB_ON_DEVICE
+    if (lane < n) c0 = __ldg(o + (size_t)lane * 32);
+    if (lane + 32 < n) c1 = __ldg(o + (size_t)(lane + 32) * 32);
+#endif
+  }
+  MB_MEM uint32_t next() {
+    const int p = pos++;
+#if MB_ON_DEVICE
+    const int slot = p & 31;
+    if (slot == 0 && p != 0) {
+      c0 = c1;
+      const int q = p + 32 + tid;
+      c1 = q < n_ops ? __ldg(ops + (size_t)q * 32) : 0u;
+    }
+    return __shfl_sync(0xffffffffu, c0, slot);
+#else
+    return ops[(size_t)p * 32];
+#endif
+  }
+  MB_MEM void skip(int n) { for (int i = 0; i < n; i++) (void)next(); }
+};
+
+MB_DEV void team_haar1(Team tm, float* x, int n0, int stride) {
+  if (n0 < 2) return;
+  const int half = n0 / 2;
+  const float scale = 0.70710678f;
+  const int total = stride * half;
+  for (int idx = tm.tid; idx < total; idx += tm.n) {
+    int i = idx / half, j = idx - i * half;
+    int i0 = stride * 2 * j + i, i1 = i0 + stride;
+    float t1 = scale * x[i0], t2 = scale * x[i1];
+    x[i0] = t1 + t2;
+    x[i1] = t1 - t2;
+  }
+  MB_SYNC();
+}
+MB_DEV const uint8_t* ordery_for(int stride) { return kOrdery + (stride == 2 ? 0 : stride == 4 ? 2 : stride == 8 ? 6 : 14); }
+MB_DEV void team_deinterleave(Team tm, float* x, float* tmp, int n0, int stride, int hadamard) {
+  const int n = n0 * stride;
+  const uint8_t* ord = ordery_for(stride);
+  for (int idx = tm.tid; idx < n; idx += tm.n) {
+    int i = idx / n0, j = idx - i * n0;
+    int dst = (hadamard ? (int)ord[i] : i) * n0 + j;
+    tmp[dst] = x[j * stride + i];
+  }
+  MB_SYNC();
+  for (int idx = tm.tid; idx < n; idx += tm.n) x[idx] = tmp[idx];
+  MB_SYNC();
+}
+MB_DEV void team_interleave(Team tm, float* x, float* tmp, int n0, int stride, int hadamard) {
+  const int n = n0 * stride;
+  const uint8_t* ord = ordery_for(stride);
+  for (int idx = tm.tid; idx < n; idx += tm.n) {
+    int i = idx / n0, j = idx - i * n0;
+    int src = (hadamard ? (int)ord[i] : i) * n0 + j;
+    tmp[j * stride + i] = x[src];
+  }
+  MB_SYNC();
+  for (int idx = tm.tid; idx < n; idx += tm.n) x[idx] = tmp[idx];
+  MB_SYNC();
+}
+// renormalise_vector (vq.rs:1073-1088): the energy sum keeps the reference's left-to-right order
+MB_DEV void team_renormalise(Team tm, BandsSmem* sm, float* x, int n, float gain) {
+  MB_SYNC();
+  if (tm.tid == 0) {
+    float e = 0.f;
+    for (int i = 0; i < n; i++) e += x[i] * x[i];
+    e = 1e-15f + e;
+    sm->red[0] = celt_rsqrt(e) * gain;
+  }
+  MB_SYNC();
+  const float scale = sm->red[0];
+  for (int i = tm.tid; i < n; i += tm.n) x[i] *= scale;
+  MB_SYNC();
+}
+
+struct BandsParams {
+  const uint32_t* rec;
+  const float* en;
+  const FrameMeta* meta;
+  float* xbuf;              // [frame][XBUF_STRIDE]: pulse leaves in, freq out
+  float* x_dbg;             // optional [frame][2*960] normalised spectrum after anti-collapse
+};
+
+MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsParams& P) {
+  const FrameMeta meta = P.meta[f];
+  if (!(meta.flags & 1u)) return;
+  const uint32_t* r = P.rec + rec_index(f, 0);
+  const uint32_t h0 = r[S_HDR0 * 32], status = r[S_STATUS * 32], plan = r[S_PLAN * 32];
+  const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), start = (int)MB_H0_START(h0), end = (int)MB_ST_END(status);
+  const int M = 1 << lm, N = M * SHORT_MDCT;
+  if (plan == 0xffffffffu) return;   // operation list overflow (cannot happen for legal trees; the frame stays silent)
+  float* xrow = P.xbuf + (size_t)f * XBUF_STRIDE;
+  const float* E = P.en + (size_t)f * EN_STRIDE;
+  float* norm = sm->norm;
+  float* norm2 = norm + 800;
+  // (CELT-only frames start at band 0: every fold source is written earlier in the same frame, so the fold buffer
+  //  needs no cross-frame persistence; hybrid frames will carry it in stream state)
+  for (int i = tm.tid; i < 2 * 800; i += tm.n) norm[i] = 0.f;
+  for (int idx = tm.tid; idx < C * NB_EBANDS; idx += tm.n) sm->gains[idx] = celt_exp2(fmin32(E[idx] + kEMeans[idx % NB_EBANDS], 32.0f));
+  OpReader ops;
+  ops.open(r + S_OPS * 32, (int)plan, tm.tid);
+  MB_SYNC();
+  for (int band = start; band < end; band++) {
+    const int band_start = M * eband(band), n = M * eband(band + 1) - band_start;
+    for (int idx = tm.tid; idx < C * n; idx += tm.n) {
+      int c = idx >= n, j = idx - c * n;
+      sm->win[c * WIN_Y + j] = xrow[c * N + band_start + j];
+    }
+    MB_SYNC();
+    for (;;) {
+      const uint32_t op = ops.next();
+      const uint32_t type = MB_OP_TYPE(op);
+      if (type == OP_END_BAND) break;
+      const int a = (int)MB_OP_A(op), len = (int)MB_OP_N(op);
+      const uint32_t p = MB_OP_P(op);
+      float* x = sm->win + a;
+      switch (type) {
+        case OP_SKIP: ops.skip(len); break;
+        case OP_COPY_LB: {
+          const uint32_t w1 = ops.next();
+          const float* src = ((w1 >> 11) & 1u ? norm2 : norm) + (w1 & 2047u);
+          for (int j = tm.tid; j < len; j += tm.n) sm->scratch[j] = src[j];
+          MB_SYNC();
+        } break;
+        case OP_HAAR: {
+          const int stride = 1 << (p >> 1);
+          team_haar1(tm, (p & 1u) ? sm->scratch : x, len / stride, stride);
+        } break;
+        case OP_DEINT: {
+          const int stride = 1 << ((p >> 1) & 7u);
+          team_deinterleave(tm, (p & 1u) ? sm->scratch : x, sm->tmp, len / stride, stride, (int)(p >> 4) & 1);
+        } break;
+        case OP_INTER: {
+          const int stride = 1 << ((p >> 1) & 7u);
+          team_interleave(tm, (p & 1u) ? sm->scratch : x, sm->tmp, len / stride, stride, (int)(p >> 4) & 1);
+        } break;
+        case OP_ZERO:
+          for (int j = tm.tid; j < len; j += tm.n) x[j] = 0.f;
+          MB_SYNC();
+          break;
+        case OP_FOLD: {
+          const float gain = bits2f(ops.next());
+          const uint32_t seed = ops.next();
+          const float* lb = sm->scratch + p;
+          for (int j = tm.tid; j < len; j += tm.n) {
+            uint32_t s = lcg_jump(seed, j + 1);
+            x[j] = lb[j] + ((s & 0x8000u) ? 1.0f / 256.0f : -(1.0f / 256.0f));
+          }
+          team_renormalise(tm, sm, x, len, gain);
+        } break;
+        case OP_NOISE: {
+          const float gain = bits2f(ops.next());
+          const uint32_t seed = ops.next();
+          for (int j = tm.tid; j < len; j += tm.n) {
+            uint32_t s = lcg_jump(seed, j + 1);
+            x[j] = (float)((int32_t)s >> 20);
+          }
+          team_renormalise(tm, sm, x, len, gain);
+        } break;
+        case OP_N1:
+          if (tm.tid == 0) x[0] = (p & 1u) ? -1.0f : 1.0f;
+          MB_SYNC();
+          break;
+        case OP_LBOUT: {
+          const uint32_t w1 = ops.next();
+          float* dst = ((w1 >> 11) & 1u ? norm2 : norm) + (w1 & 2047u);
+          const float scale = celt_sqrt((float)len);
+          for (int j = tm.tid; j < len; j += tm.n) dst[j] = scale * x[j];
+          MB_SYNC();
+        } break;
+        case OP_MERGE: {  // stereo_merge (bands.rs:3477-3505): the two inner products keep the reference's summation order
+          const float mid = (float)(int)(ops.next() & 0xffffu) / 32768.0f;
+          float* xx = sm->win;
+          float* yy = sm->win + WIN_Y;
+          for (int q = tm.tid; q < 2; q += tm.n) {
+            const float* o = q ? yy : xx;
+            float acc = 0.f;
+            for (int j = 0; j < len; j++) acc += yy[j] * o[j];
+            sm->red[q] = acc;
+          }
+          MB_SYNC();
+          const float xp = sm->red[0] * mid, sd = sm->red[1];
+          const float mid2 = mid * mid;
+          const float el = mid2 + sd - 2.0f * xp, er = mid2 + sd + 2.0f * xp;
+          const int degenerate = er < 6e-4f || el < 6e-4f;
+          const float lgain = degenerate ? 0.f : celt_rsqrt(el), rgain = degenerate ? 0.f : celt_rsqrt(er);
+          const int inv = (int)(p & 1u);
+          MB_SYNC();
+          for (int j = tm.tid; j < len; j += tm.n) {
+            float yv;
+            if (degenerate) yv = xx[j];
+            else {
+              float l = mid * xx[j], rv = yy[j];
+              xx[j] = lgain * (l - rv);
+              yv = rgain * (l + rv);
+            }
+            yy[j] = inv ? -yv : yv;
+          }
+          MB_SYNC();
+        } break;
+        case OP_STEREO2: {
+          const uint32_t w1 = ops.next();
+          if (tm.tid == 0) {
+            const float mid = (float)(int)(w1 & 0xffffu) / 32768.0f, side = (float)(int)(w1 >> 16) / 32768.0f;
+            float* xx = sm->win;
+            float* yy = sm->win + WIN_Y;
+            const int c = (int)(p & 1u);
+            float* x2 = c ? yy : xx;
+            float* y2 = c ? xx : yy;
+            const int sv = 1 - 2 * (int)((p >> 1) & 1u);
+            y2[0] = -(float)sv * x2[1];
+            y2[1] = (float)sv * x2[0];
+            xx[0] *= mid; xx[1] *= mid; yy[0] *= side; yy[1] *= side;
+            float t = xx[0]; xx[0] = t - yy[0]; yy[0] += t;
+            t = xx[1]; xx[1] = t - yy[1]; yy[1] += t;
+            if ((p >> 2) & 1u) { yy[0] = -yy[0]; yy[1] = -yy[1]; }
+          }
+          MB_SYNC();
+        } break;
+        case OP_AVG: {
+          const int cnt = len | ((int)p << 9);
+          for (int j = tm.tid; j < cnt; j += tm.n) norm[j] = (norm[j] + norm2[j]) * 0.5f;
+          MB_SYNC();
+        } break;
+        case OP_HYB: {
+          const uint32_t w1 = ops.next();
+          const int n1 = (int)(w1 & 2047u), cnt = (int)((w1 >> 11) & 2047u), dual = (int)((w1 >> 22) & 1u);
+          const int n2 = n1 + cnt;
+          for (int j = tm.tid; j < cnt; j += tm.n) {
+            norm[n1 + j] = norm[2 * n1 - n2 + j];
+            if (dual) norm2[n1 + j] = norm2[2 * n1 - n2 + j];
+          }
+          MB_SYNC();
+        } break;
+        case OP_ANTI: {
+          uint32_t seed = ops.next();
+          const float rr = bits2f(ops.next());
+          const int alm = (int)(p & 3u), N0 = len >> alm;
+          const uint32_t missing = p >> 2;
+          for (int k = 0; k < (1 << alm); k++) {
+            if (!(missing & (1u << k))) continue;
+            for (int j = tm.tid; j < N0; j += tm.n) {
+              uint32_t s = lcg_jump(seed, j + 1);
+              x[(j << alm) + k] = (s & 0x8000u) ? rr : -rr;
+            }
+            seed = lcg_jump(seed, N0);
+          }
+          team_renormalise(tm, sm, x, len, 1.0f);
+        } break;
+        default: break;
+      }
+    }
+    // ---- denormalise_bands for this band, in place in the spectrum row
+    if (P.x_dbg)
+      for (int idx = tm.tid; idx < C * n; idx += tm.n) {
+        int c = idx >= n, j = idx - c * n;
+        P.x_dbg[(size_t)f * 2 * MAX_N + c * MAX_N + band_start + j] = sm->win[c * WIN_Y + j];
+      }
+    for (int idx = tm.tid; idx < C * n; idx += tm.n) {
+      int c = idx >= n, j = idx - c * n;
+      xrow[c * N + band_start + j] = sm->win[c * WIN_Y + j] * sm->gains[c * NB_EBANDS + band];
+    }
+    MB_SYNC();
+  }
+}
+
+}  // namespace mb

@@ -1,0 +1,208 @@
+// Phase 2b(iv) — inverse MDCT: one warp per (frame, channel), every frame of every stream concurrently.
+//
+// Replaces:
+//   celt_synthesis / apply_inverse_mdct       src/celt/celt_decoder.rs:473-507, 573-800
+//   clt_mdct_backward, pre/post rotation      src/celt/mdct.rs:197-388 (with the reference's zero-filled overlap)
+//   KissFftState::ifft, kf_bfly2/3/4/5        src/celt/kiss_fft.rs:729-795, 900-1340
+// The spectrum row (freq, written in place by the band pass) is staged in shared memory, pre-rotated into bit-reversed
+// order, transformed by a shared-memory mixed-radix FFT that keeps the static mode's radix order (4,2,4,3,5 for 480
+// points — the rounding order is part of parity), post-rotated, folded against the window, and leaves as one coalesced
+// row of the lane's time series.
+#pragma once
+#include "mb_celt_bands.cuh"
+
+namespace mb {
+
+MB_TBL uint8_t kFftFactors[4][10] = {{5, 96, 3, 32, 4, 8, 2, 4, 4, 1}, {5, 48, 3, 16, 4, 4, 4, 1, 0, 0}, {5, 24, 3, 8, 2, 4, 4, 1, 0, 0}, {5, 12, 3, 4, 4, 1, 0, 0, 0, 0}};
+MB_TBL uint16_t kMdctTwOff[4] = {0, 960, 1440, 1680};
+
+// ---------------------------------------------------------------- stage C: FFT + IMDCT
+struct cpx { float r, i; };
+MB_DEV cpx c_mul(cpx a, cpx b) { cpx o; o.r = fma32(a.r, b.r, -(a.i * b.i)); o.i = fma32(a.r, b.i, a.i * b.r); return o; }
+MB_DEV cpx c_add(cpx a, cpx b) { cpx o; o.r = a.r + b.r; o.i = a.i + b.i; return o; }
+MB_DEV cpx c_sub(cpx a, cpx b) { cpx o; o.r = a.r - b.r; o.i = a.i - b.i; return o; }
+MB_DEV cpx fft_tw(int idx) { cpx o; o.r = bits2f(kFftTwiddles480Bits[2 * idx]); o.i = bits2f(kFftTwiddles480Bits[2 * idx + 1]); return o; }
+
+// One butterfly of radix p at (group g, position k); p points at the group's base.
+MB_DEV void bfly_one(cpx* p, int radix, int k, int m, int fstride) {
+  if (radix == 4) {
+    if (m == 1) {
+      cpx s0 = c_sub(p[0], p[2]), s1 = c_add(p[1], p[3]), s1b = c_sub(p[1], p[3]);
+      cpx f0 = c_add(p[0], p[2]);
+      p[2] = c_sub(f0, s1);
+      p[0] = c_add(f0, s1);
+      cpx a = {s0.r + s1b.i, s0.i - s1b.r}, b = {s0.r - s1b.i, s0.i + s1b.r};
+      p[1] = a; p[3] = b;
+    } else {
+      cpx s0 = c_mul(p[k + m], fft_tw(k * fstride)), s1 = c_mul(p[k + 2 * m], fft_tw(2 * k * fstride)),
+          s2 = c_mul(p[k + 3 * m], fft_tw(3 * k * fstride));
+      cpx s5 = c_sub(p[k], s1);
+      cpx f0 = c_add(p[k], s1);
+      cpx s3 = c_add(s0, s2), s4 = c_sub(s0, s2);
+      p[k + 2 * m] = c_sub(f0, s3);
+      p[k] = c_add(f0, s3);
+      cpx a = {s5.r + s4.i, s5.i - s4.r}, b = {s5.r - s4.i, s5.i + s4.r};
+      p[k + m] = a; p[k + 3 * m] = b;
+    }
+  } else if (radix == 2) {  // always the m == 4 form in the static modes (kiss_fft.rs:900-966)
+    const float t8 = 0.70710678118654752440f;
+    cpx v = p[4 + k], t;
+    if (k == 0) t = v;
+    else if (k == 1) { t.r = (v.r + v.i) * t8; t.i = (v.i - v.r) * t8; }
+    else if (k == 2) { t.r = v.i; t.i = -v.r; }
+    else { t.r = (v.i - v.r) * t8; t.i = -(v.i + v.r) * t8; }
+    p[4 + k] = c_sub(p[k], t);
+    p[k] = c_add(p[k], t);
+  } else if (radix == 3) {
+    cpx epi3 = fft_tw(fstride * m);
+    cpx s1 = c_mul(p[m + k], fft_tw(k * fstride)), s2 = c_mul(p[2 * m + k], fft_tw(2 * k * fstride));
+    cpx s3 = c_add(s1, s2), s0 = c_sub(s1, s2);
+    cpx fm = {p[k].r - 0.5f * s3.r, p[k].i - 0.5f * s3.i};
+    s0.r *= epi3.i; s0.i *= epi3.i;
+    cpx f0 = c_add(p[k], s3);
+    cpx a = {fm.r + s0.i, fm.i - s0.r}, b = {fm.r - s0.i, fm.i + s0.r};
+    p[2 * m + k] = a; p[m + k] = b; p[k] = f0;
+  } else {  // radix 5
+    cpx ya = fft_tw(fstride * m), yb = fft_tw(fstride * 2 * m);
+    cpx s0 = p[k];
+    cpx s1 = c_mul(p[m + k], fft_tw(k * fstride)), s2 = c_mul(p[2 * m + k], fft_tw(2 * k * fstride));
+    cpx s3 = c_mul(p[3 * m + k], fft_tw(3 * k * fstride)), s4 = c_mul(p[4 * m + k], fft_tw(4 * k * fstride));
+    cpx s7 = c_add(s1, s4), s10 = c_sub(s1, s4), s8 = c_add(s2, s3), s9 = c_sub(s2, s3);
+    cpx f0 = c_add(s0, c_add(s7, s8));
+    cpx s5 = {s0.r + fma32(s7.r, ya.r, s8.r * yb.r), s0.i + fma32(s7.i, ya.r, s8.i * yb.r)};
+    cpx s6 = {fma32(s10.i, ya.i, s9.i * yb.i), -fma32(s10.r, ya.i, s9.r * yb.i)};
+    p[m + k] = c_sub(s5, s6);
+    p[4 * m + k] = c_add(s5, s6);
+    cpx s11 = {s0.r + fma32(s7.r, yb.r, s8.r * ya.r), s0.i + fma32(s7.i, yb.r, s8.i * ya.r)};
+    cpx s12 = {fma32(s9.i, ya.i, (-s10.i) * yb.i), fma32(s10.r, yb.i, (-s9.r) * ya.i)};
+    p[2 * m + k] = c_add(s11, s12);
+    p[3 * m + k] = c_sub(s11, s12);
+    p[k] = f0;
+  }
+}
+
+// `nt` independent transforms of size nfft = 480 >> shift laid out back to back in `f`.
+MB_DEV void team_fft(Team tm, cpx* f, int shift, int nt) {
+  const uint8_t* fac = kFftFactors[shift];
+  const int nfft = 480 >> shift;
+  int fstride[6];
+  fstride[0] = 1;
+  int stages = 0, m;
+  do {
+    int p = fac[2 * stages];
+    m = fac[2 * stages + 1];
+    fstride[stages + 1] = fstride[stages] * p;
+    stages++;
+  } while (m != 1);
+  m = fac[2 * stages - 1];
+  for (int i = stages - 1; i >= 0; i--) {
+    int mm = i != 0 ? fac[2 * i - 1] : 1;
+    int radix = fac[2 * i], groups = fstride[i], fs = fstride[i] << shift;
+    int per = groups * m;  // butterflies per transform in this stage
+    for (int idx = tm.tid; idx < per * nt; idx += tm.n) {
+      int t = idx / per, r = idx - t * per;
+      int g = r / m, k = r - g * m;
+      bfly_one(f + t * nfft + g * mm, radix, k, m, fs);
+    }
+    MB_SYNC();
+    m = mm;
+  }
+}
+
+struct ImdctSmem {
+  float io[MAX_N];     // freq in, time-domain samples out
+  float F[MAX_N];      // FFT work: 480 complex points
+};
+
+struct ImdctParams {
+  const uint32_t* rec;
+  const FrameMeta* meta;
+  const float* xbuf;        // [frame][XBUF_STRIDE] freq
+  float* series;            // [lane][CC][series_stride]
+  uint32_t series_stride;
+  int CC;
+};
+
+// Unit u of frame f: coded channel u when both the packet and the decoder are stereo, else the single (down-mixed or
+// duplicated) spectrum.
+MB_DEV void celt_imdct_unit(Team tm, ImdctSmem* sm, uint32_t f, int u, const ImdctParams& P) {
+  const FrameMeta meta = P.meta[f];
+  if (!(meta.flags & 1u)) return;
+  const uint32_t* r = P.rec + rec_index(f, 0);
+  const uint32_t h0 = r[S_HDR0 * 32], status = r[S_STATUS * 32];
+  const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), start = (int)MB_H0_START(h0), end = (int)MB_ST_END(status);
+  const int transient = (int)MB_H0_TRANSIENT(h0), silence = (int)MB_H0_SILENCE(h0);
+  const int M = 1 << lm, N = M * SHORT_MDCT, CC = P.CC;
+  const int nch = (CC == 2 && C == 2) ? 2 : 1;
+  if (u >= nch) return;
+  const float* xrow = P.xbuf + (size_t)f * XBUF_STRIDE;
+  const int planned = r[S_PLAN * 32] != 0xffffffffu;
+  const int lo = (silence || !planned) ? 0 : M * eband(start), hi = (silence || !planned) ? 0 : M * eband(imin(end, NB_EBANDS));
+  const int downmix = CC == 1 && C == 2;
+  float* X = sm->io;
+  for (int i = tm.tid; i < N; i += tm.n) {
+    float v = 0.f;
+    if (i >= lo && i < hi) {
+      v = xrow[u * N + i];
+      if (downmix) v = 0.5f * (v + xrow[N + i]);
+    }
+    X[i] = v;
+  }
+  MB_SYNC();
+  const int nbk = transient ? M : 1;                  // short blocks
+  const int shift = transient ? MAX_LM : MAX_LM - lm;
+  const int n2 = 960 >> shift, n4 = n2 >> 1;          // per-block MDCT size / FFT size
+  cpx* F = (cpx*)sm->F;
+  const uint32_t* twb = kMdctTwiddles960Bits + kMdctTwOff[shift];
+  const int16_t* br = shift == 0 ? kFftBitrev480 : shift == 1 ? kFftBitrev240 : shift == 2 ? kFftBitrev120 : kFftBitrev60;
+  // pre-rotation + bit-reversal + conjugate (ifft = conj . fft . conj)
+  for (int idx = tm.tid; idx < nbk * n4; idx += tm.n) {
+    int b = idx / n4, i = idx - b * n4;
+    const float* in = X + b;          // element k of block b is in[k * nbk]
+    float x1 = in[(2 * i) * nbk], x2 = in[(n2 - 1 - 2 * i) * nbk];
+    float t0 = bits2f(twb[i]), t1 = bits2f(twb[n4 + i]);
+    cpx v;
+    v.r = x2 * t0 + x1 * t1;
+    v.i = -(x1 * t0 - x2 * t1);
+    F[b * n4 + br[i]] = v;
+  }
+  MB_SYNC();
+  team_fft(tm, F, shift, nbk);
+  // post-rotation and window fold against the zero-filled overlap, back into the staging row
+  float* O = X;
+  for (int idx = tm.tid; idx < nbk * n4; idx += tm.n) {
+    int b = idx / n4, i = idx - b * n4;
+    cpx v = F[b * n4 + i];
+    v.i = -v.i;
+    float t0 = bits2f(twb[i]), t1 = bits2f(twb[n4 + i]);
+    float yr = v.r * t0 + v.i * t1;     // temp[2i]
+    float yi = v.r * t1 - v.i * t0;     // temp[n2-1-2i]
+    float* ob = O + b * n2;
+    const int lim = nbk > 1 ? 120 : N;
+#pragma unroll
+    for (int q = 0; q < 2; q++) {
+      int k = q ? n2 - 1 - 2 * i : 2 * i;
+      float val = q ? yi : yr;
+      // temp[k] lands at out[60 + k]; the fold rewrites out[0..120) from temp[0..60)
+      if (k < 60) {
+        float w1 = bits2f(kWindow120Bits[59 - k]), w2 = bits2f(kWindow120Bits[60 + k]);
+        ob[59 - k] = 0.f * w2 - val * w1;     // out[i] = x2*w2 - x1*w1 with x2 = 0
+        ob[60 + k] = 0.f * w1 + val * w2;     // out[119-i] = x2*w1 + x1*w2
+      } else if (60 + k < lim) {
+        ob[60 + k] = val;
+      }
+    }
+  }
+  MB_SYNC();
+  const float SIG_SAT = 536870911.0f;
+  for (int cc = 0; cc < CC; cc++) {
+    if (nch == 2 && cc != u) continue;
+    float* out = P.series + ((size_t)meta.lane * CC + cc) * P.series_stride + HIST + meta.sample_off;
+    for (int i = tm.tid; i < N; i += tm.n) {
+      float o = O[i];
+      out[i] = o < -SIG_SAT ? -SIG_SAT : (o > SIG_SAT ? SIG_SAT : o);
+    }
+  }
+}
+
+}  // namespace mb

@@ -16,7 +16,8 @@
 #define MB_MEM __device__ __forceinline__
 #define MB_DEV_NOINLINE __device__ __noinline__
 #define MB_TBL static __device__ const
-#define MB_SYNC() __syncwarp()   /* a thread team is one warp (mb_celt_recon.cuh) */
+#define MB_SYNC() __syncwarp()   /* warp-sized thread teams (mb_celt_bands.cuh, mb_celt_imdct.cuh) */
+#define MB_CTA_SYNC() __syncthreads()
 #define MB_ON_DEVICE 1
 #else
 #define MB_DEV static inline
@@ -24,6 +25,7 @@
 #define MB_DEV_NOINLINE static
 #define MB_TBL static const
 #define MB_SYNC() ((void)0)
+#define MB_CTA_SYNC() ((void)0)
 #define MB_ON_DEVICE 0
 #endif
 
@@ -59,8 +61,11 @@ enum {
   S_NODES = S_BANDB + 21,       // CAP_NODES words
   CAP_NODES = 1344,             // 21 bands x (1 stereo split + 2 x (15 splits + 16 leaves)) rounded up
   CAP_LEAVES = 704,             // 21 bands x 2 x 16 rounded up
-  S_LEAVES = S_NODES + CAP_NODES,  // 3 words per leaf: index, gain bits, packed geometry
-  REC_SLOTS = S_LEAVES + 3 * CAP_LEAVES,
+  S_LEAVES = S_NODES + CAP_NODES,  // 3 words per leaf: index, gain bits (collapse mask after the PVQ pass), packed geometry
+  S_PLAN = S_LEAVES + 3 * CAP_LEAVES,  // 1 word: operation words written by the band plan (0xffffffff: overflow)
+  S_OPS = S_PLAN + 1,              // CAP_OPS words: the band plan's operation list (mb_celt_plan.cuh)
+  CAP_OPS = 2048,
+  REC_SLOTS = S_OPS + CAP_OPS,
 };
 
 // S_HDR0 fields

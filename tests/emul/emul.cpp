@@ -9,7 +9,7 @@
 
 #include <vector>
 
-#include "../../mousiki_b200/csrc/mb_celt_recon.cuh"
+#include "../../mousiki_b200/csrc/mb_celt_imdct.cuh"
 #include "../../mousiki_b200/csrc/mb_celt_tail.cuh"
 #include "../../mousiki_b200/csrc/mb_frame.cuh"
 
@@ -40,13 +40,22 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   for (uint32_t j = 0; j < n_lanes; j++)
     celt_energy_lane(j, n_lanes, n_ticks, nullptr, rec.data(), st.data(), nullptr, en.data(), meta.data(), samples_out, final_range_out, quirks);
   // phase 2b
-  ReconSmem* sm = new ReconSmem;
-  ReconParams rp;
-  rp.rec = rec.data(); rp.en = en.data(); rp.meta = meta.data(); rp.series = series.data(); rp.series_stride = series_stride;
-  rp.CC = CC; rp.quirks = quirks; rp.iy_dbg = iy_dbg; rp.x_dbg = x_dbg;
   Team tm = {0, 1};
-  for (uint32_t f = 0; f < F; f++) celt_recon_frame(tm, sm, f, rp);
-  delete sm;
+  std::vector<float> xbuf((size_t)F * XBUF_STRIDE, 0.f), xstage(2 * MAX_N);
+  PvqParams pq; pq.rec = rec.data(); pq.meta = meta.data(); pq.xbuf = xbuf.data(); pq.iy_dbg = iy_dbg;
+  for (uint32_t f = 0; f < F; f++) celt_pvq_frame(tm, xstage.data(), f, pq);
+  PlanParams pl; pl.rec = rec.data(); pl.en = en.data(); pl.meta = meta.data();
+  for (uint32_t f = 0; f < F; f++) celt_plan_frame(f, pl);
+  BandsSmem* bsm = new BandsSmem;
+  BandsParams bp; bp.rec = rec.data(); bp.en = en.data(); bp.meta = meta.data(); bp.xbuf = xbuf.data(); bp.x_dbg = x_dbg;
+  for (uint32_t f = 0; f < F; f++) celt_bands_frame(tm, bsm, f, bp);
+  delete bsm;
+  ImdctSmem* ism = new ImdctSmem;
+  ImdctParams ip; ip.rec = rec.data(); ip.meta = meta.data(); ip.xbuf = xbuf.data(); ip.series = series.data();
+  ip.series_stride = series_stride; ip.CC = CC;
+  for (uint32_t f = 0; f < F; f++)
+    for (int u = 0; u < CC; u++) celt_imdct_unit(tm, ism, f, u, ip);
+  delete ism;
   // phase 2c
   std::vector<float> tmp;
   float* out = pcm;
