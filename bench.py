@@ -160,7 +160,8 @@ ALG_BYTES = {
     "k_plan": 1200 + 1200,              # node stream + leaf masks in, operation list out
     "k_bands": 1200 + 504 + 7680 + 7680,  # operation list + energies + spectrum row in, freq row out (in place)
     "k_imdct": 7680 + 7680,             # freq row in, 2 x 960 f32 time-domain samples out
-    "k_tail": 7680 + 7680,              # time-domain samples in, interleaved f32 PCM out
+    "k_comb": 7680 + 3840,              # time-domain samples in, post-filtered samples out (about half the frames filter)
+    "k_deemph": 7680 + 7680,            # post-filtered samples in, interleaved f32 PCM out
 }
 PATH_BYTES = 30200
 

@@ -7,7 +7,8 @@
 //   k_plan     lane per frame                       phase 2b(ii)  (mb_celt_plan.cuh)
 //   k_bands    warp per frame                       phase 2b(iii) (mb_celt_bands.cuh)
 //   k_imdct    warp per frame-channel               phase 2b(iv)  (mb_celt_imdct.cuh)
-//   k_tail     lane per stream-channel  phase 2c (mb_celt_tail.cuh)
+//   k_comb     warp per stream-channel              phase 2c(i)   (mb_celt_tail.cuh)
+//   k_deemph   lane per stream-channel, smem tiles  phase 2c(ii)
 //   k_softclip / k_to_i16               i16 output path only
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo (see __graft_entry__.build()).
 #include <cuda_runtime.h>
@@ -78,12 +79,135 @@ __global__ void __launch_bounds__(32 * IMDCT_WARPS) k_imdct(ImdctParams P, uint3
   celt_imdct_unit(tm, &sm[threadIdx.x >> 5], unit / nu, (int)(unit % nu), P);
 }
 
-__global__ void __launch_bounds__(64) k_tail(TailParams P) {
-  uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
-  uint32_t lane = idx / (uint32_t)P.CC;
-  int c = (int)(idx - lane * (uint32_t)P.CC);
-  if (lane >= P.n_lanes) return;
-  celt_tail_lane(lane, c, P);
+// phase 2c(i): one warp per stream-channel, 4 per CTA
+constexpr int COMB_WARPS = 4;
+__global__ void __launch_bounds__(32 * COMB_WARPS) k_comb(TailParams P) {
+  __shared__ CombSmem sm[COMB_WARPS];
+  const uint32_t idx = blockIdx.x * COMB_WARPS + (threadIdx.x >> 5);
+  if (idx >= P.n_lanes * (uint32_t)P.CC) return;
+  Team tm = {(int)(threadIdx.x & 31), 32};
+  celt_comb_channel(tm, &sm[threadIdx.x >> 5], idx / (uint32_t)P.CC, (int)(idx % (uint32_t)P.CC), P);
+}
+
+// phase 2c(ii): one lane per stream-channel. A warp owns 32 neighbouring stream-channels (16 stereo streams) and moves
+// their signals through a [32 rows x CH samples] shared-memory tile: rows arrive by cp.async as coalesced 16-byte
+// pieces (double-buffered: the next tile is in flight while the current one is filtered), the serial one-pole
+// recursion runs down each lane's own row with 128-bit shared-memory accesses (row pitch CH + 4 words: conflict-free),
+// and the interleaved PCM leaves as coalesced 128-bit stores. Same arithmetic as celt_deemph_lane.
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+constexpr int DE_WARPS = 2;
+template <int CH>
+__global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
+  constexpr int PITCH = CH + 4;                 // floats per tile row
+  constexpr int PIECES = CH / 4;                // 16-byte pieces per row
+  extern __shared__ __align__(16) unsigned char de_smem[];
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  float* tiles = (float*)de_smem + (size_t)w * 2 * 32 * PITCH;       // two tiles per warp
+  __shared__ const float* row_x_[DE_WARPS][32];
+  __shared__ float* row_out_[DE_WARPS][32];
+  __shared__ int row_n_[DE_WARPS][32];
+  const float** row_x = row_x_[w];
+  float** row_out = row_out_[w];
+  int* row_n = row_n_[w];
+  const int CC = P.CC;
+  const uint32_t total = P.n_lanes * (uint32_t)CC;
+  const uint32_t idx0 = (blockIdx.x * DE_WARPS + w) * 32;
+  if (idx0 >= total) return;
+  const uint32_t idx = idx0 + l;
+  const bool live = idx < total;
+  const uint32_t lane = live ? idx / (uint32_t)CC : 0;
+  const int c = live ? (int)(idx % (uint32_t)CC) : 0;
+  const uint32_t sid = P.lane_stream ? P.lane_stream[lane] : lane;
+  StreamState& st = P.st_all[sid];
+  const float* ser = P.series + ((size_t)lane * CC + c) * P.series_stride + HIST;
+  Deemph d = {live ? st.preemph_mem[c] : 0.f, P.gain, P.apply_gain};
+
+  auto issue = [&](int k0, float* tile) {   // rows' [k0, k0 + CH) -> tile, 16 bytes per lane per piece
+#pragma unroll 4
+    for (int r = 0; r < 32; r++) {
+      const float* xr = row_x[r];
+      const int nr = row_n[r];
+#pragma unroll
+      for (int q = l; q < PIECES; q += 32)
+        if (k0 + 4 * q < nr) cp_async16(tile + r * PITCH + 4 * q, xr + k0 + 4 * q);
+    }
+    cp_async_commit();
+  };
+
+  for (uint32_t t = 0; t < P.n_ticks; t++) {
+    int N = 0;
+    const float* x = nullptr;
+    float* out = nullptr;
+    if (live) {
+      const uint32_t f = t * P.n_lanes + lane;
+      const FrameMeta m = P.meta[f];
+      if (m.flags & 1u) {
+        N = SHORT_MDCT << (int)MB_H0_LM(P.rec[rec_index(f, S_HDR0)]);
+        x = ser + m.sample_off;
+        const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
+        out = P.pcm_f32 ? P.pcm_f32 + (size_t)p * P.pcm_stride : nullptr;
+      }
+    }
+    __syncwarp();
+    row_x[l] = x; row_out[l] = out; row_n[l] = N;
+    const int max_n = __reduce_max_sync(0xffffffffu, N);
+    __syncwarp();
+    if (max_n == 0) continue;
+    issue(0, tiles);
+    int buf = 0;
+    for (int k0 = 0; k0 < max_n; k0 += CH, buf ^= 1) {
+      float* tile = tiles + buf * 32 * PITCH;
+      const bool more = k0 + CH < max_n;
+      if (more) { issue(k0 + CH, tiles + (buf ^ 1) * 32 * PITCH); cp_async_wait<1>(); } else cp_async_wait<0>();
+      __syncwarp();
+      {  // the serial recursion, this lane's row
+        const int cnt = min(CH, N - k0);
+        float4* row = (float4*)(tile + l * PITCH);
+        for (int q = 0; 4 * q < cnt; q++) {
+          float4 v = row[q];
+          v.x = d.step(v.x); v.y = d.step(v.y); v.z = d.step(v.z); v.w = d.step(v.w);
+          row[q] = v;
+        }
+      }
+      __syncwarp();
+      if (CC == 2) {
+#pragma unroll 2
+        for (int r = 0; r < 32; r += 2) {
+          float* o = row_out[r];
+          const int cnt = min(CH, row_n[r] - k0);
+          if (!o || cnt <= 0) continue;
+          o += (size_t)k0 * 2;
+          const float* tx = tile + r * PITCH;
+          const float* ty = tx + PITCH;
+          if (((uintptr_t)o & 15u) == 0) {
+            for (int j = 2 * l; j < cnt; j += 64) {   // float4 = (x[j], y[j], x[j+1], y[j+1])
+              const float2 a = *(const float2*)(tx + j), b = *(const float2*)(ty + j);
+              *(float4*)(o + 2 * j) = make_float4(a.x, b.x, a.y, b.y);
+            }
+          } else {
+            for (int e = l; e < 2 * cnt; e += 32) o[e] = (e & 1) ? ty[e >> 1] : tx[e >> 1];
+          }
+        }
+      } else {
+#pragma unroll 4
+        for (int r = 0; r < 32; r++) {
+          float* o = row_out[r];
+          const int cnt = min(CH, row_n[r] - k0);
+          if (!o || cnt <= 0) continue;
+          const float* tx = tile + r * PITCH;
+          for (int j = l; j < cnt; j += 32) o[k0 + j] = tx[j];
+        }
+      }
+      __syncwarp();
+    }
+  }
+  if (live) st.preemph_mem[c] = d.mem;
 }
 
 // opus_decode's soft clip (src/opus.rs:16-140): one lane per stream, its packets in tick order.
@@ -226,6 +350,8 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
   auto fail = [&](int code) { bd_destroy(h); return code; };
   if (cudaSetDevice(h->device) != cudaSuccess) return fail(BD_ERR_CUDA);
   if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) return fail(BD_ERR_CUDA);
+  if (cudaFuncSetAttribute(k_deemph<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(DE_WARPS * 2 * 32 * (128 + 4) * sizeof(float))) != cudaSuccess)
+    return fail(BD_ERR_CUDA);
   if (h->states.ensure((size_t)cfg->n_streams * sizeof(StreamState)) != cudaSuccess) return fail(BD_ERR_ALLOC);
   if (h->hist.ensure((size_t)cfg->n_streams * h->CC * HIST * sizeof(float)) != cudaSuccess) return fail(BD_ERR_ALLOC);
   k_reset<<<cfg->n_streams, 128, 0, h->own_stream>>>(h->states.as<StreamState>(), h->hist.as<float>(), nullptr, cfg->n_streams, h->CC);
@@ -371,10 +497,18 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     tp.st_all = h->states.as<StreamState>(); tp.hist = h->hist.as<float>(); tp.series = h->series.as<float>();
     tp.series_stride = series_stride; tp.n_lanes = n_lanes; tp.n_ticks = nt; tp.CC = CC; tp.gain = h->gain;
     tp.apply_gain = h->cfg.gain_q8 != 0; tp.pcm_f32 = pcm; tp.pcm_stride = pcm_stride;
-    h->prof_begin(BD_K_TAIL, s);
-    k_tail<<<(n_lanes * CC + 63) / 64, 64, 0, s>>>(tp);
+    h->prof_begin(BD_K_COMB, s);
+    k_comb<<<(n_lanes * CC + COMB_WARPS - 1) / COMB_WARPS, 32 * COMB_WARPS, 0, s>>>(tp);
     h->prof_end(s);
-    h->launches += 7;
+    h->prof_begin(BD_K_DEEMPH, s);
+    {
+      // tile width by the number of warps: wide tiles (more bytes in flight per warp) while warps are scarce
+      const uint32_t de_ctas = (n_lanes * CC + 32 * DE_WARPS - 1) / (32 * DE_WARPS);
+      if (de_ctas <= 4u * 148u) k_deemph<128><<<de_ctas, 32 * DE_WARPS, DE_WARPS * 2 * 32 * (128 + 4) * sizeof(float), s>>>(tp);
+      else k_deemph<32><<<de_ctas, 32 * DE_WARPS, DE_WARPS * 2 * 32 * (32 + 4) * sizeof(float), s>>>(tp);
+    }
+    h->prof_end(s);
+    h->launches += 8;
     if (d_pcm_i16) {
       h->prof_begin(BD_K_SOFTCLIP, s);
       k_softclip<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, nt, map, d_lane_stream, h->meta.as<FrameMeta>(), samples,

@@ -1,4 +1,5 @@
-// Phase 2c — time-domain tail, one lane per stream-channel, ticks in order.
+// Phase 2c — time-domain tail, ticks in order: (i) post-filter, one warp per stream-channel; (ii) de-emphasis, one
+// lane per stream-channel over shared-memory tiles.
 //
 // Replaces:
 //   comb_filter_in_place / comb_filter_const_in_place   src/celt/celt.rs:133-174, 332-443
@@ -17,46 +18,6 @@ namespace mb {
 MB_TBL float kTapsetGains[9] = {0.3066406250f, 0.2170410156f, 0.1296386719f, 0.4638671875f, 0.2680664062f, 0.f,
                                 0.7998046875f, 0.1000976562f, 0.f};
 
-MB_DEV void comb_const(float* x, int n, int T, float g10, float g11, float g12) {
-  float x4 = x[-T - 2], x3 = x[-T - 1], x2 = x[-T], x1 = x[-T + 1];
-  for (int i = 0; i < n; i++) {
-    float x0 = x[i - T + 2];
-    float acc = fma32(g10, x2, x[i]);
-    acc = fma32(g11, x1 + x3, acc);
-    acc = fma32(g12, x0 + x4, acc);
-    x[i] = acc;
-    x4 = x3; x3 = x2; x2 = x1; x1 = x0;
-  }
-}
-// x points at the first sample to filter; history is at negative offsets.
-MB_DEV void comb_filter(float* x, int n, int T0, int T1, float g0, float g1, int tapset0, int tapset1) {
-  if (n == 0) return;
-  if (g0 == 0.f && g1 == 0.f) return;
-  T0 = imax(T0, COMB_MINPERIOD);
-  T1 = imax(T1, COMB_MINPERIOD);
-  float g00 = g0 * kTapsetGains[tapset0 * 3], g01 = g0 * kTapsetGains[tapset0 * 3 + 1], g02 = g0 * kTapsetGains[tapset0 * 3 + 2];
-  float g10 = g1 * kTapsetGains[tapset1 * 3], g11 = g1 * kTapsetGains[tapset1 * 3 + 1], g12 = g1 * kTapsetGains[tapset1 * 3 + 2];
-  float x1 = x[-T1 + 1], x2 = x[-T1], x3 = x[-T1 - 1], x4 = x[-T1 - 2];
-  int overlap = imin(OVERLAP, n);
-  if (g0 == g1 && T0 == T1 && tapset0 == tapset1) overlap = 0;
-  for (int i = 0; i < overlap; i++) {
-    float x0 = x[i - T1 + 2];
-    float w = bits2f(kWindow120Bits[i]);
-    float f = w * w;
-    float omf = 1.0f - f;
-    float acc = fma32(omf * g00, x[i - T0], x[i]);
-    acc = fma32(omf * g01, x[i - T0 + 1] + x[i - T0 - 1], acc);
-    acc = fma32(omf * g02, x[i - T0 + 2] + x[i - T0 - 2], acc);
-    acc = fma32(f * g10, x2, acc);
-    acc = fma32(f * g11, x1 + x3, acc);
-    acc = fma32(f * g12, x0 + x4, acc);
-    x[i] = acc;
-    x4 = x3; x3 = x2; x2 = x1; x1 = x0;
-  }
-  if (g1 == 0.f) return;
-  if (overlap < n) comb_const(x + overlap, n - overlap, T1, g10, g11, g12);
-}
-
 struct TailParams {
   const uint32_t* rec;
   const FrameMeta* meta;
@@ -74,20 +35,65 @@ struct TailParams {
   uint32_t pcm_stride;         // elements between packets
 };
 
-// lane = stream slot, c = channel. The two channels of a stream run in neighbouring threads; each owns
-// a private copy of the (identical) post-filter parameters so that no thread reads what another writes.
-MB_DEV void celt_tail_lane(uint32_t lane, int c, const TailParams& P) {
+// ---------------------------------------------------------------- phase 2c(i): post-filter, one warp per stream-channel
+// The comb filter reads its own output T-2 .. T+2 samples back with T >= 15, so a run of min(T0, T1) - 2 >= 13
+// consecutive samples has no dependency inside the run: the warp computes such a run in parallel, then the next.
+// The channel's signal lives in a shared-memory buffer [HIST history | current frame].
+struct CombSmem { float buf[HIST + MAX_N]; };
+
+// x = first sample to filter inside the shared buffer; the history sits at negative offsets.
+MB_DEV void team_comb_filter(Team tm, float* x, int n, int T0, int T1, float g0, float g1, int tapset0, int tapset1) {
+  if (n == 0) return;
+  if (g0 == 0.f && g1 == 0.f) return;
+  T0 = imax(T0, COMB_MINPERIOD);
+  T1 = imax(T1, COMB_MINPERIOD);
+  const float g00 = g0 * kTapsetGains[tapset0 * 3], g01 = g0 * kTapsetGains[tapset0 * 3 + 1], g02 = g0 * kTapsetGains[tapset0 * 3 + 2];
+  const float g10 = g1 * kTapsetGains[tapset1 * 3], g11 = g1 * kTapsetGains[tapset1 * 3 + 1], g12 = g1 * kTapsetGains[tapset1 * 3 + 2];
+  int overlap = imin(OVERLAP, n);
+  if (g0 == g1 && T0 == T1 && tapset0 == tapset1) overlap = 0;
+  const int run0 = imin(T0, T1) - 2;
+  for (int s = 0; s < overlap; s += run0) {
+    const int e = imin(s + run0, overlap);
+    for (int i = s + tm.tid; i < e; i += tm.n) {
+      const float w = bits2f(kWindow120Bits[i]);
+      const float f = w * w;
+      const float omf = 1.0f - f;
+      float acc = fma32(omf * g00, x[i - T0], x[i]);
+      acc = fma32(omf * g01, x[i - T0 + 1] + x[i - T0 - 1], acc);
+      acc = fma32(omf * g02, x[i - T0 + 2] + x[i - T0 - 2], acc);
+      acc = fma32(f * g10, x[i - T1], acc);
+      acc = fma32(f * g11, x[i - T1 + 1] + x[i - T1 - 1], acc);
+      acc = fma32(f * g12, x[i - T1 + 2] + x[i - T1 - 2], acc);
+      x[i] = acc;
+    }
+    MB_SYNC();
+  }
+  if (g1 == 0.f) return;
+  const int run1 = T1 - 2;
+  for (int s = overlap; s < n; s += run1) {
+    const int e = imin(s + run1, n);
+    for (int i = s + tm.tid; i < e; i += tm.n) {
+      float acc = fma32(g10, x[i - T1], x[i]);
+      acc = fma32(g11, x[i - T1 + 1] + x[i - T1 - 1], acc);
+      acc = fma32(g12, x[i - T1 + 2] + x[i - T1 - 2], acc);
+      x[i] = acc;
+    }
+    MB_SYNC();
+  }
+}
+
+MB_DEV void celt_comb_channel(Team tm, CombSmem* sm, uint32_t lane, int c, const TailParams& P) {
   const int CC = P.CC;
   const uint32_t sid = P.lane_stream ? P.lane_stream[lane] : lane;
   StreamState& st = P.st_all[sid];
-  float* ser = P.series + ((size_t)lane * CC + c) * P.series_stride;
+  float* ser = P.series + ((size_t)lane * CC + c) * P.series_stride + HIST;
   float* hist = P.hist + ((size_t)sid * CC + c) * HIST;
-  for (int i = 0; i < HIST; i++) ser[i] = hist[i];
+  float* buf = sm->buf;
+  for (int i = tm.tid; i < HIST; i += tm.n) buf[i] = hist[i];
   StreamState::Pf& pf = st.pf[c];
   int pf_period = pf.period, pf_period_old = pf.period_old, pf_tapset = pf.tapset, pf_tapset_old = pf.tapset_old;
   float pf_gain = pf.gain, pf_gain_old = pf.gain_old;
-  float mem = st.preemph_mem[c];
-  uint32_t total = 0;
+  MB_SYNC();
   for (uint32_t t = 0; t < P.n_ticks; t++) {
     const uint32_t f = t * P.n_lanes + lane;
     const FrameMeta m = P.meta[f];
@@ -97,38 +103,75 @@ MB_DEV void celt_tail_lane(uint32_t lane, int c, const TailParams& P) {
     const int lm = (int)MB_H0_LM(h0), N = SHORT_MDCT << lm;
     const int new_pitch = (int)MB_H1_PITCH(h1), new_tapset = (int)MB_H0_TAPSET(h0);
     const float new_gain = 0.09375f * (float)MB_H0_QG1(h0);
-    float* x = ser + HIST + m.sample_off;
+    float* xg = ser + m.sample_off;
+    float* x = buf + HIST;
+    for (int i = tm.tid; i < N; i += tm.n) x[i] = xg[i];
+    MB_SYNC();
     pf_period = imax(pf_period, COMB_MINPERIOD);
     pf_period_old = imax(pf_period_old, COMB_MINPERIOD);
-    int first = imin(SHORT_MDCT, N);
-    comb_filter(x, first, pf_period_old, pf_period, pf_gain_old, pf_gain, imax(pf_tapset_old, 0), imax(pf_tapset, 0));
-    if (lm != 0 && first < N)
-      comb_filter(x + first, N - first, pf_period, new_pitch, pf_gain, new_gain, imax(pf_tapset, 0), imax(new_tapset, 0));
+    const int first = imin(SHORT_MDCT, N);
+    const int second = (lm != 0 && first < N) ? N - first : 0;
+    const int touched = (pf_gain_old != 0.f || pf_gain != 0.f) || (second && (pf_gain != 0.f || new_gain != 0.f));
+    team_comb_filter(tm, x, first, pf_period_old, pf_period, pf_gain_old, pf_gain, imax(pf_tapset_old, 0), imax(pf_tapset, 0));
+    if (second)
+      team_comb_filter(tm, x + first, second, pf_period, new_pitch, pf_gain, new_gain, imax(pf_tapset, 0), imax(new_tapset, 0));
     pf_period_old = pf_period; pf_gain_old = pf_gain; pf_tapset_old = pf_tapset;
     pf_period = new_pitch; pf_gain = new_gain; pf_tapset = new_tapset;
     if (lm != 0) { pf_period_old = pf_period; pf_gain_old = pf_gain; pf_tapset_old = pf_tapset; }
-    // de-emphasis + scaling + interleave (celt_decoder.rs:2157-2299)
-    const float coef0 = 0.8500061035f, inv = 1.0f / 32768.0f;
-    if (P.pcm_f32) {
-      const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
-      float* out = P.pcm_f32 + (size_t)p * P.pcm_stride + c;
-      for (int j = 0; j < N; j++) {
-        float tv = x[j] + mem + 1.0e-30f;
-        mem = coef0 * tv;
-        float v = tv * inv;
-        if (P.apply_gain) v *= P.gain;
-        out[(size_t)j * CC] = v;
-      }
-    } else {
-      for (int j = 0; j < N; j++) { float tv = x[j] + mem + 1.0e-30f; mem = coef0 * tv; }
+    if (touched)
+      for (int i = tm.tid; i < N; i += tm.n) xg[i] = x[i];
+    // slide the window: the last HIST samples become the history of the next frame
+    for (int i0 = 0; i0 < HIST; i0 += tm.n) {
+      const int i = i0 + tm.tid;
+      float v = 0.f;
+      if (i < HIST) v = buf[i + N];
+      MB_SYNC();
+      if (i < HIST) buf[i] = v;
     }
-    total = m.sample_off + (uint32_t)N;
+    MB_SYNC();
   }
-  // persist: last HIST post-filtered samples + filter memories
-  for (int i = 0; i < HIST; i++) hist[i] = ser[total + i];
-  st.preemph_mem[c] = mem;
-  pf.period = pf_period; pf.period_old = pf_period_old; pf.tapset = pf_tapset; pf.tapset_old = pf_tapset_old;
-  pf.gain = pf_gain; pf.gain_old = pf_gain_old;
+  for (int i = tm.tid; i < HIST; i += tm.n) hist[i] = buf[i];
+  if (tm.tid == 0) {
+    pf.period = pf_period; pf.period_old = pf_period_old; pf.tapset = pf_tapset; pf.tapset_old = pf_tapset_old;
+    pf.gain = pf_gain; pf.gain_old = pf_gain_old;
+  }
+}
+
+// ---------------------------------------------------------------- phase 2c(ii): de-emphasis, one lane per stream-channel
+// deemphasis (celt_decoder.rs:2157-2299): y = x + mem + 1e-30; mem = 0.8500061 * y; out = y / 32768 (* gain).
+struct Deemph {
+  float mem, gain;
+  int apply_gain;
+  MB_MEM float step(float xv) {
+    const float tv = xv + mem + 1.0e-30f;
+    mem = 0.8500061035f * tv;
+    float v = tv * (1.0f / 32768.0f);
+    if (apply_gain) v *= gain;
+    return v;
+  }
+};
+
+// Plain per-lane form (host emulation, and the reference shape of the device tile code in mb_api.cu).
+MB_DEV void celt_deemph_lane(uint32_t lane, int c, const TailParams& P) {
+  const int CC = P.CC;
+  const uint32_t sid = P.lane_stream ? P.lane_stream[lane] : lane;
+  StreamState& st = P.st_all[sid];
+  const float* ser = P.series + ((size_t)lane * CC + c) * P.series_stride + HIST;
+  Deemph d = {st.preemph_mem[c], P.gain, P.apply_gain};
+  for (uint32_t t = 0; t < P.n_ticks; t++) {
+    const uint32_t f = t * P.n_lanes + lane;
+    const FrameMeta m = P.meta[f];
+    if (!(m.flags & 1u)) continue;
+    const int N = SHORT_MDCT << (int)MB_H0_LM(P.rec[rec_index(f, S_HDR0)]);
+    const float* x = ser + m.sample_off;
+    const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
+    float* out = P.pcm_f32 ? P.pcm_f32 + (size_t)p * P.pcm_stride + c : nullptr;
+    for (int j = 0; j < N; j++) {
+      const float v = d.step(x[j]);
+      if (out) out[(size_t)j * CC] = v;
+    }
+  }
+  st.preemph_mem[c] = d.mem;
 }
 
 // float -> int16 (src/celt/float_cast.rs:38-41)

@@ -64,8 +64,12 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   tp.rec = rec.data(); tp.meta = meta.data(); tp.pkt_map = nullptr; tp.lane_stream = nullptr; tp.st_all = st.data(); tp.hist = hist.data();
   tp.series = series.data(); tp.series_stride = series_stride; tp.n_lanes = n_lanes; tp.n_ticks = n_ticks; tp.CC = CC;
   tp.gain = 1.f; tp.apply_gain = 0; tp.pcm_f32 = out; tp.pcm_stride = pcm_stride;
+  CombSmem* csm = new CombSmem;
   for (uint32_t j = 0; j < n_lanes; j++)
-    for (int c = 0; c < CC; c++) celt_tail_lane(j, c, tp);
+    for (int c = 0; c < CC; c++) celt_comb_channel(tm, csm, j, c, tp);
+  delete csm;
+  for (uint32_t j = 0; j < n_lanes; j++)
+    for (int c = 0; c < CC; c++) celt_deemph_lane(j, c, tp);
   if (pcm16) {
     for (uint32_t j = 0; j < n_lanes; j++)
       for (uint32_t t = 0; t < n_ticks; t++) {
