@@ -103,7 +103,7 @@ uint32_t bd_last_launch_count(const bd_handle* h);
  * bracketed by CUDA events on the launching stream. bd_profile_read synchronises, returns the accumulated
  * milliseconds and launch counts per kernel id (arrays of BD_K_COUNT) since the last read, and resets them. */
 enum { BD_K_PARSE = 0, BD_K_ENERGY = 1, BD_K_PVQ = 2, BD_K_PLAN = 3, BD_K_BANDS = 4, BD_K_IMDCT = 5, BD_K_COMB = 6, BD_K_DEEMPH = 7,
-       BD_K_SOFTCLIP = 8, BD_K_TO_I16 = 9, BD_K_COUNT = 10 };
+       BD_K_CLIP_I16 = 8, BD_K_COUNT = 9 };
 int bd_profile_enable(bd_handle* h, int on);
 int bd_profile_read(bd_handle* h, double* ms_out, uint32_t* launches_out);
 

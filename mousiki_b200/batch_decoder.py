@@ -193,7 +193,7 @@ class BatchDecoder:
                                           pcm_stride, C.c_void_p(d_samples), C.c_void_p(d_final_range), C.c_void_p(stream or None))
         self._check(rc, "bd_decode_grid_dev")
 
-    KERNELS = ("k_parse", "k_energy", "k_pvq", "k_plan", "k_bands", "k_imdct", "k_comb", "k_deemph", "k_softclip", "k_to_i16")
+    KERNELS = ("k_parse", "k_energy", "k_pvq", "k_plan", "k_bands", "k_imdct", "k_comb", "k_deemph", "k_clip_i16")
 
     def profile(self, on=True):
         self._check(self._lib.bd_profile_enable(self._h, int(on)), "bd_profile_enable")

@@ -9,7 +9,7 @@
 //   k_imdct    warp per frame-channel               phase 2b(iv)  (mb_celt_imdct.cuh)
 //   k_comb     warp per stream-channel              phase 2c(i)   (mb_celt_tail.cuh)
 //   k_deemph   lane per stream-channel, smem tiles  phase 2c(ii)
-//   k_softclip / k_to_i16               i16 output path only
+//   k_clip_i16 warp per stream                          soft clip + float -> int16 (i16 output path only)
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo (see __graft_entry__.build()).
 #include <cuda_runtime.h>
 #include <stdio.h>
@@ -210,22 +210,58 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
   if (live) st.preemph_mem[c] = d.mem;
 }
 
-// opus_decode's soft clip (src/opus.rs:16-140): one lane per stream, its packets in tick order.
-__global__ void __launch_bounds__(64) k_softclip(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
-                                                 const uint32_t* __restrict__ lane_stream, const FrameMeta* __restrict__ meta,
-                                                 const int32_t* __restrict__ samples_out, StreamState* st, float* pcm, uint32_t pcm_stride,
-                                                 int CC) {
-  uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
+// opus_decode's output stage (src/opus_decoder.rs:1679-1712): soft clip (src/opus.rs:16-140) then float -> int16
+// (src/celt/float_cast.rs:38-41). One warp per stream, its packets in tick order: the packet's interleaved float PCM is
+// staged in shared memory; a packet with no sample outside [-1, 1] and no carried-over nonlinearity (the common case)
+// skips the serial clipper entirely; otherwise one lane per channel runs it in shared memory. The int16 PCM leaves as
+// coalesced 32-bit stores.
+constexpr int CLIP_WARPS = 4;
+__global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
+                                                              const uint32_t* __restrict__ lane_stream, const FrameMeta* __restrict__ meta,
+                                                              const int32_t* __restrict__ samples_out, StreamState* st,
+                                                              const float* __restrict__ pcm, int16_t* __restrict__ pcm16, uint32_t pcm_stride,
+                                                              int CC) {
+  __shared__ __align__(16) float buf_[CLIP_WARPS][2 * MAX_N];
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  const uint32_t lane = blockIdx.x * CLIP_WARPS + w;
   if (lane >= n_lanes) return;
+  float* buf = buf_[w];
   StreamState& s = st[lane_stream ? lane_stream[lane] : lane];
+  float mem = l < 2 ? s.softclip_mem[l] : 0.f;
   for (uint32_t t = 0; t < n_ticks; t++) {
-    uint32_t f = t * n_lanes + lane;
+    const uint32_t f = t * n_lanes + lane;
     if (!(meta[f].flags & 1u)) continue;
-    uint32_t p = pkt_map ? pkt_map[f] : f;
-    int n = samples_out[p];
+    const uint32_t p = pkt_map ? pkt_map[f] : f;
+    const int n = samples_out[p];
     if (n <= 0) continue;
-    soft_clip_packet(pcm + (size_t)p * pcm_stride, n, CC, s.softclip_mem);
+    const int total = n * CC;
+    const float* src = pcm + (size_t)p * pcm_stride;
+    int over = 0;
+    for (int i = l; i < total; i += 32) {
+      float v = src[i];
+      over |= !(v >= -1.f && v <= 1.f);
+      buf[i] = v < -2.f ? -2.f : (v > 2.f ? 2.f : v);
+    }
+    over |= mem != 0.f;
+    over = __any_sync(0xffffffffu, over);
+    __syncwarp();
+    if (over) {
+      if (l < CC) soft_clip_channel(buf + l, n, CC, mem);
+      __syncwarp();
+    }
+    int16_t* dst = pcm16 + (size_t)p * pcm_stride;
+    if ((((uintptr_t)dst) & 3u) == 0) {
+      for (int i = 2 * l; i + 1 < total; i += 64) {
+        const uint32_t lo = (uint16_t)float2int16(buf[i]), hi = (uint16_t)float2int16(buf[i + 1]);
+        *(uint32_t*)(dst + i) = lo | (hi << 16);
+      }
+      if ((total & 1) && l == 0) dst[total - 1] = float2int16(buf[total - 1]);
+    } else {
+      for (int i = l; i < total; i += 32) dst[i] = float2int16(buf[i]);
+    }
+    __syncwarp();
   }
+  if (l < 2) s.softclip_mem[l] = mem;
 }
 // decode_float leaves the clipper memory cleared (src/opus_decoder.rs:1411-1417)
 __global__ void k_clear_softclip(uint32_t n_lanes, const uint32_t* __restrict__ lane_stream, StreamState* st) {
@@ -233,15 +269,6 @@ __global__ void k_clear_softclip(uint32_t n_lanes, const uint32_t* __restrict__ 
   if (lane >= n_lanes) return;
   StreamState& s = st[lane_stream ? lane_stream[lane] : lane];
   s.softclip_mem[0] = s.softclip_mem[1] = 0.f;
-}
-__global__ void k_to_i16(const float* __restrict__ in, int16_t* __restrict__ out, const int32_t* __restrict__ samples_out,
-                         uint32_t n_packets, uint32_t pcm_stride, int CC) {
-  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  size_t total = (size_t)n_packets * pcm_stride;
-  if (i >= total) return;
-  uint32_t p = (uint32_t)(i / pcm_stride), k = (uint32_t)(i - (size_t)p * pcm_stride);
-  int n = samples_out[p];
-  if (n > 0 && k < (uint32_t)(n * CC)) out[i] = float2int16(in[i]);
 }
 __global__ void k_reset(StreamState* st, float* hist, const uint32_t* __restrict__ ids, uint32_t n, int CC) {
   uint32_t i = blockIdx.x;
@@ -283,6 +310,9 @@ struct bd_handle {
   std::string err;
   uint32_t launches = 0;
   cudaStream_t own_stream = nullptr;
+  cudaStream_t copy_stream = nullptr;   // device -> host PCM of pass k overlaps the kernels of pass k + 1
+  std::vector<cudaEvent_t> pass_events;
+  struct PassOut { bool on = false; char* host_pcm = nullptr; const char* dev_pcm = nullptr; size_t elem = 0; } pass_out;
   DevBuf states, hist, rec, en, meta, series, xbuf;
   // staging for the host-buffer entry points
   DevBuf d_arena, d_offsets, d_pkt_map, d_lane_stream, d_flags, d_pcm, d_pcm16, d_samples, d_range, d_ids, d_dbg_iy, d_dbg_x;
@@ -350,6 +380,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
   auto fail = [&](int code) { bd_destroy(h); return code; };
   if (cudaSetDevice(h->device) != cudaSuccess) return fail(BD_ERR_CUDA);
   if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) return fail(BD_ERR_CUDA);
+  if (cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess) return fail(BD_ERR_CUDA);
   if (cudaFuncSetAttribute(k_deemph<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(DE_WARPS * 2 * 32 * (128 + 4) * sizeof(float))) != cudaSuccess)
     return fail(BD_ERR_CUDA);
   if (h->states.ensure((size_t)cfg->n_streams * sizeof(StreamState)) != cudaSuccess) return fail(BD_ERR_ALLOC);
@@ -368,6 +399,8 @@ void bd_destroy(bd_handle* h) {
   for (DevBuf* b : all) b->release();
   for (auto& sp : h->prof_spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
   for (auto e : h->prof_pool) cudaEventDestroy(e);
+  for (auto e : h->pass_events) cudaEventDestroy(e);
+  if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
 }
@@ -510,22 +543,24 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     h->prof_end(s);
     h->launches += 8;
     if (d_pcm_i16) {
-      h->prof_begin(BD_K_SOFTCLIP, s);
-      k_softclip<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, nt, map, d_lane_stream, h->meta.as<FrameMeta>(), samples,
-                                                    h->states.as<StreamState>(), pcm, pcm_stride, CC);
+      h->prof_begin(BD_K_CLIP_I16, s);
+      k_clip_i16<<<(n_lanes + CLIP_WARPS - 1) / CLIP_WARPS, 32 * CLIP_WARPS, 0, s>>>(
+          n_lanes, nt, map, d_lane_stream, h->meta.as<FrameMeta>(), samples, h->states.as<StreamState>(), pcm,
+          d_pcm_i16 + shift * pcm_stride, pcm_stride, CC);
       h->prof_end(s);
       h->launches += 1;
     } else {
       k_clear_softclip<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, d_lane_stream, h->states.as<StreamState>());
       h->launches += 1;
     }
-  }
-  if (d_pcm_i16) {
-    size_t total = (size_t)n_packets * pcm_stride;
-    h->prof_begin(BD_K_TO_I16, s);
-    k_to_i16<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(pcm_f32, d_pcm_i16, d_samples, n_packets, pcm_stride, CC);
-    h->prof_end(s);
-    h->launches += 1;
+    if (h->pass_out.on) {  // packets of this pass are cells [cell0, cell0 + cells): ship their PCM while the next pass computes
+      const size_t k = t0 / ticks_per_pass;
+      while (h->pass_events.size() <= k) { cudaEvent_t e; CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->pass_events.push_back(e); }
+      CK(cudaEventRecord(h->pass_events[k], s));
+      CK(cudaStreamWaitEvent(h->copy_stream, h->pass_events[k], 0));
+      const size_t off = cell0 * pcm_stride * h->pass_out.elem, bytes = (size_t)cells * pcm_stride * h->pass_out.elem;
+      CK(cudaMemcpyAsync(h->pass_out.host_pcm + off, h->pass_out.dev_pcm + off, bytes, cudaMemcpyDeviceToHost, h->copy_stream));
+    }
   }
   CK(cudaGetLastError());
   return BD_OK;
@@ -569,16 +604,22 @@ static int decode_host(bd_handle* h, const uint8_t* arena, const uint32_t* offse
     if (++h->h_count[sid] > n_ticks) n_ticks = h->h_count[sid];
   }
   const uint32_t n_lanes = (uint32_t)h->h_lane_stream.size();
-  const bool identity = n_ticks == 1;  // every stream at most once: cell == packet
+  bool identity = n_ticks == 1;  // every stream at most once: cell == packet
   const uint32_t* d_map = nullptr;
   if (!identity) {
     h->h_pkt_map.assign((size_t)n_lanes * n_ticks, 0xffffffffu);
     for (uint32_t sid : h->h_lane_stream) h->h_count[sid] = 0;
+    bool grid_order = (size_t)n_packets == (size_t)n_lanes * n_ticks;
     for (uint32_t p = 0; p < n_packets; p++) {
       uint32_t sid = stream_ids[p];
       uint32_t t = h->h_count[sid]++;
-      h->h_pkt_map[(size_t)t * n_lanes + h->h_lane_of_stream[sid]] = p;
+      const size_t cell = (size_t)t * n_lanes + h->h_lane_of_stream[sid];
+      h->h_pkt_map[cell] = p;
+      grid_order = grid_order && cell == p;
     }
+    identity = grid_order;  // packets already arrive tick-major in lane order: no indirection needed
+  }
+  if (!identity) {
     CK(h->d_pkt_map.ensure(h->h_pkt_map.size() * 4));
     CK(cudaMemcpyAsync(h->d_pkt_map.p, h->h_pkt_map.data(), h->h_pkt_map.size() * 4, cudaMemcpyHostToDevice, s));
     d_map = h->d_pkt_map.as<uint32_t>();
@@ -618,15 +659,26 @@ static int decode_host(bd_handle* h, const uint8_t* arena, const uint32_t* offse
     if (h->dbg_x_host) { CK(h->d_dbg_x.ensure(n_cells * 2 * MAX_N * 4)); CK(cudaMemsetAsync(h->d_dbg_x.p, 0, n_cells * 2 * MAX_N * 4, s)); d_dbg_x = h->d_dbg_x.as<float>(); }
   }
   CK(cudaMemsetAsync(h->d_samples.p, 0, (size_t)n_packets * 4, s));
+  // cell order == packet order: each pass's PCM is one contiguous block, copied out on a second stream as soon as
+  // the pass is done
+  const bool overlap_out = identity;
+  h->pass_out.on = overlap_out;
+  h->pass_out.host_pcm = pcm_f32 ? (char*)pcm_f32 : (char*)pcm_i16;
+  h->pass_out.dev_pcm = pcm_f32 ? (const char*)d_f32 : (const char*)d_i16;
+  h->pass_out.elem = pcm_f32 ? sizeof(float) : sizeof(int16_t);
   int rc = decode_grid_device(h, h->d_arena.as<uint8_t>(), h->d_offsets.as<uint32_t>(), d_map, d_flags, n_lanes, n_ticks,
                               h->d_lane_stream.as<uint32_t>(), d_f32, d_i16, pcm_stride, h->d_samples.as<int32_t>(),
                               h->d_range.as<uint32_t>(), n_packets, s, d_dbg_iy, d_dbg_x);
-  if (rc != BD_OK) return rc;
-  if (pcm_f32) CK(cudaMemcpyAsync(pcm_f32, d_f32, pcm_elems * sizeof(float), cudaMemcpyDeviceToHost, s));
-  else CK(cudaMemcpyAsync(pcm_i16, d_i16, pcm_elems * sizeof(int16_t), cudaMemcpyDeviceToHost, s));
+  h->pass_out.on = false;
+  if (rc != BD_OK) { cudaStreamSynchronize(h->copy_stream); return rc; }
+  if (!overlap_out) {
+    if (pcm_f32) CK(cudaMemcpyAsync(pcm_f32, d_f32, pcm_elems * sizeof(float), cudaMemcpyDeviceToHost, s));
+    else CK(cudaMemcpyAsync(pcm_i16, d_i16, pcm_elems * sizeof(int16_t), cudaMemcpyDeviceToHost, s));
+  }
   CK(cudaMemcpyAsync(samples_out, h->d_samples.p, (size_t)n_packets * 4, cudaMemcpyDeviceToHost, s));
   CK(cudaMemcpyAsync(final_range_out, h->d_range.p, (size_t)n_packets * 4, cudaMemcpyDeviceToHost, s));
   CK(cudaStreamSynchronize(s));
+  CK(cudaStreamSynchronize(h->copy_stream));
   if (h->dbg_max) {
     // debug captures are indexed by grid cell; scatter them back to packet order
     std::vector<int32_t> iy;

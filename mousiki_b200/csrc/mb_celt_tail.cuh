@@ -185,51 +185,53 @@ MB_DEV int16_t float2int16(float v) {
 #endif
 }
 
-// opus_pcm_soft_clip_impl (src/opus.rs:16-140), one lane per stream, all its packets of this call in
-// order, operating in place on the interleaved float PCM of each packet.
+// opus_pcm_soft_clip_impl (src/opus.rs:16-140) for one channel of one packet, in place on interleaved float PCM
+// (x = first sample of the channel, C = interleave stride); `a` is the channel's declip_mem. The +-2 clamp of the
+// whole packet has to be applied before (soft_clip_packet / the device kernel do it in parallel).
+MB_DEV void soft_clip_channel(float* x, int N, int C, float& a_io) {
+  float a = a_io;
+  for (int i = 0; i < N; i++) {
+    if (x[i * C] * a >= 0) break;
+    x[i * C] = x[i * C] + a * x[i * C] * x[i * C];
+  }
+  int curr = 0;
+  float x0 = x[0];
+  for (;;) {
+    int i;
+    for (i = curr; i < N; i++)
+      if (!(x[i * C] >= -1.f && x[i * C] <= 1.f)) break;
+    if (i == N) { a = 0; break; }
+    int peak_pos = i, start = i, end = i;
+    float maxval = fabsf(x[i * C]);
+    while (start > 0 && x[i * C] * x[(start - 1) * C] >= 0) start--;
+    while (end < N && x[i * C] * x[end * C] >= 0) {
+      if (fabsf(x[end * C]) > maxval) { maxval = fabsf(x[end * C]); peak_pos = end; }
+      end++;
+    }
+    int special = (start == 0 && x[i * C] * x[0] >= 0);
+    a = (maxval - 1) / (maxval * maxval);
+    a += a * 2.4e-7f;
+    if (x[i * C] > 0) a = -a;
+    for (i = start; i < end; i++) x[i * C] = x[i * C] + a * x[i * C] * x[i * C];
+    if (special && peak_pos >= 2) {
+      float offset = x0 - x[0];
+      float delta = offset / (float)peak_pos;
+      for (i = curr; i < peak_pos; i++) {
+        offset -= delta;
+        x[i * C] += offset;
+        x[i * C] = x[i * C] < -1.f ? -1.f : (x[i * C] > 1.f ? 1.f : x[i * C]);
+      }
+    }
+    curr = end;
+    if (curr == N) break;
+  }
+  a_io = a;
+}
+
 MB_DEV void soft_clip_packet(float* x_, int N, int C, float* declip_mem) {
   if (C < 1 || N < 1) return;
   for (int i = 0; i < N * C; i++) x_[i] = x_[i] < -2.f ? -2.f : (x_[i] > 2.f ? 2.f : x_[i]);
-  for (int c = 0; c < C; c++) {
-    float* x = x_ + c;
-    float a = declip_mem[c];
-    for (int i = 0; i < N; i++) {
-      if (x[i * C] * a >= 0) break;
-      x[i * C] = x[i * C] + a * x[i * C] * x[i * C];
-    }
-    int curr = 0;
-    float x0 = x[0];
-    for (;;) {
-      int i;
-      for (i = curr; i < N; i++)
-        if (!(x[i * C] >= -1.f && x[i * C] <= 1.f)) break;
-      if (i == N) { a = 0; break; }
-      int peak_pos = i, start = i, end = i;
-      float maxval = fabsf(x[i * C]);
-      while (start > 0 && x[i * C] * x[(start - 1) * C] >= 0) start--;
-      while (end < N && x[i * C] * x[end * C] >= 0) {
-        if (fabsf(x[end * C]) > maxval) { maxval = fabsf(x[end * C]); peak_pos = end; }
-        end++;
-      }
-      int special = (start == 0 && x[i * C] * x[0] >= 0);
-      a = (maxval - 1) / (maxval * maxval);
-      a += a * 2.4e-7f;
-      if (x[i * C] > 0) a = -a;
-      for (i = start; i < end; i++) x[i * C] = x[i * C] + a * x[i * C] * x[i * C];
-      if (special && peak_pos >= 2) {
-        float offset = x0 - x[0];
-        float delta = offset / (float)peak_pos;
-        for (i = curr; i < peak_pos; i++) {
-          offset -= delta;
-          x[i * C] += offset;
-          x[i * C] = x[i * C] < -1.f ? -1.f : (x[i * C] > 1.f ? 1.f : x[i * C]);
-        }
-      }
-      curr = end;
-      if (curr == N) break;
-    }
-    declip_mem[c] = a;
-  }
+  for (int c = 0; c < C; c++) soft_clip_channel(x_ + c, N, C, declip_mem[c]);
 }
 
 }  // namespace mb
