@@ -1349,6 +1349,9 @@ void CeltDecoder::reset() {  // types.rs:989-1043
   for (int i = 0; i < 2 * NB_EBANDS; i++) { old_ebands[i] = 0.f; old_log_e[i] = old_log_e2[i] = -28.0f; background_log_e[i] = 0.f; }
 }
 
+// window_48000_960.rs (for the front end's smooth_fade, opus_decoder.rs:100-135)
+const float* celt_window120() { init_tables_once(); return g_window; }
+
 // celt_decoder.rs:2751-3163 (prepare_frame) + :3209-4137 (celt_decode_with_ec_dred_impl)
 int celt_decode_with_ec(CeltDecoder* st, const uint8_t* data, int len, float* pcm, int frame_size, EcDec* ext_dec, int accum) {
   init_tables_once();

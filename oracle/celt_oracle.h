@@ -69,4 +69,6 @@ struct CeltDecoder {
 int celt_decode_with_ec(CeltDecoder* st, const uint8_t* data, int len, float* pcm, int frame_size,
                         EcDec* ec, int accum);
 
+const float* celt_window120();
+
 }  // namespace orc

@@ -17,6 +17,7 @@
 #include <vector>
 
 #include "celt_oracle.h"
+#include "silk_oracle.h"
 
 namespace orc {
 
@@ -143,6 +144,8 @@ static int packet_parse(const uint8_t* data, int len, int self_delimited, Parsed
 struct OpusDecoder {
   int fs = 48000, channels = 2;
   CeltDecoder celt;
+  SilkDecoder silk;
+  SilkDecControl dec_control;
   int mode = 0, prev_mode = 0, bandwidth = 0, frame_size = 0, stream_channels = 0, prev_redundancy = 0;
   int last_packet_duration = 0, decode_gain = 0;
   uint32_t range_final = 0;
@@ -153,6 +156,10 @@ struct OpusDecoder {
     if (!(fs_ == 48000 || fs_ == 24000 || fs_ == 16000 || fs_ == 12000 || fs_ == 8000) || (ch != 1 && ch != 2)) return OPUS_BAD_ARG;
     fs = fs_; channels = ch;
     celt.init(ch, 48000 / fs_);
+    silk.reset(1);
+    dec_control = SilkDecControl();  // opus_decoder.rs:1438-1448
+    dec_control.n_channels_api = ch; dec_control.n_channels_internal = 0; dec_control.api_sample_rate = fs_;
+    dec_control.internal_sample_rate = 0; dec_control.payload_size_ms = 0;
     stream_channels = ch;
     frame_size = fs_ / 400;
     reset();
@@ -160,38 +167,135 @@ struct OpusDecoder {
   }
   void reset() {  // opus_decoder.rs:1451-1476
     celt.reset();
+    silk.reset(0);
     stream_channels = channels;
     bandwidth = 0; mode = 0; prev_mode = 0; frame_size = fs / 400; prev_redundancy = 0; last_packet_duration = 0;
     range_final = 0; softclip_mem[0] = softclip_mem[1] = 0;
   }
 
-  // opus_decoder.rs:453-1133, CELT-only arm.
+  // celt_decoder.rs decode entry used for redundancy / silence frames (no shared range decoder)
+  int celt_frame(const uint8_t* data, int len, float* out, int n, int accum) { return celt_decode_with_ec(&celt, data, len, out, n, nullptr, accum); }
+
+  // opus_decoder.rs:100-135
+  void smooth_fade(const float* in1, const float* in2, float* out, int overlap) {
+    int inc = 48000 / fs;
+    for (int c = 0; c < channels; c++)
+      for (int i = 0; i < overlap; i++) {
+        if (i * inc >= 120) break;
+        float w = celt_window120()[i * inc] * celt_window120()[i * inc];
+        out[i * channels + c] = w * in2[i * channels + c] + (1.0f - w) * in1[i * channels + c];
+      }
+  }
+
+  // opus_decoder.rs:453-1133. PLC (data == null) and the transitions that call it are not restated (-5).
   int decode_frame(const uint8_t* data, int len, float* pcm, int fsz, int decode_fec) {
     int F20 = fs / 50, F10 = F20 / 2, F5 = F10 / 2, F2_5 = F5 / 2;
     if (fsz < F2_5) return OPUS_BUFFER_TOO_SMALL;
     fsz = fsz < fs / 25 * 3 ? fsz : fs / 25 * 3;
     if (data == nullptr || len <= 1) return OPUS_UNIMPLEMENTED;  // PLC row (F2)
-    int audiosize = frame_size;
-    int md = mode;
-    if (md != MODE_CELT_ONLY) return OPUS_UNIMPLEMENTED;        // SILK / hybrid rows
+    if (decode_fec) return OPUS_UNIMPLEMENTED;
+    int audiosize = frame_size, md = mode, bw = bandwidth;
+    int celt_only = md == MODE_CELT_ONLY, prev_celt_only = prev_mode == MODE_CELT_ONLY;
     EcDec dec;
     dec.init(data, (uint32_t)len);
-    if (prev_mode > 0 && prev_mode != MODE_CELT_ONLY && !prev_redundancy) return OPUS_UNIMPLEMENTED;  // transition needs PLC
+    int transition = prev_mode > 0 && ((celt_only && !prev_celt_only && !prev_redundancy) || (!celt_only && prev_celt_only));
+    if (transition && celt_only) return OPUS_UNIMPLEMENTED;  // needs decode_frame(None) = PLC
     if (audiosize > fsz) return OPUS_BAD_ARG;
+    int celt_accum = !celt_only, redundancy = 0, celt_to_silk = 0, have_range_final = 0;
+    uint32_t redundant_rng = 0, silk_range_final = 0;
+    const uint8_t* red_data = nullptr; int red_bytes = 0;
+    std::vector<float> redundant_audio;
+    if (!celt_only) {
+      if (audiosize < F10) return OPUS_UNIMPLEMENTED;  // pcm_too_small path only reachable through PLC sizes
+      int payload_ms = 1000 * audiosize / fs; if (payload_ms < 10) payload_ms = 10;
+      dec_control.n_channels_api = channels; dec_control.api_sample_rate = fs; dec_control.payload_size_ms = payload_ms;
+      dec_control.n_channels_internal = stream_channels;
+      dec_control.internal_sample_rate = md == MODE_SILK_ONLY ? (bw == BW_NB ? 8000 : (bw == BW_MB ? 12000 : 16000)) : 16000;
+      if (prev_celt_only) silk.reset(0);
+      std::vector<int16_t> so((size_t)audiosize * channels);
+      int decoded = 0;
+      while (decoded < audiosize) {
+        int r = silk.decode(&dec_control, SILK_FLAG_DECODE_NORMAL, decoded == 0, &dec, so.data() + (size_t)decoded * channels);
+        if (r == -5) return OPUS_UNIMPLEMENTED;
+        if (r <= 0) return OPUS_INTERNAL_ERROR;
+        decoded += r;
+      }
+      for (int i = 0; i < decoded * channels; i++) pcm[i] = (float)so[i] * (1.0f / 32768.0f);  // silk_int16_to_res
+      int tell = dec.tell();
+      if (tell + 17 + (md == MODE_HYBRID ? 20 : 0) <= 8 * len) {
+        redundancy = md == MODE_HYBRID ? dec.bit_logp(12) : 1;
+        if (redundancy) {
+          celt_to_silk = dec.bit_logp(1);
+          int bytes = md == MODE_HYBRID ? (int)dec.uint(256) + 2 : len - ((dec.tell() + 7) >> 3);
+          if (bytes > len || bytes < 0) return OPUS_BAD_ARG;
+          red_bytes = bytes;
+          int cutoff = len - bytes;
+          red_data = data + cutoff;
+          len = cutoff;
+          if (len * 8 < dec.tell()) { len = 0; redundancy = 0; red_data = nullptr; red_bytes = 0; }
+          if (red_bytes > 0) {
+            if (dec.storage < (uint32_t)red_bytes) return OPUS_BAD_ARG;
+            dec.storage -= (uint32_t)red_bytes;
+          }
+        }
+      }
+      if (len > 1 && md == MODE_SILK_ONLY) { silk_range_final = dec.rng; have_range_final = 1; }
+      if (redundancy) transition = 0;
+      else if (transition) return OPUS_UNIMPLEMENTED;  // CELT -> SILK without redundancy: PLC cross-fade
+    }
+    int start_band = celt_only ? 0 : 17;
     int endband = 21;
-    switch (bandwidth) { case BW_NB: endband = 13; break; case BW_MB: case BW_WB: endband = 17; break; case BW_SWB: endband = 19; break; case BW_FB: endband = 21; break; }
+    switch (bw) { case BW_NB: endband = 13; break; case BW_MB: case BW_WB: endband = 17; break; case BW_SWB: endband = 19; break; case BW_FB: endband = 21; break; }
     celt.end_band = endband;
     celt.stream_channels = stream_channels;
-    celt.start_band = 0;
-    if (md != prev_mode && prev_mode > 0 && !prev_redundancy) celt.reset();
-    int celt_frame = audiosize < F20 ? audiosize : F20;
-    if (decode_fec) return OPUS_UNIMPLEMENTED;
-    int ret = celt_decode_with_ec(&celt, data, len, pcm, celt_frame, &dec, 0);
-    if (ret < 0) return ret;
-    if (ret != celt_frame) return OPUS_INTERNAL_ERROR;
+    if (redundancy && celt_to_silk) {
+      redundant_audio.assign((size_t)F5 * channels, 0.f);
+      celt.start_band = 0;
+      int r = celt_frame(red_data, red_bytes, redundant_audio.data(), F5, 0);
+      if (r != F5) return r < 0 ? r : OPUS_INTERNAL_ERROR;
+      redundant_rng = celt.rng;
+    }
+    celt.start_band = start_band;
+    uint32_t celt_final_range = 0;
+    if (md == MODE_SILK_ONLY) {
+      if (prev_mode == MODE_HYBRID && !(redundancy && celt_to_silk && prev_redundancy)) {
+        celt.start_band = 0;
+        static const uint8_t silence[2] = {0xFF, 0xFF};
+        int r = celt_frame(silence, 2, pcm, F2_5, celt_accum);
+        if (r != F2_5) return r < 0 ? r : OPUS_INTERNAL_ERROR;
+      }
+    } else {
+      if (md != prev_mode && prev_mode > 0 && !prev_redundancy) celt.reset();
+      int celt_n = audiosize < F20 ? audiosize : F20;
+      int ret = celt_decode_with_ec(&celt, data, len, pcm, celt_n, &dec, celt_accum);
+      if (ret < 0) return ret;
+      if (ret != celt_n) return OPUS_INTERNAL_ERROR;
+      if (len > 1) celt_final_range = celt.rng;
+    }
+    if (redundancy && !celt_to_silk) {
+      redundant_audio.assign((size_t)F5 * channels, 0.f);
+      celt.reset();
+      celt.start_band = 0;
+      int r = celt_frame(red_data, red_bytes, redundant_audio.data(), F5, 0);
+      if (r != F5) return r < 0 ? r : OPUS_INTERNAL_ERROR;
+      redundant_rng = celt.rng;
+    }
+    int fade = F2_5 * channels;
+    if (redundancy) {
+      if (!celt_to_silk) {
+        float* p = pcm + (size_t)(audiosize - F2_5) * channels;
+        std::vector<float> cur(p, p + fade);
+        smooth_fade(cur.data(), redundant_audio.data() + fade, p, F2_5);
+      } else if (prev_mode != MODE_SILK_ONLY || prev_redundancy) {
+        for (int i = 0; i < fade; i++) pcm[i] = redundant_audio[i];
+        std::vector<float> tail(pcm + fade, pcm + 2 * fade);
+        smooth_fade(redundant_audio.data() + fade, tail.data(), pcm + fade, F2_5);
+      }
+    }
+    uint32_t final_range = len > 1 ? (have_range_final ? silk_range_final : celt_final_range) : 0;
     prev_mode = md;
-    prev_redundancy = 0;
-    range_final = len > 1 ? celt.rng : 0;
+    prev_redundancy = redundancy && !celt_to_silk;
+    range_final = len > 1 ? final_range ^ redundant_rng : 0;
     return audiosize;
   }
 
@@ -292,6 +396,7 @@ void* orc_create(int fs, int channels, uint32_t quirks) {
   OpusDecoder* d = new OpusDecoder();
   if (d->init(fs, channels) < 0) { delete d; return nullptr; }
   d->celt.quirks = quirks;
+  d->silk.quirks = quirks;
   return d;
 }
 void orc_destroy(void* h) { delete (OpusDecoder*)h; }
@@ -321,6 +426,30 @@ int orc_decode_i16(void* h, const uint8_t* data, int len, int16_t* pcm, int fram
   if (ret > 0) for (int i = 0; i < ret * d->channels; i++) pcm[i] = float2int16(tmp[i]);
   return ret;
 }
+
+
+// ---- SILK stand-alone hooks for the known-answer tests (tests/test_silk_oracle_kat.py) ----
+void orc_silk_nlsf_decode(int wb, const int8_t* indices, int16_t* nlsf_q15, uint32_t quirks) {
+  silk_nlsf_decode(nlsf_q15, indices, wb ? silk_cb_wb() : silk_cb_nb_mb(), quirks);
+}
+void orc_silk_nlsf2a(const int16_t* nlsf_q15, int order, int16_t* a_q12, uint32_t quirks) { silk_nlsf2a(a_q12, nlsf_q15, order, quirks); }
+int32_t orc_silk_inverse_pred_gain(const int16_t* a_q12, int order) { return order == 0 ? 1 << 30 : silk_lpc_inverse_pred_gain(a_q12, order); }
+int32_t orc_silk_log2lin(int32_t x) { return silk_log2lin(x); }
+int orc_silk_gains_dequant(const int8_t* ind, int prev, int conditional, int nb_subfr, int32_t* gains) {
+  int8_t p = (int8_t)prev;
+  silk_gains_dequant(gains, ind, &p, conditional, nb_subfr);
+  return p;
+}
+void orc_silk_decode_pitch(int lag_index, int contour, int fs_khz, int nb_subfr, int32_t* lags) { silk_decode_pitch(lag_index, contour, lags, fs_khz, nb_subfr); }
+// resampler: fresh state, one call of silk_resampler on `n` input samples; returns produced samples
+int orc_silk_resample(int fs_in, int fs_out, const int16_t* in, int n, int16_t* out, int32_t* iir_state /*6, nullable*/) {
+  SilkResampler r;
+  if (r.init(fs_in, fs_out) < 0) return -1;
+  int p = r.run(out, in, n);
+  if (iir_state) memcpy(iir_state, r.s_iir, sizeof(r.s_iir));
+  return p;
+}
+void orc_set_quirks(void* h, uint32_t quirks) { OpusDecoder* d = (OpusDecoder*)h; d->celt.quirks = quirks; d->silk.quirks = quirks; }
 
 // Stage dump of the LAST decoded CELT frame (enable before decoding).
 void orc_trace_enable(void* h, int on) { OpusDecoder* d = (OpusDecoder*)h; d->celt.trace = on ? &d->trace : nullptr; }
@@ -365,6 +494,7 @@ int orc_decode_grid(int fs, int channels, uint32_t quirks, const uint8_t* arena,
       OpusDecoder d;
       d.init(fs, channels);
       d.celt.quirks = quirks;
+      d.silk.quirks = quirks;
       for (int t = 0; t < n_ticks; t++) {
         size_t p = (size_t)t * n_lanes + j;
         const uint8_t* pkt = arena + offsets[p];
