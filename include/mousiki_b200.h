@@ -36,8 +36,11 @@ extern "C" {
 #define BD_OPUS_INVALID_PACKET (-4)
 #define BD_OPUS_UNIMPLEMENTED (-5)
 
-/* Behaviour switches: bit set = mousiki's float decoder as written, clear = libopus (DESIGN.md "Quirks"). */
-#define BD_QUIRKS_MOUSIKI 0x7fu
+/* Behaviour switches: bit set = mousiki's decoder as written, clear = libopus (DESIGN.md "Quirks").
+ * bits 0..6: CELT Q1,Q2,Q5..Q9; bits 8..11: SILK S1 (nlsf_decode.rs:109 16-bit SMULBB), S2 (nlsf2a.rs:42-60 cosine
+ * ordering), S3 (code_signs.rs:112-118 sign decode stops at frame_length), S4 (dec_api.rs:150-154 mono->stereo
+ * re-initialises both channels). */
+#define BD_QUIRKS_MOUSIKI 0xf7fu
 
 typedef struct bd_handle bd_handle;
 
@@ -103,7 +106,7 @@ uint32_t bd_last_launch_count(const bd_handle* h);
  * bracketed by CUDA events on the launching stream. bd_profile_read synchronises, returns the accumulated
  * milliseconds and launch counts per kernel id (arrays of BD_K_COUNT) since the last read, and resets them. */
 enum { BD_K_PARSE = 0, BD_K_ENERGY = 1, BD_K_PVQ = 2, BD_K_PLAN = 3, BD_K_BANDS = 4, BD_K_IMDCT = 5, BD_K_COMB = 6, BD_K_DEEMPH = 7,
-       BD_K_CLIP_I16 = 8, BD_K_COUNT = 9 };
+       BD_K_CLIP_I16 = 8, BD_K_SILK = 9, BD_K_COUNT = 10 };
 int bd_profile_enable(bd_handle* h, int on);
 int bd_profile_read(bd_handle* h, double* ms_out, uint32_t* launches_out);
 

@@ -17,7 +17,7 @@ from pathlib import Path
 import numpy as np
 
 _LIB_PATH = Path(__file__).resolve().parent / "libmousiki_b200.so"
-QUIRKS_MOUSIKI = 0x7F
+QUIRKS_MOUSIKI = 0xF7F
 
 OPUS_BAD_ARG, OPUS_BUFFER_TOO_SMALL, OPUS_INTERNAL_ERROR, OPUS_INVALID_PACKET, OPUS_UNIMPLEMENTED = -1, -2, -3, -4, -5
 
@@ -193,7 +193,7 @@ class BatchDecoder:
                                           pcm_stride, C.c_void_p(d_samples), C.c_void_p(d_final_range), C.c_void_p(stream or None))
         self._check(rc, "bd_decode_grid_dev")
 
-    KERNELS = ("k_parse", "k_energy", "k_pvq", "k_plan", "k_bands", "k_imdct", "k_comb", "k_deemph", "k_clip_i16")
+    KERNELS = ("k_parse", "k_energy", "k_pvq", "k_plan", "k_bands", "k_imdct", "k_comb", "k_deemph", "k_clip_i16", "k_silk")
 
     def profile(self, on=True):
         self._check(self._lib.bd_profile_enable(self._h, int(on)), "bd_profile_enable")

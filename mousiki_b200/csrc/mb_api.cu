@@ -23,6 +23,7 @@
 #include "mb_celt_imdct.cuh"
 #include "mb_celt_tail.cuh"
 #include "mb_frame.cuh"
+#include "mb_silk_out.cuh"
 
 using namespace mb;
 
@@ -279,6 +280,40 @@ __global__ void k_reset(StreamState* st, float* hist, const uint32_t* __restrict
   for (int k = threadIdx.x; k < CC * HIST; k += blockDim.x) h[k] = 0.f;
 }
 
+
+// SILK-only packets, phase 2: one lane per stream, its packets in tick order (mb_silk_synth.cuh / mb_silk_out.cuh).
+// The stream's SILK state is staged in the lane's local memory for the pass and written back at the end.
+__global__ void __launch_bounds__(64) k_silk(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
+                                             const uint32_t* __restrict__ lane_stream, const uint32_t* __restrict__ rec,
+                                             const FrameMeta* __restrict__ meta, SilkState* st_all, float* __restrict__ pcm_f32,
+                                             int16_t* __restrict__ pcm_i16, uint32_t pcm_stride, int CC, uint32_t quirks, float gain,
+                                             int apply_gain) {
+  const uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
+  if (lane >= n_lanes) return;
+  bool any = false;
+  for (uint32_t t = 0; t < n_ticks && !any; t++) any = (meta[t * n_lanes + lane].flags & 2u) != 0;
+  if (!any) return;
+  SilkState* gs = st_all + (lane_stream ? lane_stream[lane] : lane);
+  SilkState S = *gs;
+  SilkWork W;
+  for (uint32_t t = 0; t < n_ticks; t++) {
+    const uint32_t f = t * n_lanes + lane;
+    if (!(meta[f].flags & 2u)) continue;
+    const uint32_t p = pkt_map ? pkt_map[f] : f;
+    SilkPcmOut o;
+    o.f32 = pcm_f32 ? pcm_f32 + (size_t)p * pcm_stride : nullptr;
+    o.i16 = pcm_i16 ? pcm_i16 + (size_t)p * pcm_stride : nullptr;
+    o.CC = CC; o.gain = gain; o.apply_gain = apply_gain;
+    silk_synth_packet(S, W, rec + rec_index(f, 0), quirks, o);
+  }
+  *gs = S;
+}
+__global__ void k_silk_reset(SilkState* st, const uint32_t* __restrict__ ids, uint32_t n) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  silk_state_reset(st[ids ? ids[i] : i], 1);
+}
+
 // ------------------------------------------------------------------------------------------ host side
 namespace {
 
@@ -313,7 +348,7 @@ struct bd_handle {
   cudaStream_t copy_stream = nullptr;   // device -> host PCM of pass k overlaps the kernels of pass k + 1
   std::vector<cudaEvent_t> pass_events;
   struct PassOut { bool on = false; char* host_pcm = nullptr; const char* dev_pcm = nullptr; size_t elem = 0; } pass_out;
-  DevBuf states, hist, rec, en, meta, series, xbuf;
+  DevBuf states, silk_states, hist, rec, en, meta, series, xbuf;
   // staging for the host-buffer entry points
   DevBuf d_arena, d_offsets, d_pkt_map, d_lane_stream, d_flags, d_pcm, d_pcm16, d_samples, d_range, d_ids, d_dbg_iy, d_dbg_x;
   std::vector<uint32_t> h_pkt_map, h_lane_stream, h_lane_of_stream, h_epoch, h_count;
@@ -385,6 +420,8 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
     return fail(BD_ERR_CUDA);
   if (h->states.ensure((size_t)cfg->n_streams * sizeof(StreamState)) != cudaSuccess) return fail(BD_ERR_ALLOC);
   if (h->hist.ensure((size_t)cfg->n_streams * h->CC * HIST * sizeof(float)) != cudaSuccess) return fail(BD_ERR_ALLOC);
+  if (h->silk_states.ensure((size_t)cfg->n_streams * sizeof(SilkState)) != cudaSuccess) return fail(BD_ERR_ALLOC);
+  k_silk_reset<<<(cfg->n_streams + 127) / 128, 128, 0, h->own_stream>>>(h->silk_states.as<SilkState>(), nullptr, cfg->n_streams);
   k_reset<<<cfg->n_streams, 128, 0, h->own_stream>>>(h->states.as<StreamState>(), h->hist.as<float>(), nullptr, cfg->n_streams, h->CC);
   if (cudaStreamSynchronize(h->own_stream) != cudaSuccess || cudaGetLastError() != cudaSuccess) return fail(BD_ERR_CUDA);
   *out = h;
@@ -394,7 +431,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
 void bd_destroy(bd_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  DevBuf* all[] = {&h->states, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map,
+  DevBuf* all[] = {&h->states, &h->silk_states, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map,
                    &h->d_lane_stream, &h->d_flags, &h->d_pcm, &h->d_pcm16, &h->d_samples, &h->d_range, &h->d_ids, &h->d_dbg_iy, &h->d_dbg_x};
   for (DevBuf* b : all) b->release();
   for (auto& sp : h->prof_spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -418,6 +455,7 @@ int bd_reset_streams(bd_handle* h, const uint32_t* ids, uint32_t n) {
   } else n = h->cfg.n_streams;
   if (n == 0) return BD_OK;
   k_reset<<<n, 128, 0, h->own_stream>>>(h->states.as<StreamState>(), h->hist.as<float>(), d_ids, n, h->CC);
+  k_silk_reset<<<(n + 127) / 128, 128, 0, h->own_stream>>>(h->silk_states.as<SilkState>(), d_ids, n);
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(h->own_stream));
   return BD_OK;
@@ -542,6 +580,15 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     }
     h->prof_end(s);
     h->launches += 8;
+    // SILK-only packets: written straight to the caller's PCM rows. Their samples are exact int16 values scaled by
+    // 2^-15, so on the i16 path soft clip + float2int16 is the identity and the lane stores int16 directly.
+    h->prof_begin(BD_K_SILK, s);
+    k_silk<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, nt, map, d_lane_stream, h->rec.as<uint32_t>(), h->meta.as<FrameMeta>(),
+                                              h->silk_states.as<SilkState>(), d_pcm_i16 ? nullptr : pcm,
+                                              d_pcm_i16 ? d_pcm_i16 + shift * pcm_stride : nullptr, pcm_stride, CC, h->cfg.quirks, h->gain,
+                                              h->cfg.gain_q8 != 0);
+    h->prof_end(s);
+    h->launches += 1;
     if (d_pcm_i16) {
       h->prof_begin(BD_K_CLIP_I16, s);
       k_clip_i16<<<(n_lanes + CLIP_WARPS - 1) / CLIP_WARPS, 32 * CLIP_WARPS, 0, s>>>(

@@ -77,6 +77,27 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
       continue;
     }
     uint32_t h0 = r[S_HDR0 * 32];
+    // Mode switches between SILK-only and CELT-only packets go through decode_frame(None) = concealment
+    // (opus_decoder.rs:575-593, 798-809): row F2, reported per packet without touching the stream.
+    const bool silk_cell = ((status >> 16) & 1u) != 0;
+    if ((silk_cell && st.prev_mode == 1002) || (!silk_cell && (st.prev_mode == 1000 || st.prev_mode == 1001))) {
+      meta[f] = m;
+      samples_out[p] = MB_UNIMPLEMENTED;
+      final_range_out[p] = st.range_final;
+      continue;
+    }
+    if (silk_cell) {  // SILK-only packet: synthesis runs in k_silk (mb_silk_out.cuh); here only the front-end bookkeeping
+      const int sc = (int)((h0 >> 8) & 3u) * (int)((h0 >> 5) & 7u);   // frames x subframes: 2, 4, 8, 12 -> 10, 20, 40, 60 ms
+      const int N = sc * 240;
+      m.flags = 2;
+      meta[f] = m;
+      st.prev_mode = 1000;
+      st.range_final = r[S_RANGE * 32];
+      st.last_packet_duration = N;
+      samples_out[p] = N;
+      final_range_out[p] = st.range_final;
+      continue;
+    }
     const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), start = (int)MB_H0_START(h0), end = (int)MB_ST_END(status);
     const int intra = (int)MB_H0_INTRA(h0), silence = (int)MB_H0_SILENCE(h0), transient = (int)MB_H0_TRANSIENT(h0);
     const int M = 1 << lm;

@@ -5,10 +5,11 @@
 //   opus_packet_parse_impl (code 0 framing)                              src/packet.rs:316-498
 //   decode_native_with / decode_frame argument and mode checks           src/opus_decoder.rs:453-600, 1139-1367
 // Frame kinds that are not built yet are reported per packet as BD_OPUS_UNIMPLEMENTED and leave the
-// stream state untouched: SILK-only and hybrid packets (row A16), packets with more than one frame
+// stream state untouched: hybrid packets and SILK-only packets that carry a redundancy frame (row A16), packets with more than one frame
 // (codes 1-3, row F1), lost packets / FEC (row F2).
 #pragma once
 #include "mb_celt_parse.cuh"
+#include "mb_silk_parse.cuh"
 
 namespace mb {
 
@@ -25,8 +26,12 @@ MB_DEV void parse_cell(const uint8_t* arena, const uint32_t* offsets, uint32_t p
   uint32_t toc = 0;
   if (code == MB_OK) {
     toc = data[0];
-    if (!(toc & 0x80u)) code = MB_UNIMPLEMENTED;        // SILK-only / hybrid (row A16)
-    else if (toc & 3u) code = MB_UNIMPLEMENTED;         // multi-frame packets (row F1)
+    if (toc & 3u) code = MB_UNIMPLEMENTED;              // multi-frame packets (row F1)
+    else if (!(toc & 0x80u)) {
+      if ((toc & 0x60u) == 0x60u) code = MB_UNIMPLEMENTED;   // hybrid (row A16, second half)
+      else if (len - 1 <= 1) code = MB_UNIMPLEMENTED;        // concealment (src/opus_decoder.rs:491)
+      else { silk_parse_frame(data + 1, len - 1, toc, quirks, cap_per_ch, rec_base); return; }
+    }
   }
   if (code == MB_OK) {
     const int lm = (int)((toc >> 3) & 3u);

@@ -149,6 +149,7 @@ struct OpusDecoder {
   int mode = 0, prev_mode = 0, bandwidth = 0, frame_size = 0, stream_channels = 0, prev_redundancy = 0;
   int last_packet_duration = 0, decode_gain = 0;
   uint32_t range_final = 0;
+  int last_redundancy = 0;  // test hook: the last decoded frame carried a CELT redundancy frame
   float softclip_mem[2] = {0, 0};
   CeltTrace trace;
 
@@ -293,6 +294,7 @@ struct OpusDecoder {
       }
     }
     uint32_t final_range = len > 1 ? (have_range_final ? silk_range_final : celt_final_range) : 0;
+    last_redundancy = redundancy;
     prev_mode = md;
     prev_redundancy = redundancy && !celt_to_silk;
     range_final = len > 1 ? final_range ^ redundant_rng : 0;
@@ -403,6 +405,7 @@ void orc_destroy(void* h) { delete (OpusDecoder*)h; }
 void orc_reset(void* h) { ((OpusDecoder*)h)->reset(); }
 void orc_set_gain(void* h, int gain_q8) { ((OpusDecoder*)h)->decode_gain = gain_q8; }
 uint32_t orc_final_range(void* h) { return ((OpusDecoder*)h)->range_final; }
+int orc_last_redundancy(void* h) { return ((OpusDecoder*)h)->last_redundancy; }
 int orc_last_packet_duration(void* h) { return ((OpusDecoder*)h)->last_packet_duration; }
 
 // opus_decode_float (opus_decoder.rs:1803-1826)

@@ -12,6 +12,7 @@
 #include "../../mousiki_b200/csrc/mb_celt_imdct.cuh"
 #include "../../mousiki_b200/csrc/mb_celt_tail.cuh"
 #include "../../mousiki_b200/csrc/mb_frame.cuh"
+#include "../../mousiki_b200/csrc/mb_silk_out.cuh"
 
 using namespace mb;
 
@@ -70,11 +71,29 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   delete csm;
   for (uint32_t j = 0; j < n_lanes; j++)
     for (int c = 0; c < CC; c++) celt_deemph_lane(j, c, tp);
+  // SILK-only packets (k_silk): lane per stream, ticks in order
+  {
+    std::vector<SilkState> sst(n_lanes);
+    SilkWork* W = new SilkWork;
+    for (uint32_t j = 0; j < n_lanes; j++) {
+      silk_state_reset(sst[j], 1);
+      for (uint32_t t = 0; t < n_ticks; t++) {
+        const uint32_t f = t * n_lanes + j;
+        if (!(meta[f].flags & 2u)) continue;
+        SilkPcmOut o;
+        o.f32 = pcm16 ? nullptr : out + (size_t)f * pcm_stride;
+        o.i16 = pcm16 ? pcm16 + (size_t)f * pcm_stride : nullptr;
+        o.CC = CC; o.gain = 1.f; o.apply_gain = 0;
+        silk_synth_packet(sst[j], *W, rec.data() + rec_index(f, 0), quirks, o);
+      }
+    }
+    delete W;
+  }
   if (pcm16) {
     for (uint32_t j = 0; j < n_lanes; j++)
       for (uint32_t t = 0; t < n_ticks; t++) {
         uint32_t p = t * n_lanes + j;
-        if (samples_out[p] <= 0) continue;
+        if (samples_out[p] <= 0 || !(meta[p].flags & 1u)) continue;
         soft_clip_packet(out + (size_t)p * pcm_stride, samples_out[p], CC, st[j].softclip_mem);
         for (int i = 0; i < samples_out[p] * CC; i++) pcm16[(size_t)p * pcm_stride + i] = float2int16(out[(size_t)p * pcm_stride + i]);
       }

@@ -8,7 +8,7 @@ from pathlib import Path
 import numpy as np
 
 ROOT = Path(__file__).resolve().parent.parent
-QUIRKS_MOUSIKI = 0x7F
+QUIRKS_MOUSIKI = 0xF7F  # CELT Q1..Q9 (bits 0-6) + SILK S1..S4 (bits 8-11): mousiki as written
 
 
 def _make(dirpath: Path, target: str) -> Path:
@@ -111,3 +111,36 @@ def emul_decode_grid(arena, offsets, n_lanes, n_ticks, channels, frame_size, i16
     lib.emu_decode_grid(channels, quirks, ptr(arena), ptr(offsets), n_lanes, n_ticks, stride, ptr(pcm), ptr(pcm16), ptr(samples),
                         ptr(rng), ptr(iy), ptr(xs))
     return (pcm16 if i16 else pcm), samples, rng, iy, xs
+
+
+def silk_toc(bandwidth: int, size_code: int, stereo: bool) -> int:
+    """SILK-only TOC, code 0: config = 4*bandwidth(0 NB, 1 MB, 2 WB) + size_code(0: 10 ms, 1: 20, 2: 40, 3: 60)."""
+    return ((4 * bandwidth + size_code) << 3) | (4 if stereo else 0)
+
+
+def silk_fuzz_grid(n_lanes: int, n_ticks: int, payload, toc_fn, seed: int = 1, channels: int = 2):
+    """Like fuzz_grid, for SILK-only TOCs, keeping only packets WITHOUT a redundancy frame: in SILK-only mode any
+    packet with >= 17 unread bits after the SILK payload carries a CELT redundancy frame (opus_decoder.rs:746-759),
+    an arm the CUDA path reports as unimplemented. The entropy decode is state-free, so candidates are probed one by
+    one with a fresh oracle decoder. toc_fn(k, rng) -> TOC byte for the k-th candidate."""
+    lib = oracle_lib()
+    rng = np.random.default_rng(seed)
+    need = n_lanes * n_ticks
+    pkts = []
+    pcm = np.zeros(2880 * 2, dtype=np.float32)
+    k = 0
+    while len(pkts) < need:
+        ln = int(rng.integers(payload[0], payload[1] + 1)) if isinstance(payload, tuple) else int(payload)
+        pkt = rng.integers(0, 256, size=ln + 1, dtype=np.uint8)
+        pkt[0] = toc_fn(k, rng)
+        k += 1
+        h = lib.orc_create(48000, channels, QUIRKS_MOUSIKI)
+        r = lib.orc_decode_float(h, ptr(pkt), len(pkt), ptr(pcm), 2880, 0)
+        red = lib.orc_last_redundancy(h)
+        lib.orc_destroy(h)
+        if r > 0 and not red:
+            pkts.append(pkt)
+        assert k < 200 * need, "payload range leaves too many packets with redundancy"
+    offsets = np.zeros(need + 1, dtype=np.uint32)
+    offsets[1:] = np.cumsum([len(p) for p in pkts])
+    return np.concatenate(pkts), offsets
