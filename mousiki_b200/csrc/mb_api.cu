@@ -283,7 +283,7 @@ __global__ void k_reset(StreamState* st, float* hist, const uint32_t* __restrict
 
 // SILK-only packets, phase 2: one lane per stream, its packets in tick order (mb_silk_synth.cuh / mb_silk_out.cuh).
 // The stream's SILK state is staged in the lane's local memory for the pass and written back at the end.
-__global__ void __launch_bounds__(64) k_silk(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
+__global__ void __launch_bounds__(64, 12) k_silk(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
                                              const uint32_t* __restrict__ lane_stream, const uint32_t* __restrict__ rec,
                                              const FrameMeta* __restrict__ meta, SilkState* st_all, float* __restrict__ pcm_f32,
                                              int16_t* __restrict__ pcm_i16, uint32_t pcm_stride, int CC, uint32_t quirks, float gain,
