@@ -288,6 +288,10 @@ __global__ void __launch_bounds__(64, 12) k_silk(uint32_t n_lanes, uint32_t n_ti
                                              const FrameMeta* __restrict__ meta, SilkState* st_all, float* __restrict__ pcm_f32,
                                              int16_t* __restrict__ pcm_i16, uint32_t pcm_stride, int CC, uint32_t quirks, float gain,
                                              int apply_gain) {
+  __shared__ int32_t stage[64][33];   // 32 staged output samples per lane, pitch 33: conflict-free for lockstep lanes
+  __shared__ int16_t fir[48];
+  if (threadIdx.x < 48) fir[threadIdx.x] = silk_resampler_frac_FIR_12[threadIdx.x];
+  __syncthreads();
   const uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
   if (lane >= n_lanes) return;
   bool any = false;
@@ -296,6 +300,7 @@ __global__ void __launch_bounds__(64, 12) k_silk(uint32_t n_lanes, uint32_t n_ti
   SilkState* gs = st_all + (lane_stream ? lane_stream[lane] : lane);
   SilkState S = *gs;
   SilkWork W;
+  silk_work_load(W, S);
   for (uint32_t t = 0; t < n_ticks; t++) {
     const uint32_t f = t * n_lanes + lane;
     if (!(meta[f].flags & 2u)) continue;
@@ -304,8 +309,9 @@ __global__ void __launch_bounds__(64, 12) k_silk(uint32_t n_lanes, uint32_t n_ti
     o.f32 = pcm_f32 ? pcm_f32 + (size_t)p * pcm_stride : nullptr;
     o.i16 = pcm_i16 ? pcm_i16 + (size_t)p * pcm_stride : nullptr;
     o.CC = CC; o.gain = gain; o.apply_gain = apply_gain;
-    silk_synth_packet(S, W, rec + rec_index(f, 0), quirks, o);
+    silk_synth_packet(S, W, rec + rec_index(f, 0), quirks, o, stage[threadIdx.x], fir);
   }
+  silk_work_store(W, S);
   *gs = S;
 }
 __global__ void k_silk_reset(SilkState* st, const uint32_t* __restrict__ ids, uint32_t n) {

@@ -1,19 +1,25 @@
 // Phase 2 for SILK-only packets, output side: channel plumbing of silk_decode, mid/side -> left/right, the API
-// resampler to 48 kHz and the PCM store; and the per-stream lane loop that walks a stream's packets in tick order.
+// resampler to 48 kHz and the PCM store; one call per packet from the per-stream lane loop (k_silk).
 // Reference: src/silk/dec_api.rs:132-441, stereo_ms_to_lr.rs:26-143, resampler.rs:87-176,279-369,
 // resampler_private_iir_fir.rs:80-197, resampler_private_up2_hq.rs:31-117, decoder_set_fs.rs:137-198,
 // opus_decoder.rs:596-745 (SILK arm of decode_frame), :1524-1533 (silk_int16_to_res).
+//
+// The resampler runs as a stream: every input sample goes through the 2x all-pass up-sampler (state in registers) into
+// a 10-sample register window, and the FIR interpolator emits the 3 / 4 / 6 output samples whose 8-tap window has just
+// become complete. The reference's batch structure (1 ms from the delay line, then 10 ms batches, each restarting the
+// Q16 phase accumulator) is kept exactly; what disappears is the 2x up-sampled scratch array. Output samples are
+// collected 32 at a time in a lane-private shared-memory row and leave as 128-bit stores (a full 128-byte line per
+// lane for mono float output).
 #pragma once
-#include "mb_silk_synth.cuh"
+#include "mb_silk_core.cuh"
 #include "mb_celt_energy.cuh"
 
 namespace mb {
 
-// decoder_set_fs.rs:137-198 for a fixed 48 kHz API rate. The resampler (always the IIR/FIR up-sampler here:
-// 8/12/16 -> 48 kHz) is re-initialised when the internal rate changes or the channel was reset.
-MB_DEV void silk_set_fs(SilkChanState& c, int fs_khz, int nb_subfr) {
-  const int frame_length = 5 * fs_khz * nb_subfr;
-  if (c.fs_khz != fs_khz || !c.res_ready) {
+// decoder_set_fs.rs:137-198 for a fixed 48 kHz API rate. Returns true when the output history was cleared.
+MB_DEV bool silk_set_fs(SilkChanState& c, int fs_khz, int nb_subfr) {
+  bool cleared = false;
+  if (c.fs_khz != fs_khz || !c.res_ready) {   // resampler init (always the IIR/FIR up-sampler here: 8/12/16 -> 48 kHz)
     for (int i = 0; i < 6; i++) c.res_iir[i] = 0;
     for (int i = 0; i < 8; i++) c.res_fir[i] = 0;
     for (int i = 0; i < 16; i++) c.res_delay[i] = 0;
@@ -21,81 +27,161 @@ MB_DEV void silk_set_fs(SilkChanState& c, int fs_khz, int nb_subfr) {
   }
   if (c.fs_khz != fs_khz) {
     c.first_frame_after_reset = 1; c.lag_prev = 100; c.last_gain_index = 10; c.prev_signal_type = 0;
-    for (int i = 0; i < 320; i++) c.out_buf[i] = 0;
     for (int i = 0; i < 16; i++) c.s_lpc_q14[i] = 0;
+    cleared = true;
   }
-  c.fs_khz = (int16_t)fs_khz; c.nb_subfr = (int16_t)nb_subfr; c.frame_length = (int16_t)frame_length;
+  c.fs_khz = (int16_t)fs_khz; c.nb_subfr = (int16_t)nb_subfr; c.frame_length = (int16_t)(5 * fs_khz * nb_subfr);
+  return cleared;
+}
+MB_DEV void silk_ring_clear(int16_t* h, int pos) {
+  for (int i = 0; i < 320; i++) h[(pos + i) & SILK_RING_MASK] = 0;
 }
 
-// where the samples of one packet go
+// ---- PCM sink: 32 samples staged per lane, then written out
 struct SilkPcmOut {
-  float* f32;      // interleaved, or null
-  int16_t* i16;    // interleaved, or null
+  float* f32;      // interleaved packet row, or null
+  int16_t* i16;    // interleaved packet row, or null
   int CC;          // API channels (interleave stride)
   float gain; int apply_gain;
 };
-MB_DEV void silk_store_sample(const SilkPcmOut& o, int pos, int c, int32_t v) {
-  const size_t at = (size_t)pos * o.CC + c;
-  if (o.f32) {
-    float x = (float)v * (1.0f / 32768.0f);
-    if (o.apply_gain) x *= o.gain;      // opus_decoder.rs:1376-1392
-    o.f32[at] = x;
-  } else o.i16[at] = (int16_t)v;
+struct SilkSink {
+  int32_t* stage;  // 32 words, lane-private (shared memory on the device)
+  int fill, pos, ch, dup;   // pos: sample position (per channel) of stage[0]; dup: mono stream into a stereo row
+  const SilkPcmOut* o;
+};
+MB_DEV float silk_to_float(const SilkPcmOut& o, int32_t v) {
+  float x = (float)v * (1.0f / 32768.0f);
+  if (o.apply_gain) x *= o.gain;      // opus_decoder.rs:1376-1392
+  return x;
 }
-
-// resampler_private_up2_hq.rs:31-117, one input sample -> two output samples
-MB_DEV void silk_up2(int32_t* S, int32_t in, int16_t* out2) {
-  const int32_t in32 = in << 10;
-  int32_t Y, X, o1, o2;
-  Y = s_sub(in32, S[0]); X = s_mulwb(Y, silk_resampler_up2_hq_0[0]); o1 = s_add(S[0], X); S[0] = s_add(in32, X);
-  Y = s_sub(o1, S[1]); X = s_mulwb(Y, silk_resampler_up2_hq_0[1]); o2 = s_add(S[1], X); S[1] = s_add(o1, X);
-  Y = s_sub(o2, S[2]); X = s_mlawb(Y, Y, silk_resampler_up2_hq_0[2]); o1 = s_add(S[2], X); S[2] = s_add(o2, X);
-  out2[0] = (int16_t)s_sat16(s_rr(o1, 10));
-  Y = s_sub(in32, S[3]); X = s_mulwb(Y, silk_resampler_up2_hq_1[0]); o1 = s_add(S[3], X); S[3] = s_add(in32, X);
-  Y = s_sub(o1, S[4]); X = s_mulwb(Y, silk_resampler_up2_hq_1[1]); o2 = s_add(S[4], X); S[4] = s_add(o1, X);
-  Y = s_sub(o2, S[5]); X = s_mlawb(Y, Y, silk_resampler_up2_hq_1[2]); o1 = s_add(S[5], X); S[5] = s_add(o2, X);
-  out2[1] = (int16_t)s_sat16(s_rr(o1, 10));
-}
-
-// resampler_private_iir_fir.rs:80-197: `n_in` samples in, batches of 10 ms; returns the number of samples written.
-// up: lane-private window of 8 + 2*batch samples; iir/fir: the persistent filter state (registers while running).
-MB_DEV_NOINLINE int silk_iir_fir(int32_t* iir, int16_t* fir, int16_t* up, const int16_t* in, int n_in, int batch, int32_t inc_q16,
-                                 const SilkPcmOut& o, int pos, int c) {
-  if (n_in <= 0) return 0;
-  for (int i = 0; i < 8; i++) up[i] = fir[i];
-  int produced = 0, n = 0;
-  while (n_in > 0) {
-    n = n_in < batch ? n_in : batch;
-    for (int k = 0; k < n; k++) silk_up2(iir, in[k], up + 8 + 2 * k);
-    const int32_t max_idx = n << 17;
-    for (int32_t idx = 0; idx < max_idx; idx += inc_q16) {
-      const int ti = ((idx & 0xffff) * 12) >> 16;
-      const int16_t* b = up + (idx >> 16);
-      const int16_t* f = silk_resampler_frac_FIR_12 + 4 * ti;
-      const int16_t* r = silk_resampler_frac_FIR_12 + 4 * (11 - ti);
-      int32_t acc = (int32_t)b[0] * f[0];
-      acc += (int32_t)b[1] * f[1]; acc += (int32_t)b[2] * f[2]; acc += (int32_t)b[3] * f[3];
-      acc += (int32_t)b[4] * r[3]; acc += (int32_t)b[5] * r[2]; acc += (int32_t)b[6] * r[1]; acc += (int32_t)b[7] * r[0];
-      silk_store_sample(o, pos + produced, c, s_sat16((acc + (1 << 14)) >> 15));
-      produced++;
+MB_DEV_NOINLINE void silk_sink_flush(SilkSink& s) {
+  const SilkPcmOut& o = *s.o;
+  const int n = s.fill;
+  if (o.CC == 1 || s.dup) {
+    const int rep = s.dup ? 2 : 1;
+    if (o.f32) {
+      float* dst = o.f32 + (size_t)s.pos * rep;
+#if MB_ON_DEVICE
+      if (n == 32 && (((uintptr_t)dst) & 15u) == 0) {
+        if (rep == 1) {
+#pragma unroll
+          for (int q = 0; q < 8; q++)
+            ((float4*)dst)[q] = make_float4(silk_to_float(o, s.stage[4 * q]), silk_to_float(o, s.stage[4 * q + 1]),
+                                            silk_to_float(o, s.stage[4 * q + 2]), silk_to_float(o, s.stage[4 * q + 3]));
+        } else {
+#pragma unroll
+          for (int q = 0; q < 16; q++) {
+            const float a = silk_to_float(o, s.stage[2 * q]), b = silk_to_float(o, s.stage[2 * q + 1]);
+            ((float4*)dst)[q] = make_float4(a, a, b, b);
+          }
+        }
+      } else
+#endif
+        for (int i = 0; i < n; i++) { const float x = silk_to_float(o, s.stage[i]); for (int r = 0; r < rep; r++) dst[i * rep + r] = x; }
+    } else {
+      int16_t* dst = o.i16 + (size_t)s.pos * rep;
+#if MB_ON_DEVICE
+      if (n == 32 && (((uintptr_t)dst) & 15u) == 0) {
+        if (rep == 1) {
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            uint32_t w[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) w[j] = (uint32_t)(uint16_t)s.stage[8 * q + 2 * j] | ((uint32_t)(uint16_t)s.stage[8 * q + 2 * j + 1] << 16);
+            ((uint4*)dst)[q] = make_uint4(w[0], w[1], w[2], w[3]);
+          }
+        } else {
+#pragma unroll
+          for (int q = 0; q < 8; q++) {
+            uint32_t w[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) { const uint32_t v = (uint16_t)s.stage[4 * q + j]; w[j] = v | (v << 16); }
+            ((uint4*)dst)[q] = make_uint4(w[0], w[1], w[2], w[3]);
+          }
+        }
+      } else
+#endif
+        for (int i = 0; i < n; i++) for (int r = 0; r < rep; r++) dst[i * rep + r] = (int16_t)s.stage[i];
     }
-    in += n; n_in -= n;
-    if (n_in > 0) for (int i = 0; i < 8; i++) up[i] = up[2 * n + i];
+  } else {  // one channel of an interleaved stereo row
+    if (o.f32) for (int i = 0; i < n; i++) o.f32[(size_t)(s.pos + i) * 2 + s.ch] = silk_to_float(o, s.stage[i]);
+    else for (int i = 0; i < n; i++) o.i16[(size_t)(s.pos + i) * 2 + s.ch] = (int16_t)s.stage[i];
   }
-  for (int i = 0; i < 8; i++) fir[i] = up[2 * n + i];
-  return produced;
+  s.pos += n; s.fill = 0;
+}
+MB_DEV void silk_sink_put(SilkSink& s, int32_t v) {
+  s.stage[s.fill++] = v;
+  if (s.fill == 32) silk_sink_flush(s);
 }
 
-// resampler.rs:279-369 (silk_resampler) for the up-sampling kernels: 1 ms from the delay line, then the rest.
-MB_DEV int silk_resample48(SilkChanState& c, int16_t* up, const int16_t* in, int n_in, const SilkPcmOut& o, int pos, int ch) {
+// input of the resampler: sample k of the frame, read from a ring (mono path: one sample of delay through s_mid) or
+// from the left/right staging rows
+struct SilkSrc {
+  const int16_t* p; int base, mask, first, has_first;
+  MB_MEM int32_t at(int k) const { return (has_first && k == 0) ? first : (int32_t)p[(base + k) & mask]; }
+};
+
+// resampler.rs:279-369 + resampler_private_iir_fir.rs:80-197 + resampler_private_up2_hq.rs:31-117, streamed.
+// `fir`: the 12 x 4 interpolation table (shared-memory copy on the device). Returns the number of samples produced.
+MB_DEV_NOINLINE int silk_resample48(SilkChanState& c, const SilkSrc& in, int n_in, const int16_t* fir, SilkSink& sink) {
   const int fs = c.fs_khz;
   const int delay = fs == 8 ? 0 : (fs == 12 ? 4 : 7);                 // DELAY_MATRIX_DEC[.][48 kHz] (resampler.rs:228)
   const int32_t inc = fs == 8 ? 21846 : (fs == 12 ? 32768 : 43691);   // compute_inv_ratio_q16(fs, 48000, up2x = 1)
-  const int ns = fs - delay;
-  for (int i = 0; i < ns; i++) c.res_delay[delay + i] = in[i];
-  int produced = silk_iir_fir(c.res_iir, c.res_fir, up, c.res_delay, fs, 10 * fs, inc, o, pos, ch);
-  produced += silk_iir_fir(c.res_iir, c.res_fir, up, in + ns, n_in - fs, 10 * fs, inc, o, pos + produced, ch);
-  for (int i = 0; i < delay; i++) c.res_delay[i] = in[n_in - delay + i];
+  int32_t S0 = c.res_iir[0], S1 = c.res_iir[1], S2 = c.res_iir[2], S3 = c.res_iir[3], S4 = c.res_iir[4], S5 = c.res_iir[5];
+  const int32_t c00 = s_shl(silk_resampler_up2_hq_0[0], 16), c01 = s_shl(silk_resampler_up2_hq_0[1], 16), c02 = s_shl(silk_resampler_up2_hq_0[2], 16);
+  const int32_t c10 = s_shl(silk_resampler_up2_hq_1[0], 16), c11 = s_shl(silk_resampler_up2_hq_1[1], 16), c12 = s_shl(silk_resampler_up2_hq_1[2], 16);
+  int32_t w[10];                     // the newest 10 up-sampled values, w[9] newest
+#pragma unroll
+  for (int j = 0; j < 8; j++) w[2 + j] = c.res_fir[j];
+  w[0] = w[1] = 0;
+  int produced = 0;
+  int t = 0;                         // position in the delayed input stream: res_delay[0, delay) ++ in[0, n_in - delay)
+  int n = fs;                        // first batch: one millisecond
+  while (t < n_in) {
+    if (n > n_in - t) n = n_in - t;
+    const int32_t max_idx = n << 17;
+    int32_t idx = 0;
+    for (int k = -1; k < n; k++) {
+      if (k >= 0) {
+        const int32_t x = t < delay ? (int32_t)c.res_delay[t] : in.at(t - delay);
+        t++;
+        const int32_t in32 = x << 10;
+        int32_t Y, X, o1, o2;
+        Y = s_sub(in32, S0); X = s_mulhi(Y, c00); o1 = s_add(S0, X); S0 = s_add(in32, X);
+        Y = s_sub(o1, S1); X = s_mulhi(Y, c01); o2 = s_add(S1, X); S1 = s_add(o1, X);
+        Y = s_sub(o2, S2); X = s_add(Y, s_mulhi(Y, c02)); o1 = s_add(S2, X); S2 = s_add(o2, X);
+        const int32_t u0 = s_sat16(s_rr(o1, 10));
+        Y = s_sub(in32, S3); X = s_mulhi(Y, c10); o1 = s_add(S3, X); S3 = s_add(in32, X);
+        Y = s_sub(o1, S4); X = s_mulhi(Y, c11); o2 = s_add(S4, X); S4 = s_add(o1, X);
+        Y = s_sub(o2, S5); X = s_add(Y, s_mulhi(Y, c12)); o1 = s_add(S5, X); S5 = s_add(o2, X);
+        const int32_t u1 = s_sat16(s_rr(o1, 10));
+#pragma unroll
+        for (int j = 0; j < 8; j++) w[j] = w[j + 2];
+        w[8] = u0; w[9] = u1;
+      }
+      // window position of w[j] inside the batch buffer (tail = 0..7, sample k -> 8 + 2k, 9 + 2k): 2k + j. An output with
+      // integer position b reads buffer[b .. b + 8): complete once b + 7 <= 2k + 9, i.e. b <= 2k + 2; b = 2k + 1 starts
+      // at w[1], b = 2k + 2 at w[2].
+      while (idx < max_idx && (idx >> 16) <= 2 * k + 2) {
+        const bool hi = (idx >> 16) == 2 * k + 2;
+        const int ti = ((idx & 0xffff) * 12) >> 16;
+        const int16_t* f = fir + 4 * ti;
+        const int16_t* r = fir + 4 * (11 - ti);
+        int32_t acc = (hi ? w[2] : w[1]) * f[0];
+        acc += (hi ? w[3] : w[2]) * f[1]; acc += (hi ? w[4] : w[3]) * f[2]; acc += (hi ? w[5] : w[4]) * f[3];
+        acc += (hi ? w[6] : w[5]) * r[3]; acc += (hi ? w[7] : w[6]) * r[2]; acc += (hi ? w[8] : w[7]) * r[1];
+        acc += (hi ? w[9] : w[8]) * r[0];
+        silk_sink_put(sink, s_sat16((acc + (1 << 14)) >> 15));
+        produced++;
+        idx += inc;
+      }
+    }
+    n = 10 * fs;
+  }
+#pragma unroll
+  for (int j = 0; j < 8; j++) c.res_fir[j] = (int16_t)w[2 + j];
+  c.res_iir[0] = S0; c.res_iir[1] = S1; c.res_iir[2] = S2; c.res_iir[3] = S3; c.res_iir[4] = S4; c.res_iir[5] = S5;
+  for (int i = 0; i < delay; i++) c.res_delay[i] = (int16_t)in.at(n_in - delay + i);
   return produced;
 }
 
@@ -122,9 +208,22 @@ MB_DEV_NOINLINE void silk_ms_to_lr(SilkState& S, int16_t* x1, int16_t* x2, const
   }
 }
 
+// lane start / end: the rings are the live copy of out_buf while the lane runs
+MB_DEV void silk_work_load(SilkWork& W, const SilkState& S) {
+  for (int n = 0; n < 2; n++) {
+    W.pos[n] = 0;
+    for (int k = 0; k < 320; k++) W.hist[n][k] = S.ch[n].out_buf[k];
+  }
+}
+MB_DEV void silk_work_store(const SilkWork& W, SilkState& S) {
+  for (int n = 0; n < 2; n++)
+    for (int k = 0; k < 320; k++) S.ch[n].out_buf[k] = W.hist[n][(W.pos[n] + k) & SILK_RING_MASK];
+}
+
 // One SILK-only packet of one stream: silk_decode (dec_api.rs:132-441) once per 10/20 ms SILK frame in the packet.
-// Returns samples per channel written at 48 kHz.
-MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const uint32_t* rec_base, uint32_t quirks, const SilkPcmOut& o) {
+// stage: 32 lane-private words; fir: interpolation table. Returns samples per channel written at 48 kHz.
+MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const uint32_t* rec_base, uint32_t quirks, const SilkPcmOut& o,
+                                      int32_t* stage, const int16_t* fir) {
   const uint32_t h0 = rec_base[S_HDR0 * 32];
   const int fs = (int)MB_SH_FS(h0), nb = (int)MB_SH_SUBFR(h0), n_frames = (int)MB_SH_FRAMES(h0), nci = (int)MB_SH_NCI(h0);
   const int CC = o.CC;
@@ -133,11 +232,12 @@ MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const uint32_t*
   for (int i = 0; i < n_frames; i++) {
     const uint32_t* fr = rec_base + (SL_BASE + i * SL_FRAME_WORDS) * 32;
     if (nci > S.n_channels_internal) {                       // dec_api.rs:150-154
-      if (quirks & S4_STEREO_REINIT) silk_chan_reset(S.ch[0]);
-      silk_chan_reset(S.ch[1]);
+      if (quirks & S4_STEREO_REINIT) { silk_chan_reset(S.ch[0]); silk_ring_clear(W.hist[0], W.pos[0]); }
+      silk_chan_reset(S.ch[1]); silk_ring_clear(W.hist[1], W.pos[1]);
     }
     const bool stereo_to_mono = nci == 1 && S.n_channels_internal == 2 && fs == S.ch[0].fs_khz;
-    for (int n = 0; n < nci; n++) silk_set_fs(S.ch[n], fs, nb);
+    for (int n = 0; n < nci; n++)
+      if (silk_set_fs(S.ch[n], fs, nb)) silk_ring_clear(W.hist[n], W.pos[n]);
     if (CC == 2 && nci == 2 && (S.n_channels_api == 1 || S.n_channels_internal == 1)) {   // dec_api.rs:181-191
       S.pred_prev_q13[0] = S.pred_prev_q13[1] = 0; S.s_side[0] = S.s_side[1] = 0;
       for (int k = 0; k < 6; k++) S.ch[1].res_iir[k] = S.ch[0].res_iir[k];
@@ -150,7 +250,7 @@ MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const uint32_t*
     const int dom = (int)fr[64];
     if (nci == 2 && !dom && S.prev_decode_only_middle) {     // dec_api.rs:263-271
       SilkChanState& c = S.ch[1];
-      for (int k = 0; k < 320; k++) c.out_buf[k] = 0;
+      silk_ring_clear(W.hist[1], W.pos[1]);
       for (int k = 0; k < 16; k++) c.s_lpc_q14[k] = 0;
       c.lag_prev = 100; c.last_gain_index = 10; c.prev_signal_type = 0; c.first_frame_after_reset = 1;
     }
@@ -158,38 +258,55 @@ MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const uint32_t*
       const uint32_t* chw = fr + (3 + n * SL_CH_WORDS) * 32;
       int16_t* h = W.hist[n];
       SilkChanState& c = S.ch[n];
+      const int hp = W.pos[n];
       if (n == 0 || !dom) {
         SilkSide sd;
         silk_side_load(sd, chw);
         SilkFrameParams P;
-        for (int k = 0; k < ltp_mem; k++) h[k] = c.out_buf[k];
         silk_frame_params(c, sd, P, quirks);
-        silk_frame_core(c, sd, P, chw + SL_IDX_WORDS * 32, h, W.sltp_q15);
+        silk_frame_core(c, sd, P, chw + SL_IDX_WORDS * 32, h, hp, W.sltp_q15);
         c.prev_signal_type = sd.signal_type;               // plc.rs:123
         c.first_frame_after_reset = 0;
-        for (int k = 0; k < ltp_mem; k++) c.out_buf[k] = h[k + L];   // decode_frame.rs:207-230
         c.lag_prev = (int16_t)P.pitch_l[nb - 1];
+        W.pos[n] = (hp + L) & SILK_RING_MASK;              // decode_frame.rs:207-230: the history window slides by a frame
       } else {
-        for (int k = 0; k < L; k++) h[ltp_mem + k] = 0;
+        // side channel not coded: the frame is zeros and the history is left alone (dec_api.rs:318-321)
       }
-      for (int k = 0; k < L; k++) W.lr[n][2 + k] = h[ltp_mem + k];
     }
-    if (CC == 2 && nci == 2) silk_ms_to_lr(S, W.lr[0], W.lr[1], pred, fs, L);
-    else {
-      W.lr[0][0] = S.s_mid[0]; W.lr[0][1] = S.s_mid[1];
-      S.s_mid[0] = W.lr[0][L]; S.s_mid[1] = W.lr[0][L + 1];
-    }
-    const int active = CC < nci ? CC : nci;
+    SilkSink sink;
+    sink.stage = stage; sink.fill = 0; sink.o = &o; sink.dup = 0;
     int n_out = 0;
-    for (int n = 0; n < active; n++) n_out = silk_resample48(S.ch[n], W.up, W.lr[n] + 1, L, o, pos, n);
-    if (CC == 2 && nci == 1) {
-      if (stereo_to_mono) silk_resample48(S.ch[1], W.up, W.lr[0] + 1, L, o, pos, 1);
-      else {
-        for (int k = 0; k < n_out; k++) {
-          if (o.f32) o.f32[(size_t)(pos + k) * 2 + 1] = o.f32[(size_t)(pos + k) * 2];
-          else o.i16[(size_t)(pos + k) * 2 + 1] = o.i16[(size_t)(pos + k) * 2];
-        }
+    if (CC == 2 && nci == 2) {
+      for (int n = 0; n < 2; n++) {
+        const bool coded = n == 0 || !dom;
+        const int b = W.pos[n] + ltp_mem - L;              // first sample of the frame just written
+        for (int k = 0; k < L; k++) W.lr[n][2 + k] = coded ? W.hist[n][(b + k) & SILK_RING_MASK] : (int16_t)0;
       }
+      silk_ms_to_lr(S, W.lr[0], W.lr[1], pred, fs, L);
+      for (int n = 0; n < 2; n++) {
+        SilkSrc src; src.p = W.lr[n] + 1; src.base = 0; src.mask = 0xffff; src.first = 0; src.has_first = 0;
+        sink.pos = pos; sink.ch = n;
+        n_out = silk_resample48(S.ch[n], src, L, fir, sink);
+        if (sink.fill) silk_sink_flush(sink);
+      }
+    } else {
+      // mid only: one sample of delay through s_mid (dec_api.rs:341-347), read straight from the ring
+      const int b = W.pos[0] + ltp_mem - L;
+      SilkSrc src; src.p = W.hist[0]; src.base = b - 1; src.mask = SILK_RING_MASK; src.first = S.s_mid[1]; src.has_first = 1;
+      const int16_t m0 = W.hist[0][(b + L - 2) & SILK_RING_MASK], m1 = W.hist[0][(b + L - 1) & SILK_RING_MASK];
+      if (CC == 2 && stereo_to_mono) {
+        sink.pos = pos; sink.ch = 0;
+        n_out = silk_resample48(S.ch[0], src, L, fir, sink);
+        if (sink.fill) silk_sink_flush(sink);
+        sink.pos = pos; sink.ch = 1;
+        silk_resample48(S.ch[1], src, L, fir, sink);
+        if (sink.fill) silk_sink_flush(sink);
+      } else {
+        sink.pos = pos; sink.ch = 0; sink.dup = CC == 2;
+        n_out = silk_resample48(S.ch[0], src, L, fir, sink);
+        if (sink.fill) silk_sink_flush(sink);
+      }
+      S.s_mid[0] = m0; S.s_mid[1] = m1;
     }
     S.prev_decode_only_middle = (int8_t)dom;
     pos += n_out;

@@ -274,14 +274,6 @@ MB_DEV_NOINLINE void silk_nlsf2a(int16_t* a_q12, const int16_t* nlsf, int d, uin
 }
 
 // ---- one SILK frame of one channel --------------------------------------------------------------------------------
-// Lane-private working set of the synthesis (local memory).
-struct SilkWork {
-  int16_t hist[2][640];      // per channel: [0, ltp_mem) LTP history, [ltp_mem, ltp_mem + frame_length) the frame being built
-  int32_t sltp_q15[640];     // gain-normalised LTP state of the running frame (decode_core.rs s_ltp_q15)
-  int16_t lr[2][322];        // mid/side -> left/right staging (2 history samples + frame), also the resampler input
-  int16_t up[2 * 160 + 8];   // resampler: FIR tail + 2x up-sampled batch
-};
-
 struct SilkFrameParams {     // decoder_control.rs
   int32_t gains_q16[4], pitch_l[4];
   int16_t a_q12[2][16], b_q14[20];
@@ -340,100 +332,6 @@ MB_DEV_NOINLINE void silk_frame_params(SilkChanState& st, SilkSide& sd, SilkFram
       for (int i = 0; i < 5; i++) P.b_q14[k * 5 + i] = (int16_t)(vq[sd.ltp[k] * 5 + i] << 7);
     P.ltp_scale_q14 = silk_LTPScales_table_Q14[sd.ltp_scale];
   } else sd.per_index = 0;
-}
-
-// decode_core.rs:28-330. `pulse_words`: the frame's pulses in the cell record (2 x i16 per word, stride 32 words).
-// `h`: this channel's hist[] (see SilkWork); the frame is written to h[ltp_mem ...].
-MB_DEV_NOINLINE void silk_frame_core(SilkChanState& st, const SilkSide& sd, SilkFrameParams& P, const uint32_t* pulse_words, int16_t* h,
-                                     int32_t* sltp_q15) {
-  const int fs = st.fs_khz, nb = st.nb_subfr, sub = 5 * fs, ltp_mem = 20 * fs, order = fs == 16 ? 16 : 10;
-  const int32_t offset_q10 = silk_Quantization_Offsets_Q10[(sd.signal_type >> 1) * 2 + sd.quant_offset];
-  const bool interp = sd.interp_q2 < 4;
-  int32_t seed = sd.seed;
-  int32_t lpc[16];                   // synthesis history, lpc[j] = sLPC_Q14 of sample (i - 1 - j)
-  for (int j = 0; j < 16; j++) lpc[j] = st.s_lpc_q14[15 - j];
-  int sltp_idx = ltp_mem;
-  int16_t* xq = h + ltp_mem;
-  int32_t prev_gain = st.prev_gain_q16;
-  for (int k = 0; k < nb; k++) {
-    const int16_t* A = P.a_q12[k >> 1];
-    const int16_t* B = P.b_q14 + 5 * k;
-    const int32_t gain_q16 = P.gains_q16[k], gain_q10 = gain_q16 >> 6;
-    int32_t inv_gain_q31 = silk_inverse32(gain_q16, 47);
-    int32_t gain_adj = 1 << 16;
-    if (gain_q16 != prev_gain) {
-      gain_adj = silk_div32(prev_gain, gain_q16, 16);
-      for (int j = 0; j < 16; j++) lpc[j] = s_mulww(gain_adj, lpc[j]);
-    }
-    prev_gain = gain_q16;
-    const bool voiced = sd.signal_type == SILK_T_VOICED;   // (the lost-frame voiced transition needs loss_count > 0)
-    int pl = 0;
-    if (voiced) {
-      const int lag = P.pitch_l[k];
-      if (k == 0 || (k == 2 && interp)) {
-        // re-whitening: LPC analysis filter over the last lag + 2 history samples (lpc_analysis_filter.rs:18-45), each
-        // scaled into the gain-normalised domain. At k == 2 the history includes the two subframes just synthesised,
-        // which already sit behind the history in h[] (decode_core.rs:165-173 copies them there).
-        if (k == 0) inv_gain_q31 = s_shl(s_mulwb(inv_gain_q31, P.ltp_scale_q14), 2);
-        const int16_t* in = h + k * sub;        // in[ltp_mem - 1] is the newest history sample
-        for (int i = 0; i < lag + 2; i++) {
-          const int ix = ltp_mem - 1 - i;
-          int32_t acc = (int32_t)in[ix - 1] * A[0];
-          for (int j = 1; j < order; j++) acc = s_add(acc, (int32_t)in[ix - 1 - j] * A[j]);
-          const int32_t r = s_sat16(s_rr(s_sub(s_shl(in[ix], 12), acc), 12));
-          sltp_q15[sltp_idx - 1 - i] = s_mulwb(inv_gain_q31, r);
-        }
-      } else if (gain_adj != (1 << 16)) {
-        for (int i = 0; i < lag + 2; i++) sltp_q15[sltp_idx - 1 - i] = s_mulww(gain_adj, sltp_q15[sltp_idx - 1 - i]);
-      }
-      pl = sltp_idx - lag + 2;
-    }
-    for (int i = 0; i < sub; i++) {
-      // excitation (decode_core.rs:93-111); pulses of sample n = k*sub + i
-      const int n = k * sub + i;
-      const uint32_t w = pulse_words[(n >> 1) * 32];
-      const int32_t pulse = (int16_t)((n & 1) ? (w >> 16) : (w & 0xffffu));
-      seed = s_add(907633515, (int32_t)((uint32_t)seed * 196314165u));
-      int32_t e = pulse << 14;
-      if (e > 0) e -= 1280; else if (e < 0) e += 1280;
-      e += offset_q10 << 4;
-      if (seed < 0) e = -e;
-      seed = s_add(seed, pulse);
-      int32_t res = e;
-      if (voiced) {
-        int32_t p = 2;
-        p = s_mlawb(p, sltp_q15[pl], B[0]);
-        p = s_mlawb(p, sltp_q15[pl - 1], B[1]);
-        p = s_mlawb(p, sltp_q15[pl - 2], B[2]);
-        p = s_mlawb(p, sltp_q15[pl - 3], B[3]);
-        p = s_mlawb(p, sltp_q15[pl - 4], B[4]);
-        pl++;
-        res = s_add(e, s_shl(p, 1));
-        sltp_q15[sltp_idx++] = s_shl(res, 1);
-      }
-      // short-term prediction: wrapping adds commute, so the 10/16 products are summed as independent partial sums
-      int32_t p0 = order >> 1, p1 = 0, p2 = 0, p3 = 0;
-#pragma unroll
-      for (int j = 0; j < 8; j += 4) {
-        p0 = s_mlawb(p0, lpc[j], A[j]); p1 = s_mlawb(p1, lpc[j + 1], A[j + 1]);
-        p2 = s_mlawb(p2, lpc[j + 2], A[j + 2]); p3 = s_mlawb(p3, lpc[j + 3], A[j + 3]);
-      }
-      p0 = s_mlawb(p0, lpc[8], A[8]); p1 = s_mlawb(p1, lpc[9], A[9]);
-      if (order == 16) {
-        p2 = s_mlawb(p2, lpc[10], A[10]); p3 = s_mlawb(p3, lpc[11], A[11]);
-        p0 = s_mlawb(p0, lpc[12], A[12]); p1 = s_mlawb(p1, lpc[13], A[13]);
-        p2 = s_mlawb(p2, lpc[14], A[14]); p3 = s_mlawb(p3, lpc[15], A[15]);
-      }
-      const int32_t pred = s_add(s_add(p0, p1), s_add(p2, p3));
-      const int32_t s = s_sat32((int64_t)res + s_sat32((int64_t)pred << 4));
-#pragma unroll
-      for (int j = 15; j > 0; j--) lpc[j] = lpc[j - 1];
-      lpc[0] = s;
-      xq[n] = (int16_t)s_sat16(s_rr(s_mulww(s, gain_q10), 8));
-    }
-  }
-  st.prev_gain_q16 = prev_gain;
-  for (int j = 0; j < 16; j++) st.s_lpc_q14[15 - j] = lpc[j];
 }
 
 }  // namespace mb

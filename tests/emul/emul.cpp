@@ -77,6 +77,8 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
     SilkWork* W = new SilkWork;
     for (uint32_t j = 0; j < n_lanes; j++) {
       silk_state_reset(sst[j], 1);
+      silk_work_load(*W, sst[j]);
+      int32_t stage[32];
       for (uint32_t t = 0; t < n_ticks; t++) {
         const uint32_t f = t * n_lanes + j;
         if (!(meta[f].flags & 2u)) continue;
@@ -84,7 +86,7 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
         o.f32 = pcm16 ? nullptr : out + (size_t)f * pcm_stride;
         o.i16 = pcm16 ? pcm16 + (size_t)f * pcm_stride : nullptr;
         o.CC = CC; o.gain = 1.f; o.apply_gain = 0;
-        silk_synth_packet(sst[j], *W, rec.data() + rec_index(f, 0), quirks, o);
+        silk_synth_packet(sst[j], *W, rec.data() + rec_index(f, 0), quirks, o, stage, silk_resampler_frac_FIR_12);
       }
     }
     delete W;
