@@ -285,7 +285,8 @@ __global__ void k_reset(StreamState* st, float* hist, const uint32_t* __restrict
 // The stream's SILK state is staged in the lane's local memory for the pass and written back at the end.
 __global__ void __launch_bounds__(64, 12) k_silk(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
                                              const uint32_t* __restrict__ lane_stream, const uint32_t* __restrict__ rec,
-                                             const FrameMeta* __restrict__ meta, SilkState* st_all, float* __restrict__ pcm_f32,
+                                             const FrameMeta* __restrict__ meta, SilkState* st_all, uint32_t* silk_hist,
+                                             uint32_t n_streams, float* __restrict__ pcm_f32,
                                              int16_t* __restrict__ pcm_i16, uint32_t pcm_stride, int CC, uint32_t quirks, float gain,
                                              int apply_gain) {
   __shared__ int32_t stage[64][33];   // 32 staged output samples per lane, pitch 33: conflict-free for lockstep lanes
@@ -297,10 +298,13 @@ __global__ void __launch_bounds__(64, 12) k_silk(uint32_t n_lanes, uint32_t n_ti
   bool any = false;
   for (uint32_t t = 0; t < n_ticks && !any; t++) any = (meta[t * n_lanes + lane].flags & 2u) != 0;
   if (!any) return;
-  SilkState* gs = st_all + (lane_stream ? lane_stream[lane] : lane);
+  const uint32_t sid = lane_stream ? lane_stream[lane] : lane;
+  SilkState* gs = st_all + sid;
   SilkState S = *gs;
   SilkWork W;
-  silk_work_load(W, S);
+  SilkHistRef H = {silk_hist, n_streams, sid};
+  int side_live = 0;
+  silk_hist_load(W, H, 0);
   for (uint32_t t = 0; t < n_ticks; t++) {
     const uint32_t f = t * n_lanes + lane;
     if (!(meta[f].flags & 2u)) continue;
@@ -309,15 +313,18 @@ __global__ void __launch_bounds__(64, 12) k_silk(uint32_t n_lanes, uint32_t n_ti
     o.f32 = pcm_f32 ? pcm_f32 + (size_t)p * pcm_stride : nullptr;
     o.i16 = pcm_i16 ? pcm_i16 + (size_t)p * pcm_stride : nullptr;
     o.CC = CC; o.gain = gain; o.apply_gain = apply_gain;
-    silk_synth_packet(S, W, rec + rec_index(f, 0), quirks, o, stage[threadIdx.x], fir);
+    silk_synth_packet(S, W, H, side_live, rec + rec_index(f, 0), quirks, o, stage[threadIdx.x], fir);
   }
-  silk_work_store(W, S);
+  silk_hist_store(W, H, 0);
+  if (side_live) silk_hist_store(W, H, 1);
   *gs = S;
 }
-__global__ void k_silk_reset(SilkState* st, const uint32_t* __restrict__ ids, uint32_t n) {
+__global__ void k_silk_reset(SilkState* st, uint32_t* silk_hist, uint32_t n_streams, const uint32_t* __restrict__ ids, uint32_t n) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  silk_state_reset(st[ids ? ids[i] : i], 1);
+  const uint32_t sid = ids ? ids[i] : i;
+  silk_state_reset(st[sid], 1);
+  for (int k = 0; k < 320; k++) silk_hist[(size_t)k * n_streams + sid] = 0;
 }
 
 // ------------------------------------------------------------------------------------------ host side
@@ -354,7 +361,7 @@ struct bd_handle {
   cudaStream_t copy_stream = nullptr;   // device -> host PCM of pass k overlaps the kernels of pass k + 1
   std::vector<cudaEvent_t> pass_events;
   struct PassOut { bool on = false; char* host_pcm = nullptr; const char* dev_pcm = nullptr; size_t elem = 0; } pass_out;
-  DevBuf states, silk_states, hist, rec, en, meta, series, xbuf;
+  DevBuf states, silk_states, silk_hist, hist, rec, en, meta, series, xbuf;
   // staging for the host-buffer entry points
   DevBuf d_arena, d_offsets, d_pkt_map, d_lane_stream, d_flags, d_pcm, d_pcm16, d_samples, d_range, d_ids, d_dbg_iy, d_dbg_x;
   std::vector<uint32_t> h_pkt_map, h_lane_stream, h_lane_of_stream, h_epoch, h_count;
@@ -427,7 +434,9 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
   if (h->states.ensure((size_t)cfg->n_streams * sizeof(StreamState)) != cudaSuccess) return fail(BD_ERR_ALLOC);
   if (h->hist.ensure((size_t)cfg->n_streams * h->CC * HIST * sizeof(float)) != cudaSuccess) return fail(BD_ERR_ALLOC);
   if (h->silk_states.ensure((size_t)cfg->n_streams * sizeof(SilkState)) != cudaSuccess) return fail(BD_ERR_ALLOC);
-  k_silk_reset<<<(cfg->n_streams + 127) / 128, 128, 0, h->own_stream>>>(h->silk_states.as<SilkState>(), nullptr, cfg->n_streams);
+  if (h->silk_hist.ensure((size_t)cfg->n_streams * 320 * sizeof(uint32_t)) != cudaSuccess) return fail(BD_ERR_ALLOC);
+  k_silk_reset<<<(cfg->n_streams + 127) / 128, 128, 0, h->own_stream>>>(h->silk_states.as<SilkState>(), h->silk_hist.as<uint32_t>(),
+                                                                        cfg->n_streams, nullptr, cfg->n_streams);
   k_reset<<<cfg->n_streams, 128, 0, h->own_stream>>>(h->states.as<StreamState>(), h->hist.as<float>(), nullptr, cfg->n_streams, h->CC);
   if (cudaStreamSynchronize(h->own_stream) != cudaSuccess || cudaGetLastError() != cudaSuccess) return fail(BD_ERR_CUDA);
   *out = h;
@@ -437,7 +446,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
 void bd_destroy(bd_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  DevBuf* all[] = {&h->states, &h->silk_states, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map,
+  DevBuf* all[] = {&h->states, &h->silk_states, &h->silk_hist, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map,
                    &h->d_lane_stream, &h->d_flags, &h->d_pcm, &h->d_pcm16, &h->d_samples, &h->d_range, &h->d_ids, &h->d_dbg_iy, &h->d_dbg_x};
   for (DevBuf* b : all) b->release();
   for (auto& sp : h->prof_spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -461,7 +470,7 @@ int bd_reset_streams(bd_handle* h, const uint32_t* ids, uint32_t n) {
   } else n = h->cfg.n_streams;
   if (n == 0) return BD_OK;
   k_reset<<<n, 128, 0, h->own_stream>>>(h->states.as<StreamState>(), h->hist.as<float>(), d_ids, n, h->CC);
-  k_silk_reset<<<(n + 127) / 128, 128, 0, h->own_stream>>>(h->silk_states.as<SilkState>(), d_ids, n);
+  k_silk_reset<<<(n + 127) / 128, 128, 0, h->own_stream>>>(h->silk_states.as<SilkState>(), h->silk_hist.as<uint32_t>(), h->cfg.n_streams, d_ids, n);
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(h->own_stream));
   return BD_OK;
@@ -590,7 +599,8 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     // 2^-15, so on the i16 path soft clip + float2int16 is the identity and the lane stores int16 directly.
     h->prof_begin(BD_K_SILK, s);
     k_silk<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, nt, map, d_lane_stream, h->rec.as<uint32_t>(), h->meta.as<FrameMeta>(),
-                                              h->silk_states.as<SilkState>(), d_pcm_i16 ? nullptr : pcm,
+                                              h->silk_states.as<SilkState>(), h->silk_hist.as<uint32_t>(), h->cfg.n_streams,
+                                              d_pcm_i16 ? nullptr : pcm,
                                               d_pcm_i16 ? d_pcm_i16 + shift * pcm_stride : nullptr, pcm_stride, CC, h->cfg.quirks, h->gain,
                                               h->cfg.gain_q8 != 0);
     h->prof_end(s);

@@ -208,27 +208,38 @@ MB_DEV_NOINLINE void silk_ms_to_lr(SilkState& S, int16_t* x1, int16_t* x2, const
   }
 }
 
-// lane start / end: the rings are the live copy of out_buf while the lane runs
-MB_DEV void silk_work_load(SilkWork& W, const SilkState& S) {
-  for (int n = 0; n < 2; n++) {
-    W.pos[n] = 0;
-    for (int k = 0; k < 320; k++) W.hist[n][k] = S.ch[n].out_buf[k];
+// Output history in HBM: 2 channels x 160 words (2 samples each) per stream, structure-of-arrays over streams —
+// word k of channel n of stream sid at hist[(n * 160 + k) * n_streams + sid] — so the lanes of a warp move it with
+// coalesced 128-byte transactions. While a lane runs, its rings are the live copy; the side channel is only loaded
+// (and stored back) when a packet actually uses it.
+struct SilkHistRef { uint32_t* base; size_t n_streams, sid; };
+MB_DEV void silk_hist_load(SilkWork& W, const SilkHistRef& H, int n) {
+  W.pos[n] = 0;
+  const uint32_t* g = H.base + (size_t)n * 160 * H.n_streams + H.sid;
+  for (int k = 0; k < 160; k++) {
+    const uint32_t v = g[(size_t)k * H.n_streams];
+    W.hist[n][2 * k] = (int16_t)(v & 0xffffu); W.hist[n][2 * k + 1] = (int16_t)(v >> 16);
   }
 }
-MB_DEV void silk_work_store(const SilkWork& W, SilkState& S) {
-  for (int n = 0; n < 2; n++)
-    for (int k = 0; k < 320; k++) S.ch[n].out_buf[k] = W.hist[n][(W.pos[n] + k) & SILK_RING_MASK];
+MB_DEV void silk_hist_store(const SilkWork& W, const SilkHistRef& H, int n) {
+  uint32_t* g = H.base + (size_t)n * 160 * H.n_streams + H.sid;
+  const int p = W.pos[n];
+  for (int k = 0; k < 160; k++)
+    g[(size_t)k * H.n_streams] = (uint32_t)(uint16_t)W.hist[n][(p + 2 * k) & SILK_RING_MASK] |
+                                 ((uint32_t)(uint16_t)W.hist[n][(p + 2 * k + 1) & SILK_RING_MASK] << 16);
 }
 
 // One SILK-only packet of one stream: silk_decode (dec_api.rs:132-441) once per 10/20 ms SILK frame in the packet.
-// stage: 32 lane-private words; fir: interpolation table. Returns samples per channel written at 48 kHz.
-MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const uint32_t* rec_base, uint32_t quirks, const SilkPcmOut& o,
-                                      int32_t* stage, const int16_t* fir) {
+// stage: 32 lane-private words; fir: interpolation table; side_live: the side channel's ring holds its history.
+// Returns samples per channel written at 48 kHz.
+MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const SilkHistRef& H, int& side_live, const uint32_t* rec_base,
+                                      uint32_t quirks, const SilkPcmOut& o, int32_t* stage, const int16_t* fir) {
   const uint32_t h0 = rec_base[S_HDR0 * 32];
   const int fs = (int)MB_SH_FS(h0), nb = (int)MB_SH_SUBFR(h0), n_frames = (int)MB_SH_FRAMES(h0), nci = (int)MB_SH_NCI(h0);
   const int CC = o.CC;
   const int L = 5 * fs * nb, ltp_mem = 20 * fs;
   int pos = 0;
+  if (nci == 2 && !side_live) { silk_hist_load(W, H, 1); side_live = 1; }
   for (int i = 0; i < n_frames; i++) {
     const uint32_t* fr = rec_base + (SL_BASE + i * SL_FRAME_WORDS) * 32;
     if (nci > S.n_channels_internal) {                       // dec_api.rs:150-154

@@ -74,8 +74,9 @@ MB_DEV int32_t silk_log2lin(int32_t x) {
 
 // ---- persistent per-stream state (HBM). Reference: silk Decoder (dec_api.rs:35-46), DecoderState
 // (decoder_state.rs:99-131), DecoderSampleRateState (decoder_set_fs.rs:63-124), Resampler (resampler.rs:40-48).
+// The output history (the last 20 ms per channel, decoder_set_fs.rs out_buf) lives in its own structure-of-arrays
+// buffer, see silk_work_load / silk_work_store in mb_silk_out.cuh.
 struct SilkChanState {
-  int16_t out_buf[320];          // the last ltp_mem_length (<= 320) output samples: LTP re-whitening history
   int32_t s_lpc_q14[16];
   int16_t prev_nlsf_q15[16];
   int32_t res_iir[6];            // up2_hq all-pass state of the API resampler
@@ -91,7 +92,6 @@ struct SilkState {
   int8_t n_channels_api, n_channels_internal, prev_decode_only_middle, pad;
 };
 MB_DEV void silk_chan_reset(SilkChanState& c) {   // init_decoder.rs:14-26 + DecoderState::default
-  for (int i = 0; i < 320; i++) c.out_buf[i] = 0;
   for (int i = 0; i < 16; i++) { c.s_lpc_q14[i] = 0; c.prev_nlsf_q15[i] = 0; c.res_delay[i] = 0; }
   for (int i = 0; i < 6; i++) c.res_iir[i] = 0;
   for (int i = 0; i < 8; i++) c.res_fir[i] = 0;

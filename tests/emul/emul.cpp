@@ -77,7 +77,10 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
     SilkWork* W = new SilkWork;
     for (uint32_t j = 0; j < n_lanes; j++) {
       silk_state_reset(sst[j], 1);
-      silk_work_load(*W, sst[j]);
+      std::vector<uint32_t> hist(320, 0);
+      SilkHistRef H = {hist.data(), 1, 0};
+      int side_live = 0;
+      silk_hist_load(*W, H, 0);
       int32_t stage[32];
       for (uint32_t t = 0; t < n_ticks; t++) {
         const uint32_t f = t * n_lanes + j;
@@ -86,7 +89,7 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
         o.f32 = pcm16 ? nullptr : out + (size_t)f * pcm_stride;
         o.i16 = pcm16 ? pcm16 + (size_t)f * pcm_stride : nullptr;
         o.CC = CC; o.gain = 1.f; o.apply_gain = 0;
-        silk_synth_packet(sst[j], *W, rec.data() + rec_index(f, 0), quirks, o, stage, silk_resampler_frac_FIR_12);
+        silk_synth_packet(sst[j], *W, H, side_live, rec.data() + rec_index(f, 0), quirks, o, stage, silk_resampler_frac_FIR_12);
       }
     }
     delete W;
