@@ -142,7 +142,7 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
   };
 
   for (uint32_t t = 0; t < P.n_ticks; t++) {
-    int N = 0;
+    int N = 0, hyb = 0;
     const float* x = nullptr;
     float* out = nullptr;
     if (live) {
@@ -153,8 +153,12 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
         x = ser + m.sample_off;
         const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
         out = P.pcm_f32 ? P.pcm_f32 + (size_t)p * P.pcm_stride : nullptr;
+        if (m.flags & 4u) d.mem = 0.f;                 // CELT reset before this frame
+        if ((m.flags & 8u) && out) hyb = 1;            // hybrid: add to the SILK samples already in the row
       }
     }
+    const unsigned hyb_mask = __ballot_sync(0xffffffffu, hyb);
+    d.apply_gain = hyb ? 0 : P.apply_gain;             // hybrid: the gain applies to SILK + CELT, at the store below
     __syncwarp();
     row_x[l] = x; row_out[l] = out; row_n[l] = N;
     const int max_n = __reduce_max_sync(0xffffffffu, N);
@@ -186,7 +190,13 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
           o += (size_t)k0 * 2;
           const float* tx = tile + r * PITCH;
           const float* ty = tx + PITCH;
-          if (((uintptr_t)o & 15u) == 0) {
+          if ((hyb_mask >> r) & 1u) {
+            for (int e = l; e < 2 * cnt; e += 32) {
+              float v = o[e] + ((e & 1) ? ty[e >> 1] : tx[e >> 1]);
+              if (P.apply_gain) v *= P.gain;
+              o[e] = v;
+            }
+          } else if (((uintptr_t)o & 15u) == 0) {
             for (int j = 2 * l; j < cnt; j += 64) {   // float4 = (x[j], y[j], x[j+1], y[j+1])
               const float2 a = *(const float2*)(tx + j), b = *(const float2*)(ty + j);
               *(float4*)(o + 2 * j) = make_float4(a.x, b.x, a.y, b.y);
@@ -202,7 +212,14 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
           const int cnt = min(CH, row_n[r] - k0);
           if (!o || cnt <= 0) continue;
           const float* tx = tile + r * PITCH;
-          for (int j = l; j < cnt; j += 32) o[k0 + j] = tx[j];
+          if ((hyb_mask >> r) & 1u) {
+            for (int j = l; j < cnt; j += 32) {
+              float v = o[k0 + j] + tx[j];
+              if (P.apply_gain) v *= P.gain;
+              o[k0 + j] = v;
+            }
+          } else
+            for (int j = l; j < cnt; j += 32) o[k0 + j] = tx[j];
         }
       }
       __syncwarp();
@@ -309,11 +326,16 @@ __global__ void __launch_bounds__(64, 12) k_silk(uint32_t n_lanes, uint32_t n_ti
     const uint32_t f = t * n_lanes + lane;
     if (!(meta[f].flags & 2u)) continue;
     const uint32_t p = pkt_map ? pkt_map[f] : f;
+    const uint32_t* rb = rec + rec_index(f, 0);
+    const bool hybrid = (meta[f].flags & 8u) != 0;
     SilkPcmOut o;
-    o.f32 = pcm_f32 ? pcm_f32 + (size_t)p * pcm_stride : nullptr;
-    o.i16 = pcm_i16 ? pcm_i16 + (size_t)p * pcm_stride : nullptr;
-    o.CC = CC; o.gain = gain; o.apply_gain = apply_gain;
-    silk_synth_packet(S, W, H, side_live, rec + rec_index(f, 0), quirks, o, stage[threadIdx.x], fir);
+    // hybrid cells always go to the float row (the CELT bands are added by k_deemph, then soft clip / gain follow);
+    // SILK-only cells are final: int16 directly on the i16 path
+    o.f32 = (hybrid || !pcm_i16) ? pcm_f32 + (size_t)p * pcm_stride : nullptr;
+    o.i16 = (hybrid || !pcm_i16) ? nullptr : pcm_i16 + (size_t)p * pcm_stride;
+    o.CC = CC; o.gain = gain; o.apply_gain = hybrid ? 0 : apply_gain;
+    silk_synth_packet(S, W, H, side_live, rb[(hybrid ? S_SILK_HYB : S_HDR0) * 32], rb + (hybrid ? S_SILK_HYB + 1 : SL_BASE) * 32, quirks, o,
+                      stage[threadIdx.x], fir);
   }
   silk_hist_store(W, H, 0);
   if (side_live) silk_hist_store(W, H, 1);
@@ -555,6 +577,16 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     k_energy<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, nt, map, h->rec.as<uint32_t>(), h->states.as<StreamState>(), d_lane_stream,
                                                 h->en.as<float>(), h->meta.as<FrameMeta>(), samples, range, h->cfg.quirks);
     h->prof_end(s);
+    // SILK synthesis (SILK-only and hybrid cells), before the CELT tail so that k_deemph can add the CELT bands of hybrid
+    // frames on top. SILK-only samples are exact int16 values scaled by 2^-15: on the i16 path soft clip + float2int16
+    // is the identity and the lane stores int16 directly; hybrid cells go through the float row.
+    h->prof_begin(BD_K_SILK, s);
+    k_silk<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, nt, map, d_lane_stream, h->rec.as<uint32_t>(), h->meta.as<FrameMeta>(),
+                                              h->silk_states.as<SilkState>(), h->silk_hist.as<uint32_t>(), h->cfg.n_streams, pcm,
+                                              d_pcm_i16 ? d_pcm_i16 + shift * pcm_stride : nullptr, pcm_stride, CC, h->cfg.quirks, h->gain,
+                                              h->cfg.gain_q8 != 0);
+    h->prof_end(s);
+    h->launches += 1;
     PvqParams pq;
     pq.rec = h->rec.as<uint32_t>(); pq.meta = h->meta.as<FrameMeta>(); pq.xbuf = h->xbuf.as<float>();
     pq.iy_dbg = d_dbg_iy ? d_dbg_iy + cell0 * 2 * MAX_N : nullptr;
@@ -595,16 +627,6 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     }
     h->prof_end(s);
     h->launches += 8;
-    // SILK-only packets: written straight to the caller's PCM rows. Their samples are exact int16 values scaled by
-    // 2^-15, so on the i16 path soft clip + float2int16 is the identity and the lane stores int16 directly.
-    h->prof_begin(BD_K_SILK, s);
-    k_silk<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, nt, map, d_lane_stream, h->rec.as<uint32_t>(), h->meta.as<FrameMeta>(),
-                                              h->silk_states.as<SilkState>(), h->silk_hist.as<uint32_t>(), h->cfg.n_streams,
-                                              d_pcm_i16 ? nullptr : pcm,
-                                              d_pcm_i16 ? d_pcm_i16 + shift * pcm_stride : nullptr, pcm_stride, CC, h->cfg.quirks, h->gain,
-                                              h->cfg.gain_q8 != 0);
-    h->prof_end(s);
-    h->launches += 1;
     if (d_pcm_i16) {
       h->prof_begin(BD_K_CLIP_I16, s);
       k_clip_i16<<<(n_lanes + CLIP_WARPS - 1) / CLIP_WARPS, 32 * CLIP_WARPS, 0, s>>>(

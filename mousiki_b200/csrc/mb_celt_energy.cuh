@@ -51,7 +51,8 @@ struct FrameMeta {
   uint32_t seed_in;      // LCG seed for quant_all_bands (= rng left by the previous frame)
   uint32_t sample_off;   // first sample of this frame in the lane's time series (excluding HIST)
   uint32_t lane;         // lane (stream slot) of this call
-  uint32_t flags;        // bit0: frame runs through phases 2b/2c
+  uint32_t flags;        // bit0: frame runs through phases 2b/2c; bit1: SILK synthesis (k_silk); bit2: CELT state reset before
+                         // this frame; bit3: the CELT output is added to the SILK output already in the PCM row (hybrid)
 };
 enum { EN_STRIDE = 3 * 2 * NB_EBANDS };  // per-frame energy scratch: E, prev1 (old_log_e), prev2 (old_log_e2)
 
@@ -77,16 +78,19 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
       continue;
     }
     uint32_t h0 = r[S_HDR0 * 32];
-    // Mode switches between SILK-only and CELT-only packets go through decode_frame(None) = concealment
-    // (opus_decoder.rs:575-593, 798-809): row F2, reported per packet without touching the stream.
-    const bool silk_cell = ((status >> 16) & 1u) != 0;
-    if ((silk_cell && st.prev_mode == 1002) || (!silk_cell && (st.prev_mode == 1000 || st.prev_mode == 1001))) {
+    // Mode switches that go through decode_frame(None) = concealment (opus_decoder.rs:575-593, 798-809: CELT-only <->
+    // SILK-only / hybrid) or through the 2.5 ms CELT silence frame (hybrid -> SILK-only, :868-893) are rows F1/F2: reported
+    // per packet without touching the stream.
+    const bool silk_bit = ((status >> 16) & 1u) != 0, hybrid = ((status >> 17) & 1u) != 0;
+    const bool silk_only = silk_bit && !hybrid;
+    if ((!silk_bit && (st.prev_mode == 1000 || st.prev_mode == 1001)) || (silk_bit && st.prev_mode == 1002) ||
+        (silk_only && st.prev_mode == 1001)) {
       meta[f] = m;
       samples_out[p] = MB_UNIMPLEMENTED;
       final_range_out[p] = st.range_final;
       continue;
     }
-    if (silk_cell) {  // SILK-only packet: synthesis runs in k_silk (mb_silk_out.cuh); here only the front-end bookkeeping
+    if (silk_only) {  // SILK-only packet: synthesis runs in k_silk (mb_silk_out.cuh); here only the front-end bookkeeping
       const int sc = (int)((h0 >> 8) & 3u) * (int)((h0 >> 5) & 7u);   // frames x subframes: 2, 4, 8, 12 -> 10, 20, 40, 60 ms
       const int N = sc * 240;
       m.flags = 2;
@@ -97,6 +101,14 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
       samples_out[p] = N;
       final_range_out[p] = st.range_final;
       continue;
+    }
+    // SILK-only -> hybrid: the CELT decoder is reset before the frame (opus_decoder.rs:895-898). The energy side is reset
+    // here; the tail kernels reset their own state (post-filter, history, de-emphasis memory) on flag bit 2.
+    const bool celt_reset = hybrid && st.prev_mode == 1000;
+    if (celt_reset) {
+      for (int i = 0; i < 2 * NB_EBANDS; i++) { st.old_ebands[i] = 0.f; st.old_log_e[i] = -28.f; st.old_log_e2[i] = -28.f; st.background_log_e[i] = 0.f; }
+      st.rng = 0; st.loss_duration = 0;
+      m.seed_in = 0;
     }
     const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), start = (int)MB_H0_START(h0), end = (int)MB_ST_END(status);
     const int intra = (int)MB_H0_INTRA(h0), silence = (int)MB_H0_SILENCE(h0), transient = (int)MB_H0_TRANSIENT(h0);
@@ -168,7 +180,7 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
     st.loss_duration = 0;
     if (status & (1u << 13)) st.celt_error = 1;
     const int N = M * SHORT_MDCT;
-    m.flags = 1;
+    m.flags = hybrid ? (1u | 2u | 8u | (celt_reset ? 4u : 0u)) : 1u;   // bit0 CELT, bit1 SILK, bit2 CELT reset, bit3 accumulate
     meta[f] = m;
     sample_off += (uint32_t)N;
     int code = MB_ST_CODE(status);
@@ -176,7 +188,7 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
       samples_out[p] = code;
       final_range_out[p] = st.range_final;
     } else {
-      st.prev_mode = 1002;
+      st.prev_mode = hybrid ? 1001 : 1002;
       st.range_final = st.rng;
       st.last_packet_duration = N;
       samples_out[p] = N;

@@ -321,13 +321,15 @@ MB_DEV int laplace_symbol(RangeDec& dec, uint32_t fs, uint32_t decay) {
 
 // Whole-frame parse. `rec_base` = &rec[rec_index(f, 0)].
 // Returns the status word (also stored in S_STATUS).
+// `pre`: a range decoder already positioned behind the SILK payload of a hybrid frame (null: open a fresh one);
+// `status_extra`: bits OR-ed into the status word (cell kind).
 MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, int C, int start, int end, uint32_t quirks,
-                                          int disable_inv, uint32_t* rec_base) {
+                                          int disable_inv, uint32_t* rec_base, const RangeDec* pre = nullptr, uint32_t status_extra = 0) {
   ParseCtx cx;
   cx.w.base = rec_base; cx.w.n_nodes = 0; cx.w.n_leaves = 0; cx.w.overflow = 0;
   cx.disable_inv = disable_inv; cx.lm_frame = lm;
   RangeDec& dec = cx.dec;
-  dec.open(data, (uint32_t)len);
+  if (pre) dec = *pre; else dec.open(data, (uint32_t)len);
   const int M = 1 << lm;
   const int len_bits = len * 8;
 
@@ -699,7 +701,7 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
                        ((uint32_t)pf_tapset << 20) | ((uint32_t)pf_qg1 << 22) | ((uint32_t)start << 26));
   cx.w.put(S_HDR1, (uint32_t)pf_pitch | ((uint32_t)imin(cx.w.n_nodes, CAP_NODES) << 11) | ((uint32_t)imin(cx.w.n_leaves, CAP_LEAVES) << 22));
   cx.w.put(S_RANGE, dec.rng);
-  uint32_t status = (uint32_t)(uint8_t)(int8_t)code | ((uint32_t)end << 8) | ((uint32_t)(dec.error != 0) << 13) | (1u << 14);
+  uint32_t status = (uint32_t)(uint8_t)(int8_t)code | ((uint32_t)end << 8) | ((uint32_t)(dec.error != 0) << 13) | (1u << 14) | status_extra;
   cx.w.put(S_STATUS, status);
   return status;
 }

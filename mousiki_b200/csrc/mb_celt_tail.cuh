@@ -101,6 +101,11 @@ MB_DEV void celt_comb_channel(Team tm, CombSmem* sm, uint32_t lane, int c, const
     const uint32_t* r = P.rec + rec_index(f, 0);
     const uint32_t h0 = r[S_HDR0 * 32], h1 = r[S_HDR1 * 32];
     const int lm = (int)MB_H0_LM(h0), N = SHORT_MDCT << lm;
+    if (m.flags & 4u) {  // CELT decoder reset before this frame (SILK-only -> hybrid)
+      for (int i = tm.tid; i < HIST; i += tm.n) buf[i] = 0.f;
+      pf_period = pf_period_old = 0; pf_tapset = pf_tapset_old = 0; pf_gain = pf_gain_old = 0.f;
+      MB_SYNC();
+    }
     const int new_pitch = (int)MB_H1_PITCH(h1), new_tapset = (int)MB_H0_TAPSET(h0);
     const float new_gain = 0.09375f * (float)MB_H0_QG1(h0);
     float* xg = ser + m.sample_off;
@@ -142,10 +147,13 @@ MB_DEV void celt_comb_channel(Team tm, CombSmem* sm, uint32_t lane, int c, const
 struct Deemph {
   float mem, gain;
   int apply_gain;
-  MB_MEM float step(float xv) {
+  // prev/accum: hybrid frames add the CELT signal to the SILK samples already in the row (celt_decoder.rs:2261-2266);
+  // the decode gain then applies to the sum (opus_decoder.rs:1376-1392)
+  MB_MEM float step(float xv, float prev = 0.f, bool accum = false) {
     const float tv = xv + mem + 1.0e-30f;
     mem = 0.8500061035f * tv;
     float v = tv * (1.0f / 32768.0f);
+    if (accum) v = prev + v;
     if (apply_gain) v *= gain;
     return v;
   }
@@ -166,8 +174,10 @@ MB_DEV void celt_deemph_lane(uint32_t lane, int c, const TailParams& P) {
     const float* x = ser + m.sample_off;
     const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
     float* out = P.pcm_f32 ? P.pcm_f32 + (size_t)p * P.pcm_stride + c : nullptr;
+    if (m.flags & 4u) d.mem = 0.f;
+    const bool accum = (m.flags & 8u) != 0;
     for (int j = 0; j < N; j++) {
-      const float v = d.step(x[j]);
+      const float v = d.step(x[j], accum && out ? out[(size_t)j * CC] : 0.f, accum);
       if (out) out[(size_t)j * CC] = v;
     }
   }

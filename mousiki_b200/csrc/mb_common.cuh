@@ -65,7 +65,8 @@ enum {
   S_PLAN = S_LEAVES + 3 * CAP_LEAVES,  // 1 word: operation words written by the band plan (0xffffffff: overflow)
   S_OPS = S_PLAN + 1,              // CAP_OPS words: the band plan's operation list (mb_celt_plan.cuh)
   CAP_OPS = 2048,
-  REC_SLOTS = S_OPS + CAP_OPS,
+  S_SILK_HYB = S_OPS + CAP_OPS,    // hybrid cells: SILK header word, then one SILK frame record (mb_silk_parse.cuh)
+  REC_SLOTS = S_SILK_HYB + 344,
 };
 
 // S_HDR0 fields

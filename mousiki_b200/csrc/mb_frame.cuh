@@ -28,9 +28,27 @@ MB_DEV void parse_cell(const uint8_t* arena, const uint32_t* offsets, uint32_t p
     toc = data[0];
     if (toc & 3u) code = MB_UNIMPLEMENTED;              // multi-frame packets (row F1)
     else if (!(toc & 0x80u)) {
-      if ((toc & 0x60u) == 0x60u) code = MB_UNIMPLEMENTED;   // hybrid (row A16, second half)
-      else if (len - 1 <= 1) code = MB_UNIMPLEMENTED;        // concealment (src/opus_decoder.rs:491)
-      else { silk_parse_frame(data + 1, len - 1, toc, quirks, cap_per_ch, rec_base); return; }
+      if (len - 1 <= 1) code = MB_UNIMPLEMENTED;             // concealment (src/opus_decoder.rs:491)
+      else if ((toc & 0x60u) == 0x60u) {
+        // hybrid: SILK WB payload, optional redundancy header, then CELT bands 17.. from the same range decoder
+        // (src/opus_decoder.rs:596-985)
+        const int lm = (toc & 0x08u) ? 3 : 2;                // 20 / 10 ms
+        const int C = (toc & 4u) ? 2 : 1;
+        if ((SHORT_MDCT << lm) > cap_per_ch) code = MB_BUFFER_TOO_SMALL;
+        else {
+          RangeDec ec;
+          ec.open(data + 1, (uint32_t)(len - 1));
+          silk_parse_payload(ec, 16, lm == 3 ? 4 : 2, 1, C, quirks, rec_base + (S_SILK_HYB + 1) * 32);
+          int redundancy = 0;
+          if (ec.tell() + 17 + 20 <= 8 * (len - 1)) redundancy = ec.bit_logp(12);
+          if (redundancy) code = MB_UNIMPLEMENTED;           // CELT redundancy frame + cross-fade: next row
+          else {
+            rec_base[S_SILK_HYB * 32] = 16u | ((uint32_t)(lm == 3 ? 4 : 2) << 5) | (1u << 8) | ((uint32_t)C << 10);
+            celt_parse_frame(data + 1, len - 1, lm, C, 17, (toc & 0x10u) ? 21 : 19, quirks, disable_inv, rec_base, &ec, 3u << 16);
+            return;
+          }
+        }
+      } else { silk_parse_frame(data + 1, len - 1, toc, quirks, cap_per_ch, rec_base); return; }
     }
   }
   if (code == MB_OK) {

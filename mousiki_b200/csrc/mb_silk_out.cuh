@@ -232,16 +232,16 @@ MB_DEV void silk_hist_store(const SilkWork& W, const SilkHistRef& H, int n) {
 // One SILK-only packet of one stream: silk_decode (dec_api.rs:132-441) once per 10/20 ms SILK frame in the packet.
 // stage: 32 lane-private words; fir: interpolation table; side_live: the side channel's ring holds its history.
 // Returns samples per channel written at 48 kHz.
-MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const SilkHistRef& H, int& side_live, const uint32_t* rec_base,
+// h0: the SILK header word; frames: the first frame record (SILK-only: slots S_HDR0 / SL_BASE, hybrid: S_SILK_HYB / + 1).
+MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const SilkHistRef& H, int& side_live, uint32_t h0, const uint32_t* frames,
                                       uint32_t quirks, const SilkPcmOut& o, int32_t* stage, const int16_t* fir) {
-  const uint32_t h0 = rec_base[S_HDR0 * 32];
   const int fs = (int)MB_SH_FS(h0), nb = (int)MB_SH_SUBFR(h0), n_frames = (int)MB_SH_FRAMES(h0), nci = (int)MB_SH_NCI(h0);
   const int CC = o.CC;
   const int L = 5 * fs * nb, ltp_mem = 20 * fs;
   int pos = 0;
   if (nci == 2 && !side_live) { silk_hist_load(W, H, 1); side_live = 1; }
   for (int i = 0; i < n_frames; i++) {
-    const uint32_t* fr = rec_base + (SL_BASE + i * SL_FRAME_WORDS) * 32;
+    const uint32_t* fr = frames + (i * SL_FRAME_WORDS) * 32;
     if (nci > S.n_channels_internal) {                       // dec_api.rs:150-154
       if (quirks & S4_STEREO_REINIT) { silk_chan_reset(S.ch[0]); silk_ring_clear(W.hist[0], W.pos[0]); }
       silk_chan_reset(S.ch[1]); silk_ring_clear(W.hist[1], W.pos[1]);

@@ -223,20 +223,10 @@ MB_DEV void silk_store_pulses(const int16_t* q, int frame_length, uint32_t* w /*
   for (int k = 0; 2 * k < frame_length; k++) w[k * 32] = (uint32_t)(uint16_t)q[2 * k] | ((uint32_t)(uint16_t)q[2 * k + 1] << 16);
 }
 
-// The SILK payload of one SILK-only Opus frame. `data`/`len`: the frame without its TOC. Returns through rec_base.
-// cap_per_ch: PCM capacity per channel at 48 kHz.
-MB_DEV_NOINLINE void silk_parse_frame(const uint8_t* data, int len, uint32_t toc, uint32_t quirks, int cap_per_ch, uint32_t* rec_base) {
-  const int bw = (int)((toc >> 5) & 3u);                 // 0 NB, 1 MB, 2 WB (3 = SWB never appears in SILK-only configs 0..11)
-  const int sc = (int)((toc >> 3) & 3u);                 // 10, 20, 40, 60 ms
-  const int fs_khz = bw == 0 ? 8 : (bw == 1 ? 12 : 16);
-  const int n_frames = sc <= 1 ? 1 : sc;                 // dec_api.rs:351-359
-  const int nb_subfr = sc == 0 ? 2 : 4;
-  const int nci = (toc & 4u) ? 2 : 1;
-  const int samples48 = (sc == 3 ? 2880 : (480 << sc));
-  if (samples48 > cap_per_ch) { rec_base[S_STATUS * 32] = (uint32_t)(uint8_t)(int8_t)MB_BUFFER_TOO_SMALL | (1u << 16); return; }
+// The SILK payload behind an open range decoder: flags, LBRR skip, and per frame the stereo predictor and each channel's
+// side information + pulses, stored from slot `frames` on (frame i at frames + i * SL_FRAME_WORDS * 32 words).
+MB_DEV_NOINLINE void silk_parse_payload(RangeDec& ec, int fs_khz, int nb_subfr, int n_frames, int nci, uint32_t quirks, uint32_t* frames) {
   const SilkRate R = silk_rate(fs_khz, nb_subfr);
-  RangeDec ec;
-  ec.open(data, (uint32_t)len);
   int vad[2][3], lbrr_flags[2][3], prev_type[2] = {0, 0}, prev_lag[2] = {0, 0};
   for (int n = 0; n < nci; n++) {                        // dec_api.rs:451-456
     for (int i = 0; i < n_frames; i++) vad[n][i] = ec.bit_logp(1);
@@ -273,7 +263,7 @@ MB_DEV_NOINLINE void silk_parse_frame(const uint8_t* data, int len, uint32_t toc
   // conditional-coding mode of the side channel for frame_index > 0, where it is the previous frame of this packet.
   int prev_dom = 0;
   for (int i = 0; i < n_frames; i++) {
-    uint32_t* fr = rec_base + (SL_BASE + i * SL_FRAME_WORDS) * 32;
+    uint32_t* fr = frames + (i * SL_FRAME_WORDS) * 32;
     int32_t pred[2] = {0, 0};
     if (nci == 2) {
       silk_parse_stereo_pred(ec, pred);
@@ -300,6 +290,21 @@ MB_DEV_NOINLINE void silk_parse_frame(const uint8_t* data, int len, uint32_t toc
     }
     prev_dom = decode_only_middle;
   }
+}
+
+// One SILK-only Opus frame. `data`/`len`: the frame without its TOC. cap_per_ch: PCM capacity per channel at 48 kHz.
+MB_DEV_NOINLINE void silk_parse_frame(const uint8_t* data, int len, uint32_t toc, uint32_t quirks, int cap_per_ch, uint32_t* rec_base) {
+  const int bw = (int)((toc >> 5) & 3u);                 // 0 NB, 1 MB, 2 WB (3 = SWB never appears in SILK-only configs 0..11)
+  const int sc = (int)((toc >> 3) & 3u);                 // 10, 20, 40, 60 ms
+  const int fs_khz = bw == 0 ? 8 : (bw == 1 ? 12 : 16);
+  const int n_frames = sc <= 1 ? 1 : sc;                 // dec_api.rs:351-359
+  const int nb_subfr = sc == 0 ? 2 : 4;
+  const int nci = (toc & 4u) ? 2 : 1;
+  const int samples48 = (sc == 3 ? 2880 : (480 << sc));
+  if (samples48 > cap_per_ch) { rec_base[S_STATUS * 32] = (uint32_t)(uint8_t)(int8_t)MB_BUFFER_TOO_SMALL | (1u << 16); return; }
+  RangeDec ec;
+  ec.open(data, (uint32_t)len);
+  silk_parse_payload(ec, fs_khz, nb_subfr, n_frames, nci, quirks, rec_base + SL_BASE * 32);
   // SILK-only redundancy test (opus_decoder.rs:746-759): when at least 17 bits remain the frame carries a CELT
   // redundancy frame. That arm is not built yet: such packets are reported as unimplemented before any state moves.
   int code = MB_OK;

@@ -65,12 +65,6 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   tp.rec = rec.data(); tp.meta = meta.data(); tp.pkt_map = nullptr; tp.lane_stream = nullptr; tp.st_all = st.data(); tp.hist = hist.data();
   tp.series = series.data(); tp.series_stride = series_stride; tp.n_lanes = n_lanes; tp.n_ticks = n_ticks; tp.CC = CC;
   tp.gain = 1.f; tp.apply_gain = 0; tp.pcm_f32 = out; tp.pcm_stride = pcm_stride;
-  CombSmem* csm = new CombSmem;
-  for (uint32_t j = 0; j < n_lanes; j++)
-    for (int c = 0; c < CC; c++) celt_comb_channel(tm, csm, j, c, tp);
-  delete csm;
-  for (uint32_t j = 0; j < n_lanes; j++)
-    for (int c = 0; c < CC; c++) celt_deemph_lane(j, c, tp);
   // SILK-only packets (k_silk): lane per stream, ticks in order
   {
     std::vector<SilkState> sst(n_lanes);
@@ -85,15 +79,24 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
       for (uint32_t t = 0; t < n_ticks; t++) {
         const uint32_t f = t * n_lanes + j;
         if (!(meta[f].flags & 2u)) continue;
+        const bool hybrid = (meta[f].flags & 8u) != 0;
+        const uint32_t* rb = rec.data() + rec_index(f, 0);
         SilkPcmOut o;
-        o.f32 = pcm16 ? nullptr : out + (size_t)f * pcm_stride;
-        o.i16 = pcm16 ? pcm16 + (size_t)f * pcm_stride : nullptr;
+        o.f32 = (hybrid || !pcm16) ? out + (size_t)f * pcm_stride : nullptr;
+        o.i16 = (hybrid || !pcm16) ? nullptr : pcm16 + (size_t)f * pcm_stride;
         o.CC = CC; o.gain = 1.f; o.apply_gain = 0;
-        silk_synth_packet(sst[j], *W, H, side_live, rec.data() + rec_index(f, 0), quirks, o, stage, silk_resampler_frac_FIR_12);
+        silk_synth_packet(sst[j], *W, H, side_live, rb[(hybrid ? S_SILK_HYB : S_HDR0) * 32], rb + (hybrid ? S_SILK_HYB + 1 : SL_BASE) * 32,
+                          quirks, o, stage, silk_resampler_frac_FIR_12);
       }
     }
     delete W;
   }
+  CombSmem* csm = new CombSmem;
+  for (uint32_t j = 0; j < n_lanes; j++)
+    for (int c = 0; c < CC; c++) celt_comb_channel(tm, csm, j, c, tp);
+  delete csm;
+  for (uint32_t j = 0; j < n_lanes; j++)
+    for (int c = 0; c < CC; c++) celt_deemph_lane(j, c, tp);
   if (pcm16) {
     for (uint32_t j = 0; j < n_lanes; j++)
       for (uint32_t t = 0; t < n_ticks; t++) {
