@@ -69,6 +69,24 @@ __global__ void __launch_bounds__(32 * BANDS_WARPS) k_bands(BandsParams P, uint3
   celt_bands_frame(tm, &sm[threadIdx.x >> 5], f, P);
 }
 
+// Hybrid frames: one warp per lane, the lane's ticks in order, because the reference's fold buffer outlives the frame
+// (mb_celt_bands.cuh); `fold` is [stream][FOLD_WORDS].  Lanes without a hybrid frame leave after one pass over the flags.
+__global__ void __launch_bounds__(32 * BANDS_WARPS) k_bands_hyb(BandsParams P, uint32_t n_lanes, uint32_t n_ticks,
+                                                                 const uint32_t* __restrict__ lane_stream, float* fold) {
+  __shared__ BandsSmem sm[BANDS_WARPS];
+  const uint32_t lane = blockIdx.x * BANDS_WARPS + (threadIdx.x >> 5);
+  if (lane >= n_lanes) return;
+  Team tm = {(int)(threadIdx.x & 31), 32};
+  uint32_t any = 0;
+  for (uint32_t t = tm.tid; t < n_ticks; t += 32) any |= P.meta[(size_t)t * n_lanes + lane].flags & 8u;
+  if (!__any_sync(0xffffffffu, any != 0)) return;
+  float* fb = fold + (size_t)(lane_stream ? lane_stream[lane] : lane) * FOLD_WORDS;
+  for (uint32_t t = 0; t < n_ticks; t++) {
+    const uint32_t f = t * n_lanes + lane;
+    if (P.meta[f].flags & 8u) celt_bands_frame(tm, &sm[threadIdx.x >> 5], f, P, fb);
+  }
+}
+
 // one warp per (frame, channel); 4 units per CTA
 constexpr int IMDCT_WARPS = 4;
 __global__ void __launch_bounds__(32 * IMDCT_WARPS) k_imdct(ImdctParams P, uint32_t n_units) {
@@ -383,7 +401,7 @@ struct bd_handle {
   cudaStream_t copy_stream = nullptr;   // device -> host PCM of pass k overlaps the kernels of pass k + 1
   std::vector<cudaEvent_t> pass_events;
   struct PassOut { bool on = false; char* host_pcm = nullptr; const char* dev_pcm = nullptr; size_t elem = 0; } pass_out;
-  DevBuf states, silk_states, silk_hist, hist, rec, en, meta, series, xbuf;
+  DevBuf states, silk_states, silk_hist, fold, hist, rec, en, meta, series, xbuf;
   // staging for the host-buffer entry points
   DevBuf d_arena, d_offsets, d_pkt_map, d_lane_stream, d_flags, d_pcm, d_pcm16, d_samples, d_range, d_ids, d_dbg_iy, d_dbg_x;
   std::vector<uint32_t> h_pkt_map, h_lane_stream, h_lane_of_stream, h_epoch, h_count;
@@ -457,6 +475,8 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
   if (h->hist.ensure((size_t)cfg->n_streams * h->CC * HIST * sizeof(float)) != cudaSuccess) return fail(BD_ERR_ALLOC);
   if (h->silk_states.ensure((size_t)cfg->n_streams * sizeof(SilkState)) != cudaSuccess) return fail(BD_ERR_ALLOC);
   if (h->silk_hist.ensure((size_t)cfg->n_streams * 320 * sizeof(uint32_t)) != cudaSuccess) return fail(BD_ERR_ALLOC);
+  if (h->fold.ensure((size_t)cfg->n_streams * FOLD_WORDS * sizeof(float)) != cudaSuccess) return fail(BD_ERR_ALLOC);
+  if (cudaMemsetAsync(h->fold.p, 0, (size_t)cfg->n_streams * FOLD_WORDS * sizeof(float), h->own_stream) != cudaSuccess) return fail(BD_ERR_CUDA);
   k_silk_reset<<<(cfg->n_streams + 127) / 128, 128, 0, h->own_stream>>>(h->silk_states.as<SilkState>(), h->silk_hist.as<uint32_t>(),
                                                                         cfg->n_streams, nullptr, cfg->n_streams);
   k_reset<<<cfg->n_streams, 128, 0, h->own_stream>>>(h->states.as<StreamState>(), h->hist.as<float>(), nullptr, cfg->n_streams, h->CC);
@@ -468,7 +488,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
 void bd_destroy(bd_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  DevBuf* all[] = {&h->states, &h->silk_states, &h->silk_hist, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map,
+  DevBuf* all[] = {&h->states, &h->silk_states, &h->silk_hist, &h->fold, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map,
                    &h->d_lane_stream, &h->d_flags, &h->d_pcm, &h->d_pcm16, &h->d_samples, &h->d_range, &h->d_ids, &h->d_dbg_iy, &h->d_dbg_x};
   for (DevBuf* b : all) b->release();
   for (auto& sp : h->prof_spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -603,6 +623,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     bp.x_dbg = d_dbg_x ? d_dbg_x + cell0 * 2 * MAX_N : nullptr;
     h->prof_begin(BD_K_BANDS, s);
     k_bands<<<(cells + BANDS_WARPS - 1) / BANDS_WARPS, 32 * BANDS_WARPS, 0, s>>>(bp, cells);
+    k_bands_hyb<<<(n_lanes + BANDS_WARPS - 1) / BANDS_WARPS, 32 * BANDS_WARPS, 0, s>>>(bp, n_lanes, nt, d_lane_stream, h->fold.as<float>());
     h->prof_end(s);
     ImdctParams ip;
     ip.rec = h->rec.as<uint32_t>(); ip.meta = h->meta.as<FrameMeta>(); ip.xbuf = h->xbuf.as<float>(); ip.series = h->series.as<float>();

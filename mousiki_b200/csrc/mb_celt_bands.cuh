@@ -119,9 +119,14 @@ struct BandsParams {
   float* x_dbg;             // optional [frame][2*960] normalised spectrum after anti-collapse
 };
 
-MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsParams& P) {
+// fold: the stream's persistent fold buffer (FOLD_WORDS floats) for hybrid frames, else null.  The reference keeps
+// `scratch.norm_storage` in the decoder and never clears it (src/celt/bands.rs:2614-2625, src/celt/types.rs:400,416):
+// a hybrid frame starts at band 17, so its first folds read what EARLIER frames of the stream left there.  Frames that
+// carry flag 8 therefore run only when `fold` is given (tick order per stream); the parallel pass skips them.
+MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsParams& P, float* fold = nullptr) {
   const FrameMeta meta = P.meta[f];
   if (!(meta.flags & 1u)) return;
+  if (((meta.flags & 8u) != 0) != (fold != nullptr)) return;
   const uint32_t* r = P.rec + rec_index(f, 0);
   const uint32_t h0 = r[S_HDR0 * 32], status = r[S_STATUS * 32], plan = r[S_PLAN * 32];
   const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), start = (int)MB_H0_START(h0), end = (int)MB_ST_END(status);
@@ -132,8 +137,13 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
   float* norm = sm->norm;
   float* norm2 = norm + 800;
   // (CELT-only frames start at band 0: every fold source is written earlier in the same frame, so the fold buffer
-  //  needs no cross-frame persistence; hybrid frames will carry it in stream state)
-  for (int i = tm.tid; i < 2 * 800; i += tm.n) norm[i] = 0.f;
+  //  needs no cross-frame persistence)
+  const int norm_len = M * (eband(NB_EBANDS - 1) - eband(start));   // the reference's norm2 = norm + norm_len
+  if (fold) {
+    for (int i = tm.tid; i < norm_len; i += tm.n) { norm[i] = fold[i]; norm2[i] = fold[norm_len + i]; }
+  } else {
+    for (int i = tm.tid; i < 2 * 800; i += tm.n) norm[i] = 0.f;
+  }
   for (int idx = tm.tid; idx < C * NB_EBANDS; idx += tm.n) sm->gains[idx] = celt_exp2(fmin32(E[idx] + kEMeans[idx % NB_EBANDS], 32.0f));
   OpReader ops;
   ops.open(r + S_OPS * 32, (int)plan, tm.tid);
@@ -156,8 +166,9 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
         case OP_SKIP: ops.skip(len); break;
         case OP_COPY_LB: {
           const uint32_t w1 = ops.next();
-          const float* src = ((w1 >> 11) & 1u ? norm2 : norm) + (w1 & 2047u);
-          for (int j = tm.tid; j < len; j += tm.n) sm->scratch[j] = src[j];
+          float* src = ((w1 >> 11) & 1u ? norm2 : norm) + (w1 & 2047u);
+          if (p & 1u) { for (int j = tm.tid; j < len; j += tm.n) src[j] = sm->scratch[j]; }
+          else for (int j = tm.tid; j < len; j += tm.n) sm->scratch[j] = src[j];
           MB_SYNC();
         } break;
         case OP_HAAR: {
@@ -297,6 +308,13 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
     for (int idx = tm.tid; idx < C * n; idx += tm.n) {
       int c = idx >= n, j = idx - c * n;
       xrow[c * N + band_start + j] = sm->win[c * WIN_Y + j] * sm->gains[c * NB_EBANDS + band];
+    }
+    MB_SYNC();
+  }
+  if (fold) {
+    for (int i = tm.tid; i < norm_len; i += tm.n) {
+      fold[i] = norm[i];
+      if (C == 2) fold[norm_len + i] = norm2[i];
     }
     MB_SYNC();
   }

@@ -22,7 +22,7 @@ namespace mb {
 enum {
   OP_END_BAND = 0,
   OP_SKIP = 1,      // n = words to skip after this one
-  OP_COPY_LB = 2,   // scratch[0..n) = norm[w1 & 2047 ..] (w1 bit 11: second fold buffer)                        +1 word
+  OP_COPY_LB = 2,   // scratch[0..n) = norm[w1 & 2047 ..] (w1 bit 11: second fold buffer); p & 1: the other way  +1 word
   OP_HAAR = 3,      // haar1 over n samples, stride 1 << (p >> 1), buffer p & 1 (0 window at a, 1 scratch)
   OP_DEINT = 4,     // deinterleave_hadamard: stride 1 << ((p >> 1) & 7), hadamard p >> 4, buffer p & 1
   OP_INTER = 5,     // interleave_hadamard, same fields
@@ -57,6 +57,7 @@ struct Plan {
   int node_pos, leaf_pos, n_ops, n_fold, overflow;
   uint32_t seed;
   int tf_change;
+  int lb_inplace;            // last band of a hybrid frame: the fold source is transformed in place (see plan_band)
 
   MB_MEM void put(uint32_t w) {
     if (n_ops < CAP_OPS) ops[(size_t)n_ops * 32] = w; else overflow = 1;
@@ -170,10 +171,14 @@ MB_DEV uint32_t plan_band(Plan& P, int a, int n, int B, int lb_src, int lb_which
   const int B0 = B, n_b0 = n_b;
   const int il_stride_log = ilog2_exact(B0 << recombine);
   if (B0 > 1 && have_lb) P.put(MB_OP(OP_DEINT, 0, n, 1 | (il_stride_log << 1) | (long_blocks << 4)));
+  // The reference hands the last band no scratch, so the transforms above run on the fold buffer itself
+  // (bands.rs:2176-2200); its fold buffer outlives the frame (types.rs:400), and the next hybrid frame of the stream reads it.
+  const int write_back = have_lb && P.lb_inplace && P.n_ops > lb_begin + 2;
+  if (write_back) { P.put(MB_OP(OP_COPY_LB, 0, n, 1)); P.put((uint32_t)lb_src | ((uint32_t)lb_which << 11)); }
   const int lb_end = P.n_ops;
   const int folds_before = P.n_fold;
   uint32_t cm = plan_partition(P, a, n, B, have_lb ? 0 : -1, gain, fill);
-  if (have_lb && P.n_fold == folds_before) P.set(lb_begin, MB_OP(OP_SKIP, 0, lb_end - lb_begin - 1, 0));  // nobody folded: dead work
+  if (have_lb && !write_back && P.n_fold == folds_before) P.set(lb_begin, MB_OP(OP_SKIP, 0, lb_end - lb_begin - 1, 0));  // nobody folded: dead work
   if (B0 > 1) P.put(MB_OP(OP_INTER, a, n, (il_stride_log << 1) | (long_blocks << 4)));
   n_b = n_b0;
   B = B0;
@@ -249,7 +254,7 @@ MB_DEV void celt_plan_frame(uint32_t f, const PlanParams& Q) {
   const int M = 1 << lm;
   Plan P;
   P.nodes = r + S_NODES * 32; P.leaves = r + S_LEAVES * 32; P.ops = r + S_OPS * 32;
-  P.node_pos = 0; P.leaf_pos = 0; P.n_ops = 0; P.n_fold = 0; P.overflow = 0; P.seed = meta.seed_in; P.tf_change = 0;
+  P.node_pos = 0; P.leaf_pos = 0; P.n_ops = 0; P.n_fold = 0; P.overflow = 0; P.seed = meta.seed_in; P.tf_change = 0; P.lb_inplace = 0;
   uint8_t collapse[2 * NB_EBANDS];
   uint16_t anti_pos[NB_EBANDS];
   for (int i = 0; i < 2 * NB_EBANDS; i++) collapse[i] = 0;
@@ -260,6 +265,7 @@ MB_DEV void celt_plan_frame(uint32_t f, const PlanParams& Q) {
     const uint32_t ba = r[(S_BANDA + i) * 32];
     const int band_start = M * eband(i), n = M * eband(i + 1) - band_start;
     P.tf_change = MB_BA_TF(ba);
+    P.lb_inplace = start != 0 && i + 1 == end;
     if (i == start + 1) {  // special_hybrid_folding (bands.rs:3517-3555)
       const int n1 = M * (eband(start + 1) - eband(start)), n2 = M * (eband(start + 2) - eband(start + 1));
       if (n2 > n1) { P.put(MB_OP(OP_HYB, 0, 0, 0)); P.put((uint32_t)n1 | ((uint32_t)(n2 - n1) << 11) | (MB_H0_DUAL(h0) << 22)); }

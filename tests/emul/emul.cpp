@@ -50,6 +50,10 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   BandsSmem* bsm = new BandsSmem;
   BandsParams bp; bp.rec = rec.data(); bp.en = en.data(); bp.meta = meta.data(); bp.xbuf = xbuf.data(); bp.x_dbg = x_dbg;
   for (uint32_t f = 0; f < F; f++) celt_bands_frame(tm, bsm, f, bp);
+  {  // hybrid frames: tick order per stream, fold buffer carried in stream state (k_bands_hyb)
+    std::vector<float> fold((size_t)n_lanes * FOLD_WORDS, 0.f);
+    for (uint32_t f = 0; f < F; f++) celt_bands_frame(tm, bsm, f, bp, fold.data() + (size_t)(f % n_lanes) * FOLD_WORDS);
+  }
   delete bsm;
   ImdctSmem* ism = new ImdctSmem;
   ImdctParams ip; ip.rec = rec.data(); ip.meta = meta.data(); ip.xbuf = xbuf.data(); ip.series = series.data();

@@ -162,11 +162,11 @@ def test_gpu_cres_known_answer():
 
 
 def test_gpu_unsupported_packets_report_per_packet_codes():
-    """Hybrid / multi-frame / lost packets are reported per packet and never poison the batch."""
+    """Redundancy-carrying / multi-frame / lost packets are reported per packet and never poison the batch."""
     from mousiki_b200 import BatchDecoder, pack_packets
 
     good = bytes([helpers.celt_toc(3, True)]) + bytes(helpers.lcg_bytes(1, 100))
-    silk = bytes([0x78]) + bytes(helpers.lcg_bytes(2, 30))  # hybrid FB 20 ms
+    silk = bytes([helpers.silk_toc(2, 1, False)]) + bytes(300)  # SILK WB 20 ms, spare bits: carries a CELT redundancy frame
     code1 = bytes([helpers.celt_toc(2, False) | 1]) + bytes(helpers.lcg_bytes(3, 40))
     arena, offsets = pack_packets([good, silk, code1, good])
     with BatchDecoder(4, 48000, 2) as dec:

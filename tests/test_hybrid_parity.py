@@ -1,0 +1,185 @@
+"""Hybrid packets (SILK WB 16 kHz + CELT bands 17..): the product against the oracle and
+against the reference's own hybrid decode vector.
+
+CPU: host build of the kernel bodies (tests/emul). GPU (-m gpu): the CUDA path through the C ABI.
+What is compared: sample counts and final_range bit for bit (one range decoder runs through the SILK payload, the
+redundancy flag and the CELT bands); PCM bit for bit on the CPU emulation (same float expression order as the oracle)
+and <= 1 LSB at int16 scale on the GPU (the tolerance BASELINE.json's north_star states for float PCM).
+Corpus: `TOC || random bytes` (the reference's fuzz construction, tests/test_opus_decode.rs:372-407) restricted to
+packets without a redundancy frame (helpers.silk_fuzz_grid); the reference's golden vector is
+tests/hybrid_decode.rs:55-124 transcribed into tests/golden/ref_hybrid_vectors.npz (tools/gen_ref_vectors.py).
+
+The FB 20 ms cases matter most: the reference's fold buffer (`norm_storage`, src/celt/types.rs:400,416) outlives the
+frame and its last band is transformed in place (src/celt/bands.rs:2176-2200), so a hybrid frame depends on the fold
+buffer the previous frames of the stream left behind."""
+import numpy as np
+import pytest
+
+import helpers
+
+S2 = 1 << 9
+TOL = 1.0 / 32768.0
+
+
+def hyb_toc(fb, ms20, stereo):
+    """config 12/13 = SWB 10/20 ms, 14/15 = FB 10/20 ms (RFC 6716 table 2, src/packet.rs:30-78)."""
+    return ((12 + 2 * int(fb) + int(ms20)) << 3) | (4 if stereo else 0)
+
+
+# fullband, 20 ms, packet stereo, decoder channels, payload range, seed
+CASES = [
+    (1, 1, False, 1, (30, 160), 1),
+    (1, 1, True, 2, (40, 200), 2),
+    (0, 1, False, 2, (30, 120), 3),
+    (1, 0, True, 1, (20, 100), 4),
+    (0, 0, True, 2, (20, 100), 5),
+    (1, 0, False, 1, (20, 80), 6),
+]
+
+
+def _corpus(fb, ms20, stereo, ch, payload, seed, lanes, ticks):
+    return helpers.silk_fuzz_grid(lanes, ticks, payload, lambda k, r: hyb_toc(fb, ms20, stereo), seed=seed, channels=ch)
+
+
+def _mixed_toc(k, rng):
+    """SILK-only WB and hybrid packets drawn per packet; SILK -> hybrid resets the CELT half (opus_decoder.rs:744-751),
+    hybrid -> SILK-only needs the CELT fade-out frame (next row) and must come back as -5."""
+    if rng.integers(0, 4) == 0:
+        return helpers.silk_toc(2, int(rng.integers(0, 2)), bool(rng.integers(0, 2)))
+    return hyb_toc(rng.integers(0, 2), rng.integers(0, 2), rng.integers(0, 2))
+
+
+def _golden_grid():
+    g = np.load(helpers.ROOT / "tests" / "golden" / "ref_hybrid_vectors.npz")
+    pk = [g["TRANSITION_SILK_PACKET"].astype(np.uint8), g["TRANSITION_HYBRID_PACKET"].astype(np.uint8)]
+    offsets = np.zeros(3, dtype=np.uint32)
+    offsets[1:] = np.cumsum([len(p) for p in pk])
+    return g, np.concatenate(pk), offsets
+
+
+@pytest.mark.parametrize("fb,ms20,stereo,ch,payload,seed", CASES)
+def test_emul_hybrid_matches_oracle(fb, ms20, stereo, ch, payload, seed):
+    lanes, ticks = 6, 7
+    arena, offsets = _corpus(fb, ms20, stereo, ch, payload, seed, lanes, ticks)
+    for i16 in (False, True):
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 960, i16=i16)
+        pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, ticks, ch, 960, i16=i16)
+        assert np.all(so > 0)
+        assert np.array_equal(so, se)
+        assert np.array_equal(ro, re)
+        assert np.array_equal(po, pe)
+
+
+def test_emul_hybrid_reference_vector():
+    """SILK WB packet then hybrid FB packet on a mono decoder: final_range 1329918976, 960 samples within 1e-4 of the
+    reference's PCM with quirk S2 off (libopus NLSF2A ordering; see test_silk_oracle_kat.test_hybrid_transition_vectors)."""
+    g, arena, offsets = _golden_grid()
+    for q, within in ((helpers.QUIRKS_MOUSIKI, False), (helpers.QUIRKS_MOUSIKI & ~S2, True)):
+        pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, 1, 2, 1, 960, quirks=q)
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, 1, 2, 1, 960, quirks=q)
+        assert se.tolist() == [960, 960]
+        assert int(re[1]) == int(g["TRANSITION_HYBRID_RANGE"][0])
+        assert np.array_equal(pe, po)
+        err = float(np.abs(pe[1, :960] - g["TRANSITION_HYBRID_PCM"]).max())
+        assert (err <= 1e-4) == within, (q, err)
+
+
+def test_emul_hybrid_after_silk_resets_celt_and_back_is_reported():
+    lanes, ticks = 8, 8
+    for ch in (1, 2):
+        arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, (30, 160), _mixed_toc, seed=60 + ch, channels=ch)
+        pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, ticks, ch, 960)
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 960)
+        tocs = arena[offsets[:-1]].reshape(ticks, lanes)
+        se2, so2 = se.reshape(ticks, lanes), so.reshape(ticks, lanes)
+        checked = 0
+        for j in range(lanes):
+            for t in range(ticks):
+                hybrid = (tocs[t, j] & 0x60) == 0x60
+                if t and not hybrid and (tocs[t - 1, j] & 0x60) == 0x60:
+                    assert se2[t, j] == -5       # hybrid -> SILK-only: CELT fade-out frame, next row
+                    break                        # the oracle decoded it: the streams part ways here
+                f = t * lanes + j
+                assert se2[t, j] == so2[t, j] and re[f] == ro[f] and np.array_equal(pe[f], po[f])
+                checked += 1
+        assert checked > lanes * 2
+
+
+# ---------------------------------------------------------------------------------------------- GPU
+def _decode_gpu(arena, offsets, lanes, ticks, ch, frame_size, i16, **kw):
+    from mousiki_b200 import BatchDecoder
+
+    ids = np.tile(np.arange(lanes, dtype=np.uint32), ticks)
+    with BatchDecoder(lanes, 48000, ch, **kw) as dec:
+        if i16:
+            return dec.decode(arena, offsets, ids, frame_size)
+        return dec.decode_float(arena, offsets, ids, frame_size)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fb,ms20,stereo,ch,payload,seed", CASES)
+def test_gpu_hybrid_matches_oracle(fb, ms20, stereo, ch, payload, seed):
+    lanes, ticks = 70, 6
+    arena, offsets = _corpus(fb, ms20, stereo, ch, payload, seed, lanes, ticks)
+    po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 960)
+    pg, sg, rg = _decode_gpu(arena, offsets, lanes, ticks, ch, 960, False)
+    assert np.array_equal(so, sg)
+    assert np.array_equal(ro, rg), "final_range must be bit-exact"
+    assert float(np.abs(po - pg).max()) <= TOL
+    p16o, _, _ = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 960, i16=True)
+    p16g, s16, r16 = _decode_gpu(arena, offsets, lanes, ticks, ch, 960, True)
+    assert np.array_equal(so, s16) and np.array_equal(ro, r16)
+    assert int(np.abs(p16o.astype(np.int32) - p16g.astype(np.int32)).max()) <= 1
+
+
+@pytest.mark.gpu
+def test_gpu_hybrid_reference_vector():
+    g, arena, offsets = _golden_grid()
+    pg, sg, rg = _decode_gpu(arena, offsets, 1, 2, 1, 960, False, quirks=helpers.QUIRKS_MOUSIKI & ~S2)
+    assert sg.tolist() == [960, 960]
+    assert int(rg[1]) == int(g["TRANSITION_HYBRID_RANGE"][0])
+    assert float(np.abs(pg[1, :960] - g["TRANSITION_HYBRID_PCM"]).max()) <= 1e-4
+
+
+@pytest.mark.gpu
+def test_gpu_hybrid_state_across_calls():
+    """One packet per stream per call == all ticks in one call: SILK state, CELT state and the fold buffer all live
+    in HBM between calls."""
+    from mousiki_b200 import BatchDecoder
+
+    lanes, ticks = 48, 6
+    arena, offsets = _corpus(1, 1, True, 2, (40, 200), 71, lanes, ticks)
+    pa, sa, ra = _decode_gpu(arena, offsets, lanes, ticks, 2, 960, False)
+    po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, 2, 960)
+    assert np.array_equal(sa, so) and np.array_equal(ra, ro) and float(np.abs(pa - po).max()) <= TOL
+    ids = np.arange(lanes, dtype=np.uint32)
+    with BatchDecoder(lanes, 48000, 2) as dec:
+        for t in range(ticks):
+            a = arena[offsets[t * lanes]:offsets[(t + 1) * lanes]]
+            o = (offsets[t * lanes:(t + 1) * lanes + 1] - offsets[t * lanes]).astype(np.uint32)
+            p, s, r = dec.decode_float(a, o, ids, 960)
+            assert np.array_equal(s, sa[t * lanes:(t + 1) * lanes])
+            assert np.array_equal(r, ra[t * lanes:(t + 1) * lanes])
+            assert np.array_equal(p[:, :1920], pa[t * lanes:(t + 1) * lanes, :1920]), "same kernels, same order: bit-identical"
+
+
+@pytest.mark.gpu
+def test_gpu_hybrid_silk_mix():
+    lanes, ticks = 64, 8
+    arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, (30, 160), _mixed_toc, seed=81, channels=2)
+    pg, sg, rg = _decode_gpu(arena, offsets, lanes, ticks, 2, 960, False)
+    po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, 2, 960)
+    tocs = arena[offsets[:-1]].reshape(ticks, lanes)
+    sg2, so2 = sg.reshape(ticks, lanes), so.reshape(ticks, lanes)
+    checked = 0
+    for j in range(lanes):
+        for t in range(ticks):
+            hybrid = (tocs[t, j] & 0x60) == 0x60
+            if t and not hybrid and (tocs[t - 1, j] & 0x60) == 0x60:
+                assert sg2[t, j] == -5
+                break
+            f = t * lanes + j
+            assert sg2[t, j] == so2[t, j] and rg[f] == ro[f]
+            assert float(np.abs(pg[f] - po[f]).max()) <= TOL
+            checked += 1
+    assert checked > lanes * 2
