@@ -28,7 +28,7 @@
 using namespace mb;
 
 // ------------------------------------------------------------------------------------------ kernels
-__global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ arena, const uint32_t* __restrict__ offsets,
+__global__ void __launch_bounds__(128, 7) k_parse(const uint8_t* __restrict__ arena, const uint32_t* __restrict__ offsets,
                                                const uint32_t* __restrict__ pkt_map, uint32_t n_cells, uint32_t* __restrict__ rec, int CC,
                                                uint32_t quirks, int disable_inv, int cap_per_ch, const uint8_t* __restrict__ flags) {
   uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;

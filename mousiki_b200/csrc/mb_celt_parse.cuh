@@ -323,13 +323,16 @@ MB_DEV int laplace_symbol(RangeDec& dec, uint32_t fs, uint32_t decay) {
 // Returns the status word (also stored in S_STATUS).
 // `pre`: a range decoder already positioned behind the SILK payload of a hybrid frame (null: open a fresh one);
 // `status_extra`: bits OR-ed into the status word (cell kind).
-MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, int C, int start, int end, uint32_t quirks,
+// START is a template parameter so that the CELT-only instance keeps `start == 0` folded away (the hybrid instance starts at 17).
+template <int START>
+MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, int C, int end, uint32_t quirks,
                                           int disable_inv, uint32_t* rec_base, const RangeDec* pre = nullptr, uint32_t status_extra = 0) {
+  constexpr int start = START;
   ParseCtx cx;
   cx.w.base = rec_base; cx.w.n_nodes = 0; cx.w.n_leaves = 0; cx.w.overflow = 0;
   cx.disable_inv = disable_inv; cx.lm_frame = lm;
   RangeDec& dec = cx.dec;
-  if (pre) dec = *pre; else dec.open(data, (uint32_t)len);
+  if (START != 0 && pre) dec = *pre; else dec.open(data, (uint32_t)len);
   const int M = 1 << lm;
   const int len_bits = len * 8;
 

@@ -44,7 +44,7 @@ MB_DEV void parse_cell(const uint8_t* arena, const uint32_t* offsets, uint32_t p
           if (redundancy) code = MB_UNIMPLEMENTED;           // CELT redundancy frame + cross-fade: next row
           else {
             rec_base[S_SILK_HYB * 32] = 16u | ((uint32_t)(lm == 3 ? 4 : 2) << 5) | (1u << 8) | ((uint32_t)C << 10);
-            celt_parse_frame(data + 1, len - 1, lm, C, 17, (toc & 0x10u) ? 21 : 19, quirks, disable_inv, rec_base, &ec, 3u << 16);
+            celt_parse_frame<17>(data + 1, len - 1, lm, C, (toc & 0x10u) ? 21 : 19, quirks, disable_inv, rec_base, &ec, 3u << 16);
             return;
           }
         }
@@ -60,7 +60,7 @@ MB_DEV void parse_cell(const uint8_t* arena, const uint32_t* offsets, uint32_t p
       const int bw = (int)((toc >> 5) & 3u);
       const int end = bw == 0 ? 13 : bw == 1 ? 17 : bw == 2 ? 19 : 21;
       const int C = (toc & 4u) ? 2 : 1;
-      celt_parse_frame(data + 1, len - 1, lm, C, 0, end, quirks, disable_inv, rec_base);
+      celt_parse_frame<0>(data + 1, len - 1, lm, C, end, quirks, disable_inv, rec_base);
       (void)CC;
       return;
     }
