@@ -20,6 +20,7 @@
 #include <vector>
 
 #include "../../include/mousiki_b200.h"
+#include "mb_host_packets.h"
 #include "mb_celt_imdct.cuh"
 #include "mb_celt_tail.cuh"
 #include "mb_frame.cuh"
@@ -40,10 +41,11 @@ __global__ void __launch_bounds__(128, 7) k_parse(const uint8_t* __restrict__ ar
 __global__ void __launch_bounds__(64) k_energy(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
                                                const uint32_t* __restrict__ rec, StreamState* st, const uint32_t* __restrict__ lane_stream,
                                                float* __restrict__ en, FrameMeta* __restrict__ meta, int32_t* __restrict__ samples_out,
-                                               uint32_t* __restrict__ final_range_out, uint32_t quirks) {
+                                               uint32_t* __restrict__ final_range_out, uint32_t quirks,
+                                               const uint8_t* __restrict__ flags) {
   uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
   if (lane >= n_lanes) return;
-  celt_energy_lane(lane, n_lanes, n_ticks, pkt_map, rec, st, lane_stream, en, meta, samples_out, final_range_out, quirks);
+  celt_energy_lane(lane, n_lanes, n_ticks, pkt_map, rec, st, lane_stream, en, meta, samples_out, final_range_out, quirks, flags);
 }
 
 constexpr int PVQ_THREADS = 64;
@@ -170,7 +172,7 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
         N = SHORT_MDCT << (int)MB_H0_LM(P.rec[rec_index(f, S_HDR0)]);
         x = ser + m.sample_off;
         const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
-        out = P.pcm_f32 ? P.pcm_f32 + (size_t)p * P.pcm_stride : nullptr;
+        out = P.pcm_f32 ? P.pcm_f32 + pcm_elem_off(P.out_map, p, P.pcm_stride) : nullptr;
         if (m.flags & 4u) d.mem = 0.f;                 // CELT reset before this frame
         if ((m.flags & 8u) && out) hyb = 1;            // hybrid: add to the SILK samples already in the row
       }
@@ -255,8 +257,9 @@ constexpr int CLIP_WARPS = 4;
 __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
                                                               const uint32_t* __restrict__ lane_stream, const FrameMeta* __restrict__ meta,
                                                               const int32_t* __restrict__ samples_out, StreamState* st,
-                                                              const float* __restrict__ pcm, int16_t* __restrict__ pcm16, uint32_t pcm_stride,
-                                                              int CC) {
+                                                              float* __restrict__ pcm, int16_t* __restrict__ pcm16, uint32_t pcm_stride,
+                                                              int CC, const uint32_t* __restrict__ out_map,
+                                                              const uint8_t* __restrict__ flags) {
   __shared__ __align__(16) float buf_[CLIP_WARPS][2 * MAX_N];
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
   const uint32_t lane = blockIdx.x * CLIP_WARPS + w;
@@ -268,10 +271,26 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
     const uint32_t f = t * n_lanes + lane;
     if (!(meta[f].flags & 1u)) continue;
     const uint32_t p = pkt_map ? pkt_map[f] : f;
-    const int n = samples_out[p];
+    int n = samples_out[p];
     if (n <= 0) continue;
+    if (out_map) {
+      // a packet cut into frames is clipped as a whole (src/opus_decoder.rs:1352-1366): its frames sit in the following
+      // ticks and in one contiguous stretch of the row; if one of them failed, the reference never reaches the clipper
+      if (flags[p] & 4u) continue;
+      bool failed = false;
+      uint32_t t2 = t + 1;
+      for (; t2 < n_ticks; t2++) {
+        const uint32_t p2 = pkt_map[t2 * n_lanes + lane];
+        if (p2 == 0xffffffffu || !(flags[p2] & 4u)) break;
+        const int n2 = samples_out[p2];
+        if (n2 <= 0) failed = true; else n += n2;
+      }
+      if (failed) continue;
+    }
     const int total = n * CC;
-    const float* src = pcm + (size_t)p * pcm_stride;
+    const size_t eo = pcm_elem_off(out_map, p, pcm_stride);
+    float* src = pcm + eo;
+    if (total > 2 * MAX_N) buf = src;   // long multi-frame packet: clip in place in the float scratch row
     int over = 0;
     for (int i = l; i < total; i += 32) {
       float v = src[i];
@@ -285,7 +304,7 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
       if (l < CC) soft_clip_channel(buf + l, n, CC, mem);
       __syncwarp();
     }
-    int16_t* dst = pcm16 + (size_t)p * pcm_stride;
+    int16_t* dst = pcm16 + eo;
     if ((((uintptr_t)dst) & 3u) == 0) {
       for (int i = 2 * l; i + 1 < total; i += 64) {
         const uint32_t lo = (uint16_t)float2int16(buf[i]), hi = (uint16_t)float2int16(buf[i + 1]);
@@ -296,6 +315,7 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
       for (int i = l; i < total; i += 32) dst[i] = float2int16(buf[i]);
     }
     __syncwarp();
+    buf = buf_[w];
   }
   if (l < 2) s.softclip_mem[l] = mem;
 }
@@ -323,7 +343,7 @@ __global__ void __launch_bounds__(64, 12) k_silk(uint32_t n_lanes, uint32_t n_ti
                                              const FrameMeta* __restrict__ meta, SilkState* st_all, uint32_t* silk_hist,
                                              uint32_t n_streams, float* __restrict__ pcm_f32,
                                              int16_t* __restrict__ pcm_i16, uint32_t pcm_stride, int CC, uint32_t quirks, float gain,
-                                             int apply_gain) {
+                                             int apply_gain, const uint32_t* __restrict__ out_map) {
   __shared__ int32_t stage[64][33];   // 32 staged output samples per lane, pitch 33: conflict-free for lockstep lanes
   __shared__ int16_t fir[48];
   if (threadIdx.x < 48) fir[threadIdx.x] = silk_resampler_frac_FIR_12[threadIdx.x];
@@ -349,8 +369,8 @@ __global__ void __launch_bounds__(64, 12) k_silk(uint32_t n_lanes, uint32_t n_ti
     SilkPcmOut o;
     // hybrid cells always go to the float row (the CELT bands are added by k_deemph, then soft clip / gain follow);
     // SILK-only cells are final: int16 directly on the i16 path
-    o.f32 = (hybrid || !pcm_i16) ? pcm_f32 + (size_t)p * pcm_stride : nullptr;
-    o.i16 = (hybrid || !pcm_i16) ? nullptr : pcm_i16 + (size_t)p * pcm_stride;
+    o.f32 = (hybrid || !pcm_i16) ? pcm_f32 + pcm_elem_off(out_map, p, pcm_stride) : nullptr;
+    o.i16 = (hybrid || !pcm_i16) ? nullptr : pcm_i16 + pcm_elem_off(out_map, p, pcm_stride);
     o.CC = CC; o.gain = gain; o.apply_gain = hybrid ? 0 : apply_gain;
     silk_synth_packet(S, W, H, side_live, rb[(hybrid ? S_SILK_HYB : S_HDR0) * 32], rb + (hybrid ? S_SILK_HYB + 1 : SL_BASE) * 32, quirks, o,
                       stage[threadIdx.x], fir);
@@ -403,8 +423,10 @@ struct bd_handle {
   struct PassOut { bool on = false; char* host_pcm = nullptr; const char* dev_pcm = nullptr; size_t elem = 0; } pass_out;
   DevBuf states, silk_states, silk_hist, fold, hist, rec, en, meta, series, xbuf;
   // staging for the host-buffer entry points
-  DevBuf d_arena, d_offsets, d_pkt_map, d_lane_stream, d_flags, d_pcm, d_pcm16, d_samples, d_range, d_ids, d_dbg_iy, d_dbg_x;
-  std::vector<uint32_t> h_pkt_map, h_lane_stream, h_lane_of_stream, h_epoch, h_count;
+  DevBuf d_arena, d_offsets, d_pkt_map, d_out_map, d_lane_stream, d_flags, d_pcm, d_pcm16, d_samples, d_range, d_ids, d_dbg_iy, d_dbg_x;
+  std::vector<uint32_t> h_pkt_map, h_lane_stream, h_lane_of_stream, h_epoch, h_count, h_tick, v_range;
+  std::vector<int32_t> v_samples;
+  mbh::Split split;
   uint32_t epoch = 0;
   int32_t* dbg_iy_host = nullptr;
   float* dbg_x_host = nullptr;
@@ -488,7 +510,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
 void bd_destroy(bd_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  DevBuf* all[] = {&h->states, &h->silk_states, &h->silk_hist, &h->fold, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map,
+  DevBuf* all[] = {&h->states, &h->silk_states, &h->silk_hist, &h->fold, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map, &h->d_out_map,
                    &h->d_lane_stream, &h->d_flags, &h->d_pcm, &h->d_pcm16, &h->d_samples, &h->d_range, &h->d_ids, &h->d_dbg_iy, &h->d_dbg_x};
   for (DevBuf* b : all) b->release();
   for (auto& sp : h->prof_spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -557,7 +579,7 @@ int bd_debug_capture(bd_handle* h, int32_t* pulses_host, float* spectrum_host, u
 static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32_t* d_offsets, const uint32_t* d_pkt_map,
                               const uint8_t* d_flags, uint32_t n_lanes, uint32_t n_ticks, const uint32_t* d_lane_stream, float* d_pcm_f32,
                               int16_t* d_pcm_i16, uint32_t pcm_stride, int32_t* d_samples, uint32_t* d_range, uint32_t n_packets,
-                              cudaStream_t s, int32_t* d_dbg_iy, float* d_dbg_x) {
+                              cudaStream_t s, int32_t* d_dbg_iy, float* d_dbg_x, const uint32_t* d_out_map = nullptr) {
   if (n_lanes == 0 || n_ticks == 0) return BD_OK;
   const int CC = h->CC;
   if (pcm_stride < (uint32_t)(SHORT_MDCT * CC)) return BD_ERR_BAD_ARG;
@@ -595,7 +617,8 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     h->prof_end(s);
     h->prof_begin(BD_K_ENERGY, s);
     k_energy<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, nt, map, h->rec.as<uint32_t>(), h->states.as<StreamState>(), d_lane_stream,
-                                                h->en.as<float>(), h->meta.as<FrameMeta>(), samples, range, h->cfg.quirks);
+                                                h->en.as<float>(), h->meta.as<FrameMeta>(), samples, range, h->cfg.quirks,
+                                                d_out_map ? flg : nullptr);
     h->prof_end(s);
     // SILK synthesis (SILK-only and hybrid cells), before the CELT tail so that k_deemph can add the CELT bands of hybrid
     // frames on top. SILK-only samples are exact int16 values scaled by 2^-15: on the i16 path soft clip + float2int16
@@ -604,7 +627,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     k_silk<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, nt, map, d_lane_stream, h->rec.as<uint32_t>(), h->meta.as<FrameMeta>(),
                                               h->silk_states.as<SilkState>(), h->silk_hist.as<uint32_t>(), h->cfg.n_streams, pcm,
                                               d_pcm_i16 ? d_pcm_i16 + shift * pcm_stride : nullptr, pcm_stride, CC, h->cfg.quirks, h->gain,
-                                              h->cfg.gain_q8 != 0);
+                                              h->cfg.gain_q8 != 0, d_out_map);
     h->prof_end(s);
     h->launches += 1;
     PvqParams pq;
@@ -635,7 +658,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     tp.rec = h->rec.as<uint32_t>(); tp.meta = h->meta.as<FrameMeta>(); tp.pkt_map = map; tp.lane_stream = d_lane_stream;
     tp.st_all = h->states.as<StreamState>(); tp.hist = h->hist.as<float>(); tp.series = h->series.as<float>();
     tp.series_stride = series_stride; tp.n_lanes = n_lanes; tp.n_ticks = nt; tp.CC = CC; tp.gain = h->gain;
-    tp.apply_gain = h->cfg.gain_q8 != 0; tp.pcm_f32 = pcm; tp.pcm_stride = pcm_stride;
+    tp.apply_gain = h->cfg.gain_q8 != 0; tp.pcm_f32 = pcm; tp.pcm_stride = pcm_stride; tp.out_map = d_out_map;
     h->prof_begin(BD_K_COMB, s);
     k_comb<<<(n_lanes * CC + COMB_WARPS - 1) / COMB_WARPS, 32 * COMB_WARPS, 0, s>>>(tp);
     h->prof_end(s);
@@ -652,7 +675,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
       h->prof_begin(BD_K_CLIP_I16, s);
       k_clip_i16<<<(n_lanes + CLIP_WARPS - 1) / CLIP_WARPS, 32 * CLIP_WARPS, 0, s>>>(
           n_lanes, nt, map, d_lane_stream, h->meta.as<FrameMeta>(), samples, h->states.as<StreamState>(), pcm,
-          d_pcm_i16 + shift * pcm_stride, pcm_stride, CC);
+          d_pcm_i16 + shift * pcm_stride, pcm_stride, CC, d_out_map, flg);
       h->prof_end(s);
       h->launches += 1;
     } else {
@@ -684,9 +707,11 @@ int bd_decode_grid_dev(bd_handle* h, const uint8_t* d_arena, const uint32_t* d_o
                             d_samples_out, d_final_range_out, n_lanes * n_ticks, (cudaStream_t)cuda_stream, nullptr, nullptr);
 }
 
-static int decode_host(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
-                       const uint8_t* flags, float* pcm_f32, int16_t* pcm_i16, uint32_t pcm_stride, int32_t* samples_out,
-                       uint32_t* final_range_out) {
+// out_map (host, 2 words per packet: PCM row, element offset in the row) and n_rows come from the multi-frame split
+// (mb_host_packets.h): the "packets" are then frames, several of which share one PCM row. Null: packet p owns row p.
+static int decode_host_impl(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
+                            const uint8_t* flags, float* pcm_f32, int16_t* pcm_i16, uint32_t pcm_stride, int32_t* samples_out,
+                            uint32_t* final_range_out, const uint32_t* out_map, uint32_t n_rows) {
   if (!h || !arena || !offsets || !stream_ids || !samples_out || !final_range_out || (!pcm_f32 && !pcm_i16)) return BD_ERR_BAD_ARG;
   if (n_packets == 0) return BD_OK;
   CK(cudaSetDevice(h->device));
@@ -698,7 +723,6 @@ static int decode_host(bd_handle* h, const uint8_t* arena, const uint32_t* offse
   h->epoch++;
   if (h->epoch == 0) { std::fill(h->h_epoch.begin(), h->h_epoch.end(), 0u); h->epoch = 1; }
   h->h_lane_stream.clear();
-  uint32_t n_ticks = 0;
   for (uint32_t p = 0; p < n_packets; p++) {
     uint32_t sid = stream_ids[p];
     if (sid >= S) return BD_ERR_BAD_ARG;
@@ -707,19 +731,34 @@ static int decode_host(bd_handle* h, const uint8_t* arena, const uint32_t* offse
       h->h_lane_of_stream[sid] = (uint32_t)h->h_lane_stream.size();
       h->h_lane_stream.push_back(sid);
     }
-    if (++h->h_count[sid] > n_ticks) n_ticks = h->h_count[sid];
   }
   const uint32_t n_lanes = (uint32_t)h->h_lane_stream.size();
-  bool identity = n_ticks == 1;  // every stream at most once: cell == packet
+  // tick = occurrence number of the stream in this call. The frames of one multi-frame packet must not straddle a
+  // pass boundary (k_clip_i16 soft-clips the packet as a whole): the group moves to the next pass, leaving empty cells.
+  uint32_t tpp = h->max_frames_per_pass / n_lanes;
+  if (tpp == 0) tpp = 1;
+  h->h_tick.resize(n_packets);
+  uint32_t n_ticks = 0;
+  for (uint32_t p = 0; p < n_packets; p++) {
+    const uint32_t sid = stream_ids[p];
+    uint32_t cur = h->h_count[sid];
+    if (out_map && !(flags[p] & mbh::VF_CONTINUATION)) {
+      uint32_t g = 1;
+      while (p + g < n_packets && (flags[p + g] & mbh::VF_CONTINUATION)) g++;
+      if (g > tpp) return BD_ERR_BAD_ARG;   // max_frames_per_pass too small for this many lanes
+      if (cur % tpp + g > tpp) cur = (cur / tpp + 1) * tpp;
+    }
+    h->h_tick[p] = cur;
+    h->h_count[sid] = cur + 1;
+    if (cur + 1 > n_ticks) n_ticks = cur + 1;
+  }
+  bool identity = n_ticks == 1 && !out_map;  // every stream at most once: cell == packet
   const uint32_t* d_map = nullptr;
   if (!identity) {
     h->h_pkt_map.assign((size_t)n_lanes * n_ticks, 0xffffffffu);
-    for (uint32_t sid : h->h_lane_stream) h->h_count[sid] = 0;
-    bool grid_order = (size_t)n_packets == (size_t)n_lanes * n_ticks;
+    bool grid_order = (size_t)n_packets == (size_t)n_lanes * n_ticks && !out_map;
     for (uint32_t p = 0; p < n_packets; p++) {
-      uint32_t sid = stream_ids[p];
-      uint32_t t = h->h_count[sid]++;
-      const size_t cell = (size_t)t * n_lanes + h->h_lane_of_stream[sid];
+      const size_t cell = (size_t)h->h_tick[p] * n_lanes + h->h_lane_of_stream[stream_ids[p]];
       h->h_pkt_map[cell] = p;
       grid_order = grid_order && cell == p;
     }
@@ -746,7 +785,13 @@ static int decode_host(bd_handle* h, const uint8_t* arena, const uint32_t* offse
   CK(h->d_flags.ensure(n_packets));
   CK(cudaMemcpyAsync(h->d_flags.p, flags, n_packets, cudaMemcpyHostToDevice, s));
   d_flags = h->d_flags.as<uint8_t>();
-  const size_t pcm_elems = (size_t)n_packets * pcm_stride;
+  const uint32_t* d_out_map = nullptr;
+  if (out_map) {
+    CK(h->d_out_map.ensure((size_t)n_packets * 8));
+    CK(cudaMemcpyAsync(h->d_out_map.p, out_map, (size_t)n_packets * 8, cudaMemcpyHostToDevice, s));
+    d_out_map = h->d_out_map.as<uint32_t>();
+  }
+  const size_t pcm_elems = (size_t)n_rows * pcm_stride;
   float* d_f32 = nullptr;
   int16_t* d_i16 = nullptr;
   if (pcm_f32) {
@@ -774,7 +819,7 @@ static int decode_host(bd_handle* h, const uint8_t* arena, const uint32_t* offse
   h->pass_out.elem = pcm_f32 ? sizeof(float) : sizeof(int16_t);
   int rc = decode_grid_device(h, h->d_arena.as<uint8_t>(), h->d_offsets.as<uint32_t>(), d_map, d_flags, n_lanes, n_ticks,
                               h->d_lane_stream.as<uint32_t>(), d_f32, d_i16, pcm_stride, h->d_samples.as<int32_t>(),
-                              h->d_range.as<uint32_t>(), n_packets, s, d_dbg_iy, d_dbg_x);
+                              h->d_range.as<uint32_t>(), n_rows, s, d_dbg_iy, d_dbg_x, d_out_map);
   h->pass_out.on = false;
   if (rc != BD_OK) { cudaStreamSynchronize(h->copy_stream); return rc; }
   if (!overlap_out) {
@@ -798,6 +843,27 @@ static int decode_host(bd_handle* h, const uint8_t* arena, const uint32_t* offse
       if (d_dbg_x) memcpy(h->dbg_x_host + (size_t)p * 2 * MAX_N, xs.data() + cidx * 2 * MAX_N, 2 * MAX_N * 4);
     }
   }
+  return BD_OK;
+}
+
+// Packets with more than one frame are cut into frames here (mb_host_packets.h); a call without any takes the
+// zero-copy path above.
+static int decode_host(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
+                       const uint8_t* flags, float* pcm_f32, int16_t* pcm_i16, uint32_t pcm_stride, int32_t* samples_out,
+                       uint32_t* final_range_out) {
+  if (!h || !arena || !offsets || !stream_ids || !samples_out || !final_range_out || (!pcm_f32 && !pcm_i16)) return BD_ERR_BAD_ARG;
+  if (n_packets == 0 || !mbh::needs_split(arena, offsets, n_packets))
+    return decode_host_impl(h, arena, offsets, stream_ids, n_packets, flags, pcm_f32, pcm_i16, pcm_stride, samples_out, final_range_out,
+                            nullptr, n_packets);
+  mbh::Split& S = h->split;
+  mbh::split_batch(arena, offsets, stream_ids, flags, n_packets, (int)(pcm_stride / (uint32_t)h->CC), h->CC, &S);
+  const uint32_t nv = (uint32_t)S.stream_ids.size();
+  h->v_samples.resize(nv);
+  h->v_range.resize(nv);
+  int rc = decode_host_impl(h, S.arena.data(), S.offsets.data(), S.stream_ids.data(), nv, S.flags.data(), pcm_f32, pcm_i16, pcm_stride,
+                            h->v_samples.data(), h->v_range.data(), S.out_map.data(), n_packets);
+  if (rc != BD_OK) return rc;
+  mbh::merge_results(S, n_packets, h->v_samples.data(), h->v_range.data(), samples_out, final_range_out);
   return BD_OK;
 }
 

@@ -60,9 +60,11 @@ enum { EN_STRIDE = 3 * 2 * NB_EBANDS };  // per-frame energy scratch: E, prev1 (
 // per-packet outputs) is pkt_map ? pkt_map[f] : f. Cells without a packet carry S_STATUS bit 15.
 MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, const uint32_t* pkt_map, const uint32_t* rec,
                              StreamState* st_all, const uint32_t* lane_stream, float* en, FrameMeta* meta, int32_t* samples_out,
-                             uint32_t* final_range_out, uint32_t quirks) {
+                             uint32_t* final_range_out, uint32_t quirks, const uint8_t* flags = nullptr) {
   StreamState& st = st_all[lane_stream ? lane_stream[lane] : lane];
   uint32_t sample_off = 0;
+  bool pkt_failed = false;   // an earlier frame of the same multi-frame packet failed: the reference returns there
+                             // (src/opus_decoder.rs:1339-1350), so the remaining frames must not touch the stream
   for (uint32_t t = 0; t < n_ticks; t++) {
     const uint32_t f = t * n_lanes + lane;
     const uint32_t* r = rec + rec_index(f, 0);
@@ -71,10 +73,13 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
     m.seed_in = st.rng; m.sample_off = sample_off; m.lane = lane; m.flags = 0;
     if (MB_ST_EMPTY(status)) { meta[f] = m; continue; }
     const uint32_t p = pkt_map ? pkt_map[f] : f;
-    if (!MB_ST_DECODED(status)) {  // rejected before the CELT decoder ran (unsupported mode, PLC, bad TOC)
+    const bool continuation = flags && (flags[p] & 4u);
+    if (!continuation) pkt_failed = false;
+    if (pkt_failed || !MB_ST_DECODED(status)) {  // rejected before the decoder ran (unsupported mode, PLC, bad TOC)
       meta[f] = m;
-      samples_out[p] = MB_ST_CODE(status);
+      samples_out[p] = pkt_failed ? MB_UNIMPLEMENTED : MB_ST_CODE(status);
       final_range_out[p] = st.range_final;
+      pkt_failed = true;
       continue;
     }
     uint32_t h0 = r[S_HDR0 * 32];
@@ -88,6 +93,7 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
       meta[f] = m;
       samples_out[p] = MB_UNIMPLEMENTED;
       final_range_out[p] = st.range_final;
+      pkt_failed = true;
       continue;
     }
     if (silk_only) {  // SILK-only packet: synthesis runs in k_silk (mb_silk_out.cuh); here only the front-end bookkeeping

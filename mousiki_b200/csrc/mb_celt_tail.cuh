@@ -33,6 +33,7 @@ struct TailParams {
   int apply_gain;
   float* pcm_f32;              // [packet][pcm_stride] interleaved, or null
   uint32_t pcm_stride;         // elements between packets
+  const uint32_t* out_map = nullptr;  // see pcm_elem_off
 };
 
 // ---------------------------------------------------------------- phase 2c(i): post-filter, one warp per stream-channel
@@ -173,7 +174,7 @@ MB_DEV void celt_deemph_lane(uint32_t lane, int c, const TailParams& P) {
     const int N = SHORT_MDCT << (int)MB_H0_LM(P.rec[rec_index(f, S_HDR0)]);
     const float* x = ser + m.sample_off;
     const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
-    float* out = P.pcm_f32 ? P.pcm_f32 + (size_t)p * P.pcm_stride + c : nullptr;
+    float* out = P.pcm_f32 ? P.pcm_f32 + pcm_elem_off(P.out_map, p, P.pcm_stride) + c : nullptr;
     if (m.flags & 4u) d.mem = 0.f;
     const bool accum = (m.flags & 8u) != 0;
     for (int j = 0; j < N; j++) {

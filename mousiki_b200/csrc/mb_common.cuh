@@ -70,6 +70,12 @@ enum {
   FOLD_WORDS = 608                 // hybrid fold buffer per stream: 2 channels x 8*(eband(20)-eband(17)) floats
 };
 
+// First PCM element of packet p: row p of the caller's buffer, or (calls cut into frames by mb_host_packets.h) row
+// out_map[2p] at element out_map[2p+1].
+MB_DEV size_t pcm_elem_off(const uint32_t* out_map, uint32_t p, uint32_t stride) {
+  return out_map ? (size_t)out_map[2 * p] * stride + out_map[2 * p + 1] : (size_t)p * stride;
+}
+
 // S_HDR0 fields
 #define MB_H0_LM(h) ((h) & 3u)
 #define MB_H0_C(h) ((((h) >> 2) & 1u) + 1u)

@@ -5,8 +5,9 @@
 //   opus_packet_parse_impl (code 0 framing)                              src/packet.rs:316-498
 //   decode_native_with / decode_frame argument and mode checks           src/opus_decoder.rs:453-600, 1139-1367
 // Frame kinds that are not built yet are reported per packet as BD_OPUS_UNIMPLEMENTED and leave the
-// stream state untouched: hybrid packets and SILK-only packets that carry a redundancy frame (row A16), packets with more than one frame
-// (codes 1-3, row F1), lost packets / FEC (row F2).
+// stream state untouched: packets that carry a redundancy frame (row F1), lost packets / FEC (row F2). Packets with more than
+// one frame (codes 1-3) arrive here already cut into code-0 frames by the host entry points (mb_host_packets.h); on the
+// device-resident grid entry point they are reported as BD_OPUS_UNIMPLEMENTED.
 #pragma once
 #include "mb_celt_parse.cuh"
 #include "mb_silk_parse.cuh"
@@ -17,6 +18,9 @@ namespace mb {
 MB_DEV void parse_cell(const uint8_t* arena, const uint32_t* offsets, uint32_t pkt, uint32_t* rec_base, int CC, uint32_t quirks,
                        int disable_inv, int cap_per_ch, const uint8_t* flags) {
   if (pkt == 0xffffffffu) { rec_base[S_STATUS * 32] = 1u << 15; return; }
+  // bits 4..7 of the flags: the host front end already rejected the packet (mb_host_packets.h: invalid framing,
+  // row too small for all its frames); the cell only exists to report the code with the stream's final_range
+  if (flags && (flags[pkt] >> 4)) { rec_base[S_STATUS * 32] = (uint32_t)(uint8_t)(int8_t)(-(int)(flags[pkt] >> 4)); return; }
   const uint32_t off = offsets[pkt];
   const int len = (int)(offsets[pkt + 1] - off);
   if (len == 0 && !flags) { rec_base[S_STATUS * 32] = 1u << 15; return; }

@@ -9,6 +9,7 @@
 
 #include <vector>
 
+#include "../../mousiki_b200/csrc/mb_host_packets.h"
 #include "../../mousiki_b200/csrc/mb_celt_imdct.cuh"
 #include "../../mousiki_b200/csrc/mb_celt_tail.cuh"
 #include "../../mousiki_b200/csrc/mb_frame.cuh"
@@ -111,6 +112,29 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
       }
   }
   return 0;
+}
+
+// ---- the host front end for multi-frame packets (mb_host_packets.h), exposed for the CPU tests
+static mbh::Split g_split;
+
+// Cuts the batch into frames; returns the number of virtual packets, *arena_bytes = size of the virtual arena.
+uint32_t emu_split_batch(const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, const uint8_t* flags, uint32_t n_packets,
+                         int cap_per_ch, int CC, uint32_t* arena_bytes) {
+  mbh::split_batch(arena, offsets, stream_ids, flags, n_packets, cap_per_ch, CC, &g_split);
+  *arena_bytes = (uint32_t)g_split.arena.size();
+  return (uint32_t)g_split.stream_ids.size();
+}
+// Copies the result of the last emu_split_batch out: offsets[nv+1], stream_ids[nv], flags[nv], out_map[2*nv], first[n_packets+1].
+void emu_split_fetch(uint8_t* arena, uint32_t* offsets, uint32_t* stream_ids, uint8_t* flags, uint32_t* out_map, uint32_t* first) {
+  memcpy(arena, g_split.arena.data(), g_split.arena.size());
+  memcpy(offsets, g_split.offsets.data(), g_split.offsets.size() * 4);
+  memcpy(stream_ids, g_split.stream_ids.data(), g_split.stream_ids.size() * 4);
+  memcpy(flags, g_split.flags.data(), g_split.flags.size());
+  memcpy(out_map, g_split.out_map.data(), g_split.out_map.size() * 4);
+  memcpy(first, g_split.first.data(), g_split.first.size() * 4);
+}
+void emu_merge_results(uint32_t n_packets, const int32_t* v_samples, const uint32_t* v_range, int32_t* samples_out, uint32_t* final_range_out) {
+  mbh::merge_results(g_split, n_packets, v_samples, v_range, samples_out, final_range_out);
 }
 
 }  // extern "C"

@@ -144,3 +144,58 @@ def silk_fuzz_grid(n_lanes: int, n_ticks: int, payload, toc_fn, seed: int = 1, c
     offsets = np.zeros(need + 1, dtype=np.uint32)
     offsets[1:] = np.cumsum([len(p) for p in pkts])
     return np.concatenate(pkts), offsets
+
+
+# ---------------------------------------------------------------------------------------------- multi-frame packets
+def _frame_len_bytes(n: int) -> bytes:
+    """RFC 6716 section 3.2.1 frame length coding."""
+    if n < 252:
+        return bytes([n])
+    return bytes([252 + (n & 3), (n - (252 + (n & 3))) // 4])
+
+
+def multiframe_packet(toc: int, frames, code: int, vbr: bool = False, pad: int = 0) -> np.ndarray:
+    """Packs `frames` (byte strings) behind a TOC with frame-count code 1, 2 or 3 (RFC 6716 section 3.2). code 1 needs two
+    equal-sized frames, code 2 two frames, code 3 any count (CBR unless vbr), optionally with `pad` bytes of padding (plus its length bytes)."""
+    toc = (toc & ~3) | code
+    frames = [bytes(f) for f in frames]
+    if code == 1:
+        assert len(frames) == 2 and len(frames[0]) == len(frames[1])
+        body = frames[0] + frames[1]
+    elif code == 2:
+        assert len(frames) == 2
+        body = _frame_len_bytes(len(frames[0])) + frames[0] + frames[1]
+    else:
+        fc = len(frames) | (0x80 if vbr else 0) | (0x40 if pad else 0)
+        body = bytes([fc])
+        padding = b""
+        if pad:  # `pad` padding bytes: each 255 length byte stands for 254 of them and announces another length byte
+            body += bytes([255] * (pad // 254)) + bytes([pad % 254])
+            padding = bytes(pad)
+        if vbr:
+            for f in frames[:-1]:
+                body += _frame_len_bytes(len(f))
+        else:
+            assert len({len(f) for f in frames}) == 1
+        body += b"".join(frames) + padding
+    return np.frombuffer(bytes([toc]) + body, dtype=np.uint8).copy()
+
+
+def split_batch(arena, offsets, stream_ids, cap_per_ch, channels, flags=None):
+    """The product's host front end (mousiki_b200/csrc/mb_host_packets.h) through the emulation library."""
+    lib = emul_lib()
+    lib.emu_split_batch.restype = C.c_uint32
+    n = len(offsets) - 1
+    arena = np.ascontiguousarray(arena, dtype=np.uint8)
+    offsets = np.ascontiguousarray(offsets, dtype=np.uint32)
+    stream_ids = np.ascontiguousarray(stream_ids, dtype=np.uint32)
+    nbytes = C.c_uint32(0)
+    nv = lib.emu_split_batch(ptr(arena), ptr(offsets), ptr(stream_ids), ptr(flags) if flags is not None else None, n, int(cap_per_ch),
+                             int(channels), C.byref(nbytes))
+    out = {"arena": np.zeros(max(nbytes.value, 1), dtype=np.uint8), "offsets": np.zeros(nv + 1, dtype=np.uint32),
+           "stream_ids": np.zeros(nv, dtype=np.uint32), "flags": np.zeros(nv, dtype=np.uint8), "out_map": np.zeros(2 * nv, dtype=np.uint32),
+           "first": np.zeros(n + 1, dtype=np.uint32)}
+    lib.emu_split_fetch(ptr(out["arena"]), ptr(out["offsets"]), ptr(out["stream_ids"]), ptr(out["flags"]), ptr(out["out_map"]),
+                        ptr(out["first"]))
+    out["arena"] = out["arena"][:nbytes.value]
+    return out
