@@ -70,7 +70,10 @@ const char* bd_last_error(const bd_handle* h);
  * BD_OPUS_UNIMPLEMENTED until built); flags may be NULL. pcm receives packet p's interleaved samples at
  * pcm + p * pcm_stride (pcm_stride elements >= frame_size * channels; the per-channel capacity
  * pcm_stride / channels plays the role of `frame_size`). samples_out[p] = samples per channel (>= 0) or an
- * Opus error code; final_range_out[p] = Decoder::final_range() after that packet. Returns BD_OK or an API error. */
+ * Opus error code; final_range_out[p] = Decoder::final_range() after that packet. Returns BD_OK or an API error.
+ * Packets with several frames (TOC codes 1-3, padding: opus_packet_parse_impl, src/packet.rs:316-498) are cut into
+ * frames on the host; the frames of a packet run in consecutive ticks of the stream and fill the packet's row in
+ * order; a frame that fails ends the packet with its code, as the frame loop of src/opus_decoder.rs:1339-1350 does. */
 int bd_decode_f32(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
                   const uint8_t* flags, float* pcm, uint32_t pcm_stride, int32_t* samples_out, uint32_t* final_range_out);
 /* Decoder::decode / opus_decode (i16: soft clip + round; src/codec.rs:843-859, src/opus_decoder.rs:1632-1715). */
@@ -81,7 +84,9 @@ int bd_decode_i16(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, c
  * Regular grid: packet (t, j) = index t * n_lanes + j belongs to stream lane_stream[j] (NULL: stream j);
  * a zero-length packet marks "nothing for this lane at this tick". All pointers are DEVICE pointers;
  * cuda_stream is a cudaStream_t (NULL = default stream). The call returns after enqueueing; results are
- * valid once the stream is synchronised. d_pcm_f32 or d_pcm_i16 may be NULL (but not both non-NULL). */
+ * valid once the stream is synchronised. d_pcm_f32 or d_pcm_i16 may be NULL (but not both non-NULL).
+ * Every packet must hold ONE frame (TOC code 0) here: the host is not allowed to look at the bytes, so a packet with
+ * codes 1-3 comes back as BD_OPUS_UNIMPLEMENTED; cut such packets into frames before uploading them. */
 int bd_decode_grid_dev(bd_handle* h, const uint8_t* d_arena, const uint32_t* d_offsets, uint32_t n_lanes, uint32_t n_ticks,
                        const uint32_t* d_lane_stream, float* d_pcm_f32, int16_t* d_pcm_i16, uint32_t pcm_stride,
                        int32_t* d_samples_out, uint32_t* d_final_range_out, void* cuda_stream);

@@ -162,12 +162,12 @@ def test_gpu_cres_known_answer():
 
 
 def test_gpu_unsupported_packets_report_per_packet_codes():
-    """Redundancy-carrying / multi-frame / lost packets are reported per packet and never poison the batch."""
+    """Redundancy-carrying / concealment packets are reported per packet and never poison the batch."""
     from mousiki_b200 import BatchDecoder, pack_packets
 
     good = bytes([helpers.celt_toc(3, True)]) + bytes(helpers.lcg_bytes(1, 100))
     silk = bytes([helpers.silk_toc(2, 1, False)]) + bytes(300)  # SILK WB 20 ms, spare bits: carries a CELT redundancy frame
-    code1 = bytes([helpers.celt_toc(2, False) | 1]) + bytes(helpers.lcg_bytes(3, 40))
+    code1 = bytes([helpers.celt_toc(2, False), 0x55])  # one payload byte: a concealment frame (src/opus_decoder.rs:491)
     arena, offsets = pack_packets([good, silk, code1, good])
     with BatchDecoder(4, 48000, 2) as dec:
         pcm, samples, rng = dec.decode_float(arena, offsets, np.arange(4, dtype=np.uint32), 960)
