@@ -23,8 +23,19 @@ FRAME = 960
 POOL = 2048
 
 
+KINDS = {
+    # BASELINE config 3: SILK-only WB mono 20 ms @ ~16 kb/s
+    "silk": {"toc": helpers.silk_toc(2, 1, False), "payload": (8, 40), "ch": 1, "streams": 100_000,
+             "workload": "silk_only_wb_mono_20ms_1e5_streams"},
+    # BASELINE config 4: hybrid FB stereo 20 ms @ ~32 kb/s (SILK WB mid/side + CELT bands 17..20)
+    "hybrid": {"toc": ((15 << 3) | 4), "payload": (60, 100), "ch": 2, "streams": 20_000,
+               "workload": "hybrid_fb_stereo_20ms_2e4_streams"},
+}
+KIND = KINDS["silk"]
+
+
 def corpus(streams, ticks, seed):
-    pa, po = helpers.silk_fuzz_grid(POOL, 1, (8, 40), lambda k, r: helpers.silk_toc(2, 1, False), seed=seed, channels=1)
+    pa, po = helpers.silk_fuzz_grid(POOL, 1, KIND["payload"], lambda k, r: KIND["toc"], seed=seed, channels=KIND["ch"])
     lens = np.diff(po.astype(np.int64))
     rng = np.random.default_rng(seed + 1)
     pick = rng.integers(0, POOL, size=streams * ticks)
@@ -47,17 +58,21 @@ def main():
     from mousiki_b200 import BatchDecoder
 
     ap = argparse.ArgumentParser()
-    ap.add_argument("--streams", type=int, default=100_000)
+    ap.add_argument("--kind", choices=sorted(KINDS), default="silk")
+    ap.add_argument("--streams", type=int, default=0)
     ap.add_argument("--ticks", type=int, default=10)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(0)
-    streams, ticks = args.streams, args.ticks
+    global KIND
+    KIND = KINDS[args.kind]
+    CH = KIND["ch"]
+    streams, ticks = args.streams or KIND["streams"], args.ticks
     n = streams * ticks
     arena, offsets = corpus(streams, ticks, 5)
-    dec = BatchDecoder(streams, 48000, 1, device=0)
+    dec = BatchDecoder(streams, 48000, CH, device=0)
     # parity gate: first 64 streams
     cs = 64
     sel = (np.arange(ticks)[:, None] * streams + np.arange(cs)[None, :]).reshape(-1)
@@ -67,19 +82,20 @@ def main():
     sa = np.concatenate([arena[offsets[p]:offsets[p + 1]] for p in sel])
     ids = np.tile(np.arange(cs, dtype=np.uint32), ticks)
     pcm, samples, rng = dec.decode(sa, so, ids, FRAME)
-    rp, rs, rr = helpers.oracle_decode_grid(sa, so, cs, ticks, 1, FRAME, i16=True)
+    rp, rs, rr = helpers.oracle_decode_grid(sa, so, cs, ticks, CH, FRAME, i16=True)
     parity = {"packets_checked": int(len(sel)), "final_range_mismatches": int((rng != rr).sum()),
-              "sample_count_mismatches": int((samples != rs).sum()), "pcm_i16_mismatches": int((pcm != rp).sum())}
+              "sample_count_mismatches": int((samples != rs).sum()), "pcm_i16_mismatches": int((pcm != rp).sum()),
+              "pcm_i16_max_abs_diff": int(np.abs(pcm.astype(np.int32) - rp.astype(np.int32)).max())}
     dec.reset()
     d_arena = torch.from_numpy(arena).to(dev)
     d_offsets = torch.from_numpy(offsets.view(np.int32)).to(dev)
-    d_pcm = torch.empty((n, FRAME), dtype=torch.float32, device=dev)
+    d_pcm = torch.empty((n, FRAME * CH), dtype=torch.float32, device=dev)
     d_samples = torch.zeros(n, dtype=torch.int32, device=dev)
     d_range = torch.zeros(n, dtype=torch.int32, device=dev)
     stream = torch.cuda.current_stream()
 
     def step():
-        dec.decode_grid_device(d_arena.data_ptr(), d_offsets.data_ptr(), streams, ticks, d_pcm.data_ptr(), FRAME, d_samples.data_ptr(),
+        dec.decode_grid_device(d_arena.data_ptr(), d_offsets.data_ptr(), streams, ticks, d_pcm.data_ptr(), FRAME * CH, d_samples.data_ptr(),
                                d_range.data_ptr(), stream=stream.cuda_stream)
 
     for _ in range(args.warmup):
@@ -101,13 +117,13 @@ def main():
     cst = 256 * cores
     ca, co = corpus(cst, ticks, 9)
     lib = helpers.oracle_lib()
-    cp = np.zeros((cst * ticks, FRAME), dtype=np.int16)
+    cp = np.zeros((cst * ticks, FRAME * CH), dtype=np.int16)
     csm = np.zeros(cst * ticks, dtype=np.int32)
     crg = np.zeros(cst * ticks, dtype=np.uint32)
     tot, passes = 0.0, 0
     while tot < 8.0:
         t0 = time.perf_counter()
-        lib.orc_decode_grid(48000, 1, helpers.QUIRKS_MOUSIKI, helpers.ptr(ca), helpers.ptr(co), cst, ticks, FRAME, None, helpers.ptr(cp),
+        lib.orc_decode_grid(48000, CH, helpers.QUIRKS_MOUSIKI, helpers.ptr(ca), helpers.ptr(co), cst, ticks, FRAME, None, helpers.ptr(cp),
                             helpers.ptr(csm), helpers.ptr(crg), cores)
         tot += time.perf_counter() - t0
         passes += 1
@@ -116,6 +132,8 @@ def main():
     # algorithmic bytes per 20 ms WB mono frame: packet ~27 B + record (9 + 160 words) written and read + state 2 x 1.1 KB
     # read and written once per pass (amortised over `ticks`) + PCM out 960 x 4 B
     alg = 27 + 2 * 169 * 4 + 2 * 2 * 1100 / ticks + 960 * 4
+    if args.kind == "hybrid":  # stereo SILK record + state, and the f32 stereo row is written by k_silk then re-read and re-written by k_deemph
+        alg = 80 + 2 * (3 + 2 * 169) * 4 + 2 * 2 * 2200 / ticks + 960 * 2 * 4
     peak = 6535.4
     try:
         peak = float(json.loads((ROOT / "MEASURED_PEAKS.json").read_text())["hbm_gbs"])
@@ -123,8 +141,8 @@ def main():
         pass
     silk_ms = kms.get("k_silk", 0.0)
     line = {"metric": "decoded_audio_seconds_per_second", "value": audio_s * args.steps / (ms * 1e-3), "unit": "audio-s/s", "n_gpus": 1,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "dtype": "int32",
-            "config": {"workload": "silk_only_wb_mono_20ms_1e5_streams", "streams": streams, "frames_per_stream_per_step": ticks,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "dtype": "int32" if args.kind == "silk" else "int32+f32",
+            "config": {"workload": KIND["workload"], "streams": streams, "frames_per_stream_per_step": ticks,
                        "mean_payload_bytes": float(lens.mean()), "output": "f32 PCM left in HBM"},
             "kernel_ms_per_step": kms,
             "roofline": {"bound": "hbm", "kernel": "k_silk", "alg_bytes_per_frame": alg, "achieved": alg * n / (silk_ms * 1e-3) / 1e9 if silk_ms else None,
