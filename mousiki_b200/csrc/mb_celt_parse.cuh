@@ -166,7 +166,7 @@ MB_DEV void parse_theta(ParseCtx& cx, Theta& s, int n, int& b, int B, int B0, in
 // One quant_band call (mono path; src/celt/bands.rs:2133-2291 + quant_partition :1917-2131),
 // integer side only. The split tree is walked with an explicit stack (depth <= LM+2) so that the
 // lanes of a warp keep iterating one common loop instead of diverging through recursion.
-MB_DEV void parse_band(ParseCtx& cx, int x_off, int n, int b, int B, int lm, float gain, int tf_change) {
+MB_DEV_NOINLINE void parse_band(ParseCtx& cx, int x_off, int n, int b, int B, int lm, float gain, int tf_change) {
   if (n == 1) {  // quant_band_n1 (bands.rs:642-704), mono call
     uint32_t sign = 0;
     if (cx.remaining_bits >= 1 << BITRES) { sign = cx.dec.raw_bits(1); cx.remaining_bits -= 1 << BITRES; }
@@ -251,7 +251,7 @@ MB_DEV void parse_band(ParseCtx& cx, int x_off, int n, int b, int B, int lm, flo
 }
 
 // quant_band_stereo, integer side (src/celt/bands.rs:2294-2514)
-MB_DEV void parse_band_stereo(ParseCtx& cx, int x_off, int y_off, int n, int b, int B, int lm, int tf_change) {
+MB_DEV_NOINLINE void parse_band_stereo(ParseCtx& cx, int x_off, int y_off, int n, int b, int B, int lm, int tf_change) {
   if (n == 1) {
     uint32_t signs = 0;
     for (int c = 0; c < 2; c++)

@@ -72,6 +72,10 @@ MB_DEV void silk_side_load(SilkSide& s, const uint32_t* w /*stride 32*/) {
   s.interp_q2 = (int8_t)a; s.seed = (int8_t)(a >> 8); s.cond = (int8_t)(a >> 16); s.coded = (int8_t)(a >> 24);
 }
 
+// Every SILK symbol is an 8-bit inverse-CDF read: one out-of-line copy keeps the parse small enough for the
+// instruction cache (inlined at ~60 sites the payload parser alone was 330 KB of SASS).
+MB_DEV_NOINLINE int silk_icdf(RangeDec& ec, const uint8_t* tab, unsigned ftb) { return ec.icdf(tab, ftb); }
+
 // per-rate constants (decoder_set_fs.rs:137-198): everything the entropy side needs from the sampling rate
 struct SilkRate {
   int fs_khz, nb_subfr, frame_length, order;
@@ -92,35 +96,35 @@ MB_DEV SilkRate silk_rate(int fs_khz, int nb_subfr) {
 }
 
 // decode_indices.rs:109-269. prev_type / prev_lag: the ec_prev_* pair of this channel (packet-local, see header).
-MB_DEV void silk_parse_indices(RangeDec& ec, const SilkRate& R, int vad, int lbrr, int cond, int& prev_type, int& prev_lag, SilkSide& s) {
-  const int raw = (lbrr || vad) ? ec.icdf(silk_type_offset_VAD_iCDF, 8) + 2 : ec.icdf(silk_type_offset_no_VAD_iCDF, 8);
+MB_DEV_NOINLINE void silk_parse_indices(RangeDec& ec, const SilkRate& R, int vad, int lbrr, int cond, int& prev_type, int& prev_lag, SilkSide& s) {
+  const int raw = (lbrr || vad) ? silk_icdf(ec, silk_type_offset_VAD_iCDF, 8) + 2 : silk_icdf(ec, silk_type_offset_no_VAD_iCDF, 8);
   s.signal_type = (int8_t)(raw >> 1);
   s.quant_offset = (int8_t)(raw & 1);
-  if (cond == SILK_COND_COND) s.gains[0] = (int8_t)ec.icdf(silk_delta_gain_iCDF, 8);
+  if (cond == SILK_COND_COND) s.gains[0] = (int8_t)silk_icdf(ec, silk_delta_gain_iCDF, 8);
   else {
-    const int msb = ec.icdf(silk_gain_iCDF + 8 * s.signal_type, 8);
-    s.gains[0] = (int8_t)((msb << 3) | ec.icdf(silk_uniform8_iCDF, 8));
+    const int msb = silk_icdf(ec, silk_gain_iCDF + 8 * s.signal_type, 8);
+    s.gains[0] = (int8_t)((msb << 3) | silk_icdf(ec, silk_uniform8_iCDF, 8));
   }
-  for (int k = 1; k < 4; k++) s.gains[k] = k < R.nb_subfr ? (int8_t)ec.icdf(silk_delta_gain_iCDF, 8) : 0;
-  const int cb1 = ec.icdf(R.cb1_icdf + (s.signal_type >> 1) * 32, 8);
+  for (int k = 1; k < 4; k++) s.gains[k] = k < R.nb_subfr ? (int8_t)silk_icdf(ec, silk_delta_gain_iCDF, 8) : 0;
+  const int cb1 = silk_icdf(ec, R.cb1_icdf + (s.signal_type >> 1) * 32, 8);
   s.nlsf[0] = (int8_t)cb1;
   const uint8_t* sel = R.ec_sel + cb1 * (R.order >> 1);
   for (int i = 0; i < 16; i++) {
     if (i >= R.order) { s.nlsf[i + 1] = 0; continue; }
     const uint32_t e = sel[i >> 1];
     const int ix = (int)((i & 1) ? ((e >> 5) & 7u) : ((e >> 1) & 7u)) * 9;   // nlsf_unpack.rs:30-47 (entropy table select)
-    int v = ec.icdf(R.ec_icdf + ix, 8);
-    if (v == 0) v -= ec.icdf(silk_NLSF_EXT_iCDF, 8);
-    else if (v == 8) v += ec.icdf(silk_NLSF_EXT_iCDF, 8);
+    int v = silk_icdf(ec, R.ec_icdf + ix, 8);
+    if (v == 0) v -= silk_icdf(ec, silk_NLSF_EXT_iCDF, 8);
+    else if (v == 8) v += silk_icdf(ec, silk_NLSF_EXT_iCDF, 8);
     s.nlsf[i + 1] = (int8_t)(v - 4);
   }
-  s.interp_q2 = R.nb_subfr == 4 ? (int8_t)ec.icdf(silk_NLSF_interpolation_factor_iCDF, 8) : 4;
+  s.interp_q2 = R.nb_subfr == 4 ? (int8_t)silk_icdf(ec, silk_NLSF_interpolation_factor_iCDF, 8) : 4;
   s.lag_index = 0; s.contour = 0; s.per_index = 0; s.ltp_scale = 0;
   s.ltp[0] = s.ltp[1] = s.ltp[2] = s.ltp[3] = 0;
   if (s.signal_type == SILK_T_VOICED) {
     bool absolute = true;
     if (cond == SILK_COND_COND && prev_type == SILK_T_VOICED) {
-      const int delta = ec.icdf(silk_pitch_delta_iCDF, 8);
+      const int delta = silk_icdf(ec, silk_pitch_delta_iCDF, 8);
       if (delta > 0) {
         int v = prev_lag + delta - 9;
         s.lag_index = (int16_t)(v > 32767 ? 32767 : (v < -32768 ? -32768 : v));
@@ -128,35 +132,35 @@ MB_DEV void silk_parse_indices(RangeDec& ec, const SilkRate& R, int vad, int lbr
       }
     }
     if (absolute) {
-      const int hi = ec.icdf(silk_pitch_lag_iCDF, 8);
-      s.lag_index = (int16_t)(hi * (R.fs_khz >> 1) + ec.icdf(R.lag_low_icdf, 8));
+      const int hi = silk_icdf(ec, silk_pitch_lag_iCDF, 8);
+      s.lag_index = (int16_t)(hi * (R.fs_khz >> 1) + silk_icdf(ec, R.lag_low_icdf, 8));
     }
     prev_lag = s.lag_index;
-    s.contour = (int8_t)ec.icdf(R.contour_icdf, 8);
-    s.per_index = (int8_t)ec.icdf(silk_LTP_per_index_iCDF, 8);
+    s.contour = (int8_t)silk_icdf(ec, R.contour_icdf, 8);
+    s.per_index = (int8_t)silk_icdf(ec, silk_LTP_per_index_iCDF, 8);
     const uint8_t* g = s.per_index == 0 ? silk_LTP_gain_iCDF_0 : (s.per_index == 1 ? silk_LTP_gain_iCDF_1 : silk_LTP_gain_iCDF_2);
-    for (int k = 0; k < R.nb_subfr; k++) s.ltp[k] = (int8_t)ec.icdf(g, 8);
-    s.ltp_scale = cond == SILK_COND_INDEP ? (int8_t)ec.icdf(silk_LTPscale_iCDF, 8) : 0;
+    for (int k = 0; k < R.nb_subfr; k++) s.ltp[k] = (int8_t)silk_icdf(ec, g, 8);
+    s.ltp_scale = cond == SILK_COND_INDEP ? (int8_t)silk_icdf(ec, silk_LTPscale_iCDF, 8) : 0;
   }
-  s.seed = (int8_t)ec.icdf(silk_uniform4_iCDF, 8);
+  s.seed = (int8_t)silk_icdf(ec, silk_uniform4_iCDF, 8);
   prev_type = s.signal_type;
 }
 
 // one binary split of the shell code (shell_coder.rs:36-45)
 MB_DEV void silk_split(RangeDec& ec, int total, const uint8_t* table, int& a, int& b) {
-  if (total > 0) { a = ec.icdf(table + silk_shell_code_table_offsets[total], 8); b = total - a; }
+  if (total > 0) { a = silk_icdf(ec, table + silk_shell_code_table_offsets[total], 8); b = total - a; }
   else { a = 0; b = 0; }
 }
 
 // decode_pulses.rs:50-158 + code_signs.rs:93-125. q: frame_length rounded up to 16 entries.
 MB_DEV_NOINLINE void silk_parse_pulses(RangeDec& ec, int16_t* q, int signal_type, int quant_offset, int frame_length, uint32_t quirks) {
-  const int rate = ec.icdf(silk_rate_levels_iCDF + 9 * (signal_type >> 1), 8);
+  const int rate = silk_icdf(ec, silk_rate_levels_iCDF + 9 * (signal_type >> 1), 8);
   const int nblocks = (frame_length + 15) >> 4;
   uint8_t sum[20], nls[20];
   for (int i = 0; i < nblocks; i++) {
     int n = 0;
-    int v = ec.icdf(silk_pulses_per_block_iCDF + 18 * rate, 8);
-    while (v == 17) { n++; v = ec.icdf(silk_pulses_per_block_iCDF + 18 * 9 + (n == 10), 8); }
+    int v = silk_icdf(ec, silk_pulses_per_block_iCDF + 18 * rate, 8);
+    while (v == 17) { n++; v = silk_icdf(ec, silk_pulses_per_block_iCDF + 18 * 9 + (n == 10), 8); }
     sum[i] = (uint8_t)v; nls[i] = (uint8_t)n;
   }
   for (int i = 0; i < nblocks; i++) {
@@ -180,7 +184,7 @@ MB_DEV_NOINLINE void silk_parse_pulses(RangeDec& ec, int16_t* q, int signal_type
     if (nls[i] == 0) continue;
     for (int k = 0; k < 16; k++) {
       int v = q[16 * i + k];
-      for (int j = 0; j < nls[i]; j++) v = (v << 1) + ec.icdf(silk_lsb_iCDF, 8);
+      for (int j = 0; j < nls[i]; j++) v = (v << 1) + silk_icdf(ec, silk_lsb_iCDF, 8);
       q[16 * i + k] = (int16_t)v;
     }
   }
@@ -205,11 +209,11 @@ MB_DEV_NOINLINE void silk_parse_pulses(RangeDec& ec, int16_t* q, int signal_type
 }
 
 // stereo_decode_pred.rs:21-56
-MB_DEV void silk_parse_stereo_pred(RangeDec& ec, int32_t pred_q13[2]) {
+MB_DEV_NOINLINE void silk_parse_stereo_pred(RangeDec& ec, int32_t pred_q13[2]) {
   int ix[2][3];
-  const int n = ec.icdf(silk_stereo_pred_joint_iCDF, 8);
+  const int n = silk_icdf(ec, silk_stereo_pred_joint_iCDF, 8);
   ix[0][2] = n / 5; ix[1][2] = n - 5 * ix[0][2];
-  for (int c = 0; c < 2; c++) { ix[c][0] = ec.icdf(silk_uniform3_iCDF, 8); ix[c][1] = ec.icdf(silk_uniform5_iCDF, 8); }
+  for (int c = 0; c < 2; c++) { ix[c][0] = silk_icdf(ec, silk_uniform3_iCDF, 8); ix[c][1] = silk_icdf(ec, silk_uniform5_iCDF, 8); }
   for (int c = 0; c < 2; c++) {
     const int k = ix[c][0] + 3 * ix[c][2];
     const int32_t low = silk_stereo_pred_quant_Q13[k];
@@ -238,7 +242,7 @@ MB_DEV_NOINLINE void silk_parse_payload(RangeDec& ec, int fs_khz, int nb_subfr, 
     if (flag) {
       if (n_frames == 1) lbrr_flags[n][0] = 1;
       else {
-        const int sym = ec.icdf(n_frames == 2 ? silk_LBRR_flags_2_iCDF : silk_LBRR_flags_3_iCDF, 8) + 1;
+        const int sym = silk_icdf(ec, n_frames == 2 ? silk_LBRR_flags_2_iCDF : silk_LBRR_flags_3_iCDF, 8) + 1;
         for (int i = 0; i < n_frames; i++) lbrr_flags[n][i] = (sym >> i) & 1;
       }
     }
@@ -253,7 +257,7 @@ MB_DEV_NOINLINE void silk_parse_payload(RangeDec& ec, int fs_khz, int nb_subfr, 
       if (nci == 2 && n == 0) {
         int32_t skip[2];
         silk_parse_stereo_pred(ec, skip);
-        if (!lbrr_flags[1][i]) decode_only_middle = ec.icdf(silk_stereo_only_code_mid_iCDF, 8);
+        if (!lbrr_flags[1][i]) decode_only_middle = silk_icdf(ec, silk_stereo_only_code_mid_iCDF, 8);
       }
       const int cond = (i > 0 && lbrr_flags[n][i - 1]) ? SILK_COND_COND : SILK_COND_INDEP;
       silk_parse_indices(ec, R, 0, 1, cond, prev_type[n], prev_lag[n], side);
@@ -267,7 +271,7 @@ MB_DEV_NOINLINE void silk_parse_payload(RangeDec& ec, int fs_khz, int nb_subfr, 
     int32_t pred[2] = {0, 0};
     if (nci == 2) {
       silk_parse_stereo_pred(ec, pred);
-      decode_only_middle = vad[1][i] == 0 ? ec.icdf(silk_stereo_only_code_mid_iCDF, 8) : 0;
+      decode_only_middle = vad[1][i] == 0 ? silk_icdf(ec, silk_stereo_only_code_mid_iCDF, 8) : 0;
     } else decode_only_middle = 0;
     fr[0] = (uint32_t)pred[0]; fr[32] = (uint32_t)pred[1]; fr[64] = (uint32_t)decode_only_middle;
     for (int n = 0; n < nci; n++) {
