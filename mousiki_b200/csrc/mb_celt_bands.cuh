@@ -19,11 +19,12 @@ MB_TBL float kEMeans[25] = {6.4375f, 6.25f, 5.75f, 5.3125f, 5.0625f, 4.8125f, 4.
 MB_TBL uint8_t kOrdery[30] = {1, 0, 3, 0, 2, 1, 7, 0, 4, 3, 6, 1, 5, 2, 15, 0, 8, 7, 12, 3, 11, 4, 14, 1, 9, 6, 13, 2, 10, 5};
 
 // Shared-memory working set of one frame: 9.4 KB.
+enum { NORM_MAX = 624 };       // 8 * eband(20): the longest fold buffer (bands.rs:2614-2617)
 struct BandsSmem {
-  float win[2 * WIN_Y];        // x | y of the current band
+  float win2[2][2 * WIN_Y];    // x | y of the current band, and of the next one on its way in (cp.async)
   float scratch[176];          // transformed copy of the fold source
   float tmp[176];              // permutation scratch
-  float norm[2 * 800];         // fold buffers (norm | norm2), bands.rs:2614-2617
+  float norm[2 * NORM_MAX];    // fold buffers (norm | norm2)
   float gains[2 * NB_EBANDS];
   float red[4];
 };
@@ -62,8 +63,9 @@ MB_DEV void team_haar1(Team tm, float* x, int n0, int stride) {
   const int half = n0 / 2;
   const float scale = 0.70710678f;
   const int total = stride * half;
+  const int sl = ilog2_exact(stride);   // stride is a power of two; the butterflies are independent, any order will do
   for (int idx = tm.tid; idx < total; idx += tm.n) {
-    int i = idx / half, j = idx - i * half;
+    int i = idx & (stride - 1), j = idx >> sl;
     int i0 = stride * 2 * j + i, i1 = i0 + stride;
     float t1 = scale * x[i0], t2 = scale * x[i1];
     x[i0] = t1 + t2;
@@ -75,10 +77,11 @@ MB_DEV const uint8_t* ordery_for(int stride) { return kOrdery + (stride == 2 ? 0
 MB_DEV void team_deinterleave(Team tm, float* x, float* tmp, int n0, int stride, int hadamard) {
   const int n = n0 * stride;
   const uint8_t* ord = ordery_for(stride);
+  const int sl = ilog2_exact(stride);
   for (int idx = tm.tid; idx < n; idx += tm.n) {
-    int i = idx / n0, j = idx - i * n0;
+    int i = idx & (stride - 1), j = idx >> sl;
     int dst = (hadamard ? (int)ord[i] : i) * n0 + j;
-    tmp[dst] = x[j * stride + i];
+    tmp[dst] = x[idx];
   }
   MB_SYNC();
   for (int idx = tm.tid; idx < n; idx += tm.n) x[idx] = tmp[idx];
@@ -87,10 +90,11 @@ MB_DEV void team_deinterleave(Team tm, float* x, float* tmp, int n0, int stride,
 MB_DEV void team_interleave(Team tm, float* x, float* tmp, int n0, int stride, int hadamard) {
   const int n = n0 * stride;
   const uint8_t* ord = ordery_for(stride);
+  const int sl = ilog2_exact(stride);
   for (int idx = tm.tid; idx < n; idx += tm.n) {
-    int i = idx / n0, j = idx - i * n0;
+    int i = idx & (stride - 1), j = idx >> sl;
     int src = (hadamard ? (int)ord[i] : i) * n0 + j;
-    tmp[j * stride + i] = x[src];
+    tmp[idx] = x[src];
   }
   MB_SYNC();
   for (int idx = tm.tid; idx < n; idx += tm.n) x[idx] = tmp[idx];
@@ -135,25 +139,44 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
   float* xrow = P.xbuf + (size_t)f * XBUF_STRIDE;
   const float* E = P.en + (size_t)f * EN_STRIDE;
   float* norm = sm->norm;
-  float* norm2 = norm + 800;
+  float* norm2 = norm + NORM_MAX;
   // (CELT-only frames start at band 0: every fold source is written earlier in the same frame, so the fold buffer
   //  needs no cross-frame persistence)
   const int norm_len = M * (eband(NB_EBANDS - 1) - eband(start));   // the reference's norm2 = norm + norm_len
   if (fold) {
     for (int i = tm.tid; i < norm_len; i += tm.n) { norm[i] = fold[i]; norm2[i] = fold[norm_len + i]; }
   } else {
-    for (int i = tm.tid; i < 2 * 800; i += tm.n) norm[i] = 0.f;
+    for (int i = tm.tid; i < 2 * NORM_MAX; i += tm.n) norm[i] = 0.f;
   }
   for (int idx = tm.tid; idx < C * NB_EBANDS; idx += tm.n) sm->gains[idx] = celt_exp2(fmin32(E[idx] + kEMeans[idx % NB_EBANDS], 32.0f));
   OpReader ops;
   ops.open(r + S_OPS * 32, (int)plan, tm.tid);
   MB_SYNC();
+  // The band window is double-buffered: while band b is rebuilt, band b+1 streams in from the spectrum row (cp.async),
+  // so the global-memory latency of the row is paid once per frame instead of once per band.
+  auto fetch = [&](int band, float* w) {
+    const int b0 = M * eband(band), nb = M * eband(band + 1) - b0;
+    for (int idx = tm.tid; idx < C * nb; idx += tm.n) {
+      int c = idx >= nb, j = idx - c * nb;
+#if MB_ON_DEVICE
+      const uint32_t sa = (uint32_t)__cvta_generic_to_shared(w + c * WIN_Y + j);
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(sa), "l"(xrow + c * N + b0 + j));
+#else
+      w[c * WIN_Y + j] = xrow[c * N + b0 + j];
+#endif
+    }
+#if MB_ON_DEVICE
+    asm volatile("cp.async.commit_group;\n" ::);
+#endif
+  };
+  if (start < end) fetch(start, sm->win2[0]);
   for (int band = start; band < end; band++) {
     const int band_start = M * eband(band), n = M * eband(band + 1) - band_start;
-    for (int idx = tm.tid; idx < C * n; idx += tm.n) {
-      int c = idx >= n, j = idx - c * n;
-      sm->win[c * WIN_Y + j] = xrow[c * N + band_start + j];
-    }
+    float* const win = sm->win2[(band - start) & 1];
+    if (band + 1 < end) fetch(band + 1, sm->win2[(band + 1 - start) & 1]);
+#if MB_ON_DEVICE
+    if (band + 1 < end) asm volatile("cp.async.wait_group 1;\n" ::); else asm volatile("cp.async.wait_group 0;\n" ::);
+#endif
     MB_SYNC();
     for (;;) {
       const uint32_t op = ops.next();
@@ -161,7 +184,7 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
       if (type == OP_END_BAND) break;
       const int a = (int)MB_OP_A(op), len = (int)MB_OP_N(op);
       const uint32_t p = MB_OP_P(op);
-      float* x = sm->win + a;
+      float* x = win + a;
       switch (type) {
         case OP_SKIP: ops.skip(len); break;
         case OP_COPY_LB: {
@@ -219,8 +242,8 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
         } break;
         case OP_MERGE: {  // stereo_merge (bands.rs:3477-3505): the two inner products keep the reference's summation order
           const float mid = (float)(int)(ops.next() & 0xffffu) / 32768.0f;
-          float* xx = sm->win;
-          float* yy = sm->win + WIN_Y;
+          float* xx = win;
+          float* yy = win + WIN_Y;
           for (int q = tm.tid; q < 2; q += tm.n) {
             const float* o = q ? yy : xx;
             float acc = 0.f;
@@ -251,8 +274,8 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
           const uint32_t w1 = ops.next();
           if (tm.tid == 0) {
             const float mid = (float)(int)(w1 & 0xffffu) / 32768.0f, side = (float)(int)(w1 >> 16) / 32768.0f;
-            float* xx = sm->win;
-            float* yy = sm->win + WIN_Y;
+            float* xx = win;
+            float* yy = win + WIN_Y;
             const int c = (int)(p & 1u);
             float* x2 = c ? yy : xx;
             float* y2 = c ? xx : yy;
@@ -303,11 +326,11 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
     if (P.x_dbg)
       for (int idx = tm.tid; idx < C * n; idx += tm.n) {
         int c = idx >= n, j = idx - c * n;
-        P.x_dbg[(size_t)f * 2 * MAX_N + c * MAX_N + band_start + j] = sm->win[c * WIN_Y + j];
+        P.x_dbg[(size_t)f * 2 * MAX_N + c * MAX_N + band_start + j] = win[c * WIN_Y + j];
       }
     for (int idx = tm.tid; idx < C * n; idx += tm.n) {
       int c = idx >= n, j = idx - c * n;
-      xrow[c * N + band_start + j] = sm->win[c * WIN_Y + j] * sm->gains[c * NB_EBANDS + band];
+      xrow[c * N + band_start + j] = win[c * WIN_Y + j] * sm->gains[c * NB_EBANDS + band];
     }
     MB_SYNC();
   }

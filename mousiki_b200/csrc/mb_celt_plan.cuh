@@ -139,7 +139,7 @@ MB_DEV uint32_t plan_partition(Plan& P, int a, int n, int B, int lb, float gain,
 
 // quant_band. lb_src: offset of the fold source in the fold buffer (-1 none), lb_which: 0 norm / 1 norm2;
 // lb_out: destination offset of this band's contribution to the fold buffer (-1 none).
-MB_DEV uint32_t plan_band(Plan& P, int a, int n, int B, int lb_src, int lb_which, int lb_out, int out_which, float gain, uint32_t fill) {
+MB_DEV_NOINLINE uint32_t plan_band(Plan& P, int a, int n, int B, int lb_src, int lb_which, int lb_out, int out_which, float gain, uint32_t fill) {
   const int n0 = n, long_blocks = B == 1;
   if (n == 1) {
     const uint32_t node = P.node();
@@ -198,7 +198,7 @@ MB_DEV uint32_t plan_band(Plan& P, int a, int n, int B, int lb_src, int lb_which
 }
 
 // quant_band_stereo (x at window offset 0, y at WIN_Y)
-MB_DEV uint32_t plan_band_stereo(Plan& P, int n, int B, int lb_src, int lb_out, uint32_t fill) {
+MB_DEV_NOINLINE uint32_t plan_band_stereo(Plan& P, int n, int B, int lb_src, int lb_out, uint32_t fill) {
   if (n == 1) {
     const uint32_t node = P.node();
     P.put(MB_OP(OP_N1, 0, 1, MB_ND_SIGN(node) & 1u));

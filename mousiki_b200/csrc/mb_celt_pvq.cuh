@@ -127,15 +127,21 @@ MB_DEV uint32_t pvq_leaf(float* x, int n, int k, int B, float gain, int spread, 
 
 struct PvqParams {
   uint32_t* rec;
-  const FrameMeta* meta;
+  const FrameMeta* meta;    // null: decide from the record alone (see celt_pvq_frame)
   float* xbuf;              // [frame][XBUF_STRIDE]
   int32_t* iy_dbg;          // optional [frame][2*960] decoded pulses (parity tests), else null
 };
 
 // One frame: `tm` threads share its leaves; X is the CTA's staging row (C*N floats).
 MB_DEV void celt_pvq_frame(Team tm, float* X, uint32_t f, const PvqParams& P) {
-  if (!(P.meta[f].flags & 1u)) return;
   uint32_t* r = P.rec + rec_index(f, 0);
+  if (P.meta) { if (!(P.meta[f].flags & 1u)) return; }
+  else {
+    // no frame meta yet (the kernel runs beside k_energy): every cell whose record holds a parsed CELT part is
+    // unpacked; a cell the stream pass rejects afterwards (mode switch, failed packet) is simply never consumed
+    const uint32_t status = r[S_STATUS * 32];
+    if (!MB_ST_DECODED(status) || (((status >> 16) & 1u) && !((status >> 17) & 1u))) return;
+  }
   const uint32_t h0 = r[S_HDR0 * 32], h1 = r[S_HDR1 * 32];
   const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), spread = (int)MB_H0_SPREAD(h0);
   const int N = SHORT_MDCT << lm;
