@@ -12,6 +12,7 @@
 //   k_clip_i16 warp per stream                          soft clip + float -> int16 (i16 output path only)
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo (see __graft_entry__.build()).
 #include <cuda_runtime.h>
+#include <chrono>
 #include <stdio.h>
 #include <stdlib.h>
 
@@ -449,6 +450,7 @@ struct bd_handle {
   cudaStream_t side_stream = nullptr;   // the latency-bound per-stream kernels (k_energy, k_silk) run here beside k_pvq
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   std::vector<cudaEvent_t> pass_events;
+  size_t pass_event_next = 0;
   struct PassOut { bool on = false; char* host_pcm = nullptr; const char* dev_pcm = nullptr; size_t elem = 0; } pass_out;
   DevBuf states, silk_states, silk_hist, fold, hist, rec, en, meta, series, xbuf;
   // staging for the host-buffer entry points
@@ -718,24 +720,36 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     }
     h->prof_end(s);
     h->launches += 8;
-    if (d_pcm_i16) {
-      h->prof_begin(BD_K_CLIP_I16, s);
-      k_clip_i16<<<(n_lanes + CLIP_WARPS - 1) / CLIP_WARPS, 32 * CLIP_WARPS, 0, s>>>(
-          n_lanes, nt, map, d_lane_stream, h->meta.as<FrameMeta>(), samples, h->states.as<StreamState>(), pcm,
-          d_pcm_i16 + shift * pcm_stride, pcm_stride, CC, d_out_map, flg);
-      h->prof_end(s);
-      h->launches += 1;
-    } else {
-      k_clear_softclip<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, d_lane_stream, h->states.as<StreamState>());
-      h->launches += 1;
-    }
-    if (h->pass_out.on) {  // packets of this pass are cells [cell0, cell0 + cells): ship their PCM while the next pass computes
-      const size_t k = t0 / ticks_per_pass;
+    // ship this pass's PCM (cells [cell0 + c0, cell0 + c0 + nc)) on the copy stream while later kernels compute
+    auto ship = [&](size_t c0, size_t nc) -> int {
+      const size_t k = h->pass_event_next++;
       while (h->pass_events.size() <= k) { cudaEvent_t e; CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->pass_events.push_back(e); }
       CK(cudaEventRecord(h->pass_events[k], s));
       CK(cudaStreamWaitEvent(h->copy_stream, h->pass_events[k], 0));
-      const size_t off = cell0 * pcm_stride * h->pass_out.elem, bytes = (size_t)cells * pcm_stride * h->pass_out.elem;
+      const size_t off = (cell0 + c0) * pcm_stride * h->pass_out.elem, bytes = nc * pcm_stride * h->pass_out.elem;
       CK(cudaMemcpyAsync(h->pass_out.host_pcm + off, h->pass_out.dev_pcm + off, bytes, cudaMemcpyDeviceToHost, h->copy_stream));
+      return BD_OK;
+    };
+    if (d_pcm_i16) {
+      // The clipper walks a stream's ticks in order, so it can run tick range by tick range; with the PCM going back to the
+      // host, each range is shipped as soon as it is clipped and only the last range's copy stays exposed.
+      const uint32_t n_chunks = h->pass_out.on ? (nt < 4u ? nt : 4u) : 1u;
+      for (uint32_t c = 0; c < n_chunks; c++) {
+        const uint32_t ta = (uint32_t)((uint64_t)nt * c / n_chunks), tb = (uint32_t)((uint64_t)nt * (c + 1) / n_chunks);
+        const size_t c0 = (size_t)ta * n_lanes;
+        h->prof_begin(BD_K_CLIP_I16, s);
+        k_clip_i16<<<(n_lanes + CLIP_WARPS - 1) / CLIP_WARPS, 32 * CLIP_WARPS, 0, s>>>(
+            n_lanes, tb - ta, map ? map + c0 : nullptr, d_lane_stream, h->meta.as<FrameMeta>() + c0, map ? samples : samples + c0,
+            h->states.as<StreamState>(), map ? pcm : pcm + c0 * pcm_stride, d_pcm_i16 + (map ? 0 : (shift + c0) * pcm_stride), pcm_stride, CC,
+            d_out_map, flg);
+        h->prof_end(s);
+        h->launches += 1;
+        if (h->pass_out.on) { int rc = ship(c0, (size_t)(tb - ta) * n_lanes); if (rc != BD_OK) return rc; }
+      }
+    } else {
+      k_clear_softclip<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, d_lane_stream, h->states.as<StreamState>());
+      h->launches += 1;
+      if (h->pass_out.on) { int rc = ship(0, cells); if (rc != BD_OK) return rc; }
     }
   }
   CK(cudaGetLastError());
@@ -761,6 +775,7 @@ static int decode_host_impl(bd_handle* h, const uint8_t* arena, const uint32_t* 
                             uint32_t* final_range_out, const uint32_t* out_map, uint32_t n_rows) {
   if (!h || !arena || !offsets || !stream_ids || !samples_out || !final_range_out || (!pcm_f32 && !pcm_i16)) return BD_ERR_BAD_ARG;
   if (n_packets == 0) return BD_OK;
+  const auto t_entry = std::chrono::steady_clock::now();
   CK(cudaSetDevice(h->device));
   h->launches = 0;
   cudaStream_t s = h->own_stream;
@@ -861,9 +876,11 @@ static int decode_host_impl(bd_handle* h, const uint8_t* arena, const uint32_t* 
   // the pass is done
   const bool overlap_out = identity;
   h->pass_out.on = overlap_out;
+  h->pass_event_next = 0;
   h->pass_out.host_pcm = pcm_f32 ? (char*)pcm_f32 : (char*)pcm_i16;
   h->pass_out.dev_pcm = pcm_f32 ? (const char*)d_f32 : (const char*)d_i16;
   h->pass_out.elem = pcm_f32 ? sizeof(float) : sizeof(int16_t);
+  const auto t_sched = std::chrono::steady_clock::now();
   int rc = decode_grid_device(h, h->d_arena.as<uint8_t>(), h->d_offsets.as<uint32_t>(), d_map, d_flags, n_lanes, n_ticks,
                               h->d_lane_stream.as<uint32_t>(), d_f32, d_i16, pcm_stride, h->d_samples.as<int32_t>(),
                               h->d_range.as<uint32_t>(), n_rows, s, d_dbg_iy, d_dbg_x, d_out_map);
@@ -875,8 +892,15 @@ static int decode_host_impl(bd_handle* h, const uint8_t* arena, const uint32_t* 
   }
   CK(cudaMemcpyAsync(samples_out, h->d_samples.p, (size_t)n_packets * 4, cudaMemcpyDeviceToHost, s));
   CK(cudaMemcpyAsync(final_range_out, h->d_range.p, (size_t)n_packets * 4, cudaMemcpyDeviceToHost, s));
+  const auto t_enq = std::chrono::steady_clock::now();
   CK(cudaStreamSynchronize(s));
+  const auto t_dev = std::chrono::steady_clock::now();
   CK(cudaStreamSynchronize(h->copy_stream));
+  if (getenv("MOUSIKI_B200_TIMING")) {
+    auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+    fprintf(stderr, "[mousiki_b200] host schedule + staging %.2f ms, enqueue %.2f ms, wait for kernels %.2f ms, wait for the last copy %.2f ms\n",
+            ms(t_entry, t_sched), ms(t_sched, t_enq), ms(t_enq, t_dev), ms(t_dev, std::chrono::steady_clock::now()));
+  }
   if (h->dbg_max) {
     // debug captures are indexed by grid cell; scatter them back to packet order
     std::vector<int32_t> iy;
