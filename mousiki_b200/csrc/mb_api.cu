@@ -276,6 +276,79 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
   if (live) st.preemph_mem[c] = d.mem;
 }
 
+// Warp-cooperative form of soft_clip_channel (mb_celt_tail.cuh; opus_pcm_soft_clip_impl, src/opus.rs:16-140): the scans
+// for the first sample beyond +-1, for the zero crossings on either side and for the peak are ballots / a max-reduction
+// over 32 samples at a time, the correction x + a*x*x is applied in parallel. Comparisons and max are exact, every sample
+// sees the same arithmetic as in the serial form, so the result is bit-identical to it. Only the rare linear ramp of the
+// "clip before the first zero crossing" case keeps its serial float recurrence (lane 0).
+template <class Pred> __device__ __forceinline__ int warp_first(int lo, int hi, int l, Pred pred) {
+  for (int b = lo; b < hi; b += 32) {
+    const int i = b + l;
+    const unsigned m = __ballot_sync(0xffffffffu, i < hi && pred(i));
+    if (m) return b + __ffs(m) - 1;
+  }
+  return hi;
+}
+template <class Pred> __device__ __forceinline__ int warp_last_below(int hi, int l, Pred pred) {   // largest i < hi with pred(i), else -1
+  for (int b = hi; b > 0; b -= 32) {
+    const int i = b - 1 - l;
+    const unsigned m = __ballot_sync(0xffffffffu, i >= 0 && pred(i));
+    if (m) return b - 1 - (__ffs(m) - 1);
+  }
+  return -1;
+}
+__device__ __forceinline__ void soft_clip_channel_warp(float* x, int N, int C, float& a_io, int l) {
+  float a = a_io;
+  {
+    const int first = warp_first(0, N, l, [&](int i) { return x[i * C] * a >= 0; });
+    for (int i = l; i < first; i += 32) { const float v = x[i * C]; x[i * C] = v + a * v * v; }
+    __syncwarp();
+  }
+  int curr = 0;
+  const float x0 = x[0];
+  for (;;) {
+    const int i0 = warp_first(curr, N, l, [&](int i) { const float v = x[i * C]; return !(v >= -1.f && v <= 1.f); });
+    if (i0 == N) { a = 0; break; }
+    const float xi = x[i0 * C];
+    const int start = warp_last_below(i0, l, [&](int i) { return !(xi * x[i * C] >= 0); }) + 1;
+    const int end = warp_first(i0, N, l, [&](int i) { return !(xi * x[i * C] >= 0); });
+    // peak: the first position of the largest magnitude in [i0, end)
+    float mx = -1.f;
+    int mp = 0x7fffffff;
+    for (int i = i0 + l; i < end; i += 32) { const float v = fabsf(x[i * C]); if (v > mx) { mx = v; mp = i; } }
+    for (int d = 16; d; d >>= 1) {
+      const float omx = __shfl_xor_sync(0xffffffffu, mx, d);
+      const int omp = __shfl_xor_sync(0xffffffffu, mp, d);
+      if (omx > mx || (omx == mx && omp < mp)) { mx = omx; mp = omp; }
+    }
+    float maxval = fabsf(xi);
+    int peak_pos = i0;
+    if (mx > maxval) { maxval = mx; peak_pos = mp; }
+    const int special = (start == 0 && xi * x[0] >= 0);
+    a = (maxval - 1) / (maxval * maxval);
+    a += a * 2.4e-7f;
+    if (xi > 0) a = -a;
+    __syncwarp();
+    for (int i = start + l; i < end; i += 32) { const float v = x[i * C]; x[i * C] = v + a * v * v; }
+    __syncwarp();
+    if (special && peak_pos >= 2) {
+      if (l == 0) {
+        float offset = x0 - x[0];
+        const float delta = offset / (float)peak_pos;
+        for (int i = curr; i < peak_pos; i++) {
+          offset -= delta;
+          float v = x[i * C] + offset;
+          x[i * C] = v < -1.f ? -1.f : (v > 1.f ? 1.f : v);
+        }
+      }
+      __syncwarp();
+    }
+    curr = end;
+    if (curr == N) break;
+  }
+  a_io = a;
+}
+
 // opus_decode's output stage (src/opus_decoder.rs:1679-1712): soft clip (src/opus.rs:16-140) then float -> int16
 // (src/celt/float_cast.rs:38-41). One warp per stream, its packets in tick order: the packet's interleaved float PCM is
 // staged in shared memory; a packet with no sample outside [-1, 1] and no carried-over nonlinearity (the common case)
@@ -320,20 +393,50 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
     float* src = pcm + eo;
     if (total > 2 * MAX_N) buf = src;   // long multi-frame packet: clip in place in the float scratch row
     int over = 0;
-    for (int i = l; i < total; i += 32) {
-      float v = src[i];
-      over |= !(v >= -1.f && v <= 1.f);
-      buf[i] = v < -2.f ? -2.f : (v > 2.f ? 2.f : v);
+    const bool vec = ((((uintptr_t)src) & 15u) | (uint32_t)(total & 7)) == 0 && ((((uintptr_t)(pcm16 + eo)) & 15u) == 0);
+    if (vec) {  // 128-bit loads, several in flight per lane: the row is read once and nothing else hides its latency
+      const float4* s4 = (const float4*)src;
+      float4* b4 = (float4*)buf;
+      const int total4 = total >> 2;
+#pragma unroll 4
+      for (int i = l; i < total4; i += 32) {
+        float4 v = s4[i];
+        over |= !(v.x >= -1.f && v.x <= 1.f) | !(v.y >= -1.f && v.y <= 1.f) | !(v.z >= -1.f && v.z <= 1.f) | !(v.w >= -1.f && v.w <= 1.f);
+        v.x = v.x < -2.f ? -2.f : (v.x > 2.f ? 2.f : v.x); v.y = v.y < -2.f ? -2.f : (v.y > 2.f ? 2.f : v.y);
+        v.z = v.z < -2.f ? -2.f : (v.z > 2.f ? 2.f : v.z); v.w = v.w < -2.f ? -2.f : (v.w > 2.f ? 2.f : v.w);
+        b4[i] = v;
+      }
+    } else {
+      for (int i = l; i < total; i += 32) {
+        float v = src[i];
+        over |= !(v >= -1.f && v <= 1.f);
+        buf[i] = v < -2.f ? -2.f : (v > 2.f ? 2.f : v);
+      }
     }
     over |= mem != 0.f;
     over = __any_sync(0xffffffffu, over);
     __syncwarp();
     if (over) {
-      if (l < CC) soft_clip_channel(buf + l, n, CC, mem);
+      for (int c = 0; c < CC; c++) {
+        float a = __shfl_sync(0xffffffffu, mem, c);
+        soft_clip_channel_warp(buf + c, n, CC, a, l);
+        if (l == c) mem = a;
+      }
       __syncwarp();
     }
     int16_t* dst = pcm16 + eo;
-    if ((((uintptr_t)dst) & 3u) == 0) {
+    if (vec) {
+      const float4* b4 = (const float4*)buf;
+      for (int i = l; i < (total >> 3); i += 32) {
+        const float4 a = b4[2 * i], b = b4[2 * i + 1];
+        uint4 o;
+        o.x = (uint32_t)(uint16_t)float2int16(a.x) | ((uint32_t)(uint16_t)float2int16(a.y) << 16);
+        o.y = (uint32_t)(uint16_t)float2int16(a.z) | ((uint32_t)(uint16_t)float2int16(a.w) << 16);
+        o.z = (uint32_t)(uint16_t)float2int16(b.x) | ((uint32_t)(uint16_t)float2int16(b.y) << 16);
+        o.w = (uint32_t)(uint16_t)float2int16(b.z) | ((uint32_t)(uint16_t)float2int16(b.w) << 16);
+        ((uint4*)dst)[i] = o;
+      }
+    } else if ((((uintptr_t)dst) & 3u) == 0) {
       for (int i = 2 * l; i + 1 < total; i += 64) {
         const uint32_t lo = (uint16_t)float2int16(buf[i]), hi = (uint16_t)float2int16(buf[i + 1]);
         *(uint32_t*)(dst + i) = lo | (hi << 16);
@@ -449,6 +552,7 @@ struct bd_handle {
   cudaStream_t copy_stream = nullptr;   // device -> host PCM of pass k overlaps the kernels of pass k + 1
   cudaStream_t side_stream = nullptr;   // the latency-bound per-stream kernels (k_energy, k_silk) run here beside k_pvq
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  cudaStream_t clip_stream = nullptr;   // k_clip_i16 of pass k runs beside the kernels of pass k + 1
   std::vector<cudaEvent_t> pass_events;
   size_t pass_event_next = 0;
   struct PassOut { bool on = false; char* host_pcm = nullptr; const char* dev_pcm = nullptr; size_t elem = 0; } pass_out;
@@ -527,6 +631,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);   // hi = numerically smallest = most urgent
     if (cudaStreamCreateWithPriority(&h->side_stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess) return fail(BD_ERR_CUDA);
   }
+  if (cudaStreamCreateWithFlags(&h->clip_stream, cudaStreamNonBlocking) != cudaSuccess) return fail(BD_ERR_CUDA);
   if (cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) != cudaSuccess) return fail(BD_ERR_CUDA);
   if (cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) != cudaSuccess) return fail(BD_ERR_CUDA);
   if (cudaFuncSetAttribute(k_deemph<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(DE_WARPS * 2 * 32 * (128 + 4) * sizeof(float))) != cudaSuccess)
@@ -556,6 +661,7 @@ void bd_destroy(bd_handle* h) {
   for (auto e : h->pass_events) cudaEventDestroy(e);
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
   if (h->side_stream) cudaStreamDestroy(h->side_stream);
+  if (h->clip_stream) cudaStreamDestroy(h->clip_stream);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -631,7 +737,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
   const uint32_t series_stride = HIST + ticks_per_pass * MAX_N;
   CK(h->rec.ensure((size_t)((cells_max + 31) / 32) * REC_SLOTS * 32 * sizeof(uint32_t)));
   CK(h->en.ensure((size_t)cells_max * EN_STRIDE * sizeof(float)));
-  CK(h->meta.ensure((size_t)cells_max * sizeof(FrameMeta)));
+  CK(h->meta.ensure((size_t)2 * cells_max * sizeof(FrameMeta)));   // two halves: the clipper of pass k runs beside pass k+1
   CK(h->series.ensure((size_t)n_lanes * CC * series_stride * sizeof(float)));
   CK(h->xbuf.ensure((size_t)cells_max * XBUF_STRIDE * sizeof(float)));
   float* pcm_f32 = d_pcm_f32;
@@ -640,9 +746,22 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     pcm_f32 = h->d_pcm.as<float>();
   }
   const int cap_per_ch = (int)(pcm_stride / (uint32_t)CC);
-  for (uint32_t t0 = 0; t0 < n_ticks; t0 += ticks_per_pass) {
-    const uint32_t nt = (n_ticks - t0 < ticks_per_pass) ? n_ticks - t0 : ticks_per_pass;
+  // Pass sizes. With the PCM going back to the host pass by pass, only the last pass's copy is exposed: the tail of the
+  // call is cut into a short final pass (a quarter of what is left) so that most of the copy hides behind kernels.
+  // Multi-frame calls keep the regular grid of passes (the host scheduler aligned frame groups to it).
+  h->pass_event_next = 0;
+  std::vector<uint32_t> pass_ticks;
+  for (uint32_t left = n_ticks; left > 0;) {
+    uint32_t nt = left < ticks_per_pass ? left : ticks_per_pass;
+    if (h->pass_out.on && !d_out_map && nt == left && nt >= 8) nt -= nt / 4;
+    pass_ticks.push_back(nt);
+    left -= nt;
+  }
+  uint32_t t0 = 0;
+  for (size_t pi = 0; pi < pass_ticks.size(); t0 += pass_ticks[pi], pi++) {
+    const uint32_t nt = pass_ticks[pi];
     const uint32_t cells = nt * n_lanes;
+    FrameMeta* const meta_p = h->meta.as<FrameMeta>() + (pi & 1) * (size_t)cells_max;
     const size_t cell0 = (size_t)t0 * n_lanes;
     // identity mapping: shift the per-packet arrays so that cell index == local packet index
     const uint32_t* map = d_pkt_map ? d_pkt_map + cell0 : nullptr;
@@ -664,14 +783,14 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     cudaStream_t ss = h->side_stream;
     h->prof_begin(BD_K_ENERGY, ss);
     k_energy<<<(n_lanes + 63) / 64, 64, 0, ss>>>(n_lanes, nt, map, h->rec.as<uint32_t>(), h->states.as<StreamState>(), d_lane_stream,
-                                                h->en.as<float>(), h->meta.as<FrameMeta>(), samples, range, h->cfg.quirks,
+                                                h->en.as<float>(), meta_p, samples, range, h->cfg.quirks,
                                                 d_out_map ? flg : nullptr);
     h->prof_end(ss);
     // SILK synthesis (SILK-only and hybrid cells), before the CELT tail so that k_deemph can add the CELT bands of hybrid
     // frames on top. SILK-only samples are exact int16 values scaled by 2^-15: on the i16 path soft clip + float2int16
     // is the identity and the lane stores int16 directly; hybrid cells go through the float row.
     h->prof_begin(BD_K_SILK, ss);
-    k_silk<<<(n_lanes + 63) / 64, 64, 0, ss>>>(n_lanes, nt, map, d_lane_stream, h->rec.as<uint32_t>(), h->meta.as<FrameMeta>(),
+    k_silk<<<(n_lanes + 63) / 64, 64, 0, ss>>>(n_lanes, nt, map, d_lane_stream, h->rec.as<uint32_t>(), meta_p,
                                               h->silk_states.as<SilkState>(), h->silk_hist.as<uint32_t>(), h->cfg.n_streams, pcm,
                                               d_pcm_i16 ? d_pcm_i16 + shift * pcm_stride : nullptr, pcm_stride, CC, h->cfg.quirks, h->gain,
                                               h->cfg.gain_q8 != 0, d_out_map);
@@ -686,25 +805,25 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     h->prof_end(s);
     CK(cudaStreamWaitEvent(s, h->ev_join, 0));   // join: everything below needs the frame meta and the SILK rows
     PlanParams pl;
-    pl.rec = h->rec.as<uint32_t>(); pl.en = h->en.as<float>(); pl.meta = h->meta.as<FrameMeta>();
+    pl.rec = h->rec.as<uint32_t>(); pl.en = h->en.as<float>(); pl.meta = meta_p;
     h->prof_begin(BD_K_PLAN, s);
     k_plan<<<(cells + 127) / 128, 128, 0, s>>>(pl, cells);
     h->prof_end(s);
     BandsParams bp;
-    bp.rec = h->rec.as<uint32_t>(); bp.en = h->en.as<float>(); bp.meta = h->meta.as<FrameMeta>(); bp.xbuf = h->xbuf.as<float>();
+    bp.rec = h->rec.as<uint32_t>(); bp.en = h->en.as<float>(); bp.meta = meta_p; bp.xbuf = h->xbuf.as<float>();
     bp.x_dbg = d_dbg_x ? d_dbg_x + cell0 * 2 * MAX_N : nullptr;
     h->prof_begin(BD_K_BANDS, s);
     k_bands<<<(cells + BANDS_WARPS - 1) / BANDS_WARPS, 32 * BANDS_WARPS, 0, s>>>(bp, cells);
     k_bands_hyb<<<(n_lanes + BANDS_WARPS - 1) / BANDS_WARPS, 32 * BANDS_WARPS, 0, s>>>(bp, n_lanes, nt, d_lane_stream, h->fold.as<float>());
     h->prof_end(s);
     ImdctParams ip;
-    ip.rec = h->rec.as<uint32_t>(); ip.meta = h->meta.as<FrameMeta>(); ip.xbuf = h->xbuf.as<float>(); ip.series = h->series.as<float>();
+    ip.rec = h->rec.as<uint32_t>(); ip.meta = meta_p; ip.xbuf = h->xbuf.as<float>(); ip.series = h->series.as<float>();
     ip.series_stride = series_stride; ip.CC = CC;
     h->prof_begin(BD_K_IMDCT, s);
     k_imdct<<<(cells * CC + IMDCT_WARPS - 1) / IMDCT_WARPS, 32 * IMDCT_WARPS, 0, s>>>(ip, cells * CC);
     h->prof_end(s);
     TailParams tp;
-    tp.rec = h->rec.as<uint32_t>(); tp.meta = h->meta.as<FrameMeta>(); tp.pkt_map = map; tp.lane_stream = d_lane_stream;
+    tp.rec = h->rec.as<uint32_t>(); tp.meta = meta_p; tp.pkt_map = map; tp.lane_stream = d_lane_stream;
     tp.st_all = h->states.as<StreamState>(); tp.hist = h->hist.as<float>(); tp.series = h->series.as<float>();
     tp.series_stride = series_stride; tp.n_lanes = n_lanes; tp.n_ticks = nt; tp.CC = CC; tp.gain = h->gain;
     tp.apply_gain = h->cfg.gain_q8 != 0; tp.pcm_f32 = pcm; tp.pcm_stride = pcm_stride; tp.out_map = d_out_map;
@@ -721,11 +840,19 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     h->prof_end(s);
     h->launches += 8;
     // ship this pass's PCM (cells [cell0 + c0, cell0 + c0 + nc)) on the copy stream while later kernels compute
-    auto ship = [&](size_t c0, size_t nc) -> int {
+    auto next_event = [&](cudaEvent_t* out) -> int {
       const size_t k = h->pass_event_next++;
       while (h->pass_events.size() <= k) { cudaEvent_t e; CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->pass_events.push_back(e); }
-      CK(cudaEventRecord(h->pass_events[k], s));
-      CK(cudaStreamWaitEvent(h->copy_stream, h->pass_events[k], 0));
+      *out = h->pass_events[k];
+      return BD_OK;
+    };
+    // the stream the pass's PCM is final on: the clipper's for int16 output, the main stream for float output
+    cudaStream_t fin = d_pcm_i16 ? h->clip_stream : s;
+    auto ship = [&](size_t c0, size_t nc) -> int {
+      cudaEvent_t ev;
+      { int rc = next_event(&ev); if (rc != BD_OK) return rc; }
+      CK(cudaEventRecord(ev, fin));
+      CK(cudaStreamWaitEvent(h->copy_stream, ev, 0));
       const size_t off = (cell0 + c0) * pcm_stride * h->pass_out.elem, bytes = nc * pcm_stride * h->pass_out.elem;
       CK(cudaMemcpyAsync(h->pass_out.host_pcm + off, h->pass_out.dev_pcm + off, bytes, cudaMemcpyDeviceToHost, h->copy_stream));
       return BD_OK;
@@ -733,16 +860,24 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     if (d_pcm_i16) {
       // The clipper walks a stream's ticks in order, so it can run tick range by tick range; with the PCM going back to the
       // host, each range is shipped as soon as it is clipped and only the last range's copy stays exposed.
+      // The clipper has its own stream: it only touches the pass's float rows, the int16 rows and the streams' clipper
+      // memory, so pass k is clipped while the main stream already decodes pass k+1 (the frame meta is double-buffered).
+      {
+        cudaEvent_t ev;
+        { int rc = next_event(&ev); if (rc != BD_OK) return rc; }
+        CK(cudaEventRecord(ev, s));
+        CK(cudaStreamWaitEvent(h->clip_stream, ev, 0));
+      }
       const uint32_t n_chunks = h->pass_out.on ? (nt < 4u ? nt : 4u) : 1u;
       for (uint32_t c = 0; c < n_chunks; c++) {
         const uint32_t ta = (uint32_t)((uint64_t)nt * c / n_chunks), tb = (uint32_t)((uint64_t)nt * (c + 1) / n_chunks);
         const size_t c0 = (size_t)ta * n_lanes;
-        h->prof_begin(BD_K_CLIP_I16, s);
-        k_clip_i16<<<(n_lanes + CLIP_WARPS - 1) / CLIP_WARPS, 32 * CLIP_WARPS, 0, s>>>(
-            n_lanes, tb - ta, map ? map + c0 : nullptr, d_lane_stream, h->meta.as<FrameMeta>() + c0, map ? samples : samples + c0,
+        h->prof_begin(BD_K_CLIP_I16, fin);
+        k_clip_i16<<<(n_lanes + CLIP_WARPS - 1) / CLIP_WARPS, 32 * CLIP_WARPS, 0, fin>>>(
+            n_lanes, tb - ta, map ? map + c0 : nullptr, d_lane_stream, meta_p + c0, map ? samples : samples + c0,
             h->states.as<StreamState>(), map ? pcm : pcm + c0 * pcm_stride, d_pcm_i16 + (map ? 0 : (shift + c0) * pcm_stride), pcm_stride, CC,
             d_out_map, flg);
-        h->prof_end(s);
+        h->prof_end(fin);
         h->launches += 1;
         if (h->pass_out.on) { int rc = ship(c0, (size_t)(tb - ta) * n_lanes); if (rc != BD_OK) return rc; }
       }
@@ -751,6 +886,12 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
       h->launches += 1;
       if (h->pass_out.on) { int rc = ship(0, cells); if (rc != BD_OK) return rc; }
     }
+  }
+  if (d_pcm_i16) {  // join the clipper back into the caller's stream
+    const size_t k = h->pass_event_next++;
+    while (h->pass_events.size() <= k) { cudaEvent_t e; CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->pass_events.push_back(e); }
+    CK(cudaEventRecord(h->pass_events[k], h->clip_stream));
+    CK(cudaStreamWaitEvent(s, h->pass_events[k], 0));
   }
   CK(cudaGetLastError());
   return BD_OK;
