@@ -551,7 +551,7 @@ struct bd_handle {
   cudaStream_t own_stream = nullptr;
   cudaStream_t copy_stream = nullptr;   // device -> host PCM of pass k overlaps the kernels of pass k + 1
   cudaStream_t side_stream = nullptr;   // the latency-bound per-stream kernels (k_energy, k_silk) run here beside k_pvq
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_silk = nullptr;
   cudaStream_t clip_stream = nullptr;   // k_clip_i16 of pass k runs beside the kernels of pass k + 1
   std::vector<cudaEvent_t> pass_events;
   size_t pass_event_next = 0;
@@ -642,6 +642,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
   if (cudaStreamCreateWithFlags(&h->clip_stream, cudaStreamNonBlocking) != cudaSuccess) return fail(BD_ERR_CUDA);
   if (cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) != cudaSuccess) return fail(BD_ERR_CUDA);
   if (cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) != cudaSuccess) return fail(BD_ERR_CUDA);
+  if (cudaEventCreateWithFlags(&h->ev_silk, cudaEventDisableTiming) != cudaSuccess) return fail(BD_ERR_CUDA);
   if (cudaFuncSetAttribute(k_deemph<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(DE_WARPS * 2 * 32 * (128 + 4) * sizeof(float))) != cudaSuccess)
     return fail(BD_ERR_CUDA);
   if (h->states.ensure((size_t)cfg->n_streams * sizeof(StreamState)) != cudaSuccess) return fail(BD_ERR_ALLOC);
@@ -672,6 +673,7 @@ void bd_destroy(bd_handle* h) {
   if (h->clip_stream) cudaStreamDestroy(h->clip_stream);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
+  if (h->ev_silk) cudaEventDestroy(h->ev_silk);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
 }
@@ -797,6 +799,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
                                                 h->en.as<float>(), meta_p, samples, range, h->cfg.quirks,
                                                 d_out_map ? flg : nullptr);
     h->prof_end(ss);
+    CK(cudaEventRecord(h->ev_join, ss));   // the frame meta and band energies are ready: k_plan may go
     // SILK synthesis (SILK-only and hybrid cells), before the CELT tail so that k_deemph can add the CELT bands of hybrid
     // frames on top. SILK-only samples are exact int16 values scaled by 2^-15: on the i16 path soft clip + float2int16
     // is the identity and the lane stores int16 directly; hybrid cells go through the float row.
@@ -806,7 +809,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
                                               d_pcm_i16 ? d_pcm_i16 + shift * pcm_stride : nullptr, pcm_stride, CC, h->cfg.quirks, h->gain,
                                               h->cfg.gain_q8 != 0, d_out_map);
     h->prof_end(ss);
-    CK(cudaEventRecord(h->ev_join, ss));
+    CK(cudaEventRecord(h->ev_silk, ss));   // the SILK rows are written: k_deemph (hybrid accumulate) and the output stage may go
     h->launches += 1;
     PvqParams pq;
     pq.rec = h->rec.as<uint32_t>(); pq.meta = nullptr; pq.xbuf = h->xbuf.as<float>();
@@ -814,7 +817,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     h->prof_begin(BD_K_PVQ, s);
     k_pvq<<<(cells + PVQ_CELLS - 1) / PVQ_CELLS, PVQ_THREADS, 0, s>>>(pq, cells);
     h->prof_end(s);
-    CK(cudaStreamWaitEvent(s, h->ev_join, 0));   // join: everything below needs the frame meta and the SILK rows
+    CK(cudaStreamWaitEvent(s, h->ev_join, 0));   // join 1: everything below needs the frame meta
     PlanParams pl;
     pl.rec = h->rec.as<uint32_t>(); pl.en = h->en.as<float>(); pl.meta = meta_p;
     h->prof_begin(BD_K_PLAN, s);
@@ -841,6 +844,10 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     h->prof_begin(BD_K_COMB, s);
     k_comb<<<(n_lanes * CC + COMB_WARPS - 1) / COMB_WARPS, 32 * COMB_WARPS, 0, s>>>(tp);
     h->prof_end(s);
+    // join 2: k_silk ran beside k_pvq .. k_comb. (Kernels with a large shared-memory footprint, k_bands / k_imdct, only join
+    // it on an SM once that SM is idle enough to change its L1 / shared split; giving k_silk the large split up front makes
+    // them overlap but costs k_silk its L1: 15.0 -> 18.1 ms, a net loss.)
+    CK(cudaStreamWaitEvent(s, h->ev_silk, 0));
     h->prof_begin(BD_K_DEEMPH, s);
     {
       // tile width by the number of warps: wide tiles (more bytes in flight per warp) while warps are scarce
