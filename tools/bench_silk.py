@@ -28,8 +28,8 @@ KINDS = {
     "silk": {"toc": helpers.silk_toc(2, 1, False), "payload": (8, 40), "ch": 1, "streams": 100_000,
              "workload": "silk_only_wb_mono_20ms_1e5_streams"},
     # BASELINE config 4: hybrid FB stereo 20 ms @ ~32 kb/s (SILK WB mid/side + CELT bands 17..20)
-    "hybrid": {"toc": ((15 << 3) | 4), "payload": (60, 100), "ch": 2, "streams": 20_000,
-               "workload": "hybrid_fb_stereo_20ms_2e4_streams"},
+    "hybrid": {"toc": ((15 << 3) | 4), "payload": (60, 100), "ch": 2, "streams": 50_000,
+               "workload": "hybrid_fb_stereo_20ms_5e4_streams"},
 }
 KIND = KINDS["silk"]
 
@@ -72,7 +72,7 @@ def main():
     streams, ticks = args.streams or KIND["streams"], args.ticks
     n = streams * ticks
     arena, offsets = corpus(streams, ticks, 5)
-    dec = BatchDecoder(streams, 48000, CH, device=0)
+    dec = BatchDecoder(streams, 48000, CH, device=0, max_frames_per_pass=max(1 << 18, streams * ticks))  # one pass per step
     # parity gate: first 64 streams
     cs = 64
     sel = (np.arange(ticks)[:, None] * streams + np.arange(cs)[None, :]).reshape(-1)
