@@ -32,11 +32,16 @@ using namespace mb;
 // ------------------------------------------------------------------------------------------ kernels
 __global__ void __launch_bounds__(128, 7) k_parse(const uint8_t* __restrict__ arena, const uint32_t* __restrict__ offsets,
                                                const uint32_t* __restrict__ pkt_map, uint32_t n_cells, uint32_t* __restrict__ rec, int CC,
-                                               uint32_t quirks, int disable_inv, int cap_per_ch, const uint8_t* __restrict__ flags) {
+                                               uint32_t quirks, int disable_inv, int cap_per_ch, const uint8_t* __restrict__ flags,
+                                               uint32_t n_lanes, const uint32_t* __restrict__ lane_stream, const StreamState* st) {
   uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
   if (f >= n_cells) return;
   uint32_t pkt = pkt_map ? pkt_map[f] : f;
-  parse_cell(arena, offsets, pkt, rec + rec_index(f, 0), CC, quirks, disable_inv, cap_per_ch, flags);
+  uint32_t prev_pkt = 0xffffffffu;
+  const int32_t* prev_mode = nullptr;
+  if (f >= n_lanes) prev_pkt = pkt_map ? pkt_map[f - n_lanes] : f - n_lanes;
+  else prev_mode = &st[lane_stream ? lane_stream[f] : f].prev_mode;
+  parse_cell(arena, offsets, pkt, rec + rec_index(f, 0), CC, quirks, disable_inv, cap_per_ch, flags, prev_pkt, prev_mode);
 }
 
 __global__ void __launch_bounds__(64) k_energy(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
@@ -496,14 +501,16 @@ __global__ void __launch_bounds__(64, 12) k_silk(uint32_t n_lanes, uint32_t n_ti
     if (!(meta[f].flags & 2u)) continue;
     const uint32_t p = pkt_map ? pkt_map[f] : f;
     const uint32_t* rb = rec + rec_index(f, 0);
-    const bool hybrid = (meta[f].flags & 8u) != 0;
+    const bool hybrid = (meta[f].flags & 8u) != 0;                     // the CELT part is added onto the float row by k_deemph
+    const bool fadeout = ((rb[S_STATUS * 32] >> 18) & 1u) != 0;         // SILK-only cell in the hybrid record layout
+    const bool hyb_layout = fadeout || ((rb[S_STATUS * 32] >> 17) & 1u) != 0;
     SilkPcmOut o;
     // hybrid cells always go to the float row (the CELT bands are added by k_deemph, then soft clip / gain follow);
     // SILK-only cells are final: int16 directly on the i16 path
     o.f32 = (hybrid || !pcm_i16) ? pcm_f32 + pcm_elem_off(out_map, p, pcm_stride) : nullptr;
     o.i16 = (hybrid || !pcm_i16) ? nullptr : pcm_i16 + pcm_elem_off(out_map, p, pcm_stride);
-    o.CC = CC; o.gain = gain; o.apply_gain = hybrid ? 0 : apply_gain;
-    silk_synth_packet(S, W, H, side_live, rb[(hybrid ? S_SILK_HYB : S_HDR0) * 32], rb + (hybrid ? S_SILK_HYB + 1 : SL_BASE) * 32, quirks, o,
+    o.CC = CC; o.gain = gain; o.apply_gain = (hybrid && !fadeout) ? 0 : apply_gain; o.gain_from = (hybrid && fadeout) ? SHORT_MDCT : 0;
+    silk_synth_packet(S, W, H, side_live, rb[(hyb_layout ? S_SILK_HYB : S_HDR0) * 32], rb + (hyb_layout ? S_SILK_HYB + 1 : SL_BASE) * 32, quirks, o,
                       stage[threadIdx.x], fir);
   }
   silk_hist_store(W, H, 0);
@@ -786,7 +793,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     float* pcm = pcm_f32 ? pcm_f32 + shift * pcm_stride : nullptr;
     h->prof_begin(BD_K_PARSE, s);
     k_parse<<<(cells + 127) / 128, 128, 0, s>>>(d_arena, offs, map, cells, h->rec.as<uint32_t>(), CC, h->cfg.quirks, h->disable_inv,
-                                                cap_per_ch, flg);
+                                                cap_per_ch, flg, n_lanes, d_lane_stream, h->states.as<StreamState>());
     h->prof_end(s);
     // fork: k_pvq needs nothing but the records, so it runs beside k_energy / k_silk, which keep one lane per stream
     // busy for a long time and leave most of the machine idle. The two per-stream kernels go to a second stream of the

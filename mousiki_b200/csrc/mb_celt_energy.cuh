@@ -87,7 +87,11 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
     // SILK-only / hybrid) or through the 2.5 ms CELT silence frame (hybrid -> SILK-only, :868-893) are rows F1/F2: reported
     // per packet without touching the stream.
     const bool silk_bit = ((status >> 16) & 1u) != 0, hybrid = ((status >> 17) & 1u) != 0;
-    const bool silk_only = silk_bit && !hybrid;
+    // bit 18: a SILK-only cell in the hybrid record layout whose CELT slots hold the 2.5 ms silence frame that lets the CELT
+    // overlap fade out after a hybrid packet (opus_decoder.rs:868-893; parsed on a hint, see parse_cell)
+    const bool has_fadeout = ((status >> 18) & 1u) != 0;
+    const bool fadeout = has_fadeout && st.prev_mode == 1001;
+    const bool silk_only = silk_bit && !hybrid && !fadeout;
     if ((!silk_bit && (st.prev_mode == 1000 || st.prev_mode == 1001)) || (silk_bit && st.prev_mode == 1002) ||
         (silk_only && st.prev_mode == 1001)) {
       meta[f] = m;
@@ -96,13 +100,15 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
       pkt_failed = true;
       continue;
     }
+    // SILK side of the cell: header and final range sit in the hybrid layout when the cell carries the fade-out record
+    const uint32_t silk_h0 = has_fadeout ? r[S_SILK_HYB * 32] : h0;
+    const int silk_n = (int)((silk_h0 >> 8) & 3u) * (int)((silk_h0 >> 5) & 7u) * 240;   // frames x subframes: 2, 4, 8, 12 -> 10 .. 60 ms
     if (silk_only) {  // SILK-only packet: synthesis runs in k_silk (mb_silk_out.cuh); here only the front-end bookkeeping
-      const int sc = (int)((h0 >> 8) & 3u) * (int)((h0 >> 5) & 7u);   // frames x subframes: 2, 4, 8, 12 -> 10, 20, 40, 60 ms
-      const int N = sc * 240;
+      const int N = silk_n;
       m.flags = 2;
       meta[f] = m;
       st.prev_mode = 1000;
-      st.range_final = r[S_RANGE * 32];
+      st.range_final = has_fadeout ? r[(S_SILK_HYB + 342) * 32] : r[S_RANGE * 32];
       st.last_packet_duration = N;
       samples_out[p] = N;
       final_range_out[p] = st.range_final;
@@ -185,17 +191,17 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
     st.rng = r[S_RANGE * 32];
     st.loss_duration = 0;
     if (status & (1u << 13)) st.celt_error = 1;
-    const int N = M * SHORT_MDCT;
-    m.flags = hybrid ? (1u | 2u | 8u | (celt_reset ? 4u : 0u)) : 1u;   // bit0 CELT, bit1 SILK, bit2 CELT reset, bit3 accumulate
+    const int N = fadeout ? silk_n : M * SHORT_MDCT;          // samples the packet delivers
+    m.flags = (hybrid || fadeout) ? (1u | 2u | 8u | (celt_reset ? 4u : 0u)) : 1u;   // bit0 CELT, bit1 SILK, bit2 CELT reset, bit3 accumulate
     meta[f] = m;
-    sample_off += (uint32_t)N;
+    sample_off += (uint32_t)(M * SHORT_MDCT);                 // the CELT time line advances by the CELT frame
     int code = MB_ST_CODE(status);
     if (code < 0) {  // e.g. bit-budget overrun: state has advanced, the call reports the error (celt_decoder.rs:4128)
       samples_out[p] = code;
       final_range_out[p] = st.range_final;
     } else {
-      st.prev_mode = hybrid ? 1001 : 1002;
-      st.range_final = st.rng;
+      st.prev_mode = fadeout ? 1000 : (hybrid ? 1001 : 1002);
+      st.range_final = fadeout ? r[(S_SILK_HYB + 342) * 32] : st.rng;
       st.last_packet_duration = N;
       samples_out[p] = N;
       final_range_out[p] = st.range_final;

@@ -15,8 +15,14 @@
 namespace mb {
 
 // cap_per_ch: PCM capacity per channel of the caller's buffer (the reference's `frame_size`).
+// prev_pkt: the packet in the lane's previous tick of this pass (0xffffffff: none); prev_mode: the stream's prev_mode word
+// when this is the pass's first tick, else null. Only a hint ("the previous packet was hybrid"): a SILK-only packet after
+// a hybrid one needs the CELT fade-out frame (src/opus_decoder.rs:868-893), whose record is parsed here; whether it is
+// used is decided by the stream pass (k_energy), which knows the real prev_mode.
+MB_TBL uint8_t kCeltSilenceFrame[2] = {0xFF, 0xFF};
 MB_DEV void parse_cell(const uint8_t* arena, const uint32_t* offsets, uint32_t pkt, uint32_t* rec_base, int CC, uint32_t quirks,
-                       int disable_inv, int cap_per_ch, const uint8_t* flags) {
+                       int disable_inv, int cap_per_ch, const uint8_t* flags, uint32_t prev_pkt = 0xffffffffu,
+                       const int32_t* prev_mode = nullptr) {
   if (pkt == 0xffffffffu) { rec_base[S_STATUS * 32] = 1u << 15; return; }
   // bits 4..7 of the flags: the host front end already rejected the packet (mb_host_packets.h: invalid framing,
   // row too small for all its frames); the cell only exists to report the code with the stream's final_range
@@ -52,7 +58,28 @@ MB_DEV void parse_cell(const uint8_t* arena, const uint32_t* offsets, uint32_t p
             return;
           }
         }
-      } else { silk_parse_frame(data + 1, len - 1, toc, quirks, cap_per_ch, rec_base); return; }
+      } else {
+        bool after_hybrid = prev_mode && *prev_mode == 1001;
+        if (prev_pkt != 0xffffffffu && offsets[prev_pkt + 1] > offsets[prev_pkt]) {
+          const uint32_t ptoc = arena[offsets[prev_pkt]];
+          after_hybrid = !(ptoc & 0x80u) && (ptoc & 0x60u) == 0x60u;
+        }
+        const int sc = (int)((toc >> 3) & 3u);
+        if (after_hybrid && sc <= 1) {
+          // one SILK frame in the hybrid record layout, then the 2.5 ms CELT silence frame, start band 0, end band by the
+          // packet's bandwidth (NB 13, MB / WB 17: src/opus_decoder.rs:861-866)
+          const uint32_t st_silk = silk_parse_frame(data + 1, len - 1, toc, quirks, cap_per_ch, rec_base, 1);
+          if (st_silk & (1u << 14)) {
+            const uint32_t silk_rng = rec_base[S_RANGE * 32];
+            const uint32_t silk_h0 = rec_base[S_HDR0 * 32];
+            rec_base[S_SILK_HYB * 32] = silk_h0;
+            rec_base[(S_SILK_HYB + 342) * 32] = silk_rng;
+            celt_parse_frame<0>(kCeltSilenceFrame, 2, 0, (toc & 4u) ? 2 : 1, ((toc >> 5) & 3u) == 0 ? 13 : 17, quirks, disable_inv, rec_base,
+                                nullptr, (1u << 16) | (1u << 18));
+          }
+        } else silk_parse_frame(data + 1, len - 1, toc, quirks, cap_per_ch, rec_base);
+        return;
+      }
     }
   }
   if (code == MB_OK) {

@@ -43,15 +43,17 @@ struct SilkPcmOut {
   int16_t* i16;    // interleaved packet row, or null
   int CC;          // API channels (interleave stride)
   float gain; int apply_gain;
+  int gain_from;   // first sample position (per channel) the gain applies to: 0, or 120 when k_deemph finishes the first
+                   // 2.5 ms of the row (CELT fade-out after a hybrid packet) and applies the gain there itself
 };
 struct SilkSink {
   int32_t* stage;  // 32 words, lane-private (shared memory on the device)
   int fill, pos, ch, dup;   // pos: sample position (per channel) of stage[0]; dup: mono stream into a stereo row
   const SilkPcmOut* o;
 };
-MB_DEV float silk_to_float(const SilkPcmOut& o, int32_t v) {
+MB_DEV float silk_to_float(const SilkPcmOut& o, int32_t v, int pos) {
   float x = (float)v * (1.0f / 32768.0f);
-  if (o.apply_gain) x *= o.gain;      // opus_decoder.rs:1376-1392
+  if (o.apply_gain && pos >= o.gain_from) x *= o.gain;      // opus_decoder.rs:1376-1392
   return x;
 }
 MB_DEV_NOINLINE void silk_sink_flush(SilkSink& s) {
@@ -66,18 +68,18 @@ MB_DEV_NOINLINE void silk_sink_flush(SilkSink& s) {
         if (rep == 1) {
 #pragma unroll
           for (int q = 0; q < 8; q++)
-            ((float4*)dst)[q] = make_float4(silk_to_float(o, s.stage[4 * q]), silk_to_float(o, s.stage[4 * q + 1]),
-                                            silk_to_float(o, s.stage[4 * q + 2]), silk_to_float(o, s.stage[4 * q + 3]));
+            ((float4*)dst)[q] = make_float4(silk_to_float(o, s.stage[4 * q], s.pos + (4 * q)), silk_to_float(o, s.stage[4 * q + 1], s.pos + (4 * q + 1)),
+                                            silk_to_float(o, s.stage[4 * q + 2], s.pos + (4 * q + 2)), silk_to_float(o, s.stage[4 * q + 3], s.pos + (4 * q + 3)));
         } else {
 #pragma unroll
           for (int q = 0; q < 16; q++) {
-            const float a = silk_to_float(o, s.stage[2 * q]), b = silk_to_float(o, s.stage[2 * q + 1]);
+            const float a = silk_to_float(o, s.stage[2 * q], s.pos + (2 * q)), b = silk_to_float(o, s.stage[2 * q + 1], s.pos + (2 * q + 1));
             ((float4*)dst)[q] = make_float4(a, a, b, b);
           }
         }
       } else
 #endif
-        for (int i = 0; i < n; i++) { const float x = silk_to_float(o, s.stage[i]); for (int r = 0; r < rep; r++) dst[i * rep + r] = x; }
+        for (int i = 0; i < n; i++) { const float x = silk_to_float(o, s.stage[i], s.pos + (i)); for (int r = 0; r < rep; r++) dst[i * rep + r] = x; }
     } else {
       int16_t* dst = o.i16 + (size_t)s.pos * rep;
 #if MB_ON_DEVICE
@@ -104,7 +106,7 @@ MB_DEV_NOINLINE void silk_sink_flush(SilkSink& s) {
         for (int i = 0; i < n; i++) for (int r = 0; r < rep; r++) dst[i * rep + r] = (int16_t)s.stage[i];
     }
   } else {  // one channel of an interleaved stereo row
-    if (o.f32) for (int i = 0; i < n; i++) o.f32[(size_t)(s.pos + i) * 2 + s.ch] = silk_to_float(o, s.stage[i]);
+    if (o.f32) for (int i = 0; i < n; i++) o.f32[(size_t)(s.pos + i) * 2 + s.ch] = silk_to_float(o, s.stage[i], s.pos + (i));
     else for (int i = 0; i < n; i++) o.i16[(size_t)(s.pos + i) * 2 + s.ch] = (int16_t)s.stage[i];
   }
   s.pos += n; s.fill = 0;

@@ -297,7 +297,10 @@ MB_DEV_NOINLINE void silk_parse_payload(RangeDec& ec, int fs_khz, int nb_subfr, 
 }
 
 // One SILK-only Opus frame. `data`/`len`: the frame without its TOC. cap_per_ch: PCM capacity per channel at 48 kHz.
-MB_DEV_NOINLINE void silk_parse_frame(const uint8_t* data, int len, uint32_t toc, uint32_t quirks, int cap_per_ch, uint32_t* rec_base) {
+// hyb_layout: the frame record goes where a hybrid cell keeps it (S_SILK_HYB + 1), leaving the CELT slots free.
+// Returns the status word.
+MB_DEV_NOINLINE uint32_t silk_parse_frame(const uint8_t* data, int len, uint32_t toc, uint32_t quirks, int cap_per_ch, uint32_t* rec_base,
+                                          int hyb_layout = 0) {
   const int bw = (int)((toc >> 5) & 3u);                 // 0 NB, 1 MB, 2 WB (3 = SWB never appears in SILK-only configs 0..11)
   const int sc = (int)((toc >> 3) & 3u);                 // 10, 20, 40, 60 ms
   const int fs_khz = bw == 0 ? 8 : (bw == 1 ? 12 : 16);
@@ -305,17 +308,19 @@ MB_DEV_NOINLINE void silk_parse_frame(const uint8_t* data, int len, uint32_t toc
   const int nb_subfr = sc == 0 ? 2 : 4;
   const int nci = (toc & 4u) ? 2 : 1;
   const int samples48 = (sc == 3 ? 2880 : (480 << sc));
-  if (samples48 > cap_per_ch) { rec_base[S_STATUS * 32] = (uint32_t)(uint8_t)(int8_t)MB_BUFFER_TOO_SMALL | (1u << 16); return; }
+  if (samples48 > cap_per_ch) { rec_base[S_STATUS * 32] = (uint32_t)(uint8_t)(int8_t)MB_BUFFER_TOO_SMALL | (1u << 16); return rec_base[S_STATUS * 32]; }
   RangeDec ec;
   ec.open(data, (uint32_t)len);
-  silk_parse_payload(ec, fs_khz, nb_subfr, n_frames, nci, quirks, rec_base + SL_BASE * 32);
+  silk_parse_payload(ec, fs_khz, nb_subfr, n_frames, nci, quirks, rec_base + (hyb_layout ? S_SILK_HYB + 1 : SL_BASE) * 32);
   // SILK-only redundancy test (opus_decoder.rs:746-759): when at least 17 bits remain the frame carries a CELT
   // redundancy frame. That arm is not built yet: such packets are reported as unimplemented before any state moves.
   int code = MB_OK;
   if (ec.tell() + 17 <= 8 * len) code = MB_UNIMPLEMENTED;
   rec_base[S_HDR0 * 32] = (uint32_t)fs_khz | ((uint32_t)nb_subfr << 5) | ((uint32_t)n_frames << 8) | ((uint32_t)nci << 10);
   rec_base[S_RANGE * 32] = ec.rng;
-  rec_base[S_STATUS * 32] = (uint32_t)(uint8_t)(int8_t)code | (code == MB_OK ? (1u << 14) : 0u) | (1u << 16);
+  const uint32_t status = (uint32_t)(uint8_t)(int8_t)code | (code == MB_OK ? (1u << 14) : 0u) | (1u << 16);
+  rec_base[S_STATUS * 32] = status;
+  return status;
 }
 
 }  // namespace mb

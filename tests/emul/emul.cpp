@@ -37,7 +37,8 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   const int disable_inv = CC == 1;
   // phase 1
   for (uint32_t f = 0; f < F; f++)
-    parse_cell(arena, offsets, f, rec.data() + rec_index(f, 0), CC, quirks, disable_inv, (int)(pcm_stride / CC), nullptr);
+    parse_cell(arena, offsets, f, rec.data() + rec_index(f, 0), CC, quirks, disable_inv, (int)(pcm_stride / CC), nullptr,
+               f >= n_lanes ? f - n_lanes : 0xffffffffu, f >= n_lanes ? nullptr : &st[f].prev_mode);
   // phase 2a
   for (uint32_t j = 0; j < n_lanes; j++)
     celt_energy_lane(j, n_lanes, n_ticks, nullptr, rec.data(), st.data(), nullptr, en.data(), meta.data(), samples_out, final_range_out, quirks);
@@ -86,11 +87,12 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
         if (!(meta[f].flags & 2u)) continue;
         const bool hybrid = (meta[f].flags & 8u) != 0;
         const uint32_t* rb = rec.data() + rec_index(f, 0);
+        const bool hyb_layout = ((rb[S_STATUS * 32] >> 17) & 3u) != 0;   // hybrid, or SILK-only with the CELT fade-out record
         SilkPcmOut o;
         o.f32 = (hybrid || !pcm16) ? out + (size_t)f * pcm_stride : nullptr;
         o.i16 = (hybrid || !pcm16) ? nullptr : pcm16 + (size_t)f * pcm_stride;
-        o.CC = CC; o.gain = 1.f; o.apply_gain = 0;
-        silk_synth_packet(sst[j], *W, H, side_live, rb[(hybrid ? S_SILK_HYB : S_HDR0) * 32], rb + (hybrid ? S_SILK_HYB + 1 : SL_BASE) * 32,
+        o.CC = CC; o.gain = 1.f; o.apply_gain = 0; o.gain_from = 0;
+        silk_synth_packet(sst[j], *W, H, side_live, rb[(hyb_layout ? S_SILK_HYB : S_HDR0) * 32], rb + (hyb_layout ? S_SILK_HYB + 1 : SL_BASE) * 32,
                           quirks, o, stage, silk_resampler_frac_FIR_12);
       }
     }

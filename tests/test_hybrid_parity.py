@@ -43,7 +43,8 @@ def _corpus(fb, ms20, stereo, ch, payload, seed, lanes, ticks):
 
 def _mixed_toc(k, rng):
     """SILK-only WB and hybrid packets drawn per packet; SILK -> hybrid resets the CELT half (opus_decoder.rs:744-751),
-    hybrid -> SILK-only needs the CELT fade-out frame (next row) and must come back as -5."""
+    hybrid -> SILK-only lets the CELT overlap fade out through a 2.5 ms silence frame added onto the first 120 samples
+    (opus_decoder.rs:868-893)."""
     if rng.integers(0, 4) == 0:
         return helpers.silk_toc(2, int(rng.integers(0, 2)), bool(rng.integers(0, 2)))
     return hyb_toc(rng.integers(0, 2), rng.integers(0, 2), rng.integers(0, 2))
@@ -84,25 +85,32 @@ def test_emul_hybrid_reference_vector():
         assert (err <= 1e-4) == within, (q, err)
 
 
-def test_emul_hybrid_after_silk_resets_celt_and_back_is_reported():
-    lanes, ticks = 8, 8
+def test_emul_hybrid_silk_switches_both_ways():
+    lanes, ticks = 8, 10
     for ch in (1, 2):
         arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, (30, 160), _mixed_toc, seed=60 + ch, channels=ch)
-        pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, ticks, ch, 960)
-        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 960)
         tocs = arena[offsets[:-1]].reshape(ticks, lanes)
-        se2, so2 = se.reshape(ticks, lanes), so.reshape(ticks, lanes)
-        checked = 0
-        for j in range(lanes):
-            for t in range(ticks):
-                hybrid = (tocs[t, j] & 0x60) == 0x60
-                if t and not hybrid and (tocs[t - 1, j] & 0x60) == 0x60:
-                    assert se2[t, j] == -5       # hybrid -> SILK-only: CELT fade-out frame, next row
-                    break                        # the oracle decoded it: the streams part ways here
-                f = t * lanes + j
-                assert se2[t, j] == so2[t, j] and re[f] == ro[f] and np.array_equal(pe[f], po[f])
-                checked += 1
-        assert checked > lanes * 2
+        hyb = (tocs & 0x60) == 0x60
+        assert (hyb[:-1] & ~hyb[1:]).any() and (~hyb[:-1] & hyb[1:]).any(), "corpus must switch in both directions"
+        for i16 in (False, True):
+            pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, ticks, ch, 960, i16=i16)
+            po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 960, i16=i16)
+            assert (so > 0).all()
+            assert np.array_equal(se, so) and np.array_equal(re, ro) and np.array_equal(pe, po)
+
+
+def test_emul_40ms_silk_after_hybrid_is_reported():
+    """The fade-out record shares the cell with ONE SILK frame; a 40 / 60 ms SILK-only packet right after a hybrid
+    packet is reported as -5 and leaves the stream where it was."""
+    good, goff = helpers.silk_fuzz_grid(1, 2, (40, 160), lambda k, r: hyb_toc(1, 1, False), seed=5, channels=1)
+    long_a, long_o = helpers.silk_fuzz_grid(1, 1, (60, 120), lambda k, r: helpers.silk_toc(2, 2, False), seed=6, channels=1)
+    pk = [good[goff[0]:goff[1]], long_a[long_o[0]:long_o[1]], good[goff[1]:goff[2]]]
+    offsets = np.zeros(4, dtype=np.uint32)
+    offsets[1:] = np.cumsum([len(p) for p in pk])
+    pe, se, re, _, _ = helpers.emul_decode_grid(np.concatenate(pk), offsets, 1, 3, 1, 1920)
+    po, so, ro = helpers.oracle_decode_grid(good, goff, 1, 2, 1, 1920)
+    assert se.tolist() == [960, -5, 960]
+    assert np.array_equal(pe[2], po[1]) and re[2] == ro[1]
 
 
 # ---------------------------------------------------------------------------------------------- GPU
@@ -165,21 +173,27 @@ def test_gpu_hybrid_state_across_calls():
 
 @pytest.mark.gpu
 def test_gpu_hybrid_silk_mix():
-    lanes, ticks = 64, 8
+    lanes, ticks = 64, 10
     arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, (30, 160), _mixed_toc, seed=81, channels=2)
     pg, sg, rg = _decode_gpu(arena, offsets, lanes, ticks, 2, 960, False)
     po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, 2, 960)
-    tocs = arena[offsets[:-1]].reshape(ticks, lanes)
-    sg2, so2 = sg.reshape(ticks, lanes), so.reshape(ticks, lanes)
-    checked = 0
-    for j in range(lanes):
+    assert (so > 0).all()
+    assert np.array_equal(sg, so) and np.array_equal(rg, ro)
+    assert float(np.abs(pg - po).max()) <= TOL
+    p16g, s16, r16 = _decode_gpu(arena, offsets, lanes, ticks, 2, 960, True)
+    p16o, _, _ = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, 2, 960, i16=True)
+    assert np.array_equal(s16, so) and np.array_equal(r16, ro)
+    assert int(np.abs(p16o.astype(np.int32) - p16g.astype(np.int32)).max()) <= 1
+    # one packet per stream per call: the hint for the fade-out record then comes from the stream state
+    from mousiki_b200 import BatchDecoder
+
+    ids = np.arange(lanes, dtype=np.uint32)
+    with BatchDecoder(lanes, 48000, 2) as dec:
         for t in range(ticks):
-            hybrid = (tocs[t, j] & 0x60) == 0x60
-            if t and not hybrid and (tocs[t - 1, j] & 0x60) == 0x60:
-                assert sg2[t, j] == -5
-                break
-            f = t * lanes + j
-            assert sg2[t, j] == so2[t, j] and rg[f] == ro[f]
-            assert float(np.abs(pg[f] - po[f]).max()) <= TOL
-            checked += 1
-    assert checked > lanes * 2
+            a = arena[offsets[t * lanes]:offsets[(t + 1) * lanes]]
+            o = (offsets[t * lanes:(t + 1) * lanes + 1] - offsets[t * lanes]).astype(np.uint32)
+            p, s_, r = dec.decode_float(a, o, ids, 960)
+            assert np.array_equal(s_, so[t * lanes:(t + 1) * lanes]) and np.array_equal(r, ro[t * lanes:(t + 1) * lanes])
+            for j in range(lanes):
+                m = int(s_[j]) * 2
+                assert np.array_equal(p[j, :m], pg[t * lanes + j, :m])
