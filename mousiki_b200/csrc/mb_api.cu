@@ -48,10 +48,10 @@ __global__ void __launch_bounds__(64) k_energy(uint32_t n_lanes, uint32_t n_tick
                                                const uint32_t* __restrict__ rec, StreamState* st, const uint32_t* __restrict__ lane_stream,
                                                float* __restrict__ en, FrameMeta* __restrict__ meta, int32_t* __restrict__ samples_out,
                                                uint32_t* __restrict__ final_range_out, uint32_t quirks,
-                                               const uint8_t* __restrict__ flags) {
+                                               const uint8_t* __restrict__ flags, int serial_all) {
   uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
   if (lane >= n_lanes) return;
-  celt_energy_lane(lane, n_lanes, n_ticks, pkt_map, rec, st, lane_stream, en, meta, samples_out, final_range_out, quirks, flags);
+  celt_energy_lane(lane, n_lanes, n_ticks, pkt_map, rec, st, lane_stream, en, meta, samples_out, final_range_out, quirks, flags, serial_all);
 }
 
 constexpr int PVQ_THREADS = 64;
@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(PVQ_THREADS) k_pvq(PvqParams P, uint32_t n_cel
       if (P.meta) live = (P.meta[f].flags & 1u) != 0;
       else {
         const uint32_t status = P.rec[rec_index(f, S_STATUS)];
-        live = MB_ST_DECODED(status) && !(((status >> 16) & 1u) && !((status >> 17) & 1u));
+        live = MB_ST_DECODED(status) && (!((status >> 16) & 1u) || ((status >> 17) & 1u) || ((status >> 19) & 3u));   // has a CELT record
       }
     }
     const uint32_t m = __ballot_sync(0xffffffffu, live);
@@ -113,13 +113,18 @@ __global__ void __launch_bounds__(32 * BANDS_WARPS) k_bands_hyb(BandsParams P, u
   if (lane >= n_lanes) return;
   Team tm = {(int)(threadIdx.x & 31), 32};
   uint32_t any = 0;
-  for (uint32_t t = tm.tid; t < n_ticks; t += 32) any |= P.meta[(size_t)t * n_lanes + lane].flags & 8u;
+  for (uint32_t t = tm.tid; t < n_ticks; t += 32) any |= P.meta[(size_t)t * n_lanes + lane].flags & MB_FL_FOLD;
   if (!__any_sync(0xffffffffu, any != 0)) return;
   float* fb = fold + (size_t)(lane_stream ? lane_stream[lane] : lane) * FOLD_WORDS;
+  BandsSmem* my = &sm[threadIdx.x >> 5];
+  for (int w = tm.tid; w < (int)FOLD_WORDS; w += 32) my->norm[w] = fb[w];
+  __syncwarp();
   for (uint32_t t = 0; t < n_ticks; t++) {
     const uint32_t f = t * n_lanes + lane;
-    if (P.meta[f].flags & 8u) celt_bands_frame(tm, &sm[threadIdx.x >> 5], f, P, fb);
+    if (P.meta[f].flags & MB_FL_FOLD) celt_bands_frame(tm, my, f, P, true);
   }
+  __syncwarp();
+  for (int w = tm.tid; w < (int)FOLD_WORDS; w += 32) fb[w] = my->norm[w];
 }
 
 // one warp per (frame, channel); 4 units per CTA
@@ -195,7 +200,7 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
   };
 
   for (uint32_t t = 0; t < P.n_ticks; t++) {
-    int N = 0, hyb = 0;
+    int N = 0, hyb = 0, side = 0;
     const float* x = nullptr;
     float* out = nullptr;
     if (live) {
@@ -208,10 +213,11 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
         out = P.pcm_f32 ? P.pcm_f32 + pcm_elem_off(P.out_map, p, P.pcm_stride) : nullptr;
         if (m.flags & 4u) d.mem = 0.f;                 // CELT reset before this frame
         if ((m.flags & 8u) && out) hyb = 1;            // hybrid: add to the SILK samples already in the row
+        if (m.flags & 16u) { out = P.xbuf + (size_t)f * XBUF_STRIDE; side = 1; }   // redundancy frame: kept aside for k_fade
       }
     }
     const unsigned hyb_mask = __ballot_sync(0xffffffffu, hyb);
-    d.apply_gain = hyb ? 0 : P.apply_gain;             // hybrid: the gain applies to SILK + CELT, at the store below
+    d.apply_gain = (hyb || side) ? 0 : P.apply_gain;   // hybrid: the gain applies to SILK + CELT, at the store below
     __syncwarp();
     row_x[l] = x; row_out[l] = out; row_n[l] = N;
     const int max_n = __reduce_max_sync(0xffffffffu, N);
@@ -279,6 +285,13 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
     }
   }
   if (live) st.preemph_mem[c] = d.mem;
+}
+
+// Redundancy cross-fades: one thread per (cell, channel); cells without a redundancy frame leave at the flag test.
+__global__ void __launch_bounds__(128) k_fade(TailParams P, uint32_t n_cells) {
+  const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= n_cells * (uint32_t)P.CC) return;
+  celt_fade_cell(u / (uint32_t)P.CC, (int)(u % (uint32_t)P.CC), P);
 }
 
 // Warp-cooperative form of soft_clip_channel (mb_celt_tail.cuh; opus_pcm_soft_clip_impl, src/opus.rs:16-140): the scans
@@ -501,15 +514,22 @@ __global__ void __launch_bounds__(64, 12) k_silk(uint32_t n_lanes, uint32_t n_ti
     if (!(meta[f].flags & 2u)) continue;
     const uint32_t p = pkt_map ? pkt_map[f] : f;
     const uint32_t* rb = rec + rec_index(f, 0);
-    const bool hybrid = (meta[f].flags & 8u) != 0;                     // the CELT part is added onto the float row by k_deemph
-    const bool fadeout = ((rb[S_STATUS * 32] >> 18) & 1u) != 0;         // SILK-only cell in the hybrid record layout
-    const bool hyb_layout = fadeout || ((rb[S_STATUS * 32] >> 17) & 1u) != 0;
+    const uint32_t fl = meta[f].flags;
+    const bool to_float = (fl & (8u | 16u)) != 0;   // a CELT frame shares the row (hybrid, fade-out, redundancy): float row, k_deemph / k_fade finish it
+    const bool hyb_layout = ((rb[S_STATUS * 32] >> 17) & 3u) != 0;       // hybrid, or a one-frame SILK-only cell
+    if (fl & 32u) {   // CELT -> SILK: silk decoder reset (opus_decoder.rs:694-696)
+      silk_state_reset(S, 0);
+      silk_ring_clear(W.hist[0], W.pos[0]); silk_ring_clear(W.hist[1], W.pos[1]);
+      side_live = 1;
+    }
     SilkPcmOut o;
-    // hybrid cells always go to the float row (the CELT bands are added by k_deemph, then soft clip / gain follow);
     // SILK-only cells are final: int16 directly on the i16 path
-    o.f32 = (hybrid || !pcm_i16) ? pcm_f32 + pcm_elem_off(out_map, p, pcm_stride) : nullptr;
-    o.i16 = (hybrid || !pcm_i16) ? nullptr : pcm_i16 + pcm_elem_off(out_map, p, pcm_stride);
-    o.CC = CC; o.gain = gain; o.apply_gain = (hybrid && !fadeout) ? 0 : apply_gain; o.gain_from = (hybrid && fadeout) ? SHORT_MDCT : 0;
+    o.f32 = (to_float || !pcm_i16) ? pcm_f32 + pcm_elem_off(out_map, p, pcm_stride) : nullptr;
+    o.i16 = (to_float || !pcm_i16) ? nullptr : pcm_i16 + pcm_elem_off(out_map, p, pcm_stride);
+    // decode gain: once on the finished sum. Hybrid: k_deemph does it for the whole row; fade-out: k_deemph for the first
+    // 120 samples, here for the rest; redundancy: k_fade for the whole row
+    const bool fadeout = (fl & 8u) && !((rb[S_STATUS * 32] >> 17) & 1u);
+    o.CC = CC; o.gain = gain; o.apply_gain = (to_float && !fadeout) ? 0 : apply_gain; o.gain_from = fadeout ? SHORT_MDCT : 0;
     silk_synth_packet(S, W, H, side_live, rb[(hyb_layout ? S_SILK_HYB : S_HDR0) * 32], rb + (hyb_layout ? S_SILK_HYB + 1 : SL_BASE) * 32, quirks, o,
                       stage[threadIdx.x], fir);
   }
@@ -553,6 +573,7 @@ struct bd_handle {
   int disable_inv = 0;
   float gain = 1.f;
   uint32_t max_frames_per_pass = 0;
+  bool serial_bands = false;   // MOUSIKI_B200_SERIAL_BANDS=1: per-stream band pass whatever the call size (see k_energy)
   std::string err;
   uint32_t launches = 0;
   cudaStream_t own_stream = nullptr;
@@ -635,6 +656,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
   h->disable_inv = cfg->disable_phase_inversion < 0 ? (cfg->channels == 1) : (cfg->disable_phase_inversion != 0);
   h->gain = cfg->gain_q8 == 0 ? 1.f : (float)exp(0.6931471805599453094 * (double)((3.32192809488736234787f / 5120.0f) * (float)cfg->gain_q8));
   h->max_frames_per_pass = cfg->max_frames_per_pass ? cfg->max_frames_per_pass : (1u << 18);
+  { const char* sb = getenv("MOUSIKI_B200_SERIAL_BANDS"); h->serial_bands = sb && atoi(sb) > 0; }
   const char* env = getenv("MOUSIKI_B200_MAX_FRAMES_PER_PASS");
   if (env && atoi(env) > 0) h->max_frames_per_pass = (uint32_t)atoi(env);
   auto fail = [&](int code) { bd_destroy(h); return code; };
@@ -804,7 +826,8 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     h->prof_begin(BD_K_ENERGY, ss);
     k_energy<<<(n_lanes + 63) / 64, 64, 0, ss>>>(n_lanes, nt, map, h->rec.as<uint32_t>(), h->states.as<StreamState>(), d_lane_stream,
                                                 h->en.as<float>(), meta_p, samples, range, h->cfg.quirks,
-                                                d_out_map ? flg : nullptr);
+                                                d_out_map ? flg : nullptr,
+                                                h->serial_bands || n_lanes >= 148u * 6u * (uint32_t)BANDS_WARPS);   // one warp per lane fills the band-pass slots
     h->prof_end(ss);
     CK(cudaEventRecord(h->ev_join, ss));   // the frame meta and band energies are ready: k_plan may go
     // SILK synthesis (SILK-only and hybrid cells), before the CELT tail so that k_deemph can add the CELT bands of hybrid
@@ -833,6 +856,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     BandsParams bp;
     bp.rec = h->rec.as<uint32_t>(); bp.en = h->en.as<float>(); bp.meta = meta_p; bp.xbuf = h->xbuf.as<float>();
     bp.x_dbg = d_dbg_x ? d_dbg_x + cell0 * 2 * MAX_N : nullptr;
+    bp.fold_all = h->fold.as<float>(); bp.lane_stream = d_lane_stream;
     h->prof_begin(BD_K_BANDS, s);
     k_bands<<<(cells + BANDS_WARPS - 1) / BANDS_WARPS, 32 * BANDS_WARPS, 0, s>>>(bp, cells);
     k_bands_hyb<<<(n_lanes + BANDS_WARPS - 1) / BANDS_WARPS, 32 * BANDS_WARPS, 0, s>>>(bp, n_lanes, nt, d_lane_stream, h->fold.as<float>());
@@ -847,7 +871,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     tp.rec = h->rec.as<uint32_t>(); tp.meta = meta_p; tp.pkt_map = map; tp.lane_stream = d_lane_stream;
     tp.st_all = h->states.as<StreamState>(); tp.hist = h->hist.as<float>(); tp.series = h->series.as<float>();
     tp.series_stride = series_stride; tp.n_lanes = n_lanes; tp.n_ticks = nt; tp.CC = CC; tp.gain = h->gain;
-    tp.apply_gain = h->cfg.gain_q8 != 0; tp.pcm_f32 = pcm; tp.pcm_stride = pcm_stride; tp.out_map = d_out_map;
+    tp.apply_gain = h->cfg.gain_q8 != 0; tp.pcm_f32 = pcm; tp.pcm_stride = pcm_stride; tp.out_map = d_out_map; tp.xbuf = h->xbuf.as<float>();
     h->prof_begin(BD_K_COMB, s);
     k_comb<<<(n_lanes * CC + COMB_WARPS - 1) / COMB_WARPS, 32 * COMB_WARPS, 0, s>>>(tp);
     h->prof_end(s);
@@ -863,7 +887,8 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
       else k_deemph<32><<<de_ctas, 32 * DE_WARPS, DE_WARPS * 2 * 32 * (32 + 4) * sizeof(float), s>>>(tp);
     }
     h->prof_end(s);
-    h->launches += 8;
+    k_fade<<<(cells * CC + 127) / 128, 128, 0, s>>>(tp, cells);
+    h->launches += 10;   // parse, energy, pvq, plan, bands, bands_hyb, imdct, comb, deemph, fade
     h->mark("kernels", pi, s);
     // ship this pass's PCM (cells [cell0 + c0, cell0 + c0 + nc)) on the copy stream while later kernels compute
     auto next_event = [&](cudaEvent_t* out) -> int {

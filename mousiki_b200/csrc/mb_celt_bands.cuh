@@ -121,16 +121,20 @@ struct BandsParams {
   const FrameMeta* meta;
   float* xbuf;              // [frame][XBUF_STRIDE]: pulse leaves in, freq out
   float* x_dbg;             // optional [frame][2*960] normalised spectrum after anti-collapse
+  float* fold_all = nullptr;           // [stream][FOLD_WORDS]: write-back target of the parallel pass (see celt_bands_frame)
+  const uint32_t* lane_stream = nullptr;
 };
 
 // fold: the stream's persistent fold buffer (FOLD_WORDS floats) for hybrid frames, else null.  The reference keeps
 // `scratch.norm_storage` in the decoder and never clears it (src/celt/bands.rs:2614-2625, src/celt/types.rs:400,416):
 // a hybrid frame starts at band 17, so its first folds read what EARLIER frames of the stream left there.  Frames that
-// carry flag 8 therefore run only when `fold` is given (tick order per stream); the parallel pass skips them.
-MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsParams& P, float* fold = nullptr) {
+// carry a MB_FL_FOLD flag (hybrid; the CELT frames that share a SILK packet's cell; CELT-only frames behind one of those in
+// the same pass) therefore run only when `fold` is given (tick order per stream); the parallel pass skips them and, for
+// the CELT-only frames it runs, stores the words of the buffer that survive the pass (a later hybrid frame may read them).
+MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsParams& P, bool serial = false) {
   const FrameMeta meta = P.meta[f];
   if (!(meta.flags & 1u)) return;
-  if (((meta.flags & 8u) != 0) != (fold != nullptr)) return;
+  if (((meta.flags & MB_FL_FOLD) != 0) != serial) return;
   const uint32_t* r = P.rec + rec_index(f, 0);
   const uint32_t h0 = r[S_HDR0 * 32], status = r[S_STATUS * 32], plan = r[S_PLAN * 32];
   const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), start = (int)MB_H0_START(h0), end = (int)MB_ST_END(status);
@@ -139,13 +143,14 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
   float* xrow = P.xbuf + (size_t)f * XBUF_STRIDE;
   const float* E = P.en + (size_t)f * EN_STRIDE;
   float* norm = sm->norm;
-  float* norm2 = norm + NORM_MAX;
+
   // (CELT-only frames start at band 0: every fold source is written earlier in the same frame, so the fold buffer
   //  needs no cross-frame persistence)
   const int norm_len = M * (eband(NB_EBANDS - 1) - eband(start));   // the reference's norm2 = norm + norm_len
-  if (fold) {
-    for (int i = tm.tid; i < norm_len; i += tm.n) { norm[i] = fold[i]; norm2[i] = fold[norm_len + i]; }
-  } else {
+  // sm->norm is the reference's flat storage: norm at 0, norm2 at norm_len. On the serial path it is the stream's buffer
+  // (loaded by the caller, left as the previous frame left it); the parallel path starts from zeros.
+  float* norm2 = norm + norm_len;
+  if (!serial) {
     for (int i = tm.tid; i < 2 * NORM_MAX; i += tm.n) norm[i] = 0.f;
   }
   for (int idx = tm.tid; idx < C * NB_EBANDS; idx += tm.n) sm->gains[idx] = celt_exp2(fmin32(E[idx] + kEMeans[idx % NB_EBANDS], 32.0f));
@@ -334,12 +339,15 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
     }
     MB_SYNC();
   }
-  if (fold) {
-    for (int i = tm.tid; i < norm_len; i += tm.n) {
-      fold[i] = norm[i];
-      if (C == 2) fold[norm_len + i] = norm2[i];
+  // write back on the parallel path: the words of this frame's footprint that no later frame of the pass overwrites
+  // (k_energy worked the interval out: flags bits 10-19 / 20-29, in units of 2 words)
+  if (!serial && P.fold_all) {
+    const int lo = 2 * (int)((meta.flags >> 10) & 1023u), hi = 2 * (int)((meta.flags >> 20) & 1023u);
+    if (hi > lo) {
+      float* dst = P.fold_all + (size_t)(P.lane_stream ? P.lane_stream[meta.lane] : meta.lane) * FOLD_WORDS;
+      for (int w = lo + tm.tid; w < hi; w += tm.n) dst[w] = norm[w];
+      MB_SYNC();
     }
-    MB_SYNC();
   }
 }
 

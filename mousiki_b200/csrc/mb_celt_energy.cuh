@@ -33,7 +33,9 @@ struct StreamState {
   int32_t last_packet_duration;
   float softclip_mem[2];
   int32_t celt_error;
-  int32_t reserved[3];
+  int32_t prev_redundancy;   // the last packet ended in a SILK -> CELT redundancy frame (opus_decoder.rs:1117)
+  int32_t fold_serial;       // the stream has decoded a SILK-side frame: its CELT-only frames keep the fold buffer exact too
+  int32_t reserved[1];
 };
 
 MB_DEV void stream_state_reset(StreamState& s) {
@@ -43,7 +45,8 @@ MB_DEV void stream_state_reset(StreamState& s) {
   s.rng = 0; s.range_final = 0; s.loss_duration = 0; s.prev_mode = 0; s.last_packet_duration = 0;
   s.softclip_mem[0] = s.softclip_mem[1] = 0.f;
   s.celt_error = 0;
-  s.reserved[0] = s.reserved[1] = s.reserved[2] = 0;
+  s.prev_redundancy = 0; s.fold_serial = 0;
+  s.reserved[0] = 0;
 }
 
 // per-frame side data produced here and consumed by phases 2b / 2c
@@ -52,17 +55,29 @@ struct FrameMeta {
   uint32_t sample_off;   // first sample of this frame in the lane's time series (excluding HIST)
   uint32_t lane;         // lane (stream slot) of this call
   uint32_t flags;        // bit0: frame runs through phases 2b/2c; bit1: SILK synthesis (k_silk); bit2: CELT state reset before
-                         // this frame; bit3: the CELT output is added to the SILK output already in the PCM row (hybrid)
+                         // this frame; bit3: the CELT output is added to the SILK output already in the PCM row (hybrid, fade-out);
+                         // bit4: redundancy frame: the CELT output goes to the cell's spectrum row (dead by then) and k_fade
+                         // cross-fades it into the SILK row; bit5: SILK decoder reset before the packet; bit6 / bit7: the
+                         // fade at the start (CELT -> SILK) / at the end (SILK -> CELT) of the row applies
 };
-enum { EN_STRIDE = 3 * 2 * NB_EBANDS };  // per-frame energy scratch: E, prev1 (old_log_e), prev2 (old_log_e2)
+enum { EN_STRIDE = 3 * 2 * NB_EBANDS,
+       MB_FL_FOLD = 8u | 16u | 512u };   // FrameMeta.flags: the frame's band pass runs per stream, in tick order, on the persistent fold buffer
+// flags bit 9 (512): CELT-only frame behind a SILK-side frame of the same pass; bits 10-19 / 20-29: fold-buffer words
+// [lo, hi) a CELT-only frame of the parallel band pass writes back (the part no later frame of the pass overwrites)  // per-frame energy scratch: E, prev1 (old_log_e), prev2 (old_log_e2)
 
 // One lane = one stream. Frame (grid cell) of tick t is f = t * n_lanes + lane; its packet index (for the
 // per-packet outputs) is pkt_map ? pkt_map[f] : f. Cells without a packet carry S_STATUS bit 15.
 MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, const uint32_t* pkt_map, const uint32_t* rec,
                              StreamState* st_all, const uint32_t* lane_stream, float* en, FrameMeta* meta, int32_t* samples_out,
-                             uint32_t* final_range_out, uint32_t quirks, const uint8_t* flags = nullptr) {
+                             uint32_t* final_range_out, uint32_t quirks, const uint8_t* flags = nullptr, int serial_all = 0) {
   StreamState& st = st_all[lane_stream ? lane_stream[lane] : lane];
   uint32_t sample_off = 0;
+  // Band pass of CELT-only frames. The reference's fold buffer outlives the frame (mb_celt_bands.cuh), so only a pass that
+  // walks a stream's frames in order reproduces it exactly: that is what runs whenever the call has enough streams to
+  // fill the machine that way (serial_all), and for every stream that has decoded a SILK-side frame (hybrid, fade-out,
+  // redundancy: the frames that read the buffer). Otherwise CELT-only frames run all at once and write back the part of
+  // their footprint that survives the pass: exact for CELT-only streams, whose frames never read the buffer.
+  bool silk_side_seen = serial_all || st.fold_serial;
   bool pkt_failed = false;   // an earlier frame of the same multi-frame packet failed: the reference returns there
                              // (src/opus_decoder.rs:1339-1350), so the remaining frames must not touch the stream
   for (uint32_t t = 0; t < n_ticks; t++) {
@@ -87,28 +102,41 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
     // SILK-only / hybrid) or through the 2.5 ms CELT silence frame (hybrid -> SILK-only, :868-893) are rows F1/F2: reported
     // per packet without touching the stream.
     const bool silk_bit = ((status >> 16) & 1u) != 0, hybrid = ((status >> 17) & 1u) != 0;
-    // bit 18: a SILK-only cell in the hybrid record layout whose CELT slots hold the 2.5 ms silence frame that lets the CELT
-    // overlap fade out after a hybrid packet (opus_decoder.rs:868-893; parsed on a hint, see parse_cell)
-    const bool has_fadeout = ((status >> 18) & 1u) != 0;
-    const bool fadeout = has_fadeout && st.prev_mode == 1001;
-    const bool silk_only = silk_bit && !hybrid && !fadeout;
-    if ((!silk_bit && (st.prev_mode == 1000 || st.prev_mode == 1001)) || (silk_bit && st.prev_mode == 1002) ||
-        (silk_only && st.prev_mode == 1001)) {
+    // bit 18: SILK-only cell whose record sits in the hybrid layout; bits 19-20: the CELT frame sharing the cell (parse_cell):
+    // 1 the 2.5 ms silence frame that lets the CELT overlap fade out after a hybrid packet (opus_decoder.rs:868-893, parsed
+    // on a hint, used only if the stream really comes from a hybrid packet), 2 / 3 a 5 ms redundancy frame for a
+    // CELT -> SILK / SILK -> CELT switch (opus_decoder.rs:746-797, 1012-1080).
+    const bool silk_layout = ((status >> 18) & 1u) != 0;
+    const int aux = (int)((status >> 19) & 3u);
+    const bool fadeout = aux == 1 && st.prev_mode == 1001;
+    const bool red = aux >= 2;
+    const bool silk_only = silk_bit && !hybrid && !fadeout && !red;
+    // Mode switches that need concealment (decode_frame(None), opus_decoder.rs:575-593, 798-809) are row F2: reported per
+    // packet without touching the stream. A redundancy frame makes the switch clean: CELT -> SILK when the SILK packet
+    // carries one, SILK -> CELT when the previous SILK packet ended in one.
+    bool reject;
+    if (!silk_bit) reject = st.prev_mode == 1001 || (st.prev_mode == 1000 && !st.prev_redundancy);
+    else if (red) reject = hybrid || st.prev_mode == 1001;   // would need two CELT frames in the cell (fade-out + redundancy)
+    else reject = st.prev_mode == 1002 || (silk_only && st.prev_mode == 1001);
+    if (reject) {
       meta[f] = m;
       samples_out[p] = MB_UNIMPLEMENTED;
       final_range_out[p] = st.range_final;
       pkt_failed = true;
       continue;
     }
-    // SILK side of the cell: header and final range sit in the hybrid layout when the cell carries the fade-out record
-    const uint32_t silk_h0 = has_fadeout ? r[S_SILK_HYB * 32] : h0;
+    // SILK side of the cell: header and final range sit in the hybrid layout when the cell uses it
+    const uint32_t silk_h0 = silk_layout ? r[S_SILK_HYB * 32] : h0;
+    const uint32_t silk_rng = silk_layout ? r[(S_SILK_HYB + 342) * 32] : r[S_RANGE * 32];
     const int silk_n = (int)((silk_h0 >> 8) & 3u) * (int)((silk_h0 >> 5) & 7u) * 240;   // frames x subframes: 2, 4, 8, 12 -> 10 .. 60 ms
+    const uint32_t silk_reset = (silk_bit && st.prev_mode == 1002) ? 32u : 0u;          // opus_decoder.rs:694-696
     if (silk_only) {  // SILK-only packet: synthesis runs in k_silk (mb_silk_out.cuh); here only the front-end bookkeeping
       const int N = silk_n;
-      m.flags = 2;
+      m.flags = 2u | silk_reset;
       meta[f] = m;
       st.prev_mode = 1000;
-      st.range_final = has_fadeout ? r[(S_SILK_HYB + 342) * 32] : r[S_RANGE * 32];
+      st.prev_redundancy = 0;
+      st.range_final = silk_rng;
       st.last_packet_duration = N;
       samples_out[p] = N;
       final_range_out[p] = st.range_final;
@@ -116,7 +144,8 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
     }
     // SILK-only -> hybrid: the CELT decoder is reset before the frame (opus_decoder.rs:895-898). The energy side is reset
     // here; the tail kernels reset their own state (post-filter, history, de-emphasis memory) on flag bit 2.
-    const bool celt_reset = hybrid && st.prev_mode == 1000;
+    // (also before a SILK -> CELT redundancy frame, opus_decoder.rs:1040-1046; not after a packet that ended in one)
+    const bool celt_reset = (hybrid && st.prev_mode == 1000 && !st.prev_redundancy) || aux == 3;
     if (celt_reset) {
       for (int i = 0; i < 2 * NB_EBANDS; i++) { st.old_ebands[i] = 0.f; st.old_log_e[i] = -28.f; st.old_log_e2[i] = -28.f; st.background_log_e[i] = 0.f; }
       st.rng = 0; st.loss_duration = 0;
@@ -191,8 +220,13 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
     st.rng = r[S_RANGE * 32];
     st.loss_duration = 0;
     if (status & (1u << 13)) st.celt_error = 1;
-    const int N = fadeout ? silk_n : M * SHORT_MDCT;          // samples the packet delivers
-    m.flags = (hybrid || fadeout) ? (1u | 2u | 8u | (celt_reset ? 4u : 0u)) : 1u;   // bit0 CELT, bit1 SILK, bit2 CELT reset, bit3 accumulate
+    const int N = (fadeout || red) ? silk_n : M * SHORT_MDCT;   // samples the packet delivers
+    if (red) {
+      m.flags = 1u | 2u | 16u | (celt_reset ? 4u : 0u) | silk_reset;
+      if (aux == 3) m.flags |= 128u;
+      else if (st.prev_mode != 1000 || st.prev_redundancy) m.flags |= 64u;   // opus_decoder.rs:1066
+    } else m.flags = (hybrid || fadeout) ? (1u | 2u | 8u | (celt_reset ? 4u : 0u)) : (silk_side_seen ? (1u | 512u) : 1u);
+    if (m.flags & (8u | 16u)) { silk_side_seen = true; st.fold_serial = 1; }
     meta[f] = m;
     sample_off += (uint32_t)(M * SHORT_MDCT);                 // the CELT time line advances by the CELT frame
     int code = MB_ST_CODE(status);
@@ -200,11 +234,27 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
       samples_out[p] = code;
       final_range_out[p] = st.range_final;
     } else {
-      st.prev_mode = fadeout ? 1000 : (hybrid ? 1001 : 1002);
-      st.range_final = fadeout ? r[(S_SILK_HYB + 342) * 32] : st.rng;
+      st.prev_mode = (fadeout || red) ? 1000 : (hybrid ? 1001 : 1002);
+      st.prev_redundancy = aux == 3;
+      st.range_final = fadeout ? silk_rng : (red ? (silk_rng ^ st.rng) : st.rng);
       st.last_packet_duration = N;
       samples_out[p] = N;
       final_range_out[p] = st.range_final;
+    }
+  }
+  // Fold-buffer write-back of the parallel band pass (mb_celt_bands.cuh): walking the lane's CELT-only frames backwards,
+  // each one keeps the words of its footprint that no later frame of the pass covers. A frame's footprint is the first
+  // C * norm_len words of the reference's storage (bands.rs:2614-2625), capped at what hybrid frames can read.
+  int covered = 0;
+  for (uint32_t t = n_ticks; t-- > 0 && covered < (int)FOLD_WORDS;) {
+    const uint32_t f = t * n_lanes + lane;
+    const uint32_t fl = meta[f].flags;
+    if (!(fl & 1u) || (fl & MB_FL_FOLD)) continue;
+    const uint32_t h0 = rec[rec_index(f, S_HDR0)];
+    const int top = imin((int)MB_H0_C(h0) * ((int)eband(NB_EBANDS - 1) << (int)MB_H0_LM(h0)), (int)FOLD_WORDS);   // even
+    if (top > covered) {
+      meta[f].flags = fl | ((uint32_t)(covered >> 1) << 10) | ((uint32_t)(top >> 1) << 20);
+      covered = top;
     }
   }
 }

@@ -265,7 +265,7 @@ MB_DEV void celt_plan_frame(uint32_t f, const PlanParams& Q) {
     const uint32_t ba = r[(S_BANDA + i) * 32];
     const int band_start = M * eband(i), n = M * eband(i + 1) - band_start;
     P.tf_change = MB_BA_TF(ba);
-    P.lb_inplace = start != 0 && i + 1 == end;
+    P.lb_inplace = i + 1 == end;   // (CELT-only frames too: their fold buffer can be read by a later hybrid frame of the stream)
     if (i == start + 1) {  // special_hybrid_folding (bands.rs:3517-3555)
       const int n1 = M * (eband(start + 1) - eband(start)), n2 = M * (eband(start + 2) - eband(start + 1));
       if (n2 > n1) { P.put(MB_OP(OP_HYB, 0, 0, 0)); P.put((uint32_t)n1 | ((uint32_t)(n2 - n1) << 11) | (MB_H0_DUAL(h0) << 22)); }

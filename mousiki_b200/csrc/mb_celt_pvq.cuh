@@ -140,7 +140,7 @@ MB_DEV void celt_pvq_frame(Team tm, float* X, uint32_t f, const PvqParams& P) {
     // no frame meta yet (the kernel runs beside k_energy): every cell whose record holds a parsed CELT part is
     // unpacked; a cell the stream pass rejects afterwards (mode switch, failed packet) is simply never consumed
     const uint32_t status = r[S_STATUS * 32];
-    if (!MB_ST_DECODED(status) || (((status >> 16) & 1u) && !((status >> 17) & 1u))) return;
+    if (!MB_ST_DECODED(status) || (((status >> 16) & 1u) && !((status >> 17) & 1u) && !((status >> 19) & 3u))) return;   // SILK only, no CELT record
   }
   const uint32_t h0 = r[S_HDR0 * 32], h1 = r[S_HDR1 * 32];
   const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), spread = (int)MB_H0_SPREAD(h0);

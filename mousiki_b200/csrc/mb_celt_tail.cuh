@@ -34,6 +34,7 @@ struct TailParams {
   float* pcm_f32;              // [packet][pcm_stride] interleaved, or null
   uint32_t pcm_stride;         // elements between packets
   const uint32_t* out_map = nullptr;  // see pcm_elem_off
+  float* xbuf = nullptr;              // [frame][XBUF_STRIDE]: spectrum rows, dead after the IMDCT; a redundancy frame's audio goes there
 };
 
 // ---------------------------------------------------------------- phase 2c(i): post-filter, one warp per stream-channel
@@ -175,14 +176,47 @@ MB_DEV void celt_deemph_lane(uint32_t lane, int c, const TailParams& P) {
     const float* x = ser + m.sample_off;
     const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
     float* out = P.pcm_f32 ? P.pcm_f32 + pcm_elem_off(P.out_map, p, P.pcm_stride) + c : nullptr;
+    const bool side = (m.flags & 16u) != 0;       // redundancy frame: not the packet's audio, kept aside for celt_fade_cell
+    if (side) out = P.xbuf + (size_t)f * XBUF_STRIDE + c;
     if (m.flags & 4u) d.mem = 0.f;
     const bool accum = (m.flags & 8u) != 0;
+    d.apply_gain = side ? 0 : P.apply_gain;
     for (int j = 0; j < N; j++) {
       const float v = d.step(x[j], accum && out ? out[(size_t)j * CC] : 0.f, accum);
       if (out) out[(size_t)j * CC] = v;
     }
   }
   st.preemph_mem[c] = d.mem;
+}
+
+// Redundancy cross-fades (opus_decoder.rs:1048-1080, smooth_fade :100-135) for channel c of cell f, after the de-emphasis:
+// the 5 ms CELT frame kept in the cell's spectrum row replaces / blends into the SILK audio of the row, then the decode
+// gain is applied to the finished row. w = window[i]^2 over 120 samples (48 kHz).
+MB_DEV void celt_fade_cell(uint32_t f, int c, const TailParams& P) {
+  const FrameMeta m = P.meta[f];
+  if (!(m.flags & 16u) || !P.pcm_f32) return;
+  const int CC = P.CC;
+  const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
+  float* row = P.pcm_f32 + pcm_elem_off(P.out_map, p, P.pcm_stride) + c;
+  const float* red = P.xbuf + (size_t)f * XBUF_STRIDE + c;
+  const uint32_t silk_h0 = P.rec[rec_index(f, S_SILK_HYB)];
+  const int N = (int)((silk_h0 >> 8) & 3u) * (int)((silk_h0 >> 5) & 7u) * 240;
+  if (m.flags & 128u) {          // SILK -> CELT: the end of the row fades into the second half of the redundancy frame
+    for (int i = 0; i < SHORT_MDCT; i++) {
+      const float wv = bits2f(kWindow120Bits[i]), w = wv * wv;
+      float* o = row + (size_t)(N - SHORT_MDCT + i) * CC;
+      *o = w * red[(size_t)(SHORT_MDCT + i) * CC] + (1.0f - w) * *o;
+    }
+  } else if (m.flags & 64u) {    // CELT -> SILK: the redundancy frame opens the row and fades into the SILK audio
+    for (int i = 0; i < SHORT_MDCT; i++) row[(size_t)i * CC] = red[(size_t)i * CC];
+    for (int i = 0; i < SHORT_MDCT; i++) {
+      const float wv = bits2f(kWindow120Bits[i]), w = wv * wv;
+      float* o = row + (size_t)(SHORT_MDCT + i) * CC;
+      *o = w * *o + (1.0f - w) * red[(size_t)(SHORT_MDCT + i) * CC];
+    }
+  }
+  if (P.apply_gain)
+    for (int i = 0; i < N; i++) row[(size_t)i * CC] *= P.gain;
 }
 
 // float -> int16 (src/celt/float_cast.rs:38-41)

@@ -67,7 +67,7 @@ enum {
   CAP_OPS = 2048,
   S_SILK_HYB = S_OPS + CAP_OPS,    // hybrid cells: SILK header word, then one SILK frame record (mb_silk_parse.cuh)
   REC_SLOTS = S_SILK_HYB + 344,
-  FOLD_WORDS = 608                 // hybrid fold buffer per stream: 2 channels x 8*(eband(20)-eband(17)) floats
+  FOLD_WORDS = 1248                // fold buffer per stream: the reference's norm_storage, 2 channels x 8 * eband(20) floats
 };
 
 // First PCM element of packet p: row p of the caller's buffer, or (calls cut into frames by mb_host_packets.h) row

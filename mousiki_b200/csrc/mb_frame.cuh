@@ -64,20 +64,20 @@ MB_DEV void parse_cell(const uint8_t* arena, const uint32_t* offsets, uint32_t p
           const uint32_t ptoc = arena[offsets[prev_pkt]];
           after_hybrid = !(ptoc & 0x80u) && (ptoc & 0x60u) == 0x60u;
         }
-        const int sc = (int)((toc >> 3) & 3u);
-        if (after_hybrid && sc <= 1) {
-          // one SILK frame in the hybrid record layout, then the 2.5 ms CELT silence frame, start band 0, end band by the
-          // packet's bandwidth (NB 13, MB / WB 17: src/opus_decoder.rs:861-866)
-          const uint32_t st_silk = silk_parse_frame(data + 1, len - 1, toc, quirks, cap_per_ch, rec_base, 1);
-          if (st_silk & (1u << 14)) {
-            const uint32_t silk_rng = rec_base[S_RANGE * 32];
-            const uint32_t silk_h0 = rec_base[S_HDR0 * 32];
-            rec_base[S_SILK_HYB * 32] = silk_h0;
-            rec_base[(S_SILK_HYB + 342) * 32] = silk_rng;
-            celt_parse_frame<0>(kCeltSilenceFrame, 2, 0, (toc & 4u) ? 2 : 1, ((toc >> 5) & 3u) == 0 ? 13 : 17, quirks, disable_inv, rec_base,
-                                nullptr, (1u << 16) | (1u << 18));
-          }
-        } else silk_parse_frame(data + 1, len - 1, toc, quirks, cap_per_ch, rec_base);
+        SilkRedundancy red;
+        const uint32_t st_silk = silk_parse_frame(data + 1, len - 1, toc, quirks, cap_per_ch, rec_base, &red);
+        // status bits 19-20: the CELT frame that shares the cell: 1 fade-out silence, 2 redundancy CELT -> SILK (played
+        // before the SILK frame), 3 redundancy SILK -> CELT (after it). A packet that would need two of them (redundancy
+        // right after a hybrid packet) is left to the stream pass, which reports it.
+        if ((st_silk & (1u << 14)) && (st_silk & (1u << 18))) {
+          const int C = (toc & 4u) ? 2 : 1, end = ((toc >> 5) & 3u) == 0 ? 13 : 17;   // NB 13, MB / WB 17 (opus_decoder.rs:861-866)
+          const uint32_t keep = (1u << 16) | (1u << 18);
+          if (red.bytes > 0)
+            celt_parse_frame<0>(data + 1 + red.cutoff, red.bytes, 1, C, end, quirks, disable_inv, rec_base, nullptr,
+                                keep | ((red.celt_to_silk ? 2u : 3u) << 19));
+          else if (after_hybrid)
+            celt_parse_frame<0>(kCeltSilenceFrame, 2, 0, C, end, quirks, disable_inv, rec_base, nullptr, keep | (1u << 19));
+        }
         return;
       }
     }

@@ -297,10 +297,14 @@ MB_DEV_NOINLINE void silk_parse_payload(RangeDec& ec, int fs_khz, int nb_subfr, 
 }
 
 // One SILK-only Opus frame. `data`/`len`: the frame without its TOC. cap_per_ch: PCM capacity per channel at 48 kHz.
-// hyb_layout: the frame record goes where a hybrid cell keeps it (S_SILK_HYB + 1), leaving the CELT slots free.
-// Returns the status word.
+// One SILK-only Opus frame. `data`/`len`: the frame without its TOC. cap_per_ch: PCM capacity per channel at 48 kHz.
+// Packets of one SILK frame (10 / 20 ms) keep their record where a hybrid cell keeps it (S_SILK_HYB: header, frame,
+// final range in the last slot), which leaves the CELT slots of the cell free for the CELT frame such a packet may need
+// next to it: the redundancy frame it carries (opus_decoder.rs:746-797) or the fade-out frame after a hybrid packet.
+// Status bit 18 = that layout. `red` receives the redundancy split (bytes == 0: none).
+struct SilkRedundancy { int celt_to_silk, cutoff, bytes; };
 MB_DEV_NOINLINE uint32_t silk_parse_frame(const uint8_t* data, int len, uint32_t toc, uint32_t quirks, int cap_per_ch, uint32_t* rec_base,
-                                          int hyb_layout = 0) {
+                                          SilkRedundancy* red) {
   const int bw = (int)((toc >> 5) & 3u);                 // 0 NB, 1 MB, 2 WB (3 = SWB never appears in SILK-only configs 0..11)
   const int sc = (int)((toc >> 3) & 3u);                 // 10, 20, 40, 60 ms
   const int fs_khz = bw == 0 ? 8 : (bw == 1 ? 12 : 16);
@@ -308,17 +312,30 @@ MB_DEV_NOINLINE uint32_t silk_parse_frame(const uint8_t* data, int len, uint32_t
   const int nb_subfr = sc == 0 ? 2 : 4;
   const int nci = (toc & 4u) ? 2 : 1;
   const int samples48 = (sc == 3 ? 2880 : (480 << sc));
+  red->bytes = 0;
   if (samples48 > cap_per_ch) { rec_base[S_STATUS * 32] = (uint32_t)(uint8_t)(int8_t)MB_BUFFER_TOO_SMALL | (1u << 16); return rec_base[S_STATUS * 32]; }
+  const int hyb_layout = n_frames == 1;
   RangeDec ec;
   ec.open(data, (uint32_t)len);
   silk_parse_payload(ec, fs_khz, nb_subfr, n_frames, nci, quirks, rec_base + (hyb_layout ? S_SILK_HYB + 1 : SL_BASE) * 32);
-  // SILK-only redundancy test (opus_decoder.rs:746-759): when at least 17 bits remain the frame carries a CELT
-  // redundancy frame. That arm is not built yet: such packets are reported as unimplemented before any state moves.
+  // SILK-only redundancy (opus_decoder.rs:746-797): with at least 17 bits left the frame ends in a 5 ms CELT frame; one
+  // bit tells which side of the mode switch it belongs to, its size is whatever the range coder has not used.
   int code = MB_OK;
-  if (ec.tell() + 17 <= 8 * len) code = MB_UNIMPLEMENTED;
-  rec_base[S_HDR0 * 32] = (uint32_t)fs_khz | ((uint32_t)nb_subfr << 5) | ((uint32_t)n_frames << 8) | ((uint32_t)nci << 10);
+  if (ec.tell() + 17 <= 8 * len) {
+    if (!hyb_layout) code = MB_UNIMPLEMENTED;            // 40 / 60 ms packets: the cell has no room for the CELT record
+    else {
+      red->celt_to_silk = ec.bit_logp(1);
+      red->bytes = len - ((ec.tell() + 7) >> 3);
+      red->cutoff = len - red->bytes;
+      if (red->bytes < 0 || red->bytes > len) { code = MB_BAD_ARG; red->bytes = 0; }
+      else if (red->cutoff * 8 < ec.tell() || red->cutoff <= 1 || red->bytes < 2) { code = MB_UNIMPLEMENTED; red->bytes = 0; }  // degenerate splits
+    }
+  }
+  const uint32_t h0 = (uint32_t)fs_khz | ((uint32_t)nb_subfr << 5) | ((uint32_t)n_frames << 8) | ((uint32_t)nci << 10);
+  rec_base[S_HDR0 * 32] = h0;
   rec_base[S_RANGE * 32] = ec.rng;
-  const uint32_t status = (uint32_t)(uint8_t)(int8_t)code | (code == MB_OK ? (1u << 14) : 0u) | (1u << 16);
+  if (hyb_layout) { rec_base[S_SILK_HYB * 32] = h0; rec_base[(S_SILK_HYB + 342) * 32] = ec.rng; }
+  const uint32_t status = (uint32_t)(uint8_t)(int8_t)code | (code == MB_OK ? (1u << 14) : 0u) | (1u << 16) | ((uint32_t)hyb_layout << 18);
   rec_base[S_STATUS * 32] = status;
   return status;
 }

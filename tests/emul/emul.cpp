@@ -41,7 +41,8 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
                f >= n_lanes ? f - n_lanes : 0xffffffffu, f >= n_lanes ? nullptr : &st[f].prev_mode);
   // phase 2a
   for (uint32_t j = 0; j < n_lanes; j++)
-    celt_energy_lane(j, n_lanes, n_ticks, nullptr, rec.data(), st.data(), nullptr, en.data(), meta.data(), samples_out, final_range_out, quirks);
+    celt_energy_lane(j, n_lanes, n_ticks, nullptr, rec.data(), st.data(), nullptr, en.data(), meta.data(), samples_out, final_range_out, quirks,
+                     nullptr, getenv("MB_EMUL_PARALLEL_BANDS") ? 0 : 1);   // default: the per-stream band pass of large calls
   // phase 2b
   Team tm = {0, 1};
   std::vector<float> xbuf((size_t)F * XBUF_STRIDE, 0.f), xstage(2 * MAX_N);
@@ -51,10 +52,17 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   for (uint32_t f = 0; f < F; f++) celt_plan_frame(f, pl);
   BandsSmem* bsm = new BandsSmem;
   BandsParams bp; bp.rec = rec.data(); bp.en = en.data(); bp.meta = meta.data(); bp.xbuf = xbuf.data(); bp.x_dbg = x_dbg;
+  std::vector<float> fold((size_t)n_lanes * FOLD_WORDS, 0.f);
+  bp.fold_all = fold.data();
   for (uint32_t f = 0; f < F; f++) celt_bands_frame(tm, bsm, f, bp);
-  {  // hybrid frames: tick order per stream, fold buffer carried in stream state (k_bands_hyb)
-    std::vector<float> fold((size_t)n_lanes * FOLD_WORDS, 0.f);
-    for (uint32_t f = 0; f < F; f++) celt_bands_frame(tm, bsm, f, bp, fold.data() + (size_t)(f % n_lanes) * FOLD_WORDS);
+  {  // SILK-side frames: tick order per stream, fold buffer carried in stream state (k_bands_hyb)
+    for (uint32_t f = 0; f < F; f++) {
+      if (!(meta[f].flags & MB_FL_FOLD)) continue;
+      float* fb = fold.data() + (size_t)(f % n_lanes) * FOLD_WORDS;
+      memcpy(bsm->norm, fb, FOLD_WORDS * sizeof(float));
+      celt_bands_frame(tm, bsm, f, bp, true);
+      memcpy(fb, bsm->norm, FOLD_WORDS * sizeof(float));
+    }
   }
   delete bsm;
   ImdctSmem* ism = new ImdctSmem;
@@ -70,7 +78,7 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   TailParams tp;
   tp.rec = rec.data(); tp.meta = meta.data(); tp.pkt_map = nullptr; tp.lane_stream = nullptr; tp.st_all = st.data(); tp.hist = hist.data();
   tp.series = series.data(); tp.series_stride = series_stride; tp.n_lanes = n_lanes; tp.n_ticks = n_ticks; tp.CC = CC;
-  tp.gain = 1.f; tp.apply_gain = 0; tp.pcm_f32 = out; tp.pcm_stride = pcm_stride;
+  tp.gain = 1.f; tp.apply_gain = 0; tp.pcm_f32 = out; tp.pcm_stride = pcm_stride; tp.xbuf = xbuf.data();
   // SILK-only packets (k_silk): lane per stream, ticks in order
   {
     std::vector<SilkState> sst(n_lanes);
@@ -85,7 +93,12 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
       for (uint32_t t = 0; t < n_ticks; t++) {
         const uint32_t f = t * n_lanes + j;
         if (!(meta[f].flags & 2u)) continue;
-        const bool hybrid = (meta[f].flags & 8u) != 0;
+        const bool hybrid = (meta[f].flags & (8u | 16u)) != 0;   // a CELT frame shares the row: float row
+        if (meta[f].flags & 32u) {
+          silk_state_reset(sst[j], 0);
+          silk_ring_clear(W->hist[0], W->pos[0]); silk_ring_clear(W->hist[1], W->pos[1]);
+          side_live = 1;
+        }
         const uint32_t* rb = rec.data() + rec_index(f, 0);
         const bool hyb_layout = ((rb[S_STATUS * 32] >> 17) & 3u) != 0;   // hybrid, or SILK-only with the CELT fade-out record
         SilkPcmOut o;
@@ -104,6 +117,8 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   delete csm;
   for (uint32_t j = 0; j < n_lanes; j++)
     for (int c = 0; c < CC; c++) celt_deemph_lane(j, c, tp);
+  for (uint32_t f = 0; f < F; f++)
+    for (int c = 0; c < CC; c++) celt_fade_cell(f, c, tp);
   if (pcm16) {
     for (uint32_t j = 0; j < n_lanes; j++)
       for (uint32_t t = 0; t < n_ticks; t++) {

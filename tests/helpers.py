@@ -118,11 +118,12 @@ def silk_toc(bandwidth: int, size_code: int, stereo: bool) -> int:
     return ((4 * bandwidth + size_code) << 3) | (4 if stereo else 0)
 
 
-def silk_fuzz_grid(n_lanes: int, n_ticks: int, payload, toc_fn, seed: int = 1, channels: int = 2):
+def silk_fuzz_grid(n_lanes: int, n_ticks: int, payload, toc_fn, seed: int = 1, channels: int = 2, redundancy: bool = False):
     """Like fuzz_grid, for SILK-only TOCs, keeping only packets WITHOUT a redundancy frame: in SILK-only mode any
     packet with >= 17 unread bits after the SILK payload carries a CELT redundancy frame (opus_decoder.rs:746-759),
     an arm the CUDA path reports as unimplemented. The entropy decode is state-free, so candidates are probed one by
-    one with a fresh oracle decoder. toc_fn(k, rng) -> TOC byte for the k-th candidate."""
+    one with a fresh oracle decoder. toc_fn(k, rng) -> TOC byte for the k-th candidate. redundancy=True keeps those
+    packets too (whatever decodes on a fresh decoder)."""
     lib = oracle_lib()
     rng = np.random.default_rng(seed)
     need = n_lanes * n_ticks
@@ -138,7 +139,7 @@ def silk_fuzz_grid(n_lanes: int, n_ticks: int, payload, toc_fn, seed: int = 1, c
         r = lib.orc_decode_float(h, ptr(pkt), len(pkt), ptr(pcm), 2880, 0)
         red = lib.orc_last_redundancy(h)
         lib.orc_destroy(h)
-        if r > 0 and not red:
+        if r > 0 and (redundancy or not red):
             pkts.append(pkt)
         assert k < 200 * need, "payload range leaves too many packets with redundancy"
     offsets = np.zeros(need + 1, dtype=np.uint32)

@@ -166,11 +166,11 @@ def test_gpu_unsupported_packets_report_per_packet_codes():
     from mousiki_b200 import BatchDecoder, pack_packets
 
     good = bytes([helpers.celt_toc(3, True)]) + bytes(helpers.lcg_bytes(1, 100))
-    silk = bytes([helpers.silk_toc(2, 1, False)]) + bytes(300)  # SILK WB 20 ms, spare bits: carries a CELT redundancy frame
+    silk = bytes([helpers.silk_toc(2, 2, False)]) + bytes(300)  # SILK WB 40 ms with a CELT redundancy frame: no room in the cell
     code1 = bytes([helpers.celt_toc(2, False), 0x55])  # one payload byte: a concealment frame (src/opus_decoder.rs:491)
     arena, offsets = pack_packets([good, silk, code1, good])
     with BatchDecoder(4, 48000, 2) as dec:
-        pcm, samples, rng = dec.decode_float(arena, offsets, np.arange(4, dtype=np.uint32), 960)
+        pcm, samples, rng = dec.decode_float(arena, offsets, np.arange(4, dtype=np.uint32), 1920)
     assert samples[0] == 960 and samples[3] == 960
     assert samples[1] == -5 and samples[2] == -5
     assert np.array_equal(pcm[0], pcm[3]) and rng[0] == rng[3]

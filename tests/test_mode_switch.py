@@ -1,0 +1,145 @@
+"""Mode switches with redundancy: SILK-only packets that end in a 5 ms CELT
+redundancy frame (opus_decoder.rs:746-797, 1012-1080, smooth_fade :100-135), which is how an Opus stream moves between
+CELT-only and SILK-only without concealment: CELT -> SILK plays the redundancy frame in front of the SILK audio and
+cross-fades, SILK -> CELT resets the CELT decoder, decodes the frame and cross-fades the end of the row into it; the
+next CELT-only packet then needs no transition. final_range = SILK range ^ redundancy range.
+
+Corpus: `TOC || random bytes` with redundancy-carrying packets kept (in SILK-only mode every packet with >= 17 spare
+bits carries one). CPU: host emulation of the kernel bodies against the oracle, bit for bit. GPU (-m gpu): the CUDA path
+through the C ABI. Switches that still need concealment (no redundancy) are reported as -5 by both."""
+import os
+
+import numpy as np
+import pytest
+
+import helpers
+from test_hybrid_parity import hyb_toc
+
+TOL = 1.0 / 32768.0
+
+
+def _n_redundant(arena, offsets, ch):
+    lib = helpers.oracle_lib()
+    n = 0
+    pcm = np.zeros(2880 * 2, dtype=np.float32)
+    for p in range(len(offsets) - 1):
+        pkt = arena[offsets[p]:offsets[p + 1]]
+        h = lib.orc_create(48000, ch, helpers.QUIRKS_MOUSIKI)
+        lib.orc_decode_float(h, helpers.ptr(pkt), len(pkt), helpers.ptr(pcm), 2880, 0)
+        n += int(lib.orc_last_redundancy(h))
+        lib.orc_destroy(h)
+    return n
+
+
+SILK_CASES = [
+    ("wb 20 ms mono", lambda k, r: helpers.silk_toc(2, 1, False), (20, 120), 1, 1),
+    ("wb 20 ms stereo", lambda k, r: helpers.silk_toc(2, 1, True), (30, 150), 2, 2),
+    ("nb 10 ms mixed", lambda k, r: helpers.silk_toc(0, 0, bool(r.integers(0, 2))), (8, 80), 2, 3),
+    ("mb 20 ms stereo into mono", lambda k, r: helpers.silk_toc(1, 1, True), (20, 100), 1, 4),
+]
+
+
+@pytest.mark.parametrize("name,toc,payload,ch,seed", SILK_CASES, ids=[c[0] for c in SILK_CASES])
+def test_emul_silk_streams_with_redundancy_frames(name, toc, payload, ch, seed):
+    lanes, ticks = 8, 7
+    arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, payload, toc, seed=seed, channels=ch, redundancy=True)
+    assert _n_redundant(arena, offsets, ch) >= 5, "corpus must carry redundancy frames"
+    for i16 in (False, True):
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 960, i16=i16)
+        pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, ticks, ch, 960, i16=i16)
+        assert (so > 0).all()
+        assert np.array_equal(so, se) and np.array_equal(ro, re) and np.array_equal(po, pe)
+
+
+def _any_toc(k, r):
+    m = int(r.integers(0, 10))
+    if m < 4:
+        return helpers.celt_toc(int(r.integers(1, 4)), bool(r.integers(0, 2)), int(r.integers(0, 4)))
+    if m < 9:
+        return helpers.silk_toc(int(r.integers(0, 3)), int(r.integers(0, 2)), bool(r.integers(0, 2)))
+    return hyb_toc(r.integers(0, 2), r.integers(0, 2), r.integers(0, 2))
+
+
+def _compare_until_first_rejection(so, se, ro, re, po, pe, lanes, ticks, tol):
+    """Per stream: everything equal up to the first packet either side rejects. The oracle rejects exactly the switches
+    that need concealment (and may have touched its SILK state by then, opus_decoder.rs:694-809); the product rejects
+    those plus the combinations it has no room for (hybrid packets with redundancy, redundancy right after hybrid)."""
+    so2, se2 = so.reshape(ticks, lanes), se.reshape(ticks, lanes)
+    checked = switches = 0
+    for j in range(lanes):
+        for t in range(ticks):
+            f = t * lanes + j
+            if so2[t, j] < 0 or se2[t, j] < 0:
+                assert se2[t, j] < 0, "the product decoded a packet the reference path rejects"
+                break
+            assert so2[t, j] == se2[t, j] and ro[f] == re[f], (j, t)
+            err = float(np.abs(po[f].astype(np.float64) - pe[f].astype(np.float64)).max())
+            assert err <= tol, (j, t, err)
+            checked += 1
+    return checked
+
+
+def test_emul_streams_switching_between_celt_silk_and_hybrid():
+    lanes, ticks = 16, 12
+    total = 0
+    for ch in (1, 2):
+        for seed in (1, 2, 3):
+            arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, (20, 140), _any_toc, seed=seed, channels=ch, redundancy=True)
+            po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 960)
+            pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, ticks, ch, 960)
+            total += _compare_until_first_rejection(so, se, ro, re, po, pe, lanes, ticks, 0.0)
+    assert total > 200
+
+
+def test_emul_parallel_band_pass_is_exact_for_celt_only_streams():
+    """Small calls run CELT-only frames through the all-at-once band pass (MB_EMUL_PARALLEL_BANDS selects it in the
+    emulation; the default there is the per-stream pass of large calls)."""
+    arena, offsets = helpers.fuzz_grid(6, 5, (20, 200), lambda t, j, r: helpers.celt_toc(int(r.integers(0, 4)), bool(r.integers(0, 2))), seed=3)
+    po, so, ro = helpers.oracle_decode_grid(arena, offsets, 6, 5, 2, 960)
+    os.environ["MB_EMUL_PARALLEL_BANDS"] = "1"
+    try:
+        pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, 6, 5, 2, 960)
+    finally:
+        del os.environ["MB_EMUL_PARALLEL_BANDS"]
+    assert np.array_equal(so, se) and np.array_equal(ro, re) and np.array_equal(po, pe)
+
+
+# ---------------------------------------------------------------------------------------------- GPU
+def _decode_gpu(arena, offsets, lanes, ticks, ch, frame_size, i16, **kw):
+    from mousiki_b200 import BatchDecoder
+
+    ids = np.tile(np.arange(lanes, dtype=np.uint32), ticks)
+    with BatchDecoder(lanes, 48000, ch, **kw) as dec:
+        if i16:
+            return dec.decode(arena, offsets, ids, frame_size)
+        return dec.decode_float(arena, offsets, ids, frame_size)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,toc,payload,ch,seed", SILK_CASES, ids=[c[0] for c in SILK_CASES])
+def test_gpu_silk_streams_with_redundancy_frames(name, toc, payload, ch, seed):
+    lanes, ticks = 48, 6
+    arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, payload, toc, seed=seed + 10, channels=ch, redundancy=True)
+    for i16 in (False, True):
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 960, i16=i16)
+        pg, sg, rg = _decode_gpu(arena, offsets, lanes, ticks, ch, 960, i16)
+        assert np.array_equal(so, sg) and np.array_equal(ro, rg)
+        if i16:
+            assert int(np.abs(po.astype(np.int32) - pg.astype(np.int32)).max()) <= 1
+        else:
+            assert float(np.abs(po - pg).max()) <= TOL
+
+
+@pytest.mark.gpu
+def test_gpu_streams_switching_between_celt_silk_and_hybrid(monkeypatch):
+    """The per-stream band pass (what large calls use; forced here for a small one) keeps the fold buffer exact across
+    CELT-only, redundancy and hybrid frames of one stream."""
+    monkeypatch.setenv("MOUSIKI_B200_SERIAL_BANDS", "1")
+    lanes, ticks = 64, 12
+    total = 0
+    for ch in (1, 2):
+        arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, (20, 140), _any_toc, seed=20 + ch, channels=ch, redundancy=True)
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 960)
+        pg, sg, rg = _decode_gpu(arena, offsets, lanes, ticks, ch, 960, False)
+        total += _compare_until_first_rejection(so, sg, ro, rg, po, pg, lanes, ticks, TOL)
+    assert total > 300

@@ -66,12 +66,12 @@ def test_emul_silk_quirk_switches_follow_the_oracle():
 
 
 def test_emul_silk_redundancy_and_mode_switch_are_reported_not_decoded():
-    """A SILK-only packet with >= 17 spare bits carries a CELT redundancy frame; SILK<->CELT switches go through
-    concealment. Both are next-round rows: the packet must come back as OPUS_UNIMPLEMENTED (-5) and leave the stream
-    exactly where it was."""
+    """A 40 ms SILK-only packet with a CELT redundancy frame (the cell has room for the CELT record only next to ONE SILK
+    frame; 10 / 20 ms packets with redundancy decode, tests/test_mode_switch.py) and a SILK -> CELT switch without
+    redundancy (concealment): both must come back as OPUS_UNIMPLEMENTED (-5) and leave the stream exactly where it was."""
     lanes = 2
     good, goff = _corpus(2, 1, False, 1, (8, 40), 31, lanes, 2)
-    long_pkt = np.concatenate([[helpers.silk_toc(2, 1, False)], np.zeros(300, dtype=np.uint8)]).astype(np.uint8)  # zeros: few bits used
+    long_pkt = np.concatenate([[helpers.silk_toc(2, 2, False)], np.zeros(300, dtype=np.uint8)]).astype(np.uint8)  # 40 ms, zeros: few bits used
     celt_pkt = np.concatenate([[helpers.celt_toc(3, False)], helpers.lcg_bytes(5, 60)]).astype(np.uint8)
     pk = lambda p: good[goff[p]:goff[p + 1]]
     rows = [[pk(0), pk(1)], [long_pkt, celt_pkt], [pk(2), pk(3)]]
@@ -79,14 +79,14 @@ def test_emul_silk_redundancy_and_mode_switch_are_reported_not_decoded():
     offsets = np.zeros(len(flat) + 1, dtype=np.uint32)
     offsets[1:] = np.cumsum([len(p) for p in flat])
     arena = np.concatenate(flat)
-    pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, 3, 1, 960, i16=True)
+    pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, 3, 1, 1920, i16=True)
     assert se.tolist() == [960, 960, -5, -5, 960, 960]
     # reference run without the two rejected packets
     flat2 = rows[0] + rows[2]
     off2 = np.zeros(len(flat2) + 1, dtype=np.uint32)
     off2[1:] = np.cumsum([len(p) for p in flat2])
-    po, so, ro = helpers.oracle_decode_grid(np.concatenate(flat2), off2, lanes, 2, 1, 960, i16=True)
-    assert np.array_equal(po[2:], pe[4:]) and np.array_equal(ro[2:], re[4:])
+    po, so, ro = helpers.oracle_decode_grid(np.concatenate(flat2), off2, lanes, 2, 1, 1920, i16=True)
+    assert np.array_equal(po[2:, :960], pe[4:, :960]) and np.array_equal(ro[2:], re[4:])
 
 
 # ---------------------------------------------------------------------------------------------- GPU
