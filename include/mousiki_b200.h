@@ -73,7 +73,10 @@ const char* bd_last_error(const bd_handle* h);
  * Opus error code; final_range_out[p] = Decoder::final_range() after that packet. Returns BD_OK or an API error.
  * Packets with several frames (TOC codes 1-3, padding: opus_packet_parse_impl, src/packet.rs:316-498) are cut into
  * frames on the host; the frames of a packet run in consecutive ticks of the stream and fill the packet's row in
- * order; a frame that fails ends the packet with its code, as the frame loop of src/opus_decoder.rs:1339-1350 does. */
+ * order; a frame that fails ends the packet with its code, as the frame loop of src/opus_decoder.rs:1339-1350 does.
+ * Mode switches: SILK-only packets (10 / 20 ms) with a CELT redundancy frame and the hybrid -> SILK-only fade-out decode
+ * (src/opus_decoder.rs:746-797, 868-893, 1012-1080); hybrid or 40 / 60 ms SILK packets with a redundancy frame and
+ * switches that need a concealed frame of the old mode come back as BD_OPUS_UNIMPLEMENTED with the stream untouched. */
 int bd_decode_f32(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
                   const uint8_t* flags, float* pcm, uint32_t pcm_stride, int32_t* samples_out, uint32_t* final_range_out);
 /* Decoder::decode / opus_decode (i16: soft clip + round; src/codec.rs:843-859, src/opus_decoder.rs:1632-1715). */
