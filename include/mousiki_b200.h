@@ -103,6 +103,17 @@ typedef struct bd_stream_info {
 } bd_stream_info;
 int bd_get_stream_info(bd_handle* h, uint32_t stream_id, bd_stream_info* out);
 
+/* Packet queries without a decoder (src/packet.rs:30-56, 177-280; `Decoder::packet_samples`, src/codec.rs:838): host-only
+ * byte work on the packet the caller holds. Each returns the value or a negative Opus error code: BD_OPUS_BAD_ARG for an
+ * empty packet (or len == 0 / len > avail for the frame count), BD_OPUS_INVALID_PACKET for a code-3 packet without its
+ * count byte or a packet longer than 120 ms. `avail` is the slice length, `len` the `len` argument of the reference. */
+int bd_packet_get_mode(const uint8_t* packet, uint32_t avail);                 /* 1000 SILK, 1001 hybrid, 1002 CELT */
+int bd_packet_get_bandwidth(const uint8_t* packet, uint32_t avail);            /* 1101 NB .. 1105 FB (Bandwidth::to_opus_int) */
+int bd_packet_get_nb_channels(const uint8_t* packet, uint32_t avail);
+int bd_packet_get_samples_per_frame(const uint8_t* packet, uint32_t avail, uint32_t fs_hz);
+int bd_packet_get_nb_frames(const uint8_t* packet, uint32_t avail, uint32_t len);
+int bd_packet_get_nb_samples(const uint8_t* packet, uint32_t avail, uint32_t len, uint32_t fs_hz);
+
 /* Pinned host memory helpers so that a host language can stage packets/PCM for full-rate PCIe copies. */
 void* bd_alloc_pinned(uint64_t bytes);
 void bd_free_pinned(void* p);

@@ -24,6 +24,8 @@ OPUS_BAD_ARG, OPUS_BUFFER_TOO_SMALL, OPUS_INTERNAL_ERROR, OPUS_INVALID_PACKET, O
 EXPORTS = [
     "bd_create", "bd_destroy", "bd_reset_streams", "bd_last_error", "bd_decode_f32", "bd_decode_i16", "bd_decode_grid_dev",
     "bd_get_stream_info", "bd_alloc_pinned", "bd_free_pinned", "bd_last_launch_count", "bd_debug_capture", "bd_profile_enable", "bd_profile_read",
+    "bd_packet_get_mode", "bd_packet_get_bandwidth", "bd_packet_get_nb_channels", "bd_packet_get_samples_per_frame", "bd_packet_get_nb_frames",
+    "bd_packet_get_nb_samples",
 ]
 
 
@@ -73,6 +75,11 @@ def load_library():
     lib.bd_debug_capture.argtypes = [vp, vp, vp, C.c_uint32]
     lib.bd_profile_enable.argtypes = [vp, C.c_int]
     lib.bd_profile_read.argtypes = [vp, vp, vp]
+    for name in ("bd_packet_get_mode", "bd_packet_get_bandwidth", "bd_packet_get_nb_channels"):
+        getattr(lib, name).argtypes = [C.c_char_p, C.c_uint32]
+    lib.bd_packet_get_samples_per_frame.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32]
+    lib.bd_packet_get_nb_frames.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32]
+    lib.bd_packet_get_nb_samples.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.c_uint32]
     _lib = lib
     return lib
 
@@ -213,3 +220,47 @@ class BatchDecoder:
         self._check(self._lib.bd_get_stream_info(self._h, int(stream_id), C.byref(info)), "bd_get_stream_info")
         return {"final_range": info.final_range, "last_packet_duration": info.last_packet_duration, "prev_mode": info.prev_mode,
                 "celt_error": info.celt_error}
+
+
+# ---- packet queries without a decoder (src/packet.rs:30-56, 177-280; Decoder::packet_samples, src/codec.rs:838) --------------
+class PacketError(ValueError):
+    """PacketError of the reference: .code is the Opus error code (-1 BadArgument, -4 InvalidPacket)."""
+
+    def __init__(self, code):
+        super().__init__({-1: "BadArgument", -4: "InvalidPacket"}.get(code, f"error {code}"))
+        self.code = code
+
+
+def _query(name, packet, *args):
+    packet = bytes(packet)
+    r = getattr(load_library(), name)(packet, len(packet), *args)
+    if r < 0:
+        raise PacketError(r)
+    return r
+
+
+def packet_get_mode(packet):
+    """-> 1000 SILK, 1001 hybrid, 1002 CELT (opus_packet_get_mode)."""
+    return _query("bd_packet_get_mode", packet)
+
+
+def packet_get_bandwidth(packet):
+    """-> 1101 narrow .. 1105 full (opus_packet_get_bandwidth, Bandwidth::to_opus_int)."""
+    return _query("bd_packet_get_bandwidth", packet)
+
+
+def packet_get_nb_channels(packet):
+    return _query("bd_packet_get_nb_channels", packet)
+
+
+def packet_get_samples_per_frame(packet, fs_hz=48000):
+    return _query("bd_packet_get_samples_per_frame", packet, int(fs_hz))
+
+
+def packet_get_nb_frames(packet, length=None):
+    return _query("bd_packet_get_nb_frames", packet, len(packet) if length is None else int(length))
+
+
+def packet_get_nb_samples(packet, length=None, fs_hz=48000):
+    """Samples per channel the packet decodes to (opus_packet_get_nb_samples; `Decoder::packet_samples` at the decoder's rate)."""
+    return _query("bd_packet_get_nb_samples", packet, len(packet) if length is None else int(length), int(fs_hz))

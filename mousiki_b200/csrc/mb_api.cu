@@ -736,6 +736,52 @@ int bd_get_stream_info(bd_handle* h, uint32_t sid, bd_stream_info* out) {
   return BD_OK;
 }
 
+// ---- packet queries (src/packet.rs:30-56, 177-280): host-only, no decoder and no device involved
+int bd_packet_get_mode(const uint8_t* pkt, uint32_t avail) {
+  if (!pkt || !avail) return BD_OPUS_BAD_ARG;
+  const uint8_t toc = pkt[0];
+  return toc & 0x80 ? 1002 : (toc & 0x60) == 0x60 ? 1001 : 1000;
+}
+int bd_packet_get_bandwidth(const uint8_t* pkt, uint32_t avail) {
+  if (!pkt || !avail) return BD_OPUS_BAD_ARG;
+  const uint8_t toc = pkt[0];
+  const int two = (toc >> 5) & 3;
+  if (toc & 0x80) return two == 0 ? 1101 : 1102 + two;          // CELT has no medium band
+  if ((toc & 0x60) == 0x60) return toc & 0x10 ? 1105 : 1104;    // hybrid: SWB or FB
+  return 1101 + two;
+}
+int bd_packet_get_nb_channels(const uint8_t* pkt, uint32_t avail) {
+  if (!pkt || !avail) return BD_OPUS_BAD_ARG;
+  return pkt[0] & 0x04 ? 2 : 1;
+}
+int bd_packet_get_samples_per_frame(const uint8_t* pkt, uint32_t avail, uint32_t fs_hz) {
+  if (!pkt || !avail) return BD_OPUS_BAD_ARG;
+  const uint8_t toc = pkt[0];
+  const uint32_t size = (toc >> 3) & 3;
+  uint64_t n;
+  if (toc & 0x80) n = ((uint64_t)fs_hz << size) / 400;
+  else if ((toc & 0x60) == 0x60) n = toc & 0x08 ? fs_hz / 50 : fs_hz / 100;
+  else n = size == 3 ? (uint64_t)fs_hz * 60 / 1000 : ((uint64_t)fs_hz << size) / 100;
+  return n > 0x7fffffffu ? BD_OPUS_BAD_ARG : (int)n;
+}
+int bd_packet_get_nb_frames(const uint8_t* pkt, uint32_t avail, uint32_t len) {
+  if (!pkt || len == 0 || len > avail) return BD_OPUS_BAD_ARG;
+  const int code = pkt[0] & 3;
+  if (code == 0) return 1;
+  if (code != 3) return 2;
+  if (len < 2) return BD_OPUS_INVALID_PACKET;
+  return pkt[1] & 0x3f;
+}
+int bd_packet_get_nb_samples(const uint8_t* pkt, uint32_t avail, uint32_t len, uint32_t fs_hz) {
+  const int count = bd_packet_get_nb_frames(pkt, avail, len);
+  if (count < 0) return count;
+  const int per = bd_packet_get_samples_per_frame(pkt, avail, fs_hz);
+  if (per < 0) return per;
+  const uint64_t samples = (uint64_t)count * (uint64_t)per;
+  if (samples * 25 > (uint64_t)fs_hz * 3) return BD_OPUS_INVALID_PACKET;   // more than 120 ms
+  return (int)samples;
+}
+
 int bd_profile_enable(bd_handle* h, int on) {
   if (!h) return BD_ERR_BAD_ARG;
   h->prof_on = on != 0;
