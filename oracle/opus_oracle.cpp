@@ -438,6 +438,8 @@ void orc_silk_nlsf_decode(int wb, const int8_t* indices, int16_t* nlsf_q15, uint
 void orc_silk_nlsf2a(const int16_t* nlsf_q15, int order, int16_t* a_q12, uint32_t quirks) { silk_nlsf2a(a_q12, nlsf_q15, order, quirks); }
 int32_t orc_silk_inverse_pred_gain(const int16_t* a_q12, int order) { return order == 0 ? 1 << 30 : silk_lpc_inverse_pred_gain(a_q12, order); }
 int32_t orc_silk_log2lin(int32_t x) { return silk_log2lin(x); }
+// opus_pcm_soft_clip (src/opus.rs:16-150) on its own, for the known answers of src/opus.rs:157-208
+void orc_pcm_soft_clip(float* pcm, int frame_size, int channels, float* softclip_mem) { OpusDecoder::pcm_soft_clip(pcm, frame_size, channels, softclip_mem); }
 int orc_silk_gains_dequant(const int8_t* ind, int prev, int conditional, int nb_subfr, int32_t* gains) {
   int8_t p = (int8_t)prev;
   silk_gains_dequant(gains, ind, &p, conditional, nb_subfr);

@@ -66,3 +66,25 @@ def test_every_celt_toc_decodes():
                 ret = lib.orc_decode_float(h, helpers.ptr(pkt), len(pkt), helpers.ptr(out), 5760, 0)
                 assert ret == 120 << (cfg & 3), (cfg, stereo, fill, ret)
     lib.orc_destroy(h)
+
+
+def test_soft_clip_known_answers():
+    """src/opus.rs:157-208 — the four soft-clip cases of the reference (in range, a clipped peak, a carried
+    non-linearity that ends at the zero crossing, a ramp before the first zero crossing)."""
+    import ctypes as C
+    lib = helpers.oracle_lib()
+    lib.orc_pcm_soft_clip.restype = None
+
+    def clip(pcm, n, c, mem):
+        pcm, mem = np.array(pcm, dtype=np.float32), np.array(mem, dtype=np.float32)
+        lib.orc_pcm_soft_clip(C.c_void_p(pcm.ctypes.data), n, c, C.c_void_p(mem.ctypes.data))
+        return pcm, mem
+
+    pcm, mem = clip([0.1, -0.6, 0.9, 0.3], 2, 2, [0.5, -0.25])
+    assert np.array_equal(pcm, np.array([0.1, -0.6, 0.9, 0.3], dtype=np.float32)) and np.array_equal(mem, [0.0, 0.0])
+    pcm, mem = clip([2.0], 1, 1, [0.0])
+    assert abs(pcm[0] - 0.99999976) < 1e-7 and abs(mem[0] + 0.25000006) < 1e-7
+    pcm, mem = clip([0.5, 0.25, -0.25], 3, 1, [-0.25])
+    assert np.abs(pcm - np.array([0.4375, 0.234375, -0.25])).max() < 1e-6 and mem[0] == 0.0
+    pcm, mem = clip([0.5, 1.5, 1.7, -0.4], 4, 1, [0.0])
+    assert np.abs(pcm[[0, 1, 3]] - np.array([0.46972317, 0.9550162, -0.4])).max() < 1e-6 and abs(pcm[2] - 1.0) < 2e-6 and mem[0] == 0.0
