@@ -70,18 +70,27 @@ def main():
     from mousiki_b200 import BatchDecoder
 
     ap = argparse.ArgumentParser()
-    ap.add_argument("--streams", type=int, default=100_000)
+    ap.add_argument("--streams", type=int, default=100_000, help="streams of the whole job; a torchrun launch shards them by rank")
     ap.add_argument("--ticks", type=int, default=4)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     args = ap.parse_args()
-    dev = torch.device("cuda", 0)
-    torch.cuda.set_device(0)
-    streams, ticks = args.streams, args.ticks
+    sys.stdout.flush()
+    result_fd = os.dup(1)  # stdout carries the JSON line only (NCCL prints its version banner on descriptor 1)
+    os.dup2(2, 1)
+    import torch.distributed as dist
+    world, rank, local = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", "1"), ("RANK", "0"), ("LOCAL_RANK", "0")))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(local)
+    if world > 1:  # streams are independent: rank r owns streams r, r + world, ... and there is no data-path collective
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    streams, ticks = len(range(rank, args.streams, world)), args.ticks
+    streams -= streams % 2  # CELT / SILK pairs
     n = streams * ticks
     pool = pools(11)
-    arena, offsets = corpus(streams, ticks, pool, 5)
-    dec = BatchDecoder(streams, 48000, CH, device=0)
+    arena, offsets = corpus(streams, ticks, pool, 5 + 100 * rank)
+    dec = BatchDecoder(streams, 48000, CH, device=local)
     # parity gate: the first 128 streams (64 CELT, 64 SILK), every tick, f32 and the sample counts
     cs = 128
     sel = (np.arange(ticks)[:, None] * streams + np.arange(cs)[None, :]).reshape(-1)
@@ -111,6 +120,9 @@ def main():
     for _ in range(args.warmup):
         step()
     torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
     dec.profile(True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
@@ -120,10 +132,20 @@ def main():
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
     prof = dec.profile_read()
+    job = torch.tensor([ms, 0.0, float(streams)], dtype=torch.float64, device=dev)
     assert int((d_samples <= 0).sum().item()) == 0, "a packet of the corpus was rejected"
     per_ch = d_samples.to(torch.int64)
     audio_s = float(per_ch.sum().item()) / 48000.0
     celt_s = float(per_ch.view(ticks, streams)[:, 0::2].sum().item()) / 48000.0
+    if world > 1:  # max over ranks of the device time, sum of the audio and of the streams
+        job[1] = audio_s
+        t = job[:1].clone()
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(job, op=dist.ReduceOp.SUM)
+        ms, audio_s, celt_s = float(t.item()), float(job[1].item()), celt_s * float(job[1].item()) / audio_s
+        if rank:
+            dist.destroy_process_group()
+            return
     # CPU oracle on a bounded sample, all cores
     cores = os.cpu_count() or 1
     cst = 128 * cores
@@ -141,16 +163,19 @@ def main():
         passes += 1
         cpu_audio += float(csm.clip(min=0).sum()) / 48000.0
     kms = {k: v[0] / args.steps for k, v in prof.items() if v[1]}
-    line = {"metric": "decoded_audio_seconds_per_second", "value": audio_s * args.steps / (ms * 1e-3), "unit": "audio-s/s", "n_gpus": 1,
+    line = {"metric": "decoded_audio_seconds_per_second", "value": audio_s * args.steps / (ms * 1e-3), "unit": "audio-s/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "dtype": "int32+f32",
-            "config": {"workload": "mixed_celt_2.5_5_10_20ms_fb_stereo_and_silk_wb_40_60ms", "streams": streams,
+            "config": {"workload": "mixed_celt_2.5_5_10_20ms_fb_stereo_and_silk_wb_40_60ms", "streams": int(job[2].item()) if world > 1 else streams,
+                       "streams_per_gpu": streams, "sharding": f"streams by rank, {world} rank(s), no data-path collective",
                        "packets_per_stream_per_step": ticks, "audio_s_per_step": audio_s, "celt_share_of_audio": celt_s / audio_s,
                        "mean_payload_bytes": float(lens.mean()), "output": "f32 PCM left in HBM, row stride 2880 x 2"},
             "kernel_ms_per_step": kms,
             "cpu_baseline": {"value": cpu_audio / tot, "unit": "audio-s/s", "cores": cores, "kind": "port",
                              "sample": f"{passes} passes of {cst} streams x {ticks} packets ({tot:.1f} s)"},
             "parity": parity}
-    print(json.dumps(line), flush=True)
+    os.write(result_fd, (json.dumps(line) + "\n").encode())
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
