@@ -33,8 +33,8 @@ MB_DEV int32_t s_mulhi(int32_t a, int32_t b) {
 
 // `pulse_words`: the frame's pulses in the cell record (2 x i16 per word, stride 32 words).
 // `h`/`pos`: this channel's ring; the frame is written to h[(pos + ltp_mem + n) & mask].
-MB_DEV_NOINLINE void silk_frame_core(SilkChanState& st, const SilkSide& sd, SilkFrameParams& P, const uint32_t* pulse_words, int16_t* h,
-                                     int pos, int32_t* sltp_q15) {
+MB_DEV_NOINLINE void silk_frame_core(SilkChanState& st, const SilkSide& sd, SilkFrameParams& P, const uint32_t* __restrict__ pulse_words,
+                                     int16_t* __restrict__ h, int pos, int32_t* __restrict__ sltp_q15) {
   const int fs = st.fs_khz, nb = st.nb_subfr, sub = 5 * fs, ltp_mem = 20 * fs, order = fs == 16 ? 16 : 10;
   const int32_t offset_q10 = silk_Quantization_Offsets_Q10[(sd.signal_type >> 1) * 2 + sd.quant_offset];
   const bool interp = sd.interp_q2 < 4;
@@ -60,6 +60,7 @@ MB_DEV_NOINLINE void silk_frame_core(SilkChanState& st, const SilkSide& sd, Silk
     prev_gain = gain_q16;
     int32_t B0 = 0, B1 = 0, B2 = 0, B3 = 0, B4 = 0;          // LTP taps, pre-shifted
     int32_t l0 = 0, l1 = 0, l2 = 0, l3 = 0, l4 = 0;          // sltp_q15[pl], [pl-1], .. [pl-4]
+    int32_t lnext = 0;
     int pl = 0;
     if (voiced) {
       const int lag = P.pitch_l[k];
@@ -91,10 +92,13 @@ MB_DEV_NOINLINE void silk_frame_core(SilkChanState& st, const SilkSide& sd, Silk
       const int16_t* B = P.b_q14 + 5 * k;
       B0 = s_shl(B[0], 16); B1 = s_shl(B[1], 16); B2 = s_shl(B[2], 16); B3 = s_shl(B[3], 16); B4 = s_shl(B[4], 16);
       l0 = sltp_q15[pl]; l1 = sltp_q15[pl - 1]; l2 = sltp_q15[pl - 2]; l3 = sltp_q15[pl - 3]; l4 = sltp_q15[pl - 4];
+      lnext = sltp_q15[pl + 1];   // one sample ahead of the window (written at least lag - 3 >= 13 samples ago)
     }
     const int out0 = pos + ltp_mem + k * sub;
+    uint32_t w_next = pulse_words[((k * sub) >> 1) * 32];            // two pulses per record word, fetched one step ahead
     for (int i = 0; i < sub; i += 2) {
-      const uint32_t w = pulse_words[((k * sub + i) >> 1) * 32];   // two pulses per record word
+      const uint32_t w = w_next;
+      if (i + 2 < sub) w_next = pulse_words[((k * sub + i + 2) >> 1) * 32];
 #pragma unroll
       for (int u = 0; u < 2; u++) {
         // excitation (decode_core.rs:93-111)
@@ -113,7 +117,8 @@ MB_DEV_NOINLINE void silk_frame_core(SilkChanState& st, const SilkSide& sd, Silk
           res = s_add(e, s_shl(p, 1));
           sltp_q15[sltp_idx++] = s_shl(res, 1);
           pl++;
-          l4 = l3; l3 = l2; l2 = l1; l1 = l0; l0 = sltp_q15[pl];
+          l4 = l3; l3 = l2; l2 = l1; l1 = l0; l0 = lnext;
+          lnext = sltp_q15[pl + 1];
         }
         int32_t p0 = order >> 1, p1 = 0, p2 = 0, p3 = 0;
 #pragma unroll

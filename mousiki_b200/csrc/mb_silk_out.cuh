@@ -139,14 +139,16 @@ MB_DEV_NOINLINE int silk_resample48(SilkChanState& c, const SilkSrc& in, int n_i
   int produced = 0;
   int t = 0;                         // position in the delayed input stream: res_delay[0, delay) ++ in[0, n_in - delay)
   int n = fs;                        // first batch: one millisecond
+  int32_t x_next = delay > 0 ? (int32_t)c.res_delay[0] : in.at(0);
   while (t < n_in) {
     if (n > n_in - t) n = n_in - t;
     const int32_t max_idx = n << 17;
     int32_t idx = 0;
     for (int k = -1; k < n; k++) {
       if (k >= 0) {
-        const int32_t x = t < delay ? (int32_t)c.res_delay[t] : in.at(t - delay);
+        const int32_t x = x_next;    // fetched one sample ahead: the load is off the filter's dependency chain
         t++;
+        if (t < n_in) x_next = t < delay ? (int32_t)c.res_delay[t] : in.at(t - delay);
         const int32_t in32 = x << 10;
         int32_t Y, X, o1, o2;
         Y = s_sub(in32, S0); X = s_mulhi(Y, c00); o1 = s_add(S0, X); S0 = s_add(in32, X);
