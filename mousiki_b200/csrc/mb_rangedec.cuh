@@ -17,6 +17,7 @@ struct RangeDec {
   int nend_bits;
   int nbits_total;
   uint32_t rng, val, ext;
+  uint32_t pre;          // front byte at `offs`, fetched one step ahead (0 past the end)
   int rem;
   int error;
 
@@ -32,7 +33,9 @@ struct RangeDec {
       nbits_total += 8;
       rng <<= 8;
       uint32_t prev = (uint32_t)rem;
-      rem = offs < storage ? (int)byte_at(offs++) : 0;
+      rem = (int)pre;                      // the byte was fetched when the previous one was consumed
+      if (offs < storage) offs++;
+      pre = offs < storage ? byte_at(offs) : 0u;
       uint32_t sym = ((prev << 8) | (uint32_t)rem) >> 1;
       val = ((val << 8) + (255u & ~sym)) & 0x7fffffffu;
     }
@@ -42,6 +45,7 @@ struct RangeDec {
     nbits_total = 9;  // EC_CODE_BITS + 1 - ((EC_CODE_BITS - EC_CODE_EXTRA) / EC_SYM_BITS) * EC_SYM_BITS
     rng = 128u; ext = 0; error = 0;
     rem = offs < storage ? (int)byte_at(offs++) : 0;
+    pre = offs < storage ? byte_at(offs) : 0u;
     val = rng - 1u - ((uint32_t)rem >> 1);
     renorm();
   }
