@@ -134,6 +134,13 @@ int bd_profile_read(bd_handle* h, double* ms_out, uint32_t* launches_out);
  * filled when the call returns. */
 int bd_debug_capture(bd_handle* h, int32_t* pulses_host, float* spectrum_host, uint32_t max_packets);
 
+/* Test hook: replays one of the reference's unit known-answer cases on the device functions the kernels are built from
+ * (one warp on `device`; protocol in mousiki_b200/csrc/mb_kat.cuh: 1 bitexact_cos, 2 bitexact_log2tan, 3 cwrsi,
+ * 4 comb_filter, 5 ifft, 6 frame IMDCT, 7 range-decoder script, 8 pulse cache). Reference tests replayed:
+ * src/celt/bands.rs:4805-4915, cwrs.rs:681-786, celt.rs:868-1190, kiss_fft.rs:1364-1440, mdct.rs:1746-1843,
+ * entdec.rs:327-377, src/range.rs:659-695, rate.rs:1424-1465. Host word buffers in and out. */
+int bd_debug_kat(int device, int what, const uint32_t* in, uint32_t n_in, uint32_t* out, uint32_t n_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -26,6 +26,7 @@
 #include "mb_celt_tail.cuh"
 #include "mb_frame.cuh"
 #include "mb_silk_out.cuh"
+#include "mb_kat.cuh"
 
 using namespace mb;
 
@@ -545,6 +546,15 @@ __global__ void k_silk_reset(SilkState* st, uint32_t* silk_hist, uint32_t n_stre
   for (int k = 0; k < 320; k++) silk_hist[(size_t)k * n_streams + sid] = 0;
 }
 
+// unit known-answer hook: one warp runs one case on the kernel bodies (mb_kat.cuh)
+__global__ void __launch_bounds__(32) k_kat(int what, const uint32_t* __restrict__ in, uint32_t n_in, uint32_t* out, uint32_t n_out,
+                                             uint8_t* gbytes, int* rc) {
+  __shared__ KatSmem sm;
+  Team tm = {(int)threadIdx.x, 32};
+  const int r = kat_run(tm, &sm, what, in, n_in, out, n_out, gbytes);
+  if (threadIdx.x == 0) *rc = r;
+}
+
 // ------------------------------------------------------------------------------------------ host side
 namespace {
 
@@ -804,6 +814,25 @@ int bd_debug_capture(bd_handle* h, int32_t* pulses_host, float* spectrum_host, u
   if (!h) return BD_ERR_BAD_ARG;
   h->dbg_iy_host = pulses_host; h->dbg_x_host = spectrum_host; h->dbg_max = (pulses_host || spectrum_host) ? max_packets : 0;
   return BD_OK;
+}
+
+int bd_debug_kat(int device, int what, const uint32_t* in, uint32_t n_in, uint32_t* out, uint32_t n_out) {
+  if (!in || !out) return BD_ERR_BAD_ARG;
+  if (cudaSetDevice(device) != cudaSuccess) return BD_ERR_CUDA;
+  uint32_t *d_in = nullptr, *d_out = nullptr;
+  uint8_t* d_bytes = nullptr;
+  int rc = BD_ERR_CUDA, krc = -1;
+  if (cudaMalloc(&d_in, (size_t)n_in * 4 + 4) == cudaSuccess && cudaMalloc(&d_out, (size_t)n_out * 4 + 4 + sizeof(int)) == cudaSuccess &&
+      cudaMalloc(&d_bytes, 64) == cudaSuccess && cudaMemcpy(d_in, in, (size_t)n_in * 4, cudaMemcpyHostToDevice) == cudaSuccess &&
+      cudaMemset(d_out, 0, (size_t)n_out * 4 + 4 + sizeof(int)) == cudaSuccess) {
+    int* d_rc = (int*)(d_out + n_out + 1);
+    k_kat<<<1, 32>>>(what, d_in, n_in, d_out, n_out, d_bytes, d_rc);
+    if (cudaDeviceSynchronize() == cudaSuccess && cudaMemcpy(out, d_out, (size_t)n_out * 4, cudaMemcpyDeviceToHost) == cudaSuccess &&
+        cudaMemcpy(&krc, d_rc, sizeof(int), cudaMemcpyDeviceToHost) == cudaSuccess)
+      rc = krc == 0 ? BD_OK : BD_ERR_BAD_ARG;
+  }
+  cudaFree(d_in); cudaFree(d_out); cudaFree(d_bytes);
+  return rc;
 }
 
 // One or more passes over the grid (ticks are split so that a pass holds at most max_frames_per_pass cells).

@@ -123,32 +123,11 @@ struct ImdctParams {
   int CC;
 };
 
-// Unit u of frame f: coded channel u when both the packet and the decoder are stereo, else the single (down-mixed or
-// duplicated) spectrum.
-MB_DEV void celt_imdct_unit(Team tm, ImdctSmem* sm, uint32_t f, int u, const ImdctParams& P) {
-  const FrameMeta meta = P.meta[f];
-  if (!(meta.flags & 1u)) return;
-  const uint32_t* r = P.rec + rec_index(f, 0);
-  const uint32_t h0 = r[S_HDR0 * 32], status = r[S_STATUS * 32];
-  const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), start = (int)MB_H0_START(h0), end = (int)MB_ST_END(status);
-  const int transient = (int)MB_H0_TRANSIENT(h0), silence = (int)MB_H0_SILENCE(h0);
-  const int M = 1 << lm, N = M * SHORT_MDCT, CC = P.CC;
-  const int nch = (CC == 2 && C == 2) ? 2 : 1;
-  if (u >= nch) return;
-  const float* xrow = P.xbuf + (size_t)f * XBUF_STRIDE;
-  const int planned = r[S_PLAN * 32] != 0xffffffffu;
-  const int lo = (silence || !planned) ? 0 : M * eband(start), hi = (silence || !planned) ? 0 : M * eband(imin(end, NB_EBANDS));
-  const int downmix = CC == 1 && C == 2;
+// The transform itself, in place on sm->io: N = 120 << lm frequency bins in (short blocks interleaved as the band pass
+// leaves them), N time-domain samples out (clt_mdct_backward against the reference's zero-filled overlap).
+MB_DEV void celt_imdct_core(Team tm, ImdctSmem* sm, int lm, int transient) {
+  const int M = 1 << lm, N = M * SHORT_MDCT;
   float* X = sm->io;
-  for (int i = tm.tid; i < N; i += tm.n) {
-    float v = 0.f;
-    if (i >= lo && i < hi) {
-      v = xrow[u * N + i];
-      if (downmix) v = 0.5f * (v + xrow[N + i]);
-    }
-    X[i] = v;
-  }
-  MB_SYNC();
   const int nbk = transient ? M : 1;                  // short blocks
   const int shift = transient ? MAX_LM : MAX_LM - lm;
   const int n2 = 960 >> shift, n4 = n2 >> 1;          // per-block MDCT size / FFT size
@@ -194,6 +173,36 @@ MB_DEV void celt_imdct_unit(Team tm, ImdctSmem* sm, uint32_t f, int u, const Imd
     }
   }
   MB_SYNC();
+}
+
+// Unit u of frame f: coded channel u when both the packet and the decoder are stereo, else the single (down-mixed or
+// duplicated) spectrum.
+MB_DEV void celt_imdct_unit(Team tm, ImdctSmem* sm, uint32_t f, int u, const ImdctParams& P) {
+  const FrameMeta meta = P.meta[f];
+  if (!(meta.flags & 1u)) return;
+  const uint32_t* r = P.rec + rec_index(f, 0);
+  const uint32_t h0 = r[S_HDR0 * 32], status = r[S_STATUS * 32];
+  const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), start = (int)MB_H0_START(h0), end = (int)MB_ST_END(status);
+  const int transient = (int)MB_H0_TRANSIENT(h0), silence = (int)MB_H0_SILENCE(h0);
+  const int M = 1 << lm, N = M * SHORT_MDCT, CC = P.CC;
+  const int nch = (CC == 2 && C == 2) ? 2 : 1;
+  if (u >= nch) return;
+  const float* xrow = P.xbuf + (size_t)f * XBUF_STRIDE;
+  const int planned = r[S_PLAN * 32] != 0xffffffffu;
+  const int lo = (silence || !planned) ? 0 : M * eband(start), hi = (silence || !planned) ? 0 : M * eband(imin(end, NB_EBANDS));
+  const int downmix = CC == 1 && C == 2;
+  float* X = sm->io;
+  for (int i = tm.tid; i < N; i += tm.n) {
+    float v = 0.f;
+    if (i >= lo && i < hi) {
+      v = xrow[u * N + i];
+      if (downmix) v = 0.5f * (v + xrow[N + i]);
+    }
+    X[i] = v;
+  }
+  MB_SYNC();
+  celt_imdct_core(tm, sm, lm, transient);
+  float* O = X;
   const float SIG_SAT = 536870911.0f;
   for (int cc = 0; cc < CC; cc++) {
     if (nch == 2 && cc != u) continue;

@@ -1552,3 +1552,114 @@ int celt_decode_with_ec(CeltDecoder* st, const uint8_t* data, int len, float* pc
 }
 
 }  // namespace orc
+
+// ---------------------------------------------------------------- unit known-answer hooks (tests/test_unit_kat.py)
+// One word-array entry point over the building blocks above, so that the reference's unit tests for this path can be
+// replayed on the oracle; the product's kernel bodies answer the same protocol through tests/emul (CPU) and
+// bd_debug_kat (GPU). Floats travel as their bit patterns.
+//   1 bitexact_cos            in x[n]                              out cos[n]                 bands.rs:4805-4831
+//   2 bitexact_log2tan        in (isin, icos)[n]                   out v[n]                   bands.rs:4836-4884
+//   3 cwrsi                   in n, k, count, inc, i0              out y[count][n]            cwrs.rs:681-786
+//   4 comb_filter_in_place    in n, T0, T1, tap0, tap1, g0, g1, hist, x[hist + n]   out x'[n] celt.rs:868-1190
+//   5 ifft (480 >> shift)     in shift, cpx[nfft]                  out cpx[nfft]              kiss_fft.rs:1364-1440
+//   6 frame IMDCT             in lm, transient, freq[N]            out time[N]                mdct.rs:1746-1843
+//   7 range decoder script    in len, bytes[len] (one per word), ops (op, a, b)[..]           out one word per op
+//        op 0 bit_logp(a)  1 icdf(table at word offset a of the input, ftb b)  2 uint(a)  3 bits(a)  4 tell  5 tell_frac
+//        6 state: rng  7 val  8 nbits_total  9 offs  10 rem  11 error  12 nend_bits     range.rs:659-695, entdec.rs:327-377
+//   8 pulse cache             in (band, lm, pulses)[n]             out (bits, bits2pulses(bits), max pulses of the row)[n]   rate.rs:1424-1465
+extern "C" int orc_kat(int what, const uint32_t* in, uint32_t n_in, uint32_t* out, uint32_t n_out) {
+  using namespace orc;
+  init_tables_once();
+  auto F = [](uint32_t w) { return bits2f(w); };
+  auto U = [](float f) { uint32_t b; memcpy(&b, &f, 4); return b; };
+  switch (what) {
+    case 1:
+      for (uint32_t i = 0; i < n_in && i < n_out; i++) out[i] = (uint32_t)bitexact_cos((int)in[i]);
+      return 0;
+    case 2:
+      for (uint32_t i = 0; 2 * i + 1 < n_in && i < n_out; i++) out[i] = (uint32_t)bitexact_log2tan((int)in[2 * i], (int)in[2 * i + 1]);
+      return 0;
+    case 3: {
+      const int n = (int)in[0], k = (int)in[1];
+      const uint32_t count = in[2], inc = in[3], i0 = in[4];
+      std::vector<int> y(n);
+      for (uint32_t j = 0; j < count && (j + 1) * n <= n_out; j++) {
+        cwrsi(n, k, i0 + j * inc, y.data());
+        for (int t = 0; t < n; t++) out[j * n + t] = (uint32_t)y[t];
+      }
+      return 0;
+    }
+    case 4: {
+      const int n = (int)in[0], T0 = (int)in[1], T1 = (int)in[2], tap0 = (int)in[3], tap1 = (int)in[4], hist = (int)in[7];
+      std::vector<float> ch(hist + n);
+      for (int i = 0; i < hist + n; i++) ch[i] = F(in[8 + i]);
+      comb_filter_in_place(ch.data(), hist, n, T0, T1, F(in[5]), F(in[6]), tap0, tap1);
+      for (int i = 0; i < n && i < (int)n_out; i++) out[i] = U(ch[hist + i]);
+      return 0;
+    }
+    case 5: {
+      const int shift = (int)in[0], nfft = 480 >> shift;
+      cpx f[480];
+      const int16_t* br = kBitrev[shift];
+      for (int i = 0; i < nfft; i++) { f[br[i]].r = F(in[1 + 2 * i]); f[br[i]].i = -F(in[2 + 2 * i]); }   // kiss_fft.rs:739-745
+      fft_impl(f, shift);
+      for (int i = 0; i < nfft; i++) { out[2 * i] = U(f[i].r); out[2 * i + 1] = U(-f[i].i); }
+      return 0;
+    }
+    case 6: {
+      const int lm = (int)in[0], transient = (int)in[1], M = 1 << lm, N = M * SHORT_MDCT;
+      int nbk, nb, shift;
+      if (transient) { nbk = M; nb = SHORT_MDCT; shift = MAX_LM; } else { nbk = 1; nb = SHORT_MDCT << lm; shift = MAX_LM - lm; }
+      std::vector<float> temp(N), o(N + OVERLAP, 0.f);
+      for (int b = 0; b < nbk; b++) {
+        for (int k = 0; k < nb; k++) temp[k] = F(in[2 + b + k * nbk]);
+        clt_mdct_backward(temp.data(), o.data() + b * nb, N + OVERLAP - b * nb, shift, true);
+      }
+      for (int i = 0; i < N && i < (int)n_out; i++) out[i] = U(o[i]);
+      return 0;
+    }
+    case 7: {
+      const uint32_t len = in[0];
+      std::vector<uint8_t> bytes(len);
+      for (uint32_t i = 0; i < len; i++) bytes[i] = (uint8_t)in[1 + i];
+      EcDec d;
+      d.init(bytes.data(), len);
+      uint32_t o = 0;
+      for (uint32_t p = 1 + len; p + 2 < n_in && o < n_out; p += 3, o++) {
+        const uint32_t op = in[p], a = in[p + 1], b = in[p + 2];
+        switch (op) {
+          case 0: out[o] = (uint32_t)d.bit_logp(a); break;
+          case 1: {
+            uint8_t tab[64];
+            for (int i = 0; i < 64 && a + i < n_in; i++) tab[i] = (uint8_t)in[a + i];
+            out[o] = (uint32_t)d.icdf(tab, b);
+          } break;
+          case 2: out[o] = d.uint(a); break;
+          case 3: out[o] = d.bits(a); break;
+          case 4: out[o] = (uint32_t)d.tell(); break;
+          case 5: out[o] = d.tell_frac(); break;
+          case 6: out[o] = d.rng; break;
+          case 7: out[o] = d.val; break;
+          case 8: out[o] = (uint32_t)d.nbits_total; break;
+          case 9: out[o] = d.offs; break;
+          case 10: out[o] = (uint32_t)d.rem; break;
+          case 11: out[o] = (uint32_t)d.error; break;
+          case 12: out[o] = (uint32_t)d.nend_bits; break;
+          default: return -1;
+        }
+      }
+      return 0;
+    }
+    case 8:
+      for (uint32_t i = 0; 3 * i + 2 < n_in && 3 * i + 2 < n_out; i++) {
+        const int band = (int)in[3 * i], lm = (int)in[3 * i + 1], pulses = (int)in[3 * i + 2];
+        const uint8_t* t = cache_row(band, lm);
+        const int bits = (t && pulses > t[0]) ? 0 : pulses2bits(band, lm, pulses);
+        out[3 * i] = (uint32_t)bits;
+        out[3 * i + 1] = (uint32_t)bits2pulses(band, lm, bits);
+        out[3 * i + 2] = t ? t[0] : 0u;
+      }
+      return 0;
+  }
+  return -1;
+}

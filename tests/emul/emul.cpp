@@ -14,10 +14,19 @@
 #include "../../mousiki_b200/csrc/mb_celt_tail.cuh"
 #include "../../mousiki_b200/csrc/mb_frame.cuh"
 #include "../../mousiki_b200/csrc/mb_silk_out.cuh"
+#include "../../mousiki_b200/csrc/mb_kat.cuh"
 
 using namespace mb;
 
 extern "C" {
+
+// unit known-answer hooks over the kernel bodies (mb_kat.cuh), team of one
+int emu_kat(int what, const uint32_t* in, uint32_t n_in, uint32_t* out, uint32_t n_out) {
+  static KatSmem sm;
+  uint8_t bytes[64];
+  Team tm = {0, 1};
+  return kat_run(tm, &sm, what, in, n_in, out, n_out, bytes);
+}
 
 // Decodes a regular [n_ticks][n_lanes] packet grid with one fresh decoder state per lane, phases in
 // the same order as the CUDA launcher. pcm: [packet][pcm_stride]. iy_dbg/x_dbg: optional [packet][2*960].

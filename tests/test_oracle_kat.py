@@ -40,18 +40,7 @@ def test_cres_serial_state_oracle():
     assert np.array_equal(r1, r2) and np.array_equal(s1, s2)
 
 
-def test_range_decoder_symbol_kat():
-    """src/range.rs:659-695 — the symbol walk over packet 0b e4 c1 36 ec c5 80 is covered indirectly by the cres KAT
-    (every coded symbol type of the CELT header goes through the same decoder); here: tell() of a fresh decoder."""
-    lib = helpers.oracle_lib()
-    # a fresh decoder on any buffer reports 1 bit consumed (entdec.rs tests :327-377 expect tell()==1)
-    arena = np.array([0xFC, 0x0B, 0xE4, 0xC1, 0x36, 0xEC, 0xC5, 0x80], dtype=np.uint8)
-    h = lib.orc_create(48000, 2, helpers.QUIRKS_MOUSIKI)
-    out = np.zeros(960 * 2, dtype=np.float32)
-    ret = lib.orc_decode_float(h, helpers.ptr(arena), len(arena), helpers.ptr(out), 960, 0)
-    assert ret == 960
-    assert lib.orc_final_range(h) != 0
-    lib.orc_destroy(h)
+# (the symbol walk of src/range.rs:659-695 and the EcDec cases of src/celt/entdec.rs:327-377: tests/test_unit_kat.py)
 
 
 def test_every_celt_toc_decodes():
