@@ -49,10 +49,11 @@ __global__ void __launch_bounds__(64) k_energy(uint32_t n_lanes, uint32_t n_tick
                                                const uint32_t* __restrict__ rec, StreamState* st, const uint32_t* __restrict__ lane_stream,
                                                float* __restrict__ en, FrameMeta* __restrict__ meta, int32_t* __restrict__ samples_out,
                                                uint32_t* __restrict__ final_range_out, uint32_t quirks,
-                                               const uint8_t* __restrict__ flags, int serial_all) {
+                                               const uint8_t* __restrict__ flags, int serial_all, int force_float_row) {
   uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
   if (lane >= n_lanes) return;
-  celt_energy_lane(lane, n_lanes, n_ticks, pkt_map, rec, st, lane_stream, en, meta, samples_out, final_range_out, quirks, flags, serial_all);
+  celt_energy_lane(lane, n_lanes, n_ticks, pkt_map, rec, st, lane_stream, en, meta, samples_out, final_range_out, quirks, flags, serial_all,
+                   force_float_row);
 }
 
 constexpr int PVQ_THREADS = 64;
@@ -389,7 +390,8 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
   float mem = l < 2 ? s.softclip_mem[l] : 0.f;
   for (uint32_t t = 0; t < n_ticks; t++) {
     const uint32_t f = t * n_lanes + lane;
-    if (!(meta[f].flags & 1u)) continue;
+    const uint32_t fl = meta[f].flags;
+    if (!(fl & 3u)) continue;
     const uint32_t p = pkt_map ? pkt_map[f] : f;
     int n = samples_out[p];
     if (n <= 0) continue;
@@ -407,9 +409,18 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
       }
       if (failed) continue;
     }
+    // The packet's route (k_energy, the same on all its frames): float row -> clip -> int16, or int16 written by k_silk
+    // already. The latter is final unless the previous packet left a non-linearity to carry over (opus.rs:44-60).
+    const bool from_float = (fl & MB_FL_F32ROW) != 0;
+    if (!from_float && !__any_sync(0xffffffffu, mem != 0.f)) continue;
     const int total = n * CC;
     const size_t eo = pcm_elem_off(out_map, p, pcm_stride);
     float* src = pcm + eo;
+    if (!from_float) {   // SILK samples are exact multiples of 2^-15: back to float without loss, into the float scratch row
+      const int16_t* s16 = pcm16 + eo;
+      for (int i = l; i < total; i += 32) src[i] = (float)s16[i] * (1.0f / 32768.0f);
+      __syncwarp();
+    }
     if (total > 2 * MAX_N) buf = src;   // long multi-frame packet: clip in place in the float scratch row
     int over = 0;
     const bool vec = ((((uintptr_t)src) & 15u) | (uint32_t)(total & 7)) == 0 && ((((uintptr_t)(pcm16 + eo)) & 15u) == 0);
@@ -516,7 +527,8 @@ __global__ void __launch_bounds__(64, 12) k_silk(uint32_t n_lanes, uint32_t n_ti
     const uint32_t p = pkt_map ? pkt_map[f] : f;
     const uint32_t* rb = rec + rec_index(f, 0);
     const uint32_t fl = meta[f].flags;
-    const bool to_float = (fl & (8u | 16u)) != 0;   // a CELT frame shares the row (hybrid, fade-out, redundancy): float row, k_deemph / k_fade finish it
+    const bool to_float = (fl & MB_FL_F32ROW) != 0;   // the packet goes through the float row (a CELT frame shares one of its rows, or a decode gain applies)
+    const bool shared = (fl & (8u | 16u)) != 0;       // a CELT frame shares THIS row (hybrid, fade-out, redundancy): k_deemph / k_fade finish it
     const bool hyb_layout = ((rb[S_STATUS * 32] >> 17) & 3u) != 0;       // hybrid, or a one-frame SILK-only cell
     if (fl & 32u) {   // CELT -> SILK: silk decoder reset (opus_decoder.rs:694-696)
       silk_state_reset(S, 0);
@@ -530,7 +542,7 @@ __global__ void __launch_bounds__(64, 12) k_silk(uint32_t n_lanes, uint32_t n_ti
     // decode gain: once on the finished sum. Hybrid: k_deemph does it for the whole row; fade-out: k_deemph for the first
     // 120 samples, here for the rest; redundancy: k_fade for the whole row
     const bool fadeout = (fl & 8u) && !((rb[S_STATUS * 32] >> 17) & 1u);
-    o.CC = CC; o.gain = gain; o.apply_gain = (to_float && !fadeout) ? 0 : apply_gain; o.gain_from = fadeout ? SHORT_MDCT : 0;
+    o.CC = CC; o.gain = gain; o.apply_gain = (shared && !fadeout) ? 0 : apply_gain; o.gain_from = fadeout ? SHORT_MDCT : 0;
     silk_synth_packet(S, W, H, side_live, rb[(hyb_layout ? S_SILK_HYB : S_HDR0) * 32], rb + (hyb_layout ? S_SILK_HYB + 1 : SL_BASE) * 32, quirks, o,
                       stage[threadIdx.x], fir);
   }
@@ -590,6 +602,7 @@ struct bd_handle {
   cudaStream_t copy_stream = nullptr;   // device -> host PCM of pass k overlaps the kernels of pass k + 1
   cudaStream_t side_stream = nullptr;   // the latency-bound per-stream kernels (k_energy, k_silk) run here beside k_pvq
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_silk = nullptr;
+  cudaEvent_t ev_clip_done[2] = {nullptr, nullptr};   // the clipper of the pass that last used each half of the frame meta
   cudaStream_t clip_stream = nullptr;   // k_clip_i16 of pass k runs beside the kernels of pass k + 1
   std::vector<cudaEvent_t> pass_events;
   size_t pass_event_next = 0;
@@ -682,6 +695,8 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
   if (cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) != cudaSuccess) return fail(BD_ERR_CUDA);
   if (cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) != cudaSuccess) return fail(BD_ERR_CUDA);
   if (cudaEventCreateWithFlags(&h->ev_silk, cudaEventDisableTiming) != cudaSuccess) return fail(BD_ERR_CUDA);
+  for (int i = 0; i < 2; i++)
+    if (cudaEventCreateWithFlags(&h->ev_clip_done[i], cudaEventDisableTiming) != cudaSuccess) return fail(BD_ERR_CUDA);
   if (cudaFuncSetAttribute(k_deemph<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(DE_WARPS * 2 * 32 * (128 + 4) * sizeof(float))) != cudaSuccess)
     return fail(BD_ERR_CUDA);
   if (h->states.ensure((size_t)cfg->n_streams * sizeof(StreamState)) != cudaSuccess) return fail(BD_ERR_ALLOC);
@@ -713,6 +728,7 @@ void bd_destroy(bd_handle* h) {
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
   if (h->ev_silk) cudaEventDestroy(h->ev_silk);
+  for (int i = 0; i < 2; i++) if (h->ev_clip_done[i]) cudaEventDestroy(h->ev_clip_done[i]);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
 }
@@ -898,11 +914,14 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     CK(cudaEventRecord(h->ev_fork, s));
     CK(cudaStreamWaitEvent(h->side_stream, h->ev_fork, 0));
     cudaStream_t ss = h->side_stream;
+    // the clipper of pass pi - 2 read this half of the frame meta on its own stream: k_energy may only rewrite it afterwards
+    if (d_pcm_i16 && pi >= 2) CK(cudaStreamWaitEvent(ss, h->ev_clip_done[pi & 1], 0));
     h->prof_begin(BD_K_ENERGY, ss);
     k_energy<<<(n_lanes + 63) / 64, 64, 0, ss>>>(n_lanes, nt, map, h->rec.as<uint32_t>(), h->states.as<StreamState>(), d_lane_stream,
                                                 h->en.as<float>(), meta_p, samples, range, h->cfg.quirks,
                                                 d_out_map ? flg : nullptr,
-                                                h->serial_bands || n_lanes >= 148u * 6u * (uint32_t)BANDS_WARPS);   // one warp per lane fills the band-pass slots
+                                                h->serial_bands || n_lanes >= 148u * 6u * (uint32_t)BANDS_WARPS,   // one warp per lane fills the band-pass slots
+                                                h->cfg.gain_q8 != 0 || !d_pcm_i16);   // direct int16 from k_silk: only the i16 API without a decode gain
     h->prof_end(ss);
     CK(cudaEventRecord(h->ev_join, ss));   // the frame meta and band energies are ready: k_plan may go
     // SILK synthesis (SILK-only and hybrid cells), before the CELT tail so that k_deemph can add the CELT bands of hybrid
@@ -1009,6 +1028,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
         h->launches += 1;
         if (h->pass_out.on) { int rc = ship(c0, (size_t)(tb - ta) * n_lanes); if (rc != BD_OK) return rc; }
       }
+      CK(cudaEventRecord(h->ev_clip_done[pi & 1], fin));
     } else {
       k_clear_softclip<<<(n_lanes + 63) / 64, 64, 0, s>>>(n_lanes, d_lane_stream, h->states.as<StreamState>());
       h->launches += 1;

@@ -61,7 +61,8 @@ struct FrameMeta {
                          // fade at the start (CELT -> SILK) / at the end (SILK -> CELT) of the row applies
 };
 enum { EN_STRIDE = 3 * 2 * NB_EBANDS,
-       MB_FL_FOLD = 8u | 16u | 512u };   // FrameMeta.flags: the frame's band pass runs per stream, in tick order, on the persistent fold buffer
+       MB_FL_FOLD = 8u | 16u | 512u,
+       MB_FL_F32ROW = 256u };  // the packet's PCM goes through the float row (k_deemph / k_fade / k_clip_i16), set on all its frames   // FrameMeta.flags: the frame's band pass runs per stream, in tick order, on the persistent fold buffer
 // flags bit 9 (512): CELT-only frame behind a SILK-side frame of the same pass; bits 10-19 / 20-29: fold-buffer words
 // [lo, hi) a CELT-only frame of the parallel band pass writes back (the part no later frame of the pass overwrites)  // per-frame energy scratch: E, prev1 (old_log_e), prev2 (old_log_e2)
 
@@ -69,7 +70,8 @@ enum { EN_STRIDE = 3 * 2 * NB_EBANDS,
 // per-packet outputs) is pkt_map ? pkt_map[f] : f. Cells without a packet carry S_STATUS bit 15.
 MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, const uint32_t* pkt_map, const uint32_t* rec,
                              StreamState* st_all, const uint32_t* lane_stream, float* en, FrameMeta* meta, int32_t* samples_out,
-                             uint32_t* final_range_out, uint32_t quirks, const uint8_t* flags = nullptr, int serial_all = 0) {
+                             uint32_t* final_range_out, uint32_t quirks, const uint8_t* flags = nullptr, int serial_all = 0,
+                             int force_float_row = 0) {
   StreamState& st = st_all[lane_stream ? lane_stream[lane] : lane];
   uint32_t sample_off = 0;
   // Band pass of CELT-only frames. The reference's fold buffer outlives the frame (mb_celt_bands.cuh), so only a pass that
@@ -80,6 +82,10 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
   bool silk_side_seen = serial_all || st.fold_serial;
   bool pkt_failed = false;   // an earlier frame of the same multi-frame packet failed: the reference returns there
                              // (src/opus_decoder.rs:1339-1350), so the remaining frames must not touch the stream
+  // Output route of the packet, decided once for all its frames (MB_FL_F32ROW): SILK-only packets may leave k_silk as
+  // int16 directly (the i16 API), but only if NO frame of the packet shares its row with a CELT frame and no decode gain
+  // applies; otherwise every frame goes through the float row and the packet through the clipper.
+  uint32_t pkt_route = 0;
   for (uint32_t t = 0; t < n_ticks; t++) {
     const uint32_t f = t * n_lanes + lane;
     const uint32_t* r = rec + rec_index(f, 0);
@@ -89,7 +95,20 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
     if (MB_ST_EMPTY(status)) { meta[f] = m; continue; }
     const uint32_t p = pkt_map ? pkt_map[f] : f;
     const bool continuation = flags && (flags[p] & 4u);
-    if (!continuation) pkt_failed = false;
+    if (!continuation) {
+      pkt_failed = false;
+      bool celt_part = force_float_row != 0;
+      for (uint32_t t2 = t; t2 < n_ticks && !celt_part; t2++) {
+        const uint32_t f2 = t2 * n_lanes + lane;
+        if (t2 > t) {
+          const uint32_t p2 = pkt_map ? pkt_map[f2] : f2;
+          if (!flags || p2 == 0xffffffffu || !(flags[p2] & 4u)) break;
+        }
+        const uint32_t s2 = rec[rec_index(f2, S_STATUS)];
+        celt_part = MB_ST_DECODED(s2) && (!((s2 >> 16) & 1u) || ((s2 >> 17) & 1u) || ((s2 >> 19) & 3u));
+      }
+      pkt_route = celt_part ? MB_FL_F32ROW : 0u;
+    }
     if (pkt_failed || !MB_ST_DECODED(status)) {  // rejected before the decoder ran (unsupported mode, PLC, bad TOC)
       meta[f] = m;
       samples_out[p] = pkt_failed ? MB_UNIMPLEMENTED : MB_ST_CODE(status);
@@ -132,7 +151,7 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
     const uint32_t silk_reset = (silk_bit && st.prev_mode == 1002) ? 32u : 0u;          // opus_decoder.rs:694-696
     if (silk_only) {  // SILK-only packet: synthesis runs in k_silk (mb_silk_out.cuh); here only the front-end bookkeeping
       const int N = silk_n;
-      m.flags = 2u | silk_reset;
+      m.flags = 2u | silk_reset | pkt_route;
       meta[f] = m;
       st.prev_mode = 1000;
       st.prev_redundancy = 0;
@@ -227,6 +246,7 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
       else if (st.prev_mode != 1000 || st.prev_redundancy) m.flags |= 64u;   // opus_decoder.rs:1066
     } else m.flags = (hybrid || fadeout) ? (1u | 2u | 8u | (celt_reset ? 4u : 0u)) : (silk_side_seen ? (1u | 512u) : 1u);
     if (m.flags & (8u | 16u)) { silk_side_seen = true; st.fold_serial = 1; }
+    m.flags |= MB_FL_F32ROW;
     meta[f] = m;
     sample_off += (uint32_t)(M * SHORT_MDCT);                 // the CELT time line advances by the CELT frame
     int code = MB_ST_CODE(status);

@@ -37,6 +37,7 @@ MB_DEV void parse_cell(const uint8_t* arena, const uint32_t* offsets, uint32_t p
   if (code == MB_OK) {
     toc = data[0];
     if (toc & 3u) code = MB_UNIMPLEMENTED;              // multi-frame packets (row F1)
+    else if (len - 1 > 1275) code = MB_INVALID_PACKET;  // src/packet.rs:465: a frame is at most 1275 bytes
     else if (!(toc & 0x80u)) {
       if (len - 1 <= 1) code = MB_UNIMPLEMENTED;             // concealment (src/opus_decoder.rs:491)
       else if ((toc & 0x60u) == 0x60u) {

@@ -28,6 +28,10 @@ int emu_kat(int what, const uint32_t* in, uint32_t n_in, uint32_t* out, uint32_t
   return kat_run(tm, &sm, what, in, n_in, out, n_out, bytes);
 }
 
+// decode gain of the following emu_decode_grid calls (Q8 dB, 0 = none; src/opus_decoder.rs:1376-1392)
+static int g_gain_q8 = 0;
+void emu_set_gain(int gain_q8) { g_gain_q8 = gain_q8; }
+
 // Decodes a regular [n_ticks][n_lanes] packet grid with one fresh decoder state per lane, phases in
 // the same order as the CUDA launcher. pcm: [packet][pcm_stride]. iy_dbg/x_dbg: optional [packet][2*960].
 int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_t* offsets, uint32_t n_lanes, uint32_t n_ticks,
@@ -51,7 +55,8 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   // phase 2a
   for (uint32_t j = 0; j < n_lanes; j++)
     celt_energy_lane(j, n_lanes, n_ticks, nullptr, rec.data(), st.data(), nullptr, en.data(), meta.data(), samples_out, final_range_out, quirks,
-                     nullptr, getenv("MB_EMUL_PARALLEL_BANDS") ? 0 : 1);   // default: the per-stream band pass of large calls
+                     nullptr, getenv("MB_EMUL_PARALLEL_BANDS") ? 0 : 1,   // default: the per-stream band pass of large calls
+                     g_gain_q8 != 0 || !pcm16);
   // phase 2b
   Team tm = {0, 1};
   std::vector<float> xbuf((size_t)F * XBUF_STRIDE, 0.f), xstage(2 * MAX_N);
@@ -87,7 +92,8 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   TailParams tp;
   tp.rec = rec.data(); tp.meta = meta.data(); tp.pkt_map = nullptr; tp.lane_stream = nullptr; tp.st_all = st.data(); tp.hist = hist.data();
   tp.series = series.data(); tp.series_stride = series_stride; tp.n_lanes = n_lanes; tp.n_ticks = n_ticks; tp.CC = CC;
-  tp.gain = 1.f; tp.apply_gain = 0; tp.pcm_f32 = out; tp.pcm_stride = pcm_stride; tp.xbuf = xbuf.data();
+  tp.gain = g_gain_q8 == 0 ? 1.f : (float)exp(0.6931471805599453094 * (double)((3.32192809488736234787f / 5120.0f) * (float)g_gain_q8));
+  tp.apply_gain = g_gain_q8 != 0; tp.pcm_f32 = out; tp.pcm_stride = pcm_stride; tp.xbuf = xbuf.data();
   // SILK-only packets (k_silk): lane per stream, ticks in order
   {
     std::vector<SilkState> sst(n_lanes);
@@ -102,7 +108,8 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
       for (uint32_t t = 0; t < n_ticks; t++) {
         const uint32_t f = t * n_lanes + j;
         if (!(meta[f].flags & 2u)) continue;
-        const bool hybrid = (meta[f].flags & (8u | 16u)) != 0;   // a CELT frame shares the row: float row
+        const bool hybrid = (meta[f].flags & MB_FL_F32ROW) != 0;   // the packet goes through the float row
+        const bool shared = (meta[f].flags & (8u | 16u)) != 0;     // a CELT frame shares this row
         if (meta[f].flags & 32u) {
           silk_state_reset(sst[j], 0);
           silk_ring_clear(W->hist[0], W->pos[0]); silk_ring_clear(W->hist[1], W->pos[1]);
@@ -113,7 +120,8 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
         SilkPcmOut o;
         o.f32 = (hybrid || !pcm16) ? out + (size_t)f * pcm_stride : nullptr;
         o.i16 = (hybrid || !pcm16) ? nullptr : pcm16 + (size_t)f * pcm_stride;
-        o.CC = CC; o.gain = 1.f; o.apply_gain = 0; o.gain_from = 0;
+        const bool fadeout = (meta[f].flags & 8u) && !((rb[S_STATUS * 32] >> 17) & 1u);
+        o.CC = CC; o.gain = tp.gain; o.apply_gain = (shared && !fadeout) ? 0 : tp.apply_gain; o.gain_from = fadeout ? SHORT_MDCT : 0;
         silk_synth_packet(sst[j], *W, H, side_live, rb[(hyb_layout ? S_SILK_HYB : S_HDR0) * 32], rb + (hyb_layout ? S_SILK_HYB + 1 : SL_BASE) * 32,
                           quirks, o, stage, silk_resampler_frac_FIR_12);
       }
@@ -132,7 +140,11 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
     for (uint32_t j = 0; j < n_lanes; j++)
       for (uint32_t t = 0; t < n_ticks; t++) {
         uint32_t p = t * n_lanes + j;
-        if (samples_out[p] <= 0 || !(meta[p].flags & 1u)) continue;
+        if (samples_out[p] <= 0 || !(meta[p].flags & 3u)) continue;
+        if (!(meta[p].flags & MB_FL_F32ROW)) {   // int16 straight from the SILK lane: final unless a non-linearity carries over
+          if (st[j].softclip_mem[0] == 0.f && st[j].softclip_mem[1] == 0.f) continue;
+          for (int i = 0; i < samples_out[p] * CC; i++) out[(size_t)p * pcm_stride + i] = (float)pcm16[(size_t)p * pcm_stride + i] * (1.0f / 32768.0f);
+        }
         soft_clip_packet(out + (size_t)p * pcm_stride, samples_out[p], CC, st[j].softclip_mem);
         for (int i = 0; i < samples_out[p] * CC; i++) pcm16[(size_t)p * pcm_stride + i] = float2int16(out[(size_t)p * pcm_stride + i]);
       }
