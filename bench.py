@@ -12,7 +12,10 @@ libopus exists on these boxes, see DESIGN.md "Corpus".
   e2e    through the reference-facing host call (BatchDecoder.decode / bd_decode_i16 = mousiki Decoder::decode):
          pinned host packets -> H2D -> kernels -> D2H i16 PCM + sample counts + final_range, wall time of the call.
   --impl reference: the CPU restatement of mousiki's float decoder (oracle/, the reference itself cannot be built
-         here: no Rust toolchain), all host threads, on a bounded sample of the same workload.
+         here: no Rust toolchain), all host threads, on a bounded sample of the same workload; built on the box it runs
+         on with -O3 -march=native -ffp-contract=off.
+  --scaling strong: ONE fixed corpus of --streams streams in total (default 10^5, the north star's job) sharded over the
+         ranks by stream id; the per-stream checksums are all-gathered with NCCL and must not depend on the rank count.
 """
 import argparse
 import json
@@ -99,6 +102,34 @@ class ClockSampler:
                 "reasons": sorted(reasons)}
 
 
+_NATIVE = None
+
+
+def oracle_native_lib():
+    """The oracle built for THIS host's CPU (-O3 -march=native -ffp-contract=off), for the timed
+    CPU arm only; the file name carries a signature of the CPU so that a library built elsewhere is never loaded.
+    Falls back to the portable build (-O2) if the compiler is missing. Returns (lib, "native" | "portable")."""
+    global _NATIVE
+    if _NATIVE is not None:
+        return _NATIVE
+    import ctypes as C
+    import hashlib
+
+    import helpers
+    try:
+        flags = next(l for l in open("/proc/cpuinfo") if l.startswith("flags"))
+        model = next(l for l in open("/proc/cpuinfo") if l.startswith("model name"))
+        sig = hashlib.sha1((flags + model).encode()).hexdigest()[:10]
+        target = f"_build/liboracle_native_{sig}.so"
+        subprocess.run(["make", "-C", str(ROOT / "oracle"), target], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        lib = C.CDLL(str(ROOT / "oracle" / target))
+        lib.orc_decode_grid.argtypes = helpers.oracle_lib().orc_decode_grid.argtypes
+        _NATIVE = (lib, "native")
+    except Exception:
+        _NATIVE = (helpers.oracle_lib(), "portable")
+    return _NATIVE
+
+
 def cpu_reference_rate(streams, ticks, threads, min_seconds=0.0, seed=7):
     """The CPU restatement of mousiki's float decoder (oracle/, kind "port") on `streams` x `ticks` frames of the same
     workload, `threads` std::threads, i16 output like the reference's own codec_bench (src/bin/codec_bench.rs:679-702:
@@ -107,7 +138,7 @@ def cpu_reference_rate(streams, ticks, threads, min_seconds=0.0, seed=7):
     import helpers
 
     arena, offsets = make_corpus(streams, ticks, seed)
-    lib = helpers.oracle_lib()
+    lib, _ = oracle_native_lib()
     n = streams * ticks
     pcm = np.zeros((n, FRAME * CH), dtype=np.int16)
     samples = np.zeros(n, dtype=np.int32)
@@ -132,10 +163,9 @@ def run_reference(args):
     streams = 128 * cores
     for _ in range(args.warmup):
         cpu_reference_rate(streams, TICKS, cores)
-    t0 = time.perf_counter()
+    dt = 0.0
     for _ in range(args.steps):
-        cpu_reference_rate(streams, TICKS, cores)
-    dt = time.perf_counter() - t0
+        dt += cpu_reference_rate(streams, TICKS, cores)[1]     # the decode loop only (src/bin/codec_bench.rs:679-702), not the corpus set-up
     value = args.steps * streams * TICKS * AUDIO_S_PER_FRAME / dt
     sample = f"{streams} streams x {TICKS} frames per step ({cores} threads, one decoder per stream, i16 out)"
     line = {
@@ -143,7 +173,7 @@ def run_reference(args):
         "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "config": {"workload": WORKLOAD, "note": "CPU restatement of mousiki's float decoder (oracle/); the Rust "
                                         "reference cannot be built on this box (no cargo/rustc)"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "build": oracle_native_lib()[1]},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -173,39 +203,82 @@ def hbm_peak():
         return 6650.0, "fallback"
 
 
-def verify_against_oracle(dec, arena, offsets, streams, ticks, check_streams=64):
-    """Parity gate printed with the number: first `check_streams` streams, all ticks, against the oracle."""
+def oracle_tail(arena, offsets, streams, ticks, check, repeats, i16):
+    """What the reference path leaves for the first `check` streams of a [ticks][streams] grid after the grid has been
+    decoded `repeats` times in a row by the same decoders (the bench never resets between steps): the outputs of the LAST
+    repeat, from the oracle (one decoder per stream, all `ticks * repeats` packets in sequence)."""
     import helpers
 
-    sel = (np.arange(ticks)[:, None] * streams + np.arange(check_streams)[None, :]).reshape(-1)
+    sel = (np.arange(ticks)[:, None] * streams + np.arange(check)[None, :]).reshape(-1)
     lens = np.diff(offsets.astype(np.int64))
-    sub_off = np.zeros(len(sel) + 1, dtype=np.uint32)
-    sub_off[1:] = np.cumsum(lens[sel])
-    sub_arena = np.concatenate([arena[offsets[p]:offsets[p + 1]] for p in sel])
-    ids = np.tile(np.arange(check_streams, dtype=np.uint32), ticks)
-    dec.reset()
-    pcm, samples, rng = dec.decode_float(sub_arena, sub_off, ids, FRAME)
-    ref_pcm, ref_samples, ref_rng = helpers.oracle_decode_grid(sub_arena, sub_off, check_streams, ticks, CH, FRAME)
-    dec.reset()
-    i16a = np.clip(np.rint(pcm * 32768.0), -32768, 32767)
-    i16b = np.clip(np.rint(ref_pcm * 32768.0), -32768, 32767)
-    num = float((ref_pcm.astype(np.float64) ** 2).sum())
-    den = float(((ref_pcm.astype(np.float64) - pcm) ** 2).sum())
+    one = np.concatenate([arena[offsets[p]:offsets[p + 1]] for p in sel])
+    sub_arena = np.tile(one, repeats)
+    sub_off = np.zeros(len(sel) * repeats + 1, dtype=np.uint32)
+    sub_off[1:] = np.cumsum(np.tile(lens[sel], repeats))
+    pcm, samples, rng = helpers.oracle_decode_grid(sub_arena, sub_off, check, ticks * repeats, CH, FRAME, i16=i16)
+    k = len(sel) * (repeats - 1)
+    return sel, pcm[k:], samples[k:], rng[k:]
+
+
+def parity_report(pcm, samples, rng, ref_pcm, ref_samples, ref_rng, what):
+    """Gates printed with the number: final_range and sample counts exact, PCM in i16 LSB / f32 / SNR."""
+    if pcm.dtype == np.int16:
+        a, b = pcm.astype(np.int64), ref_pcm.astype(np.int64)
+        fa, fb = pcm.astype(np.float64) / 32768.0, ref_pcm.astype(np.float64) / 32768.0
+    else:
+        a = np.clip(np.rint(pcm.astype(np.float64) * 32768.0), -32768, 32767)
+        b = np.clip(np.rint(ref_pcm.astype(np.float64) * 32768.0), -32768, 32767)
+        fa, fb = pcm.astype(np.float64), ref_pcm.astype(np.float64)
+    num, den = float((fb ** 2).sum()), float(((fb - fa) ** 2).sum())
     return {
-        "packets_checked": int(len(sel)),
+        "checked": what, "packets_checked": int(len(samples)),
         "final_range_mismatches": int((rng != ref_rng).sum()),
         "sample_count_mismatches": int((samples != ref_samples).sum()),
-        "pcm_max_abs_err_i16_lsb": float(np.abs(i16a - i16b).max()),
-        "pcm_max_abs_err_f32": float(np.abs(pcm - ref_pcm).max()),
+        "pcm_max_abs_err_i16_lsb": float(np.abs(a - b).max()),
+        "pcm_max_abs_err_f32": float(np.abs(fa - fb).max()),
         "snr_db": None if den == 0 else 10 * float(np.log10(max(num, 1e-30) / den)),
     }
 
 
+def make_strong_corpus(total_streams, ticks, lo, hi, seed=4242):
+    """Streams [lo, hi) of ONE fixed corpus of `total_streams` streams (bytes of stream s do not depend on the sharding):
+    generated stream-major in blocks of 1000 streams, returned as this rank's [ticks][hi - lo] grid."""
+    blocks = []
+    for b0 in range(lo - lo % 1000, hi, 1000):
+        g = np.random.default_rng([seed, b0 // 1000]).integers(0, 256, size=(1000, ticks, PAYLOAD + 1), dtype=np.uint8)
+        blocks.append(g[max(lo - b0, 0):max(min(hi - b0, 1000), 0)])
+    g = np.concatenate(blocks) if blocks else np.zeros((0, ticks, PAYLOAD + 1), dtype=np.uint8)
+    g[:, :, 0] = 0xFC
+    arena = np.ascontiguousarray(g.transpose(1, 0, 2)).reshape(-1)
+    offsets = (np.arange((hi - lo) * ticks + 1, dtype=np.uint64) * (PAYLOAD + 1)).astype(np.uint32)
+    return arena, offsets
+
+
+def d2h_probe(torch, dev, mbytes=256, reps=4):
+    """Device -> pinned host copy rate of this rank while every rank copies at once (explains the e2e arm at N GPUs: the box's
+    host fabric, not the decoder, bounds the PCM going back). GB/s."""
+    n = mbytes << 20
+    d = torch.empty(n, dtype=torch.uint8, device=dev)
+    h = torch.empty(n, dtype=torch.uint8).pin_memory()
+    h.copy_(d, non_blocking=True)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        h.copy_(d, non_blocking=True)
+    e1.record()
+    torch.cuda.synchronize()
+    return reps * n / (e0.elapsed_time(e1) * 1e-3) / 1e9
+
+
 def run_gpu(args):
+    import hashlib
+
     import torch
     import torch.distributed as dist
 
     from mousiki_b200 import BatchDecoder
+    from mousiki_b200.sharding import gather_checksums, shard_range
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -217,12 +290,20 @@ def run_gpu(args):
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
-    streams, ticks = args.streams, args.ticks
+    ticks = args.ticks
+    strong = args.scaling == "strong"
+    if strong:
+        total_streams = args.streams if args.streams != STREAMS else 100_000
+        lo, hi = shard_range(total_streams, world, rank)
+        streams = hi - lo
+        arena, offsets = make_strong_corpus(total_streams, ticks, lo, hi)
+    else:
+        streams = args.streams
+        total_streams = streams * world
+        arena, offsets = make_corpus(streams, ticks, 1000 + rank)  # every rank owns its own streams: no data-path collective
     n = streams * ticks
-    arena, offsets = make_corpus(streams, ticks, 1000 + rank)  # every rank owns its own streams: no data-path collective
     dec = BatchDecoder(streams, 48000, CH, device=local_rank)
-
-    parity = verify_against_oracle(dec, arena, offsets, streams, ticks) if rank == 0 else None
+    check = min(64, streams)
 
     # ---- device-resident arm ("value")
     d_arena = torch.from_numpy(arena).to(dev)
@@ -259,7 +340,22 @@ def run_gpu(args):
     prof = dec.profile_read()
     dec.profile(False)
     assert int((d_samples != FRAME).sum().item()) == 0, "a packet failed to decode in the timed region"
-    checksum = int(d_range.to(torch.int64).bitwise_and(0xFFFFFFFF).sum().item()) & 0xFFFFFFFF
+    # per-stream checksums of the LAST timed step: sum of final_range over the stream's packets (low word) and a sum over the
+    # PCM bit patterns (high word); both computed on the device, 8 bytes per stream leave it
+    fr = d_range.view(ticks, streams).to(torch.int64).bitwise_and_(0xFFFFFFFF).sum(dim=0).bitwise_and_(0xFFFFFFFF)
+    pc = torch.zeros(streams, dtype=torch.int64, device=dev)
+    bits = d_pcm.view(torch.int32).view(ticks, streams, FRAME * CH)
+    for t in range(ticks):
+        pc += bits[t].sum(dim=1, dtype=torch.int64)
+    local_sums = ((pc.bitwise_and_(0xFFFFFFFF) << 32) | fr).cpu().numpy().view(np.uint64)
+    # parity gate on the TIMED configuration: the first streams of the last timed call, straight from its output buffers
+    parity = None
+    if rank == 0:
+        sel, ref_pcm, ref_samples, ref_rng = oracle_tail(arena, offsets, streams, ticks, check, args.warmup + args.steps, False)
+        idx = torch.from_numpy(sel.astype(np.int64)).to(dev)
+        parity = parity_report(d_pcm[idx].cpu().numpy(), d_samples[idx].cpu().numpy(), d_range[idx].cpu().numpy().view(np.uint32),
+                               ref_pcm, ref_samples, ref_rng,
+                               f"first {check} streams x {ticks} frames of the last timed bd_decode_grid_dev call ({streams} lanes), f32")
 
     # ---- end-to-end arm: the host call a user makes, pinned host buffers, copies inside the timed region
     h_arena = torch.from_numpy(arena).pin_memory().numpy()
@@ -268,9 +364,10 @@ def run_gpu(args):
     h_pcm = torch.empty((n, FRAME * CH), dtype=torch.int16).pin_memory().numpy()
     h_samples = torch.empty(n, dtype=torch.int32).pin_memory().numpy()
     h_range = torch.empty(n, dtype=torch.int32).pin_memory().numpy().view(np.uint32)
-    del d_pcm
+    del d_pcm, bits
     torch.cuda.empty_cache()
     e2e_steps = max(1, min(args.steps, 3))
+    dec.reset()
     for _ in range(2):
         dec.decode_into(h_arena, h_offsets, h_ids, h_pcm, h_samples, h_range)
     if world > 1:
@@ -282,21 +379,34 @@ def run_gpu(args):
     e2e_s = time.perf_counter() - t0
     assert (h_samples == FRAME).all()
     clocks = sampler.stop() if rank == 0 else None
-
-    t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
-    sums = torch.tensor([checksum], dtype=torch.int64, device=dev)
+    e2e_parity = None
+    if rank == 0:
+        sel, ref_pcm, ref_samples, ref_rng = oracle_tail(arena, offsets, streams, ticks, check, 2 + e2e_steps, True)
+        e2e_parity = parity_report(h_pcm[sel], h_samples[sel], h_range[sel], ref_pcm, ref_samples, ref_rng,
+                                   f"first {check} streams x {ticks} frames of the last timed bd_decode_i16 call ({streams} lanes), i16")
     if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)  # max over ranks
-        gathered = [torch.zeros_like(sums) for _ in range(world)]
-        dist.all_gather(gathered, sums)           # NCCL carries only the per-rank checksums
-        sums = torch.stack(gathered).reshape(-1)
-    ms, e2e_ms = float(t[0].item()), float(t[1].item())
+        dist.barrier()
+    d2h_gbs = d2h_probe(torch, dev)
+
+    t = torch.tensor([ms, e2e_s * 1e3, -d2h_gbs], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)  # max over ranks (slowest copy rate)
+    if strong:
+        sums = gather_checksums(local_sums, total_streams, world, rank, device=dev)   # NCCL carries only the per-stream checksums
+    else:  # weak scaling: every rank has `streams` streams of its own
+        buf = torch.from_numpy(local_sums.view(np.int64)).to(dev)
+        if world > 1:
+            out = [torch.zeros_like(buf) for _ in range(world)]
+            dist.all_gather(out, buf)
+            buf = torch.cat(out)
+        sums = buf.cpu().numpy().view(np.uint64)
+    ms, e2e_ms, d2h_min = float(t[0].item()), float(t[1].item()), -float(t[2].item())
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return 0
 
-    audio_s_per_step = world * n * AUDIO_S_PER_FRAME
+    audio_s_per_step = total_streams * ticks * AUDIO_S_PER_FRAME
     value = audio_s_per_step * args.steps / (ms * 1e-3)
     e2e_value = audio_s_per_step * e2e_steps / (e2e_ms * 1e-3)
     peak, peak_kind = hbm_peak()
@@ -304,35 +414,56 @@ def run_gpu(args):
     top_ms, top_launches = prof[top]
     frames_per_launch = n * args.steps / top_launches
     achieved = ALG_BYTES[top] * frames_per_launch / (top_ms / top_launches * 1e-3) / 1e9
+    # the band pass has two forms; calls with >= 3552 lanes run every frame through the per-stream one (mb_api.cu)
+    top_name = "k_bands_hyb" if top == "k_bands" and streams >= 148 * 6 * 4 else top
     traffic = None
     tf = ROOT / "profiles" / "roofline_traffic.json"
     if tf.exists():
-        traffic = json.loads(tf.read_text()).get(top)
-    cores = os.cpu_count() or 1
-    cpu_streams = 128 * cores
-    cpu_value, cpu_s, cpu_passes = cpu_reference_rate(cpu_streams, TICKS, cores, min_seconds=12.0)
+        traffic = json.loads(tf.read_text()).get(top_name)
+    cpu_baseline = None
+    if world == 1:
+        cores = os.cpu_count() or 1
+        cpu_streams = 128 * cores
+        cpu_value, cpu_s, cpu_passes = cpu_reference_rate(cpu_streams, TICKS, cores, min_seconds=12.0)
+        cpu_baseline = {"value": cpu_value, "unit": UNIT, "cores": cores, "kind": "port", "build": oracle_native_lib()[1],
+                        "sample": f"{cpu_passes} passes of {cpu_streams} streams x {TICKS} frames ({cpu_s:.1f} s of CPU wall time), {cores} threads, "
+                                  "fresh decoder per stream, i16 out"}
+    fr_hash = hashlib.sha256((sums & np.uint64(0xFFFFFFFF)).astype(np.uint32).tobytes()).hexdigest()
+    pcm_hash = hashlib.sha256((sums >> np.uint64(32)).astype(np.uint32).tobytes()).hexdigest()
+    checks = {"streams": int(len(sums)), "final_range_sha256": fr_hash, "pcm_bits_sha256": pcm_hash,
+              "what": "per-stream sums over the last timed step, all-gathered with NCCL" if world > 1 else "per-stream sums over the last timed step"}
+    if strong:
+        gold = ROOT / "tests" / "golden" / "strong_scaling_checksums.json"
+        if gold.exists():
+            want = json.loads(gold.read_text()).get(f"{total_streams}x{ticks}x{args.warmup + args.steps}")
+            if want:
+                checks["final_range_matches_golden"] = want["final_range_sha256"] == fr_hash
+                checks["pcm_matches_1gpu_run"] = want.get("pcm_bits_sha256") == pcm_hash
+                assert checks["final_range_matches_golden"], "per-stream final_range checksums differ from the committed 1-GPU / oracle vector"
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "streams_per_gpu": streams, "frames_per_stream_per_step": ticks, "payload_bytes": PAYLOAD,
-                   "packets": "TOC 0xFC + seeded random bytes (reference fuzz construction)", "output": "f32 PCM left in HBM",
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD if not strong else f"celt_only_48k_stereo_20ms_64kbps_{total_streams}_streams_x{ticks}_frames_one_job",
+                   "streams_per_gpu": streams, "streams_total": total_streams, "frames_per_stream_per_step": ticks, "payload_bytes": PAYLOAD,
+                   "packets": "P-fuzz: TOC 0xFC + seeded random bytes (reference fuzz construction)", "output": "f32 PCM left in HBM",
                    "l2": "per-step working set (scratch + PCM, several GB) exceeds the 126 MB L2", "sharding": f"streams by rank, {world} rank(s), no data-path collective"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h_arena.nbytes + h_offsets.nbytes + h_ids.nbytes + n),
                 "d2h_bytes_per_step": int(h_pcm.nbytes + h_samples.nbytes + h_range.nbytes), "ms_per_step": e2e_ms / e2e_steps,
-                "steps": e2e_steps, "api": "BatchDecoder.decode_into -> bd_decode_i16 (mousiki Decoder::decode), pinned host buffers"},
+                "steps": e2e_steps, "api": "BatchDecoder.decode_into -> bd_decode_i16 (mousiki Decoder::decode), pinned host buffers",
+                "pcie_d2h_gbs": d2h_min, "pcie_d2h_note": "device -> pinned host rate of the slowest rank with all ranks copying at once; "
+                "d2h_bytes_per_step / this = the floor of the e2e step"},
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
+        "roofline": {"bound": "hbm", "kernel": top_name, "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "alg_bytes_per_frame": ALG_BYTES[top],
                      "avg_launch_ms": top_ms / top_launches,
-                     "path": {"alg_bytes_per_frame": PATH_BYTES, "achieved": PATH_BYTES * n * args.steps / (ms * 1e-3) / 1e9 / world,
-                              "frac": PATH_BYTES * n * args.steps / (ms * 1e-3) / 1e9 / world / peak}},
+                     "path": {"alg_bytes_per_frame": PATH_BYTES, "achieved": PATH_BYTES * n * args.steps / (ms * 1e-3) / 1e9,
+                              "frac": PATH_BYTES * n * args.steps / (ms * 1e-3) / 1e9 / peak}},
         "kernel_ms_per_step": {k: v[0] / args.steps for k, v in prof.items() if v[1]},
-        "cpu_baseline": {"value": cpu_value, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{cpu_passes} passes of {cpu_streams} streams x {TICKS} frames ({cpu_s:.1f} s of CPU wall time), {cores} threads, "
-                                   "fresh decoder per stream, i16 out"},
+        "cpu_baseline": cpu_baseline,
         "parity": parity,
-        "checksums": [int(x) for x in sums.tolist()],
+        "parity_e2e": e2e_parity,
+        "checksums": checks,
     }
     _emit(line)
     if world > 1:
@@ -366,6 +497,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--streams", type=int, default=STREAMS, help="streams per GPU (default: the BASELINE workload)")
     ap.add_argument("--ticks", type=int, default=TICKS, help="frames per stream per step")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --streams streams per GPU (the driver's contract); strong: one fixed corpus of --streams streams "
+                         "(default 10^5) sharded over the ranks, per-stream checksums all-gathered and compared with the golden vector")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -152,6 +152,48 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   return 0;
 }
 
+// Operation-list statistics of a CELT grid (tools/op_histogram.py): per op type, how many and over how many samples.
+int emu_op_histogram(int CC, uint32_t quirks, const uint8_t* arena, const uint32_t* offsets, uint32_t n_lanes, uint32_t n_ticks,
+                     uint64_t* count /*16*/, uint64_t* samples /*16*/, uint64_t* totals /*4: frames, op words, nodes, leaves*/) {
+  const uint32_t F = n_lanes * n_ticks;
+  std::vector<uint32_t> rec(((size_t)F + 31) / 32 * REC_SLOTS * 32, 0);
+  std::vector<StreamState> st(n_lanes);
+  for (auto& s : st) stream_state_reset(s);
+  std::vector<float> en((size_t)F * EN_STRIDE, 0.f);
+  std::vector<FrameMeta> meta(F);
+  std::vector<int32_t> so(F);
+  std::vector<uint32_t> fr(F);
+  for (uint32_t f = 0; f < F; f++)
+    parse_cell(arena, offsets, f, rec.data() + rec_index(f, 0), CC, quirks, CC == 1, 960, nullptr, f >= n_lanes ? f - n_lanes : 0xffffffffu,
+               f >= n_lanes ? nullptr : &st[f].prev_mode);
+  for (uint32_t j = 0; j < n_lanes; j++)
+    celt_energy_lane(j, n_lanes, n_ticks, nullptr, rec.data(), st.data(), nullptr, en.data(), meta.data(), so.data(), fr.data(), quirks, nullptr, 1, 1);
+  Team tm = {0, 1};
+  std::vector<float> xbuf((size_t)F * XBUF_STRIDE, 0.f), xstage(2 * MAX_N);
+  PvqParams pq; pq.rec = rec.data(); pq.meta = meta.data(); pq.xbuf = xbuf.data(); pq.iy_dbg = nullptr;
+  for (uint32_t f = 0; f < F; f++) celt_pvq_frame(tm, xstage.data(), f, pq);
+  PlanParams pl; pl.rec = rec.data(); pl.en = en.data(); pl.meta = meta.data();
+  for (uint32_t f = 0; f < F; f++) celt_plan_frame(f, pl);
+  for (int i = 0; i < 16; i++) count[i] = samples[i] = 0;
+  for (int i = 0; i < 4; i++) totals[i] = 0;
+  for (uint32_t f = 0; f < F; f++) {
+    if (!(meta[f].flags & 1u)) continue;
+    const uint32_t* r = rec.data() + rec_index(f, 0);
+    const uint32_t n = r[S_PLAN * 32];
+    if (n == 0xffffffffu) continue;
+    totals[0]++; totals[1] += n; totals[2] += MB_H1_NNODES(r[S_HDR1 * 32]); totals[3] += MB_H1_NLEAVES(r[S_HDR1 * 32]);
+    for (uint32_t p = 0; p < n;) {
+      const uint32_t op = r[(S_OPS + p) * 32], type = MB_OP_TYPE(op);
+      count[type]++; samples[type] += type == OP_AVG ? (MB_OP_N(op) | (MB_OP_P(op) << 9)) : MB_OP_N(op);
+      p++;
+      if (type == OP_SKIP) p += MB_OP_N(op);
+      else if (type == OP_COPY_LB || type == OP_LBOUT || type == OP_MERGE || type == OP_STEREO2 || type == OP_HYB) p += 1;
+      else if (type == OP_FOLD || type == OP_NOISE || type == OP_ANTI) p += 2;
+    }
+  }
+  return 0;
+}
+
 // ---- the host front end for multi-frame packets (mb_host_packets.h), exposed for the CPU tests
 static mbh::Split g_split;
 

@@ -184,3 +184,25 @@ def test_gpu_buffer_too_small():
     with BatchDecoder(1, 48000, 2) as dec:
         _, samples, _ = dec.decode_float(arena, offsets, np.zeros(1, dtype=np.uint32), 480)
     assert samples[0] == -2  # OpusDecodeError::BufferTooSmall (src/opus_decoder.rs:1318-1320)
+
+
+@pytest.mark.parametrize("i16", [False, True])
+def test_gpu_large_call_takes_the_per_stream_band_pass_pcm(i16):
+    """Calls with >= 3552 lanes (the bench's 10^4-lane configuration among them) run every frame through the per-stream
+    band pass (k_bands_hyb, mb_api.cu `serial_all`): PCM, not only final_range, of such a call against the oracle,
+    stereo 20 ms frames with the bench's payload size and a mix of frame sizes behind them."""
+    lanes, ticks = 3584, 3
+
+    def toc(t, j, rng):
+        return helpers.celt_toc(3 if t < 2 else int(rng.integers(0, 4)), True)
+
+    arena, offsets = helpers.fuzz_grid(lanes, ticks, 160, toc, seed=77)
+    po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, 2, 960, i16=i16)
+    pg, sg, rg = _decode_gpu(arena, offsets, lanes, ticks, 2, i16=i16)
+    assert np.array_equal(so, sg) and np.array_equal(ro, rg)
+    if i16:
+        assert int(np.abs(po.astype(np.int32) - pg.astype(np.int32)).max()) <= 1
+    else:
+        err = float(np.abs(po - pg).max())
+        print(f"3584 lanes: f32 max err {err:.3g}, bit-identical {np.array_equal(po, pg)}")
+        assert err <= TOL_F32
