@@ -45,15 +45,19 @@ __global__ void __launch_bounds__(128, 7) k_parse(const uint8_t* __restrict__ ar
   parse_cell(arena, offsets, pkt, rec + rec_index(f, 0), CC, quirks, disable_inv, cap_per_ch, flags, prev_pkt, prev_mode);
 }
 
-__global__ void __launch_bounds__(64) k_energy(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
+// one warp per stream, 4 streams per CTA
+constexpr int ENERGY_WARPS = 4;
+__global__ void __launch_bounds__(32 * ENERGY_WARPS) k_energy(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
                                                const uint32_t* __restrict__ rec, StreamState* st, const uint32_t* __restrict__ lane_stream,
                                                float* __restrict__ en, FrameMeta* __restrict__ meta, int32_t* __restrict__ samples_out,
                                                uint32_t* __restrict__ final_range_out, uint32_t quirks,
                                                const uint8_t* __restrict__ flags, int serial_all, int force_float_row) {
-  uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ EnergySmem sm[ENERGY_WARPS];
+  const uint32_t lane = blockIdx.x * ENERGY_WARPS + (threadIdx.x >> 5);
   if (lane >= n_lanes) return;
-  celt_energy_lane(lane, n_lanes, n_ticks, pkt_map, rec, st, lane_stream, en, meta, samples_out, final_range_out, quirks, flags, serial_all,
-                   force_float_row);
+  Team tm = {(int)(threadIdx.x & 31), 32};
+  celt_energy_stream(tm, &sm[threadIdx.x >> 5], lane, n_lanes, n_ticks, pkt_map, rec, st, lane_stream, en, meta, samples_out, final_range_out,
+                     quirks, flags, serial_all, force_float_row);
 }
 
 constexpr int PVQ_THREADS = 64;
@@ -917,7 +921,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     // the clipper of pass pi - 2 read this half of the frame meta on its own stream: k_energy may only rewrite it afterwards
     if (d_pcm_i16 && pi >= 2) CK(cudaStreamWaitEvent(ss, h->ev_clip_done[pi & 1], 0));
     h->prof_begin(BD_K_ENERGY, ss);
-    k_energy<<<(n_lanes + 63) / 64, 64, 0, ss>>>(n_lanes, nt, map, h->rec.as<uint32_t>(), h->states.as<StreamState>(), d_lane_stream,
+    k_energy<<<(n_lanes + ENERGY_WARPS - 1) / ENERGY_WARPS, 32 * ENERGY_WARPS, 0, ss>>>(n_lanes, nt, map, h->rec.as<uint32_t>(), h->states.as<StreamState>(), d_lane_stream,
                                                 h->en.as<float>(), meta_p, samples, range, h->cfg.quirks,
                                                 d_out_map ? flg : nullptr,
                                                 h->serial_bands || n_lanes >= 148u * 6u * (uint32_t)BANDS_WARPS,   // one warp per lane fills the band-pass slots

@@ -23,40 +23,62 @@ enum { NORM_MAX = 624 };       // 8 * eband(20): the longest fold buffer (bands.
 struct BandsSmem {
   float win2[2][2 * WIN_Y];    // x | y of the current band, and of the next one on its way in (cp.async)
   float scratch[176];          // transformed copy of the fold source
-  float tmp[176];              // permutation scratch
+  float tmp[MB_ON_DEVICE ? 4 : 176];   // permutation scratch (host emulation only: the device permutes through registers)
   float norm[2 * NORM_MAX];    // fold buffers (norm | norm2)
   float gains[2 * NB_EBANDS];
-  float red[4];
 };
 
-// Window of operation words: lane l holds words (base + l) and (base + 32 + l); broadcast by shuffle.
+// Window of operation words: lane l holds words (wb + l) and (wb + 32 + l); broadcast by shuffle.
 struct OpReader {
   const uint32_t* ops;
-  int n_ops, pos, tid;
+  int n_ops, pos, wb, tid;
   uint32_t c0, c1;
-  MB_MEM void open(const uint32_t* o, int n, int lane) {
-    ops = o; n_ops = n; pos = 0; tid = lane; c0 = c1 = 0;
+  MB_MEM uint32_t fetch(int q) const {
 #if MB_ON_DEVICE
-    if (lane < n) c0 = __ldg(o + (size_t)lane * 32);
-    if (lane + 32 < n) c1 = __ldg(o + (size_t)(lane + 32) * 32);
+    return q < n_ops ? __ldg(ops + (size_t)q * 32) : 0u;
+#else
+    return 0u;
 #endif
+  }
+  MB_MEM void open(const uint32_t* o, int n, int lane) {
+    ops = o; n_ops = n; pos = 0; wb = 0; tid = lane;
+    c0 = fetch(lane); c1 = fetch(lane + 32);
   }
   MB_MEM uint32_t next() {
     const int p = pos++;
 #if MB_ON_DEVICE
-    const int slot = p & 31;
-    if (slot == 0 && p != 0) {
-      c0 = c1;
-      const int q = p + 32 + tid;
-      c1 = q < n_ops ? __ldg(ops + (size_t)q * 32) : 0u;
-    }
-    return __shfl_sync(0xffffffffu, c0, slot);
+    if (p - wb >= 32) { wb += 32; c0 = c1; c1 = fetch(wb + 32 + tid); }
+    return __shfl_sync(0xffffffffu, c0, p - wb);
 #else
     return ops[(size_t)p * 32];
 #endif
   }
-  MB_MEM void skip(int n) { for (int i = 0; i < n; i++) (void)next(); }
+  MB_MEM void skip(int n) {
+    pos += n;
+#if MB_ON_DEVICE
+    if (pos - wb >= 64) { wb = pos & ~31; c0 = fetch(wb + tid); c1 = fetch(wb + 32 + tid); }
+#endif
+  }
 };
+
+// Sum over the team. On the device the 32 partial sums meet in a butterfly: the result differs from the reference's
+// left-to-right sum by rounding only (the north star's PCM tolerance is 1 LSB at 16 bits; no decision of the decoder
+// depends on these sums). A team of one (host emulation) adds in the reference's order.
+MB_DEV float team_sum(Team tm, float v) {
+#if MB_ON_DEVICE
+#pragma unroll
+  for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+#endif
+  return v;
+}
+// 1 / sqrt(x): MUFU.RSQ on the device (2 ulp), the reference's 1.0 / sqrt(x) in the emulation
+MB_DEV float band_rsqrt(float x) {
+#if MB_ON_DEVICE
+  return rsqrtf(x);
+#else
+  return celt_rsqrt(x);
+#endif
+}
 
 MB_DEV void team_haar1(Team tm, float* x, int n0, int stride) {
   if (n0 < 2) return;
@@ -74,43 +96,54 @@ MB_DEV void team_haar1(Team tm, float* x, int n0, int stride) {
   MB_SYNC();
 }
 MB_DEV const uint8_t* ordery_for(int stride) { return kOrdery + (stride == 2 ? 0 : stride == 4 ? 2 : stride == 8 ? 6 : 14); }
-MB_DEV void team_deinterleave(Team tm, float* x, float* tmp, int n0, int stride, int hadamard) {
+// (de)interleave_hadamard: a permutation of at most 176 samples. Device: every lane picks up its (at most six) source
+// samples, the warp synchronises, every lane drops them at their destinations — no scratch copy.
+MB_DEV void team_permute(Team tm, float* x, float* tmp, int n0, int stride, int hadamard, int inverse) {
   const int n = n0 * stride;
   const uint8_t* ord = ordery_for(stride);
   const int sl = ilog2_exact(stride);
+#if MB_ON_DEVICE
+  float v[6];
+#pragma unroll
+  for (int k = 0; k < 6; k++) {
+    const int idx = tm.tid + 32 * k;
+    if (idx < n) {
+      const int i = idx & (stride - 1), j = idx >> sl;
+      const int o = (hadamard ? (int)ord[i] : i) * n0 + j;
+      v[k] = inverse ? x[o] : x[idx];      // interleave: x'[idx] = x[o];  deinterleave: x'[o] = x[idx]
+    }
+  }
+  MB_SYNC();
+#pragma unroll
+  for (int k = 0; k < 6; k++) {
+    const int idx = tm.tid + 32 * k;
+    if (idx < n) {
+      const int i = idx & (stride - 1), j = idx >> sl;
+      const int o = (hadamard ? (int)ord[i] : i) * n0 + j;
+      x[inverse ? idx : o] = v[k];
+    }
+  }
+  MB_SYNC();
+#else
   for (int idx = tm.tid; idx < n; idx += tm.n) {
     int i = idx & (stride - 1), j = idx >> sl;
-    int dst = (hadamard ? (int)ord[i] : i) * n0 + j;
-    tmp[dst] = x[idx];
+    int o = (hadamard ? (int)ord[i] : i) * n0 + j;
+    if (inverse) tmp[idx] = x[o]; else tmp[o] = x[idx];
   }
   MB_SYNC();
   for (int idx = tm.tid; idx < n; idx += tm.n) x[idx] = tmp[idx];
   MB_SYNC();
+#endif
 }
-MB_DEV void team_interleave(Team tm, float* x, float* tmp, int n0, int stride, int hadamard) {
-  const int n = n0 * stride;
-  const uint8_t* ord = ordery_for(stride);
-  const int sl = ilog2_exact(stride);
-  for (int idx = tm.tid; idx < n; idx += tm.n) {
-    int i = idx & (stride - 1), j = idx >> sl;
-    int src = (hadamard ? (int)ord[i] : i) * n0 + j;
-    tmp[idx] = x[src];
-  }
-  MB_SYNC();
-  for (int idx = tm.tid; idx < n; idx += tm.n) x[idx] = tmp[idx];
-  MB_SYNC();
-}
-// renormalise_vector (vq.rs:1073-1088): the energy sum keeps the reference's left-to-right order
+MB_DEV void team_deinterleave(Team tm, float* x, float* tmp, int n0, int stride, int hadamard) { team_permute(tm, x, tmp, n0, stride, hadamard, 0); }
+MB_DEV void team_interleave(Team tm, float* x, float* tmp, int n0, int stride, int hadamard) { team_permute(tm, x, tmp, n0, stride, hadamard, 1); }
+// renormalise_vector (vq.rs:1073-1088)
 MB_DEV void team_renormalise(Team tm, BandsSmem* sm, float* x, int n, float gain) {
   MB_SYNC();
-  if (tm.tid == 0) {
-    float e = 0.f;
-    for (int i = 0; i < n; i++) e += x[i] * x[i];
-    e = 1e-15f + e;
-    sm->red[0] = celt_rsqrt(e) * gain;
-  }
-  MB_SYNC();
-  const float scale = sm->red[0];
+  float e = 0.f;
+  for (int i = tm.tid; i < n; i += tm.n) e += x[i] * x[i];
+  e = 1e-15f + team_sum(tm, e);
+  const float scale = band_rsqrt(e) * gain;
   for (int i = tm.tid; i < n; i += tm.n) x[i] *= scale;
   MB_SYNC();
 }
@@ -245,24 +278,18 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
           for (int j = tm.tid; j < len; j += tm.n) dst[j] = scale * x[j];
           MB_SYNC();
         } break;
-        case OP_MERGE: {  // stereo_merge (bands.rs:3477-3505): the two inner products keep the reference's summation order
+        case OP_MERGE: {  // stereo_merge (bands.rs:3477-3505)
           const float mid = (float)(int)(ops.next() & 0xffffu) / 32768.0f;
           float* xx = win;
           float* yy = win + WIN_Y;
-          for (int q = tm.tid; q < 2; q += tm.n) {
-            const float* o = q ? yy : xx;
-            float acc = 0.f;
-            for (int j = 0; j < len; j++) acc += yy[j] * o[j];
-            sm->red[q] = acc;
-          }
-          MB_SYNC();
-          const float xp = sm->red[0] * mid, sd = sm->red[1];
+          float a0 = 0.f, a1 = 0.f;
+          for (int j = tm.tid; j < len; j += tm.n) { const float yv = yy[j]; a0 += yv * xx[j]; a1 += yv * yv; }
+          const float xp = team_sum(tm, a0) * mid, sd = team_sum(tm, a1);
           const float mid2 = mid * mid;
           const float el = mid2 + sd - 2.0f * xp, er = mid2 + sd + 2.0f * xp;
           const int degenerate = er < 6e-4f || el < 6e-4f;
-          const float lgain = degenerate ? 0.f : celt_rsqrt(el), rgain = degenerate ? 0.f : celt_rsqrt(er);
+          const float lgain = degenerate ? 0.f : band_rsqrt(el), rgain = degenerate ? 0.f : band_rsqrt(er);
           const int inv = (int)(p & 1u);
-          MB_SYNC();
           for (int j = tm.tid; j < len; j += tm.n) {
             float yv;
             if (degenerate) yv = xx[j];

@@ -66,20 +66,37 @@ enum { EN_STRIDE = 3 * 2 * NB_EBANDS,
 // flags bit 9 (512): CELT-only frame behind a SILK-side frame of the same pass; bits 10-19 / 20-29: fold-buffer words
 // [lo, hi) a CELT-only frame of the parallel band pass writes back (the part no later frame of the pass overwrites)  // per-frame energy scratch: E, prev1 (old_log_e), prev2 (old_log_e2)
 
-// One lane = one stream. Frame (grid cell) of tick t is f = t * n_lanes + lane; its packet index (for the
-// per-packet outputs) is pkt_map ? pkt_map[f] : f. Cells without a packet carry S_STATUS bit 15.
-MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, const uint32_t* pkt_map, const uint32_t* rec,
-                             StreamState* st_all, const uint32_t* lane_stream, float* en, FrameMeta* meta, int32_t* samples_out,
-                             uint32_t* final_range_out, uint32_t quirks, const uint8_t* flags = nullptr, int serial_all = 0,
-                             int force_float_row = 0) {
+struct Team { int tid, n; };
+
+// Shared-memory working set of one stream: the four energy histories, this frame's coarse symbols.
+struct EnergySmem { float E[2 * NB_EBANDS], le[2 * NB_EBANDS], le2[2 * NB_EBANDS], bg[2 * NB_EBANDS], q[2 * NB_EBANDS]; };
+
+// One team (a warp; one thread in the host emulation) = one stream, its ticks in order. Frame (grid cell) of tick t is
+// f = t * n_lanes + lane; its packet index (for the per-packet outputs) is pkt_map ? pkt_map[f] : f. Cells without a packet
+// carry S_STATUS bit 15. The front-end bookkeeping is scalar and runs redundantly on every lane (the words it reads are
+// the same for the whole team); the 42 band energies are spread over the lanes: the coarse-energy predictor's running
+// term prev[c] of band i is the left-to-right sum of the lower bands' symbols, which every lane rebuilds for its own
+// band in the reference's order, so the result is bit-identical to the serial loop.
+MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, const uint32_t* pkt_map,
+                               const uint32_t* rec, StreamState* st_all, const uint32_t* lane_stream, float* en, FrameMeta* meta,
+                               int32_t* samples_out, uint32_t* final_range_out, uint32_t quirks, const uint8_t* flags = nullptr,
+                               int serial_all = 0, int force_float_row = 0) {
   StreamState& st = st_all[lane_stream ? lane_stream[lane] : lane];
+  const bool lead = tm.tid == 0;
+  for (int i = tm.tid; i < 2 * NB_EBANDS; i += tm.n) {
+    sm->E[i] = st.old_ebands[i]; sm->le[i] = st.old_log_e[i]; sm->le2[i] = st.old_log_e2[i]; sm->bg[i] = st.background_log_e[i];
+  }
+  uint32_t st_rng = st.rng, st_range_final = st.range_final;
+  int st_loss_duration = st.loss_duration, st_prev_mode = st.prev_mode, st_last_duration = st.last_packet_duration;
+  int st_celt_error = st.celt_error, st_prev_redundancy = st.prev_redundancy, st_fold_serial = st.fold_serial;
+  MB_SYNC();
   uint32_t sample_off = 0;
   // Band pass of CELT-only frames. The reference's fold buffer outlives the frame (mb_celt_bands.cuh), so only a pass that
   // walks a stream's frames in order reproduces it exactly: that is what runs whenever the call has enough streams to
   // fill the machine that way (serial_all), and for every stream that has decoded a SILK-side frame (hybrid, fade-out,
   // redundancy: the frames that read the buffer). Otherwise CELT-only frames run all at once and write back the part of
   // their footprint that survives the pass: exact for CELT-only streams, whose frames never read the buffer.
-  bool silk_side_seen = serial_all || st.fold_serial;
+  bool silk_side_seen = serial_all || st_fold_serial;
   bool pkt_failed = false;   // an earlier frame of the same multi-frame packet failed: the reference returns there
                              // (src/opus_decoder.rs:1339-1350), so the remaining frames must not touch the stream
   // Output route of the packet, decided once for all its frames (MB_FL_F32ROW): SILK-only packets may leave k_silk as
@@ -91,8 +108,8 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
     const uint32_t* r = rec + rec_index(f, 0);
     uint32_t status = r[S_STATUS * 32];
     FrameMeta m;
-    m.seed_in = st.rng; m.sample_off = sample_off; m.lane = lane; m.flags = 0;
-    if (MB_ST_EMPTY(status)) { meta[f] = m; continue; }
+    m.seed_in = st_rng; m.sample_off = sample_off; m.lane = lane; m.flags = 0;
+    if (MB_ST_EMPTY(status)) { if (lead) meta[f] = m; continue; }
     const uint32_t p = pkt_map ? pkt_map[f] : f;
     const bool continuation = flags && (flags[p] & 4u);
     if (!continuation) {
@@ -110,16 +127,15 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
       pkt_route = celt_part ? MB_FL_F32ROW : 0u;
     }
     if (pkt_failed || !MB_ST_DECODED(status)) {  // rejected before the decoder ran (unsupported mode, PLC, bad TOC)
-      meta[f] = m;
-      samples_out[p] = pkt_failed ? MB_UNIMPLEMENTED : MB_ST_CODE(status);
-      final_range_out[p] = st.range_final;
+      if (lead) {
+        meta[f] = m;
+        samples_out[p] = pkt_failed ? MB_UNIMPLEMENTED : MB_ST_CODE(status);
+        final_range_out[p] = st_range_final;
+      }
       pkt_failed = true;
       continue;
     }
     uint32_t h0 = r[S_HDR0 * 32];
-    // Mode switches that go through decode_frame(None) = concealment (opus_decoder.rs:575-593, 798-809: CELT-only <->
-    // SILK-only / hybrid) or through the 2.5 ms CELT silence frame (hybrid -> SILK-only, :868-893) are rows F1/F2: reported
-    // per packet without touching the stream.
     const bool silk_bit = ((status >> 16) & 1u) != 0, hybrid = ((status >> 17) & 1u) != 0;
     // bit 18: SILK-only cell whose record sits in the hybrid layout; bits 19-20: the CELT frame sharing the cell (parse_cell):
     // 1 the 2.5 ms silence frame that lets the CELT overlap fade out after a hybrid packet (opus_decoder.rs:868-893, parsed
@@ -127,20 +143,22 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
     // CELT -> SILK / SILK -> CELT switch (opus_decoder.rs:746-797, 1012-1080).
     const bool silk_layout = ((status >> 18) & 1u) != 0;
     const int aux = (int)((status >> 19) & 3u);
-    const bool fadeout = aux == 1 && st.prev_mode == 1001;
+    const bool fadeout = aux == 1 && st_prev_mode == 1001;
     const bool red = aux >= 2;
     const bool silk_only = silk_bit && !hybrid && !fadeout && !red;
     // Mode switches that need concealment (decode_frame(None), opus_decoder.rs:575-593, 798-809) are row F2: reported per
     // packet without touching the stream. A redundancy frame makes the switch clean: CELT -> SILK when the SILK packet
     // carries one, SILK -> CELT when the previous SILK packet ended in one.
     bool reject;
-    if (!silk_bit) reject = st.prev_mode == 1001 || (st.prev_mode == 1000 && !st.prev_redundancy);
-    else if (red) reject = hybrid || st.prev_mode == 1001;   // would need two CELT frames in the cell (fade-out + redundancy)
-    else reject = st.prev_mode == 1002 || (silk_only && st.prev_mode == 1001);
+    if (!silk_bit) reject = st_prev_mode == 1001 || (st_prev_mode == 1000 && !st_prev_redundancy);
+    else if (red) reject = hybrid || st_prev_mode == 1001;   // would need two CELT frames in the cell (fade-out + redundancy)
+    else reject = st_prev_mode == 1002 || (silk_only && st_prev_mode == 1001);
     if (reject) {
-      meta[f] = m;
-      samples_out[p] = MB_UNIMPLEMENTED;
-      final_range_out[p] = st.range_final;
+      if (lead) {
+        meta[f] = m;
+        samples_out[p] = MB_UNIMPLEMENTED;
+        final_range_out[p] = st_range_final;
+      }
       pkt_failed = true;
       continue;
     }
@@ -148,133 +166,148 @@ MB_DEV void celt_energy_lane(uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, 
     const uint32_t silk_h0 = silk_layout ? r[S_SILK_HYB * 32] : h0;
     const uint32_t silk_rng = silk_layout ? r[(S_SILK_HYB + 342) * 32] : r[S_RANGE * 32];
     const int silk_n = (int)((silk_h0 >> 8) & 3u) * (int)((silk_h0 >> 5) & 7u) * 240;   // frames x subframes: 2, 4, 8, 12 -> 10 .. 60 ms
-    const uint32_t silk_reset = (silk_bit && st.prev_mode == 1002) ? 32u : 0u;          // opus_decoder.rs:694-696
+    const uint32_t silk_reset = (silk_bit && st_prev_mode == 1002) ? 32u : 0u;          // opus_decoder.rs:694-696
     if (silk_only) {  // SILK-only packet: synthesis runs in k_silk (mb_silk_out.cuh); here only the front-end bookkeeping
       const int N = silk_n;
       m.flags = 2u | silk_reset | pkt_route;
-      meta[f] = m;
-      st.prev_mode = 1000;
-      st.prev_redundancy = 0;
-      st.range_final = silk_rng;
-      st.last_packet_duration = N;
-      samples_out[p] = N;
-      final_range_out[p] = st.range_final;
+      st_prev_mode = 1000;
+      st_prev_redundancy = 0;
+      st_range_final = silk_rng;
+      st_last_duration = N;
+      if (lead) {
+        meta[f] = m;
+        samples_out[p] = N;
+        final_range_out[p] = st_range_final;
+      }
       continue;
     }
     // SILK-only -> hybrid: the CELT decoder is reset before the frame (opus_decoder.rs:895-898). The energy side is reset
     // here; the tail kernels reset their own state (post-filter, history, de-emphasis memory) on flag bit 2.
     // (also before a SILK -> CELT redundancy frame, opus_decoder.rs:1040-1046; not after a packet that ended in one)
-    const bool celt_reset = (hybrid && st.prev_mode == 1000 && !st.prev_redundancy) || aux == 3;
+    const bool celt_reset = (hybrid && st_prev_mode == 1000 && !st_prev_redundancy) || aux == 3;
     if (celt_reset) {
-      for (int i = 0; i < 2 * NB_EBANDS; i++) { st.old_ebands[i] = 0.f; st.old_log_e[i] = -28.f; st.old_log_e2[i] = -28.f; st.background_log_e[i] = 0.f; }
-      st.rng = 0; st.loss_duration = 0;
+      MB_SYNC();
+      for (int i = tm.tid; i < 2 * NB_EBANDS; i += tm.n) { sm->E[i] = 0.f; sm->le[i] = -28.f; sm->le2[i] = -28.f; sm->bg[i] = 0.f; }
+      st_rng = 0; st_loss_duration = 0;
       m.seed_in = 0;
     }
     const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), start = (int)MB_H0_START(h0), end = (int)MB_ST_END(status);
     const int intra = (int)MB_H0_INTRA(h0), silence = (int)MB_H0_SILENCE(h0), transient = (int)MB_H0_TRANSIENT(h0);
     const int M = 1 << lm;
-    float* E = st.old_ebands;
-    if (C == 1)
-      for (int i = 0; i < NB_EBANDS; i++) E[i] = fmax32(E[i], E[NB_EBANDS + i]);
+    float* E = sm->E;
+    MB_SYNC();
+    // this frame's symbols: every lane fetches the words of its own (channel, band) slots
+    uint32_t wmine[2] = {0, 0};   // team of 32: slots tid and tid + 32; team of one: read again below
+    for (int idx = tm.tid, k = 0; idx < 2 * NB_EBANDS; idx += tm.n, k++) {
+      const int c = idx >= NB_EBANDS, i = idx - c * NB_EBANDS;
+      uint32_t w = 0;
+      if (c < C && i >= start && i < end) w = r[(S_ENERGY + idx) * 32];
+      if (k < 2) wmine[k] = w;
+      sm->q[idx] = (float)(int)(int16_t)(w & 0xffffu);
+      if (C == 1 && idx < NB_EBANDS) E[idx] = fmax32(E[idx], E[NB_EBANDS + idx]);
+    }
+    MB_SYNC();
     // coarse + fine + finalise (three separate float additions per band, in the reference's order)
     {
-      float prev[2] = {0.f, 0.f};
       const float coef = intra ? 0.f : kPredCoef[lm];
       const float beta = intra ? 4915.f / 32768.f : kBetaCoef[lm];
-      for (int i = start; i < end; i++)
-        for (int c = 0; c < C; c++) {
-          int idx = c * NB_EBANDS + i;
-          float q = (float)(int)(int16_t)(r[(S_ENERGY + idx) * 32] & 0xffffu);
-          float o = fmax32(E[idx], -9.0f);
-          float tmp = coef * o + prev[c] + q;
-          if (quirks & Q8_COARSE_CLAMP) {
-            tmp = tmp < -28.f ? -28.f : (tmp > 28.f ? 28.f : tmp);
-            prev[c] += q - beta * q;
-          } else prev[c] = prev[c] + q - beta * q;
-          E[idx] = tmp;
+      for (int idx = tm.tid, k = 0; idx < 2 * NB_EBANDS; idx += tm.n, k++) {
+        const int c = idx >= NB_EBANDS, i = idx - c * NB_EBANDS;
+        if (c >= C || i < start || i >= end) continue;
+        const float* qc = sm->q + c * NB_EBANDS;
+        float prev = 0.f;
+        if (quirks & Q8_COARSE_CLAMP) { for (int j = start; j < i; j++) prev += qc[j] - beta * qc[j]; }
+        else for (int j = start; j < i; j++) prev = prev + qc[j] - beta * qc[j];
+        const float q = qc[i];
+        const float o = fmax32(E[idx], -9.0f);
+        float tmp = coef * o + prev + q;
+        if (quirks & Q8_COARSE_CLAMP) tmp = tmp < -28.f ? -28.f : (tmp > 28.f ? 28.f : tmp);
+        const uint32_t w = (tm.n >= 32 && k < 2) ? wmine[k] : r[(S_ENERGY + idx) * 32];
+        const int fq = (int)((w >> 24) & 15u);
+        if (fq > 0) {
+          const float scale = (float)(1 << (14 - fq)) * (1.0f / 16384.0f);
+          tmp += ((float)(int)((w >> 16) & 255u) + 0.5f) * scale - 0.5f;
         }
-      for (int i = start; i < end; i++)
-        for (int c = 0; c < C; c++) {
-          int idx = c * NB_EBANDS + i;
-          uint32_t w = r[(S_ENERGY + idx) * 32];
-          int fq = (int)((w >> 24) & 15u);
-          if (fq > 0) {
-            float scale = (float)(1 << (14 - fq)) * (1.0f / 16384.0f);
-            E[idx] += ((float)(int)((w >> 16) & 255u) + 0.5f) * scale - 0.5f;
-          }
+        // finalise: every (band, channel) receives at most one extra bit, so the two priority passes of the reference
+        // collapse into one addition
+        if (w & (1u << 28)) {
+          const float scale = (float)(1 << (14 - fq - 1)) * (1.0f / 16384.0f);
+          tmp += ((float)(int)((w >> 29) & 1u) - 0.5f) * scale;
         }
-      // finalise: every (band, channel) receives at most one extra bit, so the two priority passes
-      // of the reference collapse into one sweep
-      for (int i = start; i < end; i++)
-        for (int c = 0; c < C; c++) {
-          int idx = c * NB_EBANDS + i;
-          uint32_t w = r[(S_ENERGY + idx) * 32];
-          if (w & (1u << 28)) {
-            int fq = (int)((w >> 24) & 15u);
-            float scale = (float)(1 << (14 - fq - 1)) * (1.0f / 16384.0f);
-            E[idx] += ((float)(int)((w >> 29) & 1u) - 0.5f) * scale;
-          }
-        }
+        E[idx] = tmp;
+      }
     }
+    MB_SYNC();
     float* ef = en + (size_t)f * EN_STRIDE;
-    if (MB_H0_ACON(h0))
-      for (int i = 0; i < 2 * NB_EBANDS; i++) { ef[2 * NB_EBANDS + i] = st.old_log_e[i]; ef[4 * NB_EBANDS + i] = st.old_log_e2[i]; }
-    if (silence)
-      for (int i = 0; i < 2 * NB_EBANDS; i++) E[i] = -28.0f;
-    for (int i = 0; i < 2 * NB_EBANDS; i++) ef[i] = E[i];
-    // state rotation (celt_decoder.rs:4023-4062)
-    if (C == 1)
-      for (int i = 0; i < NB_EBANDS; i++) E[NB_EBANDS + i] = E[i];
-    if (transient) {
-      for (int i = 0; i < 2 * NB_EBANDS; i++) st.old_log_e[i] = fmin32(st.old_log_e[i], E[i]);
-    } else {
-      for (int i = 0; i < 2 * NB_EBANDS; i++) { st.old_log_e2[i] = st.old_log_e[i]; st.old_log_e[i] = E[i]; }
+    const float increase = (float)imin(st_loss_duration + M, 160) * 0.001f;
+    // (two sweeps with the team's barrier between them: a lane reads E[i] of the other channel before anyone rewrites it.
+    //  The host emulation, a team of one, runs the first sweep into a scratch copy.)
+#if MB_ON_DEVICE
+    float ne[2], nl1[2], nl2[2];
+#else
+    float ne[2 * NB_EBANDS], nl1[2 * NB_EBANDS], nl2[2 * NB_EBANDS];
+#endif
+    for (int idx = tm.tid, k = 0; idx < 2 * NB_EBANDS; idx += tm.n, k++) {
+      const int c = idx >= NB_EBANDS, i = idx - c * NB_EBANDS;
+      if (MB_H0_ACON(h0)) { ef[2 * NB_EBANDS + idx] = sm->le[idx]; ef[4 * NB_EBANDS + idx] = sm->le2[idx]; }
+      float e = silence ? -28.0f : E[idx];
+      ef[idx] = e;
+      // state rotation (celt_decoder.rs:4023-4062)
+      if (C == 1 && c == 1) e = silence ? -28.0f : E[i];
+      float l1 = sm->le[idx], l2 = sm->le2[idx];
+      if (transient) l1 = fmin32(l1, e); else { l2 = l1; l1 = e; }
+      sm->bg[idx] = fmin32(sm->bg[idx] + increase, e);
+      if (i < start || i >= end) { e = 0.f; l1 = l2 = -28.0f; }
+      ne[k] = e; nl1[k] = l1; nl2[k] = l2;
     }
-    float increase = (float)imin(st.loss_duration + M, 160) * 0.001f;
-    for (int i = 0; i < 2 * NB_EBANDS; i++) st.background_log_e[i] = fmin32(st.background_log_e[i] + increase, E[i]);
-    for (int c = 0; c < 2; c++) {
-      for (int i = 0; i < start; i++) { E[c * NB_EBANDS + i] = 0.f; st.old_log_e[c * NB_EBANDS + i] = st.old_log_e2[c * NB_EBANDS + i] = -28.0f; }
-      for (int i = end; i < NB_EBANDS; i++) { E[c * NB_EBANDS + i] = 0.f; st.old_log_e[c * NB_EBANDS + i] = st.old_log_e2[c * NB_EBANDS + i] = -28.0f; }
-    }
-    st.rng = r[S_RANGE * 32];
-    st.loss_duration = 0;
-    if (status & (1u << 13)) st.celt_error = 1;
+    MB_SYNC();
+    for (int idx = tm.tid, k = 0; idx < 2 * NB_EBANDS; idx += tm.n, k++) { E[idx] = ne[k]; sm->le[idx] = nl1[k]; sm->le2[idx] = nl2[k]; }
+    st_rng = r[S_RANGE * 32];
+    st_loss_duration = 0;
+    if (status & (1u << 13)) st_celt_error = 1;
     const int N = (fadeout || red) ? silk_n : M * SHORT_MDCT;   // samples the packet delivers
     if (red) {
       m.flags = 1u | 2u | 16u | (celt_reset ? 4u : 0u) | silk_reset;
       if (aux == 3) m.flags |= 128u;
-      else if (st.prev_mode != 1000 || st.prev_redundancy) m.flags |= 64u;   // opus_decoder.rs:1066
+      else if (st_prev_mode != 1000 || st_prev_redundancy) m.flags |= 64u;   // opus_decoder.rs:1066
     } else m.flags = (hybrid || fadeout) ? (1u | 2u | 8u | (celt_reset ? 4u : 0u)) : (silk_side_seen ? (1u | 512u) : 1u);
-    if (m.flags & (8u | 16u)) { silk_side_seen = true; st.fold_serial = 1; }
+    if (m.flags & (8u | 16u)) { silk_side_seen = true; st_fold_serial = 1; }
     m.flags |= MB_FL_F32ROW;
-    meta[f] = m;
+    if (lead) meta[f] = m;
     sample_off += (uint32_t)(M * SHORT_MDCT);                 // the CELT time line advances by the CELT frame
     int code = MB_ST_CODE(status);
     if (code < 0) {  // e.g. bit-budget overrun: state has advanced, the call reports the error (celt_decoder.rs:4128)
-      samples_out[p] = code;
-      final_range_out[p] = st.range_final;
+      if (lead) { samples_out[p] = code; final_range_out[p] = st_range_final; }
     } else {
-      st.prev_mode = (fadeout || red) ? 1000 : (hybrid ? 1001 : 1002);
-      st.prev_redundancy = aux == 3;
-      st.range_final = fadeout ? silk_rng : (red ? (silk_rng ^ st.rng) : st.rng);
-      st.last_packet_duration = N;
-      samples_out[p] = N;
-      final_range_out[p] = st.range_final;
+      st_prev_mode = (fadeout || red) ? 1000 : (hybrid ? 1001 : 1002);
+      st_prev_redundancy = aux == 3;
+      st_range_final = fadeout ? silk_rng : (red ? (silk_rng ^ st_rng) : st_rng);
+      st_last_duration = N;
+      if (lead) { samples_out[p] = N; final_range_out[p] = st_range_final; }
     }
   }
-  // Fold-buffer write-back of the parallel band pass (mb_celt_bands.cuh): walking the lane's CELT-only frames backwards,
-  // each one keeps the words of its footprint that no later frame of the pass covers. A frame's footprint is the first
-  // C * norm_len words of the reference's storage (bands.rs:2614-2625), capped at what hybrid frames can read.
-  int covered = 0;
-  for (uint32_t t = n_ticks; t-- > 0 && covered < (int)FOLD_WORDS;) {
-    const uint32_t f = t * n_lanes + lane;
-    const uint32_t fl = meta[f].flags;
-    if (!(fl & 1u) || (fl & MB_FL_FOLD)) continue;
-    const uint32_t h0 = rec[rec_index(f, S_HDR0)];
-    const int top = imin((int)MB_H0_C(h0) * ((int)eband(NB_EBANDS - 1) << (int)MB_H0_LM(h0)), (int)FOLD_WORDS);   // even
-    if (top > covered) {
-      meta[f].flags = fl | ((uint32_t)(covered >> 1) << 10) | ((uint32_t)(top >> 1) << 20);
-      covered = top;
+  MB_SYNC();
+  for (int i = tm.tid; i < 2 * NB_EBANDS; i += tm.n) {
+    st.old_ebands[i] = sm->E[i]; st.old_log_e[i] = sm->le[i]; st.old_log_e2[i] = sm->le2[i]; st.background_log_e[i] = sm->bg[i];
+  }
+  if (lead) {
+    st.rng = st_rng; st.range_final = st_range_final; st.loss_duration = st_loss_duration; st.prev_mode = st_prev_mode;
+    st.last_packet_duration = st_last_duration; st.celt_error = st_celt_error; st.prev_redundancy = st_prev_redundancy;
+    st.fold_serial = st_fold_serial;
+    // Fold-buffer write-back of the parallel band pass (mb_celt_bands.cuh): walking the lane's CELT-only frames backwards,
+    // each one keeps the words of its footprint that no later frame of the pass covers. A frame's footprint is the first
+    // C * norm_len words of the reference's storage (bands.rs:2614-2625), capped at what hybrid frames can read.
+    int covered = 0;
+    for (uint32_t t = n_ticks; t-- > 0 && covered < (int)FOLD_WORDS;) {
+      const uint32_t f = t * n_lanes + lane;
+      const uint32_t fl = meta[f].flags;
+      if (!(fl & 1u) || (fl & MB_FL_FOLD)) continue;
+      const uint32_t h0 = rec[rec_index(f, S_HDR0)];
+      const int top = imin((int)MB_H0_C(h0) * ((int)eband(NB_EBANDS - 1) << (int)MB_H0_LM(h0)), (int)FOLD_WORDS);   // even
+      if (top > covered) {
+        meta[f].flags = fl | ((uint32_t)(covered >> 1) << 10) | ((uint32_t)(top >> 1) << 20);
+        covered = top;
+      }
     }
   }
 }

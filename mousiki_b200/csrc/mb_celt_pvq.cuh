@@ -18,7 +18,6 @@ namespace mb {
 
 enum { XBUF_STRIDE = 2 * MAX_N };   // floats per frame in the spectrum buffer (channel pitch N, packed)
 
-struct Team { int tid, n; };
 
 // ---------------------------------------------------------------- stage A: one PVQ leaf (one thread)
 // cwrsi (cwrs.rs:293-406) writing pulses straight into the spectrum as floats (|v| <= 128, exact).

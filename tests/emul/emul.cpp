@@ -53,12 +53,13 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
     parse_cell(arena, offsets, f, rec.data() + rec_index(f, 0), CC, quirks, disable_inv, (int)(pcm_stride / CC), nullptr,
                f >= n_lanes ? f - n_lanes : 0xffffffffu, f >= n_lanes ? nullptr : &st[f].prev_mode);
   // phase 2a
-  for (uint32_t j = 0; j < n_lanes; j++)
-    celt_energy_lane(j, n_lanes, n_ticks, nullptr, rec.data(), st.data(), nullptr, en.data(), meta.data(), samples_out, final_range_out, quirks,
-                     nullptr, getenv("MB_EMUL_PARALLEL_BANDS") ? 0 : 1,   // default: the per-stream band pass of large calls
-                     g_gain_q8 != 0 || !pcm16);
-  // phase 2b
   Team tm = {0, 1};
+  EnergySmem esm;
+  for (uint32_t j = 0; j < n_lanes; j++)
+    celt_energy_stream(tm, &esm, j, n_lanes, n_ticks, nullptr, rec.data(), st.data(), nullptr, en.data(), meta.data(), samples_out, final_range_out, quirks,
+                       nullptr, getenv("MB_EMUL_PARALLEL_BANDS") ? 0 : 1,   // default: the per-stream band pass of large calls
+                       g_gain_q8 != 0 || !pcm16);
+  // phase 2b
   std::vector<float> xbuf((size_t)F * XBUF_STRIDE, 0.f), xstage(2 * MAX_N);
   PvqParams pq; pq.rec = rec.data(); pq.meta = meta.data(); pq.xbuf = xbuf.data(); pq.iy_dbg = iy_dbg;
   for (uint32_t f = 0; f < F; f++) celt_pvq_frame(tm, xstage.data(), f, pq);
@@ -166,9 +167,10 @@ int emu_op_histogram(int CC, uint32_t quirks, const uint8_t* arena, const uint32
   for (uint32_t f = 0; f < F; f++)
     parse_cell(arena, offsets, f, rec.data() + rec_index(f, 0), CC, quirks, CC == 1, 960, nullptr, f >= n_lanes ? f - n_lanes : 0xffffffffu,
                f >= n_lanes ? nullptr : &st[f].prev_mode);
-  for (uint32_t j = 0; j < n_lanes; j++)
-    celt_energy_lane(j, n_lanes, n_ticks, nullptr, rec.data(), st.data(), nullptr, en.data(), meta.data(), so.data(), fr.data(), quirks, nullptr, 1, 1);
   Team tm = {0, 1};
+  EnergySmem esm;
+  for (uint32_t j = 0; j < n_lanes; j++)
+    celt_energy_stream(tm, &esm, j, n_lanes, n_ticks, nullptr, rec.data(), st.data(), nullptr, en.data(), meta.data(), so.data(), fr.data(), quirks, nullptr, 1, 1);
   std::vector<float> xbuf((size_t)F * XBUF_STRIDE, 0.f), xstage(2 * MAX_N);
   PvqParams pq; pq.rec = rec.data(); pq.meta = meta.data(); pq.xbuf = xbuf.data(); pq.iy_dbg = nullptr;
   for (uint32_t f = 0; f < F; f++) celt_pvq_frame(tm, xstage.data(), f, pq);
