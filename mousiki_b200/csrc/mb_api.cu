@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(128, 8) k_plan(PlanParams P, uint32_t n_cells)
 
 // one warp per frame; 4 frames per CTA
 constexpr int BANDS_WARPS = 4;
-__global__ void __launch_bounds__(32 * BANDS_WARPS) k_bands(BandsParams P, uint32_t n_cells) {
+__global__ void __launch_bounds__(32 * BANDS_WARPS, 6) k_bands(BandsParams P, uint32_t n_cells) {
   __shared__ BandsSmem sm[BANDS_WARPS];
   const uint32_t f = blockIdx.x * BANDS_WARPS + (threadIdx.x >> 5);
   if (f >= n_cells) return;
@@ -112,7 +112,7 @@ __global__ void __launch_bounds__(32 * BANDS_WARPS) k_bands(BandsParams P, uint3
 
 // Hybrid frames: one warp per lane, the lane's ticks in order, because the reference's fold buffer outlives the frame
 // (mb_celt_bands.cuh); `fold` is [stream][FOLD_WORDS].  Lanes without a hybrid frame leave after one pass over the flags.
-__global__ void __launch_bounds__(32 * BANDS_WARPS) k_bands_hyb(BandsParams P, uint32_t n_lanes, uint32_t n_ticks,
+__global__ void __launch_bounds__(32 * BANDS_WARPS, 6) k_bands_hyb(BandsParams P, uint32_t n_lanes, uint32_t n_ticks,
                                                                  const uint32_t* __restrict__ lane_stream, float* fold) {
   __shared__ BandsSmem sm[BANDS_WARPS];
   const uint32_t lane = blockIdx.x * BANDS_WARPS + (threadIdx.x >> 5);

@@ -23,7 +23,7 @@ enum { NORM_MAX = 624 };       // 8 * eband(20): the longest fold buffer (bands.
 struct BandsSmem {
   float win2[2][2 * WIN_Y];    // x | y of the current band, and of the next one on its way in (cp.async)
   float scratch[176];          // transformed copy of the fold source
-  float tmp[MB_ON_DEVICE ? 4 : 176];   // permutation scratch (host emulation only: the device permutes through registers)
+  float tmp[176];              // products on their way into a serial sum (and the permutation scratch of the host emulation)
   float norm[2 * NORM_MAX];    // fold buffers (norm | norm2)
   float gains[2 * NB_EBANDS];
 };
@@ -61,22 +61,26 @@ struct OpReader {
   }
 };
 
-// Sum over the team. On the device the 32 partial sums meet in a butterfly: the result differs from the reference's
-// left-to-right sum by rounding only (the north star's PCM tolerance is 1 LSB at 16 bits; no decision of the decoder
-// depends on these sums). A team of one (host emulation) adds in the reference's order.
-MB_DEV float team_sum(Team tm, float v) {
+// Left-to-right sum of p[0..n) — the reference's summation order (renormalise_vector, stereo_merge), which fixes the
+// rounding. The products were formed by the whole team; what is left for one lane is the chain of dependent additions,
+// fed by 128-bit shared-memory loads. p must be 16-byte aligned.
+MB_DEV float serial_sum(const float* p, int n) {
+  float e = 0.f;
+  int i = 0;
 #if MB_ON_DEVICE
-#pragma unroll
-  for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+  for (; i + 4 <= n; i += 4) {
+    const float4 v = *(const float4*)(p + i);
+    e += v.x; e += v.y; e += v.z; e += v.w;
+  }
 #endif
-  return v;
+  for (; i < n; i++) e += p[i];
+  return e;
 }
-// 1 / sqrt(x): MUFU.RSQ on the device (2 ulp), the reference's 1.0 / sqrt(x) in the emulation
-MB_DEV float band_rsqrt(float x) {
+MB_DEV float team_bcast(Team tm, float v, int src) {
 #if MB_ON_DEVICE
-  return rsqrtf(x);
+  return __shfl_sync(0xffffffffu, v, src);
 #else
-  return celt_rsqrt(x);
+  return v;
 #endif
 }
 
@@ -137,13 +141,14 @@ MB_DEV void team_permute(Team tm, float* x, float* tmp, int n0, int stride, int 
 }
 MB_DEV void team_deinterleave(Team tm, float* x, float* tmp, int n0, int stride, int hadamard) { team_permute(tm, x, tmp, n0, stride, hadamard, 0); }
 MB_DEV void team_interleave(Team tm, float* x, float* tmp, int n0, int stride, int hadamard) { team_permute(tm, x, tmp, n0, stride, hadamard, 1); }
-// renormalise_vector (vq.rs:1073-1088)
+// renormalise_vector (vq.rs:1073-1088): squares by the team, the energy sum in the reference's order by one lane
 MB_DEV void team_renormalise(Team tm, BandsSmem* sm, float* x, int n, float gain) {
   MB_SYNC();
-  float e = 0.f;
-  for (int i = tm.tid; i < n; i += tm.n) e += x[i] * x[i];
-  e = 1e-15f + team_sum(tm, e);
-  const float scale = band_rsqrt(e) * gain;
+  for (int i = tm.tid; i < n; i += tm.n) { const float v = x[i]; sm->tmp[i] = v * v; }
+  MB_SYNC();
+  float scale = 0.f;
+  if (tm.tid == 0) scale = celt_rsqrt(1e-15f + serial_sum(sm->tmp, n)) * gain;
+  scale = team_bcast(tm, scale, 0);
   for (int i = tm.tid; i < n; i += tm.n) x[i] *= scale;
   MB_SYNC();
 }
@@ -282,13 +287,19 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
           const float mid = (float)(int)(ops.next() & 0xffffu) / 32768.0f;
           float* xx = win;
           float* yy = win + WIN_Y;
-          float a0 = 0.f, a1 = 0.f;
-          for (int j = tm.tid; j < len; j += tm.n) { const float yv = yy[j]; a0 += yv * xx[j]; a1 += yv * yv; }
-          const float xp = team_sum(tm, a0) * mid, sd = team_sum(tm, a1);
+          // the two inner products keep the reference's summation order: products by the team, one lane per sum
+          // (the fold source in `scratch` is dead by the time a band's two channels are merged)
+          for (int j = tm.tid; j < len; j += tm.n) { const float yv = yy[j]; sm->tmp[j] = yv * xx[j]; sm->scratch[j] = yv * yv; }
+          MB_SYNC();
+          float acc = 0.f;
+          if (tm.tid < 2) acc = serial_sum(tm.tid ? sm->scratch : sm->tmp, len);
+          float xp, sd;
+          if (tm.n == 1) { xp = acc * mid; sd = serial_sum(sm->scratch, len); }
+          else { xp = team_bcast(tm, acc, 0) * mid; sd = team_bcast(tm, acc, 1); }
           const float mid2 = mid * mid;
           const float el = mid2 + sd - 2.0f * xp, er = mid2 + sd + 2.0f * xp;
           const int degenerate = er < 6e-4f || el < 6e-4f;
-          const float lgain = degenerate ? 0.f : band_rsqrt(el), rgain = degenerate ? 0.f : band_rsqrt(er);
+          const float lgain = degenerate ? 0.f : celt_rsqrt(el), rgain = degenerate ? 0.f : celt_rsqrt(er);
           const int inv = (int)(p & 1u);
           for (int j = tm.tid; j < len; j += tm.n) {
             float yv;
