@@ -20,7 +20,7 @@ MB_TBL uint8_t kOrdery[30] = {1, 0, 3, 0, 2, 1, 7, 0, 4, 3, 6, 1, 5, 2, 15, 0, 8
 
 // Shared-memory working set of one frame: 9.4 KB.
 enum { NORM_MAX = 624 };       // 8 * eband(20): the longest fold buffer (bands.rs:2614-2617)
-struct BandsSmem {
+struct alignas(16) BandsSmem {
   float win2[2][2 * WIN_Y];    // x | y of the current band, and of the next one on its way in (cp.async)
   float scratch[176];          // transformed copy of the fold source
   float tmp[176];              // products on their way into a serial sum (and the permutation scratch of the host emulation)
