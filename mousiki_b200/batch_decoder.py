@@ -16,7 +16,10 @@ from pathlib import Path
 
 import numpy as np
 
-_LIB_PATH = Path(__file__).resolve().parent / "libmousiki_b200.so"
+import os
+
+# MOUSIKI_B200_LIB: another build of the same library (A/B runs of kernel variants, tools/ab_build.sh)
+_LIB_PATH = Path(os.environ.get("MOUSIKI_B200_LIB") or Path(__file__).resolve().parent / "libmousiki_b200.so")
 QUIRKS_MOUSIKI = 0xF7F
 
 OPUS_BAD_ARG, OPUS_BUFFER_TOO_SMALL, OPUS_INTERNAL_ERROR, OPUS_INVALID_PACKET, OPUS_UNIMPLEMENTED = -1, -2, -3, -4, -5

@@ -14,8 +14,6 @@
 
 namespace mb {
 
-MB_TBL float kEMeans[25] = {6.4375f, 6.25f, 5.75f, 5.3125f, 5.0625f, 4.8125f, 4.5f, 4.375f, 4.875f, 4.6875f, 4.5625f, 4.4375f, 4.875f,
-                            4.625f, 4.3125f, 4.5f, 4.375f, 4.625f, 4.75f, 4.4375f, 3.75f, 3.75f, 3.75f, 3.75f, 3.75f};
 MB_TBL uint8_t kOrdery[30] = {1, 0, 3, 0, 2, 1, 7, 0, 4, 3, 6, 1, 5, 2, 15, 0, 8, 7, 12, 3, 11, 4, 14, 1, 9, 6, 13, 2, 10, 5};
 
 // Shared-memory working set of one frame: 9.4 KB.
@@ -68,11 +66,13 @@ MB_DEV float serial_sum(const float* p, int n) {
   float e = 0.f;
   int i = 0;
 #if MB_ON_DEVICE
+  MB_ROLLED
   for (; i + 4 <= n; i += 4) {
     const float4 v = *(const float4*)(p + i);
     e += v.x; e += v.y; e += v.z; e += v.w;
   }
 #endif
+  MB_ROLLED
   for (; i < n; i++) e += p[i];
   return e;
 }
@@ -84,12 +84,13 @@ MB_DEV float team_bcast(Team tm, float v, int src) {
 #endif
 }
 
-MB_DEV void team_haar1(Team tm, float* x, int n0, int stride) {
+MB_DEV_NOINLINE void team_haar1(Team tm, float* x, int n0, int stride) {
   if (n0 < 2) return;
   const int half = n0 / 2;
   const float scale = 0.70710678f;
   const int total = stride * half;
   const int sl = ilog2_exact(stride);   // stride is a power of two; the butterflies are independent, any order will do
+  MB_ROLLED
   for (int idx = tm.tid; idx < total; idx += tm.n) {
     int i = idx & (stride - 1), j = idx >> sl;
     int i0 = stride * 2 * j + i, i1 = i0 + stride;
@@ -100,55 +101,47 @@ MB_DEV void team_haar1(Team tm, float* x, int n0, int stride) {
   MB_SYNC();
 }
 MB_DEV const uint8_t* ordery_for(int stride) { return kOrdery + (stride == 2 ? 0 : stride == 4 ? 2 : stride == 8 ? 6 : 14); }
-// (de)interleave_hadamard: a permutation of at most 176 samples. Device: every lane picks up its (at most six) source
-// samples, the warp synchronises, every lane drops them at their destinations — no scratch copy.
-MB_DEV void team_permute(Team tm, float* x, float* tmp, int n0, int stride, int hadamard, int inverse) {
+// (de)interleave_hadamard: a permutation of at most 176 samples, through the scratch row
+MB_DEV_NOINLINE void team_permute(Team tm, float* x, float* tmp, int n0, int stride, int hadamard, int inverse) {
   const int n = n0 * stride;
   const uint8_t* ord = ordery_for(stride);
   const int sl = ilog2_exact(stride);
-#if MB_ON_DEVICE
-  float v[6];
-#pragma unroll
-  for (int k = 0; k < 6; k++) {
-    const int idx = tm.tid + 32 * k;
-    if (idx < n) {
-      const int i = idx & (stride - 1), j = idx >> sl;
-      const int o = (hadamard ? (int)ord[i] : i) * n0 + j;
-      v[k] = inverse ? x[o] : x[idx];      // interleave: x'[idx] = x[o];  deinterleave: x'[o] = x[idx]
-    }
-  }
-  MB_SYNC();
-#pragma unroll
-  for (int k = 0; k < 6; k++) {
-    const int idx = tm.tid + 32 * k;
-    if (idx < n) {
-      const int i = idx & (stride - 1), j = idx >> sl;
-      const int o = (hadamard ? (int)ord[i] : i) * n0 + j;
-      x[inverse ? idx : o] = v[k];
-    }
-  }
-  MB_SYNC();
-#else
+  MB_ROLLED
+  MB_ROLLED
   for (int idx = tm.tid; idx < n; idx += tm.n) {
-    int i = idx & (stride - 1), j = idx >> sl;
-    int o = (hadamard ? (int)ord[i] : i) * n0 + j;
-    if (inverse) tmp[idx] = x[o]; else tmp[o] = x[idx];
+    const int i = idx & (stride - 1), j = idx >> sl;
+    const int o = (hadamard ? (int)ord[i] : i) * n0 + j;
+    if (inverse) tmp[idx] = x[o]; else tmp[o] = x[idx];      // interleave: x'[idx] = x[o];  deinterleave: x'[o] = x[idx]
   }
   MB_SYNC();
+  MB_ROLLED
+  MB_ROLLED
   for (int idx = tm.tid; idx < n; idx += tm.n) x[idx] = tmp[idx];
   MB_SYNC();
-#endif
 }
 MB_DEV void team_deinterleave(Team tm, float* x, float* tmp, int n0, int stride, int hadamard) { team_permute(tm, x, tmp, n0, stride, hadamard, 0); }
 MB_DEV void team_interleave(Team tm, float* x, float* tmp, int n0, int stride, int hadamard) { team_permute(tm, x, tmp, n0, stride, hadamard, 1); }
-// renormalise_vector (vq.rs:1073-1088): squares by the team, the energy sum in the reference's order by one lane
-MB_DEV void team_renormalise(Team tm, BandsSmem* sm, float* x, int n, float gain) {
-  MB_SYNC();
-  for (int i = tm.tid; i < n; i += tm.n) { const float v = x[i]; sm->tmp[i] = v * v; }
+// renormalise_vector (vq.rs:1073-1088): the energy sum keeps the reference's left-to-right order
+#ifndef MB_BANDS_SUM_MODE
+#define MB_BANDS_SUM_MODE 0   // 0: one lane multiplies and adds (measured faster: 13.7 vs 14.1 ms per step); 1: the team multiplies, one lane adds (128-bit loads)
+#endif
+MB_DEV_NOINLINE void team_renormalise(Team tm, BandsSmem* sm, float* x, int n, float gain) {
   MB_SYNC();
   float scale = 0.f;
+#if MB_BANDS_SUM_MODE == 1
+  MB_ROLLED
+  for (int i = tm.tid; i < n; i += tm.n) { const float v = x[i]; sm->tmp[i] = v * v; }
+  MB_SYNC();
   if (tm.tid == 0) scale = celt_rsqrt(1e-15f + serial_sum(sm->tmp, n)) * gain;
+#else
+  if (tm.tid == 0) {
+    float e = 0.f;
+    for (int i = 0; i < n; i++) e += x[i] * x[i];
+    scale = celt_rsqrt(1e-15f + e) * gain;
+  }
+#endif
   scale = team_bcast(tm, scale, 0);
+  MB_ROLLED
   for (int i = tm.tid; i < n; i += tm.n) x[i] *= scale;
   MB_SYNC();
 }
@@ -189,9 +182,12 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
   // (loaded by the caller, left as the previous frame left it); the parallel path starts from zeros.
   float* norm2 = norm + norm_len;
   if (!serial) {
+    MB_ROLLED
     for (int i = tm.tid; i < 2 * NORM_MAX; i += tm.n) norm[i] = 0.f;
   }
-  for (int idx = tm.tid; idx < C * NB_EBANDS; idx += tm.n) sm->gains[idx] = celt_exp2(fmin32(E[idx] + kEMeans[idx % NB_EBANDS], 32.0f));
+  // band gains exp2(min(E + eMeans, 32)) (bands.rs:4172-4234): computed by the stream pass, which holds E anyway
+  MB_ROLLED
+  for (int idx = tm.tid; idx < C * NB_EBANDS; idx += tm.n) sm->gains[idx] = E[EN_GAINS + idx];
   OpReader ops;
   ops.open(r + S_OPS * 32, (int)plan, tm.tid);
   MB_SYNC();
@@ -199,6 +195,7 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
   // so the global-memory latency of the row is paid once per frame instead of once per band.
   auto fetch = [&](int band, float* w) {
     const int b0 = M * eband(band), nb = M * eband(band + 1) - b0;
+    MB_ROLLED
     for (int idx = tm.tid; idx < C * nb; idx += tm.n) {
       int c = idx >= nb, j = idx - c * nb;
 #if MB_ON_DEVICE
@@ -233,8 +230,10 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
         case OP_COPY_LB: {
           const uint32_t w1 = ops.next();
           float* src = ((w1 >> 11) & 1u ? norm2 : norm) + (w1 & 2047u);
-          if (p & 1u) { for (int j = tm.tid; j < len; j += tm.n) src[j] = sm->scratch[j]; }
-          else for (int j = tm.tid; j < len; j += tm.n) sm->scratch[j] = src[j];
+          float* from = (p & 1u) ? sm->scratch : src;
+          float* to = (p & 1u) ? src : sm->scratch;
+          MB_ROLLED
+          for (int j = tm.tid; j < len; j += tm.n) to[j] = from[j];
           MB_SYNC();
         } break;
         case OP_HAAR: {
@@ -250,6 +249,7 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
           team_interleave(tm, (p & 1u) ? sm->scratch : x, sm->tmp, len / stride, stride, (int)(p >> 4) & 1);
         } break;
         case OP_ZERO:
+          MB_ROLLED
           for (int j = tm.tid; j < len; j += tm.n) x[j] = 0.f;
           MB_SYNC();
           break;
@@ -257,6 +257,7 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
           const float gain = bits2f(ops.next());
           const uint32_t seed = ops.next();
           const float* lb = sm->scratch + p;
+          MB_ROLLED
           for (int j = tm.tid; j < len; j += tm.n) {
             uint32_t s = lcg_jump(seed, j + 1);
             x[j] = lb[j] + ((s & 0x8000u) ? 1.0f / 256.0f : -(1.0f / 256.0f));
@@ -266,6 +267,7 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
         case OP_NOISE: {
           const float gain = bits2f(ops.next());
           const uint32_t seed = ops.next();
+          MB_ROLLED
           for (int j = tm.tid; j < len; j += tm.n) {
             uint32_t s = lcg_jump(seed, j + 1);
             x[j] = (float)((int32_t)s >> 20);
@@ -280,6 +282,7 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
           const uint32_t w1 = ops.next();
           float* dst = ((w1 >> 11) & 1u ? norm2 : norm) + (w1 & 2047u);
           const float scale = celt_sqrt((float)len);
+          MB_ROLLED
           for (int j = tm.tid; j < len; j += tm.n) dst[j] = scale * x[j];
           MB_SYNC();
         } break;
@@ -287,20 +290,27 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
           const float mid = (float)(int)(ops.next() & 0xffffu) / 32768.0f;
           float* xx = win;
           float* yy = win + WIN_Y;
-          // the two inner products keep the reference's summation order: products by the team, one lane per sum
-          // (the fold source in `scratch` is dead by the time a band's two channels are merged)
+          // the two inner products keep the reference's summation order, one lane per sum
+          float acc = 0.f, xp, sd;
+#if MB_BANDS_SUM_MODE == 1
+          // (products by the team; the fold source in `scratch` is dead by the time a band's two channels are merged)
+          MB_ROLLED
           for (int j = tm.tid; j < len; j += tm.n) { const float yv = yy[j]; sm->tmp[j] = yv * xx[j]; sm->scratch[j] = yv * yv; }
           MB_SYNC();
-          float acc = 0.f;
           if (tm.tid < 2) acc = serial_sum(tm.tid ? sm->scratch : sm->tmp, len);
-          float xp, sd;
           if (tm.n == 1) { xp = acc * mid; sd = serial_sum(sm->scratch, len); }
           else { xp = team_bcast(tm, acc, 0) * mid; sd = team_bcast(tm, acc, 1); }
+#else
+          if (tm.tid < 2) { const float* o = tm.tid ? yy : xx; for (int j = 0; j < len; j++) acc += yy[j] * o[j]; }
+          if (tm.n == 1) { xp = acc * mid; sd = 0.f; for (int j = 0; j < len; j++) sd += yy[j] * yy[j]; }
+          else { xp = team_bcast(tm, acc, 0) * mid; sd = team_bcast(tm, acc, 1); }
+#endif
           const float mid2 = mid * mid;
           const float el = mid2 + sd - 2.0f * xp, er = mid2 + sd + 2.0f * xp;
           const int degenerate = er < 6e-4f || el < 6e-4f;
           const float lgain = degenerate ? 0.f : celt_rsqrt(el), rgain = degenerate ? 0.f : celt_rsqrt(er);
           const int inv = (int)(p & 1u);
+          MB_ROLLED
           for (int j = tm.tid; j < len; j += tm.n) {
             float yv;
             if (degenerate) yv = xx[j];
@@ -334,6 +344,7 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
         } break;
         case OP_AVG: {
           const int cnt = len | ((int)p << 9);
+          MB_ROLLED
           for (int j = tm.tid; j < cnt; j += tm.n) norm[j] = (norm[j] + norm2[j]) * 0.5f;
           MB_SYNC();
         } break;
@@ -341,6 +352,7 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
           const uint32_t w1 = ops.next();
           const int n1 = (int)(w1 & 2047u), cnt = (int)((w1 >> 11) & 2047u), dual = (int)((w1 >> 22) & 1u);
           const int n2 = n1 + cnt;
+          MB_ROLLED
           for (int j = tm.tid; j < cnt; j += tm.n) {
             norm[n1 + j] = norm[2 * n1 - n2 + j];
             if (dual) norm2[n1 + j] = norm2[2 * n1 - n2 + j];
@@ -354,6 +366,7 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
           const uint32_t missing = p >> 2;
           for (int k = 0; k < (1 << alm); k++) {
             if (!(missing & (1u << k))) continue;
+            MB_ROLLED
             for (int j = tm.tid; j < N0; j += tm.n) {
               uint32_t s = lcg_jump(seed, j + 1);
               x[(j << alm) + k] = (s & 0x8000u) ? rr : -rr;
@@ -367,10 +380,12 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
     }
     // ---- denormalise_bands for this band, in place in the spectrum row
     if (P.x_dbg)
+      MB_ROLLED
       for (int idx = tm.tid; idx < C * n; idx += tm.n) {
         int c = idx >= n, j = idx - c * n;
         P.x_dbg[(size_t)f * 2 * MAX_N + c * MAX_N + band_start + j] = win[c * WIN_Y + j];
       }
+    MB_ROLLED
     for (int idx = tm.tid; idx < C * n; idx += tm.n) {
       int c = idx >= n, j = idx - c * n;
       xrow[c * N + band_start + j] = win[c * WIN_Y + j] * sm->gains[c * NB_EBANDS + band];

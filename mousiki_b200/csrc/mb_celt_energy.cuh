@@ -14,6 +14,8 @@ namespace mb {
 
 MB_TBL float kPredCoef[4] = {29440.f / 32768.f, 26112.f / 32768.f, 21248.f / 32768.f, 16384.f / 32768.f};
 MB_TBL float kBetaCoef[4] = {30147.f / 32768.f, 22282.f / 32768.f, 12124.f / 32768.f, 6554.f / 32768.f};
+MB_TBL float kEMeans[25] = {6.4375f, 6.25f, 5.75f, 5.3125f, 5.0625f, 4.8125f, 4.5f, 4.375f, 4.875f, 4.6875f, 4.5625f, 4.4375f, 4.875f,
+                            4.625f, 4.3125f, 4.5f, 4.375f, 4.625f, 4.75f, 4.4375f, 3.75f, 3.75f, 3.75f, 3.75f, 3.75f};
 
 // Persistent per-stream state (HBM, one record per stream). Reference: OpusDecoder
 // (src/opus_decoder.rs:200-241) + OpusCustomDecoder (src/celt/types.rs:793-859), minus the
@@ -60,7 +62,8 @@ struct FrameMeta {
                          // cross-fades it into the SILK row; bit5: SILK decoder reset before the packet; bit6 / bit7: the
                          // fade at the start (CELT -> SILK) / at the end (SILK -> CELT) of the row applies
 };
-enum { EN_STRIDE = 3 * 2 * NB_EBANDS,
+enum { EN_STRIDE = 4 * 2 * NB_EBANDS, EN_GAINS = 3 * 2 * NB_EBANDS,   // per-frame energy scratch: E, prev1 (old_log_e), prev2 (old_log_e2), band gains
+      
        MB_FL_FOLD = 8u | 16u | 512u,
        MB_FL_F32ROW = 256u };  // the packet's PCM goes through the float row (k_deemph / k_fade / k_clip_i16), set on all its frames   // FrameMeta.flags: the frame's band pass runs per stream, in tick order, on the persistent fold buffer
 // flags bit 9 (512): CELT-only frame behind a SILK-side frame of the same pass; bits 10-19 / 20-29: fold-buffer words
@@ -252,6 +255,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
       if (MB_H0_ACON(h0)) { ef[2 * NB_EBANDS + idx] = sm->le[idx]; ef[4 * NB_EBANDS + idx] = sm->le2[idx]; }
       float e = silence ? -28.0f : E[idx];
       ef[idx] = e;
+      ef[EN_GAINS + idx] = celt_exp2(fmin32(e + kEMeans[i], 32.0f));   // denormalise_bands' band gain (bands.rs:4172-4234)
       // state rotation (celt_decoder.rs:4023-4062)
       if (C == 1 && c == 1) e = silence ? -28.0f : E[i];
       float l1 = sm->le[idx], l2 = sm->le2[idx];

@@ -19,6 +19,7 @@
 #define MB_SYNC() __syncwarp()   /* warp-sized thread teams (mb_celt_bands.cuh, mb_celt_imdct.cuh) */
 #define MB_CTA_SYNC() __syncthreads()
 #define MB_ON_DEVICE 1
+#define MB_ROLLED _Pragma("unroll 1")   /* keep a loop rolled: the hot kernels are bound by instruction fetch, not by loop overhead */
 #else
 #define MB_DEV static inline
 #define MB_MEM inline
@@ -27,6 +28,7 @@
 #define MB_SYNC() ((void)0)
 #define MB_CTA_SYNC() ((void)0)
 #define MB_ON_DEVICE 0
+#define MB_ROLLED
 #endif
 
 #include "celt_tables_data.h"

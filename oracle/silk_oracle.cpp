@@ -649,25 +649,314 @@ int SilkResampler::run(int16_t* out, const int16_t* in, int in_len) {
   return produced;
 }
 
+// ---- packet-loss concealment (plc.rs) and comfort noise (cng.rs) ----
+static inline int32_t silk_rand(int32_t seed) { return w_add(907633515, w_mul(seed, 196314165)); }   // cng.rs:371-373
+static inline int32_t rshift_any(int32_t v, int s) { return s <= 0 ? w_shl(v, -s) : v >> s; }           // plc.rs:372-378
+static int32_t sqrt_approx(int32_t x) {   // plc.rs:448-457
+  if (x <= 0) return 0;
+  int lz = clz32(x);
+  uint32_t ux = (uint32_t)x;
+  int rot = (24 - lz) & 31;
+  int32_t frac = (int32_t)(((ux >> rot) | (rot ? ux << (32 - rot) : 0)) & 0x7f);
+  int32_t y = (lz & 1) ? 32768 : 46214;
+  y >>= lz >> 1;
+  return smlawb(y, y, smulbb(213, frac));
+}
+static void sum_sqr_shift(const int16_t* x, int len, int32_t* energy, int* shift_out) {   // sum_sqr_shift.rs:12-75
+  if (len == 0) { *energy = 0; *shift_out = 0; return; }
+  auto acc_energy = [&](int32_t acc, int shift) {
+    int i = 0;
+    for (; i + 1 < len; i += 2) {
+      uint32_t pe = (uint32_t)((int32_t)x[i] * x[i]) + (uint32_t)((int32_t)x[i + 1] * x[i + 1]);
+      acc = w_add(acc, (int32_t)(shift <= 0 ? pe : (shift >= 32 ? 0u : pe >> shift)));
+    }
+    if (i < len) {
+      uint32_t pe = (uint32_t)((int32_t)x[i] * x[i]);
+      acc = w_add(acc, (int32_t)(shift <= 0 ? pe : (shift >= 32 ? 0u : pe >> shift)));
+    }
+    return acc;
+  };
+  int shift = 31 - __builtin_clz((uint32_t)len);
+  int32_t e = acc_energy(len, shift);
+  int lz = e == 0 ? 32 : __builtin_clz((uint32_t)e);
+  shift = shift + 3 - lz; if (shift < 0) shift = 0;
+  *energy = acc_energy(0, shift);
+  *shift_out = shift;
+}
+
+void SilkPlc::reset(int frame_length) {   // decoder_state.rs:77-95
+  *this = SilkPlc();
+  pitch_l_q8 = frame_length << 7;
+}
+void SilkCng::reset(int lpc_order) {   // cng.rs:62-80
+  int32_t step = 32767 / (lpc_order + 1), acc = 0;
+  for (int i = 0; i < SILK_MAX_ORDER; i++) {
+    if (i < lpc_order) { acc += step; smth_nlsf_q15[i] = (int16_t)acc; } else smth_nlsf_q15[i] = 0;
+  }
+  smth_gain_q16 = 0; rand_seed = 3176576;
+  memset(synth_state, 0, sizeof(synth_state));
+}
+
+// plc.rs:117-184 (silk_plc_update)
+static void plc_update(SilkChannel* st, const SilkControl* c) {
+  SilkPlc* plc = &st->plc;
+  st->prev_signal_type = st->indices.signal_type;
+  const int nb = st->nb_subfr;
+  int32_t ltp_gain_q14 = 0;
+  if (st->indices.signal_type == SILK_TYPE_VOICED) {
+    const int32_t target = c->pitch_l[nb - 1];
+    for (int j = 0; j < nb && j * st->subfr_length < target; j++) {
+      const int sf = nb - 1 - j;
+      int32_t tg = 0;
+      for (int i = 0; i < SILK_LTP_ORDER; i++) tg += c->ltp_coef_q14[sf * SILK_LTP_ORDER + i];
+      if (tg > ltp_gain_q14) { ltp_gain_q14 = tg; plc->pitch_l_q8 = w_shl(c->pitch_l[sf], 8); }
+    }
+    memset(plc->ltp_coef_q14, 0, sizeof(plc->ltp_coef_q14));
+    plc->ltp_coef_q14[SILK_LTP_ORDER / 2] = sat16(ltp_gain_q14);
+    if (ltp_gain_q14 < 11469) {
+      int32_t scale_q10 = (11469 << 10) / (ltp_gain_q14 > 1 ? ltp_gain_q14 : 1);
+      for (int i = 0; i < SILK_LTP_ORDER; i++) plc->ltp_coef_q14[i] = sat16(smulbb(plc->ltp_coef_q14[i], scale_q10) >> 10);
+    } else if (ltp_gain_q14 > 15565) {
+      int32_t scale_q14 = (15565 << 14) / (ltp_gain_q14 > 1 ? ltp_gain_q14 : 1);
+      for (int i = 0; i < SILK_LTP_ORDER; i++) plc->ltp_coef_q14[i] = sat16(smulbb(plc->ltp_coef_q14[i], scale_q14) >> 14);
+    }
+  } else {
+    plc->pitch_l_q8 = w_shl(smulbb(st->fs_khz, 18), 8);
+    memset(plc->ltp_coef_q14, 0, sizeof(plc->ltp_coef_q14));
+  }
+  memset(plc->prev_lpc_q12, 0, sizeof(plc->prev_lpc_q12));
+  memcpy(plc->prev_lpc_q12, c->pred_coef_q12[1], st->lpc_order * sizeof(int16_t));
+  plc->prev_ltp_scale_q14 = sat16(c->ltp_scale_q14);
+  plc->prev_gain_q16[0] = c->gains_q16[nb - 2];
+  plc->prev_gain_q16[1] = c->gains_q16[nb - 1];
+  plc->subfr_length = st->subfr_length;
+  plc->nb_subfr = nb;
+}
+
+// plc.rs:186-345 (silk_plc_conceal)
+static void plc_conceal(SilkChannel* st, SilkControl* c, int16_t* frame) {
+  SilkPlc* plc = &st->plc;
+  const int frame_length = st->frame_length, nb_subfr = st->nb_subfr, subfr_length = st->subfr_length;
+  const int ltp_mem = st->ltp_mem_length, order = st->lpc_order, fs_khz = st->fs_khz;
+  const int32_t prev_gain_q10[2] = {plc->prev_gain_q16[0] >> 6, plc->prev_gain_q16[1] >> 6};
+  // silk_plc_energy (plc.rs:347-368)
+  int32_t e1, e2; int s1, s2;
+  {
+    int16_t buf[2][80];
+    for (int k = 0; k < 2; k++) {
+      const int base = (k + nb_subfr - 2) * subfr_length;
+      for (int i = 0; i < subfr_length; i++) {
+        const int idx = base + i;
+        const int32_t v = idx < SILK_MAX_FRAME ? st->exc_q14[idx] : 0;
+        buf[k][i] = sat16(smulww(v, prev_gain_q10[k]) >> 8);
+      }
+    }
+    sum_sqr_shift(buf[0], subfr_length, &e1, &s1);
+    sum_sqr_shift(buf[1], subfr_length, &e2, &s2);
+  }
+  // pick_rand_slice (plc.rs:370-388): the PLC state's own subframe geometry, clamped into the excitation buffer
+  int32_t rand_slice[128];
+  {
+    const int second = !(rshift_any(e1, s2) < rshift_any(e2, s1));
+    const int sl = plc->subfr_length > 1 ? plc->subfr_length : 1, nb = plc->nb_subfr > 2 ? plc->nb_subfr : 2;
+    const int base = second ? nb * sl : (nb - 1) * sl;
+    int start = base - 128; if (start < 0) start = 0;
+    if (start > SILK_MAX_FRAME - 128) start = SILK_MAX_FRAME - 128;
+    memcpy(rand_slice, st->exc_q14 + start, sizeof(rand_slice));
+  }
+  if (st->first_frame_after_reset) memset(plc->prev_lpc_q12, 0, sizeof(plc->prev_lpc_q12));
+  int16_t* B = plc->ltp_coef_q14;
+  int32_t rand_scale_q14 = plc->rand_scale_q14;
+  static const int16_t HARM_ATT[2] = {32440, 31130}, RAND_V[2] = {31130, 26214}, RAND_UV[2] = {32440, 29491};
+  const int att = st->loss_count < 1 ? st->loss_count : 1;
+  const int32_t harm_gain_q15 = HARM_ATT[att];
+  const int32_t rand_gain_q15 = st->prev_signal_type == SILK_TYPE_VOICED ? RAND_V[att] : RAND_UV[att];
+  bwexpander(plc->prev_lpc_q12, order, 64881);
+  int16_t a_q12[SILK_MAX_ORDER] = {0};
+  memcpy(a_q12, plc->prev_lpc_q12, order * sizeof(int16_t));
+  if (st->loss_count == 0) {
+    rand_scale_q14 = 1 << 14;
+    if (st->prev_signal_type == SILK_TYPE_VOICED) {
+      for (int i = 0; i < SILK_LTP_ORDER; i++) rand_scale_q14 -= B[i];
+      if (rand_scale_q14 < 3277) rand_scale_q14 = 3277;
+      rand_scale_q14 = smulbb(rand_scale_q14, plc->prev_ltp_scale_q14) >> 14;
+    } else {
+      const int32_t inv_gain_q30 = silk_lpc_inverse_pred_gain(plc->prev_lpc_q12, order);
+      int32_t down = (1 << 30) >> 3; if (inv_gain_q30 < down) down = inv_gain_q30;
+      if (down < ((1 << 30) >> 8)) down = (1 << 30) >> 8;
+      down = w_shl(down, 3);
+      rand_scale_q14 = smulwb(down, rand_gain_q15) >> 14;
+    }
+  }
+  int32_t rand_seed = plc->rand_seed;
+  int lag = rshift_round(plc->pitch_l_q8, 8);
+  int32_t s_ltp_q14[320 + SILK_MAX_FRAME] = {0};
+  int16_t s_ltp[320] = {0};
+  const int idx = ltp_mem - lag - order - SILK_LTP_ORDER / 2;
+  lpc_analysis_filter(s_ltp + idx, st->out_buf + idx, a_q12, ltp_mem - idx, order);
+  int32_t inv_gain_q30 = inverse32_varq(plc->prev_gain_q16[1], 46);
+  if (inv_gain_q30 > (INT32_MAX >> 1)) inv_gain_q30 = INT32_MAX >> 1;
+  for (int i = idx + order; i < ltp_mem; i++) s_ltp_q14[i] = smulwb(inv_gain_q30, s_ltp[i]);
+  int buf_idx = ltp_mem;
+  for (int k = 0; k < nb_subfr; k++) {
+    for (int i = 0; i < subfr_length; i++) {
+      int32_t pred = 2;
+      for (int t = 0; t < SILK_LTP_ORDER; t++) pred = smlawb(pred, s_ltp_q14[buf_idx - lag + t - SILK_LTP_ORDER / 2], B[t]);
+      rand_seed = silk_rand(rand_seed);
+      s_ltp_q14[buf_idx] = lshift_sat32(smlawb(pred, rand_slice[(rand_seed >> 25) & 127], rand_scale_q14), 2);
+      buf_idx++;
+    }
+    for (int t = 0; t < SILK_LTP_ORDER; t++) B[t] = sat16(smulbb(harm_gain_q15, B[t]) >> 15);
+    rand_scale_q14 = smulbb(rand_scale_q14, rand_gain_q15) >> 15;
+    plc->pitch_l_q8 = w_add(plc->pitch_l_q8, smulwb(plc->pitch_l_q8, 655));
+    const int32_t max_lag_q8 = w_shl(smulbb(18, fs_khz), 8);
+    if (plc->pitch_l_q8 > max_lag_q8) plc->pitch_l_q8 = max_lag_q8;
+    lag = rshift_round(plc->pitch_l_q8, 8);
+  }
+  int32_t* s_lpc = s_ltp_q14 + ltp_mem - SILK_MAX_ORDER;
+  memcpy(s_lpc, st->s_lpc_q14, sizeof(st->s_lpc_q14));
+  for (int i = 0; i < frame_length; i++) {
+    int32_t pred = order >> 1;
+    for (int j = 0; j < order; j++) pred = smlawb(pred, s_lpc[SILK_MAX_ORDER + i - j - 1], a_q12[j]);
+    const int32_t upd = sat32_64((int64_t)s_lpc[SILK_MAX_ORDER + i] + lshift_sat32(pred, 4));
+    s_lpc[SILK_MAX_ORDER + i] = upd;
+    frame[i] = sat16(rshift_round(smulww(upd, prev_gain_q10[1]), 8));
+  }
+  memcpy(st->s_lpc_q14, s_lpc + frame_length, sizeof(st->s_lpc_q14));
+  plc->rand_seed = rand_seed;
+  plc->rand_scale_q14 = sat16(rand_scale_q14);
+  for (int k = 0; k < SILK_MAX_SUBFR; k++) c->pitch_l[k] = lag;
+}
+
+// plc.rs:46-72 (silk_plc)
+static void silk_plc(SilkChannel* st, SilkControl* c, int16_t* frame, int lost) {
+  if (st->fs_khz != st->plc.fs_khz) { st->plc.reset(st->frame_length); st->plc.fs_khz = st->fs_khz; }
+  if (lost) {
+    plc_conceal(st, c, frame);
+    st->loss_count = st->loss_count == INT32_MAX ? INT32_MAX : st->loss_count + 1;
+  } else plc_update(st, c);
+}
+
+// plc.rs:74-115 (silk_plc_glue_frames)
+static void plc_glue_frames(SilkChannel* st, int16_t* frame, int length) {
+  SilkPlc* plc = &st->plc;
+  if (st->loss_count > 0) {
+    sum_sqr_shift(frame, length, &plc->conc_energy, &plc->conc_energy_shift);
+    plc->last_frame_lost = 1;
+    return;
+  }
+  if (!plc->last_frame_lost) return;
+  int32_t energy; int eshift;
+  sum_sqr_shift(frame, length, &energy, &eshift);
+  if (eshift > plc->conc_energy_shift) plc->conc_energy >>= eshift - plc->conc_energy_shift;
+  else if (eshift < plc->conc_energy_shift) energy >>= plc->conc_energy_shift - eshift;
+  if (energy > plc->conc_energy) {
+    const int lz = clz32(plc->conc_energy > 1 ? plc->conc_energy : 1) - 1;
+    plc->conc_energy = w_shl(plc->conc_energy, lz);
+    const int rs = 24 - lz > 0 ? 24 - lz : 0;
+    if (rs > 0) energy >>= rs;
+    const int32_t frac_q24 = plc->conc_energy / (energy > 1 ? energy : 1);
+    int32_t gain_q16 = w_shl(sqrt_approx(frac_q24), 4);
+    int32_t slope_q16 = ((1 << 16) - gain_q16) / length;
+    slope_q16 = w_shl(slope_q16, 2);
+    for (int i = 0; i < length; i++) {
+      frame[i] = sat16(smulwb(gain_q16, frame[i]));
+      gain_q16 = sat32_64((int64_t)gain_q16 + slope_q16);
+      if (gain_q16 > (1 << 16)) break;
+    }
+  }
+  plc->last_frame_lost = 0;
+}
+
+// cng.rs:145-370 (apply_cng)
+static void apply_cng(SilkChannel* st, const SilkControl* c, int16_t* frame, uint32_t quirks) {
+  SilkCng* g = &st->cng;
+  const int order = st->lpc_order, length = st->frame_length;
+  if (st->fs_khz != g->fs_khz) {
+    if (g->fs_khz == -1) memset(g->synth_state, 0, order * sizeof(int32_t));
+    else g->reset(order);
+    memset(g->smth_nlsf_q15, 0, sizeof(g->smth_nlsf_q15));
+    memcpy(g->smth_nlsf_q15, st->prev_nlsf_q15, order * sizeof(int16_t));
+    g->fs_khz = st->fs_khz;
+  }
+  if (st->loss_count == 0 && st->prev_signal_type == SILK_TYPE_INACTIVE) {
+    for (int i = 0; i < order; i++) {
+      const int32_t cur = g->smth_nlsf_q15[i];
+      g->smth_nlsf_q15[i] = (int16_t)(cur + smulwb((int32_t)st->prev_nlsf_q15[i] - cur, 16348));
+    }
+    int32_t max_gain = 0; int strongest = 0;
+    for (int i = 0; i < st->nb_subfr; i++) if (c->gains_q16[i] > max_gain) { max_gain = c->gains_q16[i]; strongest = i; }
+    memmove(g->exc_buf_q14 + st->subfr_length, g->exc_buf_q14, (size_t)st->subfr_length * (st->nb_subfr - 1) * sizeof(int32_t));
+    memcpy(g->exc_buf_q14, st->exc_q14 + strongest * st->subfr_length, st->subfr_length * sizeof(int32_t));
+    for (int i = 0; i < st->nb_subfr; i++) {
+      g->smth_gain_q16 = w_add(g->smth_gain_q16, smulwb(w_sub(c->gains_q16[i], g->smth_gain_q16), 4634));
+      if (smulww(g->smth_gain_q16, 46396) > c->gains_q16[i]) g->smth_gain_q16 = c->gains_q16[i];
+    }
+  }
+  if (st->loss_count > 0) {
+    int32_t sig[SILK_MAX_FRAME + SILK_MAX_ORDER] = {0};
+    int32_t gain_q16 = smulww(st->plc.rand_scale_q14, st->plc.prev_gain_q16[1]);
+    auto smultt = [](int32_t a, int32_t b) { return w_mul(a >> 16, b >> 16); };
+    if (gain_q16 >= (1 << 21) || g->smth_gain_q16 > (1 << 23)) {
+      gain_q16 = smultt(gain_q16, gain_q16);
+      gain_q16 = w_sub(smultt(g->smth_gain_q16, g->smth_gain_q16), w_shl(gain_q16, 5));
+      gain_q16 = lshift_sat32(sqrt_approx(gain_q16), 16);
+    } else {
+      gain_q16 = smulww(gain_q16, gain_q16);
+      gain_q16 = w_sub(smulww(g->smth_gain_q16, g->smth_gain_q16), w_shl(gain_q16, 5));
+      gain_q16 = lshift_sat32(sqrt_approx(gain_q16), 8);
+    }
+    const int32_t gain_q10 = gain_q16 >> 6;
+    int mask = 255;
+    while (mask > length) mask >>= 1;
+    int32_t seed = g->rand_seed;
+    for (int i = 0; i < length; i++) {
+      seed = silk_rand(seed);
+      int ix = (seed >> 24) & mask;
+      if (ix < 0) ix = 0; if (ix > SILK_MAX_FRAME - 1) ix = SILK_MAX_FRAME - 1;
+      sig[SILK_MAX_ORDER + i] = g->exc_buf_q14[ix];
+    }
+    g->rand_seed = seed;
+    int16_t a_q12[SILK_MAX_ORDER] = {0};
+    silk_nlsf2a(a_q12, g->smth_nlsf_q15, order, quirks);
+    memcpy(sig, g->synth_state, sizeof(g->synth_state));
+    for (int i = 0; i < length; i++) {
+      int32_t pred = order >> 1;
+      for (int j = 0; j < order; j++) pred = smlawb(pred, sig[SILK_MAX_ORDER + i - 1 - j], a_q12[j]);
+      const int32_t upd = sat32_64((int64_t)sig[SILK_MAX_ORDER + i] + lshift_sat32(pred, 4));
+      sig[SILK_MAX_ORDER + i] = upd;
+      frame[i] = sat16((int32_t)frame[i] + sat16(rshift_round(smulww(upd, gain_q10), 8)));
+    }
+    memcpy(g->synth_state, sig + length, sizeof(g->synth_state));
+  } else memset(g->synth_state, 0, order * sizeof(int32_t));
+}
+
 // ---- frame + API level ----
-// decode_frame.rs:54-153 without the PLC/CNG state machines: with no lost frame they never touch the output
-// (plc.rs:46-88 update branch only feeds later concealment; cng.rs:145-233 and plc.rs glue act when loss_count > 0).
-// The one field of silk_plc_update that the normal path reads back is prev_signal_type (plc.rs:123).
-static void decode_frame(SilkDecoder* D, int n, EcDec* ec, int16_t* out, int cond) {
+// decode_frame.rs:54-153
+static void decode_frame(SilkDecoder* D, int n, EcDec* ec, int16_t* out, int lost_flag, int cond) {
   SilkChannel* st = &D->ch[n];
   SilkControl ctrl;
   int16_t pulses[SILK_MAX_FRAME + 16];
-  decode_indices(st, ec, st->n_frames_decoded, 0, cond, &st->indices);
-  decode_pulses(ec, pulses, st->indices.signal_type, st->indices.quant_offset_type, st->frame_length, D->quirks);
-  int16_t nlsf_tr[SILK_MAX_ORDER];
-  decode_parameters(st, &ctrl, cond, D->quirks, nlsf_tr);
-  decode_core(st, &ctrl, out, pulses);
-  st->prev_signal_type = st->indices.signal_type;
-  st->loss_count = 0;
-  st->first_frame_after_reset = 0;
+  int16_t nlsf_tr[SILK_MAX_ORDER] = {0};
+  const int fi = st->n_frames_decoded;
+  const int decode_payload = lost_flag == SILK_FLAG_DECODE_NORMAL || (lost_flag == SILK_FLAG_DECODE_LBRR && st->lbrr_flags[fi] != 0);
+  if (decode_payload) {
+    decode_indices(st, ec, fi, lost_flag == SILK_FLAG_DECODE_LBRR, cond, &st->indices);
+    decode_pulses(ec, pulses, st->indices.signal_type, st->indices.quant_offset_type, st->frame_length, D->quirks);
+    decode_parameters(st, &ctrl, cond, D->quirks, nlsf_tr);
+    decode_core(st, &ctrl, out, pulses);
+    silk_plc(st, &ctrl, out, 0);
+    st->loss_count = 0;
+    st->first_frame_after_reset = 0;
+  } else {
+    memset(pulses, 0, sizeof(pulses));
+    silk_plc(st, &ctrl, out, 1);
+  }
   int mv = st->ltp_mem_length - st->frame_length;  // refresh_output_buffer (decode_frame.rs:207-230)
   memmove(st->out_buf, st->out_buf + st->frame_length, mv * sizeof(int16_t));
   memcpy(st->out_buf + mv, out, st->frame_length * sizeof(int16_t));
+  apply_cng(st, &ctrl, out, D->quirks);
+  plc_glue_frames(st, out, st->frame_length);
   st->lag_prev = ctrl.pitch_l[st->nb_subfr - 1];
   if (D->trace) {
     D->trace->indices[n] = st->indices;
@@ -678,12 +967,17 @@ static void decode_frame(SilkDecoder* D, int n, EcDec* ec, int16_t* out, int con
   }
 }
 
-static void channel_reset(SilkChannel* c) { *c = SilkChannel(); }  // init_decoder.rs:14-26
+static void channel_reset(SilkChannel* c) {  // init_decoder.rs:14-26
+  *c = SilkChannel();
+  c->cng.reset(c->lpc_order);
+  c->plc.reset(c->frame_length);
+}
 
 // dec_api.rs:102-123: reset_decoder keeps n_channels_api/internal, init_decoder sets both to 1
 void SilkDecoder::reset(int init) {
   uint32_t q = quirks; SilkTrace* t = trace; int a = n_channels_api, b = n_channels_internal;
   *this = SilkDecoder();
+  channel_reset(&ch[0]); channel_reset(&ch[1]);
   quirks = q; trace = t;
   if (!init) { n_channels_api = a; n_channels_internal = b; }
 }
@@ -712,9 +1006,8 @@ static void ms_to_lr(SilkDecoder* D, int16_t* x1, int16_t* x2, const int32_t pre
   }
 }
 
-// dec_api.rs:132-441 (normal decode; FLAG_PACKET_LOST / FLAG_DECODE_LBRR are not restated -> -5)
+// dec_api.rs:132-441
 int SilkDecoder::decode(SilkDecControl* c, int lost_flag, int new_packet, EcDec* ec, int16_t* samples_out) {
-  if (lost_flag != SILK_FLAG_DECODE_NORMAL) return -5;
   int nci = c->n_channels_internal;
   if (new_packet) for (int n = 0; n < nci; n++) ch[n].n_frames_decoded = 0;
   if (nci > n_channels_internal) {
@@ -746,7 +1039,7 @@ int SilkDecoder::decode(SilkDecControl* c, int lost_flag, int new_packet, EcDec*
   n_channels_internal = c->n_channels_internal;
   int decode_only_middle = prev_decode_only_middle;
   uint32_t q = quirks;
-  if (ch[0].n_frames_decoded == 0) {  // decode_vad_and_lbrr (dec_api.rs:443-530)
+  if (lost_flag != SILK_FLAG_PACKET_LOST && ch[0].n_frames_decoded == 0) {  // decode_vad_and_lbrr (dec_api.rs:443-530)
     for (int n = 0; n < nci; n++) {
       for (int i = 0; i < ch[n].n_frames_per_packet; i++) ch[n].vad_flags[i] = ec->bit_logp(1);
       ch[n].lbrr_flag = ec->bit_logp(1);
@@ -761,7 +1054,8 @@ int SilkDecoder::decode(SilkDecControl* c, int lost_flag, int new_packet, EcDec*
         }
       }
     }
-    for (int i = 0; i < ch[0].n_frames_per_packet; i++) {
+    // the LBRR payloads are only skipped over on the way to the regular frames (dec_api.rs:478-480)
+    for (int i = 0; lost_flag == SILK_FLAG_DECODE_NORMAL && i < ch[0].n_frames_per_packet; i++) {
       for (int n = 0; n < nci; n++) {
         if (!ch[n].lbrr_flags[i]) continue;
         if (nci == 2 && n == 0) {
@@ -778,8 +1072,13 @@ int SilkDecoder::decode(SilkDecControl* c, int lost_flag, int new_packet, EcDec*
   }
   int32_t ms_pred_q13[2] = {0, 0};
   if (nci == 2) {
-    stereo_decode_pred(ec, ms_pred_q13);
-    decode_only_middle = ch[1].vad_flags[ch[0].n_frames_decoded] == 0 ? ec->icdf(silk_stereo_only_code_mid_iCDF, 8) : 0;
+    const int fi = ch[0].n_frames_decoded;
+    const int decode_ms = lost_flag == SILK_FLAG_DECODE_NORMAL || (lost_flag == SILK_FLAG_DECODE_LBRR && ch[0].lbrr_flags[fi] == 1);
+    if (decode_ms) {
+      stereo_decode_pred(ec, ms_pred_q13);
+      const int need_mid_only = lost_flag == SILK_FLAG_DECODE_NORMAL ? ch[1].vad_flags[fi] == 0 : ch[1].lbrr_flags[fi] == 0;
+      decode_only_middle = need_mid_only ? ec->icdf(silk_stereo_only_code_mid_iCDF, 8) : 0;
+    } else { ms_pred_q13[0] = pred_prev_q13[0]; ms_pred_q13[1] = pred_prev_q13[1]; }
   } else decode_only_middle = 0;
   if (nci == 2 && !decode_only_middle && prev_decode_only_middle) {
     memset(ch[1].out_buf, 0, sizeof(ch[1].out_buf));
@@ -789,14 +1088,18 @@ int SilkDecoder::decode(SilkDecControl* c, int lost_flag, int new_packet, EcDec*
   int frame_length = ch[0].frame_length;
   int16_t bufs[2][SILK_MAX_FRAME + 2];
   memset(bufs, 0, sizeof(bufs));
-  int has_side = !decode_only_middle;
+  int has_side;
+  if (lost_flag == SILK_FLAG_DECODE_NORMAL) has_side = !decode_only_middle;
+  else if (lost_flag == SILK_FLAG_PACKET_LOST) has_side = !prev_decode_only_middle;
+  else has_side = !prev_decode_only_middle || (nci == 2 && ch[1].lbrr_flags[ch[1].n_frames_decoded] == 1);
   for (int n = 0; n < nci; n++) {
     if (n == 0 || has_side) {
-      int fi = ch[0].n_frames_decoded - n, cond;
+      int fi = ch[0].n_frames_decoded - n, cond;   // conditional_coding_for_channel (dec_api.rs:560-583)
       if (fi <= 0) cond = SILK_CODE_INDEPENDENTLY;
+      else if (lost_flag == SILK_FLAG_DECODE_LBRR) cond = ch[n].lbrr_flags[fi - 1] ? SILK_CODE_CONDITIONALLY : SILK_CODE_INDEPENDENTLY;
       else if (n > 0 && prev_decode_only_middle) cond = SILK_CODE_INDEPENDENTLY_NO_LTP_SCALING;
       else cond = SILK_CODE_CONDITIONALLY;
-      decode_frame(this, n, ec, bufs[n] + 2, cond);
+      decode_frame(this, n, ec, bufs[n] + 2, lost_flag, cond);
     } else memset(bufs[n] + 2, 0, frame_length * sizeof(int16_t));
     ch[n].n_frames_decoded++;
   }
@@ -821,7 +1124,8 @@ int SilkDecoder::decode(SilkDecControl* c, int lost_flag, int new_packet, EcDec*
   }
   if (ch[0].prev_signal_type == SILK_TYPE_VOICED) { static const int mult[3] = {6, 4, 3}; c->prev_pitch_lag = ch[0].lag_prev * mult[(ch[0].fs_khz - 8) >> 2]; }
   else c->prev_pitch_lag = 0;
-  prev_decode_only_middle = decode_only_middle;
+  if (lost_flag == SILK_FLAG_PACKET_LOST) { for (int n = 0; n < nci; n++) ch[n].last_gain_index = 10; }
+  else prev_decode_only_middle = decode_only_middle;
   return n_api;
 }
 

@@ -1,7 +1,7 @@
 // ORACLE (test infrastructure only — never linked into the product library).
 // CPU restatement of mousiki's fixed-point SILK decoder as used by the full Opus decoder
-// (src/silk/dec_api.rs and the files it pulls in), normal-decode path: no PLC / CNG / LBRR *synthesis*
-// (LBRR payloads are entropy-decoded and skipped exactly like dec_api.rs:443-530 does).
+// (src/silk/dec_api.rs and the files it pulls in): normal decode, packet-loss concealment (plc.rs), comfort noise
+// (cng.rs) and LBRR (in-band FEC) frames (dec_api.rs:443-530, decode_frame.rs:54-153).
 // Quirk switches: bit set = behave like mousiki as written, clear = behave like libopus.
 #pragma once
 #include <stdint.h>
@@ -54,7 +54,29 @@ struct SilkResampler {  // resampler.rs:40-48
   int run(int16_t* out, const int16_t* in, int in_len);
 };
 
-struct SilkChannel {  // decoder_state.rs:99-131 + decoder_set_fs.rs:63-124 (PLC/CNG state not carried: see header)
+struct SilkPlc {  // decoder_state.rs:23-75 (Default); reset(): decoder_state.rs:77-95
+  int32_t pitch_l_q8 = 0;
+  int16_t ltp_coef_q14[SILK_LTP_ORDER] = {0}, prev_lpc_q12[SILK_MAX_ORDER] = {0};
+  int last_frame_lost = 0;
+  int32_t rand_seed = 0;
+  int16_t rand_scale_q14 = 0;
+  int32_t conc_energy = 0;
+  int conc_energy_shift = 0;
+  int16_t prev_ltp_scale_q14 = 0;
+  int32_t prev_gain_q16[2] = {65536, 65536};
+  int fs_khz = 0, nb_subfr = 2, subfr_length = 20;
+  void reset(int frame_length);
+};
+struct SilkCng {  // cng.rs:31-54
+  int32_t exc_buf_q14[SILK_MAX_FRAME] = {0};
+  int16_t smth_nlsf_q15[SILK_MAX_ORDER] = {0};
+  int32_t synth_state[SILK_MAX_ORDER] = {0};
+  int32_t smth_gain_q16 = 0, rand_seed = 3176576;
+  int fs_khz = -1;
+  void reset(int lpc_order);
+};
+
+struct SilkChannel {  // decoder_state.rs:99-131 + decoder_set_fs.rs:63-124
   int fs_khz = 0, fs_api_hz = 0, nb_subfr = 4, subfr_length = 0, frame_length = 0, ltp_mem_length = 0, lpc_order = 16;
   int first_frame_after_reset = 1, lag_prev = 0, last_gain_index = 0, prev_signal_type = 0;
   const uint8_t* pitch_lag_low_bits_icdf = nullptr; const uint8_t* pitch_contour_icdf = nullptr;
@@ -69,6 +91,8 @@ struct SilkChannel {  // decoder_state.rs:99-131 + decoder_set_fs.rs:63-124 (PLC
   int n_frames_decoded = 0, n_frames_per_packet = 0, ec_prev_signal_type = 0, ec_prev_lag_index = 0;
   int vad_flags[SILK_MAX_FRAMES_PER_PACKET] = {0}, lbrr_flag = 0, lbrr_flags[SILK_MAX_FRAMES_PER_PACKET] = {0};
   int loss_count = 0;
+  SilkPlc plc;
+  SilkCng cng;
   int set_fs(int fs_khz_, int fs_api_hz_);
 };
 
