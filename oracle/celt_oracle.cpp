@@ -1329,6 +1329,299 @@ static void deemphasis(float* const in[2], float* pcm, int N, int CC, int downsa
   }
 }
 
+// celt_synthesis (celt_decoder.rs:573-800): denormalise + inverse MDCT of every channel into out_syn[c][0 .. N + overlap)
+static void celt_synthesis(const float* X, float* const out_syn[2], const float* oldE, int start, int eff_end, int C, int CC, int is_transient,
+                           int lm, int downsample, int silence, uint32_t quirks) {
+  const int M = 1 << lm, N = M * SHORT_MDCT;
+  int nbk, nb, shift;
+  if (is_transient) { nbk = M; nb = SHORT_MDCT; shift = MAX_LM; }
+  else { nbk = 1; nb = SHORT_MDCT << lm; shift = MAX_LM - lm; }
+  const bool q2 = quirks & QUIRK_Q2_MDCT_ZERO_FILL;
+  std::vector<float> freq(N), freq2(N), temp(N);
+  auto imdct = [&](const float* fr, float* out) {
+    for (int b = 0; b < nbk; b++) {
+      for (int k = 0; k < nb; k++) temp[k] = fr[b + k * nbk];
+      clt_mdct_backward(temp.data(), out + b * nb, N + OVERLAP - b * nb, shift, q2);
+    }
+  };
+  if (CC == 2 && C == 1) {
+    denormalise_bands(X, freq.data(), oldE, start, eff_end, M, downsample, silence);
+    imdct(freq.data(), out_syn[0]);
+    imdct(freq.data(), out_syn[1]);
+  } else if (CC == 1 && C == 2) {
+    denormalise_bands(X, freq.data(), oldE, start, eff_end, M, downsample, silence);
+    denormalise_bands(X + N, freq2.data(), oldE + NB_EBANDS, start, eff_end, M, downsample, silence);
+    for (int i = 0; i < N; i++) freq[i] = 0.5f * (freq[i] + freq2[i]);
+    imdct(freq.data(), out_syn[0]);
+  } else {
+    for (int c = 0; c < CC; c++) {
+      denormalise_bands(X + c * N, freq.data(), oldE + c * NB_EBANDS, start, eff_end, M, downsample, silence);
+      imdct(freq.data(), out_syn[c]);
+    }
+  }
+  for (int c = 0; c < CC; c++)
+    for (int i = 0; i < N; i++) out_syn[c][i] = out_syn[c][i] < -SIG_SAT ? -SIG_SAT : (out_syn[c][i] > SIG_SAT ? SIG_SAT : out_syn[c][i]);
+}
+
+// ---------------------------------------------------------------- packet-loss concealment
+// pitch.rs:118-187 (find_best_pitch)
+static void find_best_pitch(const float* xcorr, const float* y, int len, int max_pitch, int* best_pitch) {
+  float syy = 1.0f;
+  for (int j = 0; j < len; j++) syy += y[j] * y[j];
+  float best_num0 = -1.0f, best_den0 = 0.0f, best_num1 = -1.0f, best_den1 = 0.0f;
+  best_pitch[0] = 0; best_pitch[1] = max_pitch > 1 ? 1 : 0;
+  for (int i = 0; i < max_pitch; i++) {
+    const float corr = xcorr[i];
+    if (corr > 0.0f) {
+      float corr16 = corr;
+      corr16 *= 1e-12f;
+      const float num = corr16 * corr16;
+      if (num * best_den1 > best_num1 * syy) {
+        if (num * best_den0 > best_num0 * syy) {
+          best_num1 = best_num0; best_den1 = best_den0; best_pitch[1] = best_pitch[0];
+          best_num0 = num; best_den0 = syy; best_pitch[0] = i;
+        } else { best_num1 = num; best_den1 = syy; best_pitch[1] = i; }
+      }
+    }
+    syy += y[i + len] * y[i + len] - y[i] * y[i];
+    if (syy < 1.0f) syy = 1.0f;
+  }
+}
+// pitch.rs:392-424 (celt_pitch_xcorr; every lag is a plain left-to-right inner product)
+static void celt_pitch_xcorr(const float* x, const float* y, int len, int max_pitch, float* xcorr) {
+  for (int i = 0; i < max_pitch; i++) {
+    float sum = 0.f;
+    for (int j = 0; j < len; j++) sum += x[j] * y[i + j];
+    xcorr[i] = sum;
+  }
+}
+// lpc.rs:465-530 (celt_autocorr, float)
+static void celt_autocorr(const float* x, float* ac, const float* window, int overlap, int lag, int n) {
+  const int fast_n = n - lag;
+  std::vector<float> buf(x, x + n);
+  if (overlap > 0)
+    for (int i = 0; i < overlap; i++) { const float w = window[i]; buf[i] *= w; buf[n - i - 1] *= w; }
+  celt_pitch_xcorr(buf.data(), buf.data(), fast_n, lag + 1, ac);
+  for (int k = 0; k <= lag; k++) {
+    float d = 0.f;
+    for (int i = k + fast_n; i < n; i++) d += buf[i] * buf[i - k];
+    ac[k] += d;
+  }
+}
+// lpc.rs:146-190 (celt_lpc, float; fmaf where the reference calls mul_add_f32)
+static void celt_lpc(float* lpc, const float* ac, int order) {
+  for (int i = 0; i < order; i++) lpc[i] = 0.f;
+  const float ac0 = ac[0];
+  if (ac0 <= 1e-10f) return;
+  float error = ac0;
+  for (int i = 0; i < order; i++) {
+    float rr = 0.f;
+    for (int j = 0; j < i; j++) rr = fmaf(lpc[j], ac[i - j], rr);
+    rr += ac[i + 1];
+    const float r = -(rr / error);
+    lpc[i] = r;
+    for (int j = 0; j < (i + 1) >> 1; j++) {
+      const float t1 = lpc[j], t2 = lpc[i - 1 - j];
+      lpc[j] = fmaf(r, t2, t1);
+      lpc[i - 1 - j] = fmaf(r, t1, t2);
+    }
+    const float r2 = r * r;
+    error = fmaf(-r2, error, error);
+    if (error <= 0.001f * ac0) break;
+  }
+}
+// pitch.rs:1418-1545 (pitch_downsample, float) + :1358-1384 (celt_fir5)
+static void pitch_downsample(const float* const x[2], int nch, float* x_lp, int len) {
+  const int half = len / 2;
+  for (int i = 1; i < half; i++) x_lp[i] = 0.25f * x[0][2 * i - 1] + 0.25f * x[0][2 * i + 1] + 0.5f * x[0][2 * i];
+  x_lp[0] = 0.25f * x[0][1] + 0.5f * x[0][0];
+  if (nch == 2) {
+    for (int i = 1; i < half; i++) x_lp[i] += 0.25f * x[1][2 * i - 1] + 0.25f * x[1][2 * i + 1] + 0.5f * x[1][2 * i];
+    x_lp[0] += 0.25f * x[1][1] + 0.5f * x[1][0];
+  }
+  float ac[5] = {0, 0, 0, 0, 0};
+  celt_autocorr(x_lp, ac, nullptr, 0, 4, half);
+  ac[0] *= 1.0001f;
+  for (int i = 1; i <= 4; i++) { const float coeff = 0.008f * (float)i; ac[i] -= ac[i] * coeff * coeff; }
+  float lpc[4];
+  celt_lpc(lpc, ac, 4);
+  float tmp = 1.0f;
+  for (int i = 0; i < 4; i++) { tmp *= 0.9f; lpc[i] *= tmp; }
+  const float c1 = 0.8f;
+  const float num[5] = {lpc[0] + 0.8f, fmaf(c1, lpc[0], lpc[1]), fmaf(c1, lpc[1], lpc[2]), fmaf(c1, lpc[2], lpc[3]), c1 * lpc[3]};
+  float m0 = 0, m1 = 0, m2 = 0, m3 = 0, m4 = 0;
+  for (int i = 0; i < half; i++) {
+    const float cur = x_lp[i];
+    float sum = cur;
+    sum = fmaf(num[0], m0, sum); sum = fmaf(num[1], m1, sum); sum = fmaf(num[2], m2, sum); sum = fmaf(num[3], m3, sum); sum = fmaf(num[4], m4, sum);
+    m4 = m3; m3 = m2; m2 = m1; m1 = m0; m0 = cur;
+    x_lp[i] = sum;
+  }
+}
+// pitch.rs:557-696 (pitch_search, float)
+static int pitch_search(const float* x_lp, const float* y, int len, int max_pitch) {
+  const int lag = len + max_pitch;
+  std::vector<float> x4(len >> 2), y4(lag >> 2), xcorr(max_pitch >> 1);
+  int best[2] = {0, 0};
+  for (int j = 0; j < len >> 2; j++) x4[j] = x_lp[2 * j];
+  for (int j = 0; j < lag >> 2; j++) y4[j] = y[2 * j];
+  celt_pitch_xcorr(x4.data(), y4.data(), len >> 2, max_pitch >> 2, xcorr.data());
+  find_best_pitch(xcorr.data(), y4.data(), len >> 2, max_pitch >> 2, best);
+  const int len_half = len >> 1, mp_half = max_pitch >> 1;
+  for (int i = 0; i < mp_half; i++) {
+    if (abs(i - 2 * best[0]) > 2 && abs(i - 2 * best[1]) > 2) { xcorr[i] = 0.f; continue; }
+    float sum = 0.f;
+    for (int j = 0; j < len_half; j++) sum += x_lp[j] * y[i + j];
+    xcorr[i] = sum < -1.0f ? -1.0f : sum;
+  }
+  find_best_pitch(xcorr.data(), y, len_half, mp_half, best);
+  if (best[0] > 0 && best[0] < mp_half - 1) {
+    const float a = xcorr[best[0] - 1], b = xcorr[best[0]], c = xcorr[best[0] + 1];
+    int offset = 0;
+    if ((c - a) > 0.7f * (b - a)) offset = 1;
+    else if ((a - c) > 0.7f * (b - c)) offset = -1;
+    return 2 * best[0] - offset;
+  }
+  return 2 * best[0];
+}
+// comb_filter with an output buffer and no cross-fade window (celt.rs:176-330 as prefilter_and_fold calls it: overlap 0)
+static void comb_filter_out(float* y, const float* x, int xs, int n, int T0, int T1, float g0, float g1, int tapset0, int tapset1) {
+  (void)T0; (void)tapset0;
+  if (g0 == 0.f && g1 == 0.f) { for (int i = 0; i < n; i++) y[i] = x[xs + i]; return; }
+  T1 = imax(T1, COMBFILTER_MINPERIOD);
+  if (g1 == 0.f) { for (int i = 0; i < n; i++) y[i] = x[xs + i]; return; }
+  const float g10 = g1 * kTapsetGains[tapset1][0], g11 = g1 * kTapsetGains[tapset1][1], g12 = g1 * kTapsetGains[tapset1][2];
+  float x4 = x[xs - T1 - 2], x3 = x[xs - T1 - 1], x2 = x[xs - T1], x1 = x[xs - T1 + 1];
+  for (int i = 0; i < n; i++) {
+    const float x0 = x[xs + i - T1 + 2];
+    float acc = fmaf(g10, x2, x[xs + i]);
+    acc = fmaf(g11, x1 + x3, acc);
+    acc = fmaf(g12, x0 + x4, acc);
+    y[i] = acc;
+    x4 = x3; x3 = x2; x2 = x1; x1 = x0;
+  }
+}
+// celt_decoder.rs:1327-1380 (prefilter_and_fold, float). Under Q2 the next inverse MDCT zero-fills what this writes.
+static void prefilter_and_fold(CeltDecoder* st, int n) {
+  const int start = DECODE_BUFFER_SIZE - n;
+  float etmp[OVERLAP];
+  for (int c = 0; c < st->channels; c++) {
+    float* mem = st->decode_mem[c];
+    comb_filter_out(etmp, mem, start, OVERLAP, st->postfilter_period_old, st->postfilter_period, -st->postfilter_gain_old, -st->postfilter_gain,
+                    imax(st->postfilter_tapset_old, 0), imax(st->postfilter_tapset, 0));
+    for (int i = 0; i < OVERLAP / 2; i++) mem[start + i] = g_window[i] * etmp[OVERLAP - 1 - i] + g_window[OVERLAP - 1 - i] * etmp[i];
+  }
+}
+// celt_decoder.rs:1429-1855 (celt_decode_lost, float, no deep PLC)
+static void celt_decode_lost(CeltDecoder* st, int N, int lm) {
+  const int CC = st->channels;
+  const int start_band = imin(imax(st->start_band, 0), NB_EBANDS), end_band = imin(imax(st->end_band, st->start_band), NB_EBANDS);
+  const int eff_end = imax(start_band, imin(end_band, NB_EBANDS));
+  const int loss_duration = st->loss_duration;
+  const int noise_based = loss_duration >= 40 || start_band != 0 || st->skip_plc;
+  if (noise_based) {
+    for (int c = 0; c < CC; c++) memmove(st->decode_mem[c], st->decode_mem[c] + N, (DECODE_BUFFER_SIZE - N + OVERLAP) * sizeof(float));
+    if (st->prefilter_and_fold) prefilter_and_fold(st, N);
+    const float decay = loss_duration == 0 ? 1.5f : 0.5f;
+    for (int c = 0; c < CC; c++)
+      for (int i = start_band; i < end_band; i++) {
+        const int idx = c * NB_EBANDS + i;
+        st->old_ebands[idx] = fmax32(st->background_log_e[idx], st->old_ebands[idx] - decay);
+      }
+    uint32_t seed = st->rng;
+    std::vector<float> X((size_t)CC * N, 0.f);
+    for (int c = 0; c < CC; c++)
+      for (int i = start_band; i < eff_end; i++) {
+        const int bs = eb(i) << lm;
+        int bw = (eb(i + 1) - eb(i)) << lm;
+        if (bw > N - bs) bw = N - bs > 0 ? N - bs : 0;
+        if (bw == 0) continue;
+        float* x = X.data() + c * N + bs;
+        for (int j = 0; j < bw; j++) { seed = lcg_rand(seed); x[j] = (float)((int32_t)seed >> 20); }
+        renormalise_vector(x, bw, 1.0f);
+      }
+    st->rng = seed;
+    float* out_syn[2];
+    for (int c = 0; c < CC; c++) out_syn[c] = st->decode_mem[c] + DECODE_BUFFER_SIZE - N;
+    celt_synthesis(X.data(), out_syn, st->old_ebands, start_band, eff_end, CC, CC, 0, lm, st->downsample > 1 ? st->downsample : 1, 0, st->quirks);
+    st->prefilter_and_fold = 0;
+    st->skip_plc = 1;
+  } else {
+    enum { LPC_ORDER = 24, PLC_LAG_MAX = 720, PLC_LAG_MIN = 100 };
+    int pitch_index;
+    if (loss_duration == 0) {
+      const float* views[2] = {st->decode_mem[0], st->decode_mem[1]};
+      std::vector<float> lp(DECODE_BUFFER_SIZE >> 1);
+      pitch_downsample(views, CC, lp.data(), DECODE_BUFFER_SIZE);
+      pitch_index = PLC_LAG_MAX - pitch_search(lp.data() + (PLC_LAG_MAX >> 1), lp.data(), DECODE_BUFFER_SIZE - PLC_LAG_MAX, PLC_LAG_MAX - PLC_LAG_MIN);
+      st->last_pitch_index = pitch_index;
+    } else pitch_index = st->last_pitch_index;
+    const float fade = loss_duration == 0 ? 1.0f : 0.8f;
+    pitch_index = imin(imax(pitch_index, PLC_LAG_MIN), PLC_LAG_MAX);
+    const int pi = imin(pitch_index, MAX_PERIOD);
+    const int exc_length = imin(2 * pi, MAX_PERIOD);
+    std::vector<float> exc(MAX_PERIOD + LPC_ORDER), fir(exc_length);
+    for (int c = 0; c < CC; c++) {
+      float* mem = st->decode_mem[c];
+      for (int i = 0; i < MAX_PERIOD + LPC_ORDER; i++) exc[i] = mem[DECODE_BUFFER_SIZE + OVERLAP - MAX_PERIOD - LPC_ORDER + i];
+      float* lpc = st->lpc[c];
+      if (loss_duration == 0) {
+        float ac[LPC_ORDER + 1];
+        celt_autocorr(exc.data() + LPC_ORDER, ac, g_window, OVERLAP, LPC_ORDER, MAX_PERIOD);
+        ac[0] *= 1.0001f;
+        for (int i = 1; i <= LPC_ORDER; i++) { const float f = 0.008f * 0.008f * (float)(i * i); ac[i] -= ac[i] * f; }
+        celt_lpc(lpc, ac, LPC_ORDER);
+      }
+      const int s0 = MAX_PERIOD - exc_length;
+      for (int i = 0; i < exc_length; i++) {
+        float acc = exc[LPC_ORDER + s0 + i];
+        for (int t = 0; t < LPC_ORDER; t++) acc += lpc[t] * exc[LPC_ORDER + s0 + i - 1 - t];
+        fir[i] = acc;
+      }
+      for (int i = 0; i < exc_length; i++) exc[LPC_ORDER + s0 + i] = fir[i];
+      float e1 = 1.0f, e2 = 1.0f;
+      const int dl = exc_length / 2;
+      for (int i = 0; i < dl; i++) {
+        const float a = exc[LPC_ORDER + MAX_PERIOD - dl + i]; e1 += a * a;
+        const float b = exc[LPC_ORDER + MAX_PERIOD - 2 * dl + i]; e2 += b * b;
+      }
+      e1 = fmin32(e1, e2);
+      const float decay = celt_sqrt((0.5f * e1) / e2);
+      memmove(mem, mem + N, (DECODE_BUFFER_SIZE - N) * sizeof(float));
+      const int xo = MAX_PERIOD - pi, xl = N + OVERLAP, si = DECODE_BUFFER_SIZE - N, rb = DECODE_BUFFER_SIZE - MAX_PERIOD - N + xo;
+      float att = fade * decay, s1 = 0.f;
+      int j = 0;
+      for (int i = 0; i < xl; i++) {
+        if (j >= pi) { j -= pi; att *= decay; }
+        mem[si + i] = att * exc[LPC_ORDER + xo + j];
+        const float r = mem[rb + j];
+        s1 += r * r;
+        j++;
+      }
+      float lm_[LPC_ORDER];
+      for (int i = 0; i < LPC_ORDER; i++) lm_[i] = mem[si - 1 - i];
+      for (int i = 0; i < xl; i++) {   // lpc.rs:343-376 (celt_iir)
+        float acc = mem[si + i];
+        for (int t = 0; t < LPC_ORDER; t++) acc -= lpc[t] * lm_[t];
+        mem[si + i] = acc;
+        for (int t = LPC_ORDER - 1; t >= 1; t--) lm_[t] = lm_[t - 1];
+        lm_[0] = acc;
+      }
+      float s2 = 0.f;
+      for (int i = 0; i < xl; i++) s2 += mem[si + i] * mem[si + i];
+      if (s1 > 0.2f * s2) {
+        if (s1 < s2) {
+          const float ratio = celt_sqrt((0.5f * s1 + 1.0f) / (s2 + 1.0f));
+          for (int i = 0; i < OVERLAP; i++) mem[si + i] *= 1.0f - g_window[i] * (1.0f - ratio);
+          for (int i = OVERLAP; i < xl; i++) mem[si + i] *= ratio;
+        }
+      } else for (int i = 0; i < xl; i++) mem[si + i] = 0.f;
+    }
+    st->prefilter_and_fold = 1;
+  }
+  st->loss_duration = imin(10000, loss_duration + (1 << lm));
+}
+
 void CeltDecoder::init(int channels_, int downsample_) {
   init_tables_once();
   channels = channels_;
@@ -1341,6 +1634,8 @@ void CeltDecoder::init(int channels_, int downsample_) {
 }
 void CeltDecoder::reset() {  // types.rs:989-1043
   rng = 0; error = 0; loss_duration = 0;
+  skip_plc = 1; prefilter_and_fold = 0; last_pitch_index = 0;
+  memset(lpc, 0, sizeof(lpc));
   postfilter_period = postfilter_period_old = 0;
   postfilter_gain = postfilter_gain_old = 0.f;
   postfilter_tapset = postfilter_tapset_old = 0;
@@ -1367,7 +1662,14 @@ int celt_decode_with_ec(CeltDecoder* st, const uint8_t* data, int len, float* pc
   const int M = 1 << lm, N = M * SHORT_MDCT;
   if (len > 1275) return -1;
   const int eff_end = imin(end, NB_EBANDS);
-  if (data == nullptr || len <= 1) return -5;  // packet loss concealment: not restated yet
+  if (data == nullptr || len <= 1) {   // packet loss (celt_decoder.rs:2869-2873, 3245-3309)
+    celt_decode_lost(st, N, lm);
+    float* lost_syn[2];
+    for (int c = 0; c < CC; c++) lost_syn[c] = st->decode_mem[c] + DECODE_BUFFER_SIZE - N;
+    deemphasis(lost_syn, pcm, N, CC, downsample, st->preemph_mem, accum);
+    return N / downsample;
+  }
+  if (st->loss_duration == 0) st->skip_plc = 0;
 
   EcDec own;
   EcDec* dec = ext_dec;
@@ -1399,7 +1701,23 @@ int celt_decode_with_ec(CeltDecoder* st, const uint8_t* data, int len, float* pc
   const int short_blocks = is_transient ? M : 0;
   int intra = 0;
   if (tell + 3 <= len_bits) intra = dec->bit_logp(3);
-  // (loss_duration != 0 energy fix-up, celt_decoder.rs:2943-2969, belongs to the PLC row: not reachable here)
+  if (!intra && st->loss_duration != 0) {   // celt_decoder.rs:2943-2969: the first good frame after a loss starts from safer energies
+    const int missing = imin(10, st->loss_duration >> lm);
+    const float safety = lm == 0 ? 1.5f : (lm == 1 ? 0.5f : 0.0f);
+    for (int c = 0; c < 2; c++)
+      for (int i = start; i < end; i++) {
+        const int idx = c * NB_EBANDS + i;
+        float e0 = st->old_ebands[idx];
+        const float e1 = st->old_log_e[idx], e2 = st->old_log_e2[idx];
+        if (e0 < fmax32(e1, e2)) {
+          float slope = fmax32(e1 - e0, 0.5f * (e2 - e0));
+          slope = fmin32(slope, 2.0f);
+          e0 -= fmax32((float)(missing + 1) * slope, 0.0f);
+          st->old_ebands[idx] = fmax32(e0, -20.0f);
+        } else st->old_ebands[idx] = fmin32(st->old_ebands[idx], fmin32(e1, e2));
+        st->old_ebands[idx] -= safety;
+      }
+  }
 
   unquant_coarse_energy(start, end, st->old_ebands, intra, dec, C, lm, quirks & QUIRK_Q8_COARSE_CLAMP);
   int tf_res[NB_EBANDS] = {0};
@@ -1459,39 +1777,10 @@ int celt_decode_with_ec(CeltDecoder* st, const uint8_t* data, int len, float* pc
     anti_collapse(X.data(), collapse_masks, lm, C, N, start, end, st->old_ebands, st->old_log_e, st->old_log_e2, pulses, st->rng);
   if (silence) for (int i = 0; i < 2 * NB_EBANDS; i++) st->old_ebands[i] = -28.0f;
 
-  // celt_synthesis (celt_decoder.rs:573-800)
+  if (st->prefilter_and_fold) prefilter_and_fold(st, N);   // celt_decoder.rs:3641 (after the history has moved, :3354)
   float* out_syn[2];
   for (int c = 0; c < CC; c++) out_syn[c] = st->decode_mem[c] + DECODE_BUFFER_SIZE - N;
-  {
-    int nbk, nb, shift;
-    if (is_transient) { nbk = M; nb = SHORT_MDCT; shift = MAX_LM; }
-    else { nbk = 1; nb = SHORT_MDCT << lm; shift = MAX_LM - lm; }
-    const bool q2 = quirks & QUIRK_Q2_MDCT_ZERO_FILL;
-    std::vector<float> freq(N), freq2(N), temp(N);
-    auto imdct = [&](const float* fr, float* out) {
-      for (int b = 0; b < nbk; b++) {
-        for (int k = 0; k < nb; k++) temp[k] = fr[b + k * nbk];
-        clt_mdct_backward(temp.data(), out + b * nb, N + OVERLAP - b * nb, shift, q2);
-      }
-    };
-    if (CC == 2 && C == 1) {
-      denormalise_bands(X.data(), freq.data(), st->old_ebands, start, eff_end, M, downsample, silence);
-      imdct(freq.data(), out_syn[0]);
-      imdct(freq.data(), out_syn[1]);
-    } else if (CC == 1 && C == 2) {
-      denormalise_bands(X.data(), freq.data(), st->old_ebands, start, eff_end, M, downsample, silence);
-      denormalise_bands(X.data() + N, freq2.data(), st->old_ebands + NB_EBANDS, start, eff_end, M, downsample, silence);
-      for (int i = 0; i < N; i++) freq[i] = 0.5f * (freq[i] + freq2[i]);
-      imdct(freq.data(), out_syn[0]);
-    } else {
-      for (int c = 0; c < CC; c++) {
-        denormalise_bands(X.data() + c * N, freq.data(), st->old_ebands + c * NB_EBANDS, start, eff_end, M, downsample, silence);
-        imdct(freq.data(), out_syn[c]);
-      }
-    }
-    for (int c = 0; c < CC; c++)
-      for (int i = 0; i < N; i++) out_syn[c][i] = out_syn[c][i] < -SIG_SAT ? -SIG_SAT : (out_syn[c][i] > SIG_SAT ? SIG_SAT : out_syn[c][i]);
-  }
+  celt_synthesis(X.data(), out_syn, st->old_ebands, start, eff_end, C, CC, is_transient, lm, downsample, silence, quirks);
   if (st->trace) {
     CeltTrace* t = st->trace;
     t->lm = lm; t->C = C; t->N = N; t->silence = silence; t->transient = is_transient; t->intra = intra; t->spread = spread;
@@ -1546,6 +1835,7 @@ int celt_decode_with_ec(CeltDecoder* st, const uint8_t* data, int len, float* pc
   }
   deemphasis(out_syn, pcm, N, CC, downsample, st->preemph_mem, accum);
   st->loss_duration = 0;
+  st->prefilter_and_fold = 0;
   if (dec->tell() > 8 * len) return -4;  // InvalidPacket (celt_decoder.rs:4128)
   if (dec->error) st->error = 1;
   return N / downsample;

@@ -49,6 +49,8 @@ struct CeltDecoder {
   uint32_t rng = 0;
   int error = 0;
   int loss_duration = 0;
+  int skip_plc = 1, prefilter_and_fold = 0, last_pitch_index = 0;   // types.rs:807-816 (PLC)
+  float lpc[2][24];                                                 // PLC synthesis filter per channel
   int postfilter_period = 0, postfilter_period_old = 0;
   float postfilter_gain = 0, postfilter_gain_old = 0;
   int postfilter_tapset = 0, postfilter_tapset_old = 0;

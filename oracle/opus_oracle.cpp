@@ -188,66 +188,117 @@ struct OpusDecoder {
       }
   }
 
-  // opus_decoder.rs:453-1133. PLC (data == null) and the transitions that call it are not restated (-5).
+  // opus_decoder.rs:453-1133
   int decode_frame(const uint8_t* data, int len, float* pcm, int fsz, int decode_fec) {
-    int F20 = fs / 50, F10 = F20 / 2, F5 = F10 / 2, F2_5 = F5 / 2;
+    const int F20 = fs / 50, F10 = F20 / 2, F5 = F10 / 2, F2_5 = F5 / 2;
     if (fsz < F2_5) return OPUS_BUFFER_TOO_SMALL;
     fsz = fsz < fs / 25 * 3 ? fsz : fs / 25 * 3;
-    if (data == nullptr || len <= 1) return OPUS_UNIMPLEMENTED;  // PLC row (F2)
-    if (decode_fec) return OPUS_UNIMPLEMENTED;
-    int audiosize = frame_size, md = mode, bw = bandwidth;
-    int celt_only = md == MODE_CELT_ONLY, prev_celt_only = prev_mode == MODE_CELT_ONLY;
+    if (data == nullptr || len <= 1) { data = nullptr; fsz = fsz < frame_size ? fsz : frame_size; }   // :491-496: concealment
+    int audiosize, md, bw, celt_only;
+    if (data) { audiosize = frame_size; md = mode; bw = bandwidth; celt_only = md == MODE_CELT_ONLY; }
+    else {
+      audiosize = fsz;
+      md = prev_redundancy ? MODE_CELT_ONLY : prev_mode;
+      bw = 0;
+      celt_only = md == MODE_CELT_ONLY;
+      if (md == 0) {   // nothing decoded yet: silence
+        for (int i = 0; i < audiosize * channels; i++) pcm[i] = 0.f;
+        prev_mode = 0; prev_redundancy = 0; range_final = 0;
+        return audiosize;
+      }
+      if (audiosize > F20) {   // conceal in chunks of at most 20 ms
+        int done = 0;
+        while (done < audiosize) {
+          const int chunk = audiosize - done < F20 ? audiosize - done : F20;
+          const int r = decode_frame(nullptr, 0, pcm + (size_t)done * channels, chunk, 0);
+          if (r < 0) return r;
+          if (r != chunk) return OPUS_INTERNAL_ERROR;
+          done += r;
+        }
+        prev_mode = md; prev_redundancy = 0; range_final = 0;
+        return audiosize;
+      } else if (audiosize < F20) {
+        if (audiosize > F10) audiosize = F10;
+        else if (!celt_only && audiosize > F5 && audiosize < F10) audiosize = F5;
+      }
+    }
     EcDec dec;
-    dec.init(data, (uint32_t)len);
-    int transition = prev_mode > 0 && ((celt_only && !prev_celt_only && !prev_redundancy) || (!celt_only && prev_celt_only));
-    if (transition && celt_only) return OPUS_UNIMPLEMENTED;  // needs decode_frame(None) = PLC
+    dec.init(data ? data : (const uint8_t*)"", data ? (uint32_t)len : 0u);
+    const int prev_celt_only = prev_mode == MODE_CELT_ONLY;
+    int transition = 0;
+    std::vector<float> pcm_transition;
+    if (data && prev_mode > 0 && ((celt_only && !prev_celt_only && !prev_redundancy) || (!celt_only && prev_celt_only))) {
+      transition = 1;
+      if (celt_only) {   // SILK / hybrid -> CELT without redundancy: 5 ms of the old mode's concealment to fade out of
+        pcm_transition.assign((size_t)F5 * channels, 0.f);
+        const int ts = audiosize < F5 ? audiosize : F5;
+        const int r = decode_frame(nullptr, 0, pcm_transition.data(), ts, 0);
+        if (r < 0) return r;
+        if (r != ts) return OPUS_INTERNAL_ERROR;
+      }
+    }
     if (audiosize > fsz) return OPUS_BAD_ARG;
     int celt_accum = !celt_only, redundancy = 0, celt_to_silk = 0, have_range_final = 0;
     uint32_t redundant_rng = 0, silk_range_final = 0;
     const uint8_t* red_data = nullptr; int red_bytes = 0;
     std::vector<float> redundant_audio;
     if (!celt_only) {
-      if (audiosize < F10) return OPUS_UNIMPLEMENTED;  // pcm_too_small path only reachable through PLC sizes
+      const int pcm_too_small = audiosize < F10;
+      const int silk_len = pcm_too_small ? F10 : audiosize;
       int payload_ms = 1000 * audiosize / fs; if (payload_ms < 10) payload_ms = 10;
       dec_control.n_channels_api = channels; dec_control.api_sample_rate = fs; dec_control.payload_size_ms = payload_ms;
-      dec_control.n_channels_internal = stream_channels;
-      dec_control.internal_sample_rate = md == MODE_SILK_ONLY ? (bw == BW_NB ? 8000 : (bw == BW_MB ? 12000 : 16000)) : 16000;
+      if (data) {
+        dec_control.n_channels_internal = stream_channels;
+        dec_control.internal_sample_rate = md == MODE_SILK_ONLY ? (bw == BW_NB ? 8000 : (bw == BW_MB ? 12000 : 16000)) : 16000;
+      } else if (dec_control.internal_sample_rate == 0 && silk.ch[0].fs_khz > 0) dec_control.internal_sample_rate = silk.ch[0].fs_khz * 1000;
+      if (dec_control.n_channels_internal == 0) dec_control.n_channels_internal = stream_channels;
       if (prev_celt_only) silk.reset(0);
-      std::vector<int16_t> so((size_t)audiosize * channels);
+      std::vector<int16_t> so((size_t)silk_len * channels, 0);
       int decoded = 0;
       while (decoded < audiosize) {
-        int r = silk.decode(&dec_control, SILK_FLAG_DECODE_NORMAL, decoded == 0, &dec, so.data() + (size_t)decoded * channels);
-        if (r == -5) return OPUS_UNIMPLEMENTED;
-        if (r <= 0) return OPUS_INTERNAL_ERROR;
+        const int flag = data ? (decode_fec ? SILK_FLAG_DECODE_LBRR : SILK_FLAG_DECODE_NORMAL) : SILK_FLAG_PACKET_LOST;
+        int r = silk.decode(&dec_control, flag, decoded == 0, &dec, so.data() + (size_t)decoded * channels);
+        if (r < 0 || r == 0) {
+          if (data) return OPUS_INTERNAL_ERROR;
+          for (int i = decoded * channels; i < audiosize * channels; i++) so[i] = 0;   // :699-702: a failing concealment is silence
+          r = audiosize - decoded;
+        }
         decoded += r;
       }
-      for (int i = 0; i < decoded * channels; i++) pcm[i] = (float)so[i] * (1.0f / 32768.0f);  // silk_int16_to_res
-      int tell = dec.tell();
-      if (tell + 17 + (md == MODE_HYBRID ? 20 : 0) <= 8 * len) {
-        redundancy = md == MODE_HYBRID ? dec.bit_logp(12) : 1;
-        if (redundancy) {
-          celt_to_silk = dec.bit_logp(1);
-          int bytes = md == MODE_HYBRID ? (int)dec.uint(256) + 2 : len - ((dec.tell() + 7) >> 3);
-          if (bytes > len || bytes < 0) return OPUS_BAD_ARG;
-          red_bytes = bytes;
-          int cutoff = len - bytes;
-          red_data = data + cutoff;
-          len = cutoff;
-          if (len * 8 < dec.tell()) { len = 0; redundancy = 0; red_data = nullptr; red_bytes = 0; }
-          if (red_bytes > 0) {
-            if (dec.storage < (uint32_t)red_bytes) return OPUS_BAD_ARG;
-            dec.storage -= (uint32_t)red_bytes;
+      for (int i = 0; i < audiosize * channels; i++) pcm[i] = (float)so[i] * (1.0f / 32768.0f);  // silk_int16_to_res
+      if (!decode_fec && data) {
+        const int tell = dec.tell();
+        if (tell + 17 + (md == MODE_HYBRID ? 20 : 0) <= 8 * len) {
+          redundancy = md == MODE_HYBRID ? dec.bit_logp(12) : 1;
+          if (redundancy) {
+            celt_to_silk = dec.bit_logp(1);
+            int bytes = md == MODE_HYBRID ? (int)dec.uint(256) + 2 : len - ((dec.tell() + 7) >> 3);
+            if (bytes > len || bytes < 0) return OPUS_BAD_ARG;
+            red_bytes = bytes;
+            int cutoff = len - bytes;
+            red_data = data + cutoff;
+            len = cutoff;
+            if (len * 8 < dec.tell()) { len = 0; redundancy = 0; red_data = nullptr; red_bytes = 0; }
+            if (red_bytes > 0) {
+              if (dec.storage < (uint32_t)red_bytes) return OPUS_BAD_ARG;
+              dec.storage -= (uint32_t)red_bytes;
+            }
           }
         }
       }
-      if (len > 1 && md == MODE_SILK_ONLY) { silk_range_final = dec.rng; have_range_final = 1; }
+      if (data && len > 1 && (md == MODE_SILK_ONLY || decode_fec)) { silk_range_final = dec.rng; have_range_final = 1; }
       if (redundancy) transition = 0;
-      else if (transition) return OPUS_UNIMPLEMENTED;  // CELT -> SILK without redundancy: PLC cross-fade
+      else if (transition) {   // CELT -> SILK / hybrid without redundancy: 5 ms of CELT concealment to fade out of
+        pcm_transition.assign((size_t)F5 * channels, 0.f);
+        const int ts = audiosize < F5 ? audiosize : F5;
+        const int r = decode_frame(nullptr, 0, pcm_transition.data(), ts, 0);
+        if (r < 0) return r;
+        if (r != ts) return OPUS_INTERNAL_ERROR;
+      }
     }
     int start_band = celt_only ? 0 : 17;
-    int endband = 21;
-    switch (bw) { case BW_NB: endband = 13; break; case BW_MB: case BW_WB: endband = 17; break; case BW_SWB: endband = 19; break; case BW_FB: endband = 21; break; }
-    celt.end_band = endband;
+    switch (bw) { case BW_NB: celt.end_band = 13; break; case BW_MB: case BW_WB: celt.end_band = 17; break; case BW_SWB: celt.end_band = 19; break;
+                  case BW_FB: celt.end_band = 21; break; default: break; }   // bandwidth 0 (concealment): the end band stays
     celt.stream_channels = stream_channels;
     if (redundancy && celt_to_silk) {
       redundant_audio.assign((size_t)F5 * channels, 0.f);
@@ -268,10 +319,11 @@ struct OpusDecoder {
     } else {
       if (md != prev_mode && prev_mode > 0 && !prev_redundancy) celt.reset();
       int celt_n = audiosize < F20 ? audiosize : F20;
-      int ret = celt_decode_with_ec(&celt, data, len, pcm, celt_n, &dec, celt_accum);
+      const uint8_t* celt_data = decode_fec ? nullptr : data;
+      int ret = celt_decode_with_ec(&celt, celt_data, celt_data ? len : 0, pcm, celt_n, celt_data ? &dec : nullptr, celt_accum);
       if (ret < 0) return ret;
       if (ret != celt_n) return OPUS_INTERNAL_ERROR;
-      if (len > 1) celt_final_range = celt.rng;
+      if (data && len > 1 && celt_data) celt_final_range = celt.rng;
     }
     if (redundancy && !celt_to_silk) {
       redundant_audio.assign((size_t)F5 * channels, 0.f);
@@ -292,27 +344,63 @@ struct OpusDecoder {
         std::vector<float> tail(pcm + fade, pcm + 2 * fade);
         smooth_fade(redundant_audio.data() + fade, tail.data(), pcm + fade, F2_5);
       }
+    } else if (transition && !pcm_transition.empty()) {
+      if (audiosize >= F5) {
+        for (int i = 0; i < fade; i++) pcm[i] = pcm_transition[i];
+        std::vector<float> tail(pcm + fade, pcm + 2 * fade);
+        smooth_fade(pcm_transition.data() + fade, tail.data(), pcm + fade, F2_5);
+      } else {
+        std::vector<float> cur(pcm, pcm + fade);
+        smooth_fade(pcm_transition.data(), cur.data(), pcm, F2_5);
+      }
     }
-    uint32_t final_range = len > 1 ? (have_range_final ? silk_range_final : celt_final_range) : 0;
+    const int have_packet = data != nullptr && len > 1;
+    uint32_t final_range = have_packet ? (have_range_final ? silk_range_final : celt_final_range) : 0;
     last_redundancy = redundancy;
     prev_mode = md;
     prev_redundancy = redundancy && !celt_to_silk;
-    range_final = len > 1 ? final_range ^ redundant_rng : 0;
+    range_final = have_packet ? final_range ^ redundant_rng : 0;
     return audiosize;
   }
 
-  // opus_decoder.rs:1139-1367 (no FEC / PLC arms yet)
+  // opus_decoder.rs:1139-1367
   int decode_native(const uint8_t* data, int len, float* pcm, int fsz, int decode_fec, int soft_clip) {
     if (fsz <= 0) return OPUS_BAD_ARG;
     if ((decode_fec || len == 0 || data == nullptr) && fsz % (fs / 400) != 0) return OPUS_BAD_ARG;
-    if (len == 0 || data == nullptr) return OPUS_UNIMPLEMENTED;
+    if (len == 0 || data == nullptr) {   // packet loss (:1186-1222): conceal the whole buffer, no soft clip
+      int done = 0;
+      while (done < fsz) {
+        const int r = decode_frame(nullptr, 0, pcm + (size_t)done * channels, fsz - done, 0);
+        if (r < 0) return r;
+        if (r == 0) return OPUS_INTERNAL_ERROR;
+        done += r;
+      }
+      last_packet_duration = done;
+      apply_gain_clip(pcm, done, 0);
+      return done;
+    }
     uint8_t toc = data[0];
     int pmode = packet_mode(toc), pbw = packet_bandwidth(toc), pfs = packet_samples_per_frame(toc, fs);
     int pch = (toc & 4) ? 2 : 1;
     Parsed P;
     int r = packet_parse(data, len, 0, &P);
     if (r < 0) return r;
-    if (decode_fec) return OPUS_UNIMPLEMENTED;
+    if (decode_fec) {   // :1240-1316
+      if (fsz < pfs || pmode == MODE_CELT_ONLY || mode == MODE_CELT_ONLY) return decode_native(nullptr, 0, pcm, fsz, 0, soft_clip);
+      const int duration_copy = last_packet_duration;
+      if (fsz != pfs) {
+        const int lead = fsz - pfs;
+        const int rr = decode_native(nullptr, 0, pcm, lead, 0, soft_clip);
+        if (rr < 0) { last_packet_duration = duration_copy; return rr; }
+        if (rr != lead) { last_packet_duration = duration_copy; return OPUS_INTERNAL_ERROR; }
+      }
+      mode = pmode; bandwidth = pbw; frame_size = pfs; stream_channels = pch;
+      const int ret = decode_frame(P.frames[0], P.sizes[0], pcm + (size_t)(fsz - pfs) * channels, pfs, 1);
+      if (ret < 0) return ret;
+      last_packet_duration = fsz;
+      apply_gain_clip(pcm, fsz, 0);
+      return fsz;
+    }
     if (P.count * pfs > fsz) return OPUS_BUFFER_TOO_SMALL;
     mode = pmode; bandwidth = pbw; frame_size = pfs; stream_channels = pch;
     int nb = 0;
