@@ -83,6 +83,12 @@ int bd_decode_f32(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, c
 int bd_decode_i16(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
                   const uint8_t* flags, int16_t* pcm, uint32_t pcm_stride, int32_t* samples_out, uint32_t* final_range_out);
 
+/* 24-bit output in int32 containers (opus_decode24, src/opus_decoder.rs:1718-1800; Decoder::decode_24bit, src/codec.rs:867):
+ * the float path without soft clip, then clamp(x * 2^23, -8388608, 8388607) rounded to nearest (res_to_int24,
+ * src/celt/celt_decoder.rs:3165-3176). Same arguments as bd_decode_f32 with an int32 PCM buffer. */
+int bd_decode_i24(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
+                  const uint8_t* flags, int32_t* pcm, uint32_t pcm_stride, int32_t* samples_out, uint32_t* final_range_out);
+
 /* Device-resident form of the same call for callers that already hold packets in HBM and keep PCM there.
  * Regular grid: packet (t, j) = index t * n_lanes + j belongs to stream lane_stream[j] (NULL: stream j);
  * a zero-length packet marks "nothing for this lane at this tick". All pointers are DEVICE pointers;
@@ -100,6 +106,9 @@ typedef struct bd_stream_info {
   int32_t last_packet_duration;
   int32_t prev_mode;      /* 0 none, 1000 SILK, 1001 hybrid, 1002 CELT */
   int32_t celt_error;
+  int32_t bandwidth;      /* Decoder::bandwidth (src/codec.rs:941-953): 0 before the first packet, else 1101 NB .. 1105 FB */
+  int32_t pitch;          /* Decoder::pitch (src/opus_decoder.rs:1840-1849): CELT post-filter period after a CELT-only packet,
+                             else the SILK pitch lag of the last voiced frame at 48 kHz (0 if unvoiced) */
 } bd_stream_info;
 int bd_get_stream_info(bd_handle* h, uint32_t stream_id, bd_stream_info* out);
 

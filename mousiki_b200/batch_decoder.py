@@ -28,7 +28,7 @@ EXPORTS = [
     "bd_create", "bd_destroy", "bd_reset_streams", "bd_last_error", "bd_decode_f32", "bd_decode_i16", "bd_decode_grid_dev",
     "bd_get_stream_info", "bd_alloc_pinned", "bd_free_pinned", "bd_last_launch_count", "bd_debug_capture", "bd_profile_enable", "bd_profile_read",
     "bd_packet_get_mode", "bd_packet_get_bandwidth", "bd_packet_get_nb_channels", "bd_packet_get_samples_per_frame", "bd_packet_get_nb_frames",
-    "bd_packet_get_nb_samples", "bd_debug_kat",
+    "bd_packet_get_nb_samples", "bd_debug_kat", "bd_decode_i24",
 ]
 
 
@@ -39,7 +39,8 @@ class BdConfig(C.Structure):
 
 
 class BdStreamInfo(C.Structure):
-    _fields_ = [("final_range", C.c_uint32), ("last_packet_duration", C.c_int32), ("prev_mode", C.c_int32), ("celt_error", C.c_int32)]
+    _fields_ = [("final_range", C.c_uint32), ("last_packet_duration", C.c_int32), ("prev_mode", C.c_int32), ("celt_error", C.c_int32),
+                ("bandwidth", C.c_int32), ("pitch", C.c_int32)]
 
 
 class DecoderError(RuntimeError):
@@ -65,7 +66,7 @@ def load_library():
     lib.bd_reset_streams.argtypes = [vp, u32p, C.c_uint32]
     lib.bd_last_error.argtypes = [vp]
     lib.bd_last_error.restype = C.c_char_p
-    for fn in (lib.bd_decode_f32, lib.bd_decode_i16):
+    for fn in (lib.bd_decode_f32, lib.bd_decode_i16, lib.bd_decode_i24):
         fn.argtypes = [vp, vp, vp, vp, C.c_uint32, vp, vp, C.c_uint32, vp, vp]
     lib.bd_decode_grid_dev.argtypes = [vp, vp, vp, C.c_uint32, C.c_uint32, vp, vp, vp, C.c_uint32, vp, vp, vp]
     lib.bd_get_stream_info.argtypes = [vp, C.c_uint32, C.POINTER(BdStreamInfo)]
@@ -149,7 +150,7 @@ class BatchDecoder:
             self._check(self._lib.bd_reset_streams(self._h, _p(ids), len(ids)), "bd_reset_streams")
 
     # -- Decoder::decode_float / Decoder::decode on a batch
-    def _decode(self, arena, offsets, stream_ids, frame_size, flags, i16, capture=False):
+    def _decode(self, arena, offsets, stream_ids, frame_size, flags, i16, capture=False, i24=False):
         arena = np.ascontiguousarray(arena, dtype=np.uint8)
         offsets = np.ascontiguousarray(offsets, dtype=np.uint32)
         stream_ids = np.ascontiguousarray(stream_ids, dtype=np.uint32)
@@ -157,7 +158,7 @@ class BatchDecoder:
         if len(offsets) != n + 1:
             raise ValueError("offsets must have n_packets + 1 entries")
         stride = int(frame_size) * self.channels
-        pcm = np.zeros((n, stride), dtype=np.int16 if i16 else np.float32)
+        pcm = np.zeros((n, stride), dtype=np.int16 if i16 else (np.int32 if i24 else np.float32))
         samples = np.zeros(n, dtype=np.int32)
         rng = np.zeros(n, dtype=np.uint32)
         fl = None if flags is None else np.ascontiguousarray(flags, dtype=np.uint8)
@@ -166,7 +167,7 @@ class BatchDecoder:
             iy = np.zeros((n, 2, 960), dtype=np.int32)
             xs = np.zeros((n, 2, 960), dtype=np.float32)
             self._lib.bd_debug_capture(self._h, _p(iy), _p(xs), n)
-        fn = self._lib.bd_decode_i16 if i16 else self._lib.bd_decode_f32
+        fn = self._lib.bd_decode_i16 if i16 else (self._lib.bd_decode_i24 if i24 else self._lib.bd_decode_f32)
         rc = fn(self._h, _p(arena), _p(offsets), _p(stream_ids), n, _p(fl), _p(pcm), stride, _p(samples), _p(rng))
         if capture:
             self._lib.bd_debug_capture(self._h, None, None, 0)
@@ -190,6 +191,10 @@ class BatchDecoder:
     def decode(self, arena, offsets, stream_ids, frame_size=960, flags=None):
         """i16 output with the reference's soft clip (opus_decode)."""
         return self._decode(arena, offsets, stream_ids, frame_size, flags, True)
+
+    def decode_24bit(self, arena, offsets, stream_ids, frame_size=960, flags=None):
+        """24-bit samples in int32 containers (Decoder::decode_24bit, src/codec.rs:867; opus_decode24): no soft clip."""
+        return self._decode(arena, offsets, stream_ids, frame_size, flags, False, i24=True)
 
     def decode_float_packets(self, packets, stream_ids, frame_size=960):
         arena, offsets = pack_packets(packets)
@@ -222,7 +227,7 @@ class BatchDecoder:
         info = BdStreamInfo()
         self._check(self._lib.bd_get_stream_info(self._h, int(stream_id), C.byref(info)), "bd_get_stream_info")
         return {"final_range": info.final_range, "last_packet_duration": info.last_packet_duration, "prev_mode": info.prev_mode,
-                "celt_error": info.celt_error}
+                "celt_error": info.celt_error, "bandwidth": info.bandwidth, "pitch": info.pitch}
 
 
 # ---- packet queries without a decoder (src/packet.rs:30-56, 177-280; Decoder::packet_samples, src/codec.rs:838) --------------

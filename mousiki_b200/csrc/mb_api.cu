@@ -484,6 +484,14 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
   }
   if (l < 2) s.softclip_mem[l] = mem;
 }
+// res_to_int24 (src/celt/celt_decoder.rs:3165-3176), in place on the float scratch: same 32-bit containers
+__global__ void k_f32_to_i24(float* __restrict__ pcm, size_t n) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float v = pcm[i] * (32768.0f * 256.0f);
+  v = v < -8388608.0f ? -8388608.0f : (v > 8388607.0f ? 8388607.0f : v);
+  ((int32_t*)pcm)[i] = __float2int_rn(v);
+}
 // decode_float leaves the clipper memory cleared (src/opus_decoder.rs:1411-1417)
 __global__ void k_clear_softclip(uint32_t n_lanes, const uint32_t* __restrict__ lane_stream, StreamState* st) {
   uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
@@ -599,6 +607,7 @@ struct bd_handle {
   int disable_inv = 0;
   float gain = 1.f;
   uint32_t max_frames_per_pass = 0;
+  bool want_i24 = false;       // the running host call delivers 24-bit integers (bd_decode_i24)
   bool serial_bands = false;   // MOUSIKI_B200_SERIAL_BANDS=1: per-stream band pass whatever the call size (see k_energy)
   std::string err;
   uint32_t launches = 0;
@@ -763,6 +772,14 @@ int bd_get_stream_info(bd_handle* h, uint32_t sid, bd_stream_info* out) {
   CK(cudaMemcpy(&s, h->states.as<StreamState>() + sid, sizeof(s), cudaMemcpyDeviceToHost));
   out->final_range = s.range_final; out->last_packet_duration = s.last_packet_duration; out->prev_mode = s.prev_mode;
   out->celt_error = s.celt_error;
+  out->bandwidth = s.bandwidth;
+  if (s.prev_mode == 1002) out->pitch = s.pf[0].period;                      // CELT: the post-filter period (OPUS_GET_PITCH)
+  else {                                                                     // SILK / hybrid: dec_control.prev_pitch_lag (dec_api.rs:420-427)
+    SilkState ss;
+    CK(cudaMemcpy(&ss, h->silk_states.as<SilkState>() + sid, sizeof(ss), cudaMemcpyDeviceToHost));
+    const int fs = ss.ch[0].fs_khz;
+    out->pitch = (ss.ch[0].prev_signal_type == 2 && (fs == 8 || fs == 12 || fs == 16)) ? ss.ch[0].lag_prev * (fs == 8 ? 6 : fs == 12 ? 4 : 3) : 0;
+  }
   return BD_OK;
 }
 
@@ -1171,7 +1188,7 @@ static int decode_host_impl(bd_handle* h, const uint8_t* arena, const uint32_t* 
   CK(cudaMemsetAsync(h->d_samples.p, 0, (size_t)n_packets * 4, s));
   // cell order == packet order: each pass's PCM is one contiguous block, copied out on a second stream as soon as
   // the pass is done
-  const bool overlap_out = identity;
+  const bool overlap_out = identity && !h->want_i24;
   h->pass_out.on = overlap_out;
   h->pass_event_next = 0;
   h->pass_out.host_pcm = pcm_f32 ? (char*)pcm_f32 : (char*)pcm_i16;
@@ -1183,6 +1200,10 @@ static int decode_host_impl(bd_handle* h, const uint8_t* arena, const uint32_t* 
                               h->d_range.as<uint32_t>(), n_rows, s, d_dbg_iy, d_dbg_x, d_out_map);
   h->pass_out.on = false;
   if (rc != BD_OK) { cudaStreamSynchronize(h->copy_stream); return rc; }
+  if (h->want_i24 && pcm_elems) {
+    k_f32_to_i24<<<(unsigned)((pcm_elems + 255) / 256), 256, 0, s>>>(d_f32, pcm_elems);
+    h->launches += 1;
+  }
   if (!overlap_out) {
     if (pcm_f32) CK(cudaMemcpyAsync(pcm_f32, d_f32, pcm_elems * sizeof(float), cudaMemcpyDeviceToHost, s));
     else CK(cudaMemcpyAsync(pcm_i16, d_i16, pcm_elems * sizeof(int16_t), cudaMemcpyDeviceToHost, s));
@@ -1243,6 +1264,14 @@ static int decode_host(bd_handle* h, const uint8_t* arena, const uint32_t* offse
 int bd_decode_f32(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
                   const uint8_t* flags, float* pcm, uint32_t pcm_stride, int32_t* samples_out, uint32_t* final_range_out) {
   return decode_host(h, arena, offsets, stream_ids, n_packets, flags, pcm, nullptr, pcm_stride, samples_out, final_range_out);
+}
+int bd_decode_i24(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
+                  const uint8_t* flags, int32_t* pcm, uint32_t pcm_stride, int32_t* samples_out, uint32_t* final_range_out) {
+  if (!h) return BD_ERR_BAD_ARG;
+  h->want_i24 = true;
+  const int rc = decode_host(h, arena, offsets, stream_ids, n_packets, flags, (float*)pcm, nullptr, pcm_stride, samples_out, final_range_out);
+  h->want_i24 = false;
+  return rc;
 }
 int bd_decode_i16(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
                   const uint8_t* flags, int16_t* pcm, uint32_t pcm_stride, int32_t* samples_out, uint32_t* final_range_out) {

@@ -37,7 +37,7 @@ struct StreamState {
   int32_t celt_error;
   int32_t prev_redundancy;   // the last packet ended in a SILK -> CELT redundancy frame (opus_decoder.rs:1117)
   int32_t fold_serial;       // the stream has decoded a SILK-side frame: its CELT-only frames keep the fold buffer exact too
-  int32_t reserved[1];
+  int32_t bandwidth;         // 0 before the first packet, else 1101 (NB) .. 1105 (FB) of the last packet (opus_decoder.rs:1322)
 };
 
 MB_DEV void stream_state_reset(StreamState& s) {
@@ -48,7 +48,7 @@ MB_DEV void stream_state_reset(StreamState& s) {
   s.softclip_mem[0] = s.softclip_mem[1] = 0.f;
   s.celt_error = 0;
   s.prev_redundancy = 0; s.fold_serial = 0;
-  s.reserved[0] = 0;
+  s.bandwidth = 0;
 }
 
 // per-frame side data produced here and consumed by phases 2b / 2c
@@ -91,7 +91,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
   }
   uint32_t st_rng = st.rng, st_range_final = st.range_final;
   int st_loss_duration = st.loss_duration, st_prev_mode = st.prev_mode, st_last_duration = st.last_packet_duration;
-  int st_celt_error = st.celt_error, st_prev_redundancy = st.prev_redundancy, st_fold_serial = st.fold_serial;
+  int st_celt_error = st.celt_error, st_prev_redundancy = st.prev_redundancy, st_fold_serial = st.fold_serial, st_bandwidth = st.bandwidth;
   MB_SYNC();
   uint32_t sample_off = 0;
   // Band pass of CELT-only frames. The reference's fold buffer outlives the frame (mb_celt_bands.cuh), so only a pass that
@@ -137,6 +137,10 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
       }
       pkt_failed = true;
       continue;
+    }
+    {   // opus_packet_get_bandwidth (src/packet.rs:177-204) of the packet the decoder has just taken in
+      const uint32_t toc = (status >> 21) & 255u, two = (toc >> 5) & 3u;
+      st_bandwidth = (toc & 0x80u) ? (two == 0 ? 1101 : 1102 + (int)two) : ((toc & 0x60u) == 0x60u ? ((toc & 0x10u) ? 1105 : 1104) : 1101 + (int)two);
     }
     uint32_t h0 = r[S_HDR0 * 32];
     const bool silk_bit = ((status >> 16) & 1u) != 0, hybrid = ((status >> 17) & 1u) != 0;
@@ -297,7 +301,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
   if (lead) {
     st.rng = st_rng; st.range_final = st_range_final; st.loss_duration = st_loss_duration; st.prev_mode = st_prev_mode;
     st.last_packet_duration = st_last_duration; st.celt_error = st_celt_error; st.prev_redundancy = st_prev_redundancy;
-    st.fold_serial = st_fold_serial;
+    st.fold_serial = st_fold_serial; st.bandwidth = st_bandwidth;
     // Fold-buffer write-back of the parallel band pass (mb_celt_bands.cuh): walking the lane's CELT-only frames backwards,
     // each one keeps the words of its footprint that no later frame of the pass covers. A frame's footprint is the first
     // C * norm_len words of the reference's storage (bands.rs:2614-2625), capped at what hybrid frames can read.

@@ -20,9 +20,8 @@ namespace mb {
 // a hybrid one needs the CELT fade-out frame (src/opus_decoder.rs:868-893), whose record is parsed here; whether it is
 // used is decided by the stream pass (k_energy), which knows the real prev_mode.
 MB_TBL uint8_t kCeltSilenceFrame[2] = {0xFF, 0xFF};
-MB_DEV void parse_cell(const uint8_t* arena, const uint32_t* offsets, uint32_t pkt, uint32_t* rec_base, int CC, uint32_t quirks,
-                       int disable_inv, int cap_per_ch, const uint8_t* flags, uint32_t prev_pkt = 0xffffffffu,
-                       const int32_t* prev_mode = nullptr) {
+MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint32_t pkt, uint32_t* rec_base, int CC, uint32_t quirks,
+                            int disable_inv, int cap_per_ch, const uint8_t* flags, uint32_t prev_pkt, const int32_t* prev_mode) {
   if (pkt == 0xffffffffu) { rec_base[S_STATUS * 32] = 1u << 15; return; }
   // bits 4..7 of the flags: the host front end already rejected the packet (mb_host_packets.h: invalid framing,
   // row too small for all its frames); the cell only exists to report the code with the stream's final_range
@@ -98,6 +97,17 @@ MB_DEV void parse_cell(const uint8_t* arena, const uint32_t* offsets, uint32_t p
     }
   }
   rec_base[S_STATUS * 32] = (uint32_t)(uint8_t)(int8_t)code;
+}
+
+// The cell's status word also carries the packet's TOC byte (bits 21-28): the stream pass derives the decoder's bandwidth
+// query from it (Decoder::bandwidth, src/codec.rs:941-953).
+#define MB_ST_TOC(s) (((s) >> 21) & 255u)
+MB_DEV void parse_cell(const uint8_t* arena, const uint32_t* offsets, uint32_t pkt, uint32_t* rec_base, int CC, uint32_t quirks,
+                       int disable_inv, int cap_per_ch, const uint8_t* flags, uint32_t prev_pkt = 0xffffffffu,
+                       const int32_t* prev_mode = nullptr) {
+  parse_cell_body(arena, offsets, pkt, rec_base, CC, quirks, disable_inv, cap_per_ch, flags, prev_pkt, prev_mode);
+  if (pkt != 0xffffffffu && !(flags && (flags[pkt] >> 4)) && offsets[pkt + 1] > offsets[pkt])
+    rec_base[S_STATUS * 32] |= (uint32_t)arena[offsets[pkt]] << 21;
 }
 
 }  // namespace mb

@@ -495,6 +495,24 @@ void orc_set_gain(void* h, int gain_q8) { ((OpusDecoder*)h)->decode_gain = gain_
 uint32_t orc_final_range(void* h) { return ((OpusDecoder*)h)->range_final; }
 int orc_last_redundancy(void* h) { return ((OpusDecoder*)h)->last_redundancy; }
 int orc_last_packet_duration(void* h) { return ((OpusDecoder*)h)->last_packet_duration; }
+int orc_bandwidth(void* h) { return ((OpusDecoder*)h)->bandwidth; }                                  // OPUS_GET_BANDWIDTH (opus_decoder.rs:1832)
+int orc_pitch(void* h) {                                                                              // OPUS_GET_PITCH (opus_decoder.rs:1840-1849)
+  OpusDecoder* d = (OpusDecoder*)h;
+  return d->prev_mode == MODE_CELT_ONLY ? d->celt.postfilter_period : d->dec_control.prev_pitch_lag;
+}
+// opus_decode24 (opus_decoder.rs:1718-1800): float decode without soft clip, then res_to_int24 (celt_decoder.rs:3165-3176)
+int orc_decode_i24(void* h, const uint8_t* data, int len, int32_t* pcm, int frame_size, int fec) {
+  OpusDecoder* d = (OpusDecoder*)h;
+  if (frame_size <= 0) return OPUS_BAD_ARG;
+  std::vector<float> tmp((size_t)frame_size * d->channels, 0.f);
+  const int r = d->decode_native(data, len, tmp.data(), frame_size, fec, 0);
+  for (int i = 0; i < r * d->channels; i++) {
+    float v = tmp[i] * (32768.0f * 256.0f);
+    v = v < -8388608.0f ? -8388608.0f : (v > 8388607.0f ? 8388607.0f : v);
+    pcm[i] = (int32_t)lrintf(v);
+  }
+  return r;
+}
 
 // opus_decode_float (opus_decoder.rs:1803-1826)
 int orc_decode_float(void* h, const uint8_t* data, int len, float* pcm, int frame_size, int fec) {
