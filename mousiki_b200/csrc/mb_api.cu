@@ -24,6 +24,7 @@
 #include "mb_host_packets.h"
 #include "mb_celt_imdct.cuh"
 #include "mb_celt_tail.cuh"
+#include "mb_celt_plc.cuh"
 #include "mb_frame.cuh"
 #include "mb_silk_out.cuh"
 #include "mb_kat.cuh"
@@ -48,16 +49,16 @@ __global__ void __launch_bounds__(128, 7) k_parse(const uint8_t* __restrict__ ar
 // one warp per stream, 4 streams per CTA
 constexpr int ENERGY_WARPS = 4;
 __global__ void __launch_bounds__(32 * ENERGY_WARPS) k_energy(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
-                                               const uint32_t* __restrict__ rec, StreamState* st, const uint32_t* __restrict__ lane_stream,
+                                               uint32_t* rec, StreamState* st, const uint32_t* __restrict__ lane_stream,
                                                float* __restrict__ en, FrameMeta* __restrict__ meta, int32_t* __restrict__ samples_out,
                                                uint32_t* __restrict__ final_range_out, uint32_t quirks,
-                                               const uint8_t* __restrict__ flags, int serial_all, int force_float_row) {
+                                               const uint8_t* __restrict__ flags, int serial_all, int force_float_row, int CC) {
   __shared__ EnergySmem sm[ENERGY_WARPS];
   const uint32_t lane = blockIdx.x * ENERGY_WARPS + (threadIdx.x >> 5);
   if (lane >= n_lanes) return;
   Team tm = {(int)(threadIdx.x & 31), 32};
   celt_energy_stream(tm, &sm[threadIdx.x >> 5], lane, n_lanes, n_ticks, pkt_map, rec, st, lane_stream, en, meta, samples_out, final_range_out,
-                     quirks, flags, serial_all, force_float_row);
+                     quirks, flags, serial_all, force_float_row, CC);
 }
 
 constexpr int PVQ_THREADS = 64;
@@ -154,6 +155,14 @@ __global__ void __launch_bounds__(32 * COMB_WARPS) k_comb(TailParams P) {
   celt_comb_channel(tm, &sm[threadIdx.x >> 5], idx / (uint32_t)P.CC, (int)(idx % (uint32_t)P.CC), P);
 }
 
+// the slow tail of the streams with a frame concealed by pitch repetition (mb_celt_plc.cuh): one warp per stream
+__global__ void __launch_bounds__(32) k_comb_plc(TailParams P) {
+  __shared__ PlcSmem sm;
+  if (blockIdx.x >= P.n_lanes) return;
+  Team tm = {(int)threadIdx.x, 32};
+  celt_comb_plc_lane(tm, &sm, blockIdx.x, P);
+}
+
 // phase 2c(ii): one lane per stream-channel. A warp owns 32 neighbouring stream-channels (16 stereo streams) and moves
 // their signals through a [32 rows x CH samples] shared-memory tile: rows arrive by cp.async as coalesced 16-byte
 // pieces (double-buffered: the next tile is in flight while the current one is filtered), the serial one-pole
@@ -190,7 +199,7 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
   const int c = live ? (int)(idx % (uint32_t)CC) : 0;
   const uint32_t sid = P.lane_stream ? P.lane_stream[lane] : lane;
   StreamState& st = P.st_all[sid];
-  const float* ser = P.series + ((size_t)lane * CC + c) * P.series_stride + HIST;
+  const float* ser = P.series + ((size_t)lane * CC + c) * P.series_stride + SER_PREFIX;
   Deemph d = {live ? st.preemph_mem[c] : 0.f, P.gain, P.apply_gain};
 
   auto issue = [&](int k0, float* tile) {   // rows' [k0, k0 + CH) -> tile, 16 bytes per lane per piece
@@ -395,7 +404,7 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
   for (uint32_t t = 0; t < n_ticks; t++) {
     const uint32_t f = t * n_lanes + lane;
     const uint32_t fl = meta[f].flags;
-    if (!(fl & 3u)) continue;
+    if (!(fl & (3u | MB_FL_PLC))) continue;
     const uint32_t p = pkt_map ? pkt_map[f] : f;
     int n = samples_out[p];
     if (n <= 0) continue;
@@ -416,6 +425,9 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
     // The packet's route (k_energy, the same on all its frames): float row -> clip -> int16, or int16 written by k_silk
     // already. The latter is final unless the previous packet left a non-linearity to carry over (opus.rs:44-60).
     const bool from_float = (fl & MB_FL_F32ROW) != 0;
+    // a LOST packet is not soft-clipped, and leaves the clipper's memory cleared (opus_decoder.rs:1186-1222: soft_clip = false)
+    const bool lost_pkt = flags && (flags[p] & 2u);
+    if (lost_pkt) mem = 0.f;
     if (!from_float && !__any_sync(0xffffffffu, mem != 0.f)) continue;
     const int total = n * CC;
     const size_t eo = pcm_elem_off(out_map, p, pcm_stride);
@@ -448,7 +460,7 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
       }
     }
     over |= mem != 0.f;
-    over = __any_sync(0xffffffffu, over);
+    over = __any_sync(0xffffffffu, over) && !lost_pkt;
     __syncwarp();
     if (over) {
       for (int c = 0; c < CC; c++) {
@@ -504,8 +516,8 @@ __global__ void k_reset(StreamState* st, float* hist, const uint32_t* __restrict
   if (i >= n) return;
   uint32_t sid = ids ? ids[i] : i;
   if (threadIdx.x == 0) stream_state_reset(st[sid]);
-  float* h = hist + (size_t)sid * CC * HIST;
-  for (int k = threadIdx.x; k < CC * HIST; k += blockDim.x) h[k] = 0.f;
+  float* h = hist + (size_t)sid * CC * HIST_G;
+  for (int k = threadIdx.x; k < CC * HIST_G; k += blockDim.x) h[k] = 0.f;
 }
 
 
@@ -634,6 +646,7 @@ struct bd_handle {
   std::vector<uint32_t> h_pkt_map, h_lane_stream, h_lane_of_stream, h_epoch, h_count, h_tick, v_range;
   std::vector<int32_t> v_samples;
   mbh::Split split;
+  std::vector<mbh::StreamTrack> track;   // per stream: frame size / mode of the last packet (cuts lost packets into concealment frames)
   uint32_t epoch = 0;
   int32_t* dbg_iy_host = nullptr;
   float* dbg_x_host = nullptr;
@@ -713,7 +726,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
   if (cudaFuncSetAttribute(k_deemph<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(DE_WARPS * 2 * 32 * (128 + 4) * sizeof(float))) != cudaSuccess)
     return fail(BD_ERR_CUDA);
   if (h->states.ensure((size_t)cfg->n_streams * sizeof(StreamState)) != cudaSuccess) return fail(BD_ERR_ALLOC);
-  if (h->hist.ensure((size_t)cfg->n_streams * h->CC * HIST * sizeof(float)) != cudaSuccess) return fail(BD_ERR_ALLOC);
+  if (h->hist.ensure((size_t)cfg->n_streams * h->CC * HIST_G * sizeof(float)) != cudaSuccess) return fail(BD_ERR_ALLOC);
   if (h->silk_states.ensure((size_t)cfg->n_streams * sizeof(SilkState)) != cudaSuccess) return fail(BD_ERR_ALLOC);
   if (h->silk_hist.ensure((size_t)cfg->n_streams * 320 * sizeof(uint32_t)) != cudaSuccess) return fail(BD_ERR_ALLOC);
   if (h->fold.ensure((size_t)cfg->n_streams * FOLD_WORDS * sizeof(float)) != cudaSuccess) return fail(BD_ERR_ALLOC);
@@ -757,6 +770,8 @@ int bd_reset_streams(bd_handle* h, const uint32_t* ids, uint32_t n) {
     CK(cudaMemcpyAsync(h->d_ids.p, ids, (size_t)n * 4, cudaMemcpyHostToDevice, h->own_stream));
     d_ids = h->d_ids.as<uint32_t>();
   } else n = h->cfg.n_streams;
+  if (h->track.size() == h->cfg.n_streams)
+    for (uint32_t i = 0; i < n; i++) h->track[ids ? ids[i] : i] = mbh::StreamTrack();
   if (n == 0) return BD_OK;
   k_reset<<<n, 128, 0, h->own_stream>>>(h->states.as<StreamState>(), h->hist.as<float>(), d_ids, n, h->CC);
   k_silk_reset<<<(n + 127) / 128, 128, 0, h->own_stream>>>(h->silk_states.as<SilkState>(), h->silk_hist.as<uint32_t>(), h->cfg.n_streams, d_ids, n);
@@ -888,7 +903,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
   // not the kernels, ends the call; measured on the headline workload: 71.4 -> 69.1 ms)
   if (h->pass_out.on && !d_out_map && n_ticks >= 16 && ticks_per_pass > (n_ticks + 3) / 4) ticks_per_pass = (n_ticks + 3) / 4;
   const uint32_t cells_max = ticks_per_pass * n_lanes;
-  const uint32_t series_stride = HIST + ticks_per_pass * MAX_N;
+  const uint32_t series_stride = SER_PREFIX + ticks_per_pass * MAX_N + SER_SLACK;
   CK(h->rec.ensure((size_t)((cells_max + 31) / 32) * REC_SLOTS * 32 * sizeof(uint32_t)));
   CK(h->en.ensure((size_t)cells_max * EN_STRIDE * sizeof(float)));
   CK(h->meta.ensure((size_t)2 * cells_max * sizeof(FrameMeta)));   // two halves: the clipper of pass k runs beside pass k+1
@@ -940,9 +955,10 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     h->prof_begin(BD_K_ENERGY, ss);
     k_energy<<<(n_lanes + ENERGY_WARPS - 1) / ENERGY_WARPS, 32 * ENERGY_WARPS, 0, ss>>>(n_lanes, nt, map, h->rec.as<uint32_t>(), h->states.as<StreamState>(), d_lane_stream,
                                                 h->en.as<float>(), meta_p, samples, range, h->cfg.quirks,
-                                                d_out_map ? flg : nullptr,
+                                                flg,
                                                 h->serial_bands || n_lanes >= 148u * 6u * (uint32_t)BANDS_WARPS,   // one warp per lane fills the band-pass slots
-                                                h->cfg.gain_q8 != 0 || !d_pcm_i16);   // direct int16 from k_silk: only the i16 API without a decode gain
+                                                h->cfg.gain_q8 != 0 || !d_pcm_i16,   // direct int16 from k_silk: only the i16 API without a decode gain
+                                                CC);
     h->prof_end(ss);
     CK(cudaEventRecord(h->ev_join, ss));   // the frame meta and band energies are ready: k_plan may go
     // SILK synthesis (SILK-only and hybrid cells), before the CELT tail so that k_deemph can add the CELT bands of hybrid
@@ -989,6 +1005,8 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     tp.apply_gain = h->cfg.gain_q8 != 0; tp.pcm_f32 = pcm; tp.pcm_stride = pcm_stride; tp.out_map = d_out_map; tp.xbuf = h->xbuf.as<float>();
     h->prof_begin(BD_K_COMB, s);
     k_comb<<<(n_lanes * CC + COMB_WARPS - 1) / COMB_WARPS, 32 * COMB_WARPS, 0, s>>>(tp);
+    k_comb_plc<<<n_lanes, 32, 0, s>>>(tp);   // lanes with a frame concealed by pitch repetition (the others leave after one look at their flags)
+    h->launches += 1;
     h->prof_end(s);
     // join 2: k_silk ran beside k_pvq .. k_comb. (Kernels with a large shared-memory footprint, k_bands / k_imdct, only join
     // it on an SM once that SM is idle enough to change its L1 / shared split; giving k_silk the large split up front makes
@@ -1246,11 +1264,23 @@ static int decode_host(bd_handle* h, const uint8_t* arena, const uint32_t* offse
                        const uint8_t* flags, float* pcm_f32, int16_t* pcm_i16, uint32_t pcm_stride, int32_t* samples_out,
                        uint32_t* final_range_out) {
   if (!h || !arena || !offsets || !stream_ids || !samples_out || !final_range_out || (!pcm_f32 && !pcm_i16)) return BD_ERR_BAD_ARG;
-  if (n_packets == 0 || !mbh::needs_split(arena, offsets, n_packets))
+  if (h->track.size() != h->cfg.n_streams) h->track.assign(h->cfg.n_streams, mbh::StreamTrack());
+  for (uint32_t p = 0; p < n_packets; p++) if (stream_ids[p] >= h->cfg.n_streams) return BD_ERR_BAD_ARG;
+  if (n_packets == 0 || !mbh::needs_split(arena, offsets, flags, n_packets)) {
+    // (no split: still remember what the decoders took in, for a later lost packet)
+    for (uint32_t p = 0; p < n_packets; p++) {
+      const uint32_t n = offsets[p + 1] - offsets[p];
+      if (n == 0 || (flags && (flags[p] & 3u))) continue;
+      const uint8_t toc = arena[offsets[p]];
+      if (mbh::toc_frame_samples(toc) > (int)(pcm_stride / (uint32_t)h->CC) || n - 1 > 1275) continue;
+      h->track[stream_ids[p]].frame_size = mbh::toc_frame_samples(toc);
+      h->track[stream_ids[p]].mode = (toc & 0x80) ? 1002 : ((toc & 0x60) == 0x60 ? 1001 : 1000);
+    }
     return decode_host_impl(h, arena, offsets, stream_ids, n_packets, flags, pcm_f32, pcm_i16, pcm_stride, samples_out, final_range_out,
                             nullptr, n_packets);
+  }
   mbh::Split& S = h->split;
-  mbh::split_batch(arena, offsets, stream_ids, flags, n_packets, (int)(pcm_stride / (uint32_t)h->CC), h->CC, &S);
+  mbh::split_batch(arena, offsets, stream_ids, flags, n_packets, (int)(pcm_stride / (uint32_t)h->CC), h->CC, &S, h->track.data());
   const uint32_t nv = (uint32_t)S.stream_ids.size();
   h->v_samples.resize(nv);
   h->v_range.resize(nv);

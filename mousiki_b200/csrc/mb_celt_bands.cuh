@@ -164,7 +164,7 @@ struct BandsParams {
 // the CELT-only frames it runs, stores the words of the buffer that survive the pass (a later hybrid frame may read them).
 MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsParams& P, bool serial = false) {
   const FrameMeta meta = P.meta[f];
-  if (!(meta.flags & 1u)) return;
+  if (!(meta.flags & 1u) || (meta.flags & MB_FL_PLC_PITCH)) return;   // (a frame concealed by pitch repetition has no spectrum)
   if (((meta.flags & MB_FL_FOLD) != 0) != serial) return;
   const uint32_t* r = P.rec + rec_index(f, 0);
   const uint32_t h0 = r[S_HDR0 * 32], status = r[S_STATUS * 32], plan = r[S_PLAN * 32];
@@ -393,9 +393,9 @@ MB_DEV void celt_bands_frame(Team tm, BandsSmem* sm, uint32_t f, const BandsPara
     MB_SYNC();
   }
   // write back on the parallel path: the words of this frame's footprint that no later frame of the pass overwrites
-  // (k_energy worked the interval out: flags bits 10-19 / 20-29, in units of 2 words)
+  // (k_energy worked the interval out: flags bits 10-18 / 19-27, in units of 4 words)
   if (!serial && P.fold_all) {
-    const int lo = 2 * (int)((meta.flags >> 10) & 1023u), hi = 2 * (int)((meta.flags >> 20) & 1023u);
+    const int lo = 4 * (int)((meta.flags >> 10) & 511u), hi = (meta.flags & MB_FL_PLC) ? 0 : 4 * (int)((meta.flags >> 19) & 511u);
     if (hi > lo) {
       float* dst = P.fold_all + (size_t)(P.lane_stream ? P.lane_stream[meta.lane] : meta.lane) * FOLD_WORDS;
       for (int w = lo + tm.tid; w < hi; w += tm.n) dst[w] = norm[w];

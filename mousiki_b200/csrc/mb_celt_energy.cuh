@@ -38,6 +38,12 @@ struct StreamState {
   int32_t prev_redundancy;   // the last packet ended in a SILK -> CELT redundancy frame (opus_decoder.rs:1117)
   int32_t fold_serial;       // the stream has decoded a SILK-side frame: its CELT-only frames keep the fold buffer exact too
   int32_t bandwidth;         // 0 before the first packet, else 1101 (NB) .. 1105 (FB) of the last packet (opus_decoder.rs:1322)
+  // packet-loss concealment (src/celt/types.rs:807-816, celt_decoder.rs:1429-1855)
+  int32_t skip_plc;          // no usable history for the pitch-based concealment (set by a reset and by the noise concealment)
+  int32_t prefilter_and_fold;// bookkeeping only: under quirk Q2 the next inverse MDCT zero-fills what prefilter_and_fold writes
+  int32_t last_pitch_index;  // pitch of the first concealed frame of a loss burst
+  int32_t celt_end;          // the CELT decoder's end band (set from the bandwidth of the last coded packet; a lost frame keeps it)
+  float plc_lpc[2][24];      // concealment synthesis filter per channel
 };
 
 MB_DEV void stream_state_reset(StreamState& s) {
@@ -49,6 +55,8 @@ MB_DEV void stream_state_reset(StreamState& s) {
   s.celt_error = 0;
   s.prev_redundancy = 0; s.fold_serial = 0;
   s.bandwidth = 0;
+  s.skip_plc = 1; s.prefilter_and_fold = 0; s.last_pitch_index = 0; s.celt_end = NB_EBANDS;
+  for (int c = 0; c < 2; c++) for (int i = 0; i < 24; i++) s.plc_lpc[c][i] = 0.f;
 }
 
 // per-frame side data produced here and consumed by phases 2b / 2c
@@ -62,11 +70,18 @@ struct FrameMeta {
                          // cross-fades it into the SILK row; bit5: SILK decoder reset before the packet; bit6 / bit7: the
                          // fade at the start (CELT -> SILK) / at the end (SILK -> CELT) of the row applies
 };
+// FrameMeta.flags, upper bits: 28 the frame's inverse MDCT also keeps its 120-sample overlap tail behind the frame in the
+// time series (the frame that follows conceals by pitch repetition and reads it); 30 concealed CELT frame (lost packet);
+// 31 concealed by pitch repetition (k_comb_plc synthesises it; seed_in carries loss_duration) — without bit 31 a concealed
+// frame is band-shaped noise and runs through k_plan / k_bands / k_imdct like a coded frame (seed_in = noise seed).
+enum : uint32_t { MB_FL_KEEP_TAIL = 1u << 28, MB_FL_PLC = 1u << 30, MB_FL_PLC_PITCH = 1u << 31 };
+// S_STATUS bit 29: lost frame (no payload); S_RANGE then holds the number of samples to conceal
+#define MB_ST_LOST(s) (((s) >> 29) & 1u)
 enum { EN_STRIDE = 4 * 2 * NB_EBANDS, EN_GAINS = 3 * 2 * NB_EBANDS,   // per-frame energy scratch: E, prev1 (old_log_e), prev2 (old_log_e2), band gains
       
        MB_FL_FOLD = 8u | 16u | 512u,
        MB_FL_F32ROW = 256u };  // the packet's PCM goes through the float row (k_deemph / k_fade / k_clip_i16), set on all its frames   // FrameMeta.flags: the frame's band pass runs per stream, in tick order, on the persistent fold buffer
-// flags bit 9 (512): CELT-only frame behind a SILK-side frame of the same pass; bits 10-19 / 20-29: fold-buffer words
+// flags bit 9 (512): CELT-only frame behind a SILK-side frame of the same pass; bits 10-18 / 19-27 (units of 4 words): fold-buffer words
 // [lo, hi) a CELT-only frame of the parallel band pass writes back (the part no later frame of the pass overwrites)  // per-frame energy scratch: E, prev1 (old_log_e), prev2 (old_log_e2)
 
 struct Team { int tid, n; };
@@ -81,9 +96,9 @@ struct EnergySmem { float E[2 * NB_EBANDS], le[2 * NB_EBANDS], le2[2 * NB_EBANDS
 // term prev[c] of band i is the left-to-right sum of the lower bands' symbols, which every lane rebuilds for its own
 // band in the reference's order, so the result is bit-identical to the serial loop.
 MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, const uint32_t* pkt_map,
-                               const uint32_t* rec, StreamState* st_all, const uint32_t* lane_stream, float* en, FrameMeta* meta,
+                               uint32_t* rec, StreamState* st_all, const uint32_t* lane_stream, float* en, FrameMeta* meta,
                                int32_t* samples_out, uint32_t* final_range_out, uint32_t quirks, const uint8_t* flags = nullptr,
-                               int serial_all = 0, int force_float_row = 0) {
+                               int serial_all = 0, int force_float_row = 0, int CC = 2) {
   StreamState& st = st_all[lane_stream ? lane_stream[lane] : lane];
   const bool lead = tm.tid == 0;
   for (int i = tm.tid; i < 2 * NB_EBANDS; i += tm.n) {
@@ -92,6 +107,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
   uint32_t st_rng = st.rng, st_range_final = st.range_final;
   int st_loss_duration = st.loss_duration, st_prev_mode = st.prev_mode, st_last_duration = st.last_packet_duration;
   int st_celt_error = st.celt_error, st_prev_redundancy = st.prev_redundancy, st_fold_serial = st.fold_serial, st_bandwidth = st.bandwidth;
+  int st_skip_plc = st.skip_plc, st_prefold = st.prefilter_and_fold, st_celt_end = st.celt_end;
   MB_SYNC();
   uint32_t sample_off = 0;
   // Band pass of CELT-only frames. The reference's fold buffer outlives the frame (mb_celt_bands.cuh), so only a pass that
@@ -108,7 +124,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
   uint32_t pkt_route = 0;
   for (uint32_t t = 0; t < n_ticks; t++) {
     const uint32_t f = t * n_lanes + lane;
-    const uint32_t* r = rec + rec_index(f, 0);
+    uint32_t* r = rec + rec_index(f, 0);
     uint32_t status = r[S_STATUS * 32];
     FrameMeta m;
     m.seed_in = st_rng; m.sample_off = sample_off; m.lane = lane; m.flags = 0;
@@ -128,6 +144,67 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
         celt_part = MB_ST_DECODED(s2) && (!((s2 >> 16) & 1u) || ((s2 >> 17) & 1u) || ((s2 >> 19) & 3u));
       }
       pkt_route = celt_part ? MB_FL_F32ROW : 0u;
+    }
+    if (MB_ST_LOST(status) && !pkt_failed) {
+      // ---- lost packet / frame of at most one byte: decode_frame(None) (src/opus_decoder.rs:491-575). The concealment of a
+      // stream whose last packet was CELT-only (or ended in a SILK -> CELT redundancy frame) is celt_decode_lost
+      // (src/celt/celt_decoder.rs:1429-1855); SILK / hybrid concealment is not built yet (reported as unimplemented).
+      const int audiosize = (int)r[S_RANGE * 32];
+      const int md = st_prev_redundancy ? 1002 : st_prev_mode;
+      if (md == 0) {   // nothing decoded yet: silence (opus_decoder.rs:527-540)
+        m.flags = MB_FL_PLC | MB_FL_F32ROW;   // concealed, but no CELT frame: k_fade zero-fills seed_in samples of the row
+        m.seed_in = (uint32_t)audiosize;
+        st_prev_mode = 0; st_prev_redundancy = 0; st_range_final = 0; st_last_duration = audiosize;
+        if (lead) { meta[f] = m; samples_out[p] = audiosize; final_range_out[p] = 0; }
+        continue;
+      }
+      int lmq = -1;
+      for (int q = 0; q <= MAX_LM; q++) if ((SHORT_MDCT << q) == audiosize) lmq = q;
+      if (md != 1002 || lmq < 0) {
+        if (lead) { meta[f] = m; samples_out[p] = MB_UNIMPLEMENTED; final_range_out[p] = st_range_final; }
+        pkt_failed = true;
+        continue;
+      }
+      const int start = 0, end = st_celt_end, Mq = 1 << lmq;
+      const int noise_based = st_loss_duration >= 40 || start != 0 || st_skip_plc;
+      // a synthetic frame header for the kernels downstream: LM, the DECODER's channel count, band range; no leaves, no nodes
+      if (lead) {
+        r[S_HDR0 * 32] = (uint32_t)lmq | ((uint32_t)(CC - 1) << 2) | (2u << 6) | ((uint32_t)start << 26);
+        r[S_HDR1 * 32] = 0u;
+        r[S_STATUS * 32] = status | ((uint32_t)end << 8);
+        r[S_PLAN * 32] = 0u;
+      }
+      float* ef = en + (size_t)f * EN_STRIDE;
+      if (noise_based) {
+        const float decay = st_loss_duration == 0 ? 1.5f : 0.5f;
+        MB_SYNC();
+        for (int idx = tm.tid; idx < 2 * NB_EBANDS; idx += tm.n) {
+          const int c = idx >= NB_EBANDS, i = idx - c * NB_EBANDS;
+          float e = sm->E[idx];
+          if (c < CC && i >= start && i < end) { e = fmax32(sm->bg[idx], e - decay); sm->E[idx] = e; }
+          ef[idx] = e;
+          ef[EN_GAINS + idx] = celt_exp2(fmin32(e + kEMeans[i], 32.0f));
+        }
+        MB_SYNC();
+        // the noise generator runs channel by channel over bands start .. eff_end (celt_decoder.rs:1511-1531)
+        int total = 0;
+        for (int i = start; i < imin(end, NB_EBANDS); i++) total += (eband(i + 1) - eband(i)) << lmq;
+        m.seed_in = st_rng;
+        uint32_t sd = st_rng;
+        for (int k = 0; k < CC * total; k++) sd = sd * 1664525u + 1013904223u;
+        st_rng = sd;
+        st_prefold = 0; st_skip_plc = 1;
+        m.flags = 1u | MB_FL_PLC | MB_FL_F32ROW | (silk_side_seen ? 512u : 0u);
+      } else {
+        m.seed_in = (uint32_t)st_loss_duration;
+        st_prefold = 1;
+        m.flags = 1u | MB_FL_PLC | MB_FL_PLC_PITCH | MB_FL_F32ROW;
+      }
+      st_loss_duration = imin(10000, st_loss_duration + Mq);
+      st_prev_mode = md; st_prev_redundancy = 0; st_range_final = 0; st_last_duration = audiosize;
+      sample_off += (uint32_t)audiosize;
+      if (lead) { meta[f] = m; samples_out[p] = audiosize; final_range_out[p] = 0; }
+      continue;
     }
     if (pkt_failed || !MB_ST_DECODED(status)) {  // rejected before the decoder ran (unsupported mode, PLC, bad TOC)
       if (lead) {
@@ -196,13 +273,39 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
       MB_SYNC();
       for (int i = tm.tid; i < 2 * NB_EBANDS; i += tm.n) { sm->E[i] = 0.f; sm->le[i] = -28.f; sm->le2[i] = -28.f; sm->bg[i] = 0.f; }
       st_rng = 0; st_loss_duration = 0;
+      st_skip_plc = 1; st_prefold = 0;   // (last_pitch_index and the concealment filter are only read after a frame has set them)
       m.seed_in = 0;
     }
     const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), start = (int)MB_H0_START(h0), end = (int)MB_ST_END(status);
     const int intra = (int)MB_H0_INTRA(h0), silence = (int)MB_H0_SILENCE(h0), transient = (int)MB_H0_TRANSIENT(h0);
     const int M = 1 << lm;
     float* E = sm->E;
+    st_celt_end = end;
+    if (st_loss_duration == 0) st_skip_plc = 0;      // prepare_frame (celt_decoder.rs:2875-2877)
     MB_SYNC();
+    if (C == 1) {   // celt_decoder.rs:2890-2896
+      for (int i = tm.tid; i < NB_EBANDS; i += tm.n) E[i] = fmax32(E[i], E[NB_EBANDS + i]);
+      MB_SYNC();
+    }
+    if (!intra && st_loss_duration != 0) {
+      // the first coded frame after a loss starts from safer energies (celt_decoder.rs:2943-2969), both channels
+      const int missing = imin(10, st_loss_duration >> lm);
+      const float safety = lm == 0 ? 1.5f : (lm == 1 ? 0.5f : 0.0f);
+      for (int idx = tm.tid; idx < 2 * NB_EBANDS; idx += tm.n) {
+        const int i = idx >= NB_EBANDS ? idx - NB_EBANDS : idx;
+        if (i < start || i >= end) continue;
+        float e0 = E[idx];
+        const float e1 = sm->le[idx], e2 = sm->le2[idx];
+        if (e0 < fmax32(e1, e2)) {
+          float slope = fmax32(e1 - e0, 0.5f * (e2 - e0));
+          slope = fmin32(slope, 2.0f);
+          e0 -= fmax32((float)(missing + 1) * slope, 0.0f);
+          e0 = fmax32(e0, -20.0f);
+        } else e0 = fmin32(e0, fmin32(e1, e2));
+        E[idx] = e0 - safety;
+      }
+      MB_SYNC();
+    }
     // this frame's symbols: every lane fetches the words of its own (channel, band) slots
     uint32_t wmine[2] = {0, 0};   // team of 32: slots tid and tid + 32; team of one: read again below
     for (int idx = tm.tid, k = 0; idx < 2 * NB_EBANDS; idx += tm.n, k++) {
@@ -211,7 +314,6 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
       if (c < C && i >= start && i < end) w = r[(S_ENERGY + idx) * 32];
       if (k < 2) wmine[k] = w;
       sm->q[idx] = (float)(int)(int16_t)(w & 0xffffu);
-      if (C == 1 && idx < NB_EBANDS) E[idx] = fmax32(E[idx], E[NB_EBANDS + idx]);
     }
     MB_SYNC();
     // coarse + fine + finalise (three separate float additions per band, in the reference's order)
@@ -271,7 +373,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
     MB_SYNC();
     for (int idx = tm.tid, k = 0; idx < 2 * NB_EBANDS; idx += tm.n, k++) { E[idx] = ne[k]; sm->le[idx] = nl1[k]; sm->le2[idx] = nl2[k]; }
     st_rng = r[S_RANGE * 32];
-    st_loss_duration = 0;
+    st_loss_duration = 0; st_prefold = 0;
     if (status & (1u << 13)) st_celt_error = 1;
     const int N = (fadeout || red) ? silk_n : M * SHORT_MDCT;   // samples the packet delivers
     if (red) {
@@ -302,18 +404,29 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
     st.rng = st_rng; st.range_final = st_range_final; st.loss_duration = st_loss_duration; st.prev_mode = st_prev_mode;
     st.last_packet_duration = st_last_duration; st.celt_error = st_celt_error; st.prev_redundancy = st_prev_redundancy;
     st.fold_serial = st_fold_serial; st.bandwidth = st_bandwidth;
+    st.skip_plc = st_skip_plc; st.prefilter_and_fold = st_prefold; st.celt_end = st_celt_end;
     // Fold-buffer write-back of the parallel band pass (mb_celt_bands.cuh): walking the lane's CELT-only frames backwards,
     // each one keeps the words of its footprint that no later frame of the pass covers. A frame's footprint is the first
     // C * norm_len words of the reference's storage (bands.rs:2614-2625), capped at what hybrid frames can read.
+    // Overlap tails (MB_FL_KEEP_TAIL): the frame in front of a frame concealed by pitch repetition, and the lane's last frame
+    // of the pass (the next call may start with a loss), keep the 120 samples their inverse MDCT leaves behind the frame.
+    bool need_tail = true;
+    for (uint32_t t = n_ticks; t-- > 0;) {
+      const uint32_t f = t * n_lanes + lane;
+      const uint32_t fl = meta[f].flags;
+      if (!(fl & 1u)) continue;
+      if (fl & MB_FL_PLC_PITCH) { need_tail = true; continue; }
+      if (need_tail) { meta[f].flags = fl | MB_FL_KEEP_TAIL; need_tail = false; }
+    }
     int covered = 0;
     for (uint32_t t = n_ticks; t-- > 0 && covered < (int)FOLD_WORDS;) {
       const uint32_t f = t * n_lanes + lane;
       const uint32_t fl = meta[f].flags;
-      if (!(fl & 1u) || (fl & MB_FL_FOLD)) continue;
+      if (!(fl & 1u) || (fl & MB_FL_FOLD) || (fl & MB_FL_PLC)) continue;   // (a concealed frame leaves the fold buffer alone)
       const uint32_t h0 = rec[rec_index(f, S_HDR0)];
       const int top = imin((int)MB_H0_C(h0) * ((int)eband(NB_EBANDS - 1) << (int)MB_H0_LM(h0)), (int)FOLD_WORDS);   // even
       if (top > covered) {
-        meta[f].flags = fl | ((uint32_t)(covered >> 1) << 10) | ((uint32_t)(top >> 1) << 20);
+        meta[f].flags = fl | ((uint32_t)(covered >> 2) << 10) | ((uint32_t)(top >> 2) << 19);
         covered = top;
       }
     }

@@ -112,6 +112,8 @@ MB_DEV void team_fft(Team tm, cpx* f, int shift, int nt) {
 struct ImdctSmem {
   float io[MAX_N];     // freq in, time-domain samples out
   float F[MAX_N];      // FFT work: 480 complex points
+  float tail[64];      // the 60 samples the last block writes beyond the frame (the reference's overlap region, clt_mdct_backward
+                       // writes n2 + overlap / 2 samples): only a frame concealed by pitch repetition ever reads them
 };
 
 struct ImdctParams {
@@ -169,6 +171,8 @@ MB_DEV void celt_imdct_core(Team tm, ImdctSmem* sm, int lm, int transient) {
         ob[60 + k] = 0.f * w1 + val * w2;     // out[119-i] = x2*w1 + x1*w2
       } else if (60 + k < lim) {
         ob[60 + k] = val;
+      } else if (b == nbk - 1) {
+        sm->tail[b * n2 + 60 + k - N] = val;
       }
     }
   }
@@ -179,7 +183,7 @@ MB_DEV void celt_imdct_core(Team tm, ImdctSmem* sm, int lm, int transient) {
 // duplicated) spectrum.
 MB_DEV void celt_imdct_unit(Team tm, ImdctSmem* sm, uint32_t f, int u, const ImdctParams& P) {
   const FrameMeta meta = P.meta[f];
-  if (!(meta.flags & 1u)) return;
+  if (!(meta.flags & 1u) || (meta.flags & MB_FL_PLC_PITCH)) return;
   const uint32_t* r = P.rec + rec_index(f, 0);
   const uint32_t h0 = r[S_HDR0 * 32], status = r[S_STATUS * 32];
   const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), start = (int)MB_H0_START(h0), end = (int)MB_ST_END(status);
@@ -206,11 +210,16 @@ MB_DEV void celt_imdct_unit(Team tm, ImdctSmem* sm, uint32_t f, int u, const Imd
   const float SIG_SAT = 536870911.0f;
   for (int cc = 0; cc < CC; cc++) {
     if (nch == 2 && cc != u) continue;
-    float* out = P.series + ((size_t)meta.lane * CC + cc) * P.series_stride + HIST + meta.sample_off;
+    float* out = P.series + ((size_t)meta.lane * CC + cc) * P.series_stride + SER_PREFIX + meta.sample_off;
     for (int i = tm.tid; i < N; i += tm.n) {
       float o = O[i];
       out[i] = o < -SIG_SAT ? -SIG_SAT : (o > SIG_SAT ? SIG_SAT : o);
     }
+    // The frame after this one is concealed by pitch repetition: it reads the decoder's overlap region too, which sits
+    // behind the frame in the reference's linear history (decode_mem[2048 .. 2168)) and here at the head of the lost
+    // frame's own stretch of the time series: 60 unwindowed samples, then zeros (the reference's zero fill, Q2).
+    if (meta.flags & MB_FL_KEEP_TAIL)
+      for (int i = tm.tid; i < OVERLAP; i += tm.n) out[N + i] = i < OVERLAP / 2 ? sm->tail[i] : 0.f;
   }
 }
 

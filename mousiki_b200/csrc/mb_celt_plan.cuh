@@ -255,6 +255,30 @@ MB_DEV void celt_plan_frame(uint32_t f, const PlanParams& Q) {
   Plan P;
   P.nodes = r + S_NODES * 32; P.leaves = r + S_LEAVES * 32; P.ops = r + S_OPS * 32;
   P.node_pos = 0; P.leaf_pos = 0; P.n_ops = 0; P.n_fold = 0; P.overflow = 0; P.seed = meta.seed_in; P.tf_change = 0; P.lb_inplace = 0;
+  if (meta.flags & MB_FL_PLC) {
+    // Concealed frame. Pitch repetition is synthesised in the time domain (k_comb_plc): nothing to plan. The noise
+    // concealment (celt_decoder.rs:1507-1533) fills every band of every channel with unit-norm noise; the generator runs
+    // channel by channel, so the second channel's seeds continue where the first channel's bands end.
+    if (meta.flags & MB_FL_PLC_PITCH) return;
+    const int eff_end = imin(end, NB_EBANDS);
+    uint32_t seed_c[2];
+    seed_c[0] = meta.seed_in;
+    uint32_t sd = meta.seed_in;
+    for (int i = start; i < eff_end; i++) sd = lcg_jump(sd, M * (eband(i + 1) - eband(i)));
+    seed_c[1] = sd;
+    for (int i = start; i < eff_end; i++) {
+      const int n = M * (eband(i + 1) - eband(i));
+      for (int c = 0; c < C; c++) {
+        P.put(MB_OP(OP_NOISE, c * WIN_Y, n, 0));
+        P.put(f2bits(1.0f));
+        P.put(seed_c[c]);
+        seed_c[c] = lcg_jump(seed_c[c], n);
+      }
+      P.put(MB_OP(OP_END_BAND, 0, 0, 0));
+    }
+    r[S_PLAN * 32] = (uint32_t)P.n_ops;
+    return;
+  }
   uint8_t collapse[2 * NB_EBANDS];
   uint16_t anti_pos[NB_EBANDS];
   for (int i = 0; i < 2 * NB_EBANDS; i++) collapse[i] = 0;

@@ -86,15 +86,24 @@ MB_DEV void team_comb_filter(Team tm, float* x, int n, int T0, int T1, float g0,
 
 MB_DEV void celt_comb_channel(Team tm, CombSmem* sm, uint32_t lane, int c, const TailParams& P) {
   const int CC = P.CC;
+  {  // a lane with a frame concealed by pitch repetition belongs to k_comb_plc (mb_celt_plc.cuh)
+    bool any = false;
+    for (uint32_t t = tm.tid; t < P.n_ticks; t += tm.n) any |= (P.meta[(size_t)t * P.n_lanes + lane].flags & MB_FL_PLC_PITCH) != 0;
+#if MB_ON_DEVICE
+    any = __any_sync(0xffffffffu, any);
+#endif
+    if (any) return;
+  }
   const uint32_t sid = P.lane_stream ? P.lane_stream[lane] : lane;
   StreamState& st = P.st_all[sid];
-  float* ser = P.series + ((size_t)lane * CC + c) * P.series_stride + HIST;
-  float* hist = P.hist + ((size_t)sid * CC + c) * HIST;
+  float* ser = P.series + ((size_t)lane * CC + c) * P.series_stride + SER_PREFIX;
+  float* hist = P.hist + ((size_t)sid * CC + c) * HIST_G;
   float* buf = sm->buf;
-  for (int i = tm.tid; i < HIST; i += tm.n) buf[i] = hist[i];
+  for (int i = tm.tid; i < HIST; i += tm.n) buf[i] = hist[HIST_G - OVERLAP - HIST + i];
   StreamState::Pf& pf = st.pf[c];
   int pf_period = pf.period, pf_period_old = pf.period_old, pf_tapset = pf.tapset, pf_tapset_old = pf.tapset_old;
   float pf_gain = pf.gain, pf_gain_old = pf.gain_old;
+  int total = 0, reset_at = -1;   // samples of CELT signal this pass; where the last decoder reset fell
   MB_SYNC();
   for (uint32_t t = 0; t < P.n_ticks; t++) {
     const uint32_t f = t * P.n_lanes + lane;
@@ -106,27 +115,31 @@ MB_DEV void celt_comb_channel(Team tm, CombSmem* sm, uint32_t lane, int c, const
     if (m.flags & 4u) {  // CELT decoder reset before this frame (SILK-only -> hybrid)
       for (int i = tm.tid; i < HIST; i += tm.n) buf[i] = 0.f;
       pf_period = pf_period_old = 0; pf_tapset = pf_tapset_old = 0; pf_gain = pf_gain_old = 0.f;
+      reset_at = (int)m.sample_off;
       MB_SYNC();
     }
-    const int new_pitch = (int)MB_H1_PITCH(h1), new_tapset = (int)MB_H0_TAPSET(h0);
-    const float new_gain = 0.09375f * (float)MB_H0_QG1(h0);
     float* xg = ser + m.sample_off;
     float* x = buf + HIST;
     for (int i = tm.tid; i < N; i += tm.n) x[i] = xg[i];
     MB_SYNC();
-    pf_period = imax(pf_period, COMB_MINPERIOD);
-    pf_period_old = imax(pf_period_old, COMB_MINPERIOD);
-    const int first = imin(SHORT_MDCT, N);
-    const int second = (lm != 0 && first < N) ? N - first : 0;
-    const int touched = (pf_gain_old != 0.f || pf_gain != 0.f) || (second && (pf_gain != 0.f || new_gain != 0.f));
-    team_comb_filter(tm, x, first, pf_period_old, pf_period, pf_gain_old, pf_gain, imax(pf_tapset_old, 0), imax(pf_tapset, 0));
-    if (second)
-      team_comb_filter(tm, x + first, second, pf_period, new_pitch, pf_gain, new_gain, imax(pf_tapset, 0), imax(new_tapset, 0));
-    pf_period_old = pf_period; pf_gain_old = pf_gain; pf_tapset_old = pf_tapset;
-    pf_period = new_pitch; pf_gain = new_gain; pf_tapset = new_tapset;
-    if (lm != 0) { pf_period_old = pf_period; pf_gain_old = pf_gain; pf_tapset_old = pf_tapset; }
-    if (touched)
-      for (int i = tm.tid; i < N; i += tm.n) xg[i] = x[i];
+    if (!(m.flags & MB_FL_PLC)) {   // (a concealed frame is neither post-filtered nor does it move the filter's parameters)
+      const int new_pitch = (int)MB_H1_PITCH(h1), new_tapset = (int)MB_H0_TAPSET(h0);
+      const float new_gain = 0.09375f * (float)MB_H0_QG1(h0);
+      pf_period = imax(pf_period, COMB_MINPERIOD);
+      pf_period_old = imax(pf_period_old, COMB_MINPERIOD);
+      const int first = imin(SHORT_MDCT, N);
+      const int second = (lm != 0 && first < N) ? N - first : 0;
+      const int touched = (pf_gain_old != 0.f || pf_gain != 0.f) || (second && (pf_gain != 0.f || new_gain != 0.f));
+      team_comb_filter(tm, x, first, pf_period_old, pf_period, pf_gain_old, pf_gain, imax(pf_tapset_old, 0), imax(pf_tapset, 0));
+      if (second)
+        team_comb_filter(tm, x + first, second, pf_period, new_pitch, pf_gain, new_gain, imax(pf_tapset, 0), imax(new_tapset, 0));
+      pf_period_old = pf_period; pf_gain_old = pf_gain; pf_tapset_old = pf_tapset;
+      pf_period = new_pitch; pf_gain = new_gain; pf_tapset = new_tapset;
+      if (lm != 0) { pf_period_old = pf_period; pf_gain_old = pf_gain; pf_tapset_old = pf_tapset; }
+      if (touched)
+        for (int i = tm.tid; i < N; i += tm.n) xg[i] = x[i];
+    }
+    total = (int)m.sample_off + N;
     // slide the window: the last HIST samples become the history of the next frame
     for (int i0 = 0; i0 < HIST; i0 += tm.n) {
       const int i = i0 + tm.tid;
@@ -137,7 +150,22 @@ MB_DEV void celt_comb_channel(Team tm, CombSmem* sm, uint32_t lane, int c, const
     }
     MB_SYNC();
   }
-  for (int i = tm.tid; i < HIST; i += tm.n) hist[i] = buf[i];
+  // Persistent history, laid out like the reference's decode_mem: the 2048 samples in front of `total` (this pass's series,
+  // older ones from the previous history, zeros in front of a decoder reset), then the overlap region the last frame's
+  // inverse MDCT left behind it (MB_FL_KEEP_TAIL). In place: ascending chunks, read before write.
+  if (total > 0) {
+    for (int i0 = 0; i0 < HIST_G; i0 += tm.n) {
+      const int i = i0 + tm.tid;
+      float v = 0.f;
+      if (i < HIST_G) {
+        const int s = total - (HIST_G - OVERLAP) + i;
+        if (s >= 0) v = s < reset_at ? 0.f : ser[s];
+        else v = reset_at >= 0 ? 0.f : hist[i + total];
+      }
+      MB_SYNC();
+      if (i < HIST_G) hist[i] = v;
+    }
+  }
   if (tm.tid == 0) {
     pf.period = pf_period; pf.period_old = pf_period_old; pf.tapset = pf_tapset; pf.tapset_old = pf_tapset_old;
     pf.gain = pf_gain; pf.gain_old = pf_gain_old;
@@ -166,7 +194,7 @@ MB_DEV void celt_deemph_lane(uint32_t lane, int c, const TailParams& P) {
   const int CC = P.CC;
   const uint32_t sid = P.lane_stream ? P.lane_stream[lane] : lane;
   StreamState& st = P.st_all[sid];
-  const float* ser = P.series + ((size_t)lane * CC + c) * P.series_stride + HIST;
+  const float* ser = P.series + ((size_t)lane * CC + c) * P.series_stride + SER_PREFIX;
   Deemph d = {st.preemph_mem[c], P.gain, P.apply_gain};
   for (uint32_t t = 0; t < P.n_ticks; t++) {
     const uint32_t f = t * P.n_lanes + lane;
@@ -194,6 +222,12 @@ MB_DEV void celt_deemph_lane(uint32_t lane, int c, const TailParams& P) {
 // gain is applied to the finished row. w = window[i]^2 over 120 samples (48 kHz).
 MB_DEV void celt_fade_cell(uint32_t f, int c, const TailParams& P) {
   const FrameMeta m = P.meta[f];
+  if ((m.flags & MB_FL_PLC) && !(m.flags & 1u) && P.pcm_f32) {   // a lost packet before anything was decoded: silence (opus_decoder.rs:527-540)
+    const uint32_t p0 = P.pkt_map ? P.pkt_map[f] : f;
+    float* row0 = P.pcm_f32 + pcm_elem_off(P.out_map, p0, P.pcm_stride) + c;
+    for (int i = 0; i < (int)m.seed_in; i++) row0[(size_t)i * P.CC] = 0.f;
+    return;
+  }
   if (!(m.flags & 16u) || !P.pcm_f32) return;
   const int CC = P.CC;
   const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;

@@ -39,7 +39,11 @@ namespace mb {
 enum {
   NB_EBANDS = 21, OVERLAP = 120, SHORT_MDCT = 120, MAX_LM = 3, MAX_N = 960,
   MAX_PERIOD = 1024, COMB_MINPERIOD = 15, BITRES = 3,
-  HIST = 1024,  // post-filtered history kept per channel (comb filter reaches back T+2 <= 1024)
+  HIST = 1024,  // post-filtered history the comb filter needs (it reaches back T+2 <= 1024): the shared-memory window of k_comb
+  HIST_G = 2048 + 120,  // persistent history per stream-channel in HBM, laid out like the reference's decode_mem: the last 2048
+                        // output samples, then the 120-sample overlap region (what the pitch concealment reads)
+  SER_PREFIX = 2176,    // room in front of the first frame of a lane's time series (k_comb_plc lays the history there)
+  SER_SLACK = 128,      // room behind the last frame (the overlap region of the lane's last frame)
 };
 
 // ---- quirk switches: bit set = mousiki's float decoder behaviour, clear = libopus

@@ -31,15 +31,28 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
   if (len == 0 && !flags) { rec_base[S_STATUS * 32] = 1u << 15; return; }
   int code = MB_OK;
   const uint8_t* data = arena + off;
-  if (len == 0 || (flags && (flags[pkt] & 3u))) code = MB_UNIMPLEMENTED;  // concealment / FEC (row F2)
+  if (flags && (flags[pkt] & 2u)) {
+    // lost packet (or one concealment frame of it, cut by the host): no payload. The two bytes the host put in its place
+    // say how many samples to conceal (mb_host_packets.h); the stream pass decides how (k_energy).
+    int n = len >= 2 ? (int)data[0] | ((int)data[1] << 8) : cap_per_ch;
+    if (n > cap_per_ch) n = cap_per_ch;
+    rec_base[S_RANGE * 32] = (uint32_t)n;
+    rec_base[S_STATUS * 32] = 1u << 29;
+    return;
+  }
+  if (len == 0 || (flags && (flags[pkt] & 1u))) code = MB_UNIMPLEMENTED;  // in-band FEC (row F2)
   uint32_t toc = 0;
   if (code == MB_OK) {
     toc = data[0];
     if (toc & 3u) code = MB_UNIMPLEMENTED;              // multi-frame packets (row F1)
     else if (len - 1 > 1275) code = MB_INVALID_PACKET;  // src/packet.rs:465: a frame is at most 1275 bytes
     else if (!(toc & 0x80u)) {
-      if (len - 1 <= 1) code = MB_UNIMPLEMENTED;             // concealment (src/opus_decoder.rs:491)
-      else if ((toc & 0x60u) == 0x60u) {
+      if (len - 1 <= 1) {                                    // a frame of at most one byte is a concealed frame (src/opus_decoder.rs:491-496)
+        const int sc = (int)((toc >> 3) & 3u);
+        const int n = (toc & 0x60u) == 0x60u ? ((toc & 0x08u) ? 960 : 480) : (sc == 3 ? 2880 : 480 << sc);
+        if (n > cap_per_ch) code = MB_BUFFER_TOO_SMALL;
+        else { rec_base[S_RANGE * 32] = (uint32_t)n; rec_base[S_STATUS * 32] = 1u << 29; return; }
+      } else if ((toc & 0x60u) == 0x60u) {
         // hybrid: SILK WB payload, optional redundancy header, then CELT bands 17.. from the same range decoder
         // (src/opus_decoder.rs:596-985)
         const int lm = (toc & 0x08u) ? 3 : 2;                // 20 / 10 ms
@@ -86,7 +99,7 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
     const int lm = (int)((toc >> 3) & 3u);
     const int N = SHORT_MDCT << lm;
     if (N > cap_per_ch) code = MB_BUFFER_TOO_SMALL;     // src/opus_decoder.rs:1318-1320
-    else if (len - 1 <= 1) code = MB_UNIMPLEMENTED;     // a <=1-byte frame is concealment (src/opus_decoder.rs:491)
+    else if (len - 1 <= 1) { rec_base[S_RANGE * 32] = (uint32_t)N; rec_base[S_STATUS * 32] = 1u << 29; return; }   // concealed frame (:491-496)
     else {
       const int bw = (int)((toc >> 5) & 3u);
       const int end = bw == 0 ? 13 : bw == 1 ? 17 : bw == 2 ? 19 : 21;
@@ -106,7 +119,7 @@ MB_DEV void parse_cell(const uint8_t* arena, const uint32_t* offsets, uint32_t p
                        int disable_inv, int cap_per_ch, const uint8_t* flags, uint32_t prev_pkt = 0xffffffffu,
                        const int32_t* prev_mode = nullptr) {
   parse_cell_body(arena, offsets, pkt, rec_base, CC, quirks, disable_inv, cap_per_ch, flags, prev_pkt, prev_mode);
-  if (pkt != 0xffffffffu && !(flags && (flags[pkt] >> 4)) && offsets[pkt + 1] > offsets[pkt])
+  if (pkt != 0xffffffffu && !(flags && ((flags[pkt] >> 4) || (flags[pkt] & 2u))) && offsets[pkt + 1] > offsets[pkt])
     rec_base[S_STATUS * 32] |= (uint32_t)arena[offsets[pkt]] << 21;
 }
 

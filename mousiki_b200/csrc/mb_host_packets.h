@@ -123,15 +123,23 @@ struct Split {
   void clear() { arena.clear(); offsets.clear(); stream_ids.clear(); flags.clear(); out_map.clear(); first.clear(); }
 };
 
-inline bool needs_split(const uint8_t* arena, const uint32_t* offsets, uint32_t n_packets) {
-  for (uint32_t p = 0; p < n_packets; p++)
+// What the host has to remember of a stream to cut a LOST packet into concealment frames the way decode_native /
+// decode_frame(None) do (src/opus_decoder.rs:491-575, 1186-1222): the frame size and the mode of the last packet the decoder
+// took in. Both are functions of the packets' TOC bytes alone (opus_decoder.rs:1322-1328).
+struct StreamTrack { int32_t frame_size = 0, mode = 0; };   // mode: 0 nothing yet, 1000 SILK, 1001 hybrid, 1002 CELT
+
+inline bool needs_split(const uint8_t* arena, const uint32_t* offsets, const uint8_t* flags, uint32_t n_packets) {
+  for (uint32_t p = 0; p < n_packets; p++) {
     if (offsets[p + 1] > offsets[p] && (arena[offsets[p]] & 3u)) return true;
+    if (flags && (flags[p] & 2u)) return true;
+  }
   return false;
 }
 
 // cap_per_ch: PCM capacity of a packet row per channel (the reference's `frame_size`); CC: decoder channels.
+// track: one StreamTrack per stream id (null: lost packets conceal one frame of the row's capacity).
 inline void split_batch(const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, const uint8_t* flags,
-                        uint32_t n_packets, int cap_per_ch, int CC, Split* S) {
+                        uint32_t n_packets, int cap_per_ch, int CC, Split* S, StreamTrack* track = nullptr) {
   S->clear();
   S->offsets.push_back(0);
   S->arena.reserve(offsets[n_packets] + n_packets);
@@ -152,13 +160,47 @@ inline void split_batch(const uint8_t* arena, const uint32_t* offsets, const uin
     const uint8_t* pkt = arena + offsets[p];
     const int n = (int)(offsets[p + 1] - offsets[p]);
     const uint8_t fl = flags ? (uint8_t)(flags[p] & 3u) : 0;
-    if (n == 0 || fl || !(pkt[0] & 3u)) { emit(p, fl, 0, pkt, 0, nullptr, n); continue; }  // single frame / lost: as it is
+    StreamTrack* tr = track ? track + stream_ids[p] : nullptr;
+    if (fl & 2u) {
+      // Lost packet: decode_native conceals the row's capacity (a multiple of 2.5 ms, else BadArgument) frame by frame;
+      // decode_frame(None) takes at most the last packet's frame size at a time, at most 20 ms, and only whole CELT / SILK
+      // frame sizes. Each concealment frame becomes a virtual packet whose two bytes are its sample count.
+      if (cap_per_ch <= 0 || cap_per_ch % 120) { emit(p, (uint8_t)(1u << VF_REJECT_SHIFT), 0, nullptr, 0, nullptr, 0); continue; }
+      const int fs_state = tr && tr->frame_size > 0 ? tr->frame_size : 120;
+      const int md = tr ? tr->mode : 1002;
+      int done = 0, k = 0;
+      while (done < cap_per_ch) {
+        int a = cap_per_ch - done;
+        if (a > 5760) a = 5760;
+        if (a > fs_state) a = fs_state;
+        if (md != 0) {
+          if (a > 960) a = 960;
+          else if (a < 960) {
+            if (a > 480) a = 480;
+            else if (md != 1002 && a > 240 && a < 480) a = 240;
+          }
+        }
+        const uint8_t sz[2] = {(uint8_t)(a & 255), (uint8_t)(a >> 8)};
+        emit(p, (uint8_t)(2u | (k ? VF_CONTINUATION : 0)), (uint32_t)(done * CC), sz, 0, nullptr, 2);
+        done += a; k++;
+      }
+      continue;
+    }
+    if (n == 0 || fl || !(pkt[0] & 3u)) {   // single frame / FEC request: as it is
+      if (n > 0 && !fl && tr && toc_frame_samples(pkt[0]) <= cap_per_ch && n - 1 <= 1275) {
+        tr->frame_size = toc_frame_samples(pkt[0]);
+        tr->mode = (pkt[0] & 0x80) ? 1002 : ((pkt[0] & 0x60) == 0x60 ? 1001 : 1000);
+      }
+      emit(p, fl, 0, pkt, 0, nullptr, n);
+      continue;
+    }
     Frames F;
     F.count = 0;
     int code = split_packet(pkt, n, &F);
     const int per = toc_frame_samples(pkt[0]);
     if (code == H_OK && F.count * per > cap_per_ch) code = H_BUFFER_TOO_SMALL;   // src/opus_decoder.rs:1318-1320
     if (code != H_OK) { emit(p, (uint8_t)((-code) << VF_REJECT_SHIFT), 0, nullptr, (uint8_t)(pkt[0] & ~3u), nullptr, 0); continue; }
+    if (tr) { tr->frame_size = per; tr->mode = (pkt[0] & 0x80) ? 1002 : ((pkt[0] & 0x60) == 0x60 ? 1001 : 1000); }
     for (int k = 0; k < F.count; k++)
       emit(p, k ? VF_CONTINUATION : 0, (uint32_t)(k * per * CC), nullptr, (uint8_t)(pkt[0] & ~3u), pkt + F.off[k], F.len[k]);
   }

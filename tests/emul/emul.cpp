@@ -12,6 +12,7 @@
 #include "../../mousiki_b200/csrc/mb_host_packets.h"
 #include "../../mousiki_b200/csrc/mb_celt_imdct.cuh"
 #include "../../mousiki_b200/csrc/mb_celt_tail.cuh"
+#include "../../mousiki_b200/csrc/mb_celt_plc.cuh"
 #include "../../mousiki_b200/csrc/mb_frame.cuh"
 #include "../../mousiki_b200/csrc/mb_silk_out.cuh"
 #include "../../mousiki_b200/csrc/mb_kat.cuh"
@@ -31,6 +32,10 @@ int emu_kat(int what, const uint32_t* in, uint32_t n_in, uint32_t* out, uint32_t
 // decode gain of the following emu_decode_grid calls (Q8 dB, 0 = none; src/opus_decoder.rs:1376-1392)
 static int g_gain_q8 = 0;
 void emu_set_gain(int gain_q8) { g_gain_q8 = gain_q8; }
+// per-packet flags of the following emu_decode_grid calls (bit 1: lost packet, its two payload bytes = samples to conceal;
+// null: none), as the host front end hands them to the device
+static const uint8_t* g_flags = nullptr;
+void emu_set_flags(const uint8_t* flags) { g_flags = flags; }
 
 // Decodes a regular [n_ticks][n_lanes] packet grid with one fresh decoder state per lane, phases in
 // the same order as the CUDA launcher. pcm: [packet][pcm_stride]. iy_dbg/x_dbg: optional [packet][2*960].
@@ -42,23 +47,23 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   std::vector<uint32_t> rec(tiles * REC_SLOTS * 32, 0);
   std::vector<StreamState> st(n_lanes);
   for (auto& s : st) stream_state_reset(s);
-  std::vector<float> hist((size_t)n_lanes * CC * HIST, 0.f);
+  std::vector<float> hist((size_t)n_lanes * CC * HIST_G, 0.f);
   std::vector<float> en((size_t)F * EN_STRIDE, 0.f);
   std::vector<FrameMeta> meta(F);
-  const uint32_t series_stride = HIST + n_ticks * MAX_N;
+  const uint32_t series_stride = SER_PREFIX + n_ticks * MAX_N + SER_SLACK;
   std::vector<float> series((size_t)n_lanes * CC * series_stride, 0.f);
   const int disable_inv = CC == 1;
   // phase 1
   for (uint32_t f = 0; f < F; f++)
-    parse_cell(arena, offsets, f, rec.data() + rec_index(f, 0), CC, quirks, disable_inv, (int)(pcm_stride / CC), nullptr,
+    parse_cell(arena, offsets, f, rec.data() + rec_index(f, 0), CC, quirks, disable_inv, (int)(pcm_stride / CC), g_flags,
                f >= n_lanes ? f - n_lanes : 0xffffffffu, f >= n_lanes ? nullptr : &st[f].prev_mode);
   // phase 2a
   Team tm = {0, 1};
   EnergySmem esm;
   for (uint32_t j = 0; j < n_lanes; j++)
     celt_energy_stream(tm, &esm, j, n_lanes, n_ticks, nullptr, rec.data(), st.data(), nullptr, en.data(), meta.data(), samples_out, final_range_out, quirks,
-                       nullptr, getenv("MB_EMUL_PARALLEL_BANDS") ? 0 : 1,   // default: the per-stream band pass of large calls
-                       g_gain_q8 != 0 || !pcm16);
+                       g_flags, getenv("MB_EMUL_PARALLEL_BANDS") ? 0 : 1,   // default: the per-stream band pass of large calls
+                       g_gain_q8 != 0 || !pcm16, CC);
   // phase 2b
   std::vector<float> xbuf((size_t)F * XBUF_STRIDE, 0.f), xstage(2 * MAX_N);
   PvqParams pq; pq.rec = rec.data(); pq.meta = meta.data(); pq.xbuf = xbuf.data(); pq.iy_dbg = iy_dbg;
@@ -133,6 +138,9 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   for (uint32_t j = 0; j < n_lanes; j++)
     for (int c = 0; c < CC; c++) celt_comb_channel(tm, csm, j, c, tp);
   delete csm;
+  PlcSmem* psm = new PlcSmem;
+  for (uint32_t j = 0; j < n_lanes; j++) celt_comb_plc_lane(tm, psm, j, tp);
+  delete psm;
   for (uint32_t j = 0; j < n_lanes; j++)
     for (int c = 0; c < CC; c++) celt_deemph_lane(j, c, tp);
   for (uint32_t f = 0; f < F; f++)
@@ -141,7 +149,12 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
     for (uint32_t j = 0; j < n_lanes; j++)
       for (uint32_t t = 0; t < n_ticks; t++) {
         uint32_t p = t * n_lanes + j;
-        if (samples_out[p] <= 0 || !(meta[p].flags & 3u)) continue;
+        if (samples_out[p] <= 0 || !(meta[p].flags & (3u | MB_FL_PLC))) continue;
+        if (g_flags && (g_flags[p] & 2u)) {   // a lost packet is not soft-clipped and clears the clipper's memory
+          st[j].softclip_mem[0] = st[j].softclip_mem[1] = 0.f;
+          for (int i = 0; i < samples_out[p] * CC; i++) pcm16[(size_t)p * pcm_stride + i] = float2int16(out[(size_t)p * pcm_stride + i]);
+          continue;
+        }
         if (!(meta[p].flags & MB_FL_F32ROW)) {   // int16 straight from the SILK lane: final unless a non-linearity carries over
           if (st[j].softclip_mem[0] == 0.f && st[j].softclip_mem[1] == 0.f) continue;
           for (int i = 0; i < samples_out[p] * CC; i++) out[(size_t)p * pcm_stride + i] = (float)pcm16[(size_t)p * pcm_stride + i] * (1.0f / 32768.0f);
