@@ -162,7 +162,7 @@ def test_gpu_cres_known_answer():
 
 
 def test_gpu_unsupported_packets_report_per_packet_codes():
-    """Redundancy-carrying / concealment packets are reported per packet and never poison the batch."""
+    """Packets the product cannot decode yet are reported per packet and never poison the batch; a one-byte frame is concealed."""
     from mousiki_b200 import BatchDecoder, pack_packets
 
     good = bytes([helpers.celt_toc(3, True)]) + bytes(helpers.lcg_bytes(1, 100))
@@ -172,7 +172,9 @@ def test_gpu_unsupported_packets_report_per_packet_codes():
     with BatchDecoder(4, 48000, 2) as dec:
         pcm, samples, rng = dec.decode_float(arena, offsets, np.arange(4, dtype=np.uint32), 1920)
     assert samples[0] == 960 and samples[3] == 960
-    assert samples[1] == -5 and samples[2] == -5
+    assert samples[1] == -5
+    # the one-byte frame is concealed (row F2): on a fresh decoder that is 10 ms of silence, and final_range 0
+    assert samples[2] == 480 and rng[2] == 0 and not pcm[2, :960].any()
     assert np.array_equal(pcm[0], pcm[3]) and rng[0] == rng[3]
 
 
