@@ -99,15 +99,22 @@ MB_DEV void team_fft(Team tm, cpx* f, int shift, int nt) {
     int mm = i != 0 ? fac[2 * i - 1] : 1;
     int radix = fac[2 * i], groups = fstride[i], fs = fstride[i] << shift;
     int per = groups * m;  // butterflies per transform in this stage
+    // (idx -> transform, group, position without integer division: every m below the radix-5 stage is a power of two, the
+    //  radix-5 stage has a single group, and idx / per over this small range is exact in float)
+    const int lm2 = ilog2_exact(m);
+    const float inv_per = 1.0f / (float)per;
     for (int idx = tm.tid; idx < per * nt; idx += tm.n) {
-      int t = idx / per, r = idx - t * per;
-      int g = r / m, k = r - g * m;
+      int t = 0, r = idx;
+      if (nt > 1) { t = (int)(((float)idx + 0.5f) * inv_per); r = idx - t * per; }
+      int g = 0, k = r;
+      if (groups > 1) { g = r >> lm2; k = r & (m - 1); }
       bfly_one(f + t * nfft + g * mm, radix, k, m, fs);
     }
     MB_SYNC();
     m = mm;
   }
 }
+MB_DEV int div_small(int idx, int d, float inv_d) { (void)d; return (int)(((float)idx + 0.5f) * inv_d); }   // exact for idx < 4096, d >= 12
 
 struct ImdctSmem {
   float io[MAX_N];     // freq in, time-domain samples out
@@ -137,8 +144,9 @@ MB_DEV void celt_imdct_core(Team tm, ImdctSmem* sm, int lm, int transient) {
   const uint32_t* twb = kMdctTwiddles960Bits + kMdctTwOff[shift];
   const int16_t* br = shift == 0 ? kFftBitrev480 : shift == 1 ? kFftBitrev240 : shift == 2 ? kFftBitrev120 : kFftBitrev60;
   // pre-rotation + bit-reversal + conjugate (ifft = conj . fft . conj)
+  const float inv_n4 = 1.0f / (float)n4;
   for (int idx = tm.tid; idx < nbk * n4; idx += tm.n) {
-    int b = idx / n4, i = idx - b * n4;
+    int b = nbk > 1 ? div_small(idx, n4, inv_n4) : 0, i = idx - b * n4;
     const float* in = X + b;          // element k of block b is in[k * nbk]
     float x1 = in[(2 * i) * nbk], x2 = in[(n2 - 1 - 2 * i) * nbk];
     float t0 = bits2f(twb[i]), t1 = bits2f(twb[n4 + i]);
@@ -152,7 +160,7 @@ MB_DEV void celt_imdct_core(Team tm, ImdctSmem* sm, int lm, int transient) {
   // post-rotation and window fold against the zero-filled overlap, back into the staging row
   float* O = X;
   for (int idx = tm.tid; idx < nbk * n4; idx += tm.n) {
-    int b = idx / n4, i = idx - b * n4;
+    int b = nbk > 1 ? div_small(idx, n4, inv_n4) : 0, i = idx - b * n4;
     cpx v = F[b * n4 + i];
     v.i = -v.i;
     float t0 = bits2f(twb[i]), t1 = bits2f(twb[n4 + i]);

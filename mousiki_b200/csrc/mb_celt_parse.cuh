@@ -27,9 +27,9 @@ MB_TBL uint8_t kLog2Frac[24] = {0, 8, 13, 16, 19, 21, 23, 24, 26, 27, 28, 29, 30
 MB_TBL int16_t kPvqRowOff[15] = {0, 208, 415, 621, 826, 1030, 1233, 1336, 1389, 1421, 1441, 1455, 1464, 1470, 1473};
 MB_TBL uint16_t kExp2Table8[8] = {16384, 17866, 19483, 21247, 23170, 25267, 27554, 30048};
 
-MB_DEV uint32_t pvq_u(int n, int k) {
+MB_DEV uint32_t pvq_u(int n, int k) {   // one load from the padded copy of CELT_PVQ_U_DATA (celt_tables_data.h)
   int row = n < k ? n : k, col = n < k ? k : n;
-  return kPvqU[kPvqRowOff[row] + col];
+  return kPvqU2[row * PVQ_U_PITCH + col];
 }
 MB_DEV int get_pulses(int i) { return i < 8 ? i : (8 + (i & 7)) << ((i >> 3) - 1); }
 // pulse cache row of (band, lm); lm may be -1. Returns index into kCacheBits50 or -1.
@@ -360,10 +360,13 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
 
   // ---- coarse energy symbols (quant_bands.rs:902-950; the float recurrence runs in phase 2a)
   uint32_t ew[2 * NB_EBANDS];
+  MB_ROLLED
   for (int i = 0; i < 2 * NB_EBANDS; i++) ew[i] = 0;
   {
     const uint8_t* prob = kEProbModel + (lm * 2 + intra) * 42;
+    MB_ROLLED
     for (int i = start; i < end; i++)
+      MB_ROLLED
       for (int c = 0; c < C; c++) {
         int t = dec.tell();
         int qi;
@@ -380,6 +383,7 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
   }
   // ---- tf_decode (celt_decoder.rs:2704-2748)
   int8_t tf_res[NB_EBANDS];
+  MB_ROLLED
   for (int i = 0; i < NB_EBANDS; i++) tf_res[i] = 0;
   {
     uint32_t budget = (uint32_t)len_bits;
@@ -388,6 +392,7 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
     int tf_select_rsv = lm > 0 && t + logp < budget;
     if (tf_select_rsv) budget -= 1;
     int curr = 0, tf_changed = 0;
+    MB_ROLLED
     for (int i = start; i < end; i++) {
       if (t + logp <= budget) {
         curr ^= dec.bit_logp(logp);
@@ -400,6 +405,7 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
     int tf_select = 0;
     const int8_t* sel = kTfSelect + lm * 8 + 4 * is_transient;
     if (tf_select_rsv && sel[tf_changed] != sel[2 + tf_changed]) tf_select = dec.bit_logp(1);
+    MB_ROLLED
     for (int i = start; i < end; i++) tf_res[i] = sel[2 * tf_select + tf_res[i]];
   }
   tell = dec.tell();
@@ -408,6 +414,7 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
 
   // ---- init_caps (celt.rs:799-822) + dynalloc boosts (celt_decoder.rs:3021-3044)
   int cap[NB_EBANDS], offsets[NB_EBANDS];
+  MB_ROLLED
   for (int i = 0; i < NB_EBANDS; i++) {
     int n = (eband(i + 1) - eband(i)) << lm;
     cap[i] = ((kCacheCaps50[NB_EBANDS * (2 * lm + C - 1) + i] + 64) * C * n) >> 2;
@@ -418,6 +425,7 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
   int tell_frac = (int)dec.tell_frac();
   {
     int dynalloc_logp = 6;
+    MB_ROLLED
     for (int i = start; i < end; i++) {
       int width = (C * (eband(i + 1) - eband(i))) << lm;
       int quanta = imin(width << BITRES, imax(6 << BITRES, width));
@@ -444,6 +452,7 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
   int pulses[NB_EBANDS], fine_quant[NB_EBANDS];
   uint32_t fine_prio_mask = 0;
   int intensity = 0, dual_stereo = 0, balance = 0, coded_bands;
+  MB_ROLLED
   for (int i = 0; i < NB_EBANDS; i++) { pulses[i] = 0; fine_quant[i] = 0; }
   {
     int bits1[NB_EBANDS], bits2[NB_EBANDS], thresh[NB_EBANDS], trim_offset[NB_EBANDS];
@@ -460,6 +469,7 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
         if (total >= 1 << BITRES) { dual_stereo_rsv = 1 << BITRES; total -= dual_stereo_rsv; }
       }
     }
+    MB_ROLLED
     for (int j = start; j < end; j++) {
       int n = eband(j + 1) - eband(j);
       thresh[j] = imax(C << BITRES, (3 * n) << (lm + BITRES) >> 4);
@@ -469,6 +479,7 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
     int lo = 1, hi = 10;
     while (lo <= hi) {
       int mid = (lo + hi) >> 1, done = 0, psum = 0;
+      MB_ROLLED
       for (int j = end; j-- > start;) {
         int n = eband(j + 1) - eband(j);
         int bitsj = (C * n * kBandAllocation[mid * NB_EBANDS + j]) << lm >> 2;
@@ -481,6 +492,7 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
     }
     hi = lo;
     lo -= 1;
+    MB_ROLLED
     for (int j = start; j < end; j++) {
       int n = eband(j + 1) - eband(j);
       int b1 = (C * n * kBandAllocation[lo * NB_EBANDS + j]) << lm >> 2;
@@ -496,8 +508,10 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
     // interp_bits2pulses
     const int alloc_floor = C << BITRES, stereo = C > 1, logM = lm << BITRES;
     lo = 0; hi = 64;
+    MB_ROLLED
     for (int it = 0; it < 6; it++) {
       int mid = (lo + hi) >> 1, psum = 0, done = 0;
+      MB_ROLLED
       for (int j = end; j-- > start;) {
         int tmp = bits1[j] + ((mid * bits2[j]) >> 6);
         if (tmp >= thresh[j] || done) { done = 1; psum += imin(tmp, cap[j]); }
@@ -506,6 +520,7 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
       if (psum > total) hi = mid; else lo = mid;
     }
     int psum = 0, done = 0;
+    MB_ROLLED
     for (int j = end; j-- > start;) {
       int tmp = bits1[j] + ((lo * bits2[j]) >> 6);
       if (tmp < thresh[j] && !done) tmp = tmp >= alloc_floor ? alloc_floor : 0;
@@ -548,7 +563,9 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
       int left = total - psum;
       int per = (int)((uint32_t)imax(left, 0) / (uint32_t)denom);
       left -= denom * per;
+      MB_ROLLED
       for (int j = start; j < coded; j++) pulses[j] += per * (eband(j + 1) - eband(j));
+      MB_ROLLED
       for (int j = start; j < coded; j++) {
         int add = imin(eband(j + 1) - eband(j), left);
         pulses[j] += add;
@@ -556,6 +573,7 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
       }
     }
     int bal = 0;
+    MB_ROLLED
     for (int j = start; j < coded; j++) {
       int N0 = eband(j + 1) - eband(j), N = N0 << lm;
       int bit = pulses[j] + bal;
@@ -595,6 +613,7 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
       fine_prio_mask |= (uint32_t)prio << j;
     }
     balance = bal;
+    MB_ROLLED
     for (int j = coded; j < end; j++) {
       fine_quant[j] = pulses[j] >> stereo >> BITRES;
       pulses[j] = 0;
@@ -603,14 +622,18 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
     coded_bands = coded;
   }
   // ---- fine energy bits (quant_bands.rs:1850-1880)
+  MB_ROLLED
   for (int i = start; i < end; i++) {
     if (fine_quant[i] <= 0) continue;
+    MB_ROLLED
     for (int c = 0; c < C; c++) {
       uint32_t q2 = dec.raw_bits((unsigned)fine_quant[i]);
       ew[c * NB_EBANDS + i] |= (q2 & 255u) << 16;
     }
   }
+  MB_ROLLED
   for (int i = start; i < end; i++)
+    MB_ROLLED
     for (int c = 0; c < C; c++) ew[c * NB_EBANDS + i] |= (uint32_t)imin(imax(fine_quant[i], 0), 15) << 24;
 
   // ---- band loop (bands.rs:2575-3082), integer side
@@ -622,6 +645,7 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
     const int N = M * SHORT_MDCT;
     cx.intensity = intensity;
     int lowband_offset = -1, update_lowband = 1, dual = dual_stereo;
+    MB_ROLLED
     for (int i = start; i < end; i++) {
       cx.band = i;
       int band_start = M * eband(i), n = M * eband(i + 1) - band_start;
@@ -683,10 +707,13 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
   // ---- unquant_energy_finalise bits (quant_bands.rs:1922-1970)
   {
     int bits_left = len_bits - dec.tell();
+    MB_ROLLED
     for (int prio = 0; prio < 2; prio++)
+      MB_ROLLED
       for (int i = start; i < end; i++) {
         if (bits_left < C) break;
         if (fine_quant[i] >= 8 || (int)((fine_prio_mask >> i) & 1u) != prio) continue;
+        MB_ROLLED
         for (int c = 0; c < C; c++) {
           uint32_t q2 = dec.raw_bits(1);
           ew[c * NB_EBANDS + i] |= (1u << 28) | (q2 << 29);
@@ -697,6 +724,7 @@ MB_DEV_NOINLINE uint32_t celt_parse_frame(const uint8_t* data, int len, int lm, 
   int code = MB_OK;
   if (dec.tell() > 8 * len) code = MB_INVALID_PACKET;
   if (cx.w.overflow) code = MB_INTERNAL_ERROR;
+  MB_ROLLED
   for (int i = 0; i < 2 * NB_EBANDS; i++) cx.w.put(S_ENERGY + i, ew[i]);
   cx.w.put(S_HDR0, (uint32_t)lm | ((uint32_t)(C - 1) << 2) | ((uint32_t)silence << 3) | ((uint32_t)is_transient << 4) |
                        ((uint32_t)intra << 5) | ((uint32_t)spread << 6) | ((uint32_t)anti_collapse_on << 8) |
