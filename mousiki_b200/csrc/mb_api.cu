@@ -426,7 +426,7 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
     // already. The latter is final unless the previous packet left a non-linearity to carry over (opus.rs:44-60).
     const bool from_float = (fl & MB_FL_F32ROW) != 0;
     // a LOST packet is not soft-clipped, and leaves the clipper's memory cleared (opus_decoder.rs:1186-1222: soft_clip = false)
-    const bool lost_pkt = flags && (flags[p] & 2u);
+    const bool lost_pkt = flags && (flags[p] & 3u);   // (nor is one rebuilt from in-band FEC data, :1312)
     if (lost_pkt) mem = 0.f;
     if (!from_float && !__any_sync(0xffffffffu, mem != 0.f)) continue;
     const int total = n * CC;
@@ -523,62 +523,21 @@ __global__ void k_reset(StreamState* st, float* hist, const uint32_t* __restrict
 
 // SILK-only packets, phase 2: one lane per stream, its packets in tick order (mb_silk_synth.cuh / mb_silk_out.cuh).
 // The stream's SILK state is staged in the lane's local memory for the pass and written back at the end.
-__global__ void __launch_bounds__(64, 12) k_silk(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
-                                             const uint32_t* __restrict__ lane_stream, const uint32_t* __restrict__ rec,
-                                             const FrameMeta* __restrict__ meta, SilkState* st_all, uint32_t* silk_hist,
-                                             uint32_t n_streams, float* __restrict__ pcm_f32,
-                                             int16_t* __restrict__ pcm_i16, uint32_t pcm_stride, int CC, uint32_t quirks, float gain,
-                                             int apply_gain, const uint32_t* __restrict__ out_map) {
+__global__ void __launch_bounds__(64, 12) k_silk(SilkLaneParams q) {
   __shared__ int32_t stage[64][33];   // 32 staged output samples per lane, pitch 33: conflict-free for lockstep lanes
   __shared__ int16_t fir[48];
   if (threadIdx.x < 48) fir[threadIdx.x] = silk_resampler_frac_FIR_12[threadIdx.x];
   __syncthreads();
   const uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
-  if (lane >= n_lanes) return;
-  bool any = false;
-  for (uint32_t t = 0; t < n_ticks && !any; t++) any = (meta[t * n_lanes + lane].flags & 2u) != 0;
-  if (!any) return;
-  const uint32_t sid = lane_stream ? lane_stream[lane] : lane;
-  SilkState* gs = st_all + sid;
-  SilkState S = *gs;
+  if (lane >= q.n_lanes) return;
   SilkWork W;
-  SilkHistRef H = {silk_hist, n_streams, sid};
-  int side_live = 0;
-  silk_hist_load(W, H, 0);
-  for (uint32_t t = 0; t < n_ticks; t++) {
-    const uint32_t f = t * n_lanes + lane;
-    if (!(meta[f].flags & 2u)) continue;
-    const uint32_t p = pkt_map ? pkt_map[f] : f;
-    const uint32_t* rb = rec + rec_index(f, 0);
-    const uint32_t fl = meta[f].flags;
-    const bool to_float = (fl & MB_FL_F32ROW) != 0;   // the packet goes through the float row (a CELT frame shares one of its rows, or a decode gain applies)
-    const bool shared = (fl & (8u | 16u)) != 0;       // a CELT frame shares THIS row (hybrid, fade-out, redundancy): k_deemph / k_fade finish it
-    const bool hyb_layout = ((rb[S_STATUS * 32] >> 17) & 3u) != 0;       // hybrid, or a one-frame SILK-only cell
-    if (fl & 32u) {   // CELT -> SILK: silk decoder reset (opus_decoder.rs:694-696)
-      silk_state_reset(S, 0);
-      silk_ring_clear(W.hist[0], W.pos[0]); silk_ring_clear(W.hist[1], W.pos[1]);
-      side_live = 1;
-    }
-    SilkPcmOut o;
-    // SILK-only cells are final: int16 directly on the i16 path
-    o.f32 = (to_float || !pcm_i16) ? pcm_f32 + pcm_elem_off(out_map, p, pcm_stride) : nullptr;
-    o.i16 = (to_float || !pcm_i16) ? nullptr : pcm_i16 + pcm_elem_off(out_map, p, pcm_stride);
-    // decode gain: once on the finished sum. Hybrid: k_deemph does it for the whole row; fade-out: k_deemph for the first
-    // 120 samples, here for the rest; redundancy: k_fade for the whole row
-    const bool fadeout = (fl & 8u) && !((rb[S_STATUS * 32] >> 17) & 1u);
-    o.CC = CC; o.gain = gain; o.apply_gain = (shared && !fadeout) ? 0 : apply_gain; o.gain_from = fadeout ? SHORT_MDCT : 0;
-    silk_synth_packet(S, W, H, side_live, rb[(hyb_layout ? S_SILK_HYB : S_HDR0) * 32], rb + (hyb_layout ? S_SILK_HYB + 1 : SL_BASE) * 32, quirks, o,
-                      stage[threadIdx.x], fir);
-  }
-  silk_hist_store(W, H, 0);
-  if (side_live) silk_hist_store(W, H, 1);
-  *gs = S;
+  silk_lane(q, lane, W, stage[threadIdx.x], fir);
 }
 __global__ void k_silk_reset(SilkState* st, uint32_t* silk_hist, uint32_t n_streams, const uint32_t* __restrict__ ids, uint32_t n) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint32_t sid = ids ? ids[i] : i;
-  silk_state_reset(st[sid], 1);
+  silk_state_reset(st[sid], 1);   // (marks the excitation buffers for clearing on first use, mb_silk_plc.cuh)
   for (int k = 0; k < 320; k++) silk_hist[(size_t)k * n_streams + sid] = 0;
 }
 
@@ -640,7 +599,7 @@ struct bd_handle {
     timeline.push_back({std::string(what) + " " + std::to_string(k), e});
   }
   struct PassOut { bool on = false; char* host_pcm = nullptr; const char* dev_pcm = nullptr; size_t elem = 0; } pass_out;
-  DevBuf states, silk_states, silk_hist, fold, hist, rec, en, meta, series, xbuf;
+  DevBuf states, silk_states, silk_hist, silk_exc, fold, hist, rec, en, meta, series, xbuf;
   // staging for the host-buffer entry points
   DevBuf d_arena, d_offsets, d_pkt_map, d_out_map, d_lane_stream, d_flags, d_pcm, d_pcm16, d_samples, d_range, d_ids, d_dbg_iy, d_dbg_x;
   std::vector<uint32_t> h_pkt_map, h_lane_stream, h_lane_of_stream, h_epoch, h_count, h_tick, v_range;
@@ -729,6 +688,9 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
   if (h->hist.ensure((size_t)cfg->n_streams * h->CC * HIST_G * sizeof(float)) != cudaSuccess) return fail(BD_ERR_ALLOC);
   if (h->silk_states.ensure((size_t)cfg->n_streams * sizeof(SilkState)) != cudaSuccess) return fail(BD_ERR_ALLOC);
   if (h->silk_hist.ensure((size_t)cfg->n_streams * 320 * sizeof(uint32_t)) != cudaSuccess) return fail(BD_ERR_ALLOC);
+  // excitation of the last decoded SILK frame + comfort-noise FIFO, 2 channels x 2 x 320 words per stream (mb_silk_plc.cuh);
+  // never read before the lane that owns a stream has cleared them (SilkChanState::exc_dirty)
+  if (h->silk_exc.ensure((size_t)cfg->n_streams * 1280 * sizeof(int32_t)) != cudaSuccess) return fail(BD_ERR_ALLOC);
   if (h->fold.ensure((size_t)cfg->n_streams * FOLD_WORDS * sizeof(float)) != cudaSuccess) return fail(BD_ERR_ALLOC);
   if (cudaMemsetAsync(h->fold.p, 0, (size_t)cfg->n_streams * FOLD_WORDS * sizeof(float), h->own_stream) != cudaSuccess) return fail(BD_ERR_CUDA);
   k_silk_reset<<<(cfg->n_streams + 127) / 128, 128, 0, h->own_stream>>>(h->silk_states.as<SilkState>(), h->silk_hist.as<uint32_t>(),
@@ -742,7 +704,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
 void bd_destroy(bd_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  DevBuf* all[] = {&h->states, &h->silk_states, &h->silk_hist, &h->fold, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map, &h->d_out_map,
+  DevBuf* all[] = {&h->states, &h->silk_states, &h->silk_hist, &h->silk_exc, &h->fold, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map, &h->d_out_map,
                    &h->d_lane_stream, &h->d_flags, &h->d_pcm, &h->d_pcm16, &h->d_samples, &h->d_range, &h->d_ids, &h->d_dbg_iy, &h->d_dbg_x};
   for (DevBuf* b : all) b->release();
   for (auto& sp : h->prof_spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -965,10 +927,12 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     // frames on top. SILK-only samples are exact int16 values scaled by 2^-15: on the i16 path soft clip + float2int16
     // is the identity and the lane stores int16 directly; hybrid cells go through the float row.
     h->prof_begin(BD_K_SILK, ss);
-    k_silk<<<(n_lanes + 63) / 64, 64, 0, ss>>>(n_lanes, nt, map, d_lane_stream, h->rec.as<uint32_t>(), meta_p,
-                                              h->silk_states.as<SilkState>(), h->silk_hist.as<uint32_t>(), h->cfg.n_streams, pcm,
-                                              d_pcm_i16 ? d_pcm_i16 + shift * pcm_stride : nullptr, pcm_stride, CC, h->cfg.quirks, h->gain,
-                                              h->cfg.gain_q8 != 0, d_out_map);
+    SilkLaneParams sq;
+    sq.n_lanes = n_lanes; sq.n_ticks = nt; sq.pkt_map = map; sq.lane_stream = d_lane_stream; sq.rec = h->rec.as<uint32_t>(); sq.meta = meta_p;
+    sq.st_all = h->silk_states.as<SilkState>(); sq.silk_hist = h->silk_hist.as<uint32_t>(); sq.silk_exc = h->silk_exc.as<int32_t>();
+    sq.n_streams = h->cfg.n_streams; sq.pcm_f32 = pcm; sq.pcm_i16 = d_pcm_i16 ? d_pcm_i16 + shift * pcm_stride : nullptr;
+    sq.pcm_stride = pcm_stride; sq.CC = CC; sq.quirks = h->cfg.quirks; sq.gain = h->gain; sq.apply_gain = h->cfg.gain_q8 != 0; sq.out_map = d_out_map;
+    k_silk<<<(n_lanes + 63) / 64, 64, 0, ss>>>(sq);
     h->prof_end(ss);
     CK(cudaEventRecord(h->ev_silk, ss));   // the SILK rows are written: k_deemph (hybrid accumulate) and the output stage may go
     h->launches += 1;

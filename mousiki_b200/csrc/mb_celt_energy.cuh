@@ -77,6 +77,8 @@ struct FrameMeta {
 enum : uint32_t { MB_FL_KEEP_TAIL = 1u << 28, MB_FL_PLC = 1u << 30, MB_FL_PLC_PITCH = 1u << 31 };
 // S_STATUS bit 29: lost frame (no payload); S_RANGE then holds the number of samples to conceal
 #define MB_ST_LOST(s) (((s) >> 29) & 1u)
+// S_STATUS bit 30: the cell's SILK record comes from the packet's LBRR data (in-band FEC)
+#define MB_ST_FEC(s) (((s) >> 30) & 1u)
 enum { EN_STRIDE = 4 * 2 * NB_EBANDS, EN_GAINS = 3 * 2 * NB_EBANDS,   // per-frame energy scratch: E, prev1 (old_log_e), prev2 (old_log_e2), band gains
       
        MB_FL_FOLD = 8u | 16u | 512u,
@@ -142,36 +144,22 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
         }
         const uint32_t s2 = rec[rec_index(f2, S_STATUS)];
         celt_part = MB_ST_DECODED(s2) && (!((s2 >> 16) & 1u) || ((s2 >> 17) & 1u) || ((s2 >> 19) & 3u));
+        // (concealment frames come first in their packet: they all see the mode the stream is in now)
+        if (MB_ST_LOST(s2) && (st_prev_redundancy || st_prev_mode != 1000)) celt_part = true;
       }
       pkt_route = celt_part ? MB_FL_F32ROW : 0u;
     }
-    if (MB_ST_LOST(status) && !pkt_failed) {
-      // ---- lost packet / frame of at most one byte: decode_frame(None) (src/opus_decoder.rs:491-575). The concealment of a
-      // stream whose last packet was CELT-only (or ended in a SILK -> CELT redundancy frame) is celt_decode_lost
-      // (src/celt/celt_decoder.rs:1429-1855); SILK / hybrid concealment is not built yet (reported as unimplemented).
-      const int audiosize = (int)r[S_RANGE * 32];
-      const int md = st_prev_redundancy ? 1002 : st_prev_mode;
-      if (md == 0) {   // nothing decoded yet: silence (opus_decoder.rs:527-540)
-        m.flags = MB_FL_PLC | MB_FL_F32ROW;   // concealed, but no CELT frame: k_fade zero-fills seed_in samples of the row
-        m.seed_in = (uint32_t)audiosize;
-        st_prev_mode = 0; st_prev_redundancy = 0; st_range_final = 0; st_last_duration = audiosize;
-        if (lead) { meta[f] = m; samples_out[p] = audiosize; final_range_out[p] = 0; }
-        continue;
-      }
-      int lmq = -1;
-      for (int q = 0; q <= MAX_LM; q++) if ((SHORT_MDCT << q) == audiosize) lmq = q;
-      if (md != 1002 || lmq < 0) {
-        if (lead) { meta[f] = m; samples_out[p] = MB_UNIMPLEMENTED; final_range_out[p] = st_range_final; }
-        pkt_failed = true;
-        continue;
-      }
-      const int start = 0, end = st_celt_end, Mq = 1 << lmq;
+    // ---- CELT concealment of one frame (celt_decode_lost, src/celt/celt_decoder.rs:1429-1855), bands [start, st_celt_end):
+    // band-shaped noise through k_plan / k_bands / k_imdct, or (full-band streams, short losses) pitch repetition in
+    // k_comb_plc. `extra`: flag bits of the SILK side of the frame (hybrid). Leaves m, the energies and the CELT state updated.
+    auto celt_conceal = [&](int audiosize, int lmq, int start, uint32_t extra) {
+      const int end = st_celt_end, Mq = 1 << lmq;
       const int noise_based = st_loss_duration >= 40 || start != 0 || st_skip_plc;
       // a synthetic frame header for the kernels downstream: LM, the DECODER's channel count, band range; no leaves, no nodes
       if (lead) {
         r[S_HDR0 * 32] = (uint32_t)lmq | ((uint32_t)(CC - 1) << 2) | (2u << 6) | ((uint32_t)start << 26);
         r[S_HDR1 * 32] = 0u;
-        r[S_STATUS * 32] = status | ((uint32_t)end << 8);
+        r[S_STATUS * 32] = (status & ~(31u << 8)) | ((uint32_t)end << 8);
         r[S_PLAN * 32] = 0u;
       }
       float* ef = en + (size_t)f * EN_STRIDE;
@@ -194,15 +182,38 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
         for (int k = 0; k < CC * total; k++) sd = sd * 1664525u + 1013904223u;
         st_rng = sd;
         st_prefold = 0; st_skip_plc = 1;
-        m.flags = 1u | MB_FL_PLC | MB_FL_F32ROW | (silk_side_seen ? 512u : 0u);
+        m.flags = 1u | MB_FL_PLC | MB_FL_F32ROW | (silk_side_seen ? 512u : 0u) | extra;
       } else {
         m.seed_in = (uint32_t)st_loss_duration;
         st_prefold = 1;
-        m.flags = 1u | MB_FL_PLC | MB_FL_PLC_PITCH | MB_FL_F32ROW;
+        m.flags = 1u | MB_FL_PLC | MB_FL_PLC_PITCH | MB_FL_F32ROW | extra;
       }
       st_loss_duration = imin(10000, st_loss_duration + Mq);
-      st_prev_mode = md; st_prev_redundancy = 0; st_range_final = 0; st_last_duration = audiosize;
       sample_off += (uint32_t)audiosize;
+    };
+    if (MB_ST_LOST(status) && !pkt_failed) {
+      // ---- lost packet / frame of at most one byte: decode_frame(None) (src/opus_decoder.rs:491-575). The stream conceals in
+      // the mode of its last packet (CELT-only after a SILK -> CELT redundancy frame): SILK in k_silk (mb_silk_plc.cuh), CELT
+      // as above, hybrid both (the CELT part from band 17, always noise).
+      const int audiosize = (int)r[S_RANGE * 32];
+      const int md = st_prev_redundancy ? 1002 : st_prev_mode;
+      if (md == 0) {   // nothing decoded yet: silence (opus_decoder.rs:527-540)
+        m.flags = MB_FL_PLC | MB_FL_F32ROW;   // concealed, but no CELT frame: k_fade zero-fills seed_in samples of the row
+        m.seed_in = (uint32_t)audiosize;
+        st_prev_mode = 0; st_prev_redundancy = 0; st_range_final = 0; st_last_duration = audiosize;
+        if (lead) { meta[f] = m; samples_out[p] = audiosize; final_range_out[p] = 0; }
+        continue;
+      }
+      int lmq = -1;
+      for (int q = 0; q <= MAX_LM; q++) if ((SHORT_MDCT << q) == audiosize) lmq = q;
+      if (lmq < 0) {   // (the host front end only cuts whole frame sizes)
+        if (lead) { meta[f] = m; samples_out[p] = MB_UNIMPLEMENTED; final_range_out[p] = st_range_final; }
+        pkt_failed = true;
+        continue;
+      }
+      if (md == 1000) m.flags = 2u | MB_FL_PLC | pkt_route;
+      else celt_conceal(audiosize, lmq, md == 1001 ? 17 : 0, md == 1001 ? (2u | 8u) : 0u);
+      st_prev_mode = md; st_prev_redundancy = 0; st_range_final = 0; st_last_duration = audiosize;
       if (lead) { meta[f] = m; samples_out[p] = audiosize; final_range_out[p] = 0; }
       continue;
     }
@@ -275,6 +286,16 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
       st_rng = 0; st_loss_duration = 0;
       st_skip_plc = 1; st_prefold = 0;   // (last_pitch_index and the concealment filter are only read after a frame has set them)
       m.seed_in = 0;
+    }
+    if (MB_ST_FEC(status) && hybrid) {
+      // hybrid packet decoded from its LBRR data: SILK from the record, the CELT part concealed (opus_decoder.rs:944-952)
+      const int lmq = (int)MB_H0_LM(h0);
+      st_celt_end = (int)MB_ST_END(status);
+      celt_conceal(SHORT_MDCT << lmq, lmq, 17, 2u | 8u | (celt_reset ? 4u : 0u) | silk_reset);
+      silk_side_seen = true; st_fold_serial = 1;
+      st_prev_mode = 1001; st_prev_redundancy = 0; st_range_final = silk_rng; st_last_duration = SHORT_MDCT << lmq;
+      if (lead) { meta[f] = m; samples_out[p] = SHORT_MDCT << lmq; final_range_out[p] = st_range_final; }
+      continue;
     }
     const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), start = (int)MB_H0_START(h0), end = (int)MB_ST_END(status);
     const int intra = (int)MB_H0_INTRA(h0), silence = (int)MB_H0_SILENCE(h0), transient = (int)MB_H0_TRANSIENT(h0);

@@ -31,7 +31,7 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
   if (len == 0 && !flags) { rec_base[S_STATUS * 32] = 1u << 15; return; }
   int code = MB_OK;
   const uint8_t* data = arena + off;
-  if (flags && (flags[pkt] & 2u)) {
+  if ((flags && (flags[pkt] & 2u)) || len == 0) {
     // lost packet (or one concealment frame of it, cut by the host): no payload. The two bytes the host put in its place
     // say how many samples to conceal (mb_host_packets.h); the stream pass decides how (k_energy).
     int n = len >= 2 ? (int)data[0] | ((int)data[1] << 8) : cap_per_ch;
@@ -40,7 +40,14 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
     rec_base[S_STATUS * 32] = 1u << 29;
     return;
   }
-  if (len == 0 || (flags && (flags[pkt] & 1u))) code = MB_UNIMPLEMENTED;  // in-band FEC (row F2)
+  // bit0: decode the packet's in-band FEC (LBRR) data in place of the packet (decode_native, src/opus_decoder.rs:1240-1316).
+  // Only SILK / hybrid packets carry any; a CELT-only one is concealed like a lost packet (:1247-1250).
+  const int fec = (flags && (flags[pkt] & 1u)) ? 1 : 0;
+  if (fec && (data[0] & 0x80u)) {
+    rec_base[S_RANGE * 32] = (uint32_t)cap_per_ch;
+    rec_base[S_STATUS * 32] = 1u << 29;
+    return;
+  }
   uint32_t toc = 0;
   if (code == MB_OK) {
     toc = data[0];
@@ -61,7 +68,17 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
         else {
           RangeDec ec;
           ec.open(data + 1, (uint32_t)(len - 1));
-          silk_parse_payload(ec, 16, lm == 3 ? 4 : 2, 1, C, quirks, rec_base + (S_SILK_HYB + 1) * 32);
+          silk_parse_payload(ec, 16, lm == 3 ? 4 : 2, 1, C, quirks, rec_base + (S_SILK_HYB + 1) * 32, fec);
+          if (fec) {
+            // the CELT part of a packet decoded from its LBRR data is concealed (opus_decoder.rs:944-952): no CELT parse; the
+            // cell carries the SILK record, the final range behind it, and the band range of the packet's bandwidth
+            rec_base[S_SILK_HYB * 32] = 16u | ((uint32_t)(lm == 3 ? 4 : 2) << 5) | (1u << 8) | ((uint32_t)C << 10);
+            rec_base[(S_SILK_HYB + 342) * 32] = ec.rng;
+            rec_base[S_RANGE * 32] = ec.rng;
+            rec_base[S_HDR0 * 32] = (uint32_t)lm | ((uint32_t)(C - 1) << 2) | (17u << 26);
+            rec_base[S_STATUS * 32] = (1u << 14) | (3u << 16) | (1u << 30) | ((uint32_t)((toc & 0x10u) ? 21 : 19) << 8);
+            return;
+          }
           int redundancy = 0;
           if (ec.tell() + 17 + 20 <= 8 * (len - 1)) redundancy = ec.bit_logp(12);
           if (redundancy) code = MB_UNIMPLEMENTED;           // CELT redundancy frame + cross-fade: next row
@@ -78,7 +95,7 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
           after_hybrid = !(ptoc & 0x80u) && (ptoc & 0x60u) == 0x60u;
         }
         SilkRedundancy red;
-        const uint32_t st_silk = silk_parse_frame(data + 1, len - 1, toc, quirks, cap_per_ch, rec_base, &red);
+        const uint32_t st_silk = silk_parse_frame(data + 1, len - 1, toc, quirks, cap_per_ch, rec_base, &red, fec);
         // status bits 19-20: the CELT frame that shares the cell: 1 fade-out silence, 2 redundancy CELT -> SILK (played
         // before the SILK frame), 3 redundancy SILK -> CELT (after it). A packet that would need two of them (redundancy
         // right after a hybrid packet) is left to the stream pass, which reports it.
@@ -115,11 +132,13 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
 // The cell's status word also carries the packet's TOC byte (bits 21-28): the stream pass derives the decoder's bandwidth
 // query from it (Decoder::bandwidth, src/codec.rs:941-953).
 #define MB_ST_TOC(s) (((s) >> 21) & 255u)
+#define MB_ST_LOST_BIT(s) (((s) >> 29) & 1u)
 MB_DEV void parse_cell(const uint8_t* arena, const uint32_t* offsets, uint32_t pkt, uint32_t* rec_base, int CC, uint32_t quirks,
                        int disable_inv, int cap_per_ch, const uint8_t* flags, uint32_t prev_pkt = 0xffffffffu,
                        const int32_t* prev_mode = nullptr) {
   parse_cell_body(arena, offsets, pkt, rec_base, CC, quirks, disable_inv, cap_per_ch, flags, prev_pkt, prev_mode);
-  if (pkt != 0xffffffffu && !(flags && ((flags[pkt] >> 4) || (flags[pkt] & 2u))) && offsets[pkt + 1] > offsets[pkt])
+  if (pkt != 0xffffffffu && !(flags && ((flags[pkt] >> 4) || (flags[pkt] & 2u))) && offsets[pkt + 1] > offsets[pkt] &&
+      !MB_ST_LOST_BIT(rec_base[S_STATUS * 32]))
     rec_base[S_STATUS * 32] |= (uint32_t)arena[offsets[pkt]] << 21;
 }
 

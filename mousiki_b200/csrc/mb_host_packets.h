@@ -131,7 +131,8 @@ struct StreamTrack { int32_t frame_size = 0, mode = 0; };   // mode: 0 nothing y
 inline bool needs_split(const uint8_t* arena, const uint32_t* offsets, const uint8_t* flags, uint32_t n_packets) {
   for (uint32_t p = 0; p < n_packets; p++) {
     if (offsets[p + 1] > offsets[p] && (arena[offsets[p]] & 3u)) return true;
-    if (flags && (flags[p] & 2u)) return true;
+    if (flags && (flags[p] & 3u)) return true;
+    if (flags && offsets[p + 1] == offsets[p]) return true;   // an empty packet is a lost packet (src/opus_decoder.rs:1186)
   }
   return false;
 }
@@ -161,16 +162,15 @@ inline void split_batch(const uint8_t* arena, const uint32_t* offsets, const uin
     const int n = (int)(offsets[p + 1] - offsets[p]);
     const uint8_t fl = flags ? (uint8_t)(flags[p] & 3u) : 0;
     StreamTrack* tr = track ? track + stream_ids[p] : nullptr;
-    if (fl & 2u) {
-      // Lost packet: decode_native conceals the row's capacity (a multiple of 2.5 ms, else BadArgument) frame by frame;
-      // decode_frame(None) takes at most the last packet's frame size at a time, at most 20 ms, and only whole CELT / SILK
-      // frame sizes. Each concealment frame becomes a virtual packet whose two bytes are its sample count.
-      if (cap_per_ch <= 0 || cap_per_ch % 120) { emit(p, (uint8_t)(1u << VF_REJECT_SHIFT), 0, nullptr, 0, nullptr, 0); continue; }
+    // Lost packet: decode_native conceals `want` samples (a multiple of 2.5 ms, else BadArgument) frame by frame;
+    // decode_frame(None) takes at most the last packet's frame size at a time, at most 20 ms, and only whole CELT / SILK
+    // frame sizes. Each concealment frame becomes a virtual packet whose two bytes are its sample count.
+    auto conceal = [&](int want, int k0) {
       const int fs_state = tr && tr->frame_size > 0 ? tr->frame_size : 120;
       const int md = tr ? tr->mode : 1002;
-      int done = 0, k = 0;
-      while (done < cap_per_ch) {
-        int a = cap_per_ch - done;
+      int done = 0, k = k0;
+      while (done < want) {
+        int a = want - done;
         if (a > 5760) a = 5760;
         if (a > fs_state) a = fs_state;
         if (md != 0) {
@@ -184,6 +184,29 @@ inline void split_batch(const uint8_t* arena, const uint32_t* offsets, const uin
         emit(p, (uint8_t)(2u | (k ? VF_CONTINUATION : 0)), (uint32_t)(done * CC), sz, 0, nullptr, 2);
         done += a; k++;
       }
+      return k;
+    };
+    if ((fl & 2u) || n == 0) {
+      if (cap_per_ch <= 0 || cap_per_ch % 120) { emit(p, (uint8_t)(1u << VF_REJECT_SHIFT), 0, nullptr, 0, nullptr, 0); continue; }
+      conceal(cap_per_ch, 0);
+      continue;
+    }
+    if (fl & 1u) {
+      // In-band FEC (decode_native, src/opus_decoder.rs:1240-1316): the row receives the frame BEFORE this packet, rebuilt from
+      // the packet's LBRR data. Whatever the row holds beyond one frame of the packet is concealed first; a CELT-only packet
+      // (or a decoder whose last packet was CELT-only) has no such data and the whole row is concealed.
+      if (cap_per_ch <= 0 || cap_per_ch % 120) { emit(p, (uint8_t)(1u << VF_REJECT_SHIFT), 0, nullptr, 0, nullptr, 0); continue; }
+      Frames F;
+      F.count = 0;
+      const int code = split_packet(pkt, n, &F);
+      if (code != H_OK) { emit(p, (uint8_t)((-code) << VF_REJECT_SHIFT), 0, nullptr, (uint8_t)(pkt[0] & ~3u), nullptr, 0); continue; }
+      const int per = toc_frame_samples(pkt[0]);
+      const int pmode = (pkt[0] & 0x80) ? 1002 : ((pkt[0] & 0x60) == 0x60 ? 1001 : 1000);
+      if (cap_per_ch < per || pmode == 1002 || (tr && tr->mode == 1002)) { conceal(cap_per_ch, 0); continue; }
+      const int lead = cap_per_ch - per;
+      const int k = conceal(lead, 0);
+      if (tr) { tr->frame_size = per; tr->mode = pmode; }
+      emit(p, (uint8_t)(1u | (k ? VF_CONTINUATION : 0)), (uint32_t)(lead * CC), nullptr, (uint8_t)(pkt[0] & ~3u), pkt + F.off[0], F.len[0]);
       continue;
     }
     if (n == 0 || fl || !(pkt[0] & 3u)) {   // single frame / FEC request: as it is

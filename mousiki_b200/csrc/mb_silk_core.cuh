@@ -16,7 +16,14 @@ namespace mb {
 
 enum { SILK_RING = 1024, SILK_RING_MASK = SILK_RING - 1 };
 
+// Where a decoded frame's excitation can be rebuilt from while the pass lasts (mb_silk_plc.cuh): its pulses in the cell record
+struct SilkExcSrc { const uint32_t* pulse_words; int32_t seed; int16_t from, len; int8_t signal_type, quant_offset, valid; };  // seed: at sample `from`
+struct SilkCngPush { SilkExcSrc src; int16_t sub, nb; };
+
 struct SilkWork {
+  SilkExcSrc last_exc[2];      // per channel: the last decoded frame of the pass, its excitation not yet in HBM
+  SilkCngPush cng_pend[2][4];  // per channel: comfort-noise FIFO pushes not yet applied in HBM, oldest first
+  int cng_n[2];
   int16_t hist[2][SILK_RING];  // per channel output ring (history + running frame)
   int32_t sltp_q15[640];       // gain-normalised LTP state of the running frame (decode_core.rs s_ltp_q15)
   int16_t lr[2][322];          // stereo only: mid/side -> left/right staging (2 history samples + frame)
@@ -38,7 +45,10 @@ MB_DEV_NOINLINE void silk_frame_core(SilkChanState& st, const SilkSide& sd, Silk
   const int fs = st.fs_khz, nb = st.nb_subfr, sub = 5 * fs, ltp_mem = 20 * fs, order = fs == 16 ? 16 : 10;
   const int32_t offset_q10 = silk_Quantization_Offsets_Q10[(sd.signal_type >> 1) * 2 + sd.quant_offset];
   const bool interp = sd.interp_q2 < 4;
-  const bool voiced = sd.signal_type == SILK_T_VOICED;   // (the lost-frame voiced transition needs loss_count > 0)
+  const bool voiced = sd.signal_type == SILK_T_VOICED;
+  // first frame after a loss that ended a voiced stretch: its first two subframes keep a quarter-gain pitch predictor at
+  // the previous lag (decode_core.rs:140-152)
+  const bool trans = st.loss_count > 0 && st.prev_signal_type == SILK_T_VOICED && !voiced;
   int32_t seed = sd.seed;
   int32_t lpc[16];                   // synthesis history, lpc[j] = sLPC_Q14 of sample (i - 1 - j)
 #pragma unroll
@@ -46,6 +56,7 @@ MB_DEV_NOINLINE void silk_frame_core(SilkChanState& st, const SilkSide& sd, Silk
   int sltp_idx = ltp_mem;
   int32_t prev_gain = st.prev_gain_q16;
   for (int k = 0; k < nb; k++) {
+    P.seed_at[k] = seed;
     int32_t A[16];                   // short-term taps, pre-shifted for IMAD.HI; zero above the order
 #pragma unroll
     for (int j = 0; j < 16; j++) A[j] = j < order ? s_shl(P.a_q12[k >> 1][j], 16) : 0;
@@ -62,7 +73,9 @@ MB_DEV_NOINLINE void silk_frame_core(SilkChanState& st, const SilkSide& sd, Silk
     int32_t l0 = 0, l1 = 0, l2 = 0, l3 = 0, l4 = 0;          // sltp_q15[pl], [pl-1], .. [pl-4]
     int32_t lnext = 0;
     int pl = 0;
-    if (voiced) {
+    const bool vk = voiced || (trans && k < 2);
+    if (trans && k < 2) P.pitch_l[k] = st.lag_prev;
+    if (vk) {
       const int lag = P.pitch_l[k];
       if (k == 0 || (k == 2 && interp)) {
         // re-whitening: analysis filter over the last lag + 2 samples before subframe k (at k == 2 that includes the two
@@ -90,7 +103,8 @@ MB_DEV_NOINLINE void silk_frame_core(SilkChanState& st, const SilkSide& sd, Silk
       }
       pl = sltp_idx - lag + 2;
       const int16_t* B = P.b_q14 + 5 * k;
-      B0 = s_shl(B[0], 16); B1 = s_shl(B[1], 16); B2 = s_shl(B[2], 16); B3 = s_shl(B[3], 16); B4 = s_shl(B[4], 16);
+      if (voiced) { B0 = s_shl(B[0], 16); B1 = s_shl(B[1], 16); B2 = s_shl(B[2], 16); B3 = s_shl(B[3], 16); B4 = s_shl(B[4], 16); }
+      else B2 = s_shl(4096, 16);
       l0 = sltp_q15[pl]; l1 = sltp_q15[pl - 1]; l2 = sltp_q15[pl - 2]; l3 = sltp_q15[pl - 3]; l4 = sltp_q15[pl - 4];
       lnext = sltp_q15[pl + 1];   // one sample ahead of the window (written at least lag - 3 >= 13 samples ago)
     }
@@ -110,7 +124,7 @@ MB_DEV_NOINLINE void silk_frame_core(SilkChanState& st, const SilkSide& sd, Silk
         if (seed < 0) e = -e;
         seed = s_add(seed, pulse);
         int32_t res = e;
-        if (voiced) {
+        if (vk) {
           int32_t p = 2;
           p = s_add(p, s_mulhi(l0, B0)); p = s_add(p, s_mulhi(l1, B1)); p = s_add(p, s_mulhi(l2, B2));
           p = s_add(p, s_mulhi(l3, B3)); p = s_add(p, s_mulhi(l4, B4));

@@ -11,7 +11,7 @@
 // collected 32 at a time in a lane-private shared-memory row and leave as 128-bit stores (a full 128-byte line per
 // lane for mono float output).
 #pragma once
-#include "mb_silk_core.cuh"
+#include "mb_silk_plc.cuh"
 #include "mb_celt_energy.cuh"
 
 namespace mb {
@@ -49,6 +49,7 @@ struct SilkPcmOut {
 struct SilkSink {
   int32_t* stage;  // 32 words, lane-private (shared memory on the device)
   int fill, pos, ch, dup;   // pos: sample position (per channel) of stage[0]; dup: mono stream into a stereo row
+  int limit;                // samples per channel the row takes; what lies beyond is dropped
   const SilkPcmOut* o;
 };
 MB_DEV float silk_to_float(const SilkPcmOut& o, int32_t v, int pos) {
@@ -58,7 +59,7 @@ MB_DEV float silk_to_float(const SilkPcmOut& o, int32_t v, int pos) {
 }
 MB_DEV_NOINLINE void silk_sink_flush(SilkSink& s) {
   const SilkPcmOut& o = *s.o;
-  const int n = s.fill;
+  const int n = imin(s.fill, imax(s.limit - s.pos, 0));
   if (o.CC == 1 || s.dup) {
     const int rep = s.dup ? 2 : 1;
     if (o.f32) {
@@ -109,7 +110,7 @@ MB_DEV_NOINLINE void silk_sink_flush(SilkSink& s) {
     if (o.f32) for (int i = 0; i < n; i++) o.f32[(size_t)(s.pos + i) * 2 + s.ch] = silk_to_float(o, s.stage[i], s.pos + (i));
     else for (int i = 0; i < n; i++) o.i16[(size_t)(s.pos + i) * 2 + s.ch] = (int16_t)s.stage[i];
   }
-  s.pos += n; s.fill = 0;
+  s.pos += s.fill; s.fill = 0;
 }
 MB_DEV void silk_sink_put(SilkSink& s, int32_t v) {
   s.stage[s.fill++] = v;
@@ -233,12 +234,30 @@ MB_DEV void silk_hist_store(const SilkWork& W, const SilkHistRef& H, int n) {
                                  ((uint32_t)(uint16_t)W.hist[n][(p + 2 * k + 1) & SILK_RING_MASK] << 16);
 }
 
-// One SILK-only packet of one stream: silk_decode (dec_api.rs:132-441) once per 10/20 ms SILK frame in the packet.
-// stage: 32 lane-private words; fir: interpolation table; side_live: the side channel's ring holds its history.
-// Returns samples per channel written at 48 kHz.
+// What kind of packet the lane is looking at (the lost_flag of silk_decode, dec_api.rs:132-150)
+enum { SILK_PKT_NORMAL = 0, SILK_PKT_LOST = 1, SILK_PKT_FEC = 2 };
+struct SilkPacketCtl {
+  int mode;        // SILK_PKT_*
+  int samples48;   // lost packet: samples per channel to conceal at 48 kHz (120 .. 960); else unused
+  int limit;       // samples per channel the row takes (a concealed frame shorter than 10 ms still runs a 10 ms SILK frame)
+};
+// frame word 2 of a SILK record (SL_BASE + i * SL_FRAME_WORDS + 2): bit0 decode_only_middle, and for a packet decoded from
+// its LBRR data (FEC): bit1 mid-only flag not coded (the stream's previous one stands), bit2 stereo predictor not coded
+enum { SILK_FR_DOM = 1, SILK_FR_DOM_KEPT = 2, SILK_FR_PRED_KEPT = 4 };
+
+// One SILK packet of one stream: silk_decode (dec_api.rs:132-441) once per 10/20 ms SILK frame in the packet; a lost packet
+// (no record) is one concealed frame. stage: 32 lane-private words; fir: interpolation table; side_live: the side
+// channel's ring holds its history. Returns samples per channel produced at 48 kHz.
 // h0: the SILK header word; frames: the first frame record (SILK-only: slots S_HDR0 / SL_BASE, hybrid: S_SILK_HYB / + 1).
-MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const SilkHistRef& H, int& side_live, uint32_t h0, const uint32_t* frames,
-                                      uint32_t quirks, const SilkPcmOut& o, int32_t* stage, const int16_t* fir) {
+MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const SilkHistRef& H, const SilkExcRef& X, int& side_live, uint32_t h0,
+                                      const uint32_t* frames, uint32_t quirks, const SilkPcmOut& o, int32_t* stage, const int16_t* fir,
+                                      const SilkPacketCtl& ctl) {
+  const bool lost = ctl.mode == SILK_PKT_LOST, fec = ctl.mode == SILK_PKT_FEC;
+  if (lost) {   // the packet's geometry is the decoder's own (opus_decoder.rs:651-676): rate and channels of the last packet
+    const int fs0 = S.ch[0].fs_khz;
+    if (fs0 == 0) return 0;
+    h0 = (uint32_t)fs0 | ((ctl.samples48 >= 960 ? 4u : 2u) << 5) | (1u << 8) | ((uint32_t)S.n_channels_internal << 10);
+  }
   const int fs = (int)MB_SH_FS(h0), nb = (int)MB_SH_SUBFR(h0), n_frames = (int)MB_SH_FRAMES(h0), nci = (int)MB_SH_NCI(h0);
   const int CC = o.CC;
   const int L = 5 * fs * nb, ltp_mem = 20 * fs;
@@ -247,8 +266,8 @@ MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const SilkHistR
   for (int i = 0; i < n_frames; i++) {
     const uint32_t* fr = frames + (i * SL_FRAME_WORDS) * 32;
     if (nci > S.n_channels_internal) {                       // dec_api.rs:150-154
-      if (quirks & S4_STEREO_REINIT) { silk_chan_reset(S.ch[0]); silk_ring_clear(W.hist[0], W.pos[0]); }
-      silk_chan_reset(S.ch[1]); silk_ring_clear(W.hist[1], W.pos[1]);
+      if (quirks & S4_STEREO_REINIT) { silk_chan_reset(S.ch[0]); silk_ring_clear(W.hist[0], W.pos[0]); silk_work_drop(W, 0); }
+      silk_chan_reset(S.ch[1]); silk_ring_clear(W.hist[1], W.pos[1]); silk_work_drop(W, 1);
     }
     const bool stereo_to_mono = nci == 1 && S.n_channels_internal == 2 && fs == S.ch[0].fs_khz;
     for (int n = 0; n < nci; n++)
@@ -261,41 +280,74 @@ MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const SilkHistR
       S.ch[1].res_ready = 1;
     }
     S.n_channels_api = (int8_t)CC; S.n_channels_internal = (int8_t)nci;
-    const int32_t pred[2] = {(int32_t)fr[0], (int32_t)fr[32]};
-    const int dom = (int)fr[64];
+    // stereo predictor and mid-only flag: coded, or the stream's previous ones (lost frame; LBRR frame without them)
+    const uint32_t w2 = lost ? (uint32_t)(SILK_FR_DOM_KEPT | SILK_FR_PRED_KEPT) : fr[64];
+    int32_t pred[2];
+    if (w2 & SILK_FR_PRED_KEPT) { pred[0] = S.pred_prev_q13[0]; pred[1] = S.pred_prev_q13[1]; }
+    else { pred[0] = (int32_t)fr[0]; pred[1] = (int32_t)fr[32]; }
+    const int dom = nci == 2 ? ((w2 & SILK_FR_DOM_KEPT) ? (int)S.prev_decode_only_middle : (int)(w2 & SILK_FR_DOM)) : 0;
     if (nci == 2 && !dom && S.prev_decode_only_middle) {     // dec_api.rs:263-271
       SilkChanState& c = S.ch[1];
       silk_ring_clear(W.hist[1], W.pos[1]);
       for (int k = 0; k < 16; k++) c.s_lpc_q14[k] = 0;
       c.lag_prev = 100; c.last_gain_index = 10; c.prev_signal_type = 0; c.first_frame_after_reset = 1;
     }
+    int side_coded = 0;
+    if (fec && nci == 2) { SilkSide t; silk_side_load(t, fr + (3 + SL_CH_WORDS) * 32); side_coded = t.coded; }
+    // dec_api.rs:296-306
+    const bool has_side = lost ? !S.prev_decode_only_middle : (fec ? (!S.prev_decode_only_middle || side_coded) : !dom);
+    bool modified[2] = {false, false};   // the frame that leaves the channel differs from the one its history keeps: W.lr[n] + 2
     for (int n = 0; n < nci; n++) {
-      const uint32_t* chw = fr + (3 + n * SL_CH_WORDS) * 32;
       int16_t* h = W.hist[n];
       SilkChanState& c = S.ch[n];
       const int hp = W.pos[n];
-      if (n == 0 || !dom) {
+      if (n > 0 && !has_side) continue;    // side channel absent: the frame is zeros and the channel is left alone (dec_api.rs:318-321)
+      bool coded = false;
+      SilkFrameParams P;
+      if (!lost) {
+        const uint32_t* chw = fr + (3 + n * SL_CH_WORDS) * 32;
         SilkSide sd;
         silk_side_load(sd, chw);
-        SilkFrameParams P;
-        silk_frame_params(c, sd, P, quirks);
-        silk_frame_core(c, sd, P, chw + SL_IDX_WORDS * 32, h, hp, W.sltp_q15);
-        c.prev_signal_type = sd.signal_type;               // plc.rs:123
-        c.first_frame_after_reset = 0;
-        c.lag_prev = (int16_t)P.pitch_l[nb - 1];
-        W.pos[n] = (hp + L) & SILK_RING_MASK;              // decode_frame.rs:207-230: the history window slides by a frame
-      } else {
-        // side channel not coded: the frame is zeros and the history is left alone (dec_api.rs:318-321)
+        coded = sd.coded != 0;
+        if (coded) {
+          silk_frame_params(c, sd, P, quirks);
+          silk_frame_core(c, sd, P, chw + SL_IDX_WORDS * 32, h, hp, W.sltp_q15);
+          silk_plc_update(c, sd, P);                       // plc.rs:117-184 (prev_signal_type among the rest)
+          c.loss_count = 0;
+          c.first_frame_after_reset = 0;
+          c.lag_prev = (int16_t)P.pitch_l[nb - 1];
+          W.pos[n] = (hp + L) & SILK_RING_MASK;            // decode_frame.rs:207-230: the history window slides by a frame
+          {   // the frame's excitation: in the record until somebody needs it in HBM (silk_exc_flush)
+            SilkExcSrc& e = W.last_exc[n];
+            e.pulse_words = chw + SL_IDX_WORDS * 32; e.from = 0; e.len = (int16_t)L;
+            e.seed = sd.seed; e.signal_type = sd.signal_type; e.quant_offset = sd.quant_offset; e.valid = 1;
+          }
+          silk_cng_track(c, W, X, n, chw + SL_IDX_WORDS * 32, &sd, P.gains_q16, P.seed_at);
+          modified[n] = c.plc_last_frame_lost != 0;
+        }
+      }
+      if (!coded) {   // concealed frame (decode_frame.rs:140-151)
+        c.lag_prev = (int16_t)silk_plc_conceal(c, W, X, n, h, hp, W.sltp_q15);
+        W.pos[n] = (hp + L) & SILK_RING_MASK;
+        silk_cng_track(c, W, X, n, nullptr, nullptr, nullptr, nullptr);
+        modified[n] = true;
+      }
+      if (modified[n]) {
+        const int b = W.pos[n] + ltp_mem - L;
+        for (int k = 0; k < L; k++) W.lr[n][2 + k] = h[(b + k) & SILK_RING_MASK];
+        if (!coded) silk_cng_add(c, W, X, n, W.lr[n] + 2, W.sltp_q15, quirks);
+        silk_plc_glue(c, W.lr[n] + 2, L);
       }
     }
     SilkSink sink;
-    sink.stage = stage; sink.fill = 0; sink.o = &o; sink.dup = 0;
+    sink.stage = stage; sink.fill = 0; sink.o = &o; sink.dup = 0; sink.limit = ctl.limit;
     int n_out = 0;
     if (CC == 2 && nci == 2) {
       for (int n = 0; n < 2; n++) {
-        const bool coded = n == 0 || !dom;
+        if (modified[n]) continue;
+        const bool present = n == 0 || has_side;
         const int b = W.pos[n] + ltp_mem - L;              // first sample of the frame just written
-        for (int k = 0; k < L; k++) W.lr[n][2 + k] = coded ? W.hist[n][(b + k) & SILK_RING_MASK] : (int16_t)0;
+        for (int k = 0; k < L; k++) W.lr[n][2 + k] = present ? W.hist[n][(b + k) & SILK_RING_MASK] : (int16_t)0;
       }
       silk_ms_to_lr(S, W.lr[0], W.lr[1], pred, fs, L);
       for (int n = 0; n < 2; n++) {
@@ -308,7 +360,8 @@ MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const SilkHistR
       // mid only: one sample of delay through s_mid (dec_api.rs:341-347), read straight from the ring
       const int b = W.pos[0] + ltp_mem - L;
       SilkSrc src; src.p = W.hist[0]; src.base = b - 1; src.mask = SILK_RING_MASK; src.first = S.s_mid[1]; src.has_first = 1;
-      const int16_t m0 = W.hist[0][(b + L - 2) & SILK_RING_MASK], m1 = W.hist[0][(b + L - 1) & SILK_RING_MASK];
+      int16_t m0 = W.hist[0][(b + L - 2) & SILK_RING_MASK], m1 = W.hist[0][(b + L - 1) & SILK_RING_MASK];
+      if (modified[0]) { src.p = W.lr[0]; src.base = 1; src.mask = 0xffff; m0 = W.lr[0][L]; m1 = W.lr[0][L + 1]; }
       if (CC == 2 && stereo_to_mono) {
         sink.pos = pos; sink.ch = 0;
         n_out = silk_resample48(S.ch[0], src, L, fir, sink);
@@ -323,10 +376,70 @@ MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const SilkHistR
       }
       S.s_mid[0] = m0; S.s_mid[1] = m1;
     }
-    S.prev_decode_only_middle = (int8_t)dom;
+    if (lost) { for (int n = 0; n < nci; n++) S.ch[n].last_gain_index = 10; }   // dec_api.rs:430-436
+    else S.prev_decode_only_middle = (int8_t)dom;
     pos += n_out;
   }
   return pos;
+}
+
+// ---- the per-stream lane of k_silk: the stream's SILK-side cells in tick order -------------------------------------------
+struct SilkLaneParams {
+  uint32_t n_lanes, n_ticks;
+  const uint32_t* pkt_map; const uint32_t* lane_stream; const uint32_t* rec; const FrameMeta* meta;
+  SilkState* st_all; uint32_t* silk_hist; int32_t* silk_exc; uint32_t n_streams;
+  float* pcm_f32; int16_t* pcm_i16; uint32_t pcm_stride; int CC; uint32_t quirks; float gain; int apply_gain;
+  const uint32_t* out_map;
+};
+// W: the lane's working set (local memory on the device); stage: 32 lane-private words; fir: interpolation table.
+MB_DEV void silk_lane(const SilkLaneParams& q, uint32_t lane, SilkWork& W, int32_t* stage, const int16_t* fir) {
+  bool any = false;
+  for (uint32_t t = 0; t < q.n_ticks && !any; t++) any = (q.meta[t * q.n_lanes + lane].flags & 2u) != 0;
+  if (!any) return;
+  const uint32_t sid = q.lane_stream ? q.lane_stream[lane] : lane;
+  SilkState* gs = q.st_all + sid;
+  SilkState S = *gs;
+  SilkHistRef H = {q.silk_hist, q.n_streams, sid};
+  SilkExcRef X = {q.silk_exc, q.n_streams, sid};
+  int side_live = 0;
+  silk_hist_load(W, H, 0);
+  silk_work_drop(W, 0); silk_work_drop(W, 1);
+  for (uint32_t t = 0; t < q.n_ticks; t++) {
+    const uint32_t f = t * q.n_lanes + lane;
+    const uint32_t fl = q.meta[f].flags;
+    if (!(fl & 2u)) continue;
+    const uint32_t p = q.pkt_map ? q.pkt_map[f] : f;
+    const uint32_t* rb = q.rec + rec_index(f, 0);
+    const uint32_t status = rb[S_STATUS * 32];
+    const bool to_float = (fl & MB_FL_F32ROW) != 0;   // the packet goes through the float row (a CELT frame shares one of its rows, or a decode gain applies)
+    const bool shared = (fl & (8u | 16u)) != 0;       // a CELT frame shares THIS row (hybrid, fade-out, redundancy): k_deemph / k_fade finish it
+    const bool hyb_layout = ((status >> 17) & 3u) != 0;       // hybrid, or a one-frame SILK-only cell
+    if (fl & 32u) {   // CELT -> SILK: silk decoder reset (opus_decoder.rs:694-696)
+      silk_state_reset(S, 0);
+      silk_ring_clear(W.hist[0], W.pos[0]); silk_ring_clear(W.hist[1], W.pos[1]);
+      silk_work_drop(W, 0); silk_work_drop(W, 1);
+      side_live = 1;
+    }
+    SilkPcmOut o;
+    // SILK-only cells are final: int16 directly on the i16 path
+    o.f32 = (to_float || !q.pcm_i16) ? q.pcm_f32 + pcm_elem_off(q.out_map, p, q.pcm_stride) : nullptr;
+    o.i16 = (to_float || !q.pcm_i16) ? nullptr : q.pcm_i16 + pcm_elem_off(q.out_map, p, q.pcm_stride);
+    // decode gain: once on the finished sum. Hybrid: k_deemph does it for the whole row; fade-out: k_deemph for the first
+    // 120 samples, here for the rest; redundancy: k_fade for the whole row
+    const bool fadeout = (fl & 8u) && !((status >> 17) & 1u) && !MB_ST_LOST(status);
+    o.CC = q.CC; o.gain = q.gain; o.apply_gain = (shared && !fadeout) ? 0 : q.apply_gain; o.gain_from = fadeout ? SHORT_MDCT : 0;
+    SilkPacketCtl ctl;
+    ctl.mode = MB_ST_LOST(status) ? SILK_PKT_LOST : (MB_ST_FEC(status) ? SILK_PKT_FEC : SILK_PKT_NORMAL);
+    ctl.samples48 = ctl.mode == SILK_PKT_LOST ? (int)rb[S_RANGE * 32] : 0;
+    ctl.limit = ctl.mode == SILK_PKT_LOST ? ctl.samples48 : 0x7fffffff;
+    silk_synth_packet(S, W, H, X, side_live, rb[(hyb_layout ? S_SILK_HYB : S_HDR0) * 32], rb + (hyb_layout ? S_SILK_HYB + 1 : SL_BASE) * 32, q.quirks,
+                      o, stage, fir, ctl);
+  }
+  // the pass ends: what the next call may need of this one's records goes to HBM
+  for (int n = 0; n < 2; n++) { silk_exc_flush(S.ch[n], W, X, n); silk_cng_flush(S.ch[n], W, X, n); }
+  silk_hist_store(W, H, 0);
+  if (side_live) silk_hist_store(W, H, 1);
+  *gs = S;
 }
 
 }  // namespace mb

@@ -229,7 +229,11 @@ MB_DEV void silk_store_pulses(const int16_t* q, int frame_length, uint32_t* w /*
 
 // The SILK payload behind an open range decoder: flags, LBRR skip, and per frame the stereo predictor and each channel's
 // side information + pulses, stored from slot `frames` on (frame i at frames + i * SL_FRAME_WORDS * 32 words).
-MB_DEV_NOINLINE void silk_parse_payload(RangeDec& ec, int fs_khz, int nb_subfr, int n_frames, int nci, uint32_t quirks, uint32_t* frames) {
+// fec: the packet is decoded from its LBRR data (lost_flag == FLAG_DECODE_LBRR, dec_api.rs:200-330): the LBRR frames take the
+// place of the regular ones in the record, a frame / channel without one is left for the concealment (coded = 0), and the
+// regular frames are not read at all.
+MB_DEV_NOINLINE void silk_parse_payload(RangeDec& ec, int fs_khz, int nb_subfr, int n_frames, int nci, uint32_t quirks, uint32_t* frames,
+                                        int fec = 0) {
   const SilkRate R = silk_rate(fs_khz, nb_subfr);
   int vad[2][3], lbrr_flags[2][3], prev_type[2] = {0, 0}, prev_lag[2] = {0, 0};
   for (int n = 0; n < nci; n++) {                        // dec_api.rs:451-456
@@ -250,6 +254,35 @@ MB_DEV_NOINLINE void silk_parse_payload(RangeDec& ec, int fs_khz, int nb_subfr, 
   int16_t q[336];
   SilkSide side;
   int decode_only_middle = 0;
+  if (fec) {
+    for (int i = 0; i < n_frames; i++) {
+      uint32_t* fr = frames + (i * SL_FRAME_WORDS) * 32;
+      int32_t pred[2] = {0, 0};
+      uint32_t w2 = 0;
+      if (nci == 2) {
+        if (lbrr_flags[0][i]) {
+          silk_parse_stereo_pred(ec, pred);
+          w2 = lbrr_flags[1][i] == 0 ? (uint32_t)silk_icdf(ec, silk_stereo_only_code_mid_iCDF, 8) : 0u;
+        } else w2 = 2u | 4u;   // SILK_FR_DOM_KEPT | SILK_FR_PRED_KEPT (mb_silk_out.cuh)
+      }
+      fr[0] = (uint32_t)pred[0]; fr[32] = (uint32_t)pred[1]; fr[64] = w2;
+      for (int n = 0; n < nci; n++) {
+        uint32_t* chw = fr + (3 + n * SL_CH_WORDS) * 32;
+        if (lbrr_flags[n][i]) {
+          const int cond = (i > 0 && lbrr_flags[n][i - 1]) ? SILK_COND_COND : SILK_COND_INDEP;
+          silk_parse_indices(ec, R, 0, 1, cond, prev_type[n], prev_lag[n], side);
+          silk_parse_pulses(ec, q, side.signal_type, side.quant_offset, R.frame_length, quirks);
+          side.cond = (int8_t)cond; side.coded = 1;
+          silk_side_store(side, chw);
+          silk_store_pulses(q, R.frame_length, chw + SL_IDX_WORDS * 32);
+        } else {
+          side = SilkSide(); side.coded = 0;
+          silk_side_store(side, chw);
+        }
+      }
+    }
+    return;
+  }
   // LBRR payloads are decoded and dropped (dec_api.rs:476-529); they do move ec_prev_* of their channel
   for (int i = 0; i < n_frames; i++)
     for (int n = 0; n < nci; n++) {
@@ -304,7 +337,7 @@ MB_DEV_NOINLINE void silk_parse_payload(RangeDec& ec, int fs_khz, int nb_subfr, 
 // Status bit 18 = that layout. `red` receives the redundancy split (bytes == 0: none).
 struct SilkRedundancy { int celt_to_silk, cutoff, bytes; };
 MB_DEV_NOINLINE uint32_t silk_parse_frame(const uint8_t* data, int len, uint32_t toc, uint32_t quirks, int cap_per_ch, uint32_t* rec_base,
-                                          SilkRedundancy* red) {
+                                          SilkRedundancy* red, int fec = 0) {
   const int bw = (int)((toc >> 5) & 3u);                 // 0 NB, 1 MB, 2 WB (3 = SWB never appears in SILK-only configs 0..11)
   const int sc = (int)((toc >> 3) & 3u);                 // 10, 20, 40, 60 ms
   const int fs_khz = bw == 0 ? 8 : (bw == 1 ? 12 : 16);
@@ -317,11 +350,11 @@ MB_DEV_NOINLINE uint32_t silk_parse_frame(const uint8_t* data, int len, uint32_t
   const int hyb_layout = n_frames == 1;
   RangeDec ec;
   ec.open(data, (uint32_t)len);
-  silk_parse_payload(ec, fs_khz, nb_subfr, n_frames, nci, quirks, rec_base + (hyb_layout ? S_SILK_HYB + 1 : SL_BASE) * 32);
+  silk_parse_payload(ec, fs_khz, nb_subfr, n_frames, nci, quirks, rec_base + (hyb_layout ? S_SILK_HYB + 1 : SL_BASE) * 32, fec);
   // SILK-only redundancy (opus_decoder.rs:746-797): with at least 17 bits left the frame ends in a 5 ms CELT frame; one
   // bit tells which side of the mode switch it belongs to, its size is whatever the range coder has not used.
   int code = MB_OK;
-  if (ec.tell() + 17 <= 8 * len) {
+  if (!fec && ec.tell() + 17 <= 8 * len) {   // (a packet decoded from its LBRR data takes no redundancy frame, opus_decoder.rs:746)
     if (!hyb_layout) code = MB_UNIMPLEMENTED;            // 40 / 60 ms packets: the cell has no room for the CELT record
     else {
       red->celt_to_silk = ec.bit_logp(1);
@@ -335,7 +368,8 @@ MB_DEV_NOINLINE uint32_t silk_parse_frame(const uint8_t* data, int len, uint32_t
   rec_base[S_HDR0 * 32] = h0;
   rec_base[S_RANGE * 32] = ec.rng;
   if (hyb_layout) { rec_base[S_SILK_HYB * 32] = h0; rec_base[(S_SILK_HYB + 342) * 32] = ec.rng; }
-  const uint32_t status = (uint32_t)(uint8_t)(int8_t)code | (code == MB_OK ? (1u << 14) : 0u) | (1u << 16) | ((uint32_t)hyb_layout << 18);
+  const uint32_t status = (uint32_t)(uint8_t)(int8_t)code | (code == MB_OK ? (1u << 14) : 0u) | (1u << 16) | ((uint32_t)hyb_layout << 18) |
+                          (fec ? (1u << 30) : 0u);
   rec_base[S_STATUS * 32] = status;
   return status;
 }

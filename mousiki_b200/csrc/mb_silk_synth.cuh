@@ -10,8 +10,7 @@
 // The work is integer and strictly sequential in time inside one stream (LPC/LTP recursion, IIR resampler), so the
 // parallelism is the batch: a lane owns a stream, keeps the LTP history, the scaled LTP state and the resampler window
 // in local memory (lane-interleaved, so a warp's accesses at equal indices coalesce), the 16 LPC taps and the
-// synthesis history of the running subframe in registers. PLC / CNG are not built: with no lost frame they never
-// touch the output (plc.rs:46-88, cng.rs:145-233), only prev_signal_type of plc.rs:123 is carried.
+// synthesis history of the running subframe in registers. Concealment and comfort noise: mb_silk_plc.cuh.
 #pragma once
 #include "mb_silk_parse.cuh"
 
@@ -85,12 +84,38 @@ struct SilkChanState {
   int32_t prev_gain_q16;
   int16_t fs_khz, nb_subfr, frame_length, lag_prev;
   int8_t first_frame_after_reset, last_gain_index, prev_signal_type, res_ready;
+  // packet-loss concealment (PLC state: decoder_state.rs:23-95, plc.rs) and comfort noise (cng.rs:31-80). The two excitation
+  // buffers the reference keeps beside them (exc_Q14 of the last decoded frame, the CNG excitation FIFO) live in their own
+  // structure-of-arrays buffer in HBM, see SilkExcRef in mb_silk_plc.cuh.
+  int32_t loss_count;
+  int32_t plc_pitch_l_q8, plc_rand_seed, plc_conc_energy, plc_prev_gain_q16[2];
+  int16_t plc_ltp_coef_q14[5], plc_prev_lpc_q12[16], plc_rand_scale_q14, plc_prev_ltp_scale_q14;
+  int16_t plc_fs_khz, plc_nb_subfr, plc_subfr_length, plc_conc_energy_shift;
+  int32_t cng_synth_state[16], cng_smth_gain_q16, cng_rand_seed;
+  int16_t cng_smth_nlsf_q15[16], cng_fs_khz;
+  int8_t plc_last_frame_lost, exc_dirty;   // exc_dirty: the channel's excitation buffers in HBM must read as zero (cleared lazily)
 };
 struct SilkState {
   SilkChanState ch[2];
   int16_t pred_prev_q13[2], s_mid[2], s_side[2];
   int8_t n_channels_api, n_channels_internal, prev_decode_only_middle, pad;
 };
+MB_DEV void silk_plc_reset(SilkChanState& c, int frame_length) {   // decoder_state.rs:77-95 (fs_khz is the caller's)
+  c.plc_pitch_l_q8 = frame_length << 7; c.plc_rand_seed = 0; c.plc_conc_energy = 0; c.plc_prev_gain_q16[0] = c.plc_prev_gain_q16[1] = 65536;
+  for (int i = 0; i < 5; i++) c.plc_ltp_coef_q14[i] = 0;
+  for (int i = 0; i < 16; i++) c.plc_prev_lpc_q12[i] = 0;
+  c.plc_rand_scale_q14 = 0; c.plc_prev_ltp_scale_q14 = 0; c.plc_nb_subfr = 2; c.plc_subfr_length = 20; c.plc_conc_energy_shift = 0;
+  c.plc_last_frame_lost = 0;
+}
+MB_DEV void silk_cng_reset(SilkChanState& c, int order) {        // cng.rs:62-80 (the excitation FIFO is left alone)
+  const int32_t step = 32767 / (order + 1);
+  int32_t acc = 0;
+  for (int i = 0; i < 16; i++) {
+    if (i < order) { acc += step; c.cng_smth_nlsf_q15[i] = (int16_t)acc; } else c.cng_smth_nlsf_q15[i] = 0;
+    c.cng_synth_state[i] = 0;
+  }
+  c.cng_smth_gain_q16 = 0; c.cng_rand_seed = 3176576;
+}
 MB_DEV void silk_chan_reset(SilkChanState& c) {   // init_decoder.rs:14-26 + DecoderState::default
   for (int i = 0; i < 16; i++) { c.s_lpc_q14[i] = 0; c.prev_nlsf_q15[i] = 0; c.res_delay[i] = 0; }
   for (int i = 0; i < 6; i++) c.res_iir[i] = 0;
@@ -98,6 +123,12 @@ MB_DEV void silk_chan_reset(SilkChanState& c) {   // init_decoder.rs:14-26 + Dec
   c.prev_gain_q16 = 65536;
   c.fs_khz = 0; c.nb_subfr = 4; c.frame_length = 0; c.lag_prev = 0;
   c.first_frame_after_reset = 1; c.last_gain_index = 0; c.prev_signal_type = 0; c.res_ready = 0;
+  c.loss_count = 0;
+  silk_plc_reset(c, 0);
+  c.plc_fs_khz = 0;
+  silk_cng_reset(c, 16);
+  c.cng_fs_khz = -1;
+  c.exc_dirty = 1;
 }
 MB_DEV void silk_state_reset(SilkState& s, int init) {   // dec_api.rs:102-123
   silk_chan_reset(s.ch[0]); silk_chan_reset(s.ch[1]);
@@ -180,6 +211,16 @@ MB_DEV void silk_bwexpander32(int32_t* ar, int d, int32_t chirp) {
     chirp = s_add(chirp, (int32_t)s_rr64((int64_t)chirp * cm1, 16));
   }
   ar[d - 1] = s_mulww(chirp, ar[d - 1]);
+}
+
+// bwexpander.rs:11-27 (16-bit coefficients)
+MB_DEV void silk_bwexpander16(int16_t* ar, int d, int32_t chirp) {
+  const int32_t cm1 = s_sub(chirp, 1 << 16);
+  for (int i = 0; i < d - 1; i++) {
+    ar[i] = (int16_t)s_rr64((int64_t)chirp * ar[i], 16);
+    chirp = s_add(chirp, (int32_t)s_rr64((int64_t)chirp * cm1, 16));
+  }
+  ar[d - 1] = (int16_t)s_rr64((int64_t)chirp * ar[d - 1], 16);
 }
 
 // lpc_inv_pred_gain.rs:22-104
@@ -278,6 +319,7 @@ struct SilkFrameParams {     // decoder_control.rs
   int32_t gains_q16[4], pitch_l[4];
   int16_t a_q12[2][16], b_q14[20];
   int32_t ltp_scale_q14;
+  int32_t seed_at[4];        // excitation generator state at the start of each subframe (written by the synthesis core)
 };
 
 // decode_parameters.rs:79-199
@@ -314,7 +356,7 @@ MB_DEV_NOINLINE void silk_frame_params(SilkChanState& st, SilkSide& sd, SilkFram
     for (int i = 0; i < order; i++) P.a_q12[0][i] = P.a_q12[1][i];
   }
   for (int i = 0; i < 16; i++) st.prev_nlsf_q15[i] = i < order ? nlsf[i] : 0;
-  // (bandwidth expansion after a loss, decode_parameters.rs:156-160: loss_count is always 0 without PLC)
+  if (st.loss_count > 0) { silk_bwexpander16(P.a_q12[0], order, 63570); silk_bwexpander16(P.a_q12[1], order, 63570); }   // decode_parameters.rs:156-160
   for (int k = 0; k < 4; k++) P.pitch_l[k] = 0;
   for (int k = 0; k < 20; k++) P.b_q14[k] = 0;
   P.ltp_scale_q14 = 0;

@@ -100,38 +100,20 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   tp.series = series.data(); tp.series_stride = series_stride; tp.n_lanes = n_lanes; tp.n_ticks = n_ticks; tp.CC = CC;
   tp.gain = g_gain_q8 == 0 ? 1.f : (float)exp(0.6931471805599453094 * (double)((3.32192809488736234787f / 5120.0f) * (float)g_gain_q8));
   tp.apply_gain = g_gain_q8 != 0; tp.pcm_f32 = out; tp.pcm_stride = pcm_stride; tp.xbuf = xbuf.data();
-  // SILK-only packets (k_silk): lane per stream, ticks in order
+  // SILK-side cells (k_silk): lane per stream, ticks in order
   {
     std::vector<SilkState> sst(n_lanes);
+    std::vector<uint32_t> shist((size_t)n_lanes * 320, 0);
+    std::vector<int32_t> sexc((size_t)n_lanes * 1280, 0x5a5a5a5a);   // (garbage: the lanes clear what they use)
+    for (auto& x : sst) silk_state_reset(x, 1);
     SilkWork* W = new SilkWork;
-    for (uint32_t j = 0; j < n_lanes; j++) {
-      silk_state_reset(sst[j], 1);
-      std::vector<uint32_t> hist(320, 0);
-      SilkHistRef H = {hist.data(), 1, 0};
-      int side_live = 0;
-      silk_hist_load(*W, H, 0);
-      int32_t stage[32];
-      for (uint32_t t = 0; t < n_ticks; t++) {
-        const uint32_t f = t * n_lanes + j;
-        if (!(meta[f].flags & 2u)) continue;
-        const bool hybrid = (meta[f].flags & MB_FL_F32ROW) != 0;   // the packet goes through the float row
-        const bool shared = (meta[f].flags & (8u | 16u)) != 0;     // a CELT frame shares this row
-        if (meta[f].flags & 32u) {
-          silk_state_reset(sst[j], 0);
-          silk_ring_clear(W->hist[0], W->pos[0]); silk_ring_clear(W->hist[1], W->pos[1]);
-          side_live = 1;
-        }
-        const uint32_t* rb = rec.data() + rec_index(f, 0);
-        const bool hyb_layout = ((rb[S_STATUS * 32] >> 17) & 3u) != 0;   // hybrid, or SILK-only with the CELT fade-out record
-        SilkPcmOut o;
-        o.f32 = (hybrid || !pcm16) ? out + (size_t)f * pcm_stride : nullptr;
-        o.i16 = (hybrid || !pcm16) ? nullptr : pcm16 + (size_t)f * pcm_stride;
-        const bool fadeout = (meta[f].flags & 8u) && !((rb[S_STATUS * 32] >> 17) & 1u);
-        o.CC = CC; o.gain = tp.gain; o.apply_gain = (shared && !fadeout) ? 0 : tp.apply_gain; o.gain_from = fadeout ? SHORT_MDCT : 0;
-        silk_synth_packet(sst[j], *W, H, side_live, rb[(hyb_layout ? S_SILK_HYB : S_HDR0) * 32], rb + (hyb_layout ? S_SILK_HYB + 1 : SL_BASE) * 32,
-                          quirks, o, stage, silk_resampler_frac_FIR_12);
-      }
-    }
+    SilkLaneParams sq;
+    sq.n_lanes = n_lanes; sq.n_ticks = n_ticks; sq.pkt_map = nullptr; sq.lane_stream = nullptr; sq.rec = rec.data(); sq.meta = meta.data();
+    sq.st_all = sst.data(); sq.silk_hist = shist.data(); sq.silk_exc = sexc.data(); sq.n_streams = n_lanes;
+    sq.pcm_f32 = out; sq.pcm_i16 = pcm16; sq.pcm_stride = pcm_stride; sq.CC = CC; sq.quirks = quirks; sq.gain = tp.gain; sq.apply_gain = tp.apply_gain;
+    sq.out_map = nullptr;
+    int32_t stage[32];
+    for (uint32_t j = 0; j < n_lanes; j++) silk_lane(sq, j, *W, stage, silk_resampler_frac_FIR_12);
     delete W;
   }
   CombSmem* csm = new CombSmem;
@@ -150,8 +132,9 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
       for (uint32_t t = 0; t < n_ticks; t++) {
         uint32_t p = t * n_lanes + j;
         if (samples_out[p] <= 0 || !(meta[p].flags & (3u | MB_FL_PLC))) continue;
-        if (g_flags && (g_flags[p] & 2u)) {   // a lost packet is not soft-clipped and clears the clipper's memory
+        if (g_flags && (g_flags[p] & 3u)) {   // a lost packet (or one rebuilt from FEC data) is not soft-clipped and clears the clipper's memory
           st[j].softclip_mem[0] = st[j].softclip_mem[1] = 0.f;
+          if (!(meta[p].flags & MB_FL_F32ROW)) continue;   // int16 straight from the SILK lane
           for (int i = 0; i < samples_out[p] * CC; i++) pcm16[(size_t)p * pcm_stride + i] = float2int16(out[(size_t)p * pcm_stride + i]);
           continue;
         }
@@ -211,11 +194,13 @@ int emu_op_histogram(int CC, uint32_t quirks, const uint8_t* arena, const uint32
 
 // ---- the host front end for multi-frame packets (mb_host_packets.h), exposed for the CPU tests
 static mbh::Split g_split;
+static std::vector<mbh::StreamTrack> g_track;   // per-stream memory of the front end (frame size / mode of the last packet)
+void emu_split_set_streams(uint32_t n_streams) { g_track.assign(n_streams, mbh::StreamTrack()); }
 
 // Cuts the batch into frames; returns the number of virtual packets, *arena_bytes = size of the virtual arena.
 uint32_t emu_split_batch(const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, const uint8_t* flags, uint32_t n_packets,
                          int cap_per_ch, int CC, uint32_t* arena_bytes) {
-  mbh::split_batch(arena, offsets, stream_ids, flags, n_packets, cap_per_ch, CC, &g_split);
+  mbh::split_batch(arena, offsets, stream_ids, flags, n_packets, cap_per_ch, CC, &g_split, g_track.empty() ? nullptr : g_track.data());
   *arena_bytes = (uint32_t)g_split.arena.size();
   return (uint32_t)g_split.stream_ids.size();
 }
