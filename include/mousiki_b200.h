@@ -28,6 +28,7 @@ extern "C" {
 #define BD_ERR_CUDA (-100)         /* no usable device / kernel launch or copy failed (see bd_last_error) */
 #define BD_ERR_ALLOC (-101)
 #define BD_ERR_UNIMPLEMENTED (-5)
+#define BD_ERR_TOO_LARGE (-102)    /* bd_parse_noalloc: more packets than its static scratch holds */
 
 /* per-packet codes written to samples_out[] when negative (OpusDecodeError::code, src/opus_decoder.rs:275-286) */
 #define BD_OPUS_BAD_ARG (-1)
@@ -149,6 +150,22 @@ int bd_debug_capture(bd_handle* h, int32_t* pulses_host, float* spectrum_host, u
  * src/celt/bands.rs:4805-4915, cwrs.rs:681-786, celt.rs:868-1190, kiss_fft.rs:1364-1440, mdct.rs:1746-1843,
  * entdec.rs:327-377, src/range.rs:659-695, rate.rs:1424-1465. Host word buffers in and out. */
 int bd_debug_kat(int device, int what, const uint32_t* in, uint32_t n_in, uint32_t* out, uint32_t n_out);
+
+/* Allocation-free entry point. No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Runs the entropy-parse kernel (phase 1: TOC, range decoder over the whole CELT frame) on n_packets stand-alone CELT-only
+ * single-frame packets, each taken as the first packet of a fresh decoder of `channels` channels, and reports what that kernel
+ * alone determines: samples_out[p] = samples per channel the packet decodes to at 48 kHz (or the negative Opus code bd_decode_*
+ * would report; packets of other modes / frame counts: BD_OPUS_UNIMPLEMENTED) and final_range_out[p] = the decoder's final_range
+ * after the packet (0 where bd_decode_* reports 0). d_arena / d_offsets (n_packets + 1) / d_samples_out / d_final_range_out are
+ * DEVICE pointers owned by the caller; frame_size = the caller's PCM capacity per channel (the reference's `frame_size`);
+ * cuda_stream = a cudaStream_t or NULL. The kernel is enqueued on that stream; the call does not synchronise, allocates nothing
+ * and frees nothing. Its record scratch (about 24 KB per packet) is a file-scope device array of BD_NOALLOC_MAX_PACKETS records
+ * (12.2 MB, held by every GPU that loads the library until the process exits); more packets: BD_ERR_TOO_LARGE. All calls on a
+ * GPU share that array: calls that overlap on the GPU (different streams, or graph launches in flight together) race. */
+#define BD_NOALLOC_MAX_PACKETS 512u
+int bd_parse_noalloc(int device, const uint8_t* d_arena, const uint32_t* d_offsets, uint32_t n_packets, int channels, uint32_t quirks,
+                     int frame_size, int32_t* d_samples_out, uint32_t* d_final_range_out, void* cuda_stream);
 
 #ifdef __cplusplus
 }

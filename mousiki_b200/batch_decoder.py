@@ -28,7 +28,7 @@ EXPORTS = [
     "bd_create", "bd_destroy", "bd_reset_streams", "bd_last_error", "bd_decode_f32", "bd_decode_i16", "bd_decode_grid_dev",
     "bd_get_stream_info", "bd_alloc_pinned", "bd_free_pinned", "bd_last_launch_count", "bd_debug_capture", "bd_profile_enable", "bd_profile_read",
     "bd_packet_get_mode", "bd_packet_get_bandwidth", "bd_packet_get_nb_channels", "bd_packet_get_samples_per_frame", "bd_packet_get_nb_frames",
-    "bd_packet_get_nb_samples", "bd_debug_kat", "bd_decode_i24",
+    "bd_packet_get_nb_samples", "bd_debug_kat", "bd_decode_i24", "bd_parse_noalloc",
 ]
 
 

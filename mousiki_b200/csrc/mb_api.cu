@@ -17,6 +17,7 @@
 #include <stdlib.h>
 
 #include <new>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1273,3 +1274,63 @@ int bd_decode_i16(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, c
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------ allocation-free entry point
+// bd_parse_noalloc: the entropy-parse kernel (phase 1) over a small batch with its record scratch in a file-scope device array
+// instead of the handle's cudaMalloc'ed buffers, for callers that cannot allocate (CUDA graph capture, tight serving loops).
+// No counterpart in the reference. The array is shared by every call on the GPU
+// and keeps the last call's contents: nothing in it has to start at zero (a lane only reads back the words its own parse has just
+// written), and calls that overlap on one GPU race on it.
+static __device__ __align__(256) uint32_t g_noalloc_rec[(size_t)(BD_NOALLOC_MAX_PACKETS / 32) * REC_SLOTS * 32];   // 12.2 MB
+
+// k_parse for stand-alone packets (every packet its own fresh stream), then the per-packet results straight from the record
+__global__ void __launch_bounds__(128, 7) k_parse_noalloc(const uint8_t* __restrict__ arena, const uint32_t* __restrict__ offsets,
+                                                        uint32_t n_packets, uint32_t* rec, int CC, uint32_t quirks, int disable_inv,
+                                                        int cap_per_ch, int32_t* __restrict__ samples_out,
+                                                        uint32_t* __restrict__ final_range_out) {
+  const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= n_packets) return;
+  uint32_t* r = rec + rec_index(f, 0);
+  int32_t samples = MB_UNIMPLEMENTED;
+  uint32_t range = 0;
+  const uint32_t off = offsets[f], len = offsets[f + 1] - off;
+  if (len >= 1 && (arena[off] & 0x80u) && !(arena[off] & 3u)) {   // CELT-only, one frame: final_range is the parse's alone
+    parse_cell(arena, offsets, f, r, CC, quirks, disable_inv, cap_per_ch, nullptr);
+    const uint32_t status = r[S_STATUS * 32];
+    const int code = MB_ST_CODE(status);
+    if (MB_ST_LOST(status)) samples = (int32_t)r[S_RANGE * 32];   // frame of at most one byte: concealed, no range
+    else if (!MB_ST_DECODED(status) || code < 0) samples = code;
+    else { samples = SHORT_MDCT << (int)MB_H0_LM(r[S_HDR0 * 32]); range = r[S_RANGE * 32]; }
+  }
+  samples_out[f] = samples;
+  final_range_out[f] = range;
+}
+
+namespace {
+std::mutex g_noalloc_mu;
+uint32_t* g_noalloc_ptr[64] = {nullptr};   // per device: address of g_noalloc_rec on that device
+}  // namespace
+
+extern "C" int bd_parse_noalloc(int device, const uint8_t* d_arena, const uint32_t* d_offsets, uint32_t n_packets, int channels,
+                                uint32_t quirks, int frame_size, int32_t* d_samples_out, uint32_t* d_final_range_out, void* cuda_stream) {
+  if (device < 0 || device >= 64 || !d_arena || !d_offsets || !d_samples_out || !d_final_range_out) return BD_ERR_BAD_ARG;
+  if (channels != 1 && channels != 2) return BD_ERR_BAD_ARG;
+  if (n_packets > BD_NOALLOC_MAX_PACKETS) return BD_ERR_TOO_LARGE;   // beyond the static scratch: split the batch
+  if (n_packets == 0) return BD_OK;
+  if (cudaSetDevice(device) != cudaSuccess) return BD_ERR_CUDA;
+  uint32_t* rec = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+      // in host code `g_noalloc_rec` is only a handle of the symbol: the device address comes from the runtime, per device
+      void* p = nullptr;
+      if (cudaGetSymbolAddress(&p, g_noalloc_rec) != cudaSuccess || !p) return BD_ERR_CUDA;
+      g_noalloc_ptr[device] = (uint32_t*)p;
+    }
+    rec = g_noalloc_ptr[device];
+  }
+  k_parse_noalloc<<<(n_packets + 127) / 128, 128, 0, (cudaStream_t)cuda_stream>>>(d_arena, d_offsets, n_packets, rec, channels, quirks,
+                                                                                channels == 1, frame_size, d_samples_out,
+                                                                                d_final_range_out);
+  return cudaGetLastError() == cudaSuccess ? BD_OK : BD_ERR_CUDA;
+}
