@@ -49,18 +49,24 @@ __global__ void __launch_bounds__(128, 7) k_parse(const uint8_t* __restrict__ ar
 
 // one warp per stream, 4 streams per CTA
 constexpr int ENERGY_WARPS = 4;
-__global__ void __launch_bounds__(32 * ENERGY_WARPS) k_energy(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
-                                               uint32_t* rec, StreamState* st, const uint32_t* __restrict__ lane_stream,
-                                               float* __restrict__ en, FrameMeta* __restrict__ meta, int32_t* __restrict__ samples_out,
-                                               uint32_t* __restrict__ final_range_out, uint32_t quirks,
-                                               const uint8_t* __restrict__ flags, int serial_all, int force_float_row, int CC) {
+__global__ void __launch_bounds__(32 * ENERGY_WARPS) k_energy(EnergyParams Q) {
   __shared__ EnergySmem sm[ENERGY_WARPS];
   const uint32_t lane = blockIdx.x * ENERGY_WARPS + (threadIdx.x >> 5);
-  if (lane >= n_lanes) return;
+  if (lane >= Q.n_lanes) return;
   Team tm = {(int)(threadIdx.x & 31), 32};
-  celt_energy_stream(tm, &sm[threadIdx.x >> 5], lane, n_lanes, n_ticks, pkt_map, rec, st, lane_stream, en, meta, samples_out, final_range_out,
-                     quirks, flags, serial_all, force_float_row, CC);
+  celt_energy_stream(tm, &sm[threadIdx.x >> 5], lane, Q);
 }
+
+// The auxiliary cells of the pass (mb_common.cuh): unused ones must look empty to every per-cell kernel.
+__global__ void k_aux_clear(uint32_t* rec, FrameMeta* meta, AuxPool A) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) *A.count = 0;
+  if (i >= A.cap) return;
+  rec[rec_index(A.base + i, S_STATUS)] = 1u << 15;
+  meta[A.base + i].flags = 0;
+}
+// Cell of the u-th thread / warp of a per-cell launch: the pass's main cells, then the auxiliary pool.
+__device__ __forceinline__ uint32_t launch_cell(uint32_t u, uint32_t n_main, uint32_t aux_base) { return u < n_main ? u : aux_base + (u - n_main); }
 
 constexpr int PVQ_THREADS = 64;
 // One CTA per PVQ_CELLS consecutive cells: the first lanes read their status words (one 32-byte sector) and the CTA then
@@ -68,15 +74,15 @@ constexpr int PVQ_THREADS = 64;
 // (the kernel runs beside k_silk, whose long-lived CTAs should not have to compete with a million empty ones); a longer
 // walk per CTA costs CELT throughput (per 5e5 frames, beside k_energy: 32 cells 9.7 ms, 8 cells 8.3 ms, 1 cell 7.9 ms).
 constexpr uint32_t PVQ_CELLS = 8;
-__global__ void __launch_bounds__(PVQ_THREADS) k_pvq(PvqParams P, uint32_t n_cells) {
+__global__ void __launch_bounds__(PVQ_THREADS) k_pvq(PvqParams P, uint32_t n_cells, uint32_t n_main, uint32_t aux_base) {
   __shared__ float X[2 * MAX_N];
   __shared__ uint32_t live_s;
   Team tm = {(int)threadIdx.x, (int)blockDim.x};
   const uint32_t base = blockIdx.x * PVQ_CELLS;
   if (threadIdx.x < 32) {
-    const uint32_t f = base + threadIdx.x;
+    const uint32_t f = launch_cell(base + threadIdx.x, n_main, aux_base);
     bool live = false;
-    if (threadIdx.x < PVQ_CELLS && f < n_cells) {
+    if (threadIdx.x < PVQ_CELLS && base + threadIdx.x < n_cells) {
       if (P.meta) live = (P.meta[f].flags & 1u) != 0;
       else {
         const uint32_t status = P.rec[rec_index(f, S_STATUS)];
@@ -91,44 +97,46 @@ __global__ void __launch_bounds__(PVQ_THREADS) k_pvq(PvqParams P, uint32_t n_cel
   while (m) {
     const int i = __ffs(m) - 1;
     m &= m - 1;
-    celt_pvq_frame(tm, X, base + (uint32_t)i, P);
+    celt_pvq_frame(tm, X, launch_cell(base + (uint32_t)i, n_main, aux_base), P);
     __syncthreads();
   }
 }
 
-__global__ void __launch_bounds__(128, 8) k_plan(PlanParams P, uint32_t n_cells) {
+__global__ void __launch_bounds__(128, 8) k_plan(PlanParams P, uint32_t n_cells, uint32_t n_main, uint32_t aux_base) {
   uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
   if (f >= n_cells) return;
-  celt_plan_frame(f, P);
+  celt_plan_frame(launch_cell(f, n_main, aux_base), P);
 }
 
 // one warp per frame; 4 frames per CTA
 constexpr int BANDS_WARPS = 4;
-__global__ void __launch_bounds__(32 * BANDS_WARPS, 6) k_bands(BandsParams P, uint32_t n_cells) {
+__global__ void __launch_bounds__(32 * BANDS_WARPS, 6) k_bands(BandsParams P, uint32_t n_cells, uint32_t n_main, uint32_t aux_base) {
   __shared__ BandsSmem sm[BANDS_WARPS];
   const uint32_t f = blockIdx.x * BANDS_WARPS + (threadIdx.x >> 5);
   if (f >= n_cells) return;
   Team tm = {(int)(threadIdx.x & 31), 32};
-  celt_bands_frame(tm, &sm[threadIdx.x >> 5], f, P);
+  celt_bands_frame(tm, &sm[threadIdx.x >> 5], launch_cell(f, n_main, aux_base), P);
 }
 
 // Hybrid frames: one warp per lane, the lane's ticks in order, because the reference's fold buffer outlives the frame
 // (mb_celt_bands.cuh); `fold` is [stream][FOLD_WORDS].  Lanes without a hybrid frame leave after one pass over the flags.
-__global__ void __launch_bounds__(32 * BANDS_WARPS, 6) k_bands_hyb(BandsParams P, uint32_t n_lanes, uint32_t n_ticks,
+__global__ void __launch_bounds__(32 * BANDS_WARPS, 6) k_bands_hyb(BandsParams P, uint32_t n_lanes, const uint32_t* __restrict__ order,
+                                                                 const uint32_t* __restrict__ order_n,
                                                                  const uint32_t* __restrict__ lane_stream, float* fold) {
   __shared__ BandsSmem sm[BANDS_WARPS];
   const uint32_t lane = blockIdx.x * BANDS_WARPS + (threadIdx.x >> 5);
   if (lane >= n_lanes) return;
   Team tm = {(int)(threadIdx.x & 31), 32};
   uint32_t any = 0;
-  for (uint32_t t = tm.tid; t < n_ticks; t += 32) any |= P.meta[(size_t)t * n_lanes + lane].flags & MB_FL_FOLD;
+  const uint32_t n_frames = order_n[lane];
+  for (uint32_t k = tm.tid; k < n_frames; k += 32) any |= P.meta[order[(size_t)k * n_lanes + lane]].flags & MB_FL_FOLD;
   if (!__any_sync(0xffffffffu, any != 0)) return;
   float* fb = fold + (size_t)(lane_stream ? lane_stream[lane] : lane) * FOLD_WORDS;
   BandsSmem* my = &sm[threadIdx.x >> 5];
   for (int w = tm.tid; w < (int)FOLD_WORDS; w += 32) my->norm[w] = fb[w];
   __syncwarp();
-  for (uint32_t t = 0; t < n_ticks; t++) {
-    const uint32_t f = t * n_lanes + lane;
+  for (uint32_t k = 0; k < n_frames; k++) {
+    const uint32_t f = order[(size_t)k * n_lanes + lane];
     if (P.meta[f].flags & MB_FL_FOLD) celt_bands_frame(tm, my, f, P, true);
   }
   __syncwarp();
@@ -137,13 +145,13 @@ __global__ void __launch_bounds__(32 * BANDS_WARPS, 6) k_bands_hyb(BandsParams P
 
 // one warp per (frame, channel); 4 units per CTA
 constexpr int IMDCT_WARPS = 4;
-__global__ void __launch_bounds__(32 * IMDCT_WARPS) k_imdct(ImdctParams P, uint32_t n_units) {
+__global__ void __launch_bounds__(32 * IMDCT_WARPS) k_imdct(ImdctParams P, uint32_t n_units, uint32_t n_main, uint32_t aux_base) {
   __shared__ ImdctSmem sm[IMDCT_WARPS];
   const uint32_t unit = blockIdx.x * IMDCT_WARPS + (threadIdx.x >> 5);
   if (unit >= n_units) return;
   Team tm = {(int)(threadIdx.x & 31), 32};
   const uint32_t nu = (uint32_t)P.CC;
-  celt_imdct_unit(tm, &sm[threadIdx.x >> 5], unit / nu, (int)(unit % nu), P);
+  celt_imdct_unit(tm, &sm[threadIdx.x >> 5], launch_cell(unit / nu, n_main, aux_base), (int)(unit % nu), P);
 }
 
 // phase 2c(i): one warp per stream-channel, 4 per CTA
@@ -215,25 +223,29 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
     cp_async_commit();
   };
 
-  for (uint32_t t = 0; t < P.n_ticks; t++) {
-    int N = 0, hyb = 0, side = 0;
+  const uint32_t my_frames = live ? P.order_n[lane] : 0u;
+  const uint32_t max_frames = __reduce_max_sync(0xffffffffu, my_frames);
+  for (uint32_t k = 0; k < max_frames; k++) {
+    int N = 0, hyb = 0, side = 0, late_gain = 0;
     const float* x = nullptr;
     float* out = nullptr;
-    if (live) {
-      const uint32_t f = t * P.n_lanes + lane;
+    if (k < my_frames) {
+      const uint32_t f = P.order[(size_t)k * P.n_lanes + lane];
       const FrameMeta m = P.meta[f];
-      if (m.flags & 1u) {
-        N = SHORT_MDCT << (int)MB_H0_LM(P.rec[rec_index(f, S_HDR0)]);
-        x = ser + m.sample_off;
+      N = SHORT_MDCT << (int)MB_H0_LM(P.rec[rec_index(f, S_HDR0)]);
+      x = ser + m.sample_off;
+      if (m.flags & 16u) { out = side_row(P.xbuf, f); side = 1; }   // not the packet's audio: kept aside for k_fade
+      else {
         const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
         out = P.pcm_f32 ? P.pcm_f32 + pcm_elem_off(P.out_map, p, P.pcm_stride) : nullptr;
-        if (m.flags & 4u) d.mem = 0.f;                 // CELT reset before this frame
-        if ((m.flags & 8u) && out) hyb = 1;            // hybrid: add to the SILK samples already in the row
-        if (m.flags & 16u) { out = P.xbuf + (size_t)f * XBUF_STRIDE; side = 1; }   // redundancy frame: kept aside for k_fade
       }
+      if (m.flags & 4u) d.mem = 0.f;                 // CELT reset before this frame
+      if ((m.flags & 8u) && out) hyb = 1;            // hybrid: add to the SILK samples already in the row
+      late_gain = side || (m.flags & (64u | 128u));  // a row that waits for a cross-fade gets its gain there
     }
     const unsigned hyb_mask = __ballot_sync(0xffffffffu, hyb);
-    d.apply_gain = (hyb || side) ? 0 : P.apply_gain;   // hybrid: the gain applies to SILK + CELT, at the store below
+    const unsigned late_mask = __ballot_sync(0xffffffffu, late_gain);
+    d.apply_gain = (hyb || late_gain) ? 0 : P.apply_gain;   // hybrid: the gain applies to SILK + CELT, at the store below
     __syncwarp();
     row_x[l] = x; row_out[l] = out; row_n[l] = N;
     const int max_n = __reduce_max_sync(0xffffffffu, N);
@@ -268,7 +280,7 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
           if ((hyb_mask >> r) & 1u) {
             for (int e = l; e < 2 * cnt; e += 32) {
               float v = o[e] + ((e & 1) ? ty[e >> 1] : tx[e >> 1]);
-              if (P.apply_gain) v *= P.gain;
+              if (P.apply_gain && !((late_mask >> r) & 1u)) v *= P.gain;
               o[e] = v;
             }
           } else if (((uintptr_t)o & 15u) == 0) {
@@ -290,7 +302,7 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
           if ((hyb_mask >> r) & 1u) {
             for (int j = l; j < cnt; j += 32) {
               float v = o[k0 + j] + tx[j];
-              if (P.apply_gain) v *= P.gain;
+              if (P.apply_gain && !((late_mask >> r) & 1u)) v *= P.gain;
               o[k0 + j] = v;
             }
           } else
@@ -600,7 +612,7 @@ struct bd_handle {
     timeline.push_back({std::string(what) + " " + std::to_string(k), e});
   }
   struct PassOut { bool on = false; char* host_pcm = nullptr; const char* dev_pcm = nullptr; size_t elem = 0; } pass_out;
-  DevBuf states, silk_states, silk_hist, silk_exc, fold, hist, rec, en, meta, series, xbuf;
+  DevBuf states, silk_states, silk_hist, silk_exc, fold, hist, rec, en, meta, series, xbuf, order, side_of, aux_count;
   // staging for the host-buffer entry points
   DevBuf d_arena, d_offsets, d_pkt_map, d_out_map, d_lane_stream, d_flags, d_pcm, d_pcm16, d_samples, d_range, d_ids, d_dbg_iy, d_dbg_x;
   std::vector<uint32_t> h_pkt_map, h_lane_stream, h_lane_of_stream, h_epoch, h_count, h_tick, v_range;
@@ -705,7 +717,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
 void bd_destroy(bd_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  DevBuf* all[] = {&h->states, &h->silk_states, &h->silk_hist, &h->silk_exc, &h->fold, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map, &h->d_out_map,
+  DevBuf* all[] = {&h->order, &h->side_of, &h->aux_count, &h->states, &h->silk_states, &h->silk_hist, &h->silk_exc, &h->fold, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map, &h->d_out_map,
                    &h->d_lane_stream, &h->d_flags, &h->d_pcm, &h->d_pcm16, &h->d_samples, &h->d_range, &h->d_ids, &h->d_dbg_iy, &h->d_dbg_x};
   for (DevBuf* b : all) b->release();
   for (auto& sp : h->prof_spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -866,12 +878,20 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
   // not the kernels, ends the call; measured on the headline workload: 71.4 -> 69.1 ms)
   if (h->pass_out.on && !d_out_map && n_ticks >= 16 && ticks_per_pass > (n_ticks + 3) / 4) ticks_per_pass = (n_ticks + 3) / 4;
   const uint32_t cells_max = ticks_per_pass * n_lanes;
-  const uint32_t series_stride = SER_PREFIX + ticks_per_pass * MAX_N + SER_SLACK;
-  CK(h->rec.ensure((size_t)((cells_max + 31) / 32) * REC_SLOTS * 32 * sizeof(uint32_t)));
-  CK(h->en.ensure((size_t)cells_max * EN_STRIDE * sizeof(float)));
-  CK(h->meta.ensure((size_t)2 * cells_max * sizeof(FrameMeta)));   // two halves: the clipper of pass k runs beside pass k+1
+  // auxiliary cells (second CELT frame of a packet, mb_common.cuh): a pool per pass behind the main cells; a packet that
+  // finds it empty is reported as unimplemented
+  const uint32_t aux_cap = cells_max / 8u < 1024u ? 1024u : cells_max / 8u;
+  const uint32_t cells_all = cells_max + aux_cap;
+  // (a lane's time series also holds its auxiliary frames: 5 ms each, at most one per tick)
+  const uint32_t series_stride = SER_PREFIX + ticks_per_pass * (MAX_N + 2 * SHORT_MDCT) + SER_SLACK;
+  CK(h->rec.ensure((size_t)((cells_all + 31) / 32) * REC_SLOTS * 32 * sizeof(uint32_t)));
+  CK(h->en.ensure((size_t)cells_all * EN_STRIDE * sizeof(float)));
+  CK(h->meta.ensure((size_t)2 * cells_all * sizeof(FrameMeta)));   // two halves: the clipper of pass k runs beside pass k+1
   CK(h->series.ensure((size_t)n_lanes * CC * series_stride * sizeof(float)));
-  CK(h->xbuf.ensure((size_t)cells_max * XBUF_STRIDE * sizeof(float)));
+  CK(h->xbuf.ensure((size_t)cells_all * XBUF_STRIDE * sizeof(float)));
+  CK(h->order.ensure(((size_t)2 * cells_max + n_lanes) * sizeof(uint32_t)));   // [2 * ticks][lanes] cells, then the per-lane counts
+  CK(h->side_of.ensure((size_t)cells_max * sizeof(uint32_t)));
+  CK(h->aux_count.ensure(sizeof(uint32_t)));
   float* pcm_f32 = d_pcm_f32;
   if (d_pcm_i16) {  // the i16 path decodes to a float scratch, soft-clips, then rounds (src/opus_decoder.rs:1679-1712)
     CK(h->d_pcm.ensure((size_t)n_packets * pcm_stride * sizeof(float)));
@@ -893,7 +913,13 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
   for (size_t pi = 0; pi < pass_ticks.size(); t0 += pass_ticks[pi], pi++) {
     const uint32_t nt = pass_ticks[pi];
     const uint32_t cells = nt * n_lanes;
-    FrameMeta* const meta_p = h->meta.as<FrameMeta>() + (pi & 1) * (size_t)cells_max;
+    FrameMeta* const meta_p = h->meta.as<FrameMeta>() + (pi & 1) * (size_t)cells_all;
+    const uint32_t cells_run = cells + aux_cap;   // per-cell launches: the pass's main cells, then the auxiliary pool
+    AuxPool aux = {cells_max, aux_cap, h->aux_count.as<uint32_t>()};
+    uint32_t* const order_p = h->order.as<uint32_t>();
+    uint32_t* const order_n_p = order_p + (size_t)2 * cells_max;
+    // (only the auxiliary cells' meta, which the clipper of pass pi - 2 never reads)
+    k_aux_clear<<<(aux_cap + 255) / 256, 256, 0, s>>>(h->rec.as<uint32_t>(), meta_p, aux);
     const size_t cell0 = (size_t)t0 * n_lanes;
     // identity mapping: shift the per-packet arrays so that cell index == local packet index
     const uint32_t* map = d_pkt_map ? d_pkt_map + cell0 : nullptr;
@@ -916,12 +942,14 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     // the clipper of pass pi - 2 read this half of the frame meta on its own stream: k_energy may only rewrite it afterwards
     if (d_pcm_i16 && pi >= 2) CK(cudaStreamWaitEvent(ss, h->ev_clip_done[pi & 1], 0));
     h->prof_begin(BD_K_ENERGY, ss);
-    k_energy<<<(n_lanes + ENERGY_WARPS - 1) / ENERGY_WARPS, 32 * ENERGY_WARPS, 0, ss>>>(n_lanes, nt, map, h->rec.as<uint32_t>(), h->states.as<StreamState>(), d_lane_stream,
-                                                h->en.as<float>(), meta_p, samples, range, h->cfg.quirks,
-                                                flg,
-                                                h->serial_bands || n_lanes >= 148u * 6u * (uint32_t)BANDS_WARPS,   // one warp per lane fills the band-pass slots
-                                                h->cfg.gain_q8 != 0 || !d_pcm_i16,   // direct int16 from k_silk: only the i16 API without a decode gain
-                                                CC);
+    EnergyParams eq;
+    eq.n_lanes = n_lanes; eq.n_ticks = nt; eq.pkt_map = map; eq.rec = h->rec.as<uint32_t>(); eq.st_all = h->states.as<StreamState>();
+    eq.lane_stream = d_lane_stream; eq.en = h->en.as<float>(); eq.meta = meta_p; eq.samples_out = samples; eq.final_range_out = range;
+    eq.quirks = h->cfg.quirks; eq.flags = flg;
+    eq.serial_all = h->serial_bands || n_lanes >= 148u * 6u * (uint32_t)BANDS_WARPS;   // one warp per lane fills the band-pass slots
+    eq.force_float_row = h->cfg.gain_q8 != 0 || !d_pcm_i16;   // direct int16 from k_silk: only the i16 API without a decode gain
+    eq.CC = CC; eq.order = order_p; eq.order_n = order_n_p; eq.side_of = h->side_of.as<uint32_t>(); eq.aux = aux;
+    k_energy<<<(n_lanes + ENERGY_WARPS - 1) / ENERGY_WARPS, 32 * ENERGY_WARPS, 0, ss>>>(eq);
     h->prof_end(ss);
     CK(cudaEventRecord(h->ev_join, ss));   // the frame meta and band energies are ready: k_plan may go
     // SILK synthesis (SILK-only and hybrid cells), before the CELT tail so that k_deemph can add the CELT bands of hybrid
@@ -941,33 +969,34 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     pq.rec = h->rec.as<uint32_t>(); pq.meta = nullptr; pq.xbuf = h->xbuf.as<float>();
     pq.iy_dbg = d_dbg_iy ? d_dbg_iy + cell0 * 2 * MAX_N : nullptr;
     h->prof_begin(BD_K_PVQ, s);
-    k_pvq<<<(cells + PVQ_CELLS - 1) / PVQ_CELLS, PVQ_THREADS, 0, s>>>(pq, cells);
+    k_pvq<<<(cells_run + PVQ_CELLS - 1) / PVQ_CELLS, PVQ_THREADS, 0, s>>>(pq, cells_run, cells, cells_max);
     h->prof_end(s);
     CK(cudaStreamWaitEvent(s, h->ev_join, 0));   // join 1: everything below needs the frame meta
     PlanParams pl;
     pl.rec = h->rec.as<uint32_t>(); pl.en = h->en.as<float>(); pl.meta = meta_p;
     h->prof_begin(BD_K_PLAN, s);
-    k_plan<<<(cells + 127) / 128, 128, 0, s>>>(pl, cells);
+    k_plan<<<(cells_run + 127) / 128, 128, 0, s>>>(pl, cells_run, cells, cells_max);
     h->prof_end(s);
     BandsParams bp;
     bp.rec = h->rec.as<uint32_t>(); bp.en = h->en.as<float>(); bp.meta = meta_p; bp.xbuf = h->xbuf.as<float>();
     bp.x_dbg = d_dbg_x ? d_dbg_x + cell0 * 2 * MAX_N : nullptr;
     bp.fold_all = h->fold.as<float>(); bp.lane_stream = d_lane_stream;
     h->prof_begin(BD_K_BANDS, s);
-    k_bands<<<(cells + BANDS_WARPS - 1) / BANDS_WARPS, 32 * BANDS_WARPS, 0, s>>>(bp, cells);
-    k_bands_hyb<<<(n_lanes + BANDS_WARPS - 1) / BANDS_WARPS, 32 * BANDS_WARPS, 0, s>>>(bp, n_lanes, nt, d_lane_stream, h->fold.as<float>());
+    k_bands<<<(cells_run + BANDS_WARPS - 1) / BANDS_WARPS, 32 * BANDS_WARPS, 0, s>>>(bp, cells_run, cells, cells_max);
+    k_bands_hyb<<<(n_lanes + BANDS_WARPS - 1) / BANDS_WARPS, 32 * BANDS_WARPS, 0, s>>>(bp, n_lanes, order_p, order_n_p, d_lane_stream, h->fold.as<float>());
     h->prof_end(s);
     ImdctParams ip;
     ip.rec = h->rec.as<uint32_t>(); ip.meta = meta_p; ip.xbuf = h->xbuf.as<float>(); ip.series = h->series.as<float>();
     ip.series_stride = series_stride; ip.CC = CC;
     h->prof_begin(BD_K_IMDCT, s);
-    k_imdct<<<(cells * CC + IMDCT_WARPS - 1) / IMDCT_WARPS, 32 * IMDCT_WARPS, 0, s>>>(ip, cells * CC);
+    k_imdct<<<(cells_run * CC + IMDCT_WARPS - 1) / IMDCT_WARPS, 32 * IMDCT_WARPS, 0, s>>>(ip, cells_run * CC, cells, cells_max);
     h->prof_end(s);
     TailParams tp;
     tp.rec = h->rec.as<uint32_t>(); tp.meta = meta_p; tp.pkt_map = map; tp.lane_stream = d_lane_stream;
     tp.st_all = h->states.as<StreamState>(); tp.hist = h->hist.as<float>(); tp.series = h->series.as<float>();
     tp.series_stride = series_stride; tp.n_lanes = n_lanes; tp.n_ticks = nt; tp.CC = CC; tp.gain = h->gain;
     tp.apply_gain = h->cfg.gain_q8 != 0; tp.pcm_f32 = pcm; tp.pcm_stride = pcm_stride; tp.out_map = d_out_map; tp.xbuf = h->xbuf.as<float>();
+    tp.order = order_p; tp.order_n = order_n_p; tp.side_of = h->side_of.as<uint32_t>();
     h->prof_begin(BD_K_COMB, s);
     k_comb<<<(n_lanes * CC + COMB_WARPS - 1) / COMB_WARPS, 32 * COMB_WARPS, 0, s>>>(tp);
     k_comb_plc<<<n_lanes, 32, 0, s>>>(tp);   // lanes with a frame concealed by pitch repetition (the others leave after one look at their flags)

@@ -88,6 +88,28 @@ enum { EN_STRIDE = 4 * 2 * NB_EBANDS, EN_GAINS = 3 * 2 * NB_EBANDS,   // per-fra
 
 struct Team { int tid, n; };
 
+// The CELT frames of a lane in decode order, written by the stream pass (k_energy) and walked by every kernel that is serial
+// in time (k_bands_hyb, k_comb, k_comb_plc, k_deemph): cell of the k-th frame = order[k * n_lanes + lane], k < order_n[lane].
+// Almost always these are the lane's cells that hold a CELT frame, in tick order; auxiliary cells (mb_common.cuh) slot in
+// where their frame is decoded.
+struct EnergyParams {
+  uint32_t n_lanes, n_ticks;
+  const uint32_t* pkt_map;
+  uint32_t* rec;
+  StreamState* st_all;
+  const uint32_t* lane_stream;
+  float* en;
+  FrameMeta* meta;
+  int32_t* samples_out;
+  uint32_t* final_range_out;
+  uint32_t quirks;
+  const uint8_t* flags;
+  int serial_all, force_float_row, CC;
+  uint32_t* order; uint32_t* order_n;   // see above; order has room for 2 * n_ticks entries per lane
+  uint32_t* side_of;                    // per main cell: the cell whose side row holds the audio k_fade blends in (0xffffffff: none)
+  AuxPool aux;
+};
+
 // Shared-memory working set of one stream: the four energy histories, this frame's coarse symbols.
 struct EnergySmem { float E[2 * NB_EBANDS], le[2 * NB_EBANDS], le2[2 * NB_EBANDS], bg[2 * NB_EBANDS], q[2 * NB_EBANDS]; };
 
@@ -97,12 +119,23 @@ struct EnergySmem { float E[2 * NB_EBANDS], le[2 * NB_EBANDS], le2[2 * NB_EBANDS
 // the same for the whole team); the 42 band energies are spread over the lanes: the coarse-energy predictor's running
 // term prev[c] of band i is the left-to-right sum of the lower bands' symbols, which every lane rebuilds for its own
 // band in the reference's order, so the result is bit-identical to the serial loop.
-MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t n_lanes, uint32_t n_ticks, const uint32_t* pkt_map,
-                               uint32_t* rec, StreamState* st_all, const uint32_t* lane_stream, float* en, FrameMeta* meta,
-                               int32_t* samples_out, uint32_t* final_range_out, uint32_t quirks, const uint8_t* flags = nullptr,
-                               int serial_all = 0, int force_float_row = 0, int CC = 2) {
-  StreamState& st = st_all[lane_stream ? lane_stream[lane] : lane];
+MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const EnergyParams& Q) {
+  const uint32_t n_lanes = Q.n_lanes, n_ticks = Q.n_ticks, quirks = Q.quirks;
+  const uint32_t* pkt_map = Q.pkt_map;
+  uint32_t* rec = Q.rec;
+  float* en = Q.en;
+  FrameMeta* meta = Q.meta;
+  int32_t* samples_out = Q.samples_out;
+  uint32_t* final_range_out = Q.final_range_out;
+  const uint8_t* flags = Q.flags;
+  const int serial_all = Q.serial_all, force_float_row = Q.force_float_row, CC = Q.CC;
+  StreamState& st = Q.st_all[Q.lane_stream ? Q.lane_stream[lane] : lane];
   const bool lead = tm.tid == 0;
+  uint32_t n_order = 0;
+  auto emit_frame = [&](uint32_t cell) {   // the next CELT frame of the lane in decode order
+    if (lead) Q.order[(size_t)n_order * n_lanes + lane] = cell;
+    n_order++;
+  };
   for (int i = tm.tid; i < 2 * NB_EBANDS; i += tm.n) {
     sm->E[i] = st.old_ebands[i]; sm->le[i] = st.old_log_e[i]; sm->le2[i] = st.old_log_e2[i]; sm->bg[i] = st.background_log_e[i];
   }
@@ -130,6 +163,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
     uint32_t status = r[S_STATUS * 32];
     FrameMeta m;
     m.seed_in = st_rng; m.sample_off = sample_off; m.lane = lane; m.flags = 0;
+    if (lead) Q.side_of[f] = 0xffffffffu;
     if (MB_ST_EMPTY(status)) { if (lead) meta[f] = m; continue; }
     const uint32_t p = pkt_map ? pkt_map[f] : f;
     const bool continuation = flags && (flags[p] & 4u);
@@ -152,17 +186,18 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
     // ---- CELT concealment of one frame (celt_decode_lost, src/celt/celt_decoder.rs:1429-1855), bands [start, st_celt_end):
     // band-shaped noise through k_plan / k_bands / k_imdct, or (full-band streams, short losses) pitch repetition in
     // k_comb_plc. `extra`: flag bits of the SILK side of the frame (hybrid). Leaves m, the energies and the CELT state updated.
-    auto celt_conceal = [&](int audiosize, int lmq, int start, uint32_t extra) {
+    auto celt_conceal = [&](uint32_t fc, uint32_t* rc, uint32_t statusc, FrameMeta& mc, int audiosize, int lmq, int start, uint32_t extra) {
       const int end = st_celt_end, Mq = 1 << lmq;
+      mc.sample_off = sample_off; mc.lane = lane;
       const int noise_based = st_loss_duration >= 40 || start != 0 || st_skip_plc;
       // a synthetic frame header for the kernels downstream: LM, the DECODER's channel count, band range; no leaves, no nodes
       if (lead) {
-        r[S_HDR0 * 32] = (uint32_t)lmq | ((uint32_t)(CC - 1) << 2) | (2u << 6) | ((uint32_t)start << 26);
-        r[S_HDR1 * 32] = 0u;
-        r[S_STATUS * 32] = (status & ~(31u << 8)) | ((uint32_t)end << 8);
-        r[S_PLAN * 32] = 0u;
+        rc[S_HDR0 * 32] = (uint32_t)lmq | ((uint32_t)(CC - 1) << 2) | (2u << 6) | ((uint32_t)start << 26);
+        rc[S_HDR1 * 32] = 0u;
+        rc[S_STATUS * 32] = (statusc & ~(31u << 8)) | ((uint32_t)end << 8);
+        rc[S_PLAN * 32] = 0u;
       }
-      float* ef = en + (size_t)f * EN_STRIDE;
+      float* ef = en + (size_t)fc * EN_STRIDE;
       if (noise_based) {
         const float decay = st_loss_duration == 0 ? 1.5f : 0.5f;
         MB_SYNC();
@@ -177,19 +212,20 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
         // the noise generator runs channel by channel over bands start .. eff_end (celt_decoder.rs:1511-1531)
         int total = 0;
         for (int i = start; i < imin(end, NB_EBANDS); i++) total += (eband(i + 1) - eband(i)) << lmq;
-        m.seed_in = st_rng;
+        mc.seed_in = st_rng;
         uint32_t sd = st_rng;
         for (int k = 0; k < CC * total; k++) sd = sd * 1664525u + 1013904223u;
         st_rng = sd;
         st_prefold = 0; st_skip_plc = 1;
-        m.flags = 1u | MB_FL_PLC | MB_FL_F32ROW | (silk_side_seen ? 512u : 0u) | extra;
+        mc.flags = 1u | MB_FL_PLC | MB_FL_F32ROW | (silk_side_seen ? 512u : 0u) | extra;
       } else {
-        m.seed_in = (uint32_t)st_loss_duration;
+        mc.seed_in = (uint32_t)st_loss_duration;
         st_prefold = 1;
-        m.flags = 1u | MB_FL_PLC | MB_FL_PLC_PITCH | MB_FL_F32ROW | extra;
+        mc.flags = 1u | MB_FL_PLC | MB_FL_PLC_PITCH | MB_FL_F32ROW | extra;
       }
       st_loss_duration = imin(10000, st_loss_duration + Mq);
       sample_off += (uint32_t)audiosize;
+      emit_frame(fc);
     };
     if (MB_ST_LOST(status) && !pkt_failed) {
       // ---- lost packet / frame of at most one byte: decode_frame(None) (src/opus_decoder.rs:491-575). The stream conceals in
@@ -212,7 +248,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
         continue;
       }
       if (md == 1000) m.flags = 2u | MB_FL_PLC | pkt_route;
-      else celt_conceal(audiosize, lmq, md == 1001 ? 17 : 0, md == 1001 ? (2u | 8u) : 0u);
+      else celt_conceal(f, r, status, m, audiosize, lmq, md == 1001 ? 17 : 0, md == 1001 ? (2u | 8u) : 0u);
       st_prev_mode = md; st_prev_redundancy = 0; st_range_final = 0; st_last_duration = audiosize;
       if (lead) { meta[f] = m; samples_out[p] = audiosize; final_range_out[p] = 0; }
       continue;
@@ -246,7 +282,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
     // carries one, SILK -> CELT when the previous SILK packet ended in one.
     bool reject;
     if (!silk_bit) reject = st_prev_mode == 1001 || (st_prev_mode == 1000 && !st_prev_redundancy);
-    else if (red) reject = hybrid || st_prev_mode == 1001;   // would need two CELT frames in the cell (fade-out + redundancy)
+    else if (red) reject = !hybrid && st_prev_mode == 1001;   // SILK-only after hybrid: fade-out frame and redundancy frame in one cell
     else reject = st_prev_mode == 1002 || (silk_only && st_prev_mode == 1001);
     if (reject) {
       if (lead) {
@@ -276,136 +312,183 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
       }
       continue;
     }
-    // SILK-only -> hybrid: the CELT decoder is reset before the frame (opus_decoder.rs:895-898). The energy side is reset
-    // here; the tail kernels reset their own state (post-filter, history, de-emphasis memory) on flag bit 2.
-    // (also before a SILK -> CELT redundancy frame, opus_decoder.rs:1040-1046; not after a packet that ended in one)
-    const bool celt_reset = (hybrid && st_prev_mode == 1000 && !st_prev_redundancy) || aux == 3;
-    if (celt_reset) {
+    // A mode change resets the CELT decoder before the frame (opus_decoder.rs:895-898): SILK-only -> hybrid, CELT-only -> hybrid
+    // (behind the CELT -> SILK redundancy frame, which still runs on the old state), and before a SILK -> CELT redundancy frame
+    // (:1040-1046); not after a packet that ended in one. The energy side is reset here; the tail kernels reset their own state
+    // (post-filter, history, de-emphasis memory) on flag bit 2 of the frame.
+    auto celt_reset_now = [&]() {
       MB_SYNC();
       for (int i = tm.tid; i < 2 * NB_EBANDS; i += tm.n) { sm->E[i] = 0.f; sm->le[i] = -28.f; sm->le2[i] = -28.f; sm->bg[i] = 0.f; }
       st_rng = 0; st_loss_duration = 0;
       st_skip_plc = 1; st_prefold = 0;   // (last_pitch_index and the concealment filter are only read after a frame has set them)
-      m.seed_in = 0;
-    }
+    };
+    // ---- one coded CELT frame: the record of cell fc (the packet's own cell or an auxiliary one), energies, state rotation,
+    // its place in the lane's time series. Returns the frame's length in samples.
+    auto celt_coded = [&](uint32_t fc, const uint32_t* rc, uint32_t statusc, uint32_t flags_c) -> int {
+      FrameMeta mc;
+      mc.seed_in = st_rng; mc.sample_off = sample_off; mc.lane = lane; mc.flags = flags_c | MB_FL_F32ROW;
+      const uint32_t h0c = rc[S_HDR0 * 32];
+      const int lm = (int)MB_H0_LM(h0c), C = (int)MB_H0_C(h0c), start = (int)MB_H0_START(h0c), end = (int)MB_ST_END(statusc);
+      const int intra = (int)MB_H0_INTRA(h0c), silence = (int)MB_H0_SILENCE(h0c), transient = (int)MB_H0_TRANSIENT(h0c);
+      const int M = 1 << lm;
+      float* E = sm->E;
+      st_celt_end = end;
+      if (st_loss_duration == 0) st_skip_plc = 0;      // prepare_frame (celt_decoder.rs:2875-2877)
+      MB_SYNC();
+      if (C == 1) {   // celt_decoder.rs:2890-2896
+        for (int i = tm.tid; i < NB_EBANDS; i += tm.n) E[i] = fmax32(E[i], E[NB_EBANDS + i]);
+        MB_SYNC();
+      }
+      if (!intra && st_loss_duration != 0) {
+        // the first coded frame after a loss starts from safer energies (celt_decoder.rs:2943-2969), both channels
+        const int missing = imin(10, st_loss_duration >> lm);
+        const float safety = lm == 0 ? 1.5f : (lm == 1 ? 0.5f : 0.0f);
+        for (int idx = tm.tid; idx < 2 * NB_EBANDS; idx += tm.n) {
+          const int i = idx >= NB_EBANDS ? idx - NB_EBANDS : idx;
+          if (i < start || i >= end) continue;
+          float e0 = E[idx];
+          const float e1 = sm->le[idx], e2 = sm->le2[idx];
+          if (e0 < fmax32(e1, e2)) {
+            float slope = fmax32(e1 - e0, 0.5f * (e2 - e0));
+            slope = fmin32(slope, 2.0f);
+            e0 -= fmax32((float)(missing + 1) * slope, 0.0f);
+            e0 = fmax32(e0, -20.0f);
+          } else e0 = fmin32(e0, fmin32(e1, e2));
+          E[idx] = e0 - safety;
+        }
+        MB_SYNC();
+      }
+      // this frame's symbols: every lane fetches the words of its own (channel, band) slots
+      uint32_t wmine[2] = {0, 0};   // team of 32: slots tid and tid + 32; team of one: read again below
+      for (int idx = tm.tid, k = 0; idx < 2 * NB_EBANDS; idx += tm.n, k++) {
+        const int c = idx >= NB_EBANDS, i = idx - c * NB_EBANDS;
+        uint32_t w = 0;
+        if (c < C && i >= start && i < end) w = rc[(S_ENERGY + idx) * 32];
+        if (k < 2) wmine[k] = w;
+        sm->q[idx] = (float)(int)(int16_t)(w & 0xffffu);
+      }
+      MB_SYNC();
+      // coarse + fine + finalise (three separate float additions per band, in the reference's order)
+      {
+        const float coef = intra ? 0.f : kPredCoef[lm];
+        const float beta = intra ? 4915.f / 32768.f : kBetaCoef[lm];
+        for (int idx = tm.tid, k = 0; idx < 2 * NB_EBANDS; idx += tm.n, k++) {
+          const int c = idx >= NB_EBANDS, i = idx - c * NB_EBANDS;
+          if (c >= C || i < start || i >= end) continue;
+          const float* qc = sm->q + c * NB_EBANDS;
+          float prev = 0.f;
+          if (quirks & Q8_COARSE_CLAMP) { for (int j = start; j < i; j++) prev += qc[j] - beta * qc[j]; }
+          else for (int j = start; j < i; j++) prev = prev + qc[j] - beta * qc[j];
+          const float q = qc[i];
+          const float o = fmax32(E[idx], -9.0f);
+          float tmp = coef * o + prev + q;
+          if (quirks & Q8_COARSE_CLAMP) tmp = tmp < -28.f ? -28.f : (tmp > 28.f ? 28.f : tmp);
+          const uint32_t w = (tm.n >= 32 && k < 2) ? wmine[k] : rc[(S_ENERGY + idx) * 32];
+          const int fq = (int)((w >> 24) & 15u);
+          if (fq > 0) {
+            const float scale = (float)(1 << (14 - fq)) * (1.0f / 16384.0f);
+            tmp += ((float)(int)((w >> 16) & 255u) + 0.5f) * scale - 0.5f;
+          }
+          // finalise: every (band, channel) receives at most one extra bit, so the two priority passes of the reference
+          // collapse into one addition
+          if (w & (1u << 28)) {
+            const float scale = (float)(1 << (14 - fq - 1)) * (1.0f / 16384.0f);
+            tmp += ((float)(int)((w >> 29) & 1u) - 0.5f) * scale;
+          }
+          E[idx] = tmp;
+        }
+      }
+      MB_SYNC();
+      float* ef = en + (size_t)fc * EN_STRIDE;
+      const float increase = (float)imin(st_loss_duration + M, 160) * 0.001f;
+      // (two sweeps with the team's barrier between them: a lane reads E[i] of the other channel before anyone rewrites it.
+      //  The host emulation, a team of one, runs the first sweep into a scratch copy.)
+#if MB_ON_DEVICE
+      float ne[2], nl1[2], nl2[2];
+#else
+      float ne[2 * NB_EBANDS], nl1[2 * NB_EBANDS], nl2[2 * NB_EBANDS];
+#endif
+      for (int idx = tm.tid, k = 0; idx < 2 * NB_EBANDS; idx += tm.n, k++) {
+        const int c = idx >= NB_EBANDS, i = idx - c * NB_EBANDS;
+        if (MB_H0_ACON(h0c)) { ef[2 * NB_EBANDS + idx] = sm->le[idx]; ef[4 * NB_EBANDS + idx] = sm->le2[idx]; }
+        float e = silence ? -28.0f : E[idx];
+        ef[idx] = e;
+        ef[EN_GAINS + idx] = celt_exp2(fmin32(e + kEMeans[i], 32.0f));   // denormalise_bands' band gain (bands.rs:4172-4234)
+        // state rotation (celt_decoder.rs:4023-4062)
+        if (C == 1 && c == 1) e = silence ? -28.0f : E[i];
+        float l1 = sm->le[idx], l2 = sm->le2[idx];
+        if (transient) l1 = fmin32(l1, e); else { l2 = l1; l1 = e; }
+        sm->bg[idx] = fmin32(sm->bg[idx] + increase, e);
+        if (i < start || i >= end) { e = 0.f; l1 = l2 = -28.0f; }
+        ne[k] = e; nl1[k] = l1; nl2[k] = l2;
+      }
+      MB_SYNC();
+      for (int idx = tm.tid, k = 0; idx < 2 * NB_EBANDS; idx += tm.n, k++) { E[idx] = ne[k]; sm->le[idx] = nl1[k]; sm->le2[idx] = nl2[k]; }
+      st_rng = rc[S_RANGE * 32];
+      st_loss_duration = 0; st_prefold = 0;
+      if (statusc & (1u << 13)) st_celt_error = 1;
+      if (lead) meta[fc] = mc;
+      emit_frame(fc);
+      sample_off += (uint32_t)(M * SHORT_MDCT);                 // the CELT time line advances by the CELT frame
+      return M * SHORT_MDCT;
+    };
+    const bool celt_reset = (hybrid && st_prev_mode != 1001 && st_prev_mode > 0 && !st_prev_redundancy) || (aux == 3 && !hybrid);
     if (MB_ST_FEC(status) && hybrid) {
       // hybrid packet decoded from its LBRR data: SILK from the record, the CELT part concealed (opus_decoder.rs:944-952)
+      if (celt_reset) { celt_reset_now(); m.seed_in = 0; }
       const int lmq = (int)MB_H0_LM(h0);
       st_celt_end = (int)MB_ST_END(status);
-      celt_conceal(SHORT_MDCT << lmq, lmq, 17, 2u | 8u | (celt_reset ? 4u : 0u) | silk_reset);
+      celt_conceal(f, r, status, m, SHORT_MDCT << lmq, lmq, 17, 2u | 8u | (celt_reset ? 4u : 0u) | silk_reset);
       silk_side_seen = true; st_fold_serial = 1;
       st_prev_mode = 1001; st_prev_redundancy = 0; st_range_final = silk_rng; st_last_duration = SHORT_MDCT << lmq;
       if (lead) { meta[f] = m; samples_out[p] = SHORT_MDCT << lmq; final_range_out[p] = st_range_final; }
       continue;
     }
-    const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), start = (int)MB_H0_START(h0), end = (int)MB_ST_END(status);
-    const int intra = (int)MB_H0_INTRA(h0), silence = (int)MB_H0_SILENCE(h0), transient = (int)MB_H0_TRANSIENT(h0);
-    const int M = 1 << lm;
-    float* E = sm->E;
-    st_celt_end = end;
-    if (st_loss_duration == 0) st_skip_plc = 0;      // prepare_frame (celt_decoder.rs:2875-2877)
-    MB_SYNC();
-    if (C == 1) {   // celt_decoder.rs:2890-2896
-      for (int i = tm.tid; i < NB_EBANDS; i += tm.n) E[i] = fmax32(E[i], E[NB_EBANDS + i]);
-      MB_SYNC();
-    }
-    if (!intra && st_loss_duration != 0) {
-      // the first coded frame after a loss starts from safer energies (celt_decoder.rs:2943-2969), both channels
-      const int missing = imin(10, st_loss_duration >> lm);
-      const float safety = lm == 0 ? 1.5f : (lm == 1 ? 0.5f : 0.0f);
-      for (int idx = tm.tid; idx < 2 * NB_EBANDS; idx += tm.n) {
-        const int i = idx >= NB_EBANDS ? idx - NB_EBANDS : idx;
-        if (i < start || i >= end) continue;
-        float e0 = E[idx];
-        const float e1 = sm->le[idx], e2 = sm->le2[idx];
-        if (e0 < fmax32(e1, e2)) {
-          float slope = fmax32(e1 - e0, 0.5f * (e2 - e0));
-          slope = fmin32(slope, 2.0f);
-          e0 -= fmax32((float)(missing + 1) * slope, 0.0f);
-          e0 = fmax32(e0, -20.0f);
-        } else e0 = fmin32(e0, fmin32(e1, e2));
-        E[idx] = e0 - safety;
+    if (hybrid && red) {
+      // ---- hybrid packet with a redundancy frame (opus_decoder.rs:746-797, 1012-1080): two CELT frames, the 5 ms redundancy
+      // frame (all bands, its own range decoder; parsed into an auxiliary cell) before or after the packet's own.
+      const uint32_t aref = r[S_AUXREF * 32], ac = aref >> 2;
+      const bool c2s = ((aref >> 1) & 1u) != 0;
+      const uint32_t* ra = rec + rec_index((aref & 1u) ? ac : f, 0);
+      const uint32_t status_a = ra[S_STATUS * 32];
+      if (!(aref & 1u) || !MB_ST_DECODED(status_a)) {
+        if (lead) { meta[f] = m; samples_out[p] = (aref & 1u) ? MB_ST_CODE(status_a) : MB_UNIMPLEMENTED; final_range_out[p] = st_range_final; }
+        pkt_failed = true;
+        continue;
       }
-      MB_SYNC();
-    }
-    // this frame's symbols: every lane fetches the words of its own (channel, band) slots
-    uint32_t wmine[2] = {0, 0};   // team of 32: slots tid and tid + 32; team of one: read again below
-    for (int idx = tm.tid, k = 0; idx < 2 * NB_EBANDS; idx += tm.n, k++) {
-      const int c = idx >= NB_EBANDS, i = idx - c * NB_EBANDS;
-      uint32_t w = 0;
-      if (c < C && i >= start && i < end) w = r[(S_ENERGY + idx) * 32];
-      if (k < 2) wmine[k] = w;
-      sm->q[idx] = (float)(int)(int16_t)(w & 0xffffu);
-    }
-    MB_SYNC();
-    // coarse + fine + finalise (three separate float additions per band, in the reference's order)
-    {
-      const float coef = intra ? 0.f : kPredCoef[lm];
-      const float beta = intra ? 4915.f / 32768.f : kBetaCoef[lm];
-      for (int idx = tm.tid, k = 0; idx < 2 * NB_EBANDS; idx += tm.n, k++) {
-        const int c = idx >= NB_EBANDS, i = idx - c * NB_EBANDS;
-        if (c >= C || i < start || i >= end) continue;
-        const float* qc = sm->q + c * NB_EBANDS;
-        float prev = 0.f;
-        if (quirks & Q8_COARSE_CLAMP) { for (int j = start; j < i; j++) prev += qc[j] - beta * qc[j]; }
-        else for (int j = start; j < i; j++) prev = prev + qc[j] - beta * qc[j];
-        const float q = qc[i];
-        const float o = fmax32(E[idx], -9.0f);
-        float tmp = coef * o + prev + q;
-        if (quirks & Q8_COARSE_CLAMP) tmp = tmp < -28.f ? -28.f : (tmp > 28.f ? 28.f : tmp);
-        const uint32_t w = (tm.n >= 32 && k < 2) ? wmine[k] : r[(S_ENERGY + idx) * 32];
-        const int fq = (int)((w >> 24) & 15u);
-        if (fq > 0) {
-          const float scale = (float)(1 << (14 - fq)) * (1.0f / 16384.0f);
-          tmp += ((float)(int)((w >> 16) & 255u) + 0.5f) * scale - 0.5f;
-        }
-        // finalise: every (band, channel) receives at most one extra bit, so the two priority passes of the reference
-        // collapse into one addition
-        if (w & (1u << 28)) {
-          const float scale = (float)(1 << (14 - fq - 1)) * (1.0f / 16384.0f);
-          tmp += ((float)(int)((w >> 29) & 1u) - 0.5f) * scale;
-        }
-        E[idx] = tmp;
+      silk_side_seen = true; st_fold_serial = 1;
+      uint32_t red_rng = 0;
+      if (c2s) { celt_coded(ac, ra, status_a, 1u | 16u); red_rng = st_rng; }   // on the old CELT state
+      if (celt_reset) celt_reset_now();
+      uint32_t fl = 1u | 2u | 8u | (celt_reset ? 4u : 0u) | silk_reset;
+      if (!c2s) fl |= 128u;
+      else if (st_prev_mode != 1000 || st_prev_redundancy) fl |= 64u;                 // opus_decoder.rs:1066
+      const int N = celt_coded(f, r, status, fl);
+      const uint32_t celt_rng = st_rng;
+      if (!c2s) { celt_reset_now(); celt_coded(ac, ra, status_a, 1u | 16u | 4u); red_rng = st_rng; }
+      if (lead) Q.side_of[f] = ac;
+      const int code = MB_ST_CODE(status) < 0 ? MB_ST_CODE(status) : MB_ST_CODE(status_a);
+      if (code < 0) {
+        if (lead) { samples_out[p] = code; final_range_out[p] = st_range_final; }
+      } else {
+        st_prev_mode = 1001; st_prev_redundancy = !c2s;
+        st_range_final = celt_rng ^ red_rng;
+        st_last_duration = N;
+        if (lead) { samples_out[p] = N; final_range_out[p] = st_range_final; }
       }
+      continue;
     }
-    MB_SYNC();
-    float* ef = en + (size_t)f * EN_STRIDE;
-    const float increase = (float)imin(st_loss_duration + M, 160) * 0.001f;
-    // (two sweeps with the team's barrier between them: a lane reads E[i] of the other channel before anyone rewrites it.
-    //  The host emulation, a team of one, runs the first sweep into a scratch copy.)
-#if MB_ON_DEVICE
-    float ne[2], nl1[2], nl2[2];
-#else
-    float ne[2 * NB_EBANDS], nl1[2 * NB_EBANDS], nl2[2 * NB_EBANDS];
-#endif
-    for (int idx = tm.tid, k = 0; idx < 2 * NB_EBANDS; idx += tm.n, k++) {
-      const int c = idx >= NB_EBANDS, i = idx - c * NB_EBANDS;
-      if (MB_H0_ACON(h0)) { ef[2 * NB_EBANDS + idx] = sm->le[idx]; ef[4 * NB_EBANDS + idx] = sm->le2[idx]; }
-      float e = silence ? -28.0f : E[idx];
-      ef[idx] = e;
-      ef[EN_GAINS + idx] = celt_exp2(fmin32(e + kEMeans[i], 32.0f));   // denormalise_bands' band gain (bands.rs:4172-4234)
-      // state rotation (celt_decoder.rs:4023-4062)
-      if (C == 1 && c == 1) e = silence ? -28.0f : E[i];
-      float l1 = sm->le[idx], l2 = sm->le2[idx];
-      if (transient) l1 = fmin32(l1, e); else { l2 = l1; l1 = e; }
-      sm->bg[idx] = fmin32(sm->bg[idx] + increase, e);
-      if (i < start || i >= end) { e = 0.f; l1 = l2 = -28.0f; }
-      ne[k] = e; nl1[k] = l1; nl2[k] = l2;
-    }
-    MB_SYNC();
-    for (int idx = tm.tid, k = 0; idx < 2 * NB_EBANDS; idx += tm.n, k++) { E[idx] = ne[k]; sm->le[idx] = nl1[k]; sm->le2[idx] = nl2[k]; }
-    st_rng = r[S_RANGE * 32];
-    st_loss_duration = 0; st_prefold = 0;
-    if (status & (1u << 13)) st_celt_error = 1;
-    const int N = (fadeout || red) ? silk_n : M * SHORT_MDCT;   // samples the packet delivers
+    if (celt_reset) celt_reset_now();
+    uint32_t fl;
     if (red) {
-      m.flags = 1u | 2u | 16u | (celt_reset ? 4u : 0u) | silk_reset;
-      if (aux == 3) m.flags |= 128u;
-      else if (st_prev_mode != 1000 || st_prev_redundancy) m.flags |= 64u;   // opus_decoder.rs:1066
-    } else m.flags = (hybrid || fadeout) ? (1u | 2u | 8u | (celt_reset ? 4u : 0u)) : (silk_side_seen ? (1u | 512u) : 1u);
-    if (m.flags & (8u | 16u)) { silk_side_seen = true; st_fold_serial = 1; }
-    m.flags |= MB_FL_F32ROW;
-    if (lead) meta[f] = m;
-    sample_off += (uint32_t)(M * SHORT_MDCT);                 // the CELT time line advances by the CELT frame
+      if (lead) Q.side_of[f] = f;
+      fl = 1u | 2u | 16u | (celt_reset ? 4u : 0u) | silk_reset;
+      if (aux == 3) fl |= 128u;
+      else if (st_prev_mode != 1000 || st_prev_redundancy) fl |= 64u;   // opus_decoder.rs:1066
+    } else fl = (hybrid || fadeout) ? (1u | 2u | 8u | (celt_reset ? 4u : 0u) | silk_reset) : (silk_side_seen ? (1u | 512u) : 1u);
+    if (fl & (8u | 16u)) { silk_side_seen = true; st_fold_serial = 1; }
+    const int Nc = celt_coded(f, r, status, fl);
+    const int N = (fadeout || red) ? silk_n : Nc;   // samples the packet delivers
     int code = MB_ST_CODE(status);
     if (code < 0) {  // e.g. bit-budget overrun: state has advanced, the call reports the error (celt_decoder.rs:4128)
       if (lead) { samples_out[p] = code; final_range_out[p] = st_range_final; }
@@ -432,18 +515,17 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
     // Overlap tails (MB_FL_KEEP_TAIL): the frame in front of a frame concealed by pitch repetition, and the lane's last frame
     // of the pass (the next call may start with a loss), keep the 120 samples their inverse MDCT leaves behind the frame.
     bool need_tail = true;
-    for (uint32_t t = n_ticks; t-- > 0;) {
-      const uint32_t f = t * n_lanes + lane;
+    for (uint32_t k = n_order; k-- > 0;) {
+      const uint32_t f = Q.order[(size_t)k * n_lanes + lane];
       const uint32_t fl = meta[f].flags;
-      if (!(fl & 1u)) continue;
       if (fl & MB_FL_PLC_PITCH) { need_tail = true; continue; }
       if (need_tail) { meta[f].flags = fl | MB_FL_KEEP_TAIL; need_tail = false; }
     }
     int covered = 0;
-    for (uint32_t t = n_ticks; t-- > 0 && covered < (int)FOLD_WORDS;) {
-      const uint32_t f = t * n_lanes + lane;
+    for (uint32_t k = n_order; k-- > 0 && covered < (int)FOLD_WORDS;) {
+      const uint32_t f = Q.order[(size_t)k * n_lanes + lane];
       const uint32_t fl = meta[f].flags;
-      if (!(fl & 1u) || (fl & MB_FL_FOLD) || (fl & MB_FL_PLC)) continue;   // (a concealed frame leaves the fold buffer alone)
+      if ((fl & MB_FL_FOLD) || (fl & MB_FL_PLC)) continue;   // (a concealed frame leaves the fold buffer alone)
       const uint32_t h0 = rec[rec_index(f, S_HDR0)];
       const int top = imin((int)MB_H0_C(h0) * ((int)eband(NB_EBANDS - 1) << (int)MB_H0_LM(h0)), (int)FOLD_WORDS);   // even
       if (top > covered) {
@@ -451,6 +533,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, uint32_t 
         covered = top;
       }
     }
+    Q.order_n[lane] = n_order;
   }
 }
 

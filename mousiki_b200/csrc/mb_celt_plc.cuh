@@ -293,7 +293,8 @@ MB_DEV_NOINLINE void plc_pitch_channel(Team tm, PlcSmem* sm, float* fr, int N, i
 MB_DEV void celt_comb_plc_lane(Team tm, PlcSmem* sm, uint32_t lane, const TailParams& P) {
   const int CC = P.CC;
   bool any = false;
-  for (uint32_t t = tm.tid; t < P.n_ticks; t += tm.n) any |= (P.meta[(size_t)t * P.n_lanes + lane].flags & MB_FL_PLC_PITCH) != 0;
+  const uint32_t n_frames = P.order_n[lane];
+  for (uint32_t k = tm.tid; k < n_frames; k += tm.n) any |= (P.meta[P.order[(size_t)k * P.n_lanes + lane]].flags & MB_FL_PLC_PITCH) != 0;
 #if MB_ON_DEVICE
   any = __any_sync(0xffffffffu, any);
 #endif
@@ -310,10 +311,9 @@ MB_DEV void celt_comb_plc_lane(Team tm, PlcSmem* sm, uint32_t lane, const TailPa
   bool first_celt = true;
   uint32_t total = 0;
   MB_SYNC();
-  for (uint32_t t = 0; t < P.n_ticks; t++) {
-    const uint32_t f = t * P.n_lanes + lane;
+  for (uint32_t k = 0; k < n_frames; k++) {
+    const uint32_t f = P.order[(size_t)k * P.n_lanes + lane];
     const FrameMeta m = P.meta[f];
-    if (!(m.flags & 1u)) continue;
     const uint32_t* r = P.rec + rec_index(f, 0);
     const uint32_t h0 = r[S_HDR0 * 32], h1 = r[S_HDR1 * 32];
     const int lm = (int)MB_H0_LM(h0), N = SHORT_MDCT << lm;
@@ -331,10 +331,7 @@ MB_DEV void celt_comb_plc_lane(Team tm, PlcSmem* sm, uint32_t lane, const TailPa
       // The concealed frame comes with its own overlap region, N .. N + 120 — where the NEXT frame's inverse MDCT output
       // already sits if that frame has one (in the reference the next frame's transform simply overwrites the region later).
       bool next_has_output = false;
-      for (uint32_t t2 = t + 1; t2 < P.n_ticks; t2++) {
-        const uint32_t fl2 = P.meta[(size_t)t2 * P.n_lanes + lane].flags;
-        if (fl2 & 1u) { next_has_output = !(fl2 & MB_FL_PLC_PITCH); break; }
-      }
+      if (k + 1 < n_frames) next_has_output = !(P.meta[P.order[(size_t)(k + 1) * P.n_lanes + lane]].flags & MB_FL_PLC_PITCH);
       for (int c = 0; c < CC; c++) {
         float* fr = ser[c] + m.sample_off;
         if (next_has_output) {

@@ -34,8 +34,15 @@ struct TailParams {
   float* pcm_f32;              // [packet][pcm_stride] interleaved, or null
   uint32_t pcm_stride;         // elements between packets
   const uint32_t* out_map = nullptr;  // see pcm_elem_off
-  float* xbuf = nullptr;              // [frame][XBUF_STRIDE]: spectrum rows, dead after the IMDCT; a redundancy frame's audio goes there
+  float* xbuf = nullptr;              // [frame][XBUF_STRIDE]: spectrum rows; their upper half is the cell's side row (below)
+  const uint32_t* order = nullptr;    // the lane's CELT frames in decode order (mb_celt_energy.cuh)
+  const uint32_t* order_n = nullptr;
+  const uint32_t* side_of = nullptr;  // per main cell: the cell whose side row k_fade blends into the packet's row
 };
+// Side row of a cell: 5 ms of audio that is not the packet's own (a redundancy frame), kept for k_fade. It lives in the upper
+// half of the cell's spectrum row: such a cell's own CELT frame is at most 5 ms long and only uses the first 2 x 240 floats.
+enum { SIDE_OFF = MAX_N };
+MB_DEV float* side_row(float* xbuf, uint32_t cell) { return xbuf + (size_t)cell * XBUF_STRIDE + SIDE_OFF; }
 
 // ---------------------------------------------------------------- phase 2c(i): post-filter, one warp per stream-channel
 // The comb filter reads its own output T-2 .. T+2 samples back with T >= 15, so a run of min(T0, T1) - 2 >= 13
@@ -88,7 +95,7 @@ MB_DEV void celt_comb_channel(Team tm, CombSmem* sm, uint32_t lane, int c, const
   const int CC = P.CC;
   {  // a lane with a frame concealed by pitch repetition belongs to k_comb_plc (mb_celt_plc.cuh)
     bool any = false;
-    for (uint32_t t = tm.tid; t < P.n_ticks; t += tm.n) any |= (P.meta[(size_t)t * P.n_lanes + lane].flags & MB_FL_PLC_PITCH) != 0;
+    for (uint32_t k = tm.tid; k < P.order_n[lane]; k += tm.n) any |= (P.meta[P.order[(size_t)k * P.n_lanes + lane]].flags & MB_FL_PLC_PITCH) != 0;
 #if MB_ON_DEVICE
     any = __any_sync(0xffffffffu, any);
 #endif
@@ -105,10 +112,10 @@ MB_DEV void celt_comb_channel(Team tm, CombSmem* sm, uint32_t lane, int c, const
   float pf_gain = pf.gain, pf_gain_old = pf.gain_old;
   int total = 0, reset_at = -1;   // samples of CELT signal this pass; where the last decoder reset fell
   MB_SYNC();
-  for (uint32_t t = 0; t < P.n_ticks; t++) {
-    const uint32_t f = t * P.n_lanes + lane;
+  const uint32_t n_frames = P.order_n[lane];
+  for (uint32_t k = 0; k < n_frames; k++) {
+    const uint32_t f = P.order[(size_t)k * P.n_lanes + lane];
     const FrameMeta m = P.meta[f];
-    if (!(m.flags & 1u)) continue;
     const uint32_t* r = P.rec + rec_index(f, 0);
     const uint32_t h0 = r[S_HDR0 * 32], h1 = r[S_HDR1 * 32];
     const int lm = (int)MB_H0_LM(h0), N = SHORT_MDCT << lm;
@@ -196,19 +203,23 @@ MB_DEV void celt_deemph_lane(uint32_t lane, int c, const TailParams& P) {
   StreamState& st = P.st_all[sid];
   const float* ser = P.series + ((size_t)lane * CC + c) * P.series_stride + SER_PREFIX;
   Deemph d = {st.preemph_mem[c], P.gain, P.apply_gain};
-  for (uint32_t t = 0; t < P.n_ticks; t++) {
-    const uint32_t f = t * P.n_lanes + lane;
+  const uint32_t n_frames = P.order_n[lane];
+  for (uint32_t k = 0; k < n_frames; k++) {
+    const uint32_t f = P.order[(size_t)k * P.n_lanes + lane];
     const FrameMeta m = P.meta[f];
-    if (!(m.flags & 1u)) continue;
     const int N = SHORT_MDCT << (int)MB_H0_LM(P.rec[rec_index(f, S_HDR0)]);
     const float* x = ser + m.sample_off;
-    const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
-    float* out = P.pcm_f32 ? P.pcm_f32 + pcm_elem_off(P.out_map, p, P.pcm_stride) + c : nullptr;
-    const bool side = (m.flags & 16u) != 0;       // redundancy frame: not the packet's audio, kept aside for celt_fade_cell
-    if (side) out = P.xbuf + (size_t)f * XBUF_STRIDE + c;
+    const bool side = (m.flags & 16u) != 0;       // not the packet's audio (redundancy frame): kept aside for celt_fade_cell
+    float* out;
+    if (side) out = side_row(P.xbuf, f) + c;
+    else {
+      const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
+      out = P.pcm_f32 ? P.pcm_f32 + pcm_elem_off(P.out_map, p, P.pcm_stride) + c : nullptr;
+    }
     if (m.flags & 4u) d.mem = 0.f;
     const bool accum = (m.flags & 8u) != 0;
-    d.apply_gain = side ? 0 : P.apply_gain;
+    // the decode gain applies once to the finished row: here, unless the row still waits for a cross-fade (k_fade applies it)
+    d.apply_gain = (side || (m.flags & (64u | 128u))) ? 0 : P.apply_gain;
     for (int j = 0; j < N; j++) {
       const float v = d.step(x[j], accum && out ? out[(size_t)j * CC] : 0.f, accum);
       if (out) out[(size_t)j * CC] = v;
@@ -228,13 +239,15 @@ MB_DEV void celt_fade_cell(uint32_t f, int c, const TailParams& P) {
     for (int i = 0; i < (int)m.seed_in; i++) row0[(size_t)i * P.CC] = 0.f;
     return;
   }
-  if (!(m.flags & 16u) || !P.pcm_f32) return;
+  if (f >= P.n_lanes * P.n_ticks) return;      // (auxiliary cells have no row of their own)
+  const uint32_t src = P.side_of[f];
+  if (src == 0xffffffffu || !P.pcm_f32) return;
   const int CC = P.CC;
   const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
   float* row = P.pcm_f32 + pcm_elem_off(P.out_map, p, P.pcm_stride) + c;
-  const float* red = P.xbuf + (size_t)f * XBUF_STRIDE + c;
+  const float* red = side_row(P.xbuf, src) + c;
   const uint32_t silk_h0 = P.rec[rec_index(f, S_SILK_HYB)];
-  const int N = (int)((silk_h0 >> 8) & 3u) * (int)((silk_h0 >> 5) & 7u) * 240;
+  const int N = (int)((silk_h0 >> 8) & 3u) * (int)((silk_h0 >> 5) & 7u) * 240;   // samples of the finished row (the SILK side's)
   if (m.flags & 128u) {          // SILK -> CELT: the end of the row fades into the second half of the redundancy frame
     for (int i = 0; i < SHORT_MDCT; i++) {
       const float wv = bits2f(kWindow120Bits[i]), w = wv * wv;

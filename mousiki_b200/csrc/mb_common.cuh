@@ -76,6 +76,21 @@ enum {
   FOLD_WORDS = 1248                // fold buffer per stream: the reference's norm_storage, 2 channels x 8 * eband(20) floats
 };
 
+// Auxiliary cells: a few packets decode TWO CELT frames (a hybrid packet with a redundancy frame, a mode switch that first
+// conceals one frame in the old mode); the second one lives in an auxiliary cell, index aux.base + i, handed out from a per-pass
+// pool behind the main cells by whoever finds the need (k_parse, k_energy).
+enum { S_AUXREF = S_SILK_HYB + 343 };   // hybrid cell: (aux cell << 2) | celt_to_silk << 1 | 1 when its redundancy frame sits in an auxiliary cell, else 0
+struct AuxPool { uint32_t base, cap; uint32_t* count; };
+MB_DEV uint32_t aux_alloc(const AuxPool& A) {   // cell index, or 0xffffffff when the pool is spent
+  if (!A.count || A.cap == 0) return 0xffffffffu;
+#if MB_ON_DEVICE
+  const uint32_t i = atomicAdd(A.count, 1u);
+#else
+  const uint32_t i = (*A.count)++;
+#endif
+  return i < A.cap ? A.base + i : 0xffffffffu;
+}
+
 // First PCM element of packet p: row p of the caller's buffer, or (calls cut into frames by mb_host_packets.h) row
 // out_map[2p] at element out_map[2p+1].
 MB_DEV size_t pcm_elem_off(const uint32_t* out_map, uint32_t p, uint32_t stride) {

@@ -43,14 +43,19 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
                     uint32_t pcm_stride, float* pcm, int16_t* pcm16, int32_t* samples_out, uint32_t* final_range_out, int32_t* iy_dbg,
                     float* x_dbg) {
   const uint32_t F = n_lanes * n_ticks;
-  const size_t tiles = (F + 31) / 32;
+  const uint32_t FA = 2 * F;   // main cells, then as many auxiliary cells (mb_common.cuh)
+  const size_t tiles = (FA + 31) / 32;
   std::vector<uint32_t> rec(tiles * REC_SLOTS * 32, 0);
   std::vector<StreamState> st(n_lanes);
   for (auto& s : st) stream_state_reset(s);
   std::vector<float> hist((size_t)n_lanes * CC * HIST_G, 0.f);
-  std::vector<float> en((size_t)F * EN_STRIDE, 0.f);
-  std::vector<FrameMeta> meta(F);
-  const uint32_t series_stride = SER_PREFIX + n_ticks * MAX_N + SER_SLACK;
+  std::vector<float> en((size_t)FA * EN_STRIDE, 0.f);
+  std::vector<FrameMeta> meta(FA);
+  std::vector<uint32_t> order((size_t)2 * F, 0), order_n(n_lanes, 0), side_of(F, 0xffffffffu);
+  uint32_t aux_count = 0;
+  AuxPool aux = {F, F, &aux_count};
+  for (uint32_t a = F; a < FA; a++) { rec[rec_index(a, S_STATUS)] = 1u << 15; meta[a].flags = 0; }
+  const uint32_t series_stride = SER_PREFIX + n_ticks * (MAX_N + 2 * SHORT_MDCT) + SER_SLACK;
   std::vector<float> series((size_t)n_lanes * CC * series_stride, 0.f);
   const int disable_inv = CC == 1;
   // phase 1
@@ -60,25 +65,37 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   // phase 2a
   Team tm = {0, 1};
   EnergySmem esm;
-  for (uint32_t j = 0; j < n_lanes; j++)
-    celt_energy_stream(tm, &esm, j, n_lanes, n_ticks, nullptr, rec.data(), st.data(), nullptr, en.data(), meta.data(), samples_out, final_range_out, quirks,
-                       g_flags, getenv("MB_EMUL_PARALLEL_BANDS") ? 0 : 1,   // default: the per-stream band pass of large calls
-                       g_gain_q8 != 0 || !pcm16, CC);
+  EnergyParams eq;
+  eq.n_lanes = n_lanes; eq.n_ticks = n_ticks; eq.pkt_map = nullptr; eq.rec = rec.data(); eq.st_all = st.data(); eq.lane_stream = nullptr;
+  eq.en = en.data(); eq.meta = meta.data(); eq.samples_out = samples_out; eq.final_range_out = final_range_out; eq.quirks = quirks;
+  eq.flags = g_flags; eq.serial_all = getenv("MB_EMUL_PARALLEL_BANDS") ? 0 : 1;   // default: the per-stream band pass of large calls
+  eq.force_float_row = g_gain_q8 != 0 || !pcm16; eq.CC = CC; eq.order = order.data(); eq.order_n = order_n.data(); eq.side_of = side_of.data();
+  eq.aux = aux;
+  for (uint32_t j = 0; j < n_lanes; j++) celt_energy_stream(tm, &esm, j, eq);
   // phase 2b
-  std::vector<float> xbuf((size_t)F * XBUF_STRIDE, 0.f), xstage(2 * MAX_N);
+  std::vector<float> xbuf((size_t)FA * XBUF_STRIDE, 0.f), xstage(2 * MAX_N);
   PvqParams pq; pq.rec = rec.data(); pq.meta = meta.data(); pq.xbuf = xbuf.data(); pq.iy_dbg = iy_dbg;
-  for (uint32_t f = 0; f < F; f++) celt_pvq_frame(tm, xstage.data(), f, pq);
+  for (uint32_t f = 0; f < FA; f++) {
+    if (f >= F) pq.iy_dbg = nullptr;
+    celt_pvq_frame(tm, xstage.data(), f, pq);
+  }
   PlanParams pl; pl.rec = rec.data(); pl.en = en.data(); pl.meta = meta.data();
-  for (uint32_t f = 0; f < F; f++) celt_plan_frame(f, pl);
+  for (uint32_t f = 0; f < FA; f++) celt_plan_frame(f, pl);
   BandsSmem* bsm = new BandsSmem;
   BandsParams bp; bp.rec = rec.data(); bp.en = en.data(); bp.meta = meta.data(); bp.xbuf = xbuf.data(); bp.x_dbg = x_dbg;
   std::vector<float> fold((size_t)n_lanes * FOLD_WORDS, 0.f);
   bp.fold_all = fold.data();
-  for (uint32_t f = 0; f < F; f++) celt_bands_frame(tm, bsm, f, bp);
-  {  // SILK-side frames: tick order per stream, fold buffer carried in stream state (k_bands_hyb)
-    for (uint32_t f = 0; f < F; f++) {
+  for (uint32_t f = 0; f < FA; f++) {
+    if (f >= F) bp.x_dbg = nullptr;
+    celt_bands_frame(tm, bsm, f, bp);
+  }
+  // SILK-side frames: decode order per stream, fold buffer carried in stream state (k_bands_hyb)
+  for (uint32_t j = 0; j < n_lanes; j++) {
+    float* fb = fold.data() + (size_t)j * FOLD_WORDS;
+    for (uint32_t k = 0; k < order_n[j]; k++) {
+      const uint32_t f = order[(size_t)k * n_lanes + j];
       if (!(meta[f].flags & MB_FL_FOLD)) continue;
-      float* fb = fold.data() + (size_t)(f % n_lanes) * FOLD_WORDS;
+      bp.x_dbg = f >= F ? nullptr : x_dbg;
       memcpy(bsm->norm, fb, FOLD_WORDS * sizeof(float));
       celt_bands_frame(tm, bsm, f, bp, true);
       memcpy(fb, bsm->norm, FOLD_WORDS * sizeof(float));
@@ -88,7 +105,7 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   ImdctSmem* ism = new ImdctSmem;
   ImdctParams ip; ip.rec = rec.data(); ip.meta = meta.data(); ip.xbuf = xbuf.data(); ip.series = series.data();
   ip.series_stride = series_stride; ip.CC = CC;
-  for (uint32_t f = 0; f < F; f++)
+  for (uint32_t f = 0; f < FA; f++)
     for (int u = 0; u < CC; u++) celt_imdct_unit(tm, ism, f, u, ip);
   delete ism;
   // phase 2c
@@ -100,6 +117,7 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   tp.series = series.data(); tp.series_stride = series_stride; tp.n_lanes = n_lanes; tp.n_ticks = n_ticks; tp.CC = CC;
   tp.gain = g_gain_q8 == 0 ? 1.f : (float)exp(0.6931471805599453094 * (double)((3.32192809488736234787f / 5120.0f) * (float)g_gain_q8));
   tp.apply_gain = g_gain_q8 != 0; tp.pcm_f32 = out; tp.pcm_stride = pcm_stride; tp.xbuf = xbuf.data();
+  tp.order = order.data(); tp.order_n = order_n.data(); tp.side_of = side_of.data();
   // SILK-side cells (k_silk): lane per stream, ticks in order
   {
     std::vector<SilkState> sst(n_lanes);
@@ -165,8 +183,13 @@ int emu_op_histogram(int CC, uint32_t quirks, const uint8_t* arena, const uint32
                f >= n_lanes ? nullptr : &st[f].prev_mode);
   Team tm = {0, 1};
   EnergySmem esm;
-  for (uint32_t j = 0; j < n_lanes; j++)
-    celt_energy_stream(tm, &esm, j, n_lanes, n_ticks, nullptr, rec.data(), st.data(), nullptr, en.data(), meta.data(), so.data(), fr.data(), quirks, nullptr, 1, 1);
+  std::vector<uint32_t> order((size_t)2 * F, 0), order_n(n_lanes, 0), side_of(F, 0xffffffffu);
+  EnergyParams eq;
+  eq.n_lanes = n_lanes; eq.n_ticks = n_ticks; eq.pkt_map = nullptr; eq.rec = rec.data(); eq.st_all = st.data(); eq.lane_stream = nullptr;
+  eq.en = en.data(); eq.meta = meta.data(); eq.samples_out = so.data(); eq.final_range_out = fr.data(); eq.quirks = quirks;
+  eq.flags = nullptr; eq.serial_all = 1; eq.force_float_row = 1; eq.CC = CC; eq.order = order.data(); eq.order_n = order_n.data();
+  eq.side_of = side_of.data(); eq.aux = AuxPool{0, 0, nullptr};
+  for (uint32_t j = 0; j < n_lanes; j++) celt_energy_stream(tm, &esm, j, eq);
   std::vector<float> xbuf((size_t)F * XBUF_STRIDE, 0.f), xstage(2 * MAX_N);
   PvqParams pq; pq.rec = rec.data(); pq.meta = meta.data(); pq.xbuf = xbuf.data(); pq.iy_dbg = nullptr;
   for (uint32_t f = 0; f < F; f++) celt_pvq_frame(tm, xstage.data(), f, pq);
