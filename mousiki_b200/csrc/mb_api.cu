@@ -36,7 +36,8 @@ using namespace mb;
 __global__ void __launch_bounds__(128, 7) k_parse(const uint8_t* __restrict__ arena, const uint32_t* __restrict__ offsets,
                                                const uint32_t* __restrict__ pkt_map, uint32_t n_cells, uint32_t* __restrict__ rec, int CC,
                                                uint32_t quirks, int disable_inv, int cap_per_ch, const uint8_t* __restrict__ flags,
-                                               uint32_t n_lanes, const uint32_t* __restrict__ lane_stream, const StreamState* st) {
+                                               uint32_t n_lanes, const uint32_t* __restrict__ lane_stream, const StreamState* st,
+                                               AuxPool aux) {
   uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
   if (f >= n_cells) return;
   uint32_t pkt = pkt_map ? pkt_map[f] : f;
@@ -44,7 +45,7 @@ __global__ void __launch_bounds__(128, 7) k_parse(const uint8_t* __restrict__ ar
   const int32_t* prev_mode = nullptr;
   if (f >= n_lanes) prev_pkt = pkt_map ? pkt_map[f - n_lanes] : f - n_lanes;
   else prev_mode = &st[lane_stream ? lane_stream[f] : f].prev_mode;
-  parse_cell(arena, offsets, pkt, rec + rec_index(f, 0), CC, quirks, disable_inv, cap_per_ch, flags, prev_pkt, prev_mode);
+  parse_cell(arena, offsets, pkt, rec + rec_index(f, 0), CC, quirks, disable_inv, cap_per_ch, flags, prev_pkt, prev_mode, rec, aux);
 }
 
 // one warp per stream, 4 streams per CTA
@@ -931,7 +932,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     float* pcm = pcm_f32 ? pcm_f32 + shift * pcm_stride : nullptr;
     h->prof_begin(BD_K_PARSE, s);
     k_parse<<<(cells + 127) / 128, 128, 0, s>>>(d_arena, offs, map, cells, h->rec.as<uint32_t>(), CC, h->cfg.quirks, h->disable_inv,
-                                                cap_per_ch, flg, n_lanes, d_lane_stream, h->states.as<StreamState>());
+                                                cap_per_ch, flg, n_lanes, d_lane_stream, h->states.as<StreamState>(), aux);
     h->prof_end(s);
     // fork: k_pvq needs nothing but the records, so it runs beside k_energy / k_silk, which keep one lane per stream
     // busy for a long time and leave most of the machine idle. The two per-stream kernels go to a second stream of the

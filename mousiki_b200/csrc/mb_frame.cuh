@@ -21,7 +21,8 @@ namespace mb {
 // used is decided by the stream pass (k_energy), which knows the real prev_mode.
 MB_TBL uint8_t kCeltSilenceFrame[2] = {0xFF, 0xFF};
 MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint32_t pkt, uint32_t* rec_base, int CC, uint32_t quirks,
-                            int disable_inv, int cap_per_ch, const uint8_t* flags, uint32_t prev_pkt, const int32_t* prev_mode) {
+                            int disable_inv, int cap_per_ch, const uint8_t* flags, uint32_t prev_pkt, const int32_t* prev_mode,
+                            uint32_t* rec_all, const AuxPool& aux) {
   if (pkt == 0xffffffffu) { rec_base[S_STATUS * 32] = 1u << 15; return; }
   // bits 4..7 of the flags: the host front end already rejected the packet (mb_host_packets.h: invalid framing,
   // row too small for all its frames); the cell only exists to report the code with the stream's final_range
@@ -79,12 +80,34 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
             rec_base[S_STATUS * 32] = (1u << 14) | (3u << 16) | (1u << 30) | ((uint32_t)((toc & 0x10u) ? 21 : 19) << 8);
             return;
           }
-          int redundancy = 0;
-          if (ec.tell() + 17 + 20 <= 8 * (len - 1)) redundancy = ec.bit_logp(12);
-          if (redundancy) code = MB_UNIMPLEMENTED;           // CELT redundancy frame + cross-fade: next row
-          else {
+          int redundancy = 0, flen = len - 1;
+          const int end = (toc & 0x10u) ? 21 : 19;
+          uint32_t kind = 0;
+          rec_base[S_AUXREF * 32] = 0u;
+          if (ec.tell() + 17 + 20 <= 8 * flen) redundancy = ec.bit_logp(12);
+          if (redundancy) {
+            // a 5 ms CELT frame behind the hybrid frame, for the switch to / from CELT-only (opus_decoder.rs:746-797): its own
+            // range decoder, all bands from 0; it goes to an auxiliary cell (mb_common.cuh)
+            const int celt_to_silk = ec.bit_logp(1);
+            const int bytes = (int)ec.uint_(256) + 2;
+            const int cutoff = flen - bytes;
+            if (bytes > flen) code = MB_BAD_ARG;
+            else if (cutoff * 8 < ec.tell()) code = MB_UNIMPLEMENTED;   // (the reference then conceals the CELT part)
+            else {
+              const uint32_t a = rec_all ? aux_alloc(aux) : 0xffffffffu;
+              if (a == 0xffffffffu) code = MB_UNIMPLEMENTED;            // pool of auxiliary cells spent in this pass
+              else {
+                celt_parse_frame<0>(data + 1 + cutoff, bytes, 1, C, end, quirks, disable_inv, rec_all + rec_index(a, 0));
+                rec_base[S_AUXREF * 32] = (a << 2) | ((uint32_t)celt_to_silk << 1) | 1u;
+                kind = celt_to_silk ? 2u : 3u;
+                ec.shrink((uint32_t)bytes);
+                flen = cutoff;
+              }
+            }
+          }
+          if (code == MB_OK) {
             rec_base[S_SILK_HYB * 32] = 16u | ((uint32_t)(lm == 3 ? 4 : 2) << 5) | (1u << 8) | ((uint32_t)C << 10);
-            celt_parse_frame<17>(data + 1, len - 1, lm, C, (toc & 0x10u) ? 21 : 19, quirks, disable_inv, rec_base, &ec, 3u << 16);
+            celt_parse_frame<17>(data + 1, flen, lm, C, end, quirks, disable_inv, rec_base, &ec, (3u << 16) | (kind << 19));
             return;
           }
         }
@@ -135,8 +158,8 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
 #define MB_ST_LOST_BIT(s) (((s) >> 29) & 1u)
 MB_DEV void parse_cell(const uint8_t* arena, const uint32_t* offsets, uint32_t pkt, uint32_t* rec_base, int CC, uint32_t quirks,
                        int disable_inv, int cap_per_ch, const uint8_t* flags, uint32_t prev_pkt = 0xffffffffu,
-                       const int32_t* prev_mode = nullptr) {
-  parse_cell_body(arena, offsets, pkt, rec_base, CC, quirks, disable_inv, cap_per_ch, flags, prev_pkt, prev_mode);
+                       const int32_t* prev_mode = nullptr, uint32_t* rec_all = nullptr, const AuxPool& aux = AuxPool{0, 0, nullptr}) {
+  parse_cell_body(arena, offsets, pkt, rec_base, CC, quirks, disable_inv, cap_per_ch, flags, prev_pkt, prev_mode, rec_all, aux);
   if (pkt != 0xffffffffu && !(flags && ((flags[pkt] >> 4) || (flags[pkt] & 2u))) && offsets[pkt + 1] > offsets[pkt] &&
       !MB_ST_LOST_BIT(rec_base[S_STATUS * 32]))
     rec_base[S_STATUS * 32] |= (uint32_t)arena[offsets[pkt]] << 21;

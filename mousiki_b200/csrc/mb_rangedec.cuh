@@ -49,6 +49,11 @@ struct RangeDec {
     val = rng - 1u - ((uint32_t)rem >> 1);
     renorm();
   }
+  // the frame ends n bytes earlier than announced (a redundancy frame sits behind it, src/opus_decoder.rs:776-781)
+  MB_MEM void shrink(uint32_t n) {
+    storage -= n;
+    if (offs >= storage) pre = 0u;
+  }
   MB_MEM uint32_t decode(uint32_t ft) {
     ext = rng / ft;
     uint32_t s = val / ext;

@@ -61,7 +61,7 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   // phase 1
   for (uint32_t f = 0; f < F; f++)
     parse_cell(arena, offsets, f, rec.data() + rec_index(f, 0), CC, quirks, disable_inv, (int)(pcm_stride / CC), g_flags,
-               f >= n_lanes ? f - n_lanes : 0xffffffffu, f >= n_lanes ? nullptr : &st[f].prev_mode);
+               f >= n_lanes ? f - n_lanes : 0xffffffffu, f >= n_lanes ? nullptr : &st[f].prev_mode, rec.data(), aux);
   // phase 2a
   Team tm = {0, 1};
   EnergySmem esm;

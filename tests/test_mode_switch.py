@@ -143,3 +143,113 @@ def test_gpu_streams_switching_between_celt_silk_and_hybrid(monkeypatch):
         pg, sg, rg = _decode_gpu(arena, offsets, lanes, ticks, ch, 960, False)
         total += _compare_until_first_rejection(so, sg, ro, rg, po, pg, lanes, ticks, TOL)
     assert total > 300
+
+
+# ---------------------------------------------------------------------------------------------- hybrid packets with redundancy
+def _hyb_red_streams(lanes, ticks, ch, seed, with_celt):
+    """Streams that mix hybrid packets carrying a redundancy frame (tests/golden/hybrid_redundancy_packets.npz, found by
+    tools/gen_hybrid_red_fixture.py: the flag has probability 2^-12 in random bytes) with plain hybrid, SILK-only WB and, if
+    asked, CELT-only packets. Returns (arena, offsets, is_red[ticks * lanes])."""
+    g = np.load(helpers.ROOT / "tests" / "golden" / "hybrid_redundancy_packets.npz")
+    ra, ro = g["arena"], g["offsets"]
+    n_red = len(ro) - 1
+    rng = np.random.default_rng(seed)
+    n_plain = lanes * ticks
+
+    def plain_toc(k, r):
+        if r.integers(0, 3):
+            return hyb_toc(r.integers(0, 2), r.integers(0, 2), r.integers(0, 2))
+        return helpers.silk_toc(2, int(r.integers(0, 2)), bool(r.integers(0, 2)))
+
+    pa, po = helpers.silk_fuzz_grid(n_plain, 1, (30, 140), plain_toc, seed=seed + 1, channels=ch)
+    ca, co = helpers.fuzz_grid(n_plain, 1, (30, 140), lambda t, j, r: helpers.celt_toc(int(r.integers(1, 4)), bool(r.integers(0, 2))), seed=seed + 2)
+    pk, red = [], []
+    for t in range(ticks):
+        for j in range(lanes):
+            k = t * lanes + j
+            u = int(rng.integers(0, 10))
+            if t > 0 and u < 4:
+                i = int(rng.integers(0, n_red))
+                pk.append(ra[ro[i]:ro[i + 1]]); red.append(True)
+            elif with_celt and u < 6:
+                pk.append(ca[co[k]:co[k + 1]]); red.append(False)
+            else:
+                pk.append(pa[po[k]:po[k + 1]]); red.append(False)
+    off = np.zeros(len(pk) + 1, dtype=np.uint32)
+    off[1:] = np.cumsum([len(x) for x in pk])
+    return np.concatenate(pk).astype(np.uint8), off, np.array(red)
+
+
+def _first_diff(po, pe, lanes, red):
+    bad = np.nonzero((po != pe).any(axis=1))[0]
+    p = int(bad[0])
+    d = np.nonzero(po[p] != pe[p])[0]
+    return (f"first differing packet: tick {p // lanes} lane {p % lanes} red={red[p]}, first sample {d[0]} of {len(d)}, "
+            f"max|d|={np.abs(po[p].astype(np.float64) - pe[p]).max()} ({len(bad)} differ: {bad[:12]})")
+
+
+@pytest.mark.parametrize("ch,seed", [(1, 11), (2, 12), (2, 13)])
+def test_emul_hybrid_packets_with_redundancy_frames(ch, seed):
+    """A hybrid packet may end in a 5 ms CELT redundancy frame (opus_decoder.rs:746-797): two CELT frames in one packet, the
+    second one in an auxiliary cell (mb_common.cuh). CELT -> SILK frames run before the packet's own CELT part on the old
+    state, SILK -> CELT ones after a decoder reset; the next packet sees prev_redundancy. Streams of hybrid and SILK-only WB
+    packets: every packet decodes, bit for bit."""
+    lanes, ticks = 8, 9
+    arena, offsets, red = _hyb_red_streams(lanes, ticks, ch, seed, with_celt=False)
+    assert red.sum() >= 15
+    for i16 in (False, True):
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 960, i16=i16)
+        pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, ticks, ch, 960, i16=i16)
+        assert (so > 0).all()
+        assert np.array_equal(so, se), (so.reshape(ticks, lanes), se.reshape(ticks, lanes))
+        assert np.array_equal(ro, re), np.nonzero(ro != re)
+        assert np.array_equal(po, pe), _first_diff(po, pe, lanes, red)
+
+
+def test_emul_hybrid_redundancy_next_to_celt_only_packets():
+    """The same with CELT-only packets in the mix: the switches a redundancy frame covers decode; a stream is followed up to the
+    first switch the product still reports as unimplemented (those that conceal a frame of the old mode)."""
+    lanes, ticks = 16, 10
+    total = red_checked = 0
+    for ch, seed in ((1, 21), (2, 22)):
+        arena, offsets, red = _hyb_red_streams(lanes, ticks, ch, seed, with_celt=True)
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 960)
+        pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, ticks, ch, 960)
+        total += _compare_until_first_rejection(so, se, ro, re, po, pe, lanes, ticks, 0.0)
+        se2 = se.reshape(ticks, lanes)
+        for j in range(lanes):
+            for t in range(ticks):
+                if se2[t, j] < 0:
+                    break
+                red_checked += int(red[t * lanes + j])
+    assert total > 100 and red_checked >= 10, (total, red_checked)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ch,seed", [(1, 31), (2, 32)])
+def test_gpu_hybrid_packets_with_redundancy_frames(ch, seed):
+    """Through the C ABI, in passes of 3 ticks (the auxiliary pool is per pass)."""
+    lanes, ticks = 48, 9
+    arena, offsets, red = _hyb_red_streams(lanes, ticks, ch, seed, with_celt=False)
+    assert red.sum() >= 100
+    for i16 in (False, True):
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 960, i16=i16)
+        pg, sg, rg = _decode_gpu(arena, offsets, lanes, ticks, ch, 960, i16, max_frames_per_pass=3 * lanes)
+        assert (so > 0).all() and np.array_equal(so, sg) and np.array_equal(ro, rg)
+        if i16:
+            assert int(np.abs(po.astype(np.int32) - pg.astype(np.int32)).max()) <= 1
+        else:
+            assert float(np.abs(po - pg).max()) <= TOL
+
+
+@pytest.mark.gpu
+def test_gpu_hybrid_redundancy_next_to_celt_only_packets(monkeypatch):
+    monkeypatch.setenv("MOUSIKI_B200_SERIAL_BANDS", "1")
+    lanes, ticks = 64, 10
+    total = 0
+    for ch, seed in ((1, 41), (2, 42)):
+        arena, offsets, red = _hyb_red_streams(lanes, ticks, ch, seed, with_celt=True)
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 960)
+        pg, sg, rg = _decode_gpu(arena, offsets, lanes, ticks, ch, 960, False)
+        total += _compare_until_first_rejection(so, sg, ro, rg, po, pg, lanes, ticks, TOL)
+    assert total > 300
