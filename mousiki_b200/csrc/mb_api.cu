@@ -237,12 +237,13 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
       x = ser + m.sample_off;
       if (m.flags & 16u) { out = side_row(P.xbuf, f); side = 1; }   // not the packet's audio: kept aside for k_fade
       else {
-        const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
+        const uint32_t fo = row_cell(P, f);
+        const uint32_t p = P.pkt_map ? P.pkt_map[fo] : fo;
         out = P.pcm_f32 ? P.pcm_f32 + pcm_elem_off(P.out_map, p, P.pcm_stride) : nullptr;
       }
       if (m.flags & 4u) d.mem = 0.f;                 // CELT reset before this frame
       if ((m.flags & 8u) && out) hyb = 1;            // hybrid: add to the SILK samples already in the row
-      late_gain = side || (m.flags & (64u | 128u));  // a row that waits for a cross-fade gets its gain there
+      late_gain = side || (m.flags & MB_FL_FADE_ROW);   // a row that waits for k_fade gets its gain there
     }
     const unsigned hyb_mask = __ballot_sync(0xffffffffu, hyb);
     const unsigned late_mask = __ballot_sync(0xffffffffu, late_gain);
@@ -613,7 +614,7 @@ struct bd_handle {
     timeline.push_back({std::string(what) + " " + std::to_string(k), e});
   }
   struct PassOut { bool on = false; char* host_pcm = nullptr; const char* dev_pcm = nullptr; size_t elem = 0; } pass_out;
-  DevBuf states, silk_states, silk_hist, silk_exc, fold, hist, rec, en, meta, series, xbuf, order, side_of, aux_count;
+  DevBuf states, silk_states, silk_hist, silk_exc, fold, hist, rec, en, meta, series, xbuf, order, side_of, aux_count, aux_main;
   // staging for the host-buffer entry points
   DevBuf d_arena, d_offsets, d_pkt_map, d_out_map, d_lane_stream, d_flags, d_pcm, d_pcm16, d_samples, d_range, d_ids, d_dbg_iy, d_dbg_x;
   std::vector<uint32_t> h_pkt_map, h_lane_stream, h_lane_of_stream, h_epoch, h_count, h_tick, v_range;
@@ -718,7 +719,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
 void bd_destroy(bd_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  DevBuf* all[] = {&h->order, &h->side_of, &h->aux_count, &h->states, &h->silk_states, &h->silk_hist, &h->silk_exc, &h->fold, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map, &h->d_out_map,
+  DevBuf* all[] = {&h->order, &h->side_of, &h->aux_count, &h->aux_main, &h->states, &h->silk_states, &h->silk_hist, &h->silk_exc, &h->fold, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map, &h->d_out_map,
                    &h->d_lane_stream, &h->d_flags, &h->d_pcm, &h->d_pcm16, &h->d_samples, &h->d_range, &h->d_ids, &h->d_dbg_iy, &h->d_dbg_x};
   for (DevBuf* b : all) b->release();
   for (auto& sp : h->prof_spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -893,6 +894,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
   CK(h->order.ensure(((size_t)2 * cells_max + n_lanes) * sizeof(uint32_t)));   // [2 * ticks][lanes] cells, then the per-lane counts
   CK(h->side_of.ensure((size_t)cells_max * sizeof(uint32_t)));
   CK(h->aux_count.ensure(sizeof(uint32_t)));
+  CK(h->aux_main.ensure((size_t)aux_cap * sizeof(uint32_t)));
   float* pcm_f32 = d_pcm_f32;
   if (d_pcm_i16) {  // the i16 path decodes to a float scratch, soft-clips, then rounds (src/opus_decoder.rs:1679-1712)
     CK(h->d_pcm.ensure((size_t)n_packets * pcm_stride * sizeof(float)));
@@ -950,6 +952,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     eq.serial_all = h->serial_bands || n_lanes >= 148u * 6u * (uint32_t)BANDS_WARPS;   // one warp per lane fills the band-pass slots
     eq.force_float_row = h->cfg.gain_q8 != 0 || !d_pcm_i16;   // direct int16 from k_silk: only the i16 API without a decode gain
     eq.CC = CC; eq.order = order_p; eq.order_n = order_n_p; eq.side_of = h->side_of.as<uint32_t>(); eq.aux = aux;
+    eq.aux_main = h->aux_main.as<uint32_t>();
     k_energy<<<(n_lanes + ENERGY_WARPS - 1) / ENERGY_WARPS, 32 * ENERGY_WARPS, 0, ss>>>(eq);
     h->prof_end(ss);
     CK(cudaEventRecord(h->ev_join, ss));   // the frame meta and band energies are ready: k_plan may go
@@ -998,6 +1001,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     tp.series_stride = series_stride; tp.n_lanes = n_lanes; tp.n_ticks = nt; tp.CC = CC; tp.gain = h->gain;
     tp.apply_gain = h->cfg.gain_q8 != 0; tp.pcm_f32 = pcm; tp.pcm_stride = pcm_stride; tp.out_map = d_out_map; tp.xbuf = h->xbuf.as<float>();
     tp.order = order_p; tp.order_n = order_n_p; tp.side_of = h->side_of.as<uint32_t>();
+    tp.aux_main = h->aux_main.as<uint32_t>(); tp.aux_base = cells_max;
     h->prof_begin(BD_K_COMB, s);
     k_comb<<<(n_lanes * CC + COMB_WARPS - 1) / COMB_WARPS, 32 * COMB_WARPS, 0, s>>>(tp);
     k_comb_plc<<<n_lanes, 32, 0, s>>>(tp);   // lanes with a frame concealed by pitch repetition (the others leave after one look at their flags)

@@ -74,7 +74,8 @@ struct FrameMeta {
 // time series (the frame that follows conceals by pitch repetition and reads it); 30 concealed CELT frame (lost packet);
 // 31 concealed by pitch repetition (k_comb_plc synthesises it; seed_in carries loss_duration) — without bit 31 a concealed
 // frame is band-shaped noise and runs through k_plan / k_bands / k_imdct like a coded frame (seed_in = noise seed).
-enum : uint32_t { MB_FL_KEEP_TAIL = 1u << 28, MB_FL_PLC = 1u << 30, MB_FL_PLC_PITCH = 1u << 31 };
+// 29: k_fade finishes the packet's row (cross-fade with a side row, then the decode gain): nobody else applies the gain to it.
+enum : uint32_t { MB_FL_KEEP_TAIL = 1u << 28, MB_FL_FADE_ROW = 1u << 29, MB_FL_PLC = 1u << 30, MB_FL_PLC_PITCH = 1u << 31 };
 // S_STATUS bit 29: lost frame (no payload); S_RANGE then holds the number of samples to conceal
 #define MB_ST_LOST(s) (((s) >> 29) & 1u)
 // S_STATUS bit 30: the cell's SILK record comes from the packet's LBRR data (in-band FEC)
@@ -107,6 +108,7 @@ struct EnergyParams {
   int serial_all, force_float_row, CC;
   uint32_t* order; uint32_t* order_n;   // see above; order has room for 2 * n_ticks entries per lane
   uint32_t* side_of;                    // per main cell: the cell whose side row holds the audio k_fade blends in (0xffffffff: none)
+  uint32_t* aux_main;                   // per auxiliary cell whose frame belongs in a packet's row: that packet's main cell
   AuxPool aux;
 };
 
@@ -177,7 +179,8 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
           if (!flags || p2 == 0xffffffffu || !(flags[p2] & 4u)) break;
         }
         const uint32_t s2 = rec[rec_index(f2, S_STATUS)];
-        celt_part = MB_ST_DECODED(s2) && (!((s2 >> 16) & 1u) || ((s2 >> 17) & 1u) || ((s2 >> 19) & 3u));
+        celt_part = MB_ST_DECODED(s2) && (!((s2 >> 16) & 1u) || ((s2 >> 17) & 1u) || ((s2 >> 19) & 3u) || (rec[rec_index(f2, S_AUXREF)] & 1u) ||
+                                          (!((s2 >> 18) & 1u) && (rec[rec_index(f2, S_AUXSIL)] & 1u)));
         // (concealment frames come first in their packet: they all see the mode the stream is in now)
         if (MB_ST_LOST(s2) && (st_prev_redundancy || st_prev_mode != 1000)) celt_part = true;
       }
@@ -274,15 +277,21 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
     // CELT -> SILK / SILK -> CELT switch (opus_decoder.rs:746-797, 1012-1080).
     const bool silk_layout = ((status >> 18) & 1u) != 0;
     const int aux = (int)((status >> 19) & 3u);
-    const bool fadeout = aux == 1 && st_prev_mode == 1001;
-    const bool red = aux >= 2;
+    // (40 / 60 ms packets keep the fade-out frame in an auxiliary cell)
+    const uint32_t asil = (silk_bit && !hybrid && !silk_layout) ? r[S_AUXSIL * 32] : 0u;
+    const bool sil_aux = (asil & 1u) != 0;
+    const bool fadeout = (aux == 1 || sil_aux) && st_prev_mode == 1001;
+    // SILK-only cell whose redundancy frame sits in an auxiliary cell (40 / 60 ms packets, packets right after a hybrid one)
+    const uint32_t aref = (silk_bit && !hybrid) ? r[S_AUXREF * 32] : 0u;
+    const bool red_aux = (aref & 1u) != 0;
+    const bool red = aux >= 2 || red_aux;
     const bool silk_only = silk_bit && !hybrid && !fadeout && !red;
     // Mode switches that need concealment (decode_frame(None), opus_decoder.rs:575-593, 798-809) are row F2: reported per
     // packet without touching the stream. A redundancy frame makes the switch clean: CELT -> SILK when the SILK packet
     // carries one, SILK -> CELT when the previous SILK packet ended in one.
     bool reject;
     if (!silk_bit) reject = st_prev_mode == 1001 || (st_prev_mode == 1000 && !st_prev_redundancy);
-    else if (red) reject = !hybrid && st_prev_mode == 1001;   // SILK-only after hybrid: fade-out frame and redundancy frame in one cell
+    else if (red) reject = !hybrid && st_prev_mode == 1001 && !(red_aux && fadeout);   // after hybrid the cell must hold the fade-out frame
     else reject = st_prev_mode == 1002 || (silk_only && st_prev_mode == 1001);
     if (reject) {
       if (lead) {
@@ -447,7 +456,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
     if (hybrid && red) {
       // ---- hybrid packet with a redundancy frame (opus_decoder.rs:746-797, 1012-1080): two CELT frames, the 5 ms redundancy
       // frame (all bands, its own range decoder; parsed into an auxiliary cell) before or after the packet's own.
-      const uint32_t aref = r[S_AUXREF * 32], ac = aref >> 2;
+      const uint32_t aref = r[S_AUXREF * 32], ac = aref >> 3;
       const bool c2s = ((aref >> 1) & 1u) != 0;
       const uint32_t* ra = rec + rec_index((aref & 1u) ? ac : f, 0);
       const uint32_t status_a = ra[S_STATUS * 32];
@@ -460,7 +469,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
       uint32_t red_rng = 0;
       if (c2s) { celt_coded(ac, ra, status_a, 1u | 16u); red_rng = st_rng; }   // on the old CELT state
       if (celt_reset) celt_reset_now();
-      uint32_t fl = 1u | 2u | 8u | (celt_reset ? 4u : 0u) | silk_reset;
+      uint32_t fl = 1u | 2u | 8u | (celt_reset ? 4u : 0u) | silk_reset | MB_FL_FADE_ROW;
       if (!c2s) fl |= 128u;
       else if (st_prev_mode != 1000 || st_prev_redundancy) fl |= 64u;                 // opus_decoder.rs:1066
       const int N = celt_coded(f, r, status, fl);
@@ -478,11 +487,62 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
       }
       continue;
     }
+    // the 2.5 ms fade-out frame after a hybrid packet (opus_decoder.rs:868-893), added onto the start of the packet's row; `own`:
+    // the flags of the packet's own cell besides the CELT bit
+    auto run_silence = [&](uint32_t own) {
+      if (sil_aux) {
+        const uint32_t sc = asil >> 1;
+        const uint32_t* rs = rec + rec_index(sc, 0);
+        celt_coded(sc, rs, rs[S_STATUS * 32], 1u | 8u | (own & MB_FL_FADE_ROW));
+        m.flags = own | 8u | MB_FL_F32ROW;
+        if (lead) { Q.aux_main[sc - Q.aux.base] = f; meta[f] = m; }
+      } else celt_coded(f, r, status, 1u | 8u | own);
+    };
+    if (fadeout && !red && sil_aux) {   // 40 / 60 ms SILK-only packet after a hybrid one
+      silk_side_seen = true; st_fold_serial = 1;
+      run_silence(2u | silk_reset);
+      st_prev_mode = 1000; st_prev_redundancy = 0; st_range_final = silk_rng; st_last_duration = silk_n;
+      if (lead) { samples_out[p] = silk_n; final_range_out[p] = st_range_final; }
+      continue;
+    }
+    if (red_aux) {
+      // ---- SILK-only packet whose redundancy frame sits in an auxiliary cell; its own cell may hold the fade-out frame after a
+      // hybrid packet. Order of the reference (opus_decoder.rs:1012-1046): CELT -> SILK frame, fade-out, SILK -> CELT frame.
+      const uint32_t ac = aref >> 3;
+      const bool c2s = ((aref >> 1) & 1u) != 0;
+      const uint32_t* ra = rec + rec_index(ac, 0);
+      const uint32_t status_a = ra[S_STATUS * 32];
+      if (!MB_ST_DECODED(status_a)) {
+        if (lead) { meta[f] = m; samples_out[p] = MB_ST_CODE(status_a); final_range_out[p] = st_range_final; }
+        pkt_failed = true;
+        continue;
+      }
+      silk_side_seen = true; st_fold_serial = 1;
+      const uint32_t fades = !c2s ? 128u : ((st_prev_mode != 1000 || st_prev_redundancy) ? 64u : 0u);   // opus_decoder.rs:1066
+      const bool with_silence = fadeout && !(c2s && st_prev_redundancy);                                // :868-870
+      const uint32_t own = 2u | silk_reset | fades | MB_FL_FADE_ROW | MB_FL_F32ROW;
+      uint32_t red_rng = 0;
+      if (c2s) { celt_coded(ac, ra, status_a, 1u | 16u); red_rng = st_rng; }
+      if (with_silence) run_silence(own);
+      else { m.flags = own; if (lead) meta[f] = m; }
+      if (!c2s) { celt_reset_now(); celt_coded(ac, ra, status_a, 1u | 16u | 4u); red_rng = st_rng; }
+      if (lead) Q.side_of[f] = ac;
+      const int code = MB_ST_CODE(status_a);
+      if (code < 0) {
+        if (lead) { samples_out[p] = code; final_range_out[p] = st_range_final; }
+      } else {
+        st_prev_mode = 1000; st_prev_redundancy = !c2s;
+        st_range_final = silk_rng ^ red_rng;
+        st_last_duration = silk_n;
+        if (lead) { samples_out[p] = silk_n; final_range_out[p] = st_range_final; }
+      }
+      continue;
+    }
     if (celt_reset) celt_reset_now();
     uint32_t fl;
     if (red) {
       if (lead) Q.side_of[f] = f;
-      fl = 1u | 2u | 16u | (celt_reset ? 4u : 0u) | silk_reset;
+      fl = 1u | 2u | 16u | (celt_reset ? 4u : 0u) | silk_reset | MB_FL_FADE_ROW;
       if (aux == 3) fl |= 128u;
       else if (st_prev_mode != 1000 || st_prev_redundancy) fl |= 64u;   // opus_decoder.rs:1066
     } else fl = (hybrid || fadeout) ? (1u | 2u | 8u | (celt_reset ? 4u : 0u) | silk_reset) : (silk_side_seen ? (1u | 512u) : 1u);

@@ -38,7 +38,11 @@ struct TailParams {
   const uint32_t* order = nullptr;    // the lane's CELT frames in decode order (mb_celt_energy.cuh)
   const uint32_t* order_n = nullptr;
   const uint32_t* side_of = nullptr;  // per main cell: the cell whose side row k_fade blends into the packet's row
+  const uint32_t* aux_main = nullptr; // per auxiliary cell whose frame belongs in a packet's row: that packet's main cell
+  uint32_t aux_base = 0;
 };
+// the cell whose packet row a frame of cell f is written to
+MB_DEV uint32_t row_cell(const TailParams& P, uint32_t f) { return f >= P.n_lanes * P.n_ticks ? P.aux_main[f - P.aux_base] : f; }
 // Side row of a cell: 5 ms of audio that is not the packet's own (a redundancy frame), kept for k_fade. It lives in the upper
 // half of the cell's spectrum row: such a cell's own CELT frame is at most 5 ms long and only uses the first 2 x 240 floats.
 enum { SIDE_OFF = MAX_N };
@@ -213,13 +217,14 @@ MB_DEV void celt_deemph_lane(uint32_t lane, int c, const TailParams& P) {
     float* out;
     if (side) out = side_row(P.xbuf, f) + c;
     else {
-      const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
+      const uint32_t fo = row_cell(P, f);
+      const uint32_t p = P.pkt_map ? P.pkt_map[fo] : fo;
       out = P.pcm_f32 ? P.pcm_f32 + pcm_elem_off(P.out_map, p, P.pcm_stride) + c : nullptr;
     }
     if (m.flags & 4u) d.mem = 0.f;
     const bool accum = (m.flags & 8u) != 0;
     // the decode gain applies once to the finished row: here, unless the row still waits for a cross-fade (k_fade applies it)
-    d.apply_gain = (side || (m.flags & (64u | 128u))) ? 0 : P.apply_gain;
+    d.apply_gain = (side || (m.flags & MB_FL_FADE_ROW)) ? 0 : P.apply_gain;
     for (int j = 0; j < N; j++) {
       const float v = d.step(x[j], accum && out ? out[(size_t)j * CC] : 0.f, accum);
       if (out) out[(size_t)j * CC] = v;
@@ -246,7 +251,8 @@ MB_DEV void celt_fade_cell(uint32_t f, int c, const TailParams& P) {
   const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
   float* row = P.pcm_f32 + pcm_elem_off(P.out_map, p, P.pcm_stride) + c;
   const float* red = side_row(P.xbuf, src) + c;
-  const uint32_t silk_h0 = P.rec[rec_index(f, S_SILK_HYB)];
+  const uint32_t status = P.rec[rec_index(f, S_STATUS)];   // (SILK header: in the hybrid layout, or where 40 / 60 ms packets keep it)
+  const uint32_t silk_h0 = P.rec[rec_index(f, ((status >> 17) & 3u) ? S_SILK_HYB : S_HDR0)];
   const int N = (int)((silk_h0 >> 8) & 3u) * (int)((silk_h0 >> 5) & 7u) * 240;   // samples of the finished row (the SILK side's)
   if (m.flags & 128u) {          // SILK -> CELT: the end of the row fades into the second half of the redundancy frame
     for (int i = 0; i < SHORT_MDCT; i++) {

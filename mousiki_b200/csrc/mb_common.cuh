@@ -79,7 +79,8 @@ enum {
 // Auxiliary cells: a few packets decode TWO CELT frames (a hybrid packet with a redundancy frame, a mode switch that first
 // conceals one frame in the old mode); the second one lives in an auxiliary cell, index aux.base + i, handed out from a per-pass
 // pool behind the main cells by whoever finds the need (k_parse, k_energy).
-enum { S_AUXREF = S_SILK_HYB + 343 };   // hybrid cell: (aux cell << 2) | celt_to_silk << 1 | 1 when its redundancy frame sits in an auxiliary cell, else 0
+enum { S_AUXREF = S_SILK_HYB + 343 };   // SILK-side cell whose redundancy frame sits in an auxiliary cell: (cell << 3) | own silence frame << 2 | celt_to_silk << 1 | 1; else 0
+enum { S_AUXSIL = S_SILK_HYB + 341 };   // 40 / 60 ms SILK cells only (free in their layout): (cell << 1) | 1 = auxiliary cell with the fade-out silence frame
 struct AuxPool { uint32_t base, cap; uint32_t* count; };
 MB_DEV uint32_t aux_alloc(const AuxPool& A) {   // cell index, or 0xffffffff when the pool is spent
   if (!A.count || A.cap == 0) return 0xffffffffu;

@@ -98,7 +98,7 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
               if (a == 0xffffffffu) code = MB_UNIMPLEMENTED;            // pool of auxiliary cells spent in this pass
               else {
                 celt_parse_frame<0>(data + 1 + cutoff, bytes, 1, C, end, quirks, disable_inv, rec_all + rec_index(a, 0));
-                rec_base[S_AUXREF * 32] = (a << 2) | ((uint32_t)celt_to_silk << 1) | 1u;
+                rec_base[S_AUXREF * 32] = (a << 3) | ((uint32_t)celt_to_silk << 1) | 1u;
                 kind = celt_to_silk ? 2u : 3u;
                 ec.shrink((uint32_t)bytes);
                 flen = cutoff;
@@ -120,16 +120,38 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
         SilkRedundancy red;
         const uint32_t st_silk = silk_parse_frame(data + 1, len - 1, toc, quirks, cap_per_ch, rec_base, &red, fec);
         // status bits 19-20: the CELT frame that shares the cell: 1 fade-out silence, 2 redundancy CELT -> SILK (played
-        // before the SILK frame), 3 redundancy SILK -> CELT (after it). A packet that would need two of them (redundancy
-        // right after a hybrid packet) is left to the stream pass, which reports it.
-        if ((st_silk & (1u << 14)) && (st_silk & (1u << 18))) {
+        // before the SILK frame), 3 redundancy SILK -> CELT (after it). Where the cell has no room for the redundancy frame (40 /
+        // 60 ms packets; right after a hybrid packet, when the silence frame takes the place) it goes to an auxiliary cell:
+        // S_AUXREF = (cell << 3) | silence frame in the own cell << 2 | celt_to_silk << 1 | 1.
+        rec_base[S_AUXREF * 32] = 0u;
+        if (st_silk & (1u << 14)) {
           const int C = (toc & 4u) ? 2 : 1, end = ((toc >> 5) & 3u) == 0 ? 13 : 17;   // NB 13, MB / WB 17 (opus_decoder.rs:861-866)
           const uint32_t keep = (1u << 16) | (1u << 18);
-          if (red.bytes > 0)
+          const bool own_room = (st_silk & (1u << 18)) != 0;
+          if (red.bytes > 0 && own_room && !after_hybrid)
             celt_parse_frame<0>(data + 1 + red.cutoff, red.bytes, 1, C, end, quirks, disable_inv, rec_base, nullptr,
                                 keep | ((red.celt_to_silk ? 2u : 3u) << 19));
-          else if (after_hybrid)
-            celt_parse_frame<0>(kCeltSilenceFrame, 2, 0, C, end, quirks, disable_inv, rec_base, nullptr, keep | (1u << 19));
+          else {
+            const bool silence = own_room && after_hybrid;
+            if (red.bytes > 0) {
+              const uint32_t a = rec_all ? aux_alloc(aux) : 0xffffffffu;
+              if (a == 0xffffffffu) {   // pool of auxiliary cells spent in this pass
+                rec_base[S_STATUS * 32] = (st_silk & ~(255u | (1u << 14))) | (uint32_t)(uint8_t)(int8_t)MB_UNIMPLEMENTED;
+                return;
+              }
+              celt_parse_frame<0>(data + 1 + red.cutoff, red.bytes, 1, C, end, quirks, disable_inv, rec_all + rec_index(a, 0));
+              rec_base[S_AUXREF * 32] = (a << 3) | ((uint32_t)silence << 2) | ((uint32_t)red.celt_to_silk << 1) | 1u;
+            }
+            if (silence) celt_parse_frame<0>(kCeltSilenceFrame, 2, 0, C, end, quirks, disable_inv, rec_base, nullptr, keep | (1u << 19));
+            if (!own_room) {   // 40 / 60 ms packet right after a hybrid one: the fade-out frame goes to an auxiliary cell as well
+              rec_base[S_AUXSIL * 32] = 0u;
+              const uint32_t a2 = (after_hybrid && rec_all) ? aux_alloc(aux) : 0xffffffffu;
+              if (a2 != 0xffffffffu) {
+                celt_parse_frame<0>(kCeltSilenceFrame, 2, 0, C, end, quirks, disable_inv, rec_all + rec_index(a2, 0));
+                rec_base[S_AUXSIL * 32] = (a2 << 1) | 1u;
+              }
+            }
+          }
         }
         return;
       }

@@ -427,7 +427,8 @@ MB_DEV void silk_lane(const SilkLaneParams& q, uint32_t lane, SilkWork& W, int32
     // decode gain: once on the finished sum. Hybrid: k_deemph does it for the whole row; fade-out: k_deemph for the first
     // 120 samples, here for the rest; redundancy: k_fade for the whole row
     const bool fadeout = (fl & 8u) && !((status >> 17) & 1u) && !MB_ST_LOST(status);
-    o.CC = q.CC; o.gain = q.gain; o.apply_gain = (shared && !fadeout) ? 0 : q.apply_gain; o.gain_from = fadeout ? SHORT_MDCT : 0;
+    o.CC = q.CC; o.gain = q.gain; o.apply_gain = ((shared && !fadeout) || (fl & MB_FL_FADE_ROW)) ? 0 : q.apply_gain;
+    o.gain_from = fadeout ? SHORT_MDCT : 0;
     SilkPacketCtl ctl;
     ctl.mode = MB_ST_LOST(status) ? SILK_PKT_LOST : (MB_ST_FEC(status) ? SILK_PKT_FEC : SILK_PKT_NORMAL);
     ctl.samples48 = ctl.mode == SILK_PKT_LOST ? (int)rb[S_RANGE * 32] : 0;

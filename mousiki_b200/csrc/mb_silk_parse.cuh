@@ -355,8 +355,7 @@ MB_DEV_NOINLINE uint32_t silk_parse_frame(const uint8_t* data, int len, uint32_t
   // bit tells which side of the mode switch it belongs to, its size is whatever the range coder has not used.
   int code = MB_OK;
   if (!fec && ec.tell() + 17 <= 8 * len) {   // (a packet decoded from its LBRR data takes no redundancy frame, opus_decoder.rs:746)
-    if (!hyb_layout) code = MB_UNIMPLEMENTED;            // 40 / 60 ms packets: the cell has no room for the CELT record
-    else {
+    {   // (40 / 60 ms packets: their cell has no room for the CELT record; the caller parses it into an auxiliary cell)
       red->celt_to_silk = ec.bit_logp(1);
       red->bytes = len - ((ec.tell() + 7) >> 3);
       red->cutoff = len - red->bytes;

@@ -54,6 +54,7 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   std::vector<uint32_t> order((size_t)2 * F, 0), order_n(n_lanes, 0), side_of(F, 0xffffffffu);
   uint32_t aux_count = 0;
   AuxPool aux = {F, F, &aux_count};
+  std::vector<uint32_t> aux_main(F, 0);
   for (uint32_t a = F; a < FA; a++) { rec[rec_index(a, S_STATUS)] = 1u << 15; meta[a].flags = 0; }
   const uint32_t series_stride = SER_PREFIX + n_ticks * (MAX_N + 2 * SHORT_MDCT) + SER_SLACK;
   std::vector<float> series((size_t)n_lanes * CC * series_stride, 0.f);
@@ -70,7 +71,7 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   eq.en = en.data(); eq.meta = meta.data(); eq.samples_out = samples_out; eq.final_range_out = final_range_out; eq.quirks = quirks;
   eq.flags = g_flags; eq.serial_all = getenv("MB_EMUL_PARALLEL_BANDS") ? 0 : 1;   // default: the per-stream band pass of large calls
   eq.force_float_row = g_gain_q8 != 0 || !pcm16; eq.CC = CC; eq.order = order.data(); eq.order_n = order_n.data(); eq.side_of = side_of.data();
-  eq.aux = aux;
+  eq.aux = aux; eq.aux_main = aux_main.data();
   for (uint32_t j = 0; j < n_lanes; j++) celt_energy_stream(tm, &esm, j, eq);
   // phase 2b
   std::vector<float> xbuf((size_t)FA * XBUF_STRIDE, 0.f), xstage(2 * MAX_N);
@@ -117,7 +118,7 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   tp.series = series.data(); tp.series_stride = series_stride; tp.n_lanes = n_lanes; tp.n_ticks = n_ticks; tp.CC = CC;
   tp.gain = g_gain_q8 == 0 ? 1.f : (float)exp(0.6931471805599453094 * (double)((3.32192809488736234787f / 5120.0f) * (float)g_gain_q8));
   tp.apply_gain = g_gain_q8 != 0; tp.pcm_f32 = out; tp.pcm_stride = pcm_stride; tp.xbuf = xbuf.data();
-  tp.order = order.data(); tp.order_n = order_n.data(); tp.side_of = side_of.data();
+  tp.order = order.data(); tp.order_n = order_n.data(); tp.side_of = side_of.data(); tp.aux_main = aux_main.data(); tp.aux_base = F;
   // SILK-side cells (k_silk): lane per stream, ticks in order
   {
     std::vector<SilkState> sst(n_lanes);
@@ -188,7 +189,7 @@ int emu_op_histogram(int CC, uint32_t quirks, const uint8_t* arena, const uint32
   eq.n_lanes = n_lanes; eq.n_ticks = n_ticks; eq.pkt_map = nullptr; eq.rec = rec.data(); eq.st_all = st.data(); eq.lane_stream = nullptr;
   eq.en = en.data(); eq.meta = meta.data(); eq.samples_out = so.data(); eq.final_range_out = fr.data(); eq.quirks = quirks;
   eq.flags = nullptr; eq.serial_all = 1; eq.force_float_row = 1; eq.CC = CC; eq.order = order.data(); eq.order_n = order_n.data();
-  eq.side_of = side_of.data(); eq.aux = AuxPool{0, 0, nullptr};
+  eq.side_of = side_of.data(); eq.aux = AuxPool{0, 0, nullptr}; eq.aux_main = nullptr;
   for (uint32_t j = 0; j < n_lanes; j++) celt_energy_stream(tm, &esm, j, eq);
   std::vector<float> xbuf((size_t)F * XBUF_STRIDE, 0.f), xstage(2 * MAX_N);
   PvqParams pq; pq.rec = rec.data(); pq.meta = meta.data(); pq.xbuf = xbuf.data(); pq.iy_dbg = nullptr;

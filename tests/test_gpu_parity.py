@@ -162,17 +162,18 @@ def test_gpu_cres_known_answer():
 
 
 def test_gpu_unsupported_packets_report_per_packet_codes():
-    """Packets the product cannot decode yet are reported per packet and never poison the batch; a one-byte frame is concealed."""
+    """Odd packets are handled per packet and never poison the batch: a 40 ms SILK packet with a redundancy frame decodes (the
+    frame goes to an auxiliary cell), a one-byte frame is concealed."""
     from mousiki_b200 import BatchDecoder, pack_packets
 
     good = bytes([helpers.celt_toc(3, True)]) + bytes(helpers.lcg_bytes(1, 100))
-    silk = bytes([helpers.silk_toc(2, 2, False)]) + bytes(300)  # SILK WB 40 ms with a CELT redundancy frame: no room in the cell
+    silk = bytes([helpers.silk_toc(2, 2, False)]) + bytes(300)  # SILK WB 40 ms with a CELT redundancy frame
     code1 = bytes([helpers.celt_toc(2, False), 0x55])  # one payload byte: a concealment frame (src/opus_decoder.rs:491)
     arena, offsets = pack_packets([good, silk, code1, good])
     with BatchDecoder(4, 48000, 2) as dec:
         pcm, samples, rng = dec.decode_float(arena, offsets, np.arange(4, dtype=np.uint32), 1920)
     assert samples[0] == 960 and samples[3] == 960
-    assert samples[1] == -5
+    assert samples[1] == 1920
     # the one-byte frame is concealed (row F2): on a fresh decoder that is 10 ms of silence, and final_range 0
     assert samples[2] == 480 and rng[2] == 0 and not pcm[2, :960].any()
     assert np.array_equal(pcm[0], pcm[3]) and rng[0] == rng[3]

@@ -99,18 +99,20 @@ def test_emul_hybrid_silk_switches_both_ways():
             assert np.array_equal(se, so) and np.array_equal(re, ro) and np.array_equal(pe, po)
 
 
-def test_emul_40ms_silk_after_hybrid_is_reported():
-    """The fade-out record shares the cell with ONE SILK frame; a 40 / 60 ms SILK-only packet right after a hybrid
-    packet is reported as -5 and leaves the stream where it was."""
+def test_emul_40ms_silk_after_hybrid_decodes():
+    """A 40 ms SILK-only packet right after a hybrid packet: the cell has no room for the fade-out record next to two SILK
+    frames, so it goes to an auxiliary cell (mb_common.cuh). Bit for bit with the oracle, and so is the hybrid packet behind."""
     good, goff = helpers.silk_fuzz_grid(1, 2, (40, 160), lambda k, r: hyb_toc(1, 1, False), seed=5, channels=1)
     long_a, long_o = helpers.silk_fuzz_grid(1, 1, (60, 120), lambda k, r: helpers.silk_toc(2, 2, False), seed=6, channels=1)
     pk = [good[goff[0]:goff[1]], long_a[long_o[0]:long_o[1]], good[goff[1]:goff[2]]]
     offsets = np.zeros(4, dtype=np.uint32)
     offsets[1:] = np.cumsum([len(p) for p in pk])
-    pe, se, re, _, _ = helpers.emul_decode_grid(np.concatenate(pk), offsets, 1, 3, 1, 1920)
-    po, so, ro = helpers.oracle_decode_grid(good, goff, 1, 2, 1, 1920)
-    assert se.tolist() == [960, -5, 960]
-    assert np.array_equal(pe[2], po[1]) and re[2] == ro[1]
+    arena = np.concatenate(pk)
+    for i16 in (False, True):
+        pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, 1, 3, 1, 1920, i16=i16)
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, 1, 3, 1, 1920, i16=i16)
+        assert se.tolist() == [960, 1920, 960] == so.tolist()
+        assert np.array_equal(pe, po) and np.array_equal(re, ro)
 
 
 # ---------------------------------------------------------------------------------------------- GPU

@@ -253,3 +253,73 @@ def test_gpu_hybrid_redundancy_next_to_celt_only_packets(monkeypatch):
         pg, sg, rg = _decode_gpu(arena, offsets, lanes, ticks, ch, 960, False)
         total += _compare_until_first_rejection(so, sg, ro, rg, po, pg, lanes, ticks, TOL)
     assert total > 300
+
+
+# ---------------------------------------------------------------------------------------------- redundancy frames in auxiliary cells
+LONG_SILK_CASES = [
+    ("wb 40 ms mono", lambda k, r: helpers.silk_toc(2, 2, False), (40, 200), 1, 51),
+    ("wb 60 ms stereo", lambda k, r: helpers.silk_toc(2, 3, True), (200, 500), 2, 52),
+    ("nb/mb 10-60 ms mixed", lambda k, r: helpers.silk_toc(int(r.integers(0, 2)), int(r.integers(0, 4)), bool(r.integers(0, 2))), (10, 200), 2, 53),
+]
+
+
+@pytest.mark.parametrize("name,toc,payload,ch,seed", LONG_SILK_CASES, ids=[c[0] for c in LONG_SILK_CASES])
+def test_emul_40_and_60_ms_silk_packets_with_redundancy_frames(name, toc, payload, ch, seed):
+    lanes, ticks = 8, 6
+    arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, payload, toc, seed=seed, channels=ch, redundancy=True)
+    assert _n_redundant(arena, offsets, ch) >= 5, "corpus must carry redundancy frames"
+    for i16 in (False, True):
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 2880, i16=i16)
+        pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, ticks, ch, 2880, i16=i16)
+        assert (so > 0).all()
+        assert np.array_equal(so, se) and np.array_equal(ro, re)
+        assert np.array_equal(po, pe), _first_diff(po, pe, lanes, np.zeros(len(so), dtype=bool))
+
+
+def _silk_red_or_hybrid(k, r):
+    """SILK-only WB packets (most of them with a redundancy frame: any packet with 17 spare bits has one) next to hybrid ones:
+    SILK-only right after hybrid needs the fade-out frame AND the redundancy frame."""
+    if r.integers(0, 2):
+        return helpers.silk_toc(2, int(r.integers(0, 4)), bool(r.integers(0, 2)))
+    return hyb_toc(r.integers(0, 2), r.integers(0, 2), r.integers(0, 2))
+
+
+def test_emul_silk_redundancy_right_after_hybrid():
+    lanes, ticks = 12, 10
+    total = 0
+    for ch, seed in ((1, 61), (2, 62)):
+        arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, (30, 200), _silk_red_or_hybrid, seed=seed, channels=ch, redundancy=True)
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 2880)
+        pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, ticks, ch, 2880)
+        total += _compare_until_first_rejection(so, se, ro, re, po, pe, lanes, ticks, 0.0)
+        print(ch, "rejected by the product:", int((se < 0).sum()), "of", len(se))
+    assert total > 200
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,toc,payload,ch,seed", LONG_SILK_CASES, ids=[c[0] for c in LONG_SILK_CASES])
+def test_gpu_40_and_60_ms_silk_packets_with_redundancy_frames(name, toc, payload, ch, seed):
+    lanes, ticks = 40, 6
+    arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, payload, toc, seed=seed + 100, channels=ch, redundancy=True)
+    for i16 in (False, True):
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 2880, i16=i16)
+        pg, sg, rg = _decode_gpu(arena, offsets, lanes, ticks, ch, 2880, i16, max_frames_per_pass=4 * lanes)
+        assert (so > 0).all() and np.array_equal(so, sg) and np.array_equal(ro, rg)
+        if i16:
+            assert int(np.abs(po.astype(np.int32) - pg.astype(np.int32)).max()) <= 1
+        else:
+            assert float(np.abs(po - pg).max()) <= TOL
+
+
+@pytest.mark.gpu
+def test_gpu_silk_redundancy_right_after_hybrid(monkeypatch):
+    monkeypatch.setenv("MOUSIKI_B200_SERIAL_BANDS", "1")
+    lanes, ticks = 48, 10
+    total = 0
+    for ch, seed in ((1, 161), (2, 162)):
+        arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, (30, 200), _silk_red_or_hybrid, seed=seed, channels=ch, redundancy=True)
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 2880)
+        pg, sg, rg = _decode_gpu(arena, offsets, lanes, ticks, ch, 2880, False, max_frames_per_pass=3 * lanes)
+        assert (sg > 0).all()
+        total += _compare_until_first_rejection(so, sg, ro, rg, po, pg, lanes, ticks, TOL)
+    assert total == 2 * lanes * ticks
