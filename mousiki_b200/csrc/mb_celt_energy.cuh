@@ -171,7 +171,8 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
     const bool continuation = flags && (flags[p] & 4u);
     if (!continuation) {
       pkt_failed = false;
-      bool celt_part = force_float_row != 0;
+      // (a SILK / hybrid packet right after a CELT-only one fades in from a concealed CELT frame: float row)
+      bool celt_part = force_float_row != 0 || (MB_ST_DECODED(status) && ((status >> 16) & 1u) && st_prev_mode == 1002);
       for (uint32_t t2 = t; t2 < n_ticks && !celt_part; t2++) {
         const uint32_t f2 = t2 * n_lanes + lane;
         if (t2 > t) {
@@ -292,7 +293,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
     bool reject;
     if (!silk_bit) reject = st_prev_mode == 1001 || (st_prev_mode == 1000 && !st_prev_redundancy);
     else if (red) reject = !hybrid && st_prev_mode == 1001 && !(red_aux && fadeout);   // after hybrid the cell must hold the fade-out frame
-    else reject = st_prev_mode == 1002 || (silk_only && st_prev_mode == 1001);
+    else reject = silk_only && st_prev_mode == 1001;
     if (reject) {
       if (lead) {
         meta[f] = m;
@@ -307,9 +308,33 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
     const uint32_t silk_rng = silk_layout ? r[(S_SILK_HYB + 342) * 32] : r[S_RANGE * 32];
     const int silk_n = (int)((silk_h0 >> 8) & 3u) * (int)((silk_h0 >> 5) & 7u) * 240;   // frames x subframes: 2, 4, 8, 12 -> 10 .. 60 ms
     const uint32_t silk_reset = (silk_bit && st_prev_mode == 1002) ? 32u : 0u;          // opus_decoder.rs:694-696
+    // CELT-only -> SILK / hybrid without a redundancy frame (opus_decoder.rs:575-593, 798-809, 1083-1105): the reference conceals
+    // 5 ms in the old mode (celt_decode_lost on the CELT state as it stands) and fades from it into the packet's audio. The
+    // concealed frame goes to an auxiliary cell, its audio to that cell's side row; k_fade blends it in like a CELT -> SILK
+    // redundancy frame.
+    uint32_t trans_flags = 0;
+    if (silk_bit && !red && st_prev_mode == 1002) {
+      uint32_t ac = 0xffffffffu;
+      if (lead) ac = aux_alloc(Q.aux);
+#if MB_ON_DEVICE
+      ac = __shfl_sync(0xffffffffu, ac, 0);
+#endif
+      if (ac == 0xffffffffu) {   // pool of auxiliary cells spent in this pass
+        if (lead) { meta[f] = m; samples_out[p] = MB_UNIMPLEMENTED; final_range_out[p] = st_range_final; }
+        pkt_failed = true;
+        continue;
+      }
+      FrameMeta ma;
+      ma.seed_in = st_rng; ma.sample_off = sample_off; ma.lane = lane; ma.flags = 0;
+      celt_conceal(ac, rec + rec_index(ac, 0), 0u, ma, 2 * SHORT_MDCT, 1, 0, 16u);
+      if (lead) { meta[ac] = ma; Q.side_of[f] = ac; }
+      trans_flags = 64u | MB_FL_FADE_ROW | MB_FL_F32ROW;
+      silk_side_seen = true; st_fold_serial = 1;
+      m.seed_in = st_rng; m.sample_off = sample_off;
+    }
     if (silk_only) {  // SILK-only packet: synthesis runs in k_silk (mb_silk_out.cuh); here only the front-end bookkeeping
       const int N = silk_n;
-      m.flags = 2u | silk_reset | pkt_route;
+      m.flags = 2u | silk_reset | pkt_route | trans_flags;
       st_prev_mode = 1000;
       st_prev_redundancy = 0;
       st_range_final = silk_rng;
@@ -447,7 +472,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
       if (celt_reset) { celt_reset_now(); m.seed_in = 0; }
       const int lmq = (int)MB_H0_LM(h0);
       st_celt_end = (int)MB_ST_END(status);
-      celt_conceal(f, r, status, m, SHORT_MDCT << lmq, lmq, 17, 2u | 8u | (celt_reset ? 4u : 0u) | silk_reset);
+      celt_conceal(f, r, status, m, SHORT_MDCT << lmq, lmq, 17, 2u | 8u | (celt_reset ? 4u : 0u) | silk_reset | trans_flags);
       silk_side_seen = true; st_fold_serial = 1;
       st_prev_mode = 1001; st_prev_redundancy = 0; st_range_final = silk_rng; st_last_duration = SHORT_MDCT << lmq;
       if (lead) { meta[f] = m; samples_out[p] = SHORT_MDCT << lmq; final_range_out[p] = st_range_final; }
@@ -545,7 +570,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
       fl = 1u | 2u | 16u | (celt_reset ? 4u : 0u) | silk_reset | MB_FL_FADE_ROW;
       if (aux == 3) fl |= 128u;
       else if (st_prev_mode != 1000 || st_prev_redundancy) fl |= 64u;   // opus_decoder.rs:1066
-    } else fl = (hybrid || fadeout) ? (1u | 2u | 8u | (celt_reset ? 4u : 0u) | silk_reset) : (silk_side_seen ? (1u | 512u) : 1u);
+    } else fl = (hybrid || fadeout) ? (1u | 2u | 8u | (celt_reset ? 4u : 0u) | silk_reset | trans_flags) : (silk_side_seen ? (1u | 512u) : 1u);
     if (fl & (8u | 16u)) { silk_side_seen = true; st_fold_serial = 1; }
     const int Nc = celt_coded(f, r, status, fl);
     const int N = (fadeout || red) ? silk_n : Nc;   // samples the packet delivers

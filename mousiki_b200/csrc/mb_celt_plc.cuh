@@ -310,6 +310,21 @@ MB_DEV void celt_comb_plc_lane(Team tm, PlcSmem* sm, uint32_t lane, const TailPa
   }
   bool first_celt = true;
   uint32_t total = 0;
+  // A CELT decoder reset clears the decoder's memory: everything in front of the frame must read as zero from then on. The lane
+  // works in place in the series, where the frames in front still wait for the de-emphasis: they are parked in the stream's
+  // history buffer (free while the lane runs) and put back before the next reset / at the end.
+  int reset_at = -(1 << 30), stash_at = 0;
+  bool stashed = false;
+  auto unstash = [&]() {
+    if (!stashed) return;
+    for (int c = 0; c < CC; c++) {
+      const float* hs = P.hist + ((size_t)sid * CC + c) * HIST_G;
+      MB_ROLLED
+      for (int i = tm.tid; i < PLC_HIST; i += tm.n) ser[c][stash_at - PLC_HIST + i] = hs[i];
+    }
+    stashed = false;
+    MB_SYNC();
+  };
   MB_SYNC();
   for (uint32_t k = 0; k < n_frames; k++) {
     const uint32_t f = P.order[(size_t)k * P.n_lanes + lane];
@@ -317,6 +332,19 @@ MB_DEV void celt_comb_plc_lane(Team tm, PlcSmem* sm, uint32_t lane, const TailPa
     const uint32_t* r = P.rec + rec_index(f, 0);
     const uint32_t h0 = r[S_HDR0 * 32], h1 = r[S_HDR1 * 32];
     const int lm = (int)MB_H0_LM(h0), N = SHORT_MDCT << lm;
+    if (m.flags & 4u) {  // CELT decoder reset before this frame
+      unstash();
+      for (int c = 0; c < CC; c++) {
+        float* hs = P.hist + ((size_t)sid * CC + c) * HIST_G;
+        float* x = ser[c] + m.sample_off;
+        MB_ROLLED
+        for (int i = tm.tid; i < PLC_HIST; i += tm.n) { hs[i] = x[i - PLC_HIST]; x[i - PLC_HIST] = 0.f; }
+        StreamState::Pf& pf = st.pf[c];
+        if (tm.tid == 0) { pf.period = pf.period_old = 0; pf.tapset = pf.tapset_old = 0; pf.gain = pf.gain_old = 0.f; }
+      }
+      stashed = true; stash_at = (int)m.sample_off; reset_at = (int)m.sample_off;
+      MB_SYNC();
+    }
     if (m.flags & MB_FL_PLC_PITCH) {
       if (first_celt)   // the overlap region the previous call's last frame left
         for (int c = 0; c < CC; c++)
@@ -348,12 +376,6 @@ MB_DEV void celt_comb_plc_lane(Team tm, PlcSmem* sm, uint32_t lane, const TailPa
       for (int c = 0; c < CC; c++) {
         StreamState::Pf& pf = st.pf[c];
         float* x = ser[c] + m.sample_off;
-        if (m.flags & 4u) {  // CELT decoder reset before this frame
-          MB_ROLLED
-          for (int i = tm.tid; i < PLC_HIST; i += tm.n) x[i - PLC_HIST] = 0.f;
-          if (tm.tid == 0) { pf.period = pf.period_old = 0; pf.tapset = pf.tapset_old = 0; pf.gain = pf.gain_old = 0.f; }
-          MB_SYNC();
-        }
         const int new_pitch = (int)MB_H1_PITCH(h1), new_tapset = (int)MB_H0_TAPSET(h0);
         const float new_gain = 0.09375f * (float)MB_H0_QG1(h0);
         const int p1 = imax(pf.period, COMB_MINPERIOD), p0 = imax(pf.period_old, COMB_MINPERIOD);
@@ -377,10 +399,14 @@ MB_DEV void celt_comb_plc_lane(Team tm, PlcSmem* sm, uint32_t lane, const TailPa
     total = m.sample_off + (uint32_t)N;
   }
   MB_SYNC();
-  for (int c = 0; c < CC; c++) {   // history out: the 2048 samples in front of `total` and the overlap region behind it
+  unstash();
+  for (int c = 0; c < CC; c++) {   // history out: the 2048 samples in front of `total` (zeros in front of a reset) and the overlap region behind it
     float* hist = P.hist + ((size_t)sid * CC + c) * HIST_G;
     MB_ROLLED
-    for (int i = tm.tid; i < HIST_G; i += tm.n) hist[i] = ser[c][(int)total - PLC_HIST + i];
+    for (int i = tm.tid; i < HIST_G; i += tm.n) {
+      const int sidx = (int)total - PLC_HIST + i;
+      hist[i] = sidx < reset_at ? 0.f : ser[c][sidx];
+    }
   }
 }
 

@@ -4,6 +4,7 @@
 // product library links or calls this file; GPU parity proper is tests/test_gpu_parity.py.
 #define MB_EMUL 1
 #include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -73,6 +74,13 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   eq.force_float_row = g_gain_q8 != 0 || !pcm16; eq.CC = CC; eq.order = order.data(); eq.order_n = order_n.data(); eq.side_of = side_of.data();
   eq.aux = aux; eq.aux_main = aux_main.data();
   for (uint32_t j = 0; j < n_lanes; j++) celt_energy_stream(tm, &esm, j, eq);
+  if (getenv("MB_EMUL_DUMP"))   // debug aid: the lanes' frame lists
+    for (uint32_t j = 0; j < n_lanes; j++)
+      for (uint32_t k = 0; k < order_n[j]; k++) {
+        const uint32_t f = order[(size_t)k * n_lanes + j];
+        fprintf(stderr, "lane %u frame %u: cell %u flags %08x off %u seed %u hdr0 %08x status %08x\n", j, k, f, meta[f].flags, meta[f].sample_off,
+                meta[f].seed_in, rec[rec_index(f, S_HDR0)], rec[rec_index(f, S_STATUS)]);
+      }
   // phase 2b
   std::vector<float> xbuf((size_t)FA * XBUF_STRIDE, 0.f), xstage(2 * MAX_N);
   PvqParams pq; pq.rec = rec.data(); pq.meta = meta.data(); pq.xbuf = xbuf.data(); pq.iy_dbg = iy_dbg;
