@@ -144,15 +144,48 @@ __global__ void __launch_bounds__(32 * BANDS_WARPS, 6) k_bands_hyb(BandsParams P
   for (int w = tm.tid; w < (int)FOLD_WORDS; w += 32) fb[w] = my->norm[w];
 }
 
-// one warp per (frame, channel); 4 units per CTA
-constexpr int IMDCT_WARPS = 4;
-__global__ void __launch_bounds__(32 * IMDCT_WARPS) k_imdct(ImdctParams P, uint32_t n_units, uint32_t n_main, uint32_t aux_base) {
-  __shared__ ImdctSmem sm[IMDCT_WARPS];
-  const uint32_t unit = blockIdx.x * IMDCT_WARPS + (threadIdx.x >> 5);
-  if (unit >= n_units) return;
+// one warp per (frame, channel), 8 warps per CTA, a grid of resident CTAs that walk the units (mb_celt_imdct.cuh).
+// The twiddle / window block is packed once per device (k_imdct_tables at bd_create) and every CTA brings it into
+// shared memory with one bulk async copy (cp.async.bulk + mbarrier) before its first unit.
+constexpr int IMDCT_WARPS = 8;
+constexpr int IMDCT_CTAS_PER_SM = 3;
+static __device__ __align__(128) ImdctTables g_imdct_tables;
+__global__ void k_imdct_tables() {
+  for (int i = threadIdx.x; i < 1800; i += blockDim.x) g_imdct_tables.mdct_tw[i] = bits2f(kMdctTwiddles960Bits[i]);
+  for (int i = threadIdx.x; i < 960; i += blockDim.x) g_imdct_tables.fft_tw[i] = bits2f(kFftTwiddles480Bits[i]);
+  for (int i = threadIdx.x; i < 120; i += blockDim.x) g_imdct_tables.window[i] = bits2f(kWindow120Bits[i]);
+}
+struct ImdctCtaSmem {
+  ImdctTables T;
+  ImdctWarpSmem w[IMDCT_WARPS];
+  unsigned long long bar;
+};
+__global__ void __launch_bounds__(32 * IMDCT_WARPS, IMDCT_CTAS_PER_SM) k_imdct(ImdctParams P, uint32_t n_units, uint32_t n_main, uint32_t aux_base) {
+  extern __shared__ __align__(128) unsigned char imdct_smem_raw[];
+  ImdctCtaSmem* S = (ImdctCtaSmem*)imdct_smem_raw;
+  const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&S->bar);
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&S->T);
+    const uint32_t bytes = (uint32_t)sizeof(ImdctTables);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"((const void*)&g_imdct_tables), "r"(bytes), "r"(bar)
+                 : "memory");
+  }
+  {
+    uint32_t done = 0;
+    while (!done)
+      asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(bar) : "memory");
+  }
   Team tm = {(int)(threadIdx.x & 31), 32};
-  const uint32_t nu = (uint32_t)P.CC;
-  celt_imdct_unit(tm, &sm[threadIdx.x >> 5], launch_cell(unit / nu, n_main, aux_base), (int)(unit % nu), P);
+  const uint32_t nu = (uint32_t)P.CC, wp = threadIdx.x >> 5;
+  for (uint32_t unit = blockIdx.x * IMDCT_WARPS + wp; unit < n_units; unit += gridDim.x * IMDCT_WARPS)
+    celt_imdct_unit_w(tm, &S->w[wp], &S->T, launch_cell(unit / nu, n_main, aux_base), (int)(unit % nu), P);
 }
 
 // phase 2c(i): one warp per stream-channel, 4 per CTA
@@ -561,7 +594,7 @@ __global__ void __launch_bounds__(32) k_kat(int what, const uint32_t* __restrict
                                              uint8_t* gbytes, int* rc) {
   __shared__ KatSmem sm;
   Team tm = {(int)threadIdx.x, 32};
-  const int r = kat_run(tm, &sm, what, in, n_in, out, n_out, gbytes);
+  const int r = kat_run(tm, &sm, what, in, n_in, out, n_out, gbytes, &g_imdct_tables);
   if (threadIdx.x == 0) *rc = r;
 }
 
@@ -590,6 +623,7 @@ struct bd_handle {
   bd_config cfg;
   int device = 0;
   int CC = 2;
+  int n_sm = 148;
   int disable_inv = 0;
   float gain = 1.f;
   uint32_t max_frames_per_pass = 0;
@@ -699,6 +733,22 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
     if (cudaEventCreateWithFlags(&h->ev_clip_done[i], cudaEventDisableTiming) != cudaSuccess) return fail(BD_ERR_CUDA);
   if (cudaFuncSetAttribute(k_deemph<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(DE_WARPS * 2 * 32 * (128 + 4) * sizeof(float))) != cudaSuccess)
     return fail(BD_ERR_CUDA);
+  if (cudaFuncSetAttribute(k_imdct, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ImdctCtaSmem)) != cudaSuccess) return fail(BD_ERR_CUDA);
+  {
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, h->device) != cudaSuccess) return fail(BD_ERR_CUDA);
+    h->n_sm = prop.multiProcessorCount;
+  }
+  {   // the packed IMDCT table block of this device, written once (the stream sync below covers it)
+    static std::mutex mu;
+    static bool ready[64] = {false};
+    std::lock_guard<std::mutex> lock(mu);
+    if (h->device >= 64 || !ready[h->device]) {
+      k_imdct_tables<<<1, 256, 0, h->own_stream>>>();
+      if (cudaStreamSynchronize(h->own_stream) != cudaSuccess || cudaGetLastError() != cudaSuccess) return fail(BD_ERR_CUDA);
+      if (h->device < 64) ready[h->device] = true;
+    }
+  }
   if (h->states.ensure((size_t)cfg->n_streams * sizeof(StreamState)) != cudaSuccess) return fail(BD_ERR_ALLOC);
   if (h->hist.ensure((size_t)cfg->n_streams * h->CC * HIST_G * sizeof(float)) != cudaSuccess) return fail(BD_ERR_ALLOC);
   if (h->silk_states.ensure((size_t)cfg->n_streams * sizeof(SilkState)) != cudaSuccess) return fail(BD_ERR_ALLOC);
@@ -855,6 +905,7 @@ int bd_debug_kat(int device, int what, const uint32_t* in, uint32_t n_in, uint32
       cudaMalloc(&d_bytes, 64) == cudaSuccess && cudaMemcpy(d_in, in, (size_t)n_in * 4, cudaMemcpyHostToDevice) == cudaSuccess &&
       cudaMemset(d_out, 0, (size_t)n_out * 4 + 4 + sizeof(int)) == cudaSuccess) {
     int* d_rc = (int*)(d_out + n_out + 1);
+    k_imdct_tables<<<1, 256>>>();
     k_kat<<<1, 32>>>(what, d_in, n_in, d_out, n_out, d_bytes, d_rc);
     if (cudaDeviceSynchronize() == cudaSuccess && cudaMemcpy(out, d_out, (size_t)n_out * 4, cudaMemcpyDeviceToHost) == cudaSuccess &&
         cudaMemcpy(&krc, d_rc, sizeof(int), cudaMemcpyDeviceToHost) == cudaSuccess)
@@ -993,7 +1044,10 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     ip.rec = h->rec.as<uint32_t>(); ip.meta = meta_p; ip.xbuf = h->xbuf.as<float>(); ip.series = h->series.as<float>();
     ip.series_stride = series_stride; ip.CC = CC;
     h->prof_begin(BD_K_IMDCT, s);
-    k_imdct<<<(cells_run * CC + IMDCT_WARPS - 1) / IMDCT_WARPS, 32 * IMDCT_WARPS, 0, s>>>(ip, cells_run * CC, cells, cells_max);
+    {
+      const uint32_t want = (cells_run * CC + IMDCT_WARPS - 1) / IMDCT_WARPS, resident = (uint32_t)(h->n_sm * IMDCT_CTAS_PER_SM);
+      k_imdct<<<want < resident ? want : resident, 32 * IMDCT_WARPS, sizeof(ImdctCtaSmem), s>>>(ip, cells_run * CC, cells, cells_max);
+    }
     h->prof_end(s);
     TailParams tp;
     tp.rec = h->rec.as<uint32_t>(); tp.meta = meta_p; tp.pkt_map = map; tp.lane_stream = d_lane_stream;

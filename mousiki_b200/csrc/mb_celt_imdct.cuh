@@ -187,6 +187,217 @@ MB_DEV void celt_imdct_core(Team tm, ImdctSmem* sm, int lm, int transient) {
   MB_SYNC();
 }
 
+// ---------------------------------------------------------------- warp-resident form: what k_imdct runs
+// The same butterflies in the same order (each one's arithmetic is what parity needs; which thread computes it is free),
+// laid out so that a warp keeps the whole transform in registers.  kiss_fft's input permutation puts input i = 15 r + c
+// (c = d1 + 5 d2) at position d1 * 3L + d2 * L + w(r) of a transform of 15 L points (L = 32 >> shift): lane r of a block
+// therefore pre-rotates 15 consecutive inputs, the radix-4 / radix-2 stages below the radix-3 stage (a transform of L
+// points across the L lanes, one per c) run on warp shuffles, and the radix-3 and radix-5 stages find all their operands
+// in the lane's own 15 registers.  Short blocks of a transient frame take 4 lanes each, so 8 of them fill the warp.
+// Twiddles and the window come from one 11.5 KB block in shared memory that a CTA fetches once with a bulk async copy.
+struct ImdctTables {
+  float mdct_tw[1800];   // kMdctTwiddles960Bits: N = 1920 / 960 / 480 / 240 back to back
+  float fft_tw[960];     // kFftTwiddles480Bits: (re, im) pairs
+  float window[120];     // kWindow120Bits
+};
+static_assert(sizeof(ImdctTables) % 16 == 0, "bulk copies move multiples of 16 bytes");
+
+struct ImdctWarpSmem {
+  float io[MAX_N];       // freq in, time-domain samples out
+  float tail[64];        // see ImdctSmem
+  cpx col[15][32];       // lane-private column between the shuffle stages (rolled loop) and the register stages
+};
+
+#if MB_ON_DEVICE
+enum { MB_NL = 1 };
+#define MB_EACH_LANE(tm, ln) for (int ln = (tm).tid, mb_once_ = 1; mb_once_; mb_once_ = 0)
+#define MB_LIDX(ln) 0
+MB_DEV cpx lane_read(const cpx* snd, int src) {
+  cpx o;
+  o.r = __shfl_sync(0xffffffffu, snd[0].r, src);
+  o.i = __shfl_sync(0xffffffffu, snd[0].i, src);
+  return o;
+}
+#else
+enum { MB_NL = 32 };   // the host emulation walks the 32 lanes of the warp phase by phase
+#define MB_EACH_LANE(tm, ln) for (int ln = 0; ln < 32; ln++)
+#define MB_LIDX(ln) (ln)
+MB_DEV cpx lane_read(const cpx* snd, int src) { return snd[src]; }
+#endif
+
+MB_DEV float neg_if(float x, bool c) { return bits2f(f2bits(x) ^ (c ? 0x80000000u : 0u)); }
+// Output `d` of a radix-4 butterfly whose (twiddled) operands are a0..a3 (kiss_fft.rs kf_bfly4; x - y is x + (-y) exactly).
+MB_DEV cpx r4_mix(cpx a0, cpx a1, cpx a2, cpx a3, int d) {
+  const bool odd = (d & 1) != 0, hi = (d & 2) != 0;
+  cpx A, B, R, o;
+  A.r = a0.r + neg_if(a2.r, odd); A.i = a0.i + neg_if(a2.i, odd);
+  B.r = a1.r + neg_if(a3.r, odd); B.i = a1.i + neg_if(a3.i, odd);
+  R.r = odd ? B.i : B.r;
+  R.i = odd ? -B.r : B.i;
+  o.r = A.r + neg_if(R.r, hi);
+  o.i = A.i + neg_if(R.i, hi);
+  return o;
+}
+MB_DEV cpx tw_at(const ImdctTables* T, int idx) { cpx o; o.r = T->fft_tw[2 * idx]; o.i = T->fft_tw[2 * idx + 1]; return o; }
+// w(r): where lane r's column sits inside its L-point sub-transform (the digit reversal of the stages below radix 3)
+MB_DEV int imdct_lane_w(int r, int shift) {
+  return shift == 0 ? 8 * (r & 3) + 4 * ((r >> 2) & 1) + (r >> 3) : shift == 1 ? 4 * (r & 3) + (r >> 2) : shift == 2 ? 4 * (r & 1) + (r >> 1) : r;
+}
+
+MB_DEV void celt_imdct_core_w(Team tm, ImdctWarpSmem* sm, const ImdctTables* T, int lm, int transient) {
+  const int M = 1 << lm, N = M * SHORT_MDCT;
+  const int nbk = transient ? M : 1;
+  const int shift = transient ? MAX_LM : MAX_LM - lm;
+  const int n2 = 960 >> shift, n4 = n2 >> 1;
+  const int lgL = 5 - shift, L = 1 << lgL;
+  const float* twb = T->mdct_tw + (1920 - (1920 >> shift));
+  const float* X = sm->io;
+  const int pA = 3 - shift;                                   // radix 4, m = 1: the top two bits of r
+  const bool hasB = shift == 0 || shift == 2, hasC = shift <= 1;
+  const int pB = shift == 0 ? 2 : 0;                          // radix 2, m = 4
+  const float t8 = 0.70710678118654752440f;
+  cpx cur[MB_NL], snd[MB_NL], twC[MB_NL];
+  MB_EACH_LANE(tm, ln) {
+    const int r = ln & (L - 1), q = r & 3;
+    const int k = shift == 0 ? 4 * ((r >> 2) & 1) + (r >> 3) : (r >> 2);
+    twC[MB_LIDX(ln)] = tw_at(T, hasC ? q * k * (15 << shift) : 0);
+  }
+  MB_ROLLED
+  for (int c = 0; c < 15; c++) {
+    // pre-rotation (+ conjugate: ifft = conj . fft . conj) of input 15 r + c
+    MB_EACH_LANE(tm, ln) {
+      const int blk = ln >> lgL, r = ln & (L - 1);
+      cpx v; v.r = 0.f; v.i = 0.f;
+      if (blk < nbk) {
+        const int i = 15 * r + c;
+        const float* in = X + blk;          // element k of block b is in[k * nbk]
+        const float x1 = in[(2 * i) * nbk], x2 = in[(n2 - 1 - 2 * i) * nbk];
+        const float t0 = twb[i], t1 = twb[n4 + i];
+        v.r = x2 * t0 + x1 * t1;
+        v.i = -(x1 * t0 - x2 * t1);
+      }
+      snd[MB_LIDX(ln)] = v;
+    }
+    MB_EACH_LANE(tm, ln) {                  // radix 4, m = 1
+      const int base = ln & ~(3 << pA), d = (ln >> pA) & 3;
+      cur[MB_LIDX(ln)] = r4_mix(lane_read(snd, base), lane_read(snd, base | (1 << pA)), lane_read(snd, base | (2 << pA)),
+                                lane_read(snd, base | (3 << pA)), d);
+    }
+    if (hasB) {                             // radix 2, m = 4 (kiss_fft.rs:900-966): the upper half is turned by W8^k first
+      MB_EACH_LANE(tm, ln) {
+        const int r = ln & (L - 1), k = shift == 0 ? (r >> 3) : (r >> 1);
+        cpx v = cur[MB_LIDX(ln)], t = v;
+        if ((ln >> pB) & 1) {
+          if (k == 1) { t.r = (v.r + v.i) * t8; t.i = (v.i - v.r) * t8; }
+          else if (k == 2) { t.r = v.i; t.i = -v.r; }
+          else if (k == 3) { t.r = (v.i - v.r) * t8; t.i = -(v.i + v.r) * t8; }
+        }
+        snd[MB_LIDX(ln)] = t;
+      }
+      MB_EACH_LANE(tm, ln) {
+        const cpx mine = snd[MB_LIDX(ln)], got = lane_read(snd, ln ^ (1 << pB));
+        cur[MB_LIDX(ln)] = ((ln >> pB) & 1) ? c_sub(got, mine) : c_add(mine, got);
+      }
+    }
+    if (hasC) {                             // radix 4, m = 8 (480 points) or m = 4 (240 points): the two low bits of r
+      MB_EACH_LANE(tm, ln) {
+        const cpx v = cur[MB_LIDX(ln)];
+        snd[MB_LIDX(ln)] = (ln & 3) ? c_mul(v, twC[MB_LIDX(ln)]) : v;
+      }
+      MB_EACH_LANE(tm, ln) {
+        const int base = ln & ~3;
+        cur[MB_LIDX(ln)] = r4_mix(lane_read(snd, base), lane_read(snd, base | 1), lane_read(snd, base | 2), lane_read(snd, base | 3), ln & 3);
+      }
+    }
+    MB_EACH_LANE(tm, ln) sm->col[c][ln] = cur[MB_LIDX(ln)];
+  }
+  MB_SYNC();                                // every lane is done reading the input row: the output goes into the same row
+  MB_EACH_LANE(tm, ln) {
+    const int blk = ln >> lgL, r = ln & (L - 1), w = imdct_lane_w(r, shift);
+    if (blk < nbk) {
+      cpx v[15];
+#pragma unroll
+      for (int c = 0; c < 15; c++) v[c] = sm->col[c][ln];
+      {                                     // radix 3, m = L, k = w: p[k] = v[d1], p[m + k] = v[d1 + 5], p[2m + k] = v[d1 + 10]
+        const int fs = 5 << shift;
+        const cpx tw1 = tw_at(T, w * fs), tw2 = tw_at(T, 2 * w * fs);
+        const float epi3i = T->fft_tw[2 * 160 + 1];
+#pragma unroll
+        for (int d1 = 0; d1 < 5; d1++) {
+          const cpx p0 = v[d1];
+          cpx s1 = c_mul(v[d1 + 5], tw1), s2 = c_mul(v[d1 + 10], tw2);
+          cpx s3 = c_add(s1, s2), s0 = c_sub(s1, s2);
+          cpx fm = {p0.r - 0.5f * s3.r, p0.i - 0.5f * s3.i};
+          s0.r *= epi3i; s0.i *= epi3i;
+          cpx f0 = c_add(p0, s3);
+          cpx a = {fm.r + s0.i, fm.i - s0.r}, b = {fm.r - s0.i, fm.i + s0.r};
+          v[d1 + 10] = a; v[d1 + 5] = b; v[d1] = f0;
+        }
+      }
+      const cpx ya = tw_at(T, 96), yb = tw_at(T, 192);
+      float* ob = sm->io + blk * n2;
+      const int lim = nbk > 1 ? 120 : N;
+#pragma unroll
+      for (int d2 = 0; d2 < 3; d2++) {      // radix 5, m = 3L, k = d2 L + w: p[q m + k] = v[q + 5 d2]
+        const int k = d2 * L + w, fs = 1 << shift;
+        cpx* p = v + 5 * d2;
+        cpx s0 = p[0];
+        cpx s1 = c_mul(p[1], tw_at(T, k * fs)), s2 = c_mul(p[2], tw_at(T, 2 * k * fs));
+        cpx s3 = c_mul(p[3], tw_at(T, 3 * k * fs)), s4 = c_mul(p[4], tw_at(T, 4 * k * fs));
+        cpx s7 = c_add(s1, s4), s10 = c_sub(s1, s4), s8 = c_add(s2, s3), s9 = c_sub(s2, s3);
+        cpx f0 = c_add(s0, c_add(s7, s8));
+        cpx s5 = {s0.r + fma32(s7.r, ya.r, s8.r * yb.r), s0.i + fma32(s7.i, ya.r, s8.i * yb.r)};
+        cpx s6 = {fma32(s10.i, ya.i, s9.i * yb.i), -fma32(s10.r, ya.i, s9.r * yb.i)};
+        p[1] = c_sub(s5, s6);
+        p[4] = c_add(s5, s6);
+        cpx s11 = {s0.r + fma32(s7.r, yb.r, s8.r * ya.r), s0.i + fma32(s7.i, yb.r, s8.i * ya.r)};
+        cpx s12 = {fma32(s9.i, ya.i, (-s10.i) * yb.i), fma32(s10.r, yb.i, (-s9.r) * ya.i)};
+        p[2] = c_add(s11, s12);
+        p[3] = c_sub(s11, s12);
+        p[0] = f0;
+        // post-rotation and window fold against the zero-filled overlap
+#pragma unroll
+        for (int d1 = 0; d1 < 5; d1++) {
+          const int j = d1 * 3 * L + k;
+          cpx y = p[d1];
+          y.i = -y.i;
+          const float t0 = twb[j], t1 = twb[n4 + j];
+          const float yr = y.r * t0 + y.i * t1;     // temp[2j]
+          const float yi = y.r * t1 - y.i * t0;     // temp[n2-1-2j]
+#pragma unroll
+          for (int q = 0; q < 2; q++) {
+            const int kk = q ? n2 - 1 - 2 * j : 2 * j;
+            const float val = q ? yi : yr;
+            if (kk < 60) {
+              const float w1 = T->window[59 - kk], w2 = T->window[60 + kk];
+              ob[59 - kk] = 0.f * w2 - val * w1;
+              ob[60 + kk] = 0.f * w1 + val * w2;
+            } else if (60 + kk < lim) {
+              ob[60 + kk] = val;
+            } else if (blk == nbk - 1) {
+              sm->tail[blk * n2 + 60 + kk - N] = val;
+            }
+          }
+        }
+      }
+    }
+  }
+  MB_SYNC();
+}
+
+#if !MB_ON_DEVICE
+static const ImdctTables* imdct_tables_host() {
+  static ImdctTables* t = nullptr;
+  if (!t) {
+    t = new ImdctTables;
+    for (int i = 0; i < 1800; i++) t->mdct_tw[i] = bits2f(kMdctTwiddles960Bits[i]);
+    for (int i = 0; i < 960; i++) t->fft_tw[i] = bits2f(kFftTwiddles480Bits[i]);
+    for (int i = 0; i < 120; i++) t->window[i] = bits2f(kWindow120Bits[i]);
+  }
+  return t;
+}
+#endif
+
 // Unit u of frame f: coded channel u when both the packet and the decoder are stereo, else the single (down-mixed or
 // duplicated) spectrum.
 MB_DEV void celt_imdct_unit(Team tm, ImdctSmem* sm, uint32_t f, int u, const ImdctParams& P) {
@@ -227,6 +438,67 @@ MB_DEV void celt_imdct_unit(Team tm, ImdctSmem* sm, uint32_t f, int u, const Imd
     // behind the frame in the reference's linear history (decode_mem[2048 .. 2168)) and here at the head of the lost
     // frame's own stretch of the time series: 60 unwindowed samples, then zeros (the reference's zero fill, Q2).
     if (meta.flags & MB_FL_KEEP_TAIL)
+      for (int i = tm.tid; i < OVERLAP; i += tm.n) out[N + i] = i < OVERLAP / 2 ? sm->tail[i] : 0.f;
+  }
+}
+
+// The same unit on the warp-resident core: 128-bit row moves when the addresses allow it.
+MB_DEV void celt_imdct_unit_w(Team tm, ImdctWarpSmem* sm, const ImdctTables* T, uint32_t f, int u, const ImdctParams& P) {
+  const FrameMeta meta = P.meta[f];
+  if (!(meta.flags & 1u) || (meta.flags & MB_FL_PLC_PITCH)) return;
+  const uint32_t* r = P.rec + rec_index(f, 0);
+  const uint32_t h0 = r[S_HDR0 * 32], status = r[S_STATUS * 32];
+  const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), start = (int)MB_H0_START(h0), end = (int)MB_ST_END(status);
+  const int transient = (int)MB_H0_TRANSIENT(h0), silence = (int)MB_H0_SILENCE(h0);
+  const int M = 1 << lm, N = M * SHORT_MDCT, CC = P.CC;
+  const int nch = (CC == 2 && C == 2) ? 2 : 1;
+  if (u >= nch) return;
+  const float* xrow = P.xbuf + (size_t)f * XBUF_STRIDE;
+  const int planned = r[S_PLAN * 32] != 0xffffffffu;
+  const int lo = (silence || !planned) ? 0 : M * eband(start), hi = (silence || !planned) ? 0 : M * eband(imin(end, NB_EBANDS));
+  const int downmix = CC == 1 && C == 2;
+  float* X = sm->io;
+  MB_SYNC();                                // (the previous unit of this warp is done with the row)
+  for (int i4 = tm.tid; i4 < N / 4; i4 += tm.n) {
+    const int i = 4 * i4;
+    float4v a = {0.f, 0.f, 0.f, 0.f};
+    if (i < hi && i + 4 > lo) {
+      a = ld_f4(xrow + u * N + i);
+      if (downmix) {
+        const float4v b = ld_f4(xrow + N + i);
+        a.x = 0.5f * (a.x + b.x); a.y = 0.5f * (a.y + b.y); a.z = 0.5f * (a.z + b.z); a.w = 0.5f * (a.w + b.w);
+      }
+      if (i < lo || i + 4 > hi) {
+        if (i + 0 < lo || i + 0 >= hi) a.x = 0.f;
+        if (i + 1 < lo || i + 1 >= hi) a.y = 0.f;
+        if (i + 2 < lo || i + 2 >= hi) a.z = 0.f;
+        if (i + 3 < lo || i + 3 >= hi) a.w = 0.f;
+      }
+    }
+    st_f4(X + i, a);
+  }
+  MB_SYNC();
+  celt_imdct_core_w(tm, sm, T, lm, transient);
+  const float SIG_SAT = 536870911.0f;
+  for (int cc = 0; cc < CC; cc++) {
+    if (nch == 2 && cc != u) continue;
+    float* out = P.series + ((size_t)meta.lane * CC + cc) * P.series_stride + SER_PREFIX + meta.sample_off;
+    if ((((uintptr_t)out) & 15u) == 0) {
+      for (int i4 = tm.tid; i4 < N / 4; i4 += tm.n) {
+        float4v a = ld_f4(X + 4 * i4);
+        a.x = a.x < -SIG_SAT ? -SIG_SAT : (a.x > SIG_SAT ? SIG_SAT : a.x);
+        a.y = a.y < -SIG_SAT ? -SIG_SAT : (a.y > SIG_SAT ? SIG_SAT : a.y);
+        a.z = a.z < -SIG_SAT ? -SIG_SAT : (a.z > SIG_SAT ? SIG_SAT : a.z);
+        a.w = a.w < -SIG_SAT ? -SIG_SAT : (a.w > SIG_SAT ? SIG_SAT : a.w);
+        st_f4(out + 4 * i4, a);
+      }
+    } else {
+      for (int i = tm.tid; i < N; i += tm.n) {
+        float o = X[i];
+        out[i] = o < -SIG_SAT ? -SIG_SAT : (o > SIG_SAT ? SIG_SAT : o);
+      }
+    }
+    if (meta.flags & MB_FL_KEEP_TAIL)       // see celt_imdct_unit
       for (int i = tm.tid; i < OVERLAP; i += tm.n) out[N + i] = i < OVERLAP / 2 ? sm->tail[i] : 0.f;
   }
 }

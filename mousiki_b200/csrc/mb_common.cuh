@@ -208,6 +208,24 @@ MB_DEV float celt_rsqrt(float x) {
 #endif
 }
 MB_DEV float celt_cos_norm(float x) { return (float)cos((double)(0.5f * 3.14159265358979323846f * x)); }
+// 128-bit row moves (16-byte aligned addresses); the host emulation copies four floats
+struct float4v { float x, y, z, w; };
+MB_DEV float4v ld_f4(const float* p) {
+#if MB_ON_DEVICE
+  const float4 t = *(const float4*)p;
+  float4v o = {t.x, t.y, t.z, t.w};
+#else
+  float4v o = {p[0], p[1], p[2], p[3]};
+#endif
+  return o;
+}
+MB_DEV void st_f4(float* p, float4v v) {
+#if MB_ON_DEVICE
+  *(float4*)p = make_float4(v.x, v.y, v.z, v.w);
+#else
+  p[0] = v.x; p[1] = v.y; p[2] = v.z; p[3] = v.w;
+#endif
+}
 MB_DEV int eband(int i) { return kEBands5ms[i]; }
 MB_DEV uint32_t mask_from_bits(int b) { return b <= 0 ? 0u : (b >= 32 ? 0xffffffffu : (1u << b) - 1u); }
 

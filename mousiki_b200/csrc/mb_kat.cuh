@@ -12,10 +12,13 @@ namespace mb {
 union KatSmem {
   CombSmem comb;
   ImdctSmem imdct;
+  ImdctWarpSmem imdct_w;
 };
 
 // `gbytes`: 64 bytes the range decoder can read through its byte path (global memory on the device).
-MB_DEV int kat_run(Team tm, KatSmem* sm, int what, const uint32_t* in, uint32_t n_in, uint32_t* out, uint32_t n_out, uint8_t* gbytes) {
+// `T`: the packed IMDCT table block (shared or global memory on the device).
+MB_DEV int kat_run(Team tm, KatSmem* sm, int what, const uint32_t* in, uint32_t n_in, uint32_t* out, uint32_t n_out, uint8_t* gbytes,
+                   const ImdctTables* T) {
   switch (what) {
     case 1:
       for (uint32_t i = tm.tid; i < n_in && i < n_out; i += tm.n) out[i] = (uint32_t)bitexact_cos((int)in[i]);
@@ -61,6 +64,7 @@ MB_DEV int kat_run(Team tm, KatSmem* sm, int what, const uint32_t* in, uint32_t 
       celt_imdct_core(tm, &sm->imdct, lm, transient);
       MB_SYNC();
       for (int i = tm.tid; i < N && i < (int)n_out; i += tm.n) out[i] = f2bits(sm->imdct.io[i]);
+      for (int i = tm.tid; i < 60 && N + i < (int)n_out; i += tm.n) out[N + i] = f2bits(sm->imdct.tail[i]);
       return 0;
     }
     case 7: {   // RangeDec script, one lane
@@ -95,6 +99,16 @@ MB_DEV int kat_run(Team tm, KatSmem* sm, int what, const uint32_t* in, uint32_t 
           default: return -1;
         }
       }
+      return 0;
+    }
+    case 9: {   // celt_imdct_core_w, the warp-resident form k_imdct runs (same words as case 6)
+      const int lm = (int)in[0], transient = (int)in[1], N = SHORT_MDCT << lm;
+      for (int i = tm.tid; i < N; i += tm.n) sm->imdct_w.io[i] = bits2f(in[2 + i]);
+      MB_SYNC();
+      celt_imdct_core_w(tm, &sm->imdct_w, T, lm, transient);
+      MB_SYNC();
+      for (int i = tm.tid; i < N && i < (int)n_out; i += tm.n) out[i] = f2bits(sm->imdct_w.io[i]);
+      for (int i = tm.tid; i < 60 && N + i < (int)n_out; i += tm.n) out[N + i] = f2bits(sm->imdct_w.tail[i]);
       return 0;
     }
     case 8:

@@ -27,7 +27,7 @@ int emu_kat(int what, const uint32_t* in, uint32_t n_in, uint32_t* out, uint32_t
   static KatSmem sm;
   uint8_t bytes[64];
   Team tm = {0, 1};
-  return kat_run(tm, &sm, what, in, n_in, out, n_out, bytes);
+  return kat_run(tm, &sm, what, in, n_in, out, n_out, bytes, imdct_tables_host());
 }
 
 // decode gain of the following emu_decode_grid calls (Q8 dB, 0 = none; src/opus_decoder.rs:1376-1392)
@@ -111,11 +111,11 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
     }
   }
   delete bsm;
-  ImdctSmem* ism = new ImdctSmem;
+  ImdctWarpSmem* ism = new ImdctWarpSmem;   // the warp-resident form k_imdct runs, its 32 lanes walked phase by phase
   ImdctParams ip; ip.rec = rec.data(); ip.meta = meta.data(); ip.xbuf = xbuf.data(); ip.series = series.data();
   ip.series_stride = series_stride; ip.CC = CC;
   for (uint32_t f = 0; f < FA; f++)
-    for (int u = 0; u < CC; u++) celt_imdct_unit(tm, ism, f, u, ip);
+    for (int u = 0; u < CC; u++) celt_imdct_unit_w(tm, ism, imdct_tables_host(), f, u, ip);
   delete ism;
   // phase 2c
   std::vector<float> tmp;

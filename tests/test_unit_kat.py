@@ -308,11 +308,30 @@ def test_frame_imdct_matches_naive_definition(backend):
         for transient in ([0] if lm == 0 else [0, 1]):
             N = 120 << lm
             freq = np.cos(np.arange(N, dtype=np.float32) * np.float32(0.19)).astype(np.float32)
-            got = w2f(kat(backend, 6, np.concatenate([np.array([lm, transient], dtype=np.uint32), f2w(freq)]), N)).astype(np.float64)
             want = naive_frame_imdct(freq, lm, transient)
             n = 2 * (120 if transient else N)
             tol = 1e-3 + n * 1e-5
-            assert np.abs(got - want).max() < tol, (lm, transient, float(np.abs(got - want).max()))
+            for case in ((6,) if backend == "oracle" else (6, 9)):   # the team form over shared memory, and the warp-resident form k_imdct runs
+                got = w2f(kat(backend, case, np.concatenate([np.array([lm, transient], dtype=np.uint32), f2w(freq)]), N)).astype(np.float64)
+                assert np.abs(got - want).max() < tol, (case, lm, transient, float(np.abs(got - want).max()))
+
+
+@pytest.mark.parametrize("backend", [b for b in BACKENDS if b != "oracle"])
+def test_warp_resident_imdct_is_bit_identical_to_the_team_form(backend):
+    """k_imdct's register / shuffle layout computes every butterfly of src/celt/kiss_fft.rs:900-1340 and the rotations of
+    src/celt/mdct.rs:197-388 with the same operands in the same order as the shared-memory team form: the two agree bit for
+    bit, the 60 samples behind the frame (the overlap region a pitch concealment reads) included."""
+    rng = np.random.default_rng(77)
+    for lm in range(4):
+        for transient in ([0] if lm == 0 else [0, 1]):
+            N = 120 << lm
+            for scale in (1.0, 1e-3, 3e4):
+                freq = (rng.standard_normal(N) * scale).astype(np.float32)
+                freq[rng.integers(0, N, N // 8)] = 0.0
+                words = np.concatenate([np.array([lm, transient], dtype=np.uint32), f2w(freq)])
+                a = kat(backend, 6, words, N + 60)
+                b = kat(backend, 9, words, N + 60)
+                assert np.array_equal(a, b), (lm, transient, scale)
 
 
 # ------------------------------------------------------------------------------------------------ entdec.rs / range.rs
