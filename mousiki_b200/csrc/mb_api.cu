@@ -144,11 +144,12 @@ __global__ void __launch_bounds__(32 * BANDS_WARPS, 6) k_bands_hyb(BandsParams P
   for (int w = tm.tid; w < (int)FOLD_WORDS; w += 32) fb[w] = my->norm[w];
 }
 
-// one warp per (frame, channel), 8 warps per CTA, a grid of resident CTAs that walk the units (mb_celt_imdct.cuh).
+// one warp per (frame, channel), 12 warps per CTA, a grid of resident CTAs that walk the units (mb_celt_imdct.cuh).
 // The twiddle / window block is packed once per device (k_imdct_tables at bd_create) and every CTA brings it into
-// shared memory with one bulk async copy (cp.async.bulk + mbarrier) before its first unit.
-constexpr int IMDCT_WARPS = 8;
-constexpr int IMDCT_CTAS_PER_SM = 3;
+// shared memory with one bulk async copy (cp.async.bulk + mbarrier) before its first unit; a warp fetches the spectrum
+// row of its next unit the same way (two row buffers and two mbarriers per warp) while it transforms the current one.
+constexpr int IMDCT_WARPS = 12;
+constexpr int IMDCT_CTAS_PER_SM = 2;
 static __device__ __align__(128) ImdctTables g_imdct_tables;
 __global__ void k_imdct_tables() {
   for (int i = threadIdx.x; i < 1800; i += blockDim.x) g_imdct_tables.mdct_tw[i] = bits2f(kMdctTwiddles960Bits[i]);
@@ -157,35 +158,74 @@ __global__ void k_imdct_tables() {
 }
 struct ImdctCtaSmem {
   ImdctTables T;
-  ImdctWarpSmem w[IMDCT_WARPS];
-  unsigned long long bar;
+  float row[IMDCT_WARPS][2][IMDCT_ROW];
+  unsigned long long bar_tables;
+  unsigned long long bar_row[IMDCT_WARPS][2];
 };
+static_assert((IMDCT_ROW * sizeof(float)) % 16 == 0, "row buffers are bulk-copy destinations");
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  while (!done)
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(done)
+                 : "r"(bar), "r"(parity)
+                 : "memory");
+}
 __global__ void __launch_bounds__(32 * IMDCT_WARPS, IMDCT_CTAS_PER_SM) k_imdct(ImdctParams P, uint32_t n_units, uint32_t n_main, uint32_t aux_base) {
   extern __shared__ __align__(128) unsigned char imdct_smem_raw[];
   ImdctCtaSmem* S = (ImdctCtaSmem*)imdct_smem_raw;
-  const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&S->bar);
-  if (threadIdx.x == 0) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+  const uint32_t wp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t bar_t = (uint32_t)__cvta_generic_to_shared(&S->bar_tables);
+  const uint32_t bar_r[2] = {(uint32_t)__cvta_generic_to_shared(&S->bar_row[wp][0]), (uint32_t)__cvta_generic_to_shared(&S->bar_row[wp][1])};
+  if (threadIdx.x == 0) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_t));
+  if (lane == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_r[0]));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_r[1]));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
-    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&S->T);
-    const uint32_t bytes = (uint32_t)sizeof(ImdctTables);
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-                 "l"((const void*)&g_imdct_tables), "r"(bytes), "r"(bar)
-                 : "memory");
+  if (threadIdx.x == 0) bulk_g2s((uint32_t)__cvta_generic_to_shared(&S->T), &g_imdct_tables, (uint32_t)sizeof(ImdctTables), bar_t);
+  Team tm = {(int)lane, 32};
+  const uint32_t nu = (uint32_t)P.CC, stride = gridDim.x * IMDCT_WARPS;
+  uint32_t unit = blockIdx.x * IMDCT_WARPS + wp;
+  auto fetch = [&](const ImdctUnit& U, int b) {
+    if (lane == 0) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the row's last readers (generic proxy) come first
+      bulk_g2s((uint32_t)__cvta_generic_to_shared(&S->row[wp][b][0]), U.src, (uint32_t)U.N * 4u, bar_r[b]);
+    }
+  };
+  ImdctUnit cur;
+  cur.src = nullptr;
+  if (unit < n_units) {
+    cur = imdct_unit_plan(launch_cell(unit / nu, n_main, aux_base), (int)(unit % nu), P);
+    if (cur.src) fetch(cur, 0);
   }
-  {
-    uint32_t done = 0;
-    while (!done)
-      asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(bar) : "memory");
+  mbar_wait(bar_t, 0);
+  uint32_t phase[2] = {0, 0};
+  int b = 0;
+  while (unit < n_units) {
+    const uint32_t nxt = unit + stride;
+    ImdctUnit nx;
+    nx.src = nullptr;
+    if (nxt < n_units) {
+      nx = imdct_unit_plan(launch_cell(nxt / nu, n_main, aux_base), (int)(nxt % nu), P);
+      if (nx.src) fetch(nx, b ^ 1);
+    }
+    if (cur.src) {
+      mbar_wait(bar_r[b], phase[b]);
+      phase[b] ^= 1;
+      imdct_unit_run(tm, S->row[wp][b], &S->T, cur, P);
+    }
+    __syncwarp();
+    cur = nx;
+    unit = nxt;
+    b ^= 1;
   }
-  Team tm = {(int)(threadIdx.x & 31), 32};
-  const uint32_t nu = (uint32_t)P.CC, wp = threadIdx.x >> 5;
-  for (uint32_t unit = blockIdx.x * IMDCT_WARPS + wp; unit < n_units; unit += gridDim.x * IMDCT_WARPS)
-    celt_imdct_unit_w(tm, &S->w[wp], &S->T, launch_cell(unit / nu, n_main, aux_base), (int)(unit % nu), P);
 }
 
 // phase 2c(i): one warp per stream-channel, 4 per CTA

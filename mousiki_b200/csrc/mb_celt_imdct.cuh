@@ -190,11 +190,14 @@ MB_DEV void celt_imdct_core(Team tm, ImdctSmem* sm, int lm, int transient) {
 // ---------------------------------------------------------------- warp-resident form: what k_imdct runs
 // The same butterflies in the same order (each one's arithmetic is what parity needs; which thread computes it is free),
 // laid out so that a warp keeps the whole transform in registers.  kiss_fft's input permutation puts input i = 15 r + c
-// (c = d1 + 5 d2) at position d1 * 3L + d2 * L + w(r) of a transform of 15 L points (L = 32 >> shift): lane r of a block
-// therefore pre-rotates 15 consecutive inputs, the radix-4 / radix-2 stages below the radix-3 stage (a transform of L
-// points across the L lanes, one per c) run on warp shuffles, and the radix-3 and radix-5 stages find all their operands
-// in the lane's own 15 registers.  Short blocks of a transient frame take 4 lanes each, so 8 of them fill the warp.
-// Twiddles and the window come from one 11.5 KB block in shared memory that a CTA fetches once with a bulk async copy.
+// (c = d1 + 5 d2) at position d1 * 3L + d2 * L + w of a transform of 15 L points (L = 32 >> shift): lane r of a block
+// therefore pre-rotates 15 consecutive inputs; the radix-4 / radix-2 stages below the radix-3 stage (a transform of L
+// points across the L lanes, one per c) run on warp shuffles — a radix-4 butterfly as two exchange steps (partner two
+// digits away: a0 +- a2, a1 +- a3; then the neighbour: the four outputs), which leaves outputs 1 and 2 in each other's
+// lanes, so that after all stages lane r holds position w = bit-reversed r — and the radix-3 and radix-5 stages find
+// all their operands in the lane's own 15 registers.  Short blocks of a transient frame take 4 lanes each: 8 of them
+// fill the warp.  Twiddles and the window come from one 11.5 KB block in shared memory that a CTA fetches once with a
+// bulk async copy; the spectrum rows arrive the same way, one row ahead of the transform.
 struct ImdctTables {
   float mdct_tw[1800];   // kMdctTwiddles960Bits: N = 1920 / 960 / 480 / 240 back to back
   float fft_tw[960];     // kFftTwiddles480Bits: (re, im) pairs
@@ -202,184 +205,186 @@ struct ImdctTables {
 };
 static_assert(sizeof(ImdctTables) % 16 == 0, "bulk copies move multiples of 16 bytes");
 
-struct ImdctWarpSmem {
-  float io[MAX_N];       // freq in, time-domain samples out
-  float tail[64];        // see ImdctSmem
-  cpx col[15][32];       // lane-private column between the shuffle stages (rolled loop) and the register stages
-};
+enum { IMDCT_ROW = MAX_N + 64 };   // freq in, time-domain samples out, then the 60 samples the last block writes beyond the
+                                   // frame (the reference's overlap region; only a pitch concealment ever reads them)
 
 #if MB_ON_DEVICE
 enum { MB_NL = 1 };
 #define MB_EACH_LANE(tm, ln) for (int ln = (tm).tid, mb_once_ = 1; mb_once_; mb_once_ = 0)
 #define MB_LIDX(ln) 0
-MB_DEV cpx lane_read(const cpx* snd, int src) {
+MB_DEV cpx lane_xchg(const cpx* snd, int ln, int mask) {
   cpx o;
-  o.r = __shfl_sync(0xffffffffu, snd[0].r, src);
-  o.i = __shfl_sync(0xffffffffu, snd[0].i, src);
+  o.r = __shfl_xor_sync(0xffffffffu, snd[0].r, mask);
+  o.i = __shfl_xor_sync(0xffffffffu, snd[0].i, mask);
   return o;
 }
 #else
 enum { MB_NL = 32 };   // the host emulation walks the 32 lanes of the warp phase by phase
 #define MB_EACH_LANE(tm, ln) for (int ln = 0; ln < 32; ln++)
 #define MB_LIDX(ln) (ln)
-MB_DEV cpx lane_read(const cpx* snd, int src) { return snd[src]; }
+MB_DEV cpx lane_xchg(const cpx* snd, int ln, int mask) { return snd[ln ^ mask]; }
 #endif
 
 MB_DEV float neg_if(float x, bool c) { return bits2f(f2bits(x) ^ (c ? 0x80000000u : 0u)); }
-// Output `d` of a radix-4 butterfly whose (twiddled) operands are a0..a3 (kiss_fft.rs kf_bfly4; x - y is x + (-y) exactly).
-MB_DEV cpx r4_mix(cpx a0, cpx a1, cpx a2, cpx a3, int d) {
-  const bool odd = (d & 1) != 0, hi = (d & 2) != 0;
-  cpx A, B, R, o;
-  A.r = a0.r + neg_if(a2.r, odd); A.i = a0.i + neg_if(a2.i, odd);
-  B.r = a1.r + neg_if(a3.r, odd); B.i = a1.i + neg_if(a3.i, odd);
-  R.r = odd ? B.i : B.r;
-  R.i = odd ? -B.r : B.i;
-  o.r = A.r + neg_if(R.r, hi);
-  o.i = A.i + neg_if(R.i, hi);
+// First exchange step of a radix-4 butterfly (kf_bfly4): the lane whose digit has the high bit clear forms a0 + a2 (or
+// a1 + a3), its partner a0 - a2 (a1 - a3).  x - y is x + (-y) exactly.
+MB_DEV cpx r4_step1(cpx own, cpx got, bool hi) {
+  cpx X, Y, o;
+  X.r = hi ? got.r : own.r; X.i = hi ? got.i : own.i;
+  Y.r = hi ? own.r : got.r; Y.i = hi ? own.i : got.i;
+  o.r = X.r + neg_if(Y.r, hi);
+  o.i = X.i + neg_if(Y.i, hi);
+  return o;
+}
+// Second step: (sum02, sum13) -> outputs 0 and 2; (dif02, dif13) -> outputs 1 and 3 (dif13 turned by -i).
+MB_DEV cpx r4_step2(cpx own, cpx got, bool hi, bool lo) {
+  cpx X, Y, Z, o;
+  X.r = lo ? got.r : own.r; X.i = lo ? got.i : own.i;
+  Y.r = lo ? own.r : got.r; Y.i = lo ? own.i : got.i;
+  Z.r = hi ? Y.i : Y.r;
+  Z.i = hi ? -Y.r : Y.i;
+  o.r = X.r + neg_if(Z.r, lo);
+  o.i = X.i + neg_if(Z.i, lo);
   return o;
 }
 MB_DEV cpx tw_at(const ImdctTables* T, int idx) { cpx o; o.r = T->fft_tw[2 * idx]; o.i = T->fft_tw[2 * idx + 1]; return o; }
-// w(r): where lane r's column sits inside its L-point sub-transform (the digit reversal of the stages below radix 3)
-MB_DEV int imdct_lane_w(int r, int shift) {
-  return shift == 0 ? 8 * (r & 3) + 4 * ((r >> 2) & 1) + (r >> 3) : shift == 1 ? 4 * (r & 3) + (r >> 2) : shift == 2 ? 4 * (r & 1) + (r >> 1) : r;
+MB_DEV int bitrev_low(int r, int bits) {
+  int w = 0;
+  for (int b = 0; b < bits; b++) w |= ((r >> b) & 1) << (bits - 1 - b);
+  return w;
 }
 
-MB_DEV void celt_imdct_core_w(Team tm, ImdctWarpSmem* sm, const ImdctTables* T, int lm, int transient) {
+// In place on io[0 .. IMDCT_ROW): N = 120 << lm frequency bins in (short blocks interleaved as the band pass leaves
+// them), N time-domain samples out (clt_mdct_backward against the reference's zero-filled overlap), then the 60
+// unwindowed samples behind the frame.
+MB_DEV void celt_imdct_core_w(Team tm, float* io, const ImdctTables* T, int lm, int transient) {
   const int M = 1 << lm, N = M * SHORT_MDCT;
   const int nbk = transient ? M : 1;
   const int shift = transient ? MAX_LM : MAX_LM - lm;
   const int n2 = 960 >> shift, n4 = n2 >> 1;
   const int lgL = 5 - shift, L = 1 << lgL;
   const float* twb = T->mdct_tw + (1920 - (1920 >> shift));
-  const float* X = sm->io;
   const int pA = 3 - shift;                                   // radix 4, m = 1: the top two bits of r
   const bool hasB = shift == 0 || shift == 2, hasC = shift <= 1;
   const int pB = shift == 0 ? 2 : 0;                          // radix 2, m = 4
   const float t8 = 0.70710678118654752440f;
-  cpx cur[MB_NL], snd[MB_NL], twC[MB_NL];
+  cpx v[MB_NL][15], snd[MB_NL], twC[MB_NL];
+  int kB[MB_NL];
   MB_EACH_LANE(tm, ln) {
-    const int r = ln & (L - 1), q = r & 3;
-    const int k = shift == 0 ? 4 * ((r >> 2) & 1) + (r >> 3) : (r >> 2);
-    twC[MB_LIDX(ln)] = tw_at(T, hasC ? q * k * (15 << shift) : 0);
+    const int r = ln & (L - 1), w = bitrev_low(r, lgL);
+    kB[MB_LIDX(ln)] = ((ln >> pB) & 1) ? (w & 3) : 0;         // the upper operand of the radix-2 stage is turned by W8^k
+    twC[MB_LIDX(ln)] = tw_at(T, hasC ? (r & 3) * (w & (shift == 0 ? 7 : 3)) * (15 << shift) : 0);
   }
-  MB_ROLLED
+#pragma unroll
   for (int c = 0; c < 15; c++) {
     // pre-rotation (+ conjugate: ifft = conj . fft . conj) of input 15 r + c
     MB_EACH_LANE(tm, ln) {
       const int blk = ln >> lgL, r = ln & (L - 1);
-      cpx v; v.r = 0.f; v.i = 0.f;
+      cpx x; x.r = 0.f; x.i = 0.f;
       if (blk < nbk) {
         const int i = 15 * r + c;
-        const float* in = X + blk;          // element k of block b is in[k * nbk]
+        const float* in = io + blk;          // element k of block b is in[k * nbk]
         const float x1 = in[(2 * i) * nbk], x2 = in[(n2 - 1 - 2 * i) * nbk];
         const float t0 = twb[i], t1 = twb[n4 + i];
-        v.r = x2 * t0 + x1 * t1;
-        v.i = -(x1 * t0 - x2 * t1);
+        x.r = x2 * t0 + x1 * t1;
+        x.i = -(x1 * t0 - x2 * t1);
       }
-      snd[MB_LIDX(ln)] = v;
+      snd[MB_LIDX(ln)] = x;
     }
-    MB_EACH_LANE(tm, ln) {                  // radix 4, m = 1
-      const int base = ln & ~(3 << pA), d = (ln >> pA) & 3;
-      cur[MB_LIDX(ln)] = r4_mix(lane_read(snd, base), lane_read(snd, base | (1 << pA)), lane_read(snd, base | (2 << pA)),
-                                lane_read(snd, base | (3 << pA)), d);
-    }
-    if (hasB) {                             // radix 2, m = 4 (kiss_fft.rs:900-966): the upper half is turned by W8^k first
+    MB_EACH_LANE(tm, ln) v[MB_LIDX(ln)][c] = r4_step1(snd[MB_LIDX(ln)], lane_xchg(snd, ln, 2 << pA), ((ln >> (pA + 1)) & 1) != 0);
+    MB_EACH_LANE(tm, ln) snd[MB_LIDX(ln)] = v[MB_LIDX(ln)][c];
+    MB_EACH_LANE(tm, ln)
+      v[MB_LIDX(ln)][c] = r4_step2(snd[MB_LIDX(ln)], lane_xchg(snd, ln, 1 << pA), ((ln >> (pA + 1)) & 1) != 0, ((ln >> pA) & 1) != 0);
+    if (hasB) {                             // radix 2, m = 4 (kiss_fft.rs:900-966)
       MB_EACH_LANE(tm, ln) {
-        const int r = ln & (L - 1), k = shift == 0 ? (r >> 3) : (r >> 1);
-        cpx v = cur[MB_LIDX(ln)], t = v;
-        if ((ln >> pB) & 1) {
-          if (k == 1) { t.r = (v.r + v.i) * t8; t.i = (v.i - v.r) * t8; }
-          else if (k == 2) { t.r = v.i; t.i = -v.r; }
-          else if (k == 3) { t.r = (v.i - v.r) * t8; t.i = -(v.i + v.r) * t8; }
-        }
+        const cpx x = v[MB_LIDX(ln)][c];
+        const int k = kB[MB_LIDX(ln)];
+        const float a = (x.r + x.i) * t8, b = (x.i - x.r) * t8;
+        cpx t;
+        t.r = (k & 1) ? ((k & 2) ? b : a) : ((k & 2) ? x.i : x.r);
+        t.i = (k & 1) ? ((k & 2) ? -a : b) : ((k & 2) ? -x.r : x.i);
         snd[MB_LIDX(ln)] = t;
       }
       MB_EACH_LANE(tm, ln) {
-        const cpx mine = snd[MB_LIDX(ln)], got = lane_read(snd, ln ^ (1 << pB));
-        cur[MB_LIDX(ln)] = ((ln >> pB) & 1) ? c_sub(got, mine) : c_add(mine, got);
+        const cpx mine = snd[MB_LIDX(ln)], got = lane_xchg(snd, ln, 1 << pB);
+        v[MB_LIDX(ln)][c] = ((ln >> pB) & 1) ? c_sub(got, mine) : c_add(mine, got);
       }
     }
     if (hasC) {                             // radix 4, m = 8 (480 points) or m = 4 (240 points): the two low bits of r
       MB_EACH_LANE(tm, ln) {
-        const cpx v = cur[MB_LIDX(ln)];
-        snd[MB_LIDX(ln)] = (ln & 3) ? c_mul(v, twC[MB_LIDX(ln)]) : v;
+        const cpx x = v[MB_LIDX(ln)][c];
+        snd[MB_LIDX(ln)] = (ln & 3) ? c_mul(x, twC[MB_LIDX(ln)]) : x;
       }
-      MB_EACH_LANE(tm, ln) {
-        const int base = ln & ~3;
-        cur[MB_LIDX(ln)] = r4_mix(lane_read(snd, base), lane_read(snd, base | 1), lane_read(snd, base | 2), lane_read(snd, base | 3), ln & 3);
-      }
+      MB_EACH_LANE(tm, ln) v[MB_LIDX(ln)][c] = r4_step1(snd[MB_LIDX(ln)], lane_xchg(snd, ln, 2), (ln & 2) != 0);
+      MB_EACH_LANE(tm, ln) snd[MB_LIDX(ln)] = v[MB_LIDX(ln)][c];
+      MB_EACH_LANE(tm, ln) v[MB_LIDX(ln)][c] = r4_step2(snd[MB_LIDX(ln)], lane_xchg(snd, ln, 1), (ln & 2) != 0, (ln & 1) != 0);
     }
-    MB_EACH_LANE(tm, ln) sm->col[c][ln] = cur[MB_LIDX(ln)];
   }
   MB_SYNC();                                // every lane is done reading the input row: the output goes into the same row
   MB_EACH_LANE(tm, ln) {
-    const int blk = ln >> lgL, r = ln & (L - 1), w = imdct_lane_w(r, shift);
+    const int blk = ln >> lgL, r = ln & (L - 1), w = bitrev_low(r, lgL);
     if (blk < nbk) {
-      cpx v[15];
-#pragma unroll
-      for (int c = 0; c < 15; c++) v[c] = sm->col[c][ln];
+      cpx* p = v[MB_LIDX(ln)];
       {                                     // radix 3, m = L, k = w: p[k] = v[d1], p[m + k] = v[d1 + 5], p[2m + k] = v[d1 + 10]
         const int fs = 5 << shift;
         const cpx tw1 = tw_at(T, w * fs), tw2 = tw_at(T, 2 * w * fs);
         const float epi3i = T->fft_tw[2 * 160 + 1];
 #pragma unroll
         for (int d1 = 0; d1 < 5; d1++) {
-          const cpx p0 = v[d1];
-          cpx s1 = c_mul(v[d1 + 5], tw1), s2 = c_mul(v[d1 + 10], tw2);
+          const cpx p0 = p[d1];
+          cpx s1 = c_mul(p[d1 + 5], tw1), s2 = c_mul(p[d1 + 10], tw2);
           cpx s3 = c_add(s1, s2), s0 = c_sub(s1, s2);
           cpx fm = {p0.r - 0.5f * s3.r, p0.i - 0.5f * s3.i};
           s0.r *= epi3i; s0.i *= epi3i;
           cpx f0 = c_add(p0, s3);
           cpx a = {fm.r + s0.i, fm.i - s0.r}, b = {fm.r - s0.i, fm.i + s0.r};
-          v[d1 + 10] = a; v[d1 + 5] = b; v[d1] = f0;
+          p[d1 + 10] = a; p[d1 + 5] = b; p[d1] = f0;
         }
       }
       const cpx ya = tw_at(T, 96), yb = tw_at(T, 192);
-      float* ob = sm->io + blk * n2;
-      const int lim = nbk > 1 ? 120 : N;
+      float* ob = io + blk * n2 + 60;       // temp[k] of this block lands at ob[k]
 #pragma unroll
       for (int d2 = 0; d2 < 3; d2++) {      // radix 5, m = 3L, k = d2 L + w: p[q m + k] = v[q + 5 d2]
         const int k = d2 * L + w, fs = 1 << shift;
-        cpx* p = v + 5 * d2;
-        cpx s0 = p[0];
-        cpx s1 = c_mul(p[1], tw_at(T, k * fs)), s2 = c_mul(p[2], tw_at(T, 2 * k * fs));
-        cpx s3 = c_mul(p[3], tw_at(T, 3 * k * fs)), s4 = c_mul(p[4], tw_at(T, 4 * k * fs));
+        cpx* q = p + 5 * d2;
+        cpx s0 = q[0];
+        cpx s1 = c_mul(q[1], tw_at(T, k * fs)), s2 = c_mul(q[2], tw_at(T, 2 * k * fs));
+        cpx s3 = c_mul(q[3], tw_at(T, 3 * k * fs)), s4 = c_mul(q[4], tw_at(T, 4 * k * fs));
         cpx s7 = c_add(s1, s4), s10 = c_sub(s1, s4), s8 = c_add(s2, s3), s9 = c_sub(s2, s3);
         cpx f0 = c_add(s0, c_add(s7, s8));
         cpx s5 = {s0.r + fma32(s7.r, ya.r, s8.r * yb.r), s0.i + fma32(s7.i, ya.r, s8.i * yb.r)};
         cpx s6 = {fma32(s10.i, ya.i, s9.i * yb.i), -fma32(s10.r, ya.i, s9.r * yb.i)};
-        p[1] = c_sub(s5, s6);
-        p[4] = c_add(s5, s6);
+        q[1] = c_sub(s5, s6);
+        q[4] = c_add(s5, s6);
         cpx s11 = {s0.r + fma32(s7.r, yb.r, s8.r * ya.r), s0.i + fma32(s7.i, yb.r, s8.i * ya.r)};
         cpx s12 = {fma32(s9.i, ya.i, (-s10.i) * yb.i), fma32(s10.r, yb.i, (-s9.r) * ya.i)};
-        p[2] = c_add(s11, s12);
-        p[3] = c_sub(s11, s12);
-        p[0] = f0;
-        // post-rotation and window fold against the zero-filled overlap
+        q[2] = c_add(s11, s12);
+        q[3] = c_sub(s11, s12);
+        q[0] = f0;
+        // post-rotation: temp[2j] and temp[n2-1-2j].  A short block's upper half lands on the next block's first 60
+        // samples, which that block's fold below rewrites (the reference's zero-filled overlap, Q2); the last block's
+        // upper half is the overlap region behind the frame.
 #pragma unroll
         for (int d1 = 0; d1 < 5; d1++) {
           const int j = d1 * 3 * L + k;
-          cpx y = p[d1];
+          cpx y = q[d1];
           y.i = -y.i;
           const float t0 = twb[j], t1 = twb[n4 + j];
-          const float yr = y.r * t0 + y.i * t1;     // temp[2j]
-          const float yi = y.r * t1 - y.i * t0;     // temp[n2-1-2j]
-#pragma unroll
-          for (int q = 0; q < 2; q++) {
-            const int kk = q ? n2 - 1 - 2 * j : 2 * j;
-            const float val = q ? yi : yr;
-            if (kk < 60) {
-              const float w1 = T->window[59 - kk], w2 = T->window[60 + kk];
-              ob[59 - kk] = 0.f * w2 - val * w1;
-              ob[60 + kk] = 0.f * w1 + val * w2;
-            } else if (60 + kk < lim) {
-              ob[60 + kk] = val;
-            } else if (blk == nbk - 1) {
-              sm->tail[blk * n2 + 60 + kk - N] = val;
-            }
-          }
+          ob[2 * j] = y.r * t0 + y.i * t1;
+          ob[n2 - 1 - 2 * j] = y.r * t1 - y.i * t0;
         }
       }
+    }
+  }
+  MB_SYNC();
+  // window fold of each block's first 60 samples against the zero-filled overlap
+  for (int b = 0; b < nbk; b++) {
+    float* ob = io + b * n2;
+    for (int k = tm.tid; k < 60; k += tm.n) {
+      const float val = ob[60 + k];
+      const float w1 = T->window[59 - k], w2 = T->window[60 + k];
+      ob[59 - k] = 0.f * w2 - val * w1;     // out[i] = x2*w2 - x1*w1 with x2 = 0
+      ob[60 + k] = 0.f * w1 + val * w2;     // out[119-i] = x2*w1 + x1*w2
     }
   }
   MB_SYNC();
@@ -442,50 +447,51 @@ MB_DEV void celt_imdct_unit(Team tm, ImdctSmem* sm, uint32_t f, int u, const Imd
   }
 }
 
-// The same unit on the warp-resident core: 128-bit row moves when the addresses allow it.
-MB_DEV void celt_imdct_unit_w(Team tm, ImdctWarpSmem* sm, const ImdctTables* T, uint32_t f, int u, const ImdctParams& P) {
+// The same unit on the warp-resident core, in two halves so that k_imdct can fetch the next row while this one is
+// transformed: imdct_unit_plan reads the headers (what to fetch), imdct_unit_run transforms the staged row and writes it out.
+struct ImdctUnit {
+  const float* src;      // first spectrum row of the unit in xbuf (nullptr: nothing to do)
+  float* out;            // (meta.lane, channel 0) row position in the time series
+  uint32_t flags;
+  int N, lm, transient, lo, hi, downmix, nch, u;
+};
+MB_DEV ImdctUnit imdct_unit_plan(uint32_t f, int u, const ImdctParams& P) {
+  ImdctUnit U;
+  U.src = nullptr;
   const FrameMeta meta = P.meta[f];
-  if (!(meta.flags & 1u) || (meta.flags & MB_FL_PLC_PITCH)) return;
+  if (!(meta.flags & 1u) || (meta.flags & MB_FL_PLC_PITCH)) return U;
   const uint32_t* r = P.rec + rec_index(f, 0);
   const uint32_t h0 = r[S_HDR0 * 32], status = r[S_STATUS * 32];
   const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), start = (int)MB_H0_START(h0), end = (int)MB_ST_END(status);
-  const int transient = (int)MB_H0_TRANSIENT(h0), silence = (int)MB_H0_SILENCE(h0);
-  const int M = 1 << lm, N = M * SHORT_MDCT, CC = P.CC;
-  const int nch = (CC == 2 && C == 2) ? 2 : 1;
-  if (u >= nch) return;
-  const float* xrow = P.xbuf + (size_t)f * XBUF_STRIDE;
+  const int silence = (int)MB_H0_SILENCE(h0);
+  const int M = 1 << lm, CC = P.CC;
+  U.lm = lm; U.transient = (int)MB_H0_TRANSIENT(h0); U.N = M * SHORT_MDCT; U.u = u; U.flags = meta.flags;
+  U.nch = (CC == 2 && C == 2) ? 2 : 1;
+  if (u >= U.nch) return U;
   const int planned = r[S_PLAN * 32] != 0xffffffffu;
-  const int lo = (silence || !planned) ? 0 : M * eband(start), hi = (silence || !planned) ? 0 : M * eband(imin(end, NB_EBANDS));
-  const int downmix = CC == 1 && C == 2;
-  float* X = sm->io;
-  MB_SYNC();                                // (the previous unit of this warp is done with the row)
-  for (int i4 = tm.tid; i4 < N / 4; i4 += tm.n) {
-    const int i = 4 * i4;
-    float4v a = {0.f, 0.f, 0.f, 0.f};
-    if (i < hi && i + 4 > lo) {
-      a = ld_f4(xrow + u * N + i);
-      if (downmix) {
-        const float4v b = ld_f4(xrow + N + i);
-        a.x = 0.5f * (a.x + b.x); a.y = 0.5f * (a.y + b.y); a.z = 0.5f * (a.z + b.z); a.w = 0.5f * (a.w + b.w);
-      }
-      if (i < lo || i + 4 > hi) {
-        if (i + 0 < lo || i + 0 >= hi) a.x = 0.f;
-        if (i + 1 < lo || i + 1 >= hi) a.y = 0.f;
-        if (i + 2 < lo || i + 2 >= hi) a.z = 0.f;
-        if (i + 3 < lo || i + 3 >= hi) a.w = 0.f;
-      }
-    }
-    st_f4(X + i, a);
-  }
+  U.lo = (silence || !planned) ? 0 : M * eband(start);
+  U.hi = (silence || !planned) ? 0 : M * eband(imin(end, NB_EBANDS));
+  U.downmix = CC == 1 && C == 2;
+  U.out = P.series + ((size_t)meta.lane * CC) * P.series_stride + SER_PREFIX + meta.sample_off;
+  U.src = P.xbuf + (size_t)f * XBUF_STRIDE + u * U.N;
+  return U;
+}
+// io holds the unit's spectrum row (U.src[0 .. N), as fetched); bins outside [lo, hi) are cleared here.
+MB_DEV void imdct_unit_run(Team tm, float* io, const ImdctTables* T, const ImdctUnit& U, const ImdctParams& P) {
+  const int N = U.N, CC = P.CC;
+  if (U.downmix)
+    for (int i = tm.tid; i < N; i += tm.n) io[i] = 0.5f * (io[i] + U.src[N + i]);
+  for (int i = tm.tid; i < U.lo; i += tm.n) io[i] = 0.f;
+  for (int i = (U.hi < U.lo ? U.lo : U.hi) + tm.tid; i < N; i += tm.n) io[i] = 0.f;
   MB_SYNC();
-  celt_imdct_core_w(tm, sm, T, lm, transient);
+  celt_imdct_core_w(tm, io, T, U.lm, U.transient);
   const float SIG_SAT = 536870911.0f;
   for (int cc = 0; cc < CC; cc++) {
-    if (nch == 2 && cc != u) continue;
-    float* out = P.series + ((size_t)meta.lane * CC + cc) * P.series_stride + SER_PREFIX + meta.sample_off;
+    if (U.nch == 2 && cc != U.u) continue;
+    float* out = U.out + (size_t)cc * P.series_stride;
     if ((((uintptr_t)out) & 15u) == 0) {
       for (int i4 = tm.tid; i4 < N / 4; i4 += tm.n) {
-        float4v a = ld_f4(X + 4 * i4);
+        float4v a = ld_f4(io + 4 * i4);
         a.x = a.x < -SIG_SAT ? -SIG_SAT : (a.x > SIG_SAT ? SIG_SAT : a.x);
         a.y = a.y < -SIG_SAT ? -SIG_SAT : (a.y > SIG_SAT ? SIG_SAT : a.y);
         a.z = a.z < -SIG_SAT ? -SIG_SAT : (a.z > SIG_SAT ? SIG_SAT : a.z);
@@ -494,13 +500,21 @@ MB_DEV void celt_imdct_unit_w(Team tm, ImdctWarpSmem* sm, const ImdctTables* T, 
       }
     } else {
       for (int i = tm.tid; i < N; i += tm.n) {
-        float o = X[i];
+        float o = io[i];
         out[i] = o < -SIG_SAT ? -SIG_SAT : (o > SIG_SAT ? SIG_SAT : o);
       }
     }
-    if (meta.flags & MB_FL_KEEP_TAIL)       // see celt_imdct_unit
-      for (int i = tm.tid; i < OVERLAP; i += tm.n) out[N + i] = i < OVERLAP / 2 ? sm->tail[i] : 0.f;
+    if (U.flags & MB_FL_KEEP_TAIL)          // see celt_imdct_unit
+      for (int i = tm.tid; i < OVERLAP; i += tm.n) out[N + i] = i < OVERLAP / 2 ? io[N + i] : 0.f;
   }
+}
+// one unit start to finish (host emulation; the device kernel pipelines the two halves)
+MB_DEV void celt_imdct_unit_w(Team tm, float* io, const ImdctTables* T, uint32_t f, int u, const ImdctParams& P) {
+  const ImdctUnit U = imdct_unit_plan(f, u, P);
+  if (!U.src) return;
+  for (int i = tm.tid; i < U.N; i += tm.n) io[i] = U.src[i];
+  MB_SYNC();
+  imdct_unit_run(tm, io, T, U, P);
 }
 
 }  // namespace mb

@@ -12,7 +12,7 @@ namespace mb {
 union KatSmem {
   CombSmem comb;
   ImdctSmem imdct;
-  ImdctWarpSmem imdct_w;
+  float imdct_row[IMDCT_ROW];
 };
 
 // `gbytes`: 64 bytes the range decoder can read through its byte path (global memory on the device).
@@ -103,12 +103,11 @@ MB_DEV int kat_run(Team tm, KatSmem* sm, int what, const uint32_t* in, uint32_t 
     }
     case 9: {   // celt_imdct_core_w, the warp-resident form k_imdct runs (same words as case 6)
       const int lm = (int)in[0], transient = (int)in[1], N = SHORT_MDCT << lm;
-      for (int i = tm.tid; i < N; i += tm.n) sm->imdct_w.io[i] = bits2f(in[2 + i]);
+      for (int i = tm.tid; i < N; i += tm.n) sm->imdct_row[i] = bits2f(in[2 + i]);
       MB_SYNC();
-      celt_imdct_core_w(tm, &sm->imdct_w, T, lm, transient);
+      celt_imdct_core_w(tm, sm->imdct_row, T, lm, transient);
       MB_SYNC();
-      for (int i = tm.tid; i < N && i < (int)n_out; i += tm.n) out[i] = f2bits(sm->imdct_w.io[i]);
-      for (int i = tm.tid; i < 60 && N + i < (int)n_out; i += tm.n) out[N + i] = f2bits(sm->imdct_w.tail[i]);
+      for (int i = tm.tid; i < N + 60 && i < (int)n_out; i += tm.n) out[i] = f2bits(sm->imdct_row[i]);
       return 0;
     }
     case 8:

@@ -111,12 +111,12 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
     }
   }
   delete bsm;
-  ImdctWarpSmem* ism = new ImdctWarpSmem;   // the warp-resident form k_imdct runs, its 32 lanes walked phase by phase
+  float* ism = new float[IMDCT_ROW];   // the warp-resident form k_imdct runs, its 32 lanes walked phase by phase
   ImdctParams ip; ip.rec = rec.data(); ip.meta = meta.data(); ip.xbuf = xbuf.data(); ip.series = series.data();
   ip.series_stride = series_stride; ip.CC = CC;
   for (uint32_t f = 0; f < FA; f++)
     for (int u = 0; u < CC; u++) celt_imdct_unit_w(tm, ism, imdct_tables_host(), f, u, ip);
-  delete ism;
+  delete[] ism;
   // phase 2c
   std::vector<float> tmp;
   float* out = pcm;
