@@ -226,41 +226,51 @@ MB_DEV cpx lane_xchg(const cpx* snd, int ln, int mask) { return snd[ln ^ mask]; 
 #endif
 
 MB_DEV float neg_if(float x, bool c) { return bits2f(f2bits(x) ^ (c ? 0x80000000u : 0u)); }
-// First exchange step of a radix-4 butterfly (kf_bfly4): the lane whose digit has the high bit clear forms a0 + a2 (or
-// a1 + a3), its partner a0 - a2 (a1 - a3).  x - y is x + (-y) exactly.
+// A radix-4 butterfly (kf_bfly4) as two exchange steps; x - y is x + (-y) exactly and x + y is y + x.
+// Step 1, partner two digits away: the lane whose digit has the high bit clear forms a0 + a2 (or a1 + a3), its partner
+// a0 - a2 (a1 - a3): either way what it received plus or minus what it holds.
 MB_DEV cpx r4_step1(cpx own, cpx got, bool hi) {
-  cpx X, Y, o;
-  X.r = hi ? got.r : own.r; X.i = hi ? got.i : own.i;
-  Y.r = hi ? own.r : got.r; Y.i = hi ? own.i : got.i;
-  o.r = X.r + neg_if(Y.r, hi);
-  o.i = X.i + neg_if(Y.i, hi);
+  cpx o;
+  o.r = got.r + neg_if(own.r, hi);
+  o.i = got.i + neg_if(own.i, hi);
   return o;
 }
-// Second step: (sum02, sum13) -> outputs 0 and 2; (dif02, dif13) -> outputs 1 and 3 (dif13 turned by -i).
-MB_DEV cpx r4_step2(cpx own, cpx got, bool hi, bool lo) {
-  cpx X, Y, Z, o;
-  X.r = lo ? got.r : own.r; X.i = lo ? got.i : own.i;
-  Y.r = lo ? own.r : got.r; Y.i = lo ? own.i : got.i;
-  Z.r = hi ? Y.i : Y.r;
-  Z.i = hi ? -Y.r : Y.i;
-  o.r = X.r + neg_if(Z.r, lo);
-  o.i = X.i + neg_if(Z.i, lo);
+// Step 2, the neighbour: (sum02, sum13) -> outputs 0 and 2; (dif02, dif13) -> outputs 1 and 3 with dif13 turned by -i,
+// which its holder does before sending (r4_turn).
+MB_DEV cpx r4_turn(cpx x, bool c) {
+  cpx o;
+  o.r = c ? x.i : x.r;
+  o.i = c ? -x.r : x.i;
+  return o;
+}
+MB_DEV cpx r4_step2(cpx sent, cpx got, bool lo) {
+  cpx o;
+  o.r = got.r + neg_if(sent.r, lo);
+  o.i = got.i + neg_if(sent.i, lo);
   return o;
 }
 MB_DEV cpx tw_at(const ImdctTables* T, int idx) { cpx o; o.r = T->fft_tw[2 * idx]; o.i = T->fft_tw[2 * idx + 1]; return o; }
 MB_DEV int bitrev_low(int r, int bits) {
+#if MB_ON_DEVICE
+  return (int)(__brev((unsigned)r) >> (32 - bits));
+#else
   int w = 0;
   for (int b = 0; b < bits; b++) w |= ((r >> b) & 1) << (bits - 1 - b);
   return w;
+#endif
 }
 
 // In place on io[0 .. IMDCT_ROW): N = 120 << lm frequency bins in (short blocks interleaved as the band pass leaves
 // them), N time-domain samples out (clt_mdct_backward against the reference's zero-filled overlap), then the 60
 // unwindowed samples behind the frame.
-MB_DEV void celt_imdct_core_w(Team tm, float* io, const ImdctTables* T, int lm, int transient) {
-  const int M = 1 << lm, N = M * SHORT_MDCT;
-  const int nbk = transient ? M : 1;
-  const int shift = transient ? MAX_LM : MAX_LM - lm;
+// SH / NB >= 0 fix the transform size (480 >> SH points) and the number of blocks at compile time (addresses become
+// immediates); -1 reads them from (lm, transient).
+template <int SH, int NB>
+MB_DEV void celt_imdct_core_t(Team tm, float* io, const ImdctTables* T, int lm, int transient) {
+  const int M = 1 << lm;
+  const int nbk = NB > 0 ? NB : (transient ? M : 1);
+  const int shift = SH >= 0 ? SH : (transient ? MAX_LM : MAX_LM - lm);
+  const int N = M * SHORT_MDCT;
   const int n2 = 960 >> shift, n4 = n2 >> 1;
   const int lgL = 5 - shift, L = 1 << lgL;
   const float* twb = T->mdct_tw + (1920 - (1920 >> shift));
@@ -292,9 +302,8 @@ MB_DEV void celt_imdct_core_w(Team tm, float* io, const ImdctTables* T, int lm, 
       snd[MB_LIDX(ln)] = x;
     }
     MB_EACH_LANE(tm, ln) v[MB_LIDX(ln)][c] = r4_step1(snd[MB_LIDX(ln)], lane_xchg(snd, ln, 2 << pA), ((ln >> (pA + 1)) & 1) != 0);
-    MB_EACH_LANE(tm, ln) snd[MB_LIDX(ln)] = v[MB_LIDX(ln)][c];
-    MB_EACH_LANE(tm, ln)
-      v[MB_LIDX(ln)][c] = r4_step2(snd[MB_LIDX(ln)], lane_xchg(snd, ln, 1 << pA), ((ln >> (pA + 1)) & 1) != 0, ((ln >> pA) & 1) != 0);
+    MB_EACH_LANE(tm, ln) snd[MB_LIDX(ln)] = r4_turn(v[MB_LIDX(ln)][c], ((ln >> pA) & 3) == 3);
+    MB_EACH_LANE(tm, ln) v[MB_LIDX(ln)][c] = r4_step2(snd[MB_LIDX(ln)], lane_xchg(snd, ln, 1 << pA), ((ln >> pA) & 1) != 0);
     if (hasB) {                             // radix 2, m = 4 (kiss_fft.rs:900-966)
       MB_EACH_LANE(tm, ln) {
         const cpx x = v[MB_LIDX(ln)][c];
@@ -307,7 +316,8 @@ MB_DEV void celt_imdct_core_w(Team tm, float* io, const ImdctTables* T, int lm, 
       }
       MB_EACH_LANE(tm, ln) {
         const cpx mine = snd[MB_LIDX(ln)], got = lane_xchg(snd, ln, 1 << pB);
-        v[MB_LIDX(ln)][c] = ((ln >> pB) & 1) ? c_sub(got, mine) : c_add(mine, got);
+        v[MB_LIDX(ln)][c].r = got.r + neg_if(mine.r, ((ln >> pB) & 1) != 0);   // p[k] + t below, p[k] - t above
+        v[MB_LIDX(ln)][c].i = got.i + neg_if(mine.i, ((ln >> pB) & 1) != 0);
       }
     }
     if (hasC) {                             // radix 4, m = 8 (480 points) or m = 4 (240 points): the two low bits of r
@@ -316,8 +326,8 @@ MB_DEV void celt_imdct_core_w(Team tm, float* io, const ImdctTables* T, int lm, 
         snd[MB_LIDX(ln)] = (ln & 3) ? c_mul(x, twC[MB_LIDX(ln)]) : x;
       }
       MB_EACH_LANE(tm, ln) v[MB_LIDX(ln)][c] = r4_step1(snd[MB_LIDX(ln)], lane_xchg(snd, ln, 2), (ln & 2) != 0);
-      MB_EACH_LANE(tm, ln) snd[MB_LIDX(ln)] = v[MB_LIDX(ln)][c];
-      MB_EACH_LANE(tm, ln) v[MB_LIDX(ln)][c] = r4_step2(snd[MB_LIDX(ln)], lane_xchg(snd, ln, 1), (ln & 2) != 0, (ln & 1) != 0);
+      MB_EACH_LANE(tm, ln) snd[MB_LIDX(ln)] = r4_turn(v[MB_LIDX(ln)][c], (ln & 3) == 3);
+      MB_EACH_LANE(tm, ln) v[MB_LIDX(ln)][c] = r4_step2(snd[MB_LIDX(ln)], lane_xchg(snd, ln, 1), (ln & 1) != 0);
     }
   }
   MB_SYNC();                                // every lane is done reading the input row: the output goes into the same row
@@ -388,6 +398,13 @@ MB_DEV void celt_imdct_core_w(Team tm, float* io, const ImdctTables* T, int lm, 
     }
   }
   MB_SYNC();
+}
+
+// The two shapes nearly every 20 ms frame takes get their own instantiation; the rest share the generic one.
+MB_DEV void celt_imdct_core_w(Team tm, float* io, const ImdctTables* T, int lm, int transient) {
+  if (lm == 3 && !transient) celt_imdct_core_t<0, 1>(tm, io, T, lm, transient);
+  else if (lm == 3) celt_imdct_core_t<3, 8>(tm, io, T, lm, transient);
+  else celt_imdct_core_t<-1, 0>(tm, io, T, lm, transient);
 }
 
 #if !MB_ON_DEVICE
