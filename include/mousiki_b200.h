@@ -167,6 +167,35 @@ int bd_debug_kat(int device, int what, const uint32_t* in, uint32_t n_in, uint32
 int bd_parse_noalloc(int device, const uint8_t* d_arena, const uint32_t* d_offsets, uint32_t n_packets, int channels, uint32_t quirks,
                      int frame_size, int32_t* d_samples_out, uint32_t* d_final_range_out, void* cuda_stream);
 
+/* ---- Row A2: mousiki's LIGHTWEIGHT decoder (`mousiki::decoder::Decoder`, src/decoder.rs:142-262, the README's minimal API), batched.
+ * It is a different decoder from the one above: the float, pion-derived SILK path of
+ * src/silk/decoder.rs:971-1163 — SILK-only, mono, one 20 ms frame per packet, no LBRR — with a zero-order hold x3 to 48 kHz
+ * (src/resample.rs:3-15). Every accepted packet yields 960 samples. One decoder per stream: lane j of a call is stream j, and a
+ * call decodes n_ticks packets per lane in order (packet p = tick * n_lanes + lane; arena / offsets as in bd_decode_*; host
+ * buffers, copies inside the call). status[p] = 960, or the reference's error for that packet (the stream's state is then
+ * untouched and its row of `pcm` is cleared): */
+#define BD_LITE_ERR_TOO_SHORT (-1)        /* DecoderError::TooShortForTableOfContents, src/decoder.rs:151-153 */
+#define BD_LITE_ERR_FRAME_CODE (-2)       /* DecoderError::UnsupportedFrameCode, src/decoder.rs:167-173 */
+#define BD_LITE_ERR_CONFIG_MODE (-3)      /* DecoderError::UnsupportedConfigurationMode (hybrid / CELT), src/decoder.rs:175-184 */
+#define BD_LITE_ERR_FRAME_DURATION (-4)   /* silk DecodeError::UnsupportedFrameDuration (not 20 ms), src/silk/decoder.rs:987-993 */
+#define BD_LITE_ERR_STEREO (-5)           /* silk DecodeError::StereoUnsupported, src/silk/decoder.rs:994-996 */
+#define BD_LITE_ERR_LBRR (-7)             /* silk DecodeError::UnsupportedLowBitrateRedundancy, src/silk/decoder.rs:1021-1023 */
+typedef struct bd_lite_handle bd_lite_handle;
+/* Decoder::new() for n_streams streams on `device` (src/decoder.rs:143-148). */
+int bd_lite_create(int device, uint32_t n_streams, bd_lite_handle** out);
+void bd_lite_destroy(bd_lite_handle* h);
+/* Every stream back to Decoder::new(). */
+int bd_lite_reset(bd_lite_handle* h);
+/* Decoder::decode_float32 (src/decoder.rs:235-248): pcm[n_packets][960] f32. */
+int bd_lite_decode_f32(bd_lite_handle* h, const uint8_t* arena, const uint32_t* offsets, uint32_t n_lanes, uint32_t n_ticks, float* pcm,
+                       int32_t* status);
+/* Decoder::decode (src/decoder.rs:220-233, floor(x * 32767), src/bitdepth.rs:15-51): pcm[n_packets][960] i16. */
+int bd_lite_decode_i16(bd_lite_handle* h, const uint8_t* arena, const uint32_t* offsets, uint32_t n_lanes, uint32_t n_ticks, int16_t* pcm,
+                       int32_t* status);
+/* Decoder::decode_int24 (src/decoder.rs:252-260, rint(x * 2^23), src/bitdepth.rs:58-90): pcm[n_packets][960] i32. */
+int bd_lite_decode_i24(bd_lite_handle* h, const uint8_t* arena, const uint32_t* offsets, uint32_t n_lanes, uint32_t n_ticks, int32_t* pcm,
+                       int32_t* status);
+
 #ifdef __cplusplus
 }
 #endif

@@ -29,6 +29,7 @@ EXPORTS = [
     "bd_get_stream_info", "bd_alloc_pinned", "bd_free_pinned", "bd_last_launch_count", "bd_debug_capture", "bd_profile_enable", "bd_profile_read",
     "bd_packet_get_mode", "bd_packet_get_bandwidth", "bd_packet_get_nb_channels", "bd_packet_get_samples_per_frame", "bd_packet_get_nb_frames",
     "bd_packet_get_nb_samples", "bd_debug_kat", "bd_decode_i24", "bd_parse_noalloc",
+    "bd_lite_create", "bd_lite_destroy", "bd_lite_reset", "bd_lite_decode_f32", "bd_lite_decode_i16", "bd_lite_decode_i24",
 ]
 
 
@@ -272,3 +273,67 @@ def packet_get_nb_frames(packet, length=None):
 def packet_get_nb_samples(packet, length=None, fs_hz=48000):
     """Samples per channel the packet decodes to (opus_packet_get_nb_samples; `Decoder::packet_samples` at the decoder's rate)."""
     return _query("bd_packet_get_nb_samples", packet, len(packet) if length is None else int(length), int(fs_hz))
+
+
+class LiteBatchDecoder:
+    """mousiki's lightweight `decoder::Decoder` (src/decoder.rs:142-262), one per stream, batched on the GPU: SILK-only, mono,
+    20 ms packets, 960 samples out per packet (row A2; include/mousiki_b200.h bd_lite_*). `decode_float32`, `decode` and
+    `decode_int24` take a tick-major grid of packets (packet p = tick * n_lanes + lane, lane j = stream j) and return
+    (pcm[n_packets, 960], status[n_packets]) with status 960 or the reference's error code for that packet."""
+
+    def __init__(self, n_streams: int, device: int = 0):
+        self._lib = load_library()
+        lib = self._lib
+        lib.bd_lite_create.argtypes = [C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]
+        lib.bd_lite_destroy.argtypes = [C.c_void_p]
+        lib.bd_lite_reset.argtypes = [C.c_void_p]
+        for f in (lib.bd_lite_decode_f32, lib.bd_lite_decode_i16, lib.bd_lite_decode_i24):
+            f.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
+        h = C.c_void_p()
+        rc = lib.bd_lite_create(device, n_streams, C.byref(h))
+        if rc != 0:
+            raise DecoderError(f"bd_lite_create failed: {rc}")
+        self._h = h
+        self.n_streams = n_streams
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.bd_lite_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        self.close()
+
+    def reset(self):
+        rc = self._lib.bd_lite_reset(self._h)
+        if rc != 0:
+            raise DecoderError(f"bd_lite_reset failed: {rc}")
+
+    def _run(self, fn, dtype, arena, offsets, n_lanes):
+        arena = np.ascontiguousarray(arena, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint32)
+        n = len(offsets) - 1
+        if n % n_lanes:
+            raise ValueError("the packet grid must hold the same number of packets for every lane")
+        pcm = np.zeros((n, 960), dtype=dtype)
+        status = np.zeros(n, dtype=np.int32)
+        rc = fn(self._h, arena.ctypes.data_as(C.c_void_p), offsets.ctypes.data_as(C.c_void_p), n_lanes, n // n_lanes,
+                pcm.ctypes.data_as(C.c_void_p), status.ctypes.data_as(C.c_void_p))
+        if rc != 0:
+            raise DecoderError(f"lightweight decode failed: {rc}")
+        return pcm, status
+
+    def decode_float32(self, arena, offsets, n_lanes):
+        return self._run(self._lib.bd_lite_decode_f32, np.float32, arena, offsets, n_lanes)
+
+    def decode(self, arena, offsets, n_lanes):
+        return self._run(self._lib.bd_lite_decode_i16, np.int16, arena, offsets, n_lanes)
+
+    def decode_int24(self, arena, offsets, n_lanes):
+        return self._run(self._lib.bd_lite_decode_i24, np.int32, arena, offsets, n_lanes)

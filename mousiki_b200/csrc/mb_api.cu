@@ -29,6 +29,7 @@
 #include "mb_frame.cuh"
 #include "mb_silk_out.cuh"
 #include "mb_kat.cuh"
+#include "mb_lite.cuh"
 
 using namespace mb;
 
@@ -636,6 +637,49 @@ __global__ void __launch_bounds__(32) k_kat(int what, const uint32_t* __restrict
   Team tm = {(int)threadIdx.x, 32};
   const int r = kat_run(tm, &sm, what, in, n_in, out, n_out, gbytes, &g_imdct_tables);
   if (threadIdx.x == 0) *rc = r;
+}
+
+// Row A2, the lightweight decoder (mb_lite.cuh): one lane per stream walks its packets in tick order; after each tick the
+// warp writes its 32 rows together (each stream's 320-sample buffer held 3x, converted on the way) so the stores coalesce.
+struct LiteParams {
+  const uint8_t* arena;
+  const uint32_t* offsets;
+  LiteState* st;
+  void* pcm;          // [packet][960] f32 / i16 / i32
+  int32_t* status;    // [packet]
+  uint32_t n_lanes, n_ticks;
+  int mode;           // 0: decode_float32, 1: decode (i16), 2: decode_int24
+};
+__global__ void __launch_bounds__(64) k_lite(LiteParams P) {
+  const uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x, l32 = threadIdx.x & 31, lane0 = lane - l32;
+  const bool live = lane < P.n_lanes;
+  LiteFrame F;
+  float res[LITE_BUF], lag[LITE_MAX_RES_LAG], lpc[LITE_BUF];
+  for (uint32_t t = 0; t < P.n_ticks; t++) {
+    int rc = 0;
+    if (live) {
+      const uint32_t p = t * P.n_lanes + lane, a = P.offsets[p], b = P.offsets[p + 1];
+      rc = lite_decode_packet(P.st[lane], P.arena + a, b - a, F, res, lag, lpc);
+      P.status[p] = rc;
+    }
+    __syncwarp();
+    for (uint32_t k = 0; k < 32 && lane0 + k < P.n_lanes; k++) {
+      const int ok = __shfl_sync(0xffffffffu, rc, (int)k) == LITE_OUT;
+      const float* src = P.st[lane0 + k].silk_buffer;
+      const size_t row = ((size_t)t * P.n_lanes + lane0 + k) * LITE_OUT;
+      for (uint32_t i = l32; i < LITE_OUT; i += 32) {
+        const float v = ok ? src[i / 3] : 0.f;   // (rows of refused packets are cleared; the reference leaves `out` alone)
+        if (P.mode == 0) ((float*)P.pcm)[row + i] = v;
+        else if (P.mode == 1) ((int16_t*)P.pcm)[row + i] = (int16_t)lite_floor_i32(v * 32767.0f);
+        else ((int32_t*)P.pcm)[row + i] = (int32_t)rint((double)v * 8388608.0);
+      }
+    }
+    __syncwarp();
+  }
+}
+__global__ void k_lite_reset(LiteState* st, uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) lite_state_reset(st[i]);
 }
 
 // ------------------------------------------------------------------------------------------ host side
@@ -1461,4 +1505,82 @@ extern "C" int bd_parse_noalloc(int device, const uint8_t* d_arena, const uint32
                                                                                 channels == 1, frame_size, d_samples_out,
                                                                                 d_final_range_out);
   return cudaGetLastError() == cudaSuccess ? BD_OK : BD_ERR_CUDA;
+}
+
+// ------------------------------------------------------------------------------------------ row A2: lightweight decoder
+struct bd_lite_handle {
+  int device = 0;
+  uint32_t n_streams = 0;
+  cudaStream_t stream = nullptr;
+  DevBuf st, arena, offsets, pcm, status;
+};
+
+extern "C" int bd_lite_create(int device, uint32_t n_streams, bd_lite_handle** out) {
+  if (!out || n_streams == 0) return BD_ERR_BAD_ARG;
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) return BD_ERR_CUDA;
+  if (cudaSetDevice(device) != cudaSuccess) return BD_ERR_CUDA;
+  bd_lite_handle* h = new (std::nothrow) bd_lite_handle();
+  if (!h) return BD_ERR_ALLOC;
+  h->device = device; h->n_streams = n_streams;
+  if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return BD_ERR_CUDA; }
+  if (h->st.ensure((size_t)n_streams * sizeof(LiteState)) != cudaSuccess) { bd_lite_destroy(h); return BD_ERR_ALLOC; }
+  k_lite_reset<<<(n_streams + 127) / 128, 128, 0, h->stream>>>(h->st.as<LiteState>(), n_streams);
+  if (cudaStreamSynchronize(h->stream) != cudaSuccess || cudaGetLastError() != cudaSuccess) { bd_lite_destroy(h); return BD_ERR_CUDA; }
+  *out = h;
+  return BD_OK;
+}
+
+extern "C" void bd_lite_destroy(bd_lite_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  if (h->stream) { cudaStreamSynchronize(h->stream); cudaStreamDestroy(h->stream); }
+  h->st.release(); h->arena.release(); h->offsets.release(); h->pcm.release(); h->status.release();
+  delete h;
+}
+
+extern "C" int bd_lite_reset(bd_lite_handle* h) {
+  if (!h) return BD_ERR_BAD_ARG;
+  if (cudaSetDevice(h->device) != cudaSuccess) return BD_ERR_CUDA;
+  k_lite_reset<<<(h->n_streams + 127) / 128, 128, 0, h->stream>>>(h->st.as<LiteState>(), h->n_streams);
+  return cudaStreamSynchronize(h->stream) == cudaSuccess && cudaGetLastError() == cudaSuccess ? BD_OK : BD_ERR_CUDA;
+}
+
+namespace {
+int lite_decode(bd_lite_handle* h, const uint8_t* arena, const uint32_t* offsets, uint32_t n_lanes, uint32_t n_ticks, void* pcm, int32_t* status,
+                int mode) {
+  if (!h || !offsets || !pcm || !status || n_lanes == 0 || n_lanes > h->n_streams) return BD_ERR_BAD_ARG;
+  if (n_ticks == 0) return BD_OK;
+  const size_t n = (size_t)n_lanes * n_ticks, bytes = offsets[n], elem = mode == 1 ? 2 : 4;
+  if (bytes && !arena) return BD_ERR_BAD_ARG;
+  if (cudaSetDevice(h->device) != cudaSuccess) return BD_ERR_CUDA;
+  if (h->arena.ensure(bytes + 16) != cudaSuccess || h->offsets.ensure((n + 1) * 4) != cudaSuccess || h->pcm.ensure(n * LITE_OUT * elem) != cudaSuccess ||
+      h->status.ensure(n * 4) != cudaSuccess)
+    return BD_ERR_ALLOC;
+  cudaStream_t s = h->stream;
+  if (bytes && cudaMemcpyAsync(h->arena.p, arena, bytes, cudaMemcpyHostToDevice, s) != cudaSuccess) return BD_ERR_CUDA;
+  if (cudaMemcpyAsync(h->offsets.p, offsets, (n + 1) * 4, cudaMemcpyHostToDevice, s) != cudaSuccess) return BD_ERR_CUDA;
+  LiteParams P;
+  P.arena = h->arena.as<uint8_t>(); P.offsets = h->offsets.as<uint32_t>(); P.st = h->st.as<LiteState>(); P.pcm = h->pcm.p;
+  P.status = h->status.as<int32_t>(); P.n_lanes = n_lanes; P.n_ticks = n_ticks; P.mode = mode;
+  k_lite<<<(n_lanes + 63) / 64, 64, 0, s>>>(P);
+  if (cudaGetLastError() != cudaSuccess) return BD_ERR_CUDA;
+  if (cudaMemcpyAsync(pcm, h->pcm.p, n * LITE_OUT * elem, cudaMemcpyDeviceToHost, s) != cudaSuccess) return BD_ERR_CUDA;
+  if (cudaMemcpyAsync(status, h->status.p, n * 4, cudaMemcpyDeviceToHost, s) != cudaSuccess) return BD_ERR_CUDA;
+  return cudaStreamSynchronize(s) == cudaSuccess ? BD_OK : BD_ERR_CUDA;
+}
+}  // namespace
+
+extern "C" int bd_lite_decode_f32(bd_lite_handle* h, const uint8_t* arena, const uint32_t* offsets, uint32_t n_lanes, uint32_t n_ticks, float* pcm,
+                                  int32_t* status) {
+  return lite_decode(h, arena, offsets, n_lanes, n_ticks, pcm, status, 0);
+}
+extern "C" int bd_lite_decode_i16(bd_lite_handle* h, const uint8_t* arena, const uint32_t* offsets, uint32_t n_lanes, uint32_t n_ticks, int16_t* pcm,
+                                  int32_t* status) {
+  return lite_decode(h, arena, offsets, n_lanes, n_ticks, pcm, status, 1);
+}
+extern "C" int bd_lite_decode_i24(bd_lite_handle* h, const uint8_t* arena, const uint32_t* offsets, uint32_t n_lanes, uint32_t n_ticks, int32_t* pcm,
+                                  int32_t* status) {
+  return lite_decode(h, arena, offsets, n_lanes, n_ticks, pcm, status, 2);
 }

@@ -17,6 +17,7 @@
 #include "../../mousiki_b200/csrc/mb_frame.cuh"
 #include "../../mousiki_b200/csrc/mb_silk_out.cuh"
 #include "../../mousiki_b200/csrc/mb_kat.cuh"
+#include "../../mousiki_b200/csrc/mb_lite.cuh"
 
 using namespace mb;
 
@@ -28,6 +29,28 @@ int emu_kat(int what, const uint32_t* in, uint32_t n_in, uint32_t* out, uint32_t
   uint8_t bytes[64];
   Team tm = {0, 1};
   return kat_run(tm, &sm, what, in, n_in, out, n_out, bytes, imdct_tables_host());
+}
+
+// Row A2: the body of k_lite (mb_lite.cuh), one stream after the other; mode 0 f32, 1 i16, 2 i24 as in the kernel
+int emu_lite_decode(const uint8_t* arena, const uint32_t* offsets, uint32_t n_lanes, uint32_t n_ticks, void* pcm, int32_t* status, int mode) {
+  std::vector<LiteState> st(n_lanes);
+  for (auto& x : st) lite_state_reset(x);
+  LiteFrame* F = new LiteFrame;
+  float res[LITE_BUF], lag[LITE_MAX_RES_LAG], lpc[LITE_BUF];
+  for (uint32_t t = 0; t < n_ticks; t++)
+    for (uint32_t j = 0; j < n_lanes; j++) {
+      const uint32_t p = t * n_lanes + j;
+      const int rc = lite_decode_packet(st[j], arena + offsets[p], offsets[p + 1] - offsets[p], *F, res, lag, lpc);
+      status[p] = rc;
+      for (int i = 0; i < LITE_OUT; i++) {
+        const float v = rc == LITE_OUT ? st[j].silk_buffer[i / 3] : 0.f;
+        if (mode == 0) ((float*)pcm)[(size_t)p * LITE_OUT + i] = v;
+        else if (mode == 1) ((int16_t*)pcm)[(size_t)p * LITE_OUT + i] = (int16_t)lite_floor_i32(v * 32767.0f);
+        else ((int32_t*)pcm)[(size_t)p * LITE_OUT + i] = (int32_t)rint((double)v * 8388608.0);
+      }
+    }
+  delete F;
+  return 0;
 }
 
 // decode gain of the following emu_decode_grid calls (Q8 dB, 0 = none; src/opus_decoder.rs:1376-1392)

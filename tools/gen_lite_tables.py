@@ -8,6 +8,7 @@ from pathlib import Path
 
 REF = Path("/root/reference/src/silk")
 OUT = Path(__file__).resolve().parent.parent / "oracle" / "lite_tables_data.h"
+OUT_DEV = Path(__file__).resolve().parent.parent / "mousiki_b200" / "csrc" / "lite_tables_data.h"
 
 ICDF_SINGLE = [
     "FRAME_TYPE_VAD_INACTIVE", "FRAME_TYPE_VAD_ACTIVE", "INDEPENDENT_QUANTIZATION_GAIN_MSB_INACTIVE",
@@ -105,6 +106,40 @@ def main():
     L.append("}  // namespace lite_tab")
     OUT.write_text("\n".join(L) + "\n")
     print("wrote", OUT, len(L), "lines")
+    # The product's copy: the same distributions in the inverse-cumulative byte form its range decoder reads
+    # (icdf[i] = 256 - c[i], every total is 256), contexts of an array back to back with an offset table.
+    D = ["// Constant tables of mousiki's lightweight SILK decoder (src/silk/icdf.rs, src/silk/codebook.rs) for the k_lite kernel,",
+         "// written by tools/gen_lite_tables.py: distributions as inverse cumulative bytes (256 - c[i]), codebooks verbatim.",
+         "#pragma once", "#include <stdint.h>", "namespace mb { namespace lite_tab {"]
+    for name in ICDF_SINGLE:
+        (total, vals), = icdf_contexts(const_body(icdf, name))
+        assert total == 256 and vals[-1] == 256
+        D.append(f"MB_TBL uint8_t {name}[{len(vals)}] = {{{', '.join(str(256 - v) for v in vals)}}};")
+    for name in ICDF_ARRAY:
+        ctxs = icdf_contexts(const_body(icdf, name))
+        flat, offs = [], []
+        for total, vals in ctxs:
+            assert total == 256 and vals[-1] == 256
+            offs.append(len(flat))
+            flat += [256 - v for v in vals]
+        D.append(f"MB_TBL uint8_t {name}[{len(flat)}] = {{{', '.join(map(str, flat))}}};")
+        D.append(f"MB_TBL uint16_t {name}_OFF[{len(offs)}] = {{{', '.join(map(str, offs))}}};")
+    for name in CODEBOOK_2D:
+        rows = nested_rows(const_body(cb, name))
+        w = len(rows[0])
+        ty = "int8_t" if name.startswith("CODEBOOK_LTP") else "uint8_t"
+        D.append(f"MB_TBL {ty} {name}[{len(rows)}][{w}] = {{")
+        for r in rows:
+            D.append("  {" + ", ".join(map(str, r)) + "},")
+        D.append("};")
+    for name in CODEBOOK_1D:
+        rows = nested_rows(const_body(cb, name))
+        vals = [x for r in rows for x in r]
+        ty = "int16_t" if max(vals) < 32768 else "int32_t"
+        D.append(f"MB_TBL {ty} {name}[{len(vals)}] = {{{', '.join(map(str, vals))}}};")
+    D.append("} }  // namespace mb::lite_tab")
+    OUT_DEV.write_text("\n".join(D) + "\n")
+    print("wrote", OUT_DEV, len(D), "lines")
 
 
 if __name__ == "__main__":
