@@ -67,17 +67,21 @@ const char* bd_last_error(const bd_handle* h);
 
 /* Decoder::decode_float / opus_decode_float for a batch (src/codec.rs:892-907, src/opus_decoder.rs:1803-1826).
  * HOST buffers. Packet p is arena[offsets[p] .. offsets[p+1]) and belongs to stream_ids[p]; packets of one
- * stream are decoded in array order. flags[p] bit0 = decode_fec, bit1 = packet lost (both: row F2, reported as
- * BD_OPUS_UNIMPLEMENTED until built); flags may be NULL. pcm receives packet p's interleaved samples at
+ * stream are decoded in array order. flags[p] bit0 = decode_fec (Decoder::decode(.., fec = true): the in-band LBRR copy of
+ * the packet BEFORE this one, or concealment when there is none, src/opus_decoder.rs:1186-1316), bit1 = packet lost
+ * (Decoder::decode(None) / conceal*: concealment for the row's capacity, which must be a whole number of 2.5 ms frames);
+ * a frame of <= 1 byte is concealed too (src/opus_decoder.rs:491-496); flags may be NULL. pcm receives packet p's interleaved samples at
  * pcm + p * pcm_stride (pcm_stride elements >= frame_size * channels; the per-channel capacity
  * pcm_stride / channels plays the role of `frame_size`). samples_out[p] = samples per channel (>= 0) or an
  * Opus error code; final_range_out[p] = Decoder::final_range() after that packet. Returns BD_OK or an API error.
  * Packets with several frames (TOC codes 1-3, padding: opus_packet_parse_impl, src/packet.rs:316-498) are cut into
  * frames on the host; the frames of a packet run in consecutive ticks of the stream and fill the packet's row in
  * order; a frame that fails ends the packet with its code, as the frame loop of src/opus_decoder.rs:1339-1350 does.
- * Mode switches: SILK-only packets (10 / 20 ms) with a CELT redundancy frame and the hybrid -> SILK-only fade-out decode
- * (src/opus_decoder.rs:746-797, 868-893, 1012-1080); hybrid or 40 / 60 ms SILK packets with a redundancy frame and
- * switches that need a concealed frame of the old mode come back as BD_OPUS_UNIMPLEMENTED with the stream untouched. */
+ * Mode switches: redundancy frames on SILK-only packets of every duration and on hybrid packets, the hybrid -> SILK-only
+ * fade-out and CELT-only -> SILK / hybrid switches without a redundancy frame decode (src/opus_decoder.rs:575-640, 746-797,
+ * 868-893, 1012-1080). A CELT-only packet right after a SILK-only packet without a redundancy frame or after a hybrid packet
+ * (5 ms of SILK-side concealment cross-faded in, src/opus_decoder.rs:575-593) comes back as BD_OPUS_UNIMPLEMENTED with the
+ * stream untouched. */
 int bd_decode_f32(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
                   const uint8_t* flags, float* pcm, uint32_t pcm_stride, int32_t* samples_out, uint32_t* final_range_out);
 /* Decoder::decode / opus_decode (i16: soft clip + round; src/codec.rs:843-859, src/opus_decoder.rs:1632-1715). */
