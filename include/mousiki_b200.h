@@ -78,10 +78,9 @@ const char* bd_last_error(const bd_handle* h);
  * frames on the host; the frames of a packet run in consecutive ticks of the stream and fill the packet's row in
  * order; a frame that fails ends the packet with its code, as the frame loop of src/opus_decoder.rs:1339-1350 does.
  * Mode switches: redundancy frames on SILK-only packets of every duration and on hybrid packets, the hybrid -> SILK-only
- * fade-out and CELT-only -> SILK / hybrid switches without a redundancy frame decode (src/opus_decoder.rs:575-640, 746-797,
- * 868-893, 1012-1080). A CELT-only packet right after a SILK-only packet without a redundancy frame or after a hybrid packet
- * (5 ms of SILK-side concealment cross-faded in, src/opus_decoder.rs:575-593) comes back as BD_OPUS_UNIMPLEMENTED with the
- * stream untouched. */
+ * fade-out and mode switches without a redundancy frame, in both directions, decode (src/opus_decoder.rs:575-640, 746-797,
+ * 868-893, 1012-1112). BD_OPUS_UNIMPLEMENTED is left for a hybrid redundancy split that leaves the SILK part no room and for a
+ * pass that runs out of auxiliary cells; the stream is untouched then. */
 int bd_decode_f32(bd_handle* h, const uint8_t* arena, const uint32_t* offsets, const uint32_t* stream_ids, uint32_t n_packets,
                   const uint8_t* flags, float* pcm, uint32_t pcm_stride, int32_t* samples_out, uint32_t* final_range_out);
 /* Decoder::decode / opus_decode (i16: soft clip + round; src/codec.rs:843-859, src/opus_decoder.rs:1632-1715). */

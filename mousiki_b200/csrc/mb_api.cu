@@ -1100,6 +1100,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     sq.st_all = h->silk_states.as<SilkState>(); sq.silk_hist = h->silk_hist.as<uint32_t>(); sq.silk_exc = h->silk_exc.as<int32_t>();
     sq.n_streams = h->cfg.n_streams; sq.pcm_f32 = pcm; sq.pcm_i16 = d_pcm_i16 ? d_pcm_i16 + shift * pcm_stride : nullptr;
     sq.pcm_stride = pcm_stride; sq.CC = CC; sq.quirks = h->cfg.quirks; sq.gain = h->gain; sq.apply_gain = h->cfg.gain_q8 != 0; sq.out_map = d_out_map;
+    sq.xbuf = h->xbuf.as<float>(); sq.side_of = h->side_of.as<uint32_t>();
     k_silk<<<(n_lanes + 63) / 64, 64, 0, ss>>>(sq);
     h->prof_end(ss);
     CK(cudaEventRecord(h->ev_silk, ss));   // the SILK rows are written: k_deemph (hybrid accumulate) and the output stage may go

@@ -76,6 +76,10 @@ struct FrameMeta {
 // frame is band-shaped noise and runs through k_plan / k_bands / k_imdct like a coded frame (seed_in = noise seed).
 // 29: k_fade finishes the packet's row (cross-fade with a side row, then the decode gain): nobody else applies the gain to it.
 enum : uint32_t { MB_FL_KEEP_TAIL = 1u << 28, MB_FL_FADE_ROW = 1u << 29, MB_FL_PLC = 1u << 30, MB_FL_PLC_PITCH = 1u << 31 };
+// bit 10, only on a CELT-only frame of the serial band pass (bit 9 set: bits 10-27 carry nothing there): the packet opens with a
+// cross-fade from 5 ms concealed in the old mode, SILK-only or hybrid (opus_decoder.rs:575-593, 1092-1112). The stream's k_silk lane
+// conceals into the side row of the cell side_of[] names (bit 1 makes the lane stop at the cell), k_fade blends the first 2.5 ms.
+enum : uint32_t { MB_FL_TRANS_IN = 1u << 10 };
 // S_STATUS bit 29: lost frame (no payload); S_RANGE then holds the number of samples to conceal
 #define MB_ST_LOST(s) (((s) >> 29) & 1u)
 // S_STATUS bit 30: the cell's SILK record comes from the packet's LBRR data (in-band FEC)
@@ -291,7 +295,8 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
     // packet without touching the stream. A redundancy frame makes the switch clean: CELT -> SILK when the SILK packet
     // carries one, SILK -> CELT when the previous SILK packet ended in one.
     bool reject;
-    if (!silk_bit) reject = st_prev_mode == 1001 || (st_prev_mode == 1000 && !st_prev_redundancy);
+    const bool trans_to_celt = !silk_bit && (st_prev_mode == 1000 || st_prev_mode == 1001) && !st_prev_redundancy;
+    if (!silk_bit) reject = false;
     else if (red) reject = !hybrid && st_prev_mode == 1001 && !(red_aux && fadeout);   // after hybrid the cell must hold the fade-out frame
     else reject = silk_only && st_prev_mode == 1001;
     if (reject) {
@@ -466,7 +471,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
       sample_off += (uint32_t)(M * SHORT_MDCT);                 // the CELT time line advances by the CELT frame
       return M * SHORT_MDCT;
     };
-    const bool celt_reset = (hybrid && st_prev_mode != 1001 && st_prev_mode > 0 && !st_prev_redundancy) || (aux == 3 && !hybrid);
+    const bool celt_reset = (hybrid && st_prev_mode != 1001 && st_prev_mode > 0 && !st_prev_redundancy) || (aux == 3 && !hybrid) || trans_to_celt;
     if (MB_ST_FEC(status) && hybrid) {
       // hybrid packet decoded from its LBRR data: SILK from the record, the CELT part concealed (opus_decoder.rs:944-952)
       if (celt_reset) { celt_reset_now(); m.seed_in = 0; }
@@ -563,6 +568,35 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
       }
       continue;
     }
+    uint32_t trans_in = 0;
+    if (trans_to_celt) {
+      // ---- SILK-only / hybrid -> CELT-only without a redundancy frame (opus_decoder.rs:575-593, 895-898, 1092-1112): the reference
+      // first conceals min(frame, 5 ms) in the old mode — decode_frame(None): the SILK concealment, for a hybrid stream plus the
+      // CELT noise concealment from band 17 added on — resets the CELT decoder, decodes the packet and fades from the concealed
+      // audio into it over 2.5 ms. Neither decoder's state after that concealment is ever read again (CELT is reset right away,
+      // SILK on its next use, :694-696). The concealed audio goes to the side row of an auxiliary cell: the stream's k_silk lane
+      // writes the SILK part there, a hybrid stream's CELT part is an ordinary concealed frame in that cell (accumulating side row).
+      uint32_t ac = 0xffffffffu;
+      if (lead) ac = aux_alloc(Q.aux);
+#if MB_ON_DEVICE
+      ac = __shfl_sync(0xffffffffu, ac, 0);
+#endif
+      if (ac == 0xffffffffu) {   // pool of auxiliary cells spent in this pass
+        if (lead) { meta[f] = m; samples_out[p] = MB_UNIMPLEMENTED; final_range_out[p] = st_range_final; }
+        pkt_failed = true;
+        continue;
+      }
+      const int lmt = imin((int)MB_H0_LM(h0), 1);   // transition_size = min(audiosize, 5 ms)
+      if (st_prev_mode == 1001) {
+        FrameMeta ma;
+        ma.seed_in = st_rng; ma.sample_off = sample_off; ma.lane = lane; ma.flags = 0;
+        celt_conceal(ac, rec + rec_index(ac, 0), 0u, ma, SHORT_MDCT << lmt, lmt, 17, 8u | 16u);
+        if (lead) meta[ac] = ma;
+      }
+      if (lead) Q.side_of[f] = ac;
+      trans_in = 2u | MB_FL_TRANS_IN | MB_FL_FADE_ROW | MB_FL_F32ROW;
+      silk_side_seen = true; st_fold_serial = 1;
+    }
     if (celt_reset) celt_reset_now();
     uint32_t fl;
     if (red) {
@@ -570,7 +604,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
       fl = 1u | 2u | 16u | (celt_reset ? 4u : 0u) | silk_reset | MB_FL_FADE_ROW;
       if (aux == 3) fl |= 128u;
       else if (st_prev_mode != 1000 || st_prev_redundancy) fl |= 64u;   // opus_decoder.rs:1066
-    } else fl = (hybrid || fadeout) ? (1u | 2u | 8u | (celt_reset ? 4u : 0u) | silk_reset | trans_flags) : (silk_side_seen ? (1u | 512u) : 1u);
+    } else fl = (hybrid || fadeout) ? (1u | 2u | 8u | (celt_reset ? 4u : 0u) | silk_reset | trans_flags) : ((silk_side_seen ? (1u | 512u) : 1u) | (trans_to_celt ? (4u | trans_in) : 0u));
     if (fl & (8u | 16u)) { silk_side_seen = true; st_fold_serial = 1; }
     const int Nc = celt_coded(f, r, status, fl);
     const int N = (fadeout || red) ? silk_n : Nc;   // samples the packet delivers

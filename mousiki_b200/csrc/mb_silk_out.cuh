@@ -11,6 +11,7 @@
 // collected 32 at a time in a lane-private shared-memory row and leave as 128-bit stores (a full 128-byte line per
 // lane for mono float output).
 #pragma once
+#include "mb_celt_tail.cuh"
 #include "mb_silk_plc.cuh"
 #include "mb_celt_energy.cuh"
 
@@ -317,7 +318,10 @@ MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const SilkHistR
           c.first_frame_after_reset = 0;
           c.lag_prev = (int16_t)P.pitch_l[nb - 1];
           W.pos[n] = (hp + L) & SILK_RING_MASK;            // decode_frame.rs:207-230: the history window slides by a frame
-          {   // the frame's excitation: in the record until somebody needs it in HBM (silk_exc_flush)
+          {   // the frame's excitation: in the record until somebody needs it in HBM (silk_exc_flush). A shorter frame leaves
+              // the tail of a longer one standing in the reference's buffer (decode_core.rs:93-111 writes frame_length words),
+              // and the concealment reads across it (plc.rs:370-388): the longer one goes to HBM before it is forgotten.
+            if (W.last_exc[n].valid && W.last_exc[n].len > L) silk_exc_flush(c, W, X, n);
             SilkExcSrc& e = W.last_exc[n];
             e.pulse_words = chw + SL_IDX_WORDS * 32; e.from = 0; e.len = (int16_t)L;
             e.seed = sd.seed; e.signal_type = sd.signal_type; e.quant_offset = sd.quant_offset; e.valid = 1;
@@ -390,6 +394,7 @@ struct SilkLaneParams {
   SilkState* st_all; uint32_t* silk_hist; int32_t* silk_exc; uint32_t n_streams;
   float* pcm_f32; int16_t* pcm_i16; uint32_t pcm_stride; int CC; uint32_t quirks; float gain; int apply_gain;
   const uint32_t* out_map;
+  float* xbuf; const uint32_t* side_of;   // side rows (mb_celt_tail.cuh): where a SILK -> CELT switch without redundancy conceals into
 };
 // W: the lane's working set (local memory on the device); stage: 32 lane-private words; fir: interpolation table.
 MB_DEV void silk_lane(const SilkLaneParams& q, uint32_t lane, SilkWork& W, int32_t* stage, const int16_t* fir) {
@@ -411,6 +416,20 @@ MB_DEV void silk_lane(const SilkLaneParams& q, uint32_t lane, SilkWork& W, int32
     const uint32_t p = q.pkt_map ? q.pkt_map[f] : f;
     const uint32_t* rb = q.rec + rec_index(f, 0);
     const uint32_t status = rb[S_STATUS * 32];
+    if ((fl & 1u) && (fl & 512u) && (fl & MB_FL_TRANS_IN) && !(fl & (8u | 16u))) {
+      // a CELT-only packet right after a SILK-only / hybrid one, no redundancy frame (opus_decoder.rs:575-593): min(frame, 5 ms)
+      // concealed by the SILK decoder as it stands (decode_frame(None): a 10 ms SILK frame, of which the row takes that much),
+      // into the side row k_fade blends from. The SILK state is not read again before its next reset (:694-696).
+      SilkPcmOut o;
+      o.f32 = side_row(q.xbuf, q.side_of[f]); o.i16 = nullptr;
+      o.CC = q.CC; o.gain = q.gain; o.apply_gain = 0; o.gain_from = 0;
+      SilkPacketCtl ctl;
+      ctl.mode = SILK_PKT_LOST;
+      ctl.samples48 = imin(SHORT_MDCT << (int)MB_H0_LM(rb[S_HDR0 * 32]), 2 * SHORT_MDCT);
+      ctl.limit = ctl.samples48;
+      silk_synth_packet(S, W, H, X, side_live, 0u, rb, q.quirks, o, stage, fir, ctl);
+      continue;
+    }
     const bool to_float = (fl & MB_FL_F32ROW) != 0;   // the packet goes through the float row (a CELT frame shares one of its rows, or a decode gain applies)
     const bool shared = (fl & (8u | 16u)) != 0;       // a CELT frame shares THIS row (hybrid, fade-out, redundancy): k_deemph / k_fade finish it
     const bool hyb_layout = ((status >> 17) & 3u) != 0;       // hybrid, or a one-frame SILK-only cell

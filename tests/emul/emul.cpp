@@ -69,7 +69,7 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   const uint32_t F = n_lanes * n_ticks;
   const uint32_t FA = 2 * F;   // main cells, then as many auxiliary cells (mb_common.cuh)
   const size_t tiles = (FA + 31) / 32;
-  std::vector<uint32_t> rec(tiles * REC_SLOTS * 32, 0);
+  std::vector<uint32_t> rec(tiles * REC_SLOTS * 32, getenv("MB_EMUL_CLEAN") ? 0u : 0x5a5a5a5au);   // (scratch the device reuses between calls: stale there, garbage here)
   std::vector<StreamState> st(n_lanes);
   for (auto& s : st) stream_state_reset(s);
   std::vector<float> hist((size_t)n_lanes * CC * HIST_G, 0.f);
@@ -105,7 +105,7 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
                 meta[f].seed_in, rec[rec_index(f, S_HDR0)], rec[rec_index(f, S_STATUS)]);
       }
   // phase 2b
-  std::vector<float> xbuf((size_t)FA * XBUF_STRIDE, 0.f), xstage(2 * MAX_N);
+  std::vector<float> xbuf((size_t)FA * XBUF_STRIDE, getenv("MB_EMUL_CLEAN") ? 0.f : 12345.678f), xstage(2 * MAX_N);
   PvqParams pq; pq.rec = rec.data(); pq.meta = meta.data(); pq.xbuf = xbuf.data(); pq.iy_dbg = iy_dbg;
   for (uint32_t f = 0; f < FA; f++) {
     if (f >= F) pq.iy_dbg = nullptr;
@@ -155,13 +155,14 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
     std::vector<SilkState> sst(n_lanes);
     std::vector<uint32_t> shist((size_t)n_lanes * 320, 0);
     std::vector<int32_t> sexc((size_t)n_lanes * 1280, 0x5a5a5a5a);   // (garbage: the lanes clear what they use)
-    for (auto& x : sst) silk_state_reset(x, 1);
+    for (auto& x : sst) { memset((void*)&x, 0x5a, sizeof x); silk_state_reset(x, 1); }   // (garbage first: a reset must set every field it relies on)
     SilkWork* W = new SilkWork;
+    memset((void*)W, 0x5a, sizeof *W);   // (the device's local memory starts as garbage too)
     SilkLaneParams sq;
     sq.n_lanes = n_lanes; sq.n_ticks = n_ticks; sq.pkt_map = nullptr; sq.lane_stream = nullptr; sq.rec = rec.data(); sq.meta = meta.data();
     sq.st_all = sst.data(); sq.silk_hist = shist.data(); sq.silk_exc = sexc.data(); sq.n_streams = n_lanes;
     sq.pcm_f32 = out; sq.pcm_i16 = pcm16; sq.pcm_stride = pcm_stride; sq.CC = CC; sq.quirks = quirks; sq.gain = tp.gain; sq.apply_gain = tp.apply_gain;
-    sq.out_map = nullptr;
+    sq.out_map = nullptr; sq.xbuf = xbuf.data(); sq.side_of = side_of.data();
     int32_t stage[32];
     for (uint32_t j = 0; j < n_lanes; j++) silk_lane(sq, j, *W, stage, silk_resampler_frac_FIR_12);
     delete W;

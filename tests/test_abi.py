@@ -56,3 +56,13 @@ def test_product_does_not_reference_oracle():
             text = path.read_text(errors="ignore")
             assert "liboracle" not in text and "libemul" not in text, path
             assert not re.search(r"(#\s*include|import|from|CDLL|dlopen)[^\n]*(oracle|emul\.)", text), path
+
+
+def test_library_is_not_older_than_its_sources():
+    """The in-tree .so travels to the GPU box as built: a kernel source edited after the last `make` would be tested there
+    against a stale binary."""
+    root = Path(__file__).resolve().parent.parent
+    lib = root / "mousiki_b200" / "libmousiki_b200.so"
+    srcs = list((root / "mousiki_b200" / "csrc").glob("*.cu*")) + list((root / "mousiki_b200" / "csrc").glob("*.h")) + [root / "include" / "mousiki_b200.h"]
+    newest = max(srcs, key=lambda p: p.stat().st_mtime)
+    assert lib.stat().st_mtime >= newest.stat().st_mtime, f"{newest.name} is newer than libmousiki_b200.so: run `python __graft_entry__.py build`"

@@ -323,3 +323,69 @@ def test_gpu_silk_redundancy_right_after_hybrid(monkeypatch):
         assert (sg > 0).all()
         total += _compare_until_first_rejection(so, sg, ro, rg, po, pg, lanes, ticks, TOL)
     assert total == 2 * lanes * ticks
+
+
+# ---------------------------------------------------------------------------------------------- SILK / hybrid -> CELT-only, no redundancy
+def _old_mode_then_celt(lanes, ticks_old, old, ch, seed):
+    """`ticks_old` packets of the old mode (SILK-only of random size / bandwidth, or hybrid), then CELT-only packets of every frame
+    size, none of them with a redundancy frame: the first CELT packet opens with the cross-fade from 5 ms (2.5 ms for a 2.5 ms
+    frame) concealed in the old mode (opus_decoder.rs:575-593, 1083-1112)."""
+    n = [0]
+
+    def toc(k, r):
+        t = n[0] // lanes
+        n[0] += 1
+        if t < ticks_old:
+            if old == "silk":
+                return helpers.silk_toc(int(r.integers(0, 3)), int(r.integers(0, 2)), bool(r.integers(0, 2)))
+            return hyb_toc(r.integers(0, 2), r.integers(0, 2), r.integers(0, 2))
+        return helpers.celt_toc(int(r.integers(0, 4)), bool(r.integers(0, 2)), int(r.integers(0, 4)))
+    return helpers.silk_fuzz_grid(lanes, ticks_old + 2, (25, 140), toc, seed=seed, channels=ch, redundancy=False)
+
+
+@pytest.mark.parametrize("old,ch,seed", [("silk", 1, 41), ("silk", 2, 42), ("hybrid", 1, 43), ("hybrid", 2, 44)])
+def test_emul_switch_to_celt_without_redundancy(old, ch, seed):
+    lanes = 24
+    arena, offsets = _old_mode_then_celt(lanes, 3, old, ch, seed)
+    for i16 in (False, True):
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, 5, ch, 960, i16=i16)
+        pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, 5, ch, 960, i16=i16)
+        assert (so > 0).all() and np.array_equal(so, se) and np.array_equal(ro, re)
+        assert np.array_equal(po, pe), _first_diff(po, pe, lanes, np.ones(len(so), dtype=bool))
+
+
+def test_emul_every_mode_switch_decodes():
+    """Random walks over CELT-only, SILK-only and hybrid packets of every size, with and without redundancy frames: nothing is
+    refused any more, and everything is bit-identical to the oracle."""
+    lanes, ticks = 16, 12
+    for ch in (1, 2):
+        for seed in (1, 2, 3, 4):
+            arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, (20, 140), _any_toc, seed=seed, channels=ch, redundancy=True)
+            po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 960)
+            pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, ticks, ch, 960)
+            assert (so > 0).all() and np.array_equal(so, se) and np.array_equal(ro, re)
+            assert np.array_equal(po, pe)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("old,ch,seed", [("silk", 1, 51), ("silk", 2, 52), ("hybrid", 1, 53), ("hybrid", 2, 54)])
+def test_gpu_switch_to_celt_without_redundancy(old, ch, seed):
+    lanes = 96
+    arena, offsets = _old_mode_then_celt(lanes, 3, old, ch, seed)
+    for i16 in (False, True):
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, 5, ch, 960, i16=i16)
+        pg, sg, rg = _decode_gpu(arena, offsets, lanes, 5, ch, 960, i16)
+        assert (so > 0).all() and np.array_equal(so, sg) and np.array_equal(ro, rg)
+        err = np.abs(po.astype(np.float64) - pg.astype(np.float64)).max()
+        assert err <= (1 if i16 else TOL), err
+
+
+@pytest.mark.gpu
+def test_gpu_every_mode_switch_decodes():
+    lanes, ticks = 128, 12
+    for ch in (1, 2):
+        arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, (20, 140), _any_toc, seed=60 + ch, channels=ch, redundancy=True)
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, 960)
+        pg, sg, rg = _decode_gpu(arena, offsets, lanes, ticks, ch, 960, False)
+        assert (so > 0).all() and np.array_equal(so, sg) and np.array_equal(ro, rg)
+        assert np.abs(po.astype(np.float64) - pg.astype(np.float64)).max() <= TOL
