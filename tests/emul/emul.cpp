@@ -61,6 +61,12 @@ void emu_set_gain(int gain_q8) { g_gain_q8 = gain_q8; }
 static const uint8_t* g_flags = nullptr;
 void emu_set_flags(const uint8_t* flags) { g_flags = flags; }
 
+// debug aid for the PVQ work-balance studies (tools/pvq_balance.py): the (N, K) of every leaf of the first `max_frames` cells
+static uint32_t* g_leaf_dump = nullptr;
+static uint32_t g_leaf_cap = 0, g_leaf_n = 0;
+void emu_leaf_dump(uint32_t* buf, uint32_t cap) { g_leaf_dump = buf; g_leaf_cap = cap; g_leaf_n = 0; }
+uint32_t emu_leaf_count() { return g_leaf_n; }
+
 // Decodes a regular [n_ticks][n_lanes] packet grid with one fresh decoder state per lane, phases in
 // the same order as the CUDA launcher. pcm: [packet][pcm_stride]. iy_dbg/x_dbg: optional [packet][2*960].
 int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_t* offsets, uint32_t n_lanes, uint32_t n_ticks,
@@ -87,6 +93,16 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   for (uint32_t f = 0; f < F; f++)
     parse_cell(arena, offsets, f, rec.data() + rec_index(f, 0), CC, quirks, disable_inv, (int)(pcm_stride / CC), g_flags,
                f >= n_lanes ? f - n_lanes : 0xffffffffu, f >= n_lanes ? nullptr : &st[f].prev_mode, rec.data(), aux);
+  if (g_leaf_dump)
+    for (uint32_t f = 0; f < F; f++) {
+      const uint32_t* r = rec.data() + rec_index(f, 0);
+      if (!MB_ST_DECODED(r[S_STATUS * 32])) continue;
+      const uint32_t nl = MB_H1_NLEAVES(r[S_HDR1 * 32]);
+      for (uint32_t l = 0; l < nl && g_leaf_n + 3 <= g_leaf_cap; l++) {
+        const uint32_t g = r[(S_LEAVES + 3 * l + 2) * 32];
+        g_leaf_dump[g_leaf_n++] = f; g_leaf_dump[g_leaf_n++] = MB_LF_N(g); g_leaf_dump[g_leaf_n++] = MB_LF_K(g);
+      }
+    }
   // phase 2a
   Team tm = {0, 1};
   EnergySmem esm;
