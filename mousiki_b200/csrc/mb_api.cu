@@ -712,7 +712,7 @@ struct bd_handle {
   float gain = 1.f;
   uint32_t max_frames_per_pass = 0;
   bool want_i24 = false;       // the running host call delivers 24-bit integers (bd_decode_i24)
-  bool serial_bands = false;   // MOUSIKI_B200_SERIAL_BANDS=1: per-stream band pass whatever the call size (see k_energy)
+  bool parallel_bands = false; // MOUSIKI_B200_PARALLEL_BANDS=1: small calls run CELT-only frames through the all-at-once band pass (see k_energy)
   std::string err;
   uint32_t launches = 0;
   cudaStream_t own_stream = nullptr;
@@ -797,7 +797,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
   h->disable_inv = cfg->disable_phase_inversion < 0 ? (cfg->channels == 1) : (cfg->disable_phase_inversion != 0);
   h->gain = cfg->gain_q8 == 0 ? 1.f : (float)exp(0.6931471805599453094 * (double)((3.32192809488736234787f / 5120.0f) * (float)cfg->gain_q8));
   h->max_frames_per_pass = cfg->max_frames_per_pass ? cfg->max_frames_per_pass : (1u << 18);
-  { const char* sb = getenv("MOUSIKI_B200_SERIAL_BANDS"); h->serial_bands = sb && atoi(sb) > 0; }
+  { const char* sb = getenv("MOUSIKI_B200_PARALLEL_BANDS"); h->parallel_bands = sb && atoi(sb) > 0; }
   const char* env = getenv("MOUSIKI_B200_MAX_FRAMES_PER_PASS");
   if (env && atoi(env) > 0) h->max_frames_per_pass = (uint32_t)atoi(env);
   auto fail = [&](int code) { bd_destroy(h); return code; };
@@ -1084,7 +1084,11 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     eq.n_lanes = n_lanes; eq.n_ticks = nt; eq.pkt_map = map; eq.rec = h->rec.as<uint32_t>(); eq.st_all = h->states.as<StreamState>();
     eq.lane_stream = d_lane_stream; eq.en = h->en.as<float>(); eq.meta = meta_p; eq.samples_out = samples; eq.final_range_out = range;
     eq.quirks = h->cfg.quirks; eq.flags = flg;
-    eq.serial_all = h->serial_bands || n_lanes >= 148u * 6u * (uint32_t)BANDS_WARPS;   // one warp per lane fills the band-pass slots
+    // The per-stream band pass (k_bands_hyb) is the exact one: it carries the reference's never-cleared fold buffer through every
+    // frame of the stream. The all-at-once pass (k_bands) writes back whole footprints, including words a frame never wrote, so a
+    // hybrid / redundancy / transition frame that folds from them later may see other data than the reference does: it is an
+    // opt-in for small calls of streams known to stay CELT-only (one warp per lane fills the band-pass slots from 3552 lanes on).
+    eq.serial_all = !h->parallel_bands || n_lanes >= 148u * 6u * (uint32_t)BANDS_WARPS;
     eq.force_float_row = h->cfg.gain_q8 != 0 || !d_pcm_i16;   // direct int16 from k_silk: only the i16 API without a decode gain
     eq.CC = CC; eq.order = order_p; eq.order_n = order_n_p; eq.side_of = h->side_of.as<uint32_t>(); eq.aux = aux;
     eq.aux_main = h->aux_main.as<uint32_t>();

@@ -131,7 +131,6 @@ def test_gpu_decode_gain(name, build, ch):
 
 @pytest.mark.gpu
 def test_gpu_mixed_streams_i16_with_and_without_gain(monkeypatch):
-    monkeypatch.setenv("MOUSIKI_B200_SERIAL_BANDS", "1")
     lanes, ticks = 64, 10
     ids = np.tile(np.arange(lanes, dtype=np.uint32), ticks)
     checked = 0

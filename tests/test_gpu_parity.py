@@ -54,7 +54,12 @@ def test_gpu_matches_oracle(lm, stereo, ch, payload, bw):
     assert np.abs(i16o - i16g).max() <= 1
 
 
-def test_gpu_mixed_shapes_all_ticks_in_one_call():
+@pytest.mark.parametrize("parallel", [False, True])
+def test_gpu_mixed_shapes_all_ticks_in_one_call(parallel, monkeypatch):
+    """`parallel`: the opt-in all-at-once band pass of small calls (k_bands, MOUSIKI_B200_PARALLEL_BANDS=1), exact for streams
+    that stay CELT-only; the default is the per-stream pass (k_bands_hyb)."""
+    if parallel:
+        monkeypatch.setenv("MOUSIKI_B200_PARALLEL_BANDS", "1")
     lanes, ticks = 128, 8
 
     def toc(t, j, rng):

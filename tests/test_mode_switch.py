@@ -134,7 +134,6 @@ def test_gpu_silk_streams_with_redundancy_frames(name, toc, payload, ch, seed):
 def test_gpu_streams_switching_between_celt_silk_and_hybrid(monkeypatch):
     """The per-stream band pass (what large calls use; forced here for a small one) keeps the fold buffer exact across
     CELT-only, redundancy and hybrid frames of one stream."""
-    monkeypatch.setenv("MOUSIKI_B200_SERIAL_BANDS", "1")
     lanes, ticks = 64, 12
     total = 0
     for ch in (1, 2):
@@ -244,7 +243,6 @@ def test_gpu_hybrid_packets_with_redundancy_frames(ch, seed):
 
 @pytest.mark.gpu
 def test_gpu_hybrid_redundancy_next_to_celt_only_packets(monkeypatch):
-    monkeypatch.setenv("MOUSIKI_B200_SERIAL_BANDS", "1")
     lanes, ticks = 64, 10
     total = 0
     for ch, seed in ((1, 41), (2, 42)):
@@ -313,7 +311,6 @@ def test_gpu_40_and_60_ms_silk_packets_with_redundancy_frames(name, toc, payload
 
 @pytest.mark.gpu
 def test_gpu_silk_redundancy_right_after_hybrid(monkeypatch):
-    monkeypatch.setenv("MOUSIKI_B200_SERIAL_BANDS", "1")
     lanes, ticks = 48, 10
     total = 0
     for ch, seed in ((1, 161), (2, 162)):
