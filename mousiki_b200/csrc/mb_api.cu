@@ -13,12 +13,14 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo (see __graft_entry__.build()).
 #include <cuda_runtime.h>
 #include <chrono>
+#include <functional>
 #include <stdio.h>
 #include <stdlib.h>
 
 #include <new>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/mousiki_b200.h"
@@ -270,9 +272,12 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
   __shared__ const float* row_x_[DE_WARPS][32];
   __shared__ float* row_out_[DE_WARPS][32];
   __shared__ int row_n_[DE_WARPS][32];
+  __shared__ int16_t* row_o16_[DE_WARPS][32];
   const float** row_x = row_x_[w];
   float** row_out = row_out_[w];
   int* row_n = row_n_[w];
+  int16_t** row_o16 = row_o16_[w];
+  const uint32_t n_main = P.n_lanes * P.n_ticks;
   const int CC = P.CC;
   const uint32_t total = P.n_lanes * (uint32_t)CC;
   const uint32_t idx0 = (blockIdx.x * DE_WARPS + w) * 32;
@@ -304,6 +309,9 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
     int N = 0, hyb = 0, side = 0, late_gain = 0;
     const float* x = nullptr;
     float* out = nullptr;
+    int16_t* out16 = nullptr;            // int16 twin of the row: plain coded CELT-only frames of the int16 path only
+    uint32_t need_cell = 0xffffffffu;    // the main cell whose clipper note this frame contributes to
+    uint32_t over_mask = 0;              // bit r: row r of the warp holds a sample beyond +-1 (or could not be stored as int16)
     if (k < my_frames) {
       const uint32_t f = P.order[(size_t)k * P.n_lanes + lane];
       const FrameMeta m = P.meta[f];
@@ -313,7 +321,15 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
       else {
         const uint32_t fo = row_cell(P, f);
         const uint32_t p = P.pkt_map ? P.pkt_map[fo] : fo;
-        out = P.pcm_f32 ? P.pcm_f32 + pcm_elem_off(P.out_map, p, P.pcm_stride) : nullptr;
+        const size_t eo = pcm_elem_off(P.out_map, p, P.pcm_stride);
+        out = P.pcm_f32 ? P.pcm_f32 + eo : nullptr;
+        if (P.clip_need && out) {
+          need_cell = fo;
+          // anything but a coded CELT-only frame alone in its row (SILK part, side / fade rows, concealment) keeps the clipper's route
+          const uint32_t other = 2u | 8u | 16u | 32u | 64u | 128u | MB_FL_FADE_ROW | MB_FL_PLC | MB_FL_PLC_PITCH;
+          if (f < n_main && !(m.flags & other) && ((((uintptr_t)(P.pcm_i16 + eo)) & 7u) == 0) && ((((uintptr_t)out) & 15u) == 0))
+            out16 = P.pcm_i16 + eo;
+        }
       }
       if (m.flags & 4u) d.mem = 0.f;                 // CELT reset before this frame
       if ((m.flags & 8u) && out) hyb = 1;            // hybrid: add to the SILK samples already in the row
@@ -323,7 +339,7 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
     const unsigned late_mask = __ballot_sync(0xffffffffu, late_gain);
     d.apply_gain = (hyb || late_gain) ? 0 : P.apply_gain;   // hybrid: the gain applies to SILK + CELT, at the store below
     __syncwarp();
-    row_x[l] = x; row_out[l] = out; row_n[l] = N;
+    row_x[l] = x; row_out[l] = out; row_n[l] = N; row_o16[l] = out16;
     const int max_n = __reduce_max_sync(0xffffffffu, N);
     __syncwarp();
     if (max_n == 0) continue;
@@ -359,6 +375,19 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
               if (P.apply_gain && !((late_mask >> r) & 1u)) v *= P.gain;
               o[e] = v;
             }
+          } else if (int16_t* o16 = row_o16[r]) {   // (aligned by construction) float and int16 forms of the same samples
+            o16 += (size_t)k0 * 2;
+            int ov = 0;
+            for (int j = 2 * l; j < cnt; j += 64) {
+              const float2 a = *(const float2*)(tx + j), b = *(const float2*)(ty + j);
+              *(float4*)(o + 2 * j) = make_float4(a.x, b.x, a.y, b.y);
+              ov |= !(a.x >= -1.f && a.x <= 1.f) | !(b.x >= -1.f && b.x <= 1.f) | !(a.y >= -1.f && a.y <= 1.f) | !(b.y >= -1.f && b.y <= 1.f);
+              uint2 q;
+              q.x = (uint32_t)(uint16_t)float2int16(a.x) | ((uint32_t)(uint16_t)float2int16(b.x) << 16);
+              q.y = (uint32_t)(uint16_t)float2int16(a.y) | ((uint32_t)(uint16_t)float2int16(b.y) << 16);
+              *(uint2*)(o16 + 2 * j) = q;
+            }
+            if (__any_sync(0xffffffffu, ov)) over_mask |= 3u << r;
           } else if (((uintptr_t)o & 15u) == 0) {
             for (int j = 2 * l; j < cnt; j += 64) {   // float4 = (x[j], y[j], x[j+1], y[j+1])
               const float2 a = *(const float2*)(tx + j), b = *(const float2*)(ty + j);
@@ -381,12 +410,23 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
               if (P.apply_gain && !((late_mask >> r) & 1u)) v *= P.gain;
               o[k0 + j] = v;
             }
+          } else if (int16_t* o16 = row_o16[r]) {
+            int ov = 0;
+            for (int j = l; j < cnt; j += 32) {
+              const float v = tx[j];
+              o[k0 + j] = v;
+              ov |= !(v >= -1.f && v <= 1.f);
+              o16[k0 + j] = float2int16(v);
+            }
+            if (__any_sync(0xffffffffu, ov)) over_mask |= 1u << r;
           } else
             for (int j = l; j < cnt; j += 32) o[k0 + j] = tx[j];
         }
       }
       __syncwarp();
     }
+    // the clipper's note for this frame's packet (both channels of a stream agree: over_mask carries the pair's bits)
+    if (need_cell != 0xffffffffu) atomicMax(P.clip_need + need_cell, (out16 && !((over_mask >> l) & 1u)) ? 1u : 2u);
   }
   if (live) st.preemph_mem[c] = d.mem;
 }
@@ -419,7 +459,79 @@ template <class Pred> __device__ __forceinline__ int warp_last_below(int hi, int
   }
   return -1;
 }
-__device__ __forceinline__ void soft_clip_channel_warp(float* x, int N, int C, float& a_io, int l) {
+// Everything behind the first region, all regions at once. A region is a maximal run of samples none of which has the sign
+// opposite to its first sample beyond +-1 (zeros join either side and stay zero), its correction depends on nothing but the run's
+// largest magnitude — so the runs can be found and corrected independently: lane l walks samples [lo + l*K, lo + (l+1)*K), closes
+// the runs that begin and end inside its stretch on its own, and the runs that cross stretches are joined by one walk over the 32
+// lanes' summaries (shuffles). Same comparisons, same (maxval - 1) / maxval^2 arithmetic per run as the serial form: bit-identical.
+// Returns the coefficient of the run that reaches N (0 if it needs none) — what the serial loop leaves in `a`.
+__device__ __noinline__ float soft_clip_runs_warp(float* x, int lo, int N, int C, int l) {
+  const int K = (N - lo + 31) >> 5;
+  const int b = lo + l * K, e = min(N, b + K);
+  auto coef = [](float maxval, int sign) {
+    float a = (maxval - 1) / (maxval * maxval);
+    a += a * 2.4e-7f;
+    return sign > 0 ? -a : a;
+  };
+  int fs = 0, cs = 0, nch = 0, head_end = e, seg_begin = b;
+  float head_max = 0.f, seg_max = 0.f;
+  for (int i = b; i < e; i++) {
+    const float v = x[i * C];
+    const int sg = v > 0.f ? 1 : (v < 0.f ? -1 : 0);
+    if (sg != 0 && cs != 0 && sg != cs) {   // a run ends in front of sample i
+      if (nch == 0) { head_max = seg_max; head_end = i; }
+      else if (seg_max > 1.f) {
+        const float a = coef(seg_max, cs);
+        for (int k = seg_begin; k < i; k++) { const float u = x[k * C]; x[k * C] = u + a * u * u; }
+      }
+      nch++; seg_begin = i; seg_max = 0.f;
+    }
+    if (sg != 0) { cs = sg; if (fs == 0) fs = sg; }
+    seg_max = fmaxf(seg_max, fabsf(v));
+  }
+  if (nch == 0) head_max = seg_max;
+  const float tail_max = seg_max;
+  const int tail_begin = seg_begin, ls = cs;
+  // join the runs across lanes
+  int id = 0, csign = 0, my_h = -1, my_t = -1, hs = 0, ts = 0;
+  float cmax = 0.f, hfin = 0.f, tfin = 0.f;
+  for (int j = 0; j < 32; j++) {
+    if (lo + j * K >= N) break;
+    const int fsj = __shfl_sync(0xffffffffu, fs, j), lsj = __shfl_sync(0xffffffffu, ls, j), nchj = __shfl_sync(0xffffffffu, nch, j);
+    const float hmj = __shfl_sync(0xffffffffu, head_max, j), tmj = __shfl_sync(0xffffffffu, tail_max, j);
+    if (fsj != 0 && csign != 0 && fsj != csign) {
+      if (id == my_h) { hfin = cmax; hs = csign; }
+      if (id == my_t) { tfin = cmax; ts = csign; }
+      id++; cmax = 0.f; csign = 0;
+    }
+    if (j == l) my_h = id;
+    cmax = fmaxf(cmax, hmj);
+    if (fsj != 0 && csign == 0) csign = fsj;
+    if (nchj > 0) {
+      if (id == my_h) { hfin = cmax; hs = csign; }
+      if (id == my_t) { tfin = cmax; ts = csign; }
+      id++; cmax = tmj; csign = lsj;
+    }
+    if (j == l) my_t = id;
+  }
+  if (id == my_h) { hfin = cmax; hs = csign; }
+  if (id == my_t) { tfin = cmax; ts = csign; }
+  if (b < e) {
+    if (hfin > 1.f) {
+      const float a = coef(hfin, hs);
+      for (int k = b; k < head_end; k++) { const float u = x[k * C]; x[k * C] = u + a * u * u; }
+    }
+    if (nch > 0 && tfin > 1.f) {
+      const float a = coef(tfin, ts);
+      for (int k = tail_begin; k < e; k++) { const float u = x[k * C]; x[k * C] = u + a * u * u; }
+    }
+  }
+  __syncwarp();
+  return cmax > 1.f ? coef(cmax, csign) : 0.f;
+}
+
+// all_serial: every region in turn (the form the parallel one is checked against; also taken for rows that hold a NaN)
+__device__ __forceinline__ void soft_clip_channel_warp(float* x, int N, int C, float& a_io, int l, bool all_serial) {
   float a = a_io;
   {
     const int first = warp_first(0, N, l, [&](int i) { return x[i * C] * a >= 0; });
@@ -433,6 +545,11 @@ __device__ __forceinline__ void soft_clip_channel_warp(float* x, int N, int C, f
     if (i0 == N) { a = 0; break; }
     const float xi = x[i0 * C];
     const int start = warp_last_below(i0, l, [&](int i) { return !(xi * x[i * C] >= 0); }) + 1;
+    if (!all_serial && start != 0) {   // only a region that opens the row needs the serial form (its ramp, its peak position)
+      __syncwarp();
+      a = soft_clip_runs_warp(x, curr, N, C, l);
+      break;
+    }
     const int end = warp_first(i0, N, l, [&](int i) { return !(xi * x[i * C] >= 0); });
     // peak: the first position of the largest magnitude in [i0, end)
     float mx = -1.f;
@@ -477,12 +594,13 @@ __device__ __forceinline__ void soft_clip_channel_warp(float* x, int N, int C, f
 // skips the serial clipper entirely; otherwise one lane per channel runs it in shared memory. The int16 PCM leaves as
 // coalesced 32-bit stores.
 constexpr int CLIP_WARPS = 4;
+static __device__ unsigned long long g_clip_stats[2];   // packets the clipper skipped (int16 already stored) / worked on; read under MOUSIKI_B200_TIMING
 __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, uint32_t n_ticks, const uint32_t* __restrict__ pkt_map,
                                                               const uint32_t* __restrict__ lane_stream, const FrameMeta* __restrict__ meta,
                                                               const int32_t* __restrict__ samples_out, StreamState* st,
                                                               float* __restrict__ pcm, int16_t* __restrict__ pcm16, uint32_t pcm_stride,
                                                               int CC, const uint32_t* __restrict__ out_map,
-                                                              const uint8_t* __restrict__ flags) {
+                                                              const uint8_t* __restrict__ flags, const uint32_t* __restrict__ clip_need, bool clip_serial) {
   __shared__ __align__(16) float buf_[CLIP_WARPS][2 * MAX_N];
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
   const uint32_t lane = blockIdx.x * CLIP_WARPS + w;
@@ -490,6 +608,7 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
   float* buf = buf_[w];
   StreamState& s = st[lane_stream ? lane_stream[lane] : lane];
   float mem = l < 2 ? s.softclip_mem[l] : 0.f;
+  unsigned n_skipped = 0, n_worked = 0;
   for (uint32_t t = 0; t < n_ticks; t++) {
     const uint32_t f = t * n_lanes + lane;
     const uint32_t fl = meta[f].flags;
@@ -497,6 +616,8 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
     const uint32_t p = pkt_map ? pkt_map[f] : f;
     int n = samples_out[p];
     if (n <= 0) continue;
+    // k_deemph's note (TailParams::clip_need): 1 on every frame of the packet = its int16 samples are stored and none lies beyond +-1
+    bool stored = clip_need && clip_need[f] == 1u;
     if (out_map) {
       // a packet cut into frames is clipped as a whole (src/opus_decoder.rs:1352-1366): its frames sit in the following
       // ticks and in one contiguous stretch of the row; if one of them failed, the reference never reaches the clipper
@@ -508,6 +629,7 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
         if (p2 == 0xffffffffu || !(flags[p2] & 4u)) break;
         const int n2 = samples_out[p2];
         if (n2 <= 0) failed = true; else n += n2;
+        stored = stored && clip_need[t2 * n_lanes + lane] == 1u;
       }
       if (failed) continue;
     }
@@ -518,6 +640,9 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
     const bool lost_pkt = flags && (flags[p] & 3u);   // (nor is one rebuilt from in-band FEC data, :1312)
     if (lost_pkt) mem = 0.f;
     if (!from_float && !__any_sync(0xffffffffu, mem != 0.f)) continue;
+    // the common case of the int16 path: nothing to clip, nothing carried over, and the samples are already in place
+    if (stored && from_float && !lost_pkt && !__any_sync(0xffffffffu, mem != 0.f)) { n_skipped++; continue; }
+    n_worked++;
     const int total = n * CC;
     const size_t eo = pcm_elem_off(out_map, p, pcm_stride);
     float* src = pcm + eo;
@@ -527,7 +652,7 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
       __syncwarp();
     }
     if (total > 2 * MAX_N) buf = src;   // long multi-frame packet: clip in place in the float scratch row
-    int over = 0;
+    int over = 0, nan = 0;
     const bool vec = ((((uintptr_t)src) & 15u) | (uint32_t)(total & 7)) == 0 && ((((uintptr_t)(pcm16 + eo)) & 15u) == 0);
     if (vec) {  // 128-bit loads, several in flight per lane: the row is read once and nothing else hides its latency
       const float4* s4 = (const float4*)src;
@@ -537,6 +662,7 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
       for (int i = l; i < total4; i += 32) {
         float4 v = s4[i];
         over |= !(v.x >= -1.f && v.x <= 1.f) | !(v.y >= -1.f && v.y <= 1.f) | !(v.z >= -1.f && v.z <= 1.f) | !(v.w >= -1.f && v.w <= 1.f);
+        nan |= (v.x != v.x) | (v.y != v.y) | (v.z != v.z) | (v.w != v.w);
         v.x = v.x < -2.f ? -2.f : (v.x > 2.f ? 2.f : v.x); v.y = v.y < -2.f ? -2.f : (v.y > 2.f ? 2.f : v.y);
         v.z = v.z < -2.f ? -2.f : (v.z > 2.f ? 2.f : v.z); v.w = v.w < -2.f ? -2.f : (v.w > 2.f ? 2.f : v.w);
         b4[i] = v;
@@ -545,6 +671,7 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
       for (int i = l; i < total; i += 32) {
         float v = src[i];
         over |= !(v >= -1.f && v <= 1.f);
+        nan |= v != v;
         buf[i] = v < -2.f ? -2.f : (v > 2.f ? 2.f : v);
       }
     }
@@ -552,9 +679,10 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
     over = __any_sync(0xffffffffu, over) && !lost_pkt;
     __syncwarp();
     if (over) {
+      const bool all_serial = clip_serial || __any_sync(0xffffffffu, nan);
       for (int c = 0; c < CC; c++) {
         float a = __shfl_sync(0xffffffffu, mem, c);
-        soft_clip_channel_warp(buf + c, n, CC, a, l);
+        soft_clip_channel_warp(buf + c, n, CC, a, l, all_serial);
         if (l == c) mem = a;
       }
       __syncwarp();
@@ -584,6 +712,7 @@ __global__ void __launch_bounds__(32 * CLIP_WARPS) k_clip_i16(uint32_t n_lanes, 
     buf = buf_[w];
   }
   if (l < 2) s.softclip_mem[l] = mem;
+  if (l == 0) { atomicAdd(&g_clip_stats[0], (unsigned long long)n_skipped); atomicAdd(&g_clip_stats[1], (unsigned long long)n_worked); }
 }
 // res_to_int24 (src/celt/celt_decoder.rs:3165-3176), in place on the float scratch: same 32-bit containers
 __global__ void k_f32_to_i24(float* __restrict__ pcm, size_t n) {
@@ -712,6 +841,10 @@ struct bd_handle {
   float gain = 1.f;
   uint32_t max_frames_per_pass = 0;
   bool want_i24 = false;       // the running host call delivers 24-bit integers (bd_decode_i24)
+  std::vector<uint8_t> h_toc;               // TOC byte of every packet of the call in flight
+  std::function<void()> after_enqueue;      // host work of the call that runs beside the device work
+  bool clip_serial = false;    // MOUSIKI_B200_CLIP_SERIAL=1: the clipper walks the regions of a row one after the other (A/B and test switch)
+  bool fused_i16 = true;       // MOUSIKI_B200_FUSED_I16=0: k_deemph leaves every int16 sample to k_clip_i16 (A/B switch)
   bool parallel_bands = false; // MOUSIKI_B200_PARALLEL_BANDS=1: small calls run CELT-only frames through the all-at-once band pass (see k_energy)
   std::string err;
   uint32_t launches = 0;
@@ -732,7 +865,7 @@ struct bd_handle {
     timeline.push_back({std::string(what) + " " + std::to_string(k), e});
   }
   struct PassOut { bool on = false; char* host_pcm = nullptr; const char* dev_pcm = nullptr; size_t elem = 0; } pass_out;
-  DevBuf states, silk_states, silk_hist, silk_exc, fold, hist, rec, en, meta, series, xbuf, order, side_of, aux_count, aux_main;
+  DevBuf states, silk_states, silk_hist, silk_exc, fold, hist, rec, en, meta, series, xbuf, order, side_of, aux_count, aux_main, clip_need;
   // staging for the host-buffer entry points
   DevBuf d_arena, d_offsets, d_pkt_map, d_out_map, d_lane_stream, d_flags, d_pcm, d_pcm16, d_samples, d_range, d_ids, d_dbg_iy, d_dbg_x;
   std::vector<uint32_t> h_pkt_map, h_lane_stream, h_lane_of_stream, h_epoch, h_count, h_tick, v_range;
@@ -798,11 +931,23 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
   h->gain = cfg->gain_q8 == 0 ? 1.f : (float)exp(0.6931471805599453094 * (double)((3.32192809488736234787f / 5120.0f) * (float)cfg->gain_q8));
   h->max_frames_per_pass = cfg->max_frames_per_pass ? cfg->max_frames_per_pass : (1u << 18);
   { const char* sb = getenv("MOUSIKI_B200_PARALLEL_BANDS"); h->parallel_bands = sb && atoi(sb) > 0; }
+  { const char* sb = getenv("MOUSIKI_B200_CLIP_SERIAL"); h->clip_serial = sb && atoi(sb) > 0; }
+  { const char* sb = getenv("MOUSIKI_B200_FUSED_I16"); h->fused_i16 = !(sb && atoi(sb) == 0); }
   const char* env = getenv("MOUSIKI_B200_MAX_FRAMES_PER_PASS");
   if (env && atoi(env) > 0) h->max_frames_per_pass = (uint32_t)atoi(env);
   auto fail = [&](int code) { bd_destroy(h); return code; };
   if (cudaSetDevice(h->device) != cudaSuccess) return fail(BD_ERR_CUDA);
-  if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) return fail(BD_ERR_CUDA);
+  {
+    // The decode kernels outrank the clipper / copy side: a one-wave kernel (k_parse) that has to share its wave with clipper CTAs
+    // takes twice as long, while the clipper of pass k has the whole of pass k + 1 to finish in (MOUSIKI_B200_MAIN_PRIO: A/B switch).
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    const char* mp = getenv("MOUSIKI_B200_MAIN_PRIO");
+    int prio = mp ? atoi(mp) : (hi < lo ? lo - 1 : lo);
+    if (prio < hi) prio = hi;
+    if (prio > lo) prio = lo;
+    if (cudaStreamCreateWithPriority(&h->own_stream, cudaStreamNonBlocking, prio) != cudaSuccess) return fail(BD_ERR_CUDA);
+  }
   if (cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess) return fail(BD_ERR_CUDA);
   {
     int prio_lo = 0, prio_hi = 0;
@@ -853,7 +998,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
 void bd_destroy(bd_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  DevBuf* all[] = {&h->order, &h->side_of, &h->aux_count, &h->aux_main, &h->states, &h->silk_states, &h->silk_hist, &h->silk_exc, &h->fold, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map, &h->d_out_map,
+  DevBuf* all[] = {&h->order, &h->side_of, &h->aux_count, &h->aux_main, &h->clip_need, &h->states, &h->silk_states, &h->silk_hist, &h->silk_exc, &h->fold, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map, &h->d_out_map,
                    &h->d_lane_stream, &h->d_flags, &h->d_pcm, &h->d_pcm16, &h->d_samples, &h->d_range, &h->d_ids, &h->d_dbg_iy, &h->d_dbg_x};
   for (DevBuf* b : all) b->release();
   for (auto& sp : h->prof_spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -1030,12 +1175,16 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
   CK(h->side_of.ensure((size_t)cells_max * sizeof(uint32_t)));
   CK(h->aux_count.ensure(sizeof(uint32_t)));
   CK(h->aux_main.ensure((size_t)aux_cap * sizeof(uint32_t)));
+  if (d_pcm_i16) CK(h->clip_need.ensure((size_t)2 * cells_max * sizeof(uint32_t)));
   float* pcm_f32 = d_pcm_f32;
   if (d_pcm_i16) {  // the i16 path decodes to a float scratch, soft-clips, then rounds (src/opus_decoder.rs:1679-1712)
     CK(h->d_pcm.ensure((size_t)n_packets * pcm_stride * sizeof(float)));
     pcm_f32 = h->d_pcm.as<float>();
   }
   const int cap_per_ch = (int)(pcm_stride / (uint32_t)CC);
+  // The clipper runs in line with the decode kernels: beside them (its own stream, MOUSIKI_B200_CLIP_STREAM=1) its CTAs share the
+  // one wave k_parse of the next pass fits in and double that kernel's time (measured: 58.6 vs 54.4 ms of device time per call).
+  cudaStream_t clip_s = getenv("MOUSIKI_B200_CLIP_STREAM") ? h->clip_stream : s;
   // Pass sizes. With the PCM going back to the host pass by pass, only the last pass's copy is exposed: the tail of the
   // call is cut into a short final pass (a quarter of what is left) so that most of the copy hides behind kernels.
   // Multi-frame calls keep the regular grid of passes (the host scheduler aligned frame groups to it).
@@ -1145,6 +1294,12 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     tp.apply_gain = h->cfg.gain_q8 != 0; tp.pcm_f32 = pcm; tp.pcm_stride = pcm_stride; tp.out_map = d_out_map; tp.xbuf = h->xbuf.as<float>();
     tp.order = order_p; tp.order_n = order_n_p; tp.side_of = h->side_of.as<uint32_t>();
     tp.aux_main = h->aux_main.as<uint32_t>(); tp.aux_base = cells_max;
+    uint32_t* clip_need_p = nullptr;
+    if (d_pcm_i16 && h->fused_i16) {   // (double-buffered like the frame meta: the clipper of pass pi reads it beside pass pi + 1; s is behind ev_clip_done via join 1)
+      clip_need_p = h->clip_need.as<uint32_t>() + (pi & 1) * (size_t)cells_max;
+      CK(cudaMemsetAsync(clip_need_p, 0, (size_t)cells * sizeof(uint32_t), s));
+      tp.pcm_i16 = d_pcm_i16 + shift * pcm_stride; tp.clip_need = clip_need_p;
+    }
     h->prof_begin(BD_K_COMB, s);
     k_comb<<<(n_lanes * CC + COMB_WARPS - 1) / COMB_WARPS, 32 * COMB_WARPS, 0, s>>>(tp);
     k_comb_plc<<<n_lanes, 32, 0, s>>>(tp);   // lanes with a frame concealed by pitch repetition (the others leave after one look at their flags)
@@ -1173,7 +1328,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
       return BD_OK;
     };
     // the stream the pass's PCM is final on: the clipper's for int16 output, the main stream for float output
-    cudaStream_t fin = d_pcm_i16 ? h->clip_stream : s;
+    cudaStream_t fin = d_pcm_i16 ? clip_s : s;
     auto ship = [&](size_t c0, size_t nc) -> int {
       cudaEvent_t ev;
       { int rc = next_event(&ev); if (rc != BD_OK) return rc; }
@@ -1194,7 +1349,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
         cudaEvent_t ev;
         { int rc = next_event(&ev); if (rc != BD_OK) return rc; }
         CK(cudaEventRecord(ev, s));
-        CK(cudaStreamWaitEvent(h->clip_stream, ev, 0));
+        CK(cudaStreamWaitEvent(clip_s, ev, 0));
       }
       const uint32_t n_chunks = h->pass_out.on ? (nt < 4u ? nt : 4u) : 1u;
       for (uint32_t c = 0; c < n_chunks; c++) {
@@ -1204,7 +1359,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
         k_clip_i16<<<(n_lanes + CLIP_WARPS - 1) / CLIP_WARPS, 32 * CLIP_WARPS, 0, fin>>>(
             n_lanes, tb - ta, map ? map + c0 : nullptr, d_lane_stream, meta_p + c0, map ? samples : samples + c0,
             h->states.as<StreamState>(), map ? pcm : pcm + c0 * pcm_stride, d_pcm_i16 + (map ? 0 : (shift + c0) * pcm_stride), pcm_stride, CC,
-            d_out_map, flg);
+            d_out_map, flg, clip_need_p ? clip_need_p + c0 : nullptr, h->clip_serial);
         h->prof_end(fin);
         h->launches += 1;
         if (h->pass_out.on) { int rc = ship(c0, (size_t)(tb - ta) * n_lanes); if (rc != BD_OK) return rc; }
@@ -1219,7 +1374,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
   if (d_pcm_i16) {  // join the clipper back into the caller's stream
     const size_t k = h->pass_event_next++;
     while (h->pass_events.size() <= k) { cudaEvent_t e; CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->pass_events.push_back(e); }
-    CK(cudaEventRecord(h->pass_events[k], h->clip_stream));
+    CK(cudaEventRecord(h->pass_events[k], clip_s));
     CK(cudaStreamWaitEvent(s, h->pass_events[k], 0));
   }
   CK(cudaGetLastError());
@@ -1359,7 +1514,7 @@ static int decode_host_impl(bd_handle* h, const uint8_t* arena, const uint32_t* 
                               h->d_lane_stream.as<uint32_t>(), d_f32, d_i16, pcm_stride, h->d_samples.as<int32_t>(),
                               h->d_range.as<uint32_t>(), n_rows, s, d_dbg_iy, d_dbg_x, d_out_map);
   h->pass_out.on = false;
-  if (rc != BD_OK) { cudaStreamSynchronize(h->copy_stream); return rc; }
+  if (rc != BD_OK) { cudaStreamSynchronize(h->copy_stream); h->after_enqueue = nullptr; return rc; }
   if (h->want_i24 && pcm_elems) {
     k_f32_to_i24<<<(unsigned)((pcm_elems + 255) / 256), 256, 0, s>>>(d_f32, pcm_elems);
     h->launches += 1;
@@ -1371,6 +1526,7 @@ static int decode_host_impl(bd_handle* h, const uint8_t* arena, const uint32_t* 
   CK(cudaMemcpyAsync(samples_out, h->d_samples.p, (size_t)n_packets * 4, cudaMemcpyDeviceToHost, s));
   CK(cudaMemcpyAsync(final_range_out, h->d_range.p, (size_t)n_packets * 4, cudaMemcpyDeviceToHost, s));
   const auto t_enq = std::chrono::steady_clock::now();
+  if (h->after_enqueue) { h->after_enqueue(); h->after_enqueue = nullptr; }   // host bookkeeping that nothing on the device waits for
   CK(cudaStreamSynchronize(s));
   const auto t_dev = std::chrono::steady_clock::now();
   CK(cudaStreamSynchronize(h->copy_stream));
@@ -1378,6 +1534,9 @@ static int decode_host_impl(bd_handle* h, const uint8_t* arena, const uint32_t* 
     auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
     fprintf(stderr, "[mousiki_b200] host schedule + staging %.2f ms, enqueue %.2f ms, wait for kernels %.2f ms, wait for the last copy %.2f ms\n",
             ms(t_entry, t_sched), ms(t_sched, t_enq), ms(t_enq, t_dev), ms(t_dev, std::chrono::steady_clock::now()));
+    unsigned long long cs[2] = {0, 0};
+    if (cudaMemcpyFromSymbol(cs, g_clip_stats, sizeof(cs)) == cudaSuccess)
+      fprintf(stderr, "[mousiki_b200] clipper since load: %llu packets skipped (int16 stored by k_deemph), %llu worked on\n", cs[0], cs[1]);
     for (size_t i = 1; i < h->timeline.size(); i++) {
       float t = 0;
       cudaEventElapsedTime(&t, h->timeline[0].second, h->timeline[i].second);
@@ -1406,20 +1565,56 @@ static int decode_host(bd_handle* h, const uint8_t* arena, const uint32_t* offse
                        const uint8_t* flags, float* pcm_f32, int16_t* pcm_i16, uint32_t pcm_stride, int32_t* samples_out,
                        uint32_t* final_range_out) {
   if (!h || !arena || !offsets || !stream_ids || !samples_out || !final_range_out || (!pcm_f32 && !pcm_i16)) return BD_ERR_BAD_ARG;
+  const auto t_in = std::chrono::steady_clock::now();
+  h->after_enqueue = nullptr;
   if (h->track.size() != h->cfg.n_streams) h->track.assign(h->cfg.n_streams, mbh::StreamTrack());
-  for (uint32_t p = 0; p < n_packets; p++) if (stream_ids[p] >= h->cfg.n_streams) return BD_ERR_BAD_ARG;
-  if (n_packets == 0 || !mbh::needs_split(arena, offsets, flags, n_packets)) {
-    // (no split: still remember what the decoders took in, for a later lost packet)
-    for (uint32_t p = 0; p < n_packets; p++) {
-      const uint32_t n = offsets[p + 1] - offsets[p];
-      if (n == 0 || (flags && (flags[p] & 3u))) continue;
-      const uint8_t toc = arena[offsets[p]];
-      if (mbh::toc_frame_samples(toc) > (int)(pcm_stride / (uint32_t)h->CC) || n - 1 > 1275) continue;
-      h->track[stream_ids[p]].frame_size = mbh::toc_frame_samples(toc);
-      h->track[stream_ids[p]].mode = (toc & 0x80) ? 1002 : ((toc & 0x60) == 0x60 ? 1001 : 1000);
-    }
-    return decode_host_impl(h, arena, offsets, stream_ids, n_packets, flags, pcm_f32, pcm_i16, pcm_stride, samples_out, final_range_out,
-                            nullptr, n_packets);
+  // One walk over the packets (each TOC byte is a cache miss of its own in a large arena): stream ids in range, does any packet
+  // need cutting into frames, and the TOC bytes kept aside for the note below.
+  bool split = false;
+  h->h_toc.resize(n_packets);
+  {
+    // (large calls: the walk is spread over a few host threads — it is latency-bound on the TOC misses and sits in front of all device work)
+    const uint32_t n_thr = n_packets >= (1u << 16) ? 8u : 1u;
+    uint8_t res[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // bit 0: a packet needs cutting, bit 1: a stream id out of range
+    auto walk = [&](uint32_t k) {
+      const uint32_t p0 = (uint32_t)((uint64_t)n_packets * k / n_thr), p1 = (uint32_t)((uint64_t)n_packets * (k + 1) / n_thr);
+      uint8_t r = 0;
+      for (uint32_t p = p0; p < p1; p++) {
+        if (stream_ids[p] >= h->cfg.n_streams) r |= 2;
+        const uint32_t n = offsets[p + 1] - offsets[p];
+        const uint8_t toc = n ? arena[offsets[p]] : 0;
+        h->h_toc[p] = toc;
+        if ((n && (toc & 3u)) || (flags && ((flags[p] & 3u) || n == 0))) r |= 1;   // (mbh::needs_split)
+      }
+      res[k] = r;
+    };
+    std::vector<std::thread> thr;
+    for (uint32_t k = 1; k < n_thr; k++) thr.emplace_back(walk, k);
+    walk(0);
+    for (auto& t : thr) t.join();
+    uint8_t all = 0;
+    for (uint32_t k = 0; k < n_thr; k++) all |= res[k];
+    if (all & 2) return BD_ERR_BAD_ARG;
+    split = (all & 1) != 0;
+  }
+  if (n_packets == 0 || !split) {
+    // (no split: still remember what the decoders took in, for a later lost packet — after the device work is queued, beside it)
+    h->after_enqueue = [=]() {
+      for (uint32_t p = 0; p < n_packets; p++) {
+        const uint32_t n = offsets[p + 1] - offsets[p];
+        if (n == 0 || (flags && (flags[p] & 3u))) continue;
+        const uint8_t toc = h->h_toc[p];
+        if (mbh::toc_frame_samples(toc) > (int)(pcm_stride / (uint32_t)h->CC) || n - 1 > 1275) continue;
+        h->track[stream_ids[p]].frame_size = mbh::toc_frame_samples(toc);
+        h->track[stream_ids[p]].mode = (toc & 0x80) ? 1002 : ((toc & 0x60) == 0x60 ? 1001 : 1000);
+      }
+    };
+    if (getenv("MOUSIKI_B200_TIMING"))
+      fprintf(stderr, "[mousiki_b200] packet walk %.2f ms\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_in).count());
+    const int rc0 = decode_host_impl(h, arena, offsets, stream_ids, n_packets, flags, pcm_f32, pcm_i16, pcm_stride, samples_out, final_range_out,
+                                     nullptr, n_packets);
+    if (h->after_enqueue) { h->after_enqueue(); h->after_enqueue = nullptr; }   // (a call that failed before it got there)
+    return rc0;
   }
   mbh::Split& S = h->split;
   mbh::split_batch(arena, offsets, stream_ids, flags, n_packets, (int)(pcm_stride / (uint32_t)h->CC), h->CC, &S, h->track.data());

@@ -40,6 +40,10 @@ struct TailParams {
   const uint32_t* side_of = nullptr;  // per main cell: the cell whose side row k_fade blends into the packet's row
   const uint32_t* aux_main = nullptr; // per auxiliary cell whose frame belongs in a packet's row: that packet's main cell
   uint32_t aux_base = 0;
+  // int16 output path: k_deemph also stores the int16 form of a plain coded CELT-only frame and notes per main cell whether the
+  // clipper still has work there (0: not judged, 1: int16 stored and no sample beyond +-1, 2: go through k_clip_i16)
+  int16_t* pcm_i16 = nullptr;
+  uint32_t* clip_need = nullptr;
 };
 // the cell whose packet row a frame of cell f is written to
 MB_DEV uint32_t row_cell(const TailParams& P, uint32_t f) { return f >= P.n_lanes * P.n_ticks ? P.aux_main[f - P.aux_base] : f; }
