@@ -43,8 +43,19 @@ UNIT = "audio-s/s"
 WORKLOAD = "celt_only_48k_stereo_20ms_64kbps_1e4_streams_x50_frames"
 
 
+CORPUS = os.environ.get("MOUSIKI_BENCH_CORPUS", "fuzz")   # set by --corpus
+CORPUS_NOTE = {
+    "fuzz": "P-fuzz: TOC 0xFC + seeded random bytes (reference fuzz construction)",
+    "struct": "P-struct: TOC 0xFC + 160 bytes written through the restated decoder (oracle/gen_corpus.cpp): band energies along a "
+              "per-stream envelope, ~10 % transients, post-filter on ~30 % of the frames, PCM inside +-1 on 99.8 % of the packets",
+}
+
+
 def make_corpus(streams, ticks, seed):
-    """[ticks][streams] grid of TOC(0xFC: CELT FB 20 ms stereo code 0) + 160 random bytes."""
+    """[ticks][streams] grid of TOC(0xFC: CELT FB 20 ms stereo code 0) + 160 bytes: random (P-fuzz) or structured (P-struct)."""
+    if CORPUS == "struct":
+        import helpers
+        return helpers.struct_grid(streams, ticks, PAYLOAD, 0xFC, CH, seed=seed)
     rng = np.random.default_rng(seed)
     n = streams * ticks
     arena = rng.integers(0, 256, size=(n, PAYLOAD + 1), dtype=np.uint8)
@@ -171,7 +182,7 @@ def run_reference(args):
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-        "data": "synthetic", "config": {"workload": WORKLOAD, "note": "CPU restatement of mousiki's float decoder (oracle/); the Rust "
+        "data": "synthetic", "config": {"workload": WORKLOAD, "packets": CORPUS_NOTE[CORPUS], "note": "CPU restatement of mousiki's float decoder (oracle/); the Rust "
                                         "reference cannot be built on this box (no cargo/rustc)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "build": oracle_native_lib()[1]},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -445,7 +456,7 @@ def run_gpu(args):
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD if not strong else f"celt_only_48k_stereo_20ms_64kbps_{total_streams}_streams_x{ticks}_frames_one_job",
                    "streams_per_gpu": streams, "streams_total": total_streams, "frames_per_stream_per_step": ticks, "payload_bytes": PAYLOAD,
-                   "packets": "P-fuzz: TOC 0xFC + seeded random bytes (reference fuzz construction)", "output": "f32 PCM left in HBM",
+                   "packets": CORPUS_NOTE[CORPUS], "output": "f32 PCM left in HBM",
                    "l2": "per-step working set (scratch + PCM, several GB) exceeds the 126 MB L2", "sharding": f"streams by rank, {world} rank(s), no data-path collective"},
         "e2e": None if args.no_e2e else {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h_arena.nbytes + h_offsets.nbytes + h_ids.nbytes + n),
                 "d2h_bytes_per_step": int(h_pcm.nbytes + h_samples.nbytes + h_range.nbytes), "ms_per_step": e2e_ms / e2e_steps,
@@ -489,6 +500,7 @@ def _emit(line):
 
 
 def main():
+    global CORPUS
     _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -501,7 +513,10 @@ def main():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: --streams streams per GPU (the driver's contract); strong: one fixed corpus of --streams streams "
                          "(default 10^5) sharded over the ranks, per-stream checksums all-gathered and compared with the golden vector")
+    ap.add_argument("--corpus", default=CORPUS, choices=["fuzz", "struct"],
+                    help="packet construction of the weak-scaling workload: fuzz (TOC + random bytes) or struct (oracle/gen_corpus.cpp)")
     args = ap.parse_args()
+    CORPUS = args.corpus
     if args.impl == "reference":
         return run_reference(args)
     return run_gpu(args)

@@ -300,10 +300,10 @@ static int compute_allocation(int start, int end, const int* offsets, const int*
 }
 
 // ---------------------------------------------------------------- quant_bands.rs
-static int laplace_decode(EcDec* dec, uint32_t fs, uint32_t decay) {  // quant_bands.rs:90-125
+// the symbol and its interval [fl, high) for a decoded position fm (the arithmetic of ec_laplace_decode, quant_bands.rs:90-125)
+static int laplace_map(uint32_t fm, uint32_t fs, uint32_t decay, uint32_t* fl_out, uint32_t* high_out) {
   int val = 0;
   uint32_t fl = 0;
-  uint32_t fm = dec->decode_bin(15);
   if (fm >= fs) {
     val++;
     fl = fs;
@@ -324,10 +324,32 @@ static int laplace_decode(EcDec* dec, uint32_t fs, uint32_t decay) {  // quant_b
     }
     if (fm < fl + fs) val = -val; else fl += fs;
   }
-  uint32_t high = fl + fs < 32768u ? fl + fs : 32768u;
+  *fl_out = fl;
+  *high_out = fl + fs < 32768u ? fl + fs : 32768u;
+  return val;
+}
+static int laplace_decode(EcDec* dec, uint32_t fs, uint32_t decay) {  // quant_bands.rs:90-125
+  uint32_t fl, high;
+  const int val = laplace_map(dec->decode_bin(15), fs, decay, &fl, &high);
   dec->update(fl, high, 32768u);
   return val;
 }
+#ifdef ORC_GEN
+// corpus writer: make the next laplace_decode return `want` (or the nearest value the model can express)
+static void gen_force_laplace(EcDec* dec, uint32_t fs, uint32_t decay, int want) {
+  uint32_t fm = 0, best_fm = 0;
+  int best_d = 1 << 30;
+  for (int guard = 0; guard < 4096 && fm < 32768u; guard++) {
+    uint32_t fl, high;
+    const int v = laplace_map(fm, fs, decay, &fl, &high);
+    const int d = v > want ? v - want : want - v;
+    if (d < best_d) { best_d = d; best_fm = fl; }
+    if (d == 0 || high <= fm) break;
+    fm = high;
+  }
+  dec->gen->forced = best_fm;
+}
+#endif
 
 // quant_bands.rs:902-950. Returns nothing; `qi_out` (optional) receives the raw symbols.
 static void unquant_coarse_energy(int start, int end, float* oldE, int intra, EcDec* dec, int C, int lm, bool q8) {
@@ -343,6 +365,16 @@ static void unquant_coarse_energy(int start, int end, float* oldE, int intra, Ec
       int qi;
       if (budget - tell >= 15) {
         int pi = 2 * imin(i, 20);
+#ifdef ORC_GEN
+        if (dec->gen) {   // corpus writer: the band energy follows the stream's envelope (level, tilt, slow loudness, per-band wander)
+          GenCtl* g = dec->gen;
+          const float target = g->level + g->loud + g->tilt * (float)(10 - i) * 0.1f + g->band_dev[idx];
+          const float pred = coef * fmax32(oldE[idx], -9.0f) + prev[c];
+          int want = (int)floorf(target - pred + 0.5f);
+          want = want < -12 ? -12 : (want > 12 ? 12 : want);
+          gen_force_laplace(dec, (uint32_t)prob[pi] << 7, (uint32_t)prob[pi + 1] << 6, want);
+        }
+#endif
         qi = laplace_decode(dec, (uint32_t)prob[pi] << 7, (uint32_t)prob[pi + 1] << 6);
       } else if (budget - tell >= 2) {
         qi = dec->icdf(kSmallEnergyIcdf, 2);
@@ -1680,16 +1712,27 @@ int celt_decode_with_ec(CeltDecoder* st, const uint8_t* data, int len, float* pc
   int tell = dec->tell();
   int silence = 0;
   if (tell >= len_bits) silence = 1;
-  else if (tell == 1) silence = dec->bit_logp(15);
+  else if (tell == 1) {
+#ifdef ORC_GEN
+    if (dec->gen) dec->gen->forced = 0;
+#endif
+    silence = dec->bit_logp(15);
+  }
   if (silence) { dec->nbits_total += len_bits - dec->tell(); tell = len_bits; }
   else tell = dec->tell();
 
   float postfilter_gain = 0.f;
   int postfilter_pitch = 0, postfilter_tapset = 0;
   if (start == 0 && tell + 16 <= len_bits) {
+#ifdef ORC_GEN
+    if (dec->gen) dec->gen->forced = dec->gen->unit() < dec->gen->p_postfilter;
+#endif
     if (dec->bit_logp(1)) {
       int octave = (int)dec->uint(6);
       postfilter_pitch = (16 << octave) + (int)dec->bits(4 + octave) - 1;
+#ifdef ORC_GEN
+      if (dec->gen) dec->gen->forced = dec->gen->next() % 3u;   // a mild comb (gain 0.09 - 0.28), as on voiced material
+#endif
       int qg = (int)dec->bits(3);
       if (dec->tell() + 2 <= len_bits) postfilter_tapset = dec->icdf(kTapsetIcdf, 2);
       postfilter_gain = 0.09375f * (float)(qg + 1);
@@ -1697,10 +1740,19 @@ int celt_decode_with_ec(CeltDecoder* st, const uint8_t* data, int len, float* pc
     tell = dec->tell();
   }
   int is_transient = 0;
+#ifdef ORC_GEN
+  if (dec->gen) dec->gen->forced = dec->gen->unit() < dec->gen->p_transient;
+#endif
   if (lm > 0 && tell + 3 <= len_bits) { is_transient = dec->bit_logp(3); tell = dec->tell(); }
+#ifdef ORC_GEN
+  if (dec->gen) dec->gen->forced = dec->gen->frame == 0;   // intra energy on the first frame of a stream only
+#endif
   const int short_blocks = is_transient ? M : 0;
   int intra = 0;
   if (tell + 3 <= len_bits) intra = dec->bit_logp(3);
+#ifdef ORC_GEN
+  if (dec->gen) dec->gen->forced = -1;
+#endif
   if (!intra && st->loss_duration != 0) {   // celt_decoder.rs:2943-2969: the first good frame after a loss starts from safer energies
     const int missing = imin(10, st->loss_duration >> lm);
     const float safety = lm == 0 ? 1.5f : (lm == 1 ? 0.5f : 0.0f);

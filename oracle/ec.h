@@ -18,7 +18,37 @@ static const uint32_t EC_CODE_BOT = EC_CODE_TOP >> EC_SYM_BITS;
 
 static inline int ec_ilog(uint32_t v) { return v ? 32 - __builtin_clz(v) : 0; }
 
+#ifdef ORC_GEN
+struct EcEnc;
+struct EcDec;
+// Corpus writer (tools/, bench.py --corpus struct; never part of the checker build): with ORC_GEN defined a decoder may be
+// "driven": every symbol it asks for is CHOSEN (drawn from the symbol's own model, or forced by the site that asks) and written
+// to a range encoder, whose rng / bit count the decoder mirrors — ec_tell is the same function of both, so the decoder's budget
+// logic walks exactly the path a decoder reading the finished bytes will walk.
+struct GenCtl {
+  EcEnc* enc = nullptr;
+  uint64_t s = 0x9e3779b97f4a7c15ull;
+  int64_t forced = -1;            // the next draw, when a site wants a particular symbol
+  uint32_t next() { s ^= s << 13; s ^= s >> 7; s ^= s << 17; return (uint32_t)(s >> 16); }
+  float unit() { return (float)(next() & 0xffffff) * (1.0f / 16777216.0f); }
+  uint32_t draw(uint32_t ft) {
+    uint32_t v = forced >= 0 ? (uint32_t)forced : next() % ft;
+    forced = -1;
+    return v < ft ? v : ft - 1;
+  }
+  // policy state of the CELT sites (celt_oracle.cpp)
+  int frame = 0;
+  float level = 0.f, tilt = 0.f, loud = 0.f, band_dev[2 * 21] = {0};
+  float p_transient = 0.1f, p_postfilter = 0.3f;
+};
+#endif
+
 struct EcDec {
+#ifdef ORC_GEN
+  GenCtl* gen = nullptr;
+  inline void gen_sync();
+  inline void gen_open(GenCtl* g, uint32_t len);
+#endif
   const uint8_t* buf = nullptr;
   uint32_t storage = 0, end_offs = 0, end_window = 0;
   int nend_bits = 0, nbits_total = 0;
@@ -47,23 +77,35 @@ struct EcDec {
     normalize();
   }
   uint32_t decode(uint32_t ft) {
+#ifdef ORC_GEN
+    if (gen) return gen->draw(ft);
+#endif
     ext = rng / ft;
     uint32_t s = val / ext;
     return ft - (s + 1 < ft ? s + 1 : ft);
   }
   uint32_t decode_bin(unsigned bits) {
+#ifdef ORC_GEN
+    if (gen) return gen->draw(1u << bits);
+#endif
     ext = rng >> bits;
     uint32_t s = val / ext;
     uint32_t top = 1u << bits;
     return top - (s + 1 < top ? s + 1 : top);
   }
   void update(uint32_t fl, uint32_t fh, uint32_t ft) {
+#ifdef ORC_GEN
+    if (gen) { gen_update(fl, fh, ft); return; }
+#endif
     uint32_t s = ext * (ft - fh);
     val -= s;
     rng = fl > 0 ? ext * (fh - fl) : rng - s;
     normalize();
   }
   int bit_logp(unsigned logp) {
+#ifdef ORC_GEN
+    if (gen) return gen_bit_logp(logp);
+#endif
     uint32_t r = rng, d = val, s = r >> logp;
     int ret = d < s;
     if (!ret) val = d - s;
@@ -72,6 +114,9 @@ struct EcDec {
     return ret;
   }
   int icdf(const uint8_t* tab, unsigned ftb) {
+#ifdef ORC_GEN
+    if (gen) return gen_icdf(tab, ftb);
+#endif
     uint32_t s = rng, d = val, r = s >> ftb, t;
     int ret = -1;
     do { t = s; s = r * tab[++ret]; } while (d < s);
@@ -80,6 +125,9 @@ struct EcDec {
     return ret;
   }
   uint32_t bits(unsigned n) {
+#ifdef ORC_GEN
+    if (gen) return gen_bits(n);
+#endif
     uint32_t window = end_window; int available = nend_bits;
     if ((unsigned)available < n) {
       do { window |= (uint32_t)read_byte_from_end() << available; available += EC_SYM_BITS; }
@@ -91,6 +139,9 @@ struct EcDec {
     return ret;
   }
   uint32_t uint(uint32_t ft) {
+#ifdef ORC_GEN
+    if (gen) return gen_uint(ft);
+#endif
     ft--;
     int ftb = ec_ilog(ft);
     if (ftb > EC_UINT_BITS) {
@@ -118,6 +169,13 @@ struct EcDec {
     b += r > corr[b];
     return nbits - (uint32_t)((l << 3) + (int)b);
   }
+#ifdef ORC_GEN
+  inline void gen_update(uint32_t fl, uint32_t fh, uint32_t ft);
+  inline int gen_bit_logp(unsigned logp);
+  inline int gen_icdf(const uint8_t* tab, unsigned ftb);
+  inline uint32_t gen_bits(unsigned n);
+  inline uint32_t gen_uint(uint32_t ft);
+#endif
 };
 
 // Range ENCODER (libopus-format bitstream writer). Used only to synthesise
@@ -227,5 +285,56 @@ struct EcEnc {
     }
   }
 };
+
+#ifdef ORC_GEN
+inline void EcDec::gen_sync() { rng = gen->enc->rng; nbits_total = gen->enc->nbits_total; }
+inline void EcDec::gen_open(GenCtl* g, uint32_t len) {
+  gen = g; buf = nullptr; storage = len; error = 0; end_offs = 0; end_window = 0; nend_bits = 0; offs = 0; val = 0; ext = 0; rem = 0;
+  gen_sync();
+}
+inline void EcDec::gen_update(uint32_t fl, uint32_t fh, uint32_t ft) { gen->enc->encode(fl, fh, ft); gen_sync(); }
+inline int EcDec::gen_bit_logp(unsigned logp) {
+  int v = gen->forced >= 0 ? (int)(gen->forced != 0) : (int)((gen->next() & ((1u << logp) - 1u)) == 0);
+  gen->forced = -1;
+  gen->enc->bit_logp(v, logp);
+  gen_sync();
+  return v;
+}
+inline int EcDec::gen_icdf(const uint8_t* tab, unsigned ftb) {
+  int n = 0;
+  while (tab[n] != 0) n++;
+  n++;                                     // symbols 0 .. n-1, tab[n-1] == 0
+  int sym;
+  if (gen->forced >= 0) { sym = (int)gen->forced; gen->forced = -1; if (sym >= n) sym = n - 1; }
+  else {                                   // drawn from the table's own distribution
+    const uint32_t ft = 1u << ftb, u = gen->next() % ft;
+    sym = 0;
+    while (sym < n - 1 && ft - tab[sym] <= u) sym++;
+  }
+  // (a symbol of probability zero cannot be written: move to a neighbour that has some)
+  while (sym > 0 && tab[sym - 1] == tab[sym]) sym--;
+  if (sym == 0 && (1u << ftb) == tab[0]) { sym = 1; while (sym < n - 1 && tab[sym - 1] == tab[sym]) sym++; }
+  gen->enc->icdf(sym, tab, ftb);
+  gen_sync();
+  return sym;
+}
+inline uint32_t EcDec::gen_bits(unsigned n) {
+  if (n == 0) return 0;
+  uint32_t v = gen->forced >= 0 ? (uint32_t)gen->forced : gen->next();
+  gen->forced = -1;
+  v &= n >= 32 ? 0xffffffffu : ((1u << n) - 1u);
+  gen->enc->bits(v, n);
+  nbits_total = gen->enc->nbits_total;
+  return v;
+}
+inline uint32_t EcDec::gen_uint(uint32_t ft) {
+  uint32_t t;
+  if (gen->forced >= 0) { t = (uint32_t)gen->forced; gen->forced = -1; if (t >= ft) t = ft - 1; }
+  else t = (uint32_t)((((uint64_t)gen->next() << 16) ^ gen->next()) % ft);
+  gen->enc->uint(t, ft);
+  gen_sync();
+  return t;
+}
+#endif
 
 }  // namespace orc

@@ -200,3 +200,37 @@ def split_batch(arena, offsets, stream_ids, cap_per_ch, channels, flags=None):
                         ptr(out["first"]))
     out["arena"] = out["arena"][:nbytes.value]
     return out
+
+
+_ORCGEN = None
+
+
+def orcgen_lib():
+    global _ORCGEN
+    if _ORCGEN is None:
+        lib = C.CDLL(str(_make(ROOT / "oracle", "_build/liborcgen.so")))
+        lib.orcgen_celt_grid.argtypes = [C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_uint32,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        _ORCGEN = lib
+    return _ORCGEN
+
+
+STRUCT_LEVEL = 0.0   # mean band energy of a P-struct stream relative to the codec's eMeans (log2 units); see DESIGN.md section 6
+
+
+def struct_grid(n_lanes: int, n_ticks: int, payload: int, toc: int, channels: int, seed: int = 1, level: float = STRUCT_LEVEL,
+                want_pcm: bool = False, quirks: int = QUIRKS_MOUSIKI, threads=None):
+    """P-struct: [n_ticks][n_lanes] grid of structured CELT-only packets (oracle/gen_corpus.cpp: written through the restated
+    decoder, band energies steered along a per-stream envelope, ~10 % transients, post-filter on ~30 % of the frames, PCM inside
+    +-1). Same layout as fuzz_grid. -> (arena, offsets[, pcm, final_range])."""
+    lib = orcgen_lib()
+    n = n_lanes * n_ticks
+    arena = np.zeros(n * (payload + 1), dtype=np.uint8)
+    offsets = np.zeros(n + 1, dtype=np.uint32)
+    frame = 120 << ((toc >> 3) & 3)
+    pcm = np.zeros((n, frame * channels), dtype=np.float32) if want_pcm else None
+    rng = np.zeros(n, dtype=np.uint32) if want_pcm else None
+    rc = lib.orcgen_celt_grid(seed, n_lanes, n_ticks, payload, toc, channels, level, quirks & 0x7F, ptr(arena), ptr(offsets), ptr(pcm), ptr(rng),
+                              threads or os.cpu_count() or 1)
+    assert rc == 0, "the corpus writer could not finish a frame"
+    return (arena, offsets, pcm, rng) if want_pcm else (arena, offsets)
