@@ -841,6 +841,7 @@ struct bd_handle {
   float gain = 1.f;
   uint32_t max_frames_per_pass = 0;
   bool want_i24 = false;       // the running host call delivers 24-bit integers (bd_decode_i24)
+  const uint8_t* arena_staged = nullptr;    // the host arena whose bytes are already on their way to d_arena (decode_host)
   std::vector<uint8_t> h_toc;               // TOC byte of every packet of the call in flight
   std::function<void()> after_enqueue;      // host work of the call that runs beside the device work
   bool clip_serial = false;    // MOUSIKI_B200_CLIP_SERIAL=1: the clipper walks the regions of a row one after the other (A/B and test switch)
@@ -1466,7 +1467,8 @@ static int decode_host_impl(bd_handle* h, const uint8_t* arena, const uint32_t* 
   CK(h->d_samples.ensure((size_t)n_packets * 4));
   CK(h->d_range.ensure((size_t)n_packets * 4));
   h->mark("start", 0, s);
-  CK(cudaMemcpyAsync(h->d_arena.p, arena, arena_bytes, cudaMemcpyHostToDevice, s));
+  if (h->arena_staged != arena) CK(cudaMemcpyAsync(h->d_arena.p, arena, arena_bytes, cudaMemcpyHostToDevice, s));
+  h->arena_staged = nullptr;
   CK(cudaMemcpyAsync(h->d_offsets.p, offsets, (size_t)(n_packets + 1) * 4, cudaMemcpyHostToDevice, s));
   CK(cudaMemcpyAsync(h->d_lane_stream.p, h->h_lane_stream.data(), (size_t)n_lanes * 4, cudaMemcpyHostToDevice, s));
   const uint8_t* d_flags = nullptr;
@@ -1567,6 +1569,15 @@ static int decode_host(bd_handle* h, const uint8_t* arena, const uint32_t* offse
   if (!h || !arena || !offsets || !stream_ids || !samples_out || !final_range_out || (!pcm_f32 && !pcm_i16)) return BD_ERR_BAD_ARG;
   const auto t_in = std::chrono::steady_clock::now();
   h->after_enqueue = nullptr;
+  // The packet bytes start towards the device before the host looks at them: the copy runs beside the walk and the schedule below
+  // (a call that turns out to need cutting into frames sends its re-cut arena instead; the early copy is then simply overwritten).
+  h->arena_staged = nullptr;
+  if (n_packets && offsets[n_packets] >= (1u << 20)) {
+    CK(cudaSetDevice(h->device));
+    CK(h->d_arena.ensure((size_t)offsets[n_packets] + 16));
+    CK(cudaMemcpyAsync(h->d_arena.p, arena, offsets[n_packets], cudaMemcpyHostToDevice, h->own_stream));
+    h->arena_staged = arena;
+  }
   if (h->track.size() != h->cfg.n_streams) h->track.assign(h->cfg.n_streams, mbh::StreamTrack());
   // One walk over the packets (each TOC byte is a cache miss of its own in a large arena): stream ids in range, does any packet
   // need cutting into frames, and the TOC bytes kept aside for the note below.
