@@ -40,7 +40,9 @@ extern "C" {
 /* Behaviour switches: bit set = mousiki's decoder as written, clear = libopus (DESIGN.md "Quirks").
  * bits 0..6: CELT Q1,Q2,Q5..Q9; bits 8..11: SILK S1 (nlsf_decode.rs:109 16-bit SMULBB), S2 (nlsf2a.rs:42-60 cosine
  * ordering), S3 (code_signs.rs:112-118 sign decode stops at frame_length), S4 (dec_api.rs:150-154 mono->stereo
- * re-initialises both channels). */
+ * re-initialises both channels).
+ * Q2 (bit 1, mdct.rs:373 zero fill) cleared = libopus' overlap-add between blocks: coded CELT-only frames decode, lost packets,
+ * FEC and packets with a SILK part report BD_OPUS_UNIMPLEMENTED per packet. */
 #define BD_QUIRKS_MOUSIKI 0xf7fu
 
 typedef struct bd_handle bd_handle;

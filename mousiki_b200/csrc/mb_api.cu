@@ -866,7 +866,7 @@ struct bd_handle {
     timeline.push_back({std::string(what) + " " + std::to_string(k), e});
   }
   struct PassOut { bool on = false; char* host_pcm = nullptr; const char* dev_pcm = nullptr; size_t elem = 0; } pass_out;
-  DevBuf states, silk_states, silk_hist, silk_exc, fold, hist, rec, en, meta, series, xbuf, order, side_of, aux_count, aux_main, clip_need;
+  DevBuf states, silk_states, silk_hist, silk_exc, fold, hist, rec, en, meta, series, xbuf, order, side_of, aux_count, aux_main, clip_need, tails;
   // staging for the host-buffer entry points
   DevBuf d_arena, d_offsets, d_pkt_map, d_out_map, d_lane_stream, d_flags, d_pcm, d_pcm16, d_samples, d_range, d_ids, d_dbg_iy, d_dbg_x;
   std::vector<uint32_t> h_pkt_map, h_lane_stream, h_lane_of_stream, h_epoch, h_count, h_tick, v_range;
@@ -919,7 +919,6 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
   const int fs = cfg->sample_rate_hz;
   if (!(fs == 48000 || fs == 24000 || fs == 16000 || fs == 12000 || fs == 8000)) return BD_ERR_BAD_ARG;
   if (fs != 48000) return BD_ERR_UNIMPLEMENTED;                                   // row F4
-  if ((cfg->quirks & Q2_MDCT_ZERO_FILL) == 0) return BD_ERR_UNIMPLEMENTED;        // libopus overlap-add variant not built
   if (cfg->n_streams == 0) return BD_ERR_BAD_ARG;
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) return BD_ERR_CUDA;
@@ -999,7 +998,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
 void bd_destroy(bd_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  DevBuf* all[] = {&h->order, &h->side_of, &h->aux_count, &h->aux_main, &h->clip_need, &h->states, &h->silk_states, &h->silk_hist, &h->silk_exc, &h->fold, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map, &h->d_out_map,
+  DevBuf* all[] = {&h->order, &h->side_of, &h->aux_count, &h->aux_main, &h->clip_need, &h->tails, &h->states, &h->silk_states, &h->silk_hist, &h->silk_exc, &h->fold, &h->hist, &h->rec, &h->en, &h->meta, &h->series, &h->xbuf, &h->d_arena, &h->d_offsets, &h->d_pkt_map, &h->d_out_map,
                    &h->d_lane_stream, &h->d_flags, &h->d_pcm, &h->d_pcm16, &h->d_samples, &h->d_range, &h->d_ids, &h->d_dbg_iy, &h->d_dbg_x};
   for (DevBuf* b : all) b->release();
   for (auto& sp : h->prof_spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -1177,6 +1176,8 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
   CK(h->aux_count.ensure(sizeof(uint32_t)));
   CK(h->aux_main.ensure((size_t)aux_cap * sizeof(uint32_t)));
   if (d_pcm_i16) CK(h->clip_need.ensure((size_t)2 * cells_max * sizeof(uint32_t)));
+  const bool ola = !(h->cfg.quirks & Q2_MDCT_ZERO_FILL);   // overlap-add form of the inverse MDCT (mb_celt_imdct.cuh)
+  if (ola) CK(h->tails.ensure((size_t)cells_all * CC * TAIL_STRIDE * sizeof(float)));
   float* pcm_f32 = d_pcm_f32;
   if (d_pcm_i16) {  // the i16 path decodes to a float scratch, soft-clips, then rounds (src/opus_decoder.rs:1679-1712)
     CK(h->d_pcm.ensure((size_t)n_packets * pcm_stride * sizeof(float)));
@@ -1282,6 +1283,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     ImdctParams ip;
     ip.rec = h->rec.as<uint32_t>(); ip.meta = meta_p; ip.xbuf = h->xbuf.as<float>(); ip.series = h->series.as<float>();
     ip.series_stride = series_stride; ip.CC = CC;
+    if (ola) { ip.ola = 1; ip.tails = h->tails.as<float>(); }
     h->prof_begin(BD_K_IMDCT, s);
     {
       const uint32_t want = (cells_run * CC + IMDCT_WARPS - 1) / IMDCT_WARPS, resident = (uint32_t)(h->n_sm * IMDCT_CTAS_PER_SM);
@@ -1295,6 +1297,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     tp.apply_gain = h->cfg.gain_q8 != 0; tp.pcm_f32 = pcm; tp.pcm_stride = pcm_stride; tp.out_map = d_out_map; tp.xbuf = h->xbuf.as<float>();
     tp.order = order_p; tp.order_n = order_n_p; tp.side_of = h->side_of.as<uint32_t>();
     tp.aux_main = h->aux_main.as<uint32_t>(); tp.aux_base = cells_max;
+    if (ola) { tp.ola = 1; tp.tails = h->tails.as<float>(); }
     uint32_t* clip_need_p = nullptr;
     if (d_pcm_i16 && h->fused_i16) {   // (double-buffered like the frame meta: the clipper of pass pi reads it beside pass pi + 1; s is behind ev_clip_done via join 1)
       clip_need_p = h->clip_need.as<uint32_t>() + (pi & 1) * (size_t)cells_max;

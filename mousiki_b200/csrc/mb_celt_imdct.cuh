@@ -130,7 +130,14 @@ struct ImdctParams {
   float* series;            // [lane][CC][series_stride]
   uint32_t series_stride;
   int CC;
+  // Overlap-add form (quirk Q2 cleared: clt_mdct_backward as libopus has it, without the reference's zero fill, mdct.rs:373):
+  // a block's first 60 samples take in the 60 unwindowed samples the block before it left behind. Between the short blocks of
+  // a frame that happens here; across frames the stream's post-filter pass (serial in time, celt_comb_channel) adds the term
+  // from the tail every unit stores in `tails` ([cell][CC][TAIL_STRIDE]) and clamps the frame's first 120 samples.
+  float* tails = nullptr;
+  int ola = 0;
 };
+enum { TAIL_STRIDE = 64 };
 
 // The transform itself, in place on sm->io: N = 120 << lm frequency bins in (short blocks interleaved as the band pass
 // leaves them), N time-domain samples out (clt_mdct_backward against the reference's zero-filled overlap).
@@ -266,7 +273,7 @@ MB_DEV int bitrev_low(int r, int bits) {
 // SH / NB >= 0 fix the transform size (480 >> SH points) and the number of blocks at compile time (addresses become
 // immediates); -1 reads them from (lm, transient).
 template <int SH, int NB>
-MB_DEV void celt_imdct_core_t(Team tm, float* io, const ImdctTables* T, int lm, int transient) {
+MB_DEV void celt_imdct_core_t(Team tm, float* io, const ImdctTables* T, int lm, int transient, int ola) {
   const int M = 1 << lm;
   const int nbk = NB > 0 ? NB : (transient ? M : 1);
   const int shift = SH >= 0 ? SH : (transient ? MAX_LM : MAX_LM - lm);
@@ -387,24 +394,26 @@ MB_DEV void celt_imdct_core_t(Team tm, float* io, const ImdctTables* T, int lm, 
     }
   }
   MB_SYNC();
-  // window fold of each block's first 60 samples against the zero-filled overlap
+  // window fold of each block's first 60 samples against the zero-filled overlap — or, in the overlap-add form, against the
+  // 60 unwindowed samples the block before it wrote there (the frame's first block meets the previous frame's later)
   for (int b = 0; b < nbk; b++) {
     float* ob = io + b * n2;
     for (int k = tm.tid; k < 60; k += tm.n) {
       const float val = ob[60 + k];
+      const float x2 = (ola && b > 0) ? ob[59 - k] : 0.f;
       const float w1 = T->window[59 - k], w2 = T->window[60 + k];
-      ob[59 - k] = 0.f * w2 - val * w1;     // out[i] = x2*w2 - x1*w1 with x2 = 0
-      ob[60 + k] = 0.f * w1 + val * w2;     // out[119-i] = x2*w1 + x1*w2
+      ob[59 - k] = x2 * w2 - val * w1;     // out[i] = x2*w2 - x1*w1
+      ob[60 + k] = x2 * w1 + val * w2;     // out[119-i] = x2*w1 + x1*w2
     }
   }
   MB_SYNC();
 }
 
 // The two shapes nearly every 20 ms frame takes get their own instantiation; the rest share the generic one.
-MB_DEV void celt_imdct_core_w(Team tm, float* io, const ImdctTables* T, int lm, int transient) {
-  if (lm == 3 && !transient) celt_imdct_core_t<0, 1>(tm, io, T, lm, transient);
-  else if (lm == 3) celt_imdct_core_t<3, 8>(tm, io, T, lm, transient);
-  else celt_imdct_core_t<-1, 0>(tm, io, T, lm, transient);
+MB_DEV void celt_imdct_core_w(Team tm, float* io, const ImdctTables* T, int lm, int transient, int ola = 0) {
+  if (lm == 3 && !transient) celt_imdct_core_t<0, 1>(tm, io, T, lm, transient, ola);
+  else if (lm == 3) celt_imdct_core_t<3, 8>(tm, io, T, lm, transient, ola);
+  else celt_imdct_core_t<-1, 0>(tm, io, T, lm, transient, ola);
 }
 
 #if !MB_ON_DEVICE
@@ -469,7 +478,7 @@ MB_DEV void celt_imdct_unit(Team tm, ImdctSmem* sm, uint32_t f, int u, const Imd
 struct ImdctUnit {
   const float* src;      // first spectrum row of the unit in xbuf (nullptr: nothing to do)
   float* out;            // (meta.lane, channel 0) row position in the time series
-  uint32_t flags;
+  uint32_t flags, cell;
   int N, lm, transient, lo, hi, downmix, nch, u;
 };
 MB_DEV ImdctUnit imdct_unit_plan(uint32_t f, int u, const ImdctParams& P) {
@@ -482,7 +491,7 @@ MB_DEV ImdctUnit imdct_unit_plan(uint32_t f, int u, const ImdctParams& P) {
   const int lm = (int)MB_H0_LM(h0), C = (int)MB_H0_C(h0), start = (int)MB_H0_START(h0), end = (int)MB_ST_END(status);
   const int silence = (int)MB_H0_SILENCE(h0);
   const int M = 1 << lm, CC = P.CC;
-  U.lm = lm; U.transient = (int)MB_H0_TRANSIENT(h0); U.N = M * SHORT_MDCT; U.u = u; U.flags = meta.flags;
+  U.lm = lm; U.transient = (int)MB_H0_TRANSIENT(h0); U.N = M * SHORT_MDCT; U.u = u; U.flags = meta.flags; U.cell = f;
   U.nch = (CC == 2 && C == 2) ? 2 : 1;
   if (u >= U.nch) return U;
   const int planned = r[S_PLAN * 32] != 0xffffffffu;
@@ -501,11 +510,22 @@ MB_DEV void imdct_unit_run(Team tm, float* io, const ImdctTables* T, const Imdct
   for (int i = tm.tid; i < U.lo; i += tm.n) io[i] = 0.f;
   for (int i = (U.hi < U.lo ? U.lo : U.hi) + tm.tid; i < N; i += tm.n) io[i] = 0.f;
   MB_SYNC();
-  celt_imdct_core_w(tm, io, T, U.lm, U.transient);
+  celt_imdct_core_w(tm, io, T, U.lm, U.transient, P.ola);
   const float SIG_SAT = 536870911.0f;
   for (int cc = 0; cc < CC; cc++) {
     if (U.nch == 2 && cc != U.u) continue;
     float* out = U.out + (size_t)cc * P.series_stride;
+    if (P.ola) {
+      // overlap-add form: the frame's first 120 samples still miss the previous frame's term — they leave unclamped, the
+      // post-filter pass finishes them; the 60 samples behind the frame go to the tail store for the frame that follows
+      float* tl = P.tails + ((size_t)U.cell * CC + cc) * TAIL_STRIDE;
+      for (int i = tm.tid; i < OVERLAP / 2; i += tm.n) tl[i] = io[N + i];
+      for (int i = tm.tid; i < N; i += tm.n) {
+        float o = io[i];
+        out[i] = i < OVERLAP ? o : (o < -SIG_SAT ? -SIG_SAT : (o > SIG_SAT ? SIG_SAT : o));
+      }
+      continue;
+    }
     if ((((uintptr_t)out) & 15u) == 0) {
       for (int i4 = tm.tid; i4 < N / 4; i4 += tm.n) {
         float4v a = ld_f4(io + 4 * i4);

@@ -44,6 +44,9 @@ struct TailParams {
   // clipper still has work there (0: not judged, 1: int16 stored and no sample beyond +-1, 2: go through k_clip_i16)
   int16_t* pcm_i16 = nullptr;
   uint32_t* clip_need = nullptr;
+  // overlap-add form of the inverse MDCT (quirk Q2 cleared, mb_celt_imdct.cuh): the tails the units stored, [cell][CC][64]
+  const float* tails = nullptr;
+  int ola = 0;
 };
 // the cell whose packet row a frame of cell f is written to
 MB_DEV uint32_t row_cell(const TailParams& P, uint32_t f) { return f >= P.n_lanes * P.n_ticks ? P.aux_main[f - P.aux_base] : f; }
@@ -119,6 +122,10 @@ MB_DEV void celt_comb_channel(Team tm, CombSmem* sm, uint32_t lane, int c, const
   int pf_period = pf.period, pf_period_old = pf.period_old, pf_tapset = pf.tapset, pf_tapset_old = pf.tapset_old;
   float pf_gain = pf.gain, pf_gain_old = pf.gain_old;
   int total = 0, reset_at = -1;   // samples of CELT signal this pass; where the last decoder reset fell
+  // overlap-add form: the 60 unwindowed samples the previous frame's inverse MDCT left behind it — the persisted overlap region
+  // for the first frame of the pass, nothing after a decoder reset, else the previous unit's entry in the tail store
+  const float* prev_tail = hist + HIST_G - OVERLAP;
+  bool tail_zero = false;
   MB_SYNC();
   const uint32_t n_frames = P.order_n[lane];
   for (uint32_t k = 0; k < n_frames; k++) {
@@ -131,12 +138,28 @@ MB_DEV void celt_comb_channel(Team tm, CombSmem* sm, uint32_t lane, int c, const
       for (int i = tm.tid; i < HIST; i += tm.n) buf[i] = 0.f;
       pf_period = pf_period_old = 0; pf_tapset = pf_tapset_old = 0; pf_gain = pf_gain_old = 0.f;
       reset_at = (int)m.sample_off;
+      tail_zero = true;
       MB_SYNC();
     }
     float* xg = ser + m.sample_off;
     float* x = buf + HIST;
     for (int i = tm.tid; i < N; i += tm.n) x[i] = xg[i];
     MB_SYNC();
+    if (P.ola) {
+      // out[i] = x2*w2 - x1*w1, out[119-i] = x2*w1 + x1*w2 (clt_mdct_backward, mdct.rs:376-388): the unit left -x1*w1 and x1*w2
+      // (x2 = 0); adding the x2 products gives the same two roundings. Then the clamp the unit held back for these samples.
+      const float SIG_SAT = 536870911.0f;
+      for (int i = tm.tid; i < OVERLAP / 2; i += tm.n) {
+        const float t = tail_zero ? 0.f : prev_tail[i];
+        const float w1 = bits2f(kWindow120Bits[i]), w2 = bits2f(kWindow120Bits[OVERLAP - 1 - i]);
+        const float a = t * w2 + x[i], b = t * w1 + x[OVERLAP - 1 - i];
+        x[i] = a < -SIG_SAT ? -SIG_SAT : (a > SIG_SAT ? SIG_SAT : a);
+        x[OVERLAP - 1 - i] = b < -SIG_SAT ? -SIG_SAT : (b > SIG_SAT ? SIG_SAT : b);
+      }
+      prev_tail = P.tails + ((size_t)f * CC + c) * 64;
+      tail_zero = false;
+      MB_SYNC();
+    }
     if (!(m.flags & MB_FL_PLC)) {   // (a concealed frame is neither post-filtered nor does it move the filter's parameters)
       const int new_pitch = (int)MB_H1_PITCH(h1), new_tapset = (int)MB_H0_TAPSET(h0);
       const float new_gain = 0.09375f * (float)MB_H0_QG1(h0);
@@ -144,7 +167,7 @@ MB_DEV void celt_comb_channel(Team tm, CombSmem* sm, uint32_t lane, int c, const
       pf_period_old = imax(pf_period_old, COMB_MINPERIOD);
       const int first = imin(SHORT_MDCT, N);
       const int second = (lm != 0 && first < N) ? N - first : 0;
-      const int touched = (pf_gain_old != 0.f || pf_gain != 0.f) || (second && (pf_gain != 0.f || new_gain != 0.f));
+      const int touched = P.ola || (pf_gain_old != 0.f || pf_gain != 0.f) || (second && (pf_gain != 0.f || new_gain != 0.f));
       team_comb_filter(tm, x, first, pf_period_old, pf_period, pf_gain_old, pf_gain, imax(pf_tapset_old, 0), imax(pf_tapset, 0));
       if (second)
         team_comb_filter(tm, x + first, second, pf_period, new_pitch, pf_gain, new_gain, imax(pf_tapset, 0), imax(new_tapset, 0));
@@ -174,7 +197,8 @@ MB_DEV void celt_comb_channel(Team tm, CombSmem* sm, uint32_t lane, int c, const
       float v = 0.f;
       if (i < HIST_G) {
         const int s = total - (HIST_G - OVERLAP) + i;
-        if (s >= 0) v = s < reset_at ? 0.f : ser[s];
+        if (P.ola && s >= total) v = s - total < OVERLAP / 2 ? prev_tail[s - total] : 0.f;   // (the last unit's tail; zeros behind it)
+        else if (s >= 0) v = s < reset_at ? 0.f : ser[s];
         else v = reset_at >= 0 ? 0.f : hist[i + total];
       }
       MB_SYNC();

@@ -32,6 +32,10 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
   if (len == 0 && !flags) { rec_base[S_STATUS * 32] = 1u << 15; return; }
   int code = MB_OK;
   const uint8_t* data = arena + off;
+  // The overlap-add form of the inverse MDCT (quirk Q2 cleared) is built for coded CELT-only frames: concealment, in-band FEC and
+  // packets with a SILK part are refused per packet there.
+  const bool ola = !(quirks & Q2_MDCT_ZERO_FILL);
+  if (ola && ((flags && (flags[pkt] & 3u)) || len == 0)) { rec_base[S_STATUS * 32] = (uint32_t)(uint8_t)(int8_t)MB_UNIMPLEMENTED; return; }
   if ((flags && (flags[pkt] & 2u)) || len == 0) {
     // lost packet (or one concealment frame of it, cut by the host): no payload. The two bytes the host put in its place
     // say how many samples to conceal (mb_host_packets.h); the stream pass decides how (k_energy).
@@ -53,6 +57,7 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
   if (code == MB_OK) {
     toc = data[0];
     if (toc & 3u) code = MB_UNIMPLEMENTED;              // multi-frame packets (row F1)
+    else if (ola && (!(toc & 0x80u) || len - 1 <= 1)) code = MB_UNIMPLEMENTED;
     else if (len - 1 > 1275) code = MB_INVALID_PACKET;  // src/packet.rs:465: a frame is at most 1275 bytes
     else if (!(toc & 0x80u)) {
       if (len - 1 <= 1) {                                    // a frame of at most one byte is a concealed frame (src/opus_decoder.rs:491-496)

@@ -153,6 +153,9 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   float* ism = new float[IMDCT_ROW];   // the warp-resident form k_imdct runs, its 32 lanes walked phase by phase
   ImdctParams ip; ip.rec = rec.data(); ip.meta = meta.data(); ip.xbuf = xbuf.data(); ip.series = series.data();
   ip.series_stride = series_stride; ip.CC = CC;
+  const bool ola = !(quirks & Q2_MDCT_ZERO_FILL);   // overlap-add form of the inverse MDCT (quirk Q2 cleared)
+  std::vector<float> tails(ola ? (size_t)FA * CC * TAIL_STRIDE : 0, 0.f);
+  if (ola) { ip.ola = 1; ip.tails = tails.data(); }
   for (uint32_t f = 0; f < FA; f++)
     for (int u = 0; u < CC; u++) celt_imdct_unit_w(tm, ism, imdct_tables_host(), f, u, ip);
   delete[] ism;
@@ -166,6 +169,7 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   tp.gain = g_gain_q8 == 0 ? 1.f : (float)exp(0.6931471805599453094 * (double)((3.32192809488736234787f / 5120.0f) * (float)g_gain_q8));
   tp.apply_gain = g_gain_q8 != 0; tp.pcm_f32 = out; tp.pcm_stride = pcm_stride; tp.xbuf = xbuf.data();
   tp.order = order.data(); tp.order_n = order_n.data(); tp.side_of = side_of.data(); tp.aux_main = aux_main.data(); tp.aux_base = F;
+  if (ola) { tp.ola = 1; tp.tails = tails.data(); }
   // SILK-side cells (k_silk): lane per stream, ticks in order
   {
     std::vector<SilkState> sst(n_lanes);
