@@ -841,6 +841,9 @@ struct bd_handle {
   float gain = 1.f;
   uint32_t max_frames_per_pass = 0;
   bool want_i24 = false;       // the running host call delivers 24-bit integers (bd_decode_i24)
+  std::vector<uint32_t> sched_ids;          // stream ids of the call the kept schedule (h_lane_stream, h_pkt_map) belongs to
+  uint32_t sched_n = 0, sched_lanes = 0, sched_ticks = 0;
+  bool sched_identity = false;
   const uint8_t* arena_staged = nullptr;    // the host arena whose bytes are already on their way to d_arena (decode_host)
   std::vector<uint8_t> h_toc;               // TOC byte of every packet of the call in flight
   std::function<void()> after_enqueue;      // host work of the call that runs beside the device work
@@ -1158,7 +1161,12 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
   if (ticks_per_pass > n_ticks) ticks_per_pass = n_ticks;
   // PCM going back to the host pass by pass: at least four passes, so that the first copy starts early (the copy stream,
   // not the kernels, ends the call; measured on the headline workload: 71.4 -> 69.1 ms)
-  if (h->pass_out.on && !d_out_map && n_ticks >= 16 && ticks_per_pass > (n_ticks + 3) / 4) ticks_per_pass = (n_ticks + 3) / 4;
+  {
+    const char* mp = getenv("MOUSIKI_B200_MIN_PASSES");   // (tuning switch)
+    const uint32_t min_passes = mp && atoi(mp) > 0 ? (uint32_t)atoi(mp) : 4u;
+    if (h->pass_out.on && !d_out_map && n_ticks >= 16 && ticks_per_pass > (n_ticks + min_passes - 1) / min_passes)
+      ticks_per_pass = (n_ticks + min_passes - 1) / min_passes;
+  }
   const uint32_t cells_max = ticks_per_pass * n_lanes;
   // auxiliary cells (second CELT frame of a packet, mb_common.cuh): a pool per pass behind the main cells; a packet that
   // finds it empty is reported as unimplemented
@@ -1277,7 +1285,8 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     bp.x_dbg = d_dbg_x ? d_dbg_x + cell0 * 2 * MAX_N : nullptr;
     bp.fold_all = h->fold.as<float>(); bp.lane_stream = d_lane_stream;
     h->prof_begin(BD_K_BANDS, s);
-    k_bands<<<(cells_run + BANDS_WARPS - 1) / BANDS_WARPS, 32 * BANDS_WARPS, 0, s>>>(bp, cells_run, cells, cells_max);
+    if (!eq.serial_all)   // (with the per-stream pass taking every frame, the all-at-once pass would only look at flags and leave)
+      k_bands<<<(cells_run + BANDS_WARPS - 1) / BANDS_WARPS, 32 * BANDS_WARPS, 0, s>>>(bp, cells_run, cells, cells_max);
     k_bands_hyb<<<(n_lanes + BANDS_WARPS - 1) / BANDS_WARPS, 32 * BANDS_WARPS, 0, s>>>(bp, n_lanes, order_p, order_n_p, d_lane_stream, h->fold.as<float>());
     h->prof_end(s);
     ImdctParams ip;
@@ -1322,7 +1331,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     }
     h->prof_end(s);
     k_fade<<<(cells * CC + 127) / 128, 128, 0, s>>>(tp, cells);
-    h->launches += 10;   // parse, energy, pvq, plan, bands, bands_hyb, imdct, comb, deemph, fade
+    h->launches += eq.serial_all ? 9 : 10;   // parse, energy, pvq, plan, (bands,) bands_hyb, imdct, comb, deemph, fade
     h->mark("kernels", pi, s);
     // ship this pass's PCM (cells [cell0 + c0, cell0 + c0 + nc)) on the copy stream while later kernels compute
     auto next_event = [&](cudaEvent_t* out) -> int {
@@ -1413,6 +1422,15 @@ static int decode_host_impl(bd_handle* h, const uint8_t* arena, const uint32_t* 
   cudaStream_t s = h->own_stream;
   const uint32_t S = h->cfg.n_streams;
   // ---- schedule: lane = order of first appearance of a stream in this call, tick = occurrence number
+  // (a serving loop sends the same stream-id pattern call after call: the schedule of the previous call is kept and reused when
+  //  the ids compare equal — one pass over them instead of three with scattered accesses)
+  const bool sched_hit = !out_map && h->sched_n == n_packets && h->sched_ids.size() == n_packets &&
+                         memcmp(h->sched_ids.data(), stream_ids, (size_t)n_packets * 4) == 0;
+  uint32_t n_lanes = 0, n_ticks = 0;
+  bool identity = false;
+  if (sched_hit) { n_lanes = h->sched_lanes; n_ticks = h->sched_ticks; identity = h->sched_identity; }
+  else {
+  h->sched_n = 0;
   if (h->h_epoch.size() != S) { h->h_epoch.assign(S, 0); h->h_lane_of_stream.assign(S, 0); h->h_count.assign(S, 0); h->epoch = 0; }
   h->epoch++;
   if (h->epoch == 0) { std::fill(h->h_epoch.begin(), h->h_epoch.end(), 0u); h->epoch = 1; }
@@ -1426,13 +1444,12 @@ static int decode_host_impl(bd_handle* h, const uint8_t* arena, const uint32_t* 
       h->h_lane_stream.push_back(sid);
     }
   }
-  const uint32_t n_lanes = (uint32_t)h->h_lane_stream.size();
+  n_lanes = (uint32_t)h->h_lane_stream.size();
   // tick = occurrence number of the stream in this call. The frames of one multi-frame packet must not straddle a
   // pass boundary (k_clip_i16 soft-clips the packet as a whole): the group moves to the next pass, leaving empty cells.
   uint32_t tpp = h->max_frames_per_pass / n_lanes;
   if (tpp == 0) tpp = 1;
   h->h_tick.resize(n_packets);
-  uint32_t n_ticks = 0;
   for (uint32_t p = 0; p < n_packets; p++) {
     const uint32_t sid = stream_ids[p];
     uint32_t cur = h->h_count[sid];
@@ -1446,8 +1463,7 @@ static int decode_host_impl(bd_handle* h, const uint8_t* arena, const uint32_t* 
     h->h_count[sid] = cur + 1;
     if (cur + 1 > n_ticks) n_ticks = cur + 1;
   }
-  bool identity = n_ticks == 1 && !out_map;  // every stream at most once: cell == packet
-  const uint32_t* d_map = nullptr;
+  identity = n_ticks == 1 && !out_map;  // every stream at most once: cell == packet
   if (!identity) {
     h->h_pkt_map.assign((size_t)n_lanes * n_ticks, 0xffffffffu);
     bool grid_order = (size_t)n_packets == (size_t)n_lanes * n_ticks && !out_map;
@@ -1458,6 +1474,12 @@ static int decode_host_impl(bd_handle* h, const uint8_t* arena, const uint32_t* 
     }
     identity = grid_order;  // packets already arrive tick-major in lane order: no indirection needed
   }
+  if (!out_map) {
+    h->sched_ids.assign(stream_ids, stream_ids + n_packets);
+    h->sched_n = n_packets; h->sched_lanes = n_lanes; h->sched_ticks = n_ticks; h->sched_identity = identity;
+  }
+  }
+  const uint32_t* d_map = nullptr;
   if (!identity) {
     CK(h->d_pkt_map.ensure(h->h_pkt_map.size() * 4));
     CK(cudaMemcpyAsync(h->d_pkt_map.p, h->h_pkt_map.data(), h->h_pkt_map.size() * 4, cudaMemcpyHostToDevice, s));

@@ -134,9 +134,9 @@ def read_ogg_opus(data: bytes, by_segment: bool = False):
         if page.serial != first.serial:
             continue                      # another logical stream multiplexed in: not ours
         segs = list(page.segments())
-        if segs and segs[0].startswith(b"OpusTags") and not partial:
-            continue                      # the comment header page (examples/decode.rs:75-79)
         if by_segment:
+            if segs and segs[0].startswith(b"OpusTags"):
+                continue                  # the comment header page (examples/decode.rs:75-79)
             packets.extend(s for s in segs if s)
             continue
         for n, s in zip(page.lacing, segs):
@@ -145,6 +145,10 @@ def read_ogg_opus(data: bytes, by_segment: bool = False):
                 if partial:
                     packets.append(partial)
                 partial = b""
+    # The comment header is the stream's second logical packet and may span several pages (embedded cover art): it is dropped as
+    # a whole packet, after re-assembly — its continuation pages must not turn into the first audio packet.
+    if not by_segment and packets and packets[0].startswith(b"OpusTags"):
+        packets.pop(0)
     return head, packets
 
 

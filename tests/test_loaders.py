@@ -159,3 +159,16 @@ def test_gpu_loaded_streams_decode_like_the_oracle():
     with BatchDecoder(3, 48000, 2) as dec:
         pg, sg, rg = dec.decode(arena, offsets, sid, 960)
     assert np.array_equal(so, sg) and np.array_equal(ro, rg) and np.array_equal(po, pg)
+
+
+def test_comment_header_spanning_several_pages_is_dropped_as_one_packet():
+    """An OpusTags packet with embedded cover art spans pages: its continuation pages must not come back as the
+    first audio packet. 255 * 255 + 70 bytes: one full page of 255-byte segments, then the rest on a continuation page."""
+    tags = b"OpusTags" + bytes(helpers.lcg_bytes(8, 255 * 255 + 70 - 8))
+    segs = [tags[i:i + 255] for i in range(0, len(tags), 255)]
+    assert len(segs) == 256 and len(segs[-1]) == 70
+    audio = [bytes(helpers.lcg_bytes(9, 90)), bytes(helpers.lcg_bytes(10, 33))]
+    data = (_page([_head()], header_type=2) + _page(segs[:255], seq=1) + _page(segs[255:], seq=2, header_type=1)
+            + _page(audio, seq=3, header_type=4))
+    head, packets = loaders.read_ogg_opus(data)
+    assert head.channels == 2 and packets == audio
