@@ -447,10 +447,16 @@ def run_gpu(args):
     if strong:
         gold = ROOT / "tests" / "golden" / "strong_scaling_checksums.json"
         if gold.exists():
-            want = json.loads(gold.read_text()).get(f"{total_streams}x{ticks}x{args.warmup + args.steps}")
+            table = json.loads(gold.read_text())
+            want = table.get(f"{total_streams}x{ticks}x{args.warmup + args.steps}")
+            if not want:   # another number of decodes of the corpus: a CELT-only packet's final_range does not depend on the stream's
+                           # state, so any entry of the same corpus pins it (the PCM hash does depend on it and is left out)
+                same = [v for k, v in table.items() if k.startswith(f"{total_streams}x{ticks}x")]
+                want = {"final_range_sha256": same[0]["final_range_sha256"]} if same else None
             if want:
                 checks["final_range_matches_golden"] = want["final_range_sha256"] == fr_hash
-                checks["pcm_matches_1gpu_run"] = want.get("pcm_bits_sha256") == pcm_hash
+                if "pcm_bits_sha256" in want:
+                    checks["pcm_matches_1gpu_run"] = want["pcm_bits_sha256"] == pcm_hash
                 assert checks["final_range_matches_golden"], "per-stream final_range checksums differ from the committed 1-GPU / oracle vector"
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
