@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
           need_cell = fo;
           // anything but a coded CELT-only frame alone in its row (SILK part, side / fade rows, concealment) keeps the clipper's route
           const uint32_t other = 2u | 8u | 16u | 32u | 64u | 128u | MB_FL_FADE_ROW | MB_FL_PLC | MB_FL_PLC_PITCH;
-          if (f < n_main && !(m.flags & other) && ((((uintptr_t)(P.pcm_i16 + eo)) & 7u) == 0) && ((((uintptr_t)out) & 15u) == 0))
+          if (P.ds == 1 && f < n_main && !(m.flags & other) && ((((uintptr_t)(P.pcm_i16 + eo)) & 7u) == 0) && ((((uintptr_t)out) & 15u) == 0))
             out16 = P.pcm_i16 + eo;
         }
       }
@@ -360,7 +360,19 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
         }
       }
       __syncwarp();
-      if (CC == 2) {
+      if (P.ds > 1) {
+        // output rates below 48 kHz: every ds-th filtered sample is kept (deemphasis with downsample, celt_decoder.rs:2232-2297)
+        const int ds = P.ds;
+        for (int r = 0; r < 32; r++) {
+          float* o = row_out[r];
+          const int cnt = min(CH, row_n[r] - k0);
+          if (!o || cnt <= 0) continue;
+          const float* tx = tile + r * PITCH;
+          const int cr = CC == 2 ? (r & 1) : 0;     // (idx0 is a multiple of 32: row r is channel r % CC of its stream)
+          for (int j = l; j < cnt; j += 32)
+            if ((k0 + j) % ds == 0) o[(size_t)((k0 + j) / ds) * CC + cr] = tx[j];
+        }
+      } else if (CC == 2) {
 #pragma unroll 2
         for (int r = 0; r < 32; r += 2) {
           float* o = row_out[r];
@@ -847,6 +859,7 @@ struct bd_handle {
   const uint8_t* arena_staged = nullptr;    // the host arena whose bytes are already on their way to d_arena (decode_host)
   std::vector<uint8_t> h_toc;               // TOC byte of every packet of the call in flight
   std::function<void()> after_enqueue;      // host work of the call that runs beside the device work
+  int ds = 1;                  // 48000 / sample_rate_hz
   bool clip_serial = false;    // MOUSIKI_B200_CLIP_SERIAL=1: the clipper walks the regions of a row one after the other (A/B and test switch)
   bool fused_i16 = true;       // MOUSIKI_B200_FUSED_I16=0: k_deemph leaves every int16 sample to k_clip_i16 (A/B switch)
   bool parallel_bands = false; // MOUSIKI_B200_PARALLEL_BANDS=1: small calls run CELT-only frames through the all-at-once band pass (see k_energy)
@@ -921,13 +934,15 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
   if (cfg->channels != 1 && cfg->channels != 2) return BD_ERR_BAD_ARG;
   const int fs = cfg->sample_rate_hz;
   if (!(fs == 48000 || fs == 24000 || fs == 16000 || fs == 12000 || fs == 8000)) return BD_ERR_BAD_ARG;
-  if (fs != 48000) return BD_ERR_UNIMPLEMENTED;                                   // row F4
+  // (row F4: below 48 kHz coded CELT-only frames decode — CELT's own down-sampling; the rest is refused per packet, mb_frame.cuh)
   if (cfg->n_streams == 0) return BD_ERR_BAD_ARG;
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) return BD_ERR_CUDA;
   bd_handle* h = new (std::nothrow) bd_handle();
   if (!h) return BD_ERR_ALLOC;
   h->cfg = *cfg;
+  h->ds = 48000 / fs;
+  h->cfg.quirks = (cfg->quirks & 0x00ffffffu) | (h->ds > 1 ? (uint32_t)h->ds << QX_DS_SHIFT : 0u);   // (mb_common.cuh: the kernels' copy carries the factor)
   h->device = cfg->device;
   h->CC = cfg->channels;
   h->disable_inv = cfg->disable_phase_inversion < 0 ? (cfg->channels == 1) : (cfg->disable_phase_inversion != 0);
@@ -1155,7 +1170,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
                               cudaStream_t s, int32_t* d_dbg_iy, float* d_dbg_x, const uint32_t* d_out_map = nullptr) {
   if (n_lanes == 0 || n_ticks == 0) return BD_OK;
   const int CC = h->CC;
-  if (pcm_stride < (uint32_t)(SHORT_MDCT * CC)) return BD_ERR_BAD_ARG;
+  if (pcm_stride < (uint32_t)(SHORT_MDCT / h->ds * CC)) return BD_ERR_BAD_ARG;
   if ((uint64_t)n_lanes > h->max_frames_per_pass) return BD_ERR_BAD_ARG;  // caller splits lanes (lanes are independent)
   uint32_t ticks_per_pass = h->max_frames_per_pass / n_lanes;
   if (ticks_per_pass > n_ticks) ticks_per_pass = n_ticks;
@@ -1191,7 +1206,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     CK(h->d_pcm.ensure((size_t)n_packets * pcm_stride * sizeof(float)));
     pcm_f32 = h->d_pcm.as<float>();
   }
-  const int cap_per_ch = (int)(pcm_stride / (uint32_t)CC);
+  const int cap_per_ch = (int)(pcm_stride / (uint32_t)CC) * h->ds;   // the parser compares 48 kHz frame sizes with it
   // The clipper runs in line with the decode kernels: beside them (its own stream, MOUSIKI_B200_CLIP_STREAM=1) its CTAs share the
   // one wave k_parse of the next pass fits in and double that kernel's time (measured: 58.6 vs 54.4 ms of device time per call).
   cudaStream_t clip_s = getenv("MOUSIKI_B200_CLIP_STREAM") ? h->clip_stream : s;
@@ -1293,6 +1308,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     ip.rec = h->rec.as<uint32_t>(); ip.meta = meta_p; ip.xbuf = h->xbuf.as<float>(); ip.series = h->series.as<float>();
     ip.series_stride = series_stride; ip.CC = CC;
     if (ola) { ip.ola = 1; ip.tails = h->tails.as<float>(); }
+    ip.ds = h->ds;
     h->prof_begin(BD_K_IMDCT, s);
     {
       const uint32_t want = (cells_run * CC + IMDCT_WARPS - 1) / IMDCT_WARPS, resident = (uint32_t)(h->n_sm * IMDCT_CTAS_PER_SM);
@@ -1307,6 +1323,7 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     tp.order = order_p; tp.order_n = order_n_p; tp.side_of = h->side_of.as<uint32_t>();
     tp.aux_main = h->aux_main.as<uint32_t>(); tp.aux_base = cells_max;
     if (ola) { tp.ola = 1; tp.tails = h->tails.as<float>(); }
+    tp.ds = h->ds;
     uint32_t* clip_need_p = nullptr;
     if (d_pcm_i16 && h->fused_i16) {   // (double-buffered like the frame meta: the clipper of pass pi reads it beside pass pi + 1; s is behind ev_clip_done via join 1)
       clip_need_p = h->clip_need.as<uint32_t>() + (pi & 1) * (size_t)cells_max;
@@ -1640,7 +1657,7 @@ static int decode_host(bd_handle* h, const uint8_t* arena, const uint32_t* offse
         const uint32_t n = offsets[p + 1] - offsets[p];
         if (n == 0 || (flags && (flags[p] & 3u))) continue;
         const uint8_t toc = h->h_toc[p];
-        if (mbh::toc_frame_samples(toc) > (int)(pcm_stride / (uint32_t)h->CC) || n - 1 > 1275) continue;
+        if (mbh::toc_frame_samples(toc) > (int)(pcm_stride / (uint32_t)h->CC) * h->ds || n - 1 > 1275) continue;
         h->track[stream_ids[p]].frame_size = mbh::toc_frame_samples(toc);
         h->track[stream_ids[p]].mode = (toc & 0x80) ? 1002 : ((toc & 0x60) == 0x60 ? 1001 : 1000);
       }
@@ -1653,7 +1670,10 @@ static int decode_host(bd_handle* h, const uint8_t* arena, const uint32_t* offse
     return rc0;
   }
   mbh::Split& S = h->split;
-  mbh::split_batch(arena, offsets, stream_ids, flags, n_packets, (int)(pcm_stride / (uint32_t)h->CC), h->CC, &S, h->track.data());
+  // (the splitter counts in 48 kHz samples: capacity scaled up, element offsets of the frames scaled back down)
+  mbh::split_batch(arena, offsets, stream_ids, flags, n_packets, (int)(pcm_stride / (uint32_t)h->CC) * h->ds, h->CC, &S, h->track.data());
+  if (h->ds > 1)
+    for (size_t i = 1; i < S.out_map.size(); i += 2) S.out_map[i] /= (uint32_t)h->ds;
   const uint32_t nv = (uint32_t)S.stream_ids.size();
   h->v_samples.resize(nv);
   h->v_range.resize(nv);

@@ -615,8 +615,9 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
       st_prev_mode = (fadeout || red) ? 1000 : (hybrid ? 1001 : 1002);
       st_prev_redundancy = aux == 3;
       st_range_final = fadeout ? silk_rng : (red ? (silk_rng ^ st_rng) : st_rng);
-      st_last_duration = N;
-      if (lead) { samples_out[p] = N; final_range_out[p] = st_range_final; }
+      const int Nout = N / quirk_ds(Q.quirks);   // samples at the decoder's output rate (only coded CELT-only frames get here below 48 kHz)
+      st_last_duration = Nout;
+      if (lead) { samples_out[p] = Nout; final_range_out[p] = st_range_final; }
     }
   }
   MB_SYNC();

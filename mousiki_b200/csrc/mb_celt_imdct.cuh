@@ -136,6 +136,7 @@ struct ImdctParams {
   // from the tail every unit stores in `tails` ([cell][CC][TAIL_STRIDE]) and clamps the frame's first 120 samples.
   float* tails = nullptr;
   int ola = 0;
+  int ds = 1;               // output rate 48000 / ds: bins from N / ds on are cleared (denormalise_bands, bands.rs:4198-4204)
 };
 enum { TAIL_STRIDE = 64 };
 
@@ -497,6 +498,7 @@ MB_DEV ImdctUnit imdct_unit_plan(uint32_t f, int u, const ImdctParams& P) {
   const int planned = r[S_PLAN * 32] != 0xffffffffu;
   U.lo = (silence || !planned) ? 0 : M * eband(start);
   U.hi = (silence || !planned) ? 0 : M * eband(imin(end, NB_EBANDS));
+  if (P.ds > 1) U.hi = imin(U.hi, U.N / P.ds);
   U.downmix = CC == 1 && C == 2;
   U.out = P.series + ((size_t)meta.lane * CC) * P.series_stride + SER_PREFIX + meta.sample_off;
   U.src = P.xbuf + (size_t)f * XBUF_STRIDE + u * U.N;

@@ -47,6 +47,7 @@ struct TailParams {
   // overlap-add form of the inverse MDCT (quirk Q2 cleared, mb_celt_imdct.cuh): the tails the units stored, [cell][CC][64]
   const float* tails = nullptr;
   int ola = 0;
+  int ds = 1;   // output rate 48000 / ds: the de-emphasis filter runs over every sample, every ds-th one is kept (celt_decoder.rs:2232-2297)
 };
 // the cell whose packet row a frame of cell f is written to
 MB_DEV uint32_t row_cell(const TailParams& P, uint32_t f) { return f >= P.n_lanes * P.n_ticks ? P.aux_main[f - P.aux_base] : f; }
@@ -253,6 +254,13 @@ MB_DEV void celt_deemph_lane(uint32_t lane, int c, const TailParams& P) {
     const bool accum = (m.flags & 8u) != 0;
     // the decode gain applies once to the finished row: here, unless the row still waits for a cross-fade (k_fade applies it)
     d.apply_gain = (side || (m.flags & MB_FL_FADE_ROW)) ? 0 : P.apply_gain;
+    if (P.ds > 1) {
+      for (int j = 0; j < N; j++) {
+        const float v = d.step(x[j]);
+        if (out && j % P.ds == 0) out[(size_t)(j / P.ds) * CC] = v;
+      }
+      continue;
+    }
     for (int j = 0; j < N; j++) {
       const float v = d.step(x[j], accum && out ? out[(size_t)j * CC] : 0.f, accum);
       if (out) out[(size_t)j * CC] = v;

@@ -50,6 +50,9 @@ enum {
 enum : uint32_t {
   Q1_DYNALLOC_BUDGET = 1u << 0, Q2_MDCT_ZERO_FILL = 1u << 1, Q5_FOLD_START = 1u << 2, Q6_HYBRID_LOWBAND = 1u << 3,
   Q7_EBITS_BUST = 1u << 4, Q8_COARSE_CLAMP = 1u << 5, Q9_DUAL_STEREO_RSV = 1u << 6, QUIRKS_MOUSIKI = 0x7f,
+  // not a quirk: bits 24-27 of the word the kernels receive carry the decoder's down-sampling factor 48000 / Fs (0 or 1: none),
+  // set by bd_create from bd_config.sample_rate_hz (CELT `downsample`, src/celt/celt_decoder.rs:584-776, 2232-2297)
+  QX_DS_SHIFT = 24,
 };
 
 // ---- Opus error codes (reference src/opus_decoder.rs:275-286)
@@ -94,6 +97,7 @@ MB_DEV uint32_t aux_alloc(const AuxPool& A) {   // cell index, or 0xffffffff whe
 
 // First PCM element of packet p: row p of the caller's buffer, or (calls cut into frames by mb_host_packets.h) row
 // out_map[2p] at element out_map[2p+1].
+MB_DEV int quirk_ds(uint32_t quirks) { const int d = (int)((quirks >> 24) & 15u); return d > 1 ? d : 1; }
 MB_DEV size_t pcm_elem_off(const uint32_t* out_map, uint32_t p, uint32_t stride) {
   return out_map ? (size_t)out_map[2 * p] * stride + out_map[2 * p + 1] : (size_t)p * stride;
 }

@@ -34,7 +34,8 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
   const uint8_t* data = arena + off;
   // The overlap-add form of the inverse MDCT (quirk Q2 cleared) is built for coded CELT-only frames: concealment, in-band FEC and
   // packets with a SILK part are refused per packet there.
-  const bool ola = !(quirks & Q2_MDCT_ZERO_FILL);
+  // So are output rates below 48 kHz (row F4: the CELT down-sampling path is built, the SILK resampler's other ratios are not).
+  const bool ola = !(quirks & Q2_MDCT_ZERO_FILL) || quirk_ds(quirks) > 1;
   if (ola && ((flags && (flags[pkt] & 3u)) || len == 0)) { rec_base[S_STATUS * 32] = (uint32_t)(uint8_t)(int8_t)MB_UNIMPLEMENTED; return; }
   if ((flags && (flags[pkt] & 2u)) || len == 0) {
     // lost packet (or one concealment frame of it, cut by the host): no payload. The two bytes the host put in its place

@@ -60,6 +60,9 @@ void emu_set_gain(int gain_q8) { g_gain_q8 = gain_q8; }
 // null: none), as the host front end hands them to the device
 static const uint8_t* g_flags = nullptr;
 void emu_set_flags(const uint8_t* flags) { g_flags = flags; }
+// decoder output rate 48000 / ds (row F4); pcm_stride and the sample counts are then in output samples, as on the device
+static int g_ds = 1;
+void emu_set_downsample(int ds) { g_ds = ds > 1 ? ds : 1; }
 
 // debug aid for the PVQ work-balance studies (tools/pvq_balance.py): the (N, K) of every leaf of the first `max_frames` cells
 static uint32_t* g_leaf_dump = nullptr;
@@ -72,6 +75,7 @@ uint32_t emu_leaf_count() { return g_leaf_n; }
 int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_t* offsets, uint32_t n_lanes, uint32_t n_ticks,
                     uint32_t pcm_stride, float* pcm, int16_t* pcm16, int32_t* samples_out, uint32_t* final_range_out, int32_t* iy_dbg,
                     float* x_dbg) {
+  quirks = (quirks & 0x00ffffffu) | (g_ds > 1 ? (uint32_t)g_ds << QX_DS_SHIFT : 0u);
   const uint32_t F = n_lanes * n_ticks;
   const uint32_t FA = 2 * F;   // main cells, then as many auxiliary cells (mb_common.cuh)
   const size_t tiles = (FA + 31) / 32;
@@ -91,7 +95,7 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   const int disable_inv = CC == 1;
   // phase 1
   for (uint32_t f = 0; f < F; f++)
-    parse_cell(arena, offsets, f, rec.data() + rec_index(f, 0), CC, quirks, disable_inv, (int)(pcm_stride / CC), g_flags,
+    parse_cell(arena, offsets, f, rec.data() + rec_index(f, 0), CC, quirks, disable_inv, (int)(pcm_stride / CC) * g_ds, g_flags,
                f >= n_lanes ? f - n_lanes : 0xffffffffu, f >= n_lanes ? nullptr : &st[f].prev_mode, rec.data(), aux);
   if (g_leaf_dump)
     for (uint32_t f = 0; f < F; f++) {
@@ -156,6 +160,7 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   const bool ola = !(quirks & Q2_MDCT_ZERO_FILL);   // overlap-add form of the inverse MDCT (quirk Q2 cleared)
   std::vector<float> tails(ola ? (size_t)FA * CC * TAIL_STRIDE : 0, 0.f);
   if (ola) { ip.ola = 1; ip.tails = tails.data(); }
+  ip.ds = g_ds;
   for (uint32_t f = 0; f < FA; f++)
     for (int u = 0; u < CC; u++) celt_imdct_unit_w(tm, ism, imdct_tables_host(), f, u, ip);
   delete[] ism;
@@ -170,6 +175,7 @@ int emu_decode_grid(int CC, uint32_t quirks, const uint8_t* arena, const uint32_
   tp.apply_gain = g_gain_q8 != 0; tp.pcm_f32 = out; tp.pcm_stride = pcm_stride; tp.xbuf = xbuf.data();
   tp.order = order.data(); tp.order_n = order_n.data(); tp.side_of = side_of.data(); tp.aux_main = aux_main.data(); tp.aux_base = F;
   if (ola) { tp.ola = 1; tp.tails = tails.data(); }
+  tp.ds = g_ds;
   // SILK-side cells (k_silk): lane per stream, ticks in order
   {
     std::vector<SilkState> sst(n_lanes);

@@ -86,20 +86,21 @@ def fuzz_grid(n_lanes: int, n_ticks: int, payload: int, toc_fn, seed: int = 1):
     return arena, offsets
 
 
-def oracle_decode_grid(arena, offsets, n_lanes, n_ticks, channels, frame_size, i16=False, quirks=QUIRKS_MOUSIKI, threads=None):
+def oracle_decode_grid(arena, offsets, n_lanes, n_ticks, channels, frame_size, i16=False, quirks=QUIRKS_MOUSIKI, threads=None, fs=48000):
     lib = oracle_lib()
     n = n_lanes * n_ticks
     pcm = np.zeros((n, frame_size * channels), dtype=np.int16 if i16 else np.float32)
     samples = np.zeros(n, dtype=np.int32)
     rng = np.zeros(n, dtype=np.uint32)
-    lib.orc_decode_grid(48000, channels, quirks, ptr(arena), ptr(offsets), n_lanes, n_ticks, frame_size,
+    lib.orc_decode_grid(fs, channels, quirks, ptr(arena), ptr(offsets), n_lanes, n_ticks, frame_size,
                         None if i16 else ptr(pcm), ptr(pcm) if i16 else None, ptr(samples), ptr(rng),
                         threads or os.cpu_count() or 1)
     return pcm, samples, rng
 
 
-def emul_decode_grid(arena, offsets, n_lanes, n_ticks, channels, frame_size, i16=False, quirks=QUIRKS_MOUSIKI, debug=False):
+def emul_decode_grid(arena, offsets, n_lanes, n_ticks, channels, frame_size, i16=False, quirks=QUIRKS_MOUSIKI, debug=False, fs=48000):
     lib = emul_lib()
+    lib.emu_set_downsample(48000 // fs)
     n = n_lanes * n_ticks
     stride = frame_size * channels
     pcm = np.zeros((n, stride), dtype=np.float32)
@@ -110,6 +111,7 @@ def emul_decode_grid(arena, offsets, n_lanes, n_ticks, channels, frame_size, i16
     xs = np.zeros((n, 2, 960), dtype=np.float32) if debug else None
     lib.emu_decode_grid(channels, quirks, ptr(arena), ptr(offsets), n_lanes, n_ticks, stride, ptr(pcm), ptr(pcm16), ptr(samples),
                         ptr(rng), ptr(iy), ptr(xs))
+    lib.emu_set_downsample(1)
     return (pcm16 if i16 else pcm), samples, rng, iy, xs
 
 

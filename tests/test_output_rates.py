@@ -1,0 +1,102 @@
+"""Decoder output rates below 48 kHz: `Decoder::new(8000 | 12000 | 16000 | 24000, ..)`,
+src/opus_decoder.rs:1550-1556.
+
+Built: the CELT side — `downsample = 48000 / Fs` in synthesis and de-emphasis (src/celt/celt_decoder.rs:584-776, 2232-2297;
+denormalise_bands clears the bins from N / downsample on, src/celt/bands.rs:4198-4204; the de-emphasis filter runs over every
+48 kHz sample and keeps every downsample-th one) for coded CELT-only frames, single and multi-frame packets, f32 / int16 / 24-bit.
+Not built: the SILK resampler's other ratios (src/silk/resampler.rs:279) and concealment at those rates — packets with a SILK
+part and lost packets report -5 per packet there.
+
+CPU: host emulation of the kernel bodies against the oracle, bit for bit. GPU (-m gpu): the CUDA path through the C ABI."""
+import numpy as np
+import pytest
+
+import helpers
+
+RATES = [24000, 16000, 12000, 8000]
+SHAPES = [
+    ("fb 20 ms stereo", helpers.celt_toc(3, True), 2, 960, (40, 160)),
+    ("fb 10 ms mono", helpers.celt_toc(2, False), 1, 480, (30, 90)),
+    ("swb 5 ms stereo", helpers.celt_toc(1, True, bandwidth=2), 2, 240, (20, 60)),
+    ("nb 2.5 ms mono in a stereo decoder", helpers.celt_toc(0, False, bandwidth=0), 2, 120, (8, 30)),
+]
+
+
+@pytest.mark.parametrize("fs", RATES)
+@pytest.mark.parametrize("name,toc,ch,frame48,payload", SHAPES, ids=[s[0] for s in SHAPES])
+def test_emul_output_rates(fs, name, toc, ch, frame48, payload):
+    lanes, ticks = 6, 10
+    frame = frame48 * fs // 48000
+    arena, offsets = helpers.fuzz_grid(lanes, ticks, payload, lambda t, j, r: toc, seed=7)
+    for i16 in (False, True):
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, frame, i16=i16, fs=fs)
+        pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, ticks, ch, frame, i16=i16, fs=fs)
+        assert (so == frame).all() and np.array_equal(so, se) and np.array_equal(ro, re)
+        assert np.array_equal(po, pe), (name, fs, i16)
+
+
+def _gpu(arena, offsets, ids, lanes, ch, cap, fs, i16=False, flags=None, **kw):
+    from mousiki_b200 import BatchDecoder
+
+    with BatchDecoder(lanes, fs, ch, **kw) as dec:
+        return dec.decode(arena, offsets, ids, cap, flags=flags) if i16 else dec.decode_float(arena, offsets, ids, cap, flags=flags)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fs", RATES)
+def test_gpu_output_rates(fs):
+    lanes, ticks = 128, 10
+    ids = np.tile(np.arange(lanes, dtype=np.uint32), ticks)
+    for name, toc, ch, frame48, payload in SHAPES:
+        frame = frame48 * fs // 48000
+        arena, offsets = helpers.fuzz_grid(lanes, ticks, payload, lambda t, j, r: toc, seed=23)
+        for i16 in (False, True):
+            po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, frame, i16=i16, fs=fs)
+            pg, sg, rg = _gpu(arena, offsets, ids, lanes, ch, frame, fs, i16=i16, max_frames_per_pass=4 * lanes)
+            assert np.array_equal(so, sg) and np.array_equal(ro, rg), (name, fs)
+            assert np.array_equal(po, pg), (name, fs, i16)
+
+
+@pytest.mark.gpu
+def test_gpu_output_rate_packets_of_several_frames_and_mixed_sizes():
+    """Code-3 packets of three 10 ms frames and a stream that changes its frame size every packet, at 16 kHz."""
+    lanes, groups, fs = 48, 4, 16000
+    fa, fo = helpers.fuzz_grid(lanes, 3 * groups, 70, lambda t, j, r: helpers.celt_toc(2, True), seed=29)
+    pkts = []
+    for g in range(groups):
+        for j in range(lanes):
+            fr = [bytes(fa[fo[(3 * g + k) * lanes + j] + 1:fo[(3 * g + k) * lanes + j + 1]]) for k in range(3)]
+            pkts.append(helpers.multiframe_packet(helpers.celt_toc(2, True), fr, 3))
+    offsets = np.zeros(len(pkts) + 1, dtype=np.uint32)
+    offsets[1:] = np.cumsum([len(p) for p in pkts])
+    arena = np.concatenate(pkts).astype(np.uint8)
+    ids = np.tile(np.arange(lanes, dtype=np.uint32), groups)
+    cap = 1440 * fs // 48000
+    for i16 in (False, True):
+        po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, groups, 2, cap, i16=i16, fs=fs)
+        assert (so == cap).all()
+        pg, sg, rg = _gpu(arena, offsets, ids, lanes, 2, cap, fs, i16=i16)
+        assert np.array_equal(so, sg) and np.array_equal(ro, rg) and np.array_equal(po, pg), i16
+    arena, offsets = helpers.fuzz_grid(lanes, 12, (20, 120), lambda t, j, r: helpers.celt_toc(int(r.integers(0, 4)), True), seed=31)
+    ids = np.tile(np.arange(lanes, dtype=np.uint32), 12)
+    po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, 12, 2, 320, fs=fs)
+    pg, sg, rg = _gpu(arena, offsets, ids, lanes, 2, 320, fs)
+    assert np.array_equal(so, sg) and np.array_equal(ro, rg) and np.array_equal(po, pg)
+
+
+@pytest.mark.gpu
+def test_gpu_output_rate_refuses_what_it_does_not_carry():
+    lanes, fs = 8, 24000
+    arena, offsets = helpers.fuzz_grid(lanes, 3, 60, lambda t, j, r: helpers.celt_toc(3, True), seed=37)
+    flags = np.zeros(3 * lanes, dtype=np.uint8)
+    flags[lanes + 0] = flags[lanes + 1] = 2                                                    # lost
+    arena[offsets[lanes + 2]] = arena[offsets[lanes + 3]] = helpers.silk_toc(2, 1, True)      # SILK-only
+    arena[offsets[lanes + 4]] = arena[offsets[lanes + 5]] = 0x7C                               # hybrid FB 20 ms stereo
+    ids = np.tile(np.arange(lanes, dtype=np.uint32), 3)
+    pg, sg, rg = _gpu(arena, offsets, ids, lanes, 2, 480, fs, flags=flags)
+    assert (sg[lanes:lanes + 6] == -5).all(), sg[lanes:2 * lanes]
+    assert (sg[:lanes] == 480).all() and (sg[lanes + 6:2 * lanes] == 480).all()
+    po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, 3, 2, 480, fs=fs)
+    for j in (6, 7):
+        for t in range(3):
+            assert np.array_equal(pg[t * lanes + j], po[t * lanes + j]) and rg[t * lanes + j] == ro[t * lanes + j]
