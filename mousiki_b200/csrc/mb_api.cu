@@ -947,7 +947,7 @@ int bd_create(const bd_config* cfg, bd_handle** out) {
   h->CC = cfg->channels;
   h->disable_inv = cfg->disable_phase_inversion < 0 ? (cfg->channels == 1) : (cfg->disable_phase_inversion != 0);
   h->gain = cfg->gain_q8 == 0 ? 1.f : (float)exp(0.6931471805599453094 * (double)((3.32192809488736234787f / 5120.0f) * (float)cfg->gain_q8));
-  h->max_frames_per_pass = cfg->max_frames_per_pass ? cfg->max_frames_per_pass : (1u << 18);
+  h->max_frames_per_pass = cfg->max_frames_per_pass ? cfg->max_frames_per_pass : (1u << 19);   // ~16 GB of per-frame scratch at most: one pass for the headline call (40.9 vs 41.4 ms in two)
   { const char* sb = getenv("MOUSIKI_B200_PARALLEL_BANDS"); h->parallel_bands = sb && atoi(sb) > 0; }
   { const char* sb = getenv("MOUSIKI_B200_CLIP_SERIAL"); h->clip_serial = sb && atoi(sb) > 0; }
   { const char* sb = getenv("MOUSIKI_B200_FUSED_I16"); h->fused_i16 = !(sb && atoi(sb) == 0); }
