@@ -36,7 +36,14 @@
 using namespace mb;
 
 // ------------------------------------------------------------------------------------------ kernels
-__global__ void __launch_bounds__(128, 7) k_parse(const uint8_t* __restrict__ arena, const uint32_t* __restrict__ offsets,
+#ifndef MB_PLAN_MIN_CTAS
+#define MB_PLAN_MIN_CTAS 8   // (10: 4.58 ms, 12: 5.51 ms against 4.16 ms per step)
+#endif
+// Two register budgets of the same parser: 10 CTAs per SM (51 registers) when the launch spans several waves — 8.11 against 8.76 ms
+// per step on the headline call, C3 843 k -> 884 k audio-s/s — and 7 CTAs per SM (73 registers) when all of it fits in one wave,
+// where the extra residents only slow each other down (the 13-tick passes of the host-buffer call: 9.9 against 10.3 ms).
+template <int MIN_CTAS>
+__global__ void __launch_bounds__(128, MIN_CTAS) k_parse(const uint8_t* __restrict__ arena, const uint32_t* __restrict__ offsets,
                                                const uint32_t* __restrict__ pkt_map, uint32_t n_cells, uint32_t* __restrict__ rec, int CC,
                                                uint32_t quirks, int disable_inv, int cap_per_ch, const uint8_t* __restrict__ flags,
                                                uint32_t n_lanes, const uint32_t* __restrict__ lane_stream, const StreamState* st,
@@ -106,7 +113,7 @@ __global__ void __launch_bounds__(PVQ_THREADS) k_pvq(PvqParams P, uint32_t n_cel
   }
 }
 
-__global__ void __launch_bounds__(128, 8) k_plan(PlanParams P, uint32_t n_cells, uint32_t n_main, uint32_t aux_base) {
+__global__ void __launch_bounds__(128, MB_PLAN_MIN_CTAS) k_plan(PlanParams P, uint32_t n_cells, uint32_t n_main, uint32_t aux_base) {
   uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
   if (f >= n_cells) return;
   celt_plan_frame(launch_cell(f, n_main, aux_base), P);
@@ -1242,8 +1249,12 @@ static int decode_grid_device(bd_handle* h, const uint8_t* d_arena, const uint32
     uint32_t* range = d_range + shift;
     float* pcm = pcm_f32 ? pcm_f32 + shift * pcm_stride : nullptr;
     h->prof_begin(BD_K_PARSE, s);
-    k_parse<<<(cells + 127) / 128, 128, 0, s>>>(d_arena, offs, map, cells, h->rec.as<uint32_t>(), CC, h->cfg.quirks, h->disable_inv,
-                                                cap_per_ch, flg, n_lanes, d_lane_stream, h->states.as<StreamState>(), aux);
+    if ((cells + 127) / 128 > 7u * (uint32_t)h->n_sm)
+      k_parse<10><<<(cells + 127) / 128, 128, 0, s>>>(d_arena, offs, map, cells, h->rec.as<uint32_t>(), CC, h->cfg.quirks, h->disable_inv,
+                                                      cap_per_ch, flg, n_lanes, d_lane_stream, h->states.as<StreamState>(), aux);
+    else
+      k_parse<7><<<(cells + 127) / 128, 128, 0, s>>>(d_arena, offs, map, cells, h->rec.as<uint32_t>(), CC, h->cfg.quirks, h->disable_inv,
+                                                     cap_per_ch, flg, n_lanes, d_lane_stream, h->states.as<StreamState>(), aux);
     h->prof_end(s);
     // fork: k_pvq needs nothing but the records, so it runs beside k_energy / k_silk, which keep one lane per stream
     // busy for a long time and leave most of the machine idle. The two per-stream kernels go to a second stream of the
