@@ -79,12 +79,18 @@ __global__ void k_aux_clear(uint32_t* rec, FrameMeta* meta, AuxPool A) {
 // Cell of the u-th thread / warp of a per-cell launch: the pass's main cells, then the auxiliary pool.
 __device__ __forceinline__ uint32_t launch_cell(uint32_t u, uint32_t n_main, uint32_t aux_base) { return u < n_main ? u : aux_base + (u - n_main); }
 
-constexpr int PVQ_THREADS = 64;
+#ifndef MB_PVQ_THREADS
+#define MB_PVQ_THREADS 64
+#endif
+constexpr int PVQ_THREADS = MB_PVQ_THREADS;
 // One CTA per PVQ_CELLS consecutive cells: the first lanes read their status words (one 32-byte sector) and the CTA then
 // walks the cells that hold a CELT part. A group of SILK-only or empty cells costs one load, not PVQ_CELLS CTA launches
 // (the kernel runs beside k_silk, whose long-lived CTAs should not have to compete with a million empty ones); a longer
 // walk per CTA costs CELT throughput (per 5e5 frames, beside k_energy: 32 cells 9.7 ms, 8 cells 8.3 ms, 1 cell 7.9 ms).
-constexpr uint32_t PVQ_CELLS = 8;
+#ifndef MB_PVQ_CELLS
+#define MB_PVQ_CELLS 8
+#endif
+constexpr uint32_t PVQ_CELLS = MB_PVQ_CELLS;
 __global__ void __launch_bounds__(PVQ_THREADS) k_pvq(PvqParams P, uint32_t n_cells, uint32_t n_main, uint32_t aux_base) {
   __shared__ float X[2 * MAX_N];
   __shared__ uint32_t live_s;
@@ -120,8 +126,11 @@ __global__ void __launch_bounds__(128, MB_PLAN_MIN_CTAS) k_plan(PlanParams P, ui
 }
 
 // one warp per frame; 4 frames per CTA
-constexpr int BANDS_WARPS = 4;
-__global__ void __launch_bounds__(32 * BANDS_WARPS, 6) k_bands(BandsParams P, uint32_t n_cells, uint32_t n_main, uint32_t aux_base) {
+#ifndef MB_BANDS_WARPS
+#define MB_BANDS_WARPS 4
+#endif
+constexpr int BANDS_WARPS = MB_BANDS_WARPS;
+__global__ void __launch_bounds__(32 * BANDS_WARPS, 24 / BANDS_WARPS) k_bands(BandsParams P, uint32_t n_cells, uint32_t n_main, uint32_t aux_base) {
   __shared__ BandsSmem sm[BANDS_WARPS];
   const uint32_t f = blockIdx.x * BANDS_WARPS + (threadIdx.x >> 5);
   if (f >= n_cells) return;
@@ -131,7 +140,7 @@ __global__ void __launch_bounds__(32 * BANDS_WARPS, 6) k_bands(BandsParams P, ui
 
 // Hybrid frames: one warp per lane, the lane's ticks in order, because the reference's fold buffer outlives the frame
 // (mb_celt_bands.cuh); `fold` is [stream][FOLD_WORDS].  Lanes without a hybrid frame leave after one pass over the flags.
-__global__ void __launch_bounds__(32 * BANDS_WARPS, 6) k_bands_hyb(BandsParams P, uint32_t n_lanes, const uint32_t* __restrict__ order,
+__global__ void __launch_bounds__(32 * BANDS_WARPS, 24 / BANDS_WARPS) k_bands_hyb(BandsParams P, uint32_t n_lanes, const uint32_t* __restrict__ order,
                                                                  const uint32_t* __restrict__ order_n,
                                                                  const uint32_t* __restrict__ lane_stream, float* fold) {
   __shared__ BandsSmem sm[BANDS_WARPS];
@@ -239,7 +248,10 @@ __global__ void __launch_bounds__(32 * IMDCT_WARPS, IMDCT_CTAS_PER_SM) k_imdct(I
 }
 
 // phase 2c(i): one warp per stream-channel, 4 per CTA
-constexpr int COMB_WARPS = 4;
+#ifndef MB_COMB_WARPS
+#define MB_COMB_WARPS 4
+#endif
+constexpr int COMB_WARPS = MB_COMB_WARPS;
 __global__ void __launch_bounds__(32 * COMB_WARPS) k_comb(TailParams P) {
   __shared__ CombSmem sm[COMB_WARPS];
   const uint32_t idx = blockIdx.x * COMB_WARPS + (threadIdx.x >> 5);

@@ -299,6 +299,9 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
     if (!silk_bit) reject = false;
     else if (red) reject = !hybrid && st_prev_mode == 1001 && !(red_aux && fadeout);   // after hybrid the cell must hold the fade-out frame
     else reject = silk_only && st_prev_mode == 1001;
+    // below 48 kHz a stream stays in one mode: plain SILK-only packets, or CELT-only ones (row F4; the fades, redundancy frames and
+    // concealed transition frames of a mode switch are not built at those rates)
+    if (quirk_ds(Q.quirks) > 1 && ((silk_bit && (!silk_only || st_prev_mode == 1002)) || trans_to_celt)) reject = true;
     if (reject) {
       if (lead) {
         meta[f] = m;
@@ -343,10 +346,10 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
       st_prev_mode = 1000;
       st_prev_redundancy = 0;
       st_range_final = silk_rng;
-      st_last_duration = N;
+      st_last_duration = N / quirk_ds(Q.quirks);
       if (lead) {
         meta[f] = m;
-        samples_out[p] = N;
+        samples_out[p] = N / quirk_ds(Q.quirks);
         final_range_out[p] = st_range_final;
       }
       continue;

@@ -46,6 +46,7 @@ struct SilkPcmOut {
   float gain; int apply_gain;
   int gain_from;   // first sample position (per channel) the gain applies to: 0, or 120 when k_deemph finishes the first
                    // 2.5 ms of the row (CELT fade-out after a hybrid packet) and applies the gain there itself
+  int fs_out_khz = 48;   // the decoder's output rate (row F4): 48, or 24 / 16 / 12 / 8 for SILK-only streams
 };
 struct SilkSink {
   int32_t* stage;  // 32 words, lane-private (shared memory on the device)
@@ -127,13 +128,48 @@ struct SilkSrc {
 
 // resampler.rs:279-369 + resampler_private_iir_fir.rs:80-197 + resampler_private_up2_hq.rs:31-117, streamed.
 // `fir`: the 12 x 4 interpolation table (shared-memory copy on the device). Returns the number of samples produced.
+// Output rates other than 48 kHz (row F4; resampler.rs:87-176): the same delayed input stream feeds a plain copy when the
+// output rate equals the internal one, the 2x all-pass up-sampler alone when it is twice that, else the up-sampler + FIR
+// interpolator with the ratio's own step. Output rates BELOW the internal rate (the down-FIR kernels) are refused at the parser.
 MB_DEV_NOINLINE int silk_resample48(SilkChanState& c, const SilkSrc& in, int n_in, const int16_t* fir, SilkSink& sink) {
-  const int fs = c.fs_khz;
-  const int delay = fs == 8 ? 0 : (fs == 12 ? 4 : 7);                 // DELAY_MATRIX_DEC[.][48 kHz] (resampler.rs:228)
-  const int32_t inc = fs == 8 ? 21846 : (fs == 12 ? 32768 : 43691);   // compute_inv_ratio_q16(fs, 48000, up2x = 1)
+  const int fs = c.fs_khz, fs_out = sink.o->fs_out_khz;
+  int delay = fs == 8 ? 0 : (fs == 12 ? 4 : 7);                 // DELAY_MATRIX_DEC[.][48 kHz] (resampler.rs:228)
+  int32_t inc = fs == 8 ? 21846 : (fs == 12 ? 32768 : 43691);   // compute_inv_ratio_q16(fs, 48000, up2x = 1)
   int32_t S0 = c.res_iir[0], S1 = c.res_iir[1], S2 = c.res_iir[2], S3 = c.res_iir[3], S4 = c.res_iir[4], S5 = c.res_iir[5];
   const int32_t c00 = s_shl(silk_resampler_up2_hq_0[0], 16), c01 = s_shl(silk_resampler_up2_hq_0[1], 16), c02 = s_shl(silk_resampler_up2_hq_0[2], 16);
   const int32_t c10 = s_shl(silk_resampler_up2_hq_1[0], 16), c11 = s_shl(silk_resampler_up2_hq_1[1], 16), c12 = s_shl(silk_resampler_up2_hq_1[2], 16);
+  if (fs_out != 48) {
+    const int ii = fs == 8 ? 0 : (fs == 12 ? 1 : 2), oi = fs_out == 8 ? 0 : (fs_out == 12 ? 1 : (fs_out == 16 ? 2 : 3));
+    delay = (int)silk_delay_matrix_dec[ii * 5 + oi];
+    if (fs_out == fs || fs_out == 2 * fs) {
+      const bool up2 = fs_out != fs;
+      int made = 0;
+      for (int t = 0; t < n_in; t++) {
+        const int32_t x = t < delay ? (int32_t)c.res_delay[t] : in.at(t - delay);
+        if (!up2) { silk_sink_put(sink, x); made++; continue; }
+        const int32_t in32 = x << 10;
+        int32_t Y, X, o1, o2;
+        Y = s_sub(in32, S0); X = s_mulhi(Y, c00); o1 = s_add(S0, X); S0 = s_add(in32, X);
+        Y = s_sub(o1, S1); X = s_mulhi(Y, c01); o2 = s_add(S1, X); S1 = s_add(o1, X);
+        Y = s_sub(o2, S2); X = s_add(Y, s_mulhi(Y, c02)); o1 = s_add(S2, X); S2 = s_add(o2, X);
+        silk_sink_put(sink, s_sat16(s_rr(o1, 10)));
+        Y = s_sub(in32, S3); X = s_mulhi(Y, c10); o1 = s_add(S3, X); S3 = s_add(in32, X);
+        Y = s_sub(o1, S4); X = s_mulhi(Y, c11); o2 = s_add(S4, X); S4 = s_add(o1, X);
+        Y = s_sub(o2, S5); X = s_add(Y, s_mulhi(Y, c12)); o1 = s_add(S5, X); S5 = s_add(o2, X);
+        silk_sink_put(sink, s_sat16(s_rr(o1, 10)));
+        made += 2;
+      }
+      c.res_iir[0] = S0; c.res_iir[1] = S1; c.res_iir[2] = S2; c.res_iir[3] = S3; c.res_iir[4] = S4; c.res_iir[5] = S5;
+      int16_t keep[16];
+      for (int i = 0; i < delay; i++) keep[i] = (int16_t)in.at(n_in - delay + i);
+      for (int i = 0; i < delay; i++) c.res_delay[i] = keep[i];
+      return made;
+    }
+    // compute_inv_ratio_q16 (resampler.rs:178-200) with the 2x stage in front
+    int64_t inv = ((int64_t)fs << 17) / fs_out;
+    while (((inv * fs_out) >> 16) < ((int64_t)fs << 1)) inv++;
+    inc = (int32_t)inv;
+  }
   int32_t w[10];                     // the newest 10 up-sampled values, w[9] newest
 #pragma unroll
   for (int j = 0; j < 8; j++) w[2 + j] = c.res_fir[j];
@@ -448,6 +484,7 @@ MB_DEV void silk_lane(const SilkLaneParams& q, uint32_t lane, SilkWork& W, int32
     const bool fadeout = (fl & 8u) && !((status >> 17) & 1u) && !MB_ST_LOST(status);
     o.CC = q.CC; o.gain = q.gain; o.apply_gain = ((shared && !fadeout) || (fl & MB_FL_FADE_ROW)) ? 0 : q.apply_gain;
     o.gain_from = fadeout ? SHORT_MDCT : 0;
+    o.fs_out_khz = 48 / quirk_ds(q.quirks);
     SilkPacketCtl ctl;
     ctl.mode = MB_ST_LOST(status) ? SILK_PKT_LOST : (MB_ST_FEC(status) ? SILK_PKT_FEC : SILK_PKT_NORMAL);
     ctl.samples48 = ctl.mode == SILK_PKT_LOST ? (int)rb[S_RANGE * 32] : 0;

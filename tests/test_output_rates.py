@@ -3,9 +3,10 @@ src/opus_decoder.rs:1550-1556.
 
 Built: the CELT side — `downsample = 48000 / Fs` in synthesis and de-emphasis (src/celt/celt_decoder.rs:584-776, 2232-2297;
 denormalise_bands clears the bins from N / downsample on, src/celt/bands.rs:4198-4204; the de-emphasis filter runs over every
-48 kHz sample and keeps every downsample-th one) for coded CELT-only frames, single and multi-frame packets, f32 / int16 / 24-bit.
-Not built: the SILK resampler's other ratios (src/silk/resampler.rs:279) and concealment at those rates — packets with a SILK
-part and lost packets report -5 per packet there.
+48 kHz sample and keeps every downsample-th one) for coded CELT-only frames, single and multi-frame packets, f32 / int16 / 24-bit;
+and SILK-only packets whose internal rate does not exceed the output rate — the resampler's copy, 2x and interpolating modes
+(src/silk/resampler.rs:87-176, 279-369) in the k_silk lane. Not built: the resampler's down-sampling FIRs (a WB packet in an
+8 / 12 kHz decoder), hybrid packets, mode switches and concealment at those rates — reported per packet as -5 there.
 
 CPU: host emulation of the kernel bodies against the oracle, bit for bit. GPU (-m gpu): the CUDA path through the C ABI."""
 import numpy as np
@@ -100,3 +101,84 @@ def test_gpu_output_rate_refuses_what_it_does_not_carry():
     for j in (6, 7):
         for t in range(3):
             assert np.array_equal(pg[t * lanes + j], po[t * lanes + j]) and rg[t * lanes + j] == ro[t * lanes + j]
+
+
+SILK_SHAPES = [
+    ("wb 20 ms mono", helpers.silk_toc(2, 1, False), 1, (20, 60), 960),
+    ("wb 20 ms stereo", helpers.silk_toc(2, 1, True), 2, (25, 70), 960),
+    ("nb 10 ms mono", helpers.silk_toc(0, 0, False), 1, (8, 30), 480),
+    ("mb 40 ms stereo", helpers.silk_toc(1, 2, True), 2, (40, 100), 1920),
+    ("nb 60 ms mono in a stereo decoder", helpers.silk_toc(0, 3, False), 2, (40, 90), 2880),
+]
+
+
+def _silk_fits(toc, fs):
+    return 8 + 4 * ((toc >> 5) & 3) <= fs // 1000
+
+
+@pytest.mark.parametrize("fs", RATES)
+def test_emul_silk_only_output_rates(fs):
+    lanes, ticks = 4, 6
+    ran = 0
+    for name, toc, ch, payload, frame48 in SILK_SHAPES:
+        if not _silk_fits(toc, fs):
+            continue
+        frame = frame48 * fs // 48000
+        arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, payload, lambda k, r: toc, seed=11, channels=ch)
+        for i16 in (False, True):
+            po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, frame, i16=i16, fs=fs)
+            pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, ticks, ch, frame, i16=i16, fs=fs)
+            assert (so == frame).all() and np.array_equal(so, se) and np.array_equal(ro, re), (name, fs)
+            assert np.array_equal(po, pe), (name, fs, i16)
+        ran += 1
+    assert ran >= 2
+    # a stream that changes its SILK bandwidth and frame size from packet to packet (the resampler is re-initialised on a rate change)
+    bws = [b for b in (0, 1, 2) if 8 + 4 * b <= fs // 1000]
+    arena, offsets = helpers.silk_fuzz_grid(lanes, 10, (20, 80), lambda k, r: helpers.silk_toc(int(r.choice(bws)), int(r.integers(0, 2)), True),
+                                            seed=13, channels=2)
+    cap = 960 * fs // 48000
+    po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, 10, 2, cap, fs=fs)
+    pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, 10, 2, cap, fs=fs)
+    assert (so > 0).all() and np.array_equal(so, se) and np.array_equal(ro, re) and np.array_equal(po, pe)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fs", RATES)
+def test_gpu_silk_only_output_rates(fs):
+    lanes, ticks = 64, 6
+    ids = np.tile(np.arange(lanes, dtype=np.uint32), ticks)
+    for name, toc, ch, payload, frame48 in SILK_SHAPES:
+        if not _silk_fits(toc, fs):
+            continue
+        frame = frame48 * fs // 48000
+        arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, payload, lambda k, r: toc, seed=17, channels=ch)
+        for i16 in (False, True):
+            po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, frame, i16=i16, fs=fs)
+            pg, sg, rg = _gpu(arena, offsets, ids, lanes, ch, frame, fs, i16=i16, max_frames_per_pass=2 * lanes)
+            assert np.array_equal(so, sg) and np.array_equal(ro, rg), (name, fs)
+            assert np.array_equal(po, pg), (name, fs, i16)
+    bws = [b for b in (0, 1, 2) if 8 + 4 * b <= fs // 1000]
+    arena, offsets = helpers.silk_fuzz_grid(lanes, 8, (20, 80), lambda k, r: helpers.silk_toc(int(r.choice(bws)), int(r.integers(0, 2)), True),
+                                            seed=19, channels=2)
+    ids = np.tile(np.arange(lanes, dtype=np.uint32), 8)
+    cap = 960 * fs // 48000
+    po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, 8, 2, cap, fs=fs)
+    pg, sg, rg = _gpu(arena, offsets, ids, lanes, 2, cap, fs)
+    assert np.array_equal(so, sg) and np.array_equal(ro, rg) and np.array_equal(po, pg)
+
+
+@pytest.mark.gpu
+def test_gpu_output_rate_refuses_silk_above_the_output_rate_and_mode_switches():
+    lanes, fs = 8, 12000
+    wb, wo = helpers.silk_fuzz_grid(lanes, 1, (20, 60), lambda k, r: helpers.silk_toc(2, 1, False), seed=41, channels=1)   # WB in a 12 kHz decoder
+    ids = np.arange(lanes, dtype=np.uint32)
+    pg, sg, rg = _gpu(wb, wo, ids, lanes, 1, 240, fs)
+    assert (sg == -5).all()
+    # NB SILK, then a CELT-only packet: the switch (concealed transition frame + fade) is not built below 48 kHz
+    na, no = helpers.silk_fuzz_grid(lanes, 1, (10, 40), lambda k, r: helpers.silk_toc(0, 1, False), seed=43, channels=1)
+    ca, co = helpers.fuzz_grid(lanes, 1, 40, lambda t, j, r: helpers.celt_toc(3, False), seed=45)
+    arena = np.concatenate([na, ca])
+    offsets = np.concatenate([no, no[-1] + co[1:]]).astype(np.uint32)
+    ids = np.tile(np.arange(lanes, dtype=np.uint32), 2)
+    pg, sg, rg = _gpu(arena, offsets, ids, lanes, 1, 240, fs)
+    assert (sg[:lanes] == 240).all() and (sg[lanes:] == -5).all()
