@@ -239,13 +239,19 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
       // ---- lost packet / frame of at most one byte: decode_frame(None) (src/opus_decoder.rs:491-575). The stream conceals in
       // the mode of its last packet (CELT-only after a SILK -> CELT redundancy frame): SILK in k_silk (mb_silk_plc.cuh), CELT
       // as above, hybrid both (the CELT part from band 17, always noise).
-      const int audiosize = (int)r[S_RANGE * 32];
+      const int audiosize = (int)r[S_RANGE * 32];            // in 48 kHz samples; the row takes audiosize / ds_out of them
+      const int ds_out = quirk_ds(Q.quirks);
       const int md = st_prev_redundancy ? 1002 : st_prev_mode;
       if (md == 0) {   // nothing decoded yet: silence (opus_decoder.rs:527-540)
         m.flags = MB_FL_PLC | MB_FL_F32ROW;   // concealed, but no CELT frame: k_fade zero-fills seed_in samples of the row
-        m.seed_in = (uint32_t)audiosize;
-        st_prev_mode = 0; st_prev_redundancy = 0; st_range_final = 0; st_last_duration = audiosize;
-        if (lead) { meta[f] = m; samples_out[p] = audiosize; final_range_out[p] = 0; }
+        m.seed_in = (uint32_t)(audiosize / ds_out);
+        st_prev_mode = 0; st_prev_redundancy = 0; st_range_final = 0; st_last_duration = audiosize / ds_out;
+        if (lead) { meta[f] = m; samples_out[p] = audiosize / ds_out; final_range_out[p] = 0; }
+        continue;
+      }
+      if (ds_out > 1 && md == 1001) {   // (hybrid streams are not carried below 48 kHz)
+        if (lead) { meta[f] = m; samples_out[p] = MB_UNIMPLEMENTED; final_range_out[p] = st_range_final; }
+        pkt_failed = true;
         continue;
       }
       int lmq = -1;
@@ -257,8 +263,8 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
       }
       if (md == 1000) m.flags = 2u | MB_FL_PLC | pkt_route;
       else celt_conceal(f, r, status, m, audiosize, lmq, md == 1001 ? 17 : 0, md == 1001 ? (2u | 8u) : 0u);
-      st_prev_mode = md; st_prev_redundancy = 0; st_range_final = 0; st_last_duration = audiosize;
-      if (lead) { meta[f] = m; samples_out[p] = audiosize; final_range_out[p] = 0; }
+      st_prev_mode = md; st_prev_redundancy = 0; st_range_final = 0; st_last_duration = audiosize / ds_out;
+      if (lead) { meta[f] = m; samples_out[p] = audiosize / ds_out; final_range_out[p] = 0; }
       continue;
     }
     if (pkt_failed || !MB_ST_DECODED(status)) {  // rejected before the decoder ran (unsupported mode, PLC, bad TOC)

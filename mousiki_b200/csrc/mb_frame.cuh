@@ -38,7 +38,11 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
   const bool q2_off = !(quirks & Q2_MDCT_ZERO_FILL);
   const int ds_out = quirk_ds(quirks);
   const bool ola = q2_off || ds_out > 1;
-  if (ola && ((flags && (flags[pkt] & 3u)) || len == 0)) { rec_base[S_STATUS * 32] = (uint32_t)(uint8_t)(int8_t)MB_UNIMPLEMENTED; return; }
+  // (lost packets are concealed below 48 kHz too — the stream pass refuses the hybrid case; in-band FEC is not)
+  if ((q2_off && ((flags && (flags[pkt] & 3u)) || len == 0)) || (ds_out > 1 && flags && (flags[pkt] & 1u))) {
+    rec_base[S_STATUS * 32] = (uint32_t)(uint8_t)(int8_t)MB_UNIMPLEMENTED;
+    return;
+  }
   if ((flags && (flags[pkt] & 2u)) || len == 0) {
     // lost packet (or one concealment frame of it, cut by the host): no payload. The two bytes the host put in its place
     // say how many samples to conceal (mb_host_packets.h); the stream pass decides how (k_energy).
@@ -62,7 +66,7 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
     if (toc & 3u) code = MB_UNIMPLEMENTED;              // multi-frame packets (row F1)
     // (below 48 kHz a SILK-only packet decodes when its internal rate does not exceed the output rate: the resampler's copy, 2x and
     //  interpolating modes are built, its down-sampling FIRs are not; hybrid packets and concealment frames are refused)
-    else if (ola && (len - 1 <= 1 || (!(toc & 0x80u) && (q2_off || (toc & 0x60u) == 0x60u || 8 + 4 * (int)((toc >> 5) & 3u) > 48 / ds_out))))
+    else if (ola && ((q2_off && len - 1 <= 1) || (!(toc & 0x80u) && (q2_off || (toc & 0x60u) == 0x60u || 8 + 4 * (int)((toc >> 5) & 3u) > 48 / ds_out))))
       code = MB_UNIMPLEMENTED;
     else if (len - 1 > 1275) code = MB_INVALID_PACKET;  // src/packet.rs:465: a frame is at most 1275 bytes
     else if (!(toc & 0x80u)) {

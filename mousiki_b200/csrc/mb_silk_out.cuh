@@ -488,7 +488,7 @@ MB_DEV void silk_lane(const SilkLaneParams& q, uint32_t lane, SilkWork& W, int32
     SilkPacketCtl ctl;
     ctl.mode = MB_ST_LOST(status) ? SILK_PKT_LOST : (MB_ST_FEC(status) ? SILK_PKT_FEC : SILK_PKT_NORMAL);
     ctl.samples48 = ctl.mode == SILK_PKT_LOST ? (int)rb[S_RANGE * 32] : 0;
-    ctl.limit = ctl.mode == SILK_PKT_LOST ? ctl.samples48 : 0x7fffffff;
+    ctl.limit = ctl.mode == SILK_PKT_LOST ? ctl.samples48 / quirk_ds(q.quirks) : 0x7fffffff;   // (the row counts output samples)
     silk_synth_packet(S, W, H, X, side_live, rb[(hyb_layout ? S_SILK_HYB : S_HDR0) * 32], rb + (hyb_layout ? S_SILK_HYB + 1 : SL_BASE) * 32, q.quirks,
                       o, stage, fir, ctl);
   }

@@ -6,7 +6,9 @@ denormalise_bands clears the bins from N / downsample on, src/celt/bands.rs:4198
 48 kHz sample and keeps every downsample-th one) for coded CELT-only frames, single and multi-frame packets, f32 / int16 / 24-bit;
 and SILK-only packets whose internal rate does not exceed the output rate — the resampler's copy, 2x and interpolating modes
 (src/silk/resampler.rs:87-176, 279-369) in the k_silk lane. Not built: the resampler's down-sampling FIRs (a WB packet in an
-8 / 12 kHz decoder), hybrid packets, mode switches and concealment at those rates — reported per packet as -5 there.
+8 / 12 kHz decoder), hybrid packets, mode switches and in-band FEC at those rates — reported per packet as -5 there. Lost packets
+of CELT-only and SILK-only streams are concealed at those rates like at 48 kHz (the concealment runs at the codec's own rate; only
+the sample accounting changes).
 
 CPU: host emulation of the kernel bodies against the oracle, bit for bit. GPU (-m gpu): the CUDA path through the C ABI."""
 import numpy as np
@@ -90,13 +92,13 @@ def test_gpu_output_rate_refuses_what_it_does_not_carry():
     lanes, fs = 8, 24000
     arena, offsets = helpers.fuzz_grid(lanes, 3, 60, lambda t, j, r: helpers.celt_toc(3, True), seed=37)
     flags = np.zeros(3 * lanes, dtype=np.uint8)
-    flags[lanes + 0] = flags[lanes + 1] = 2                                                    # lost
+    flags[lanes + 0] = flags[lanes + 1] = 1     # decode(fec=true) on a CELT-only packet: concealed like a loss (opus_decoder.rs:1247-1250)
     arena[offsets[lanes + 2]] = arena[offsets[lanes + 3]] = helpers.silk_toc(2, 1, True)      # SILK-only
     arena[offsets[lanes + 4]] = arena[offsets[lanes + 5]] = 0x7C                               # hybrid FB 20 ms stereo
     ids = np.tile(np.arange(lanes, dtype=np.uint32), 3)
     pg, sg, rg = _gpu(arena, offsets, ids, lanes, 2, 480, fs, flags=flags)
-    assert (sg[lanes:lanes + 6] == -5).all(), sg[lanes:2 * lanes]
-    assert (sg[:lanes] == 480).all() and (sg[lanes + 6:2 * lanes] == 480).all()
+    assert (sg[lanes + 2:lanes + 6] == -5).all(), sg[lanes:2 * lanes]
+    assert (sg[:lanes] == 480).all() and (sg[lanes:lanes + 2] == 480).all() and (sg[lanes + 6:2 * lanes] == 480).all()
     po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, 3, 2, 480, fs=fs)
     for j in (6, 7):
         for t in range(3):
@@ -182,3 +184,74 @@ def test_gpu_output_rate_refuses_silk_above_the_output_rate_and_mode_switches():
     ids = np.tile(np.arange(lanes, dtype=np.uint32), 2)
     pg, sg, rg = _gpu(arena, offsets, ids, lanes, 1, 240, fs)
     assert (sg[:lanes] == 240).all() and (sg[lanes:] == -5).all()
+
+
+def _oracle_lossy(arena, offsets, lost, lanes, ticks, ch, n, fs, i16):
+    lib = helpers.oracle_lib()
+    pcm = np.zeros((lanes * ticks, n * ch), dtype=np.int16 if i16 else np.float32)
+    samples = np.zeros(lanes * ticks, dtype=np.int32)
+    rng = np.zeros(lanes * ticks, dtype=np.uint32)
+    fn = lib.orc_decode_i16 if i16 else lib.orc_decode_float
+    for j in range(lanes):
+        h = lib.orc_create(fs, ch, helpers.QUIRKS_MOUSIKI)
+        for t in range(ticks):
+            p = t * lanes + j
+            if lost[p]:
+                samples[p] = fn(h, None, 0, helpers.ptr(pcm[p]), n, 0)
+            else:
+                pkt = np.ascontiguousarray(arena[offsets[p]:offsets[p + 1]])
+                samples[p] = fn(h, helpers.ptr(pkt), len(pkt), helpers.ptr(pcm[p]), n, 0)
+            rng[p] = lib.orc_final_range(h)
+        lib.orc_destroy(h)
+    return pcm, samples, rng
+
+
+def _lossy_streams(kind, lanes, ticks, fs, seed):
+    """-> (arena, offsets, lost, ch, frame48): CELT FB 20 ms stereo, or SILK NB 20 ms mono in a stereo decoder, with isolated losses and bursts"""
+    from test_plc_parity import lossy_grid
+    from test_silk_plc_parity import loss_pattern
+
+    if kind == "celt":
+        arena, offsets, lost = lossy_grid(lanes, ticks, 3, True, seed=seed)
+        return arena, offsets, lost, 2, 960
+    arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, (15, 50), lambda k, r: helpers.silk_toc(0, 1, False), seed=seed, channels=2)
+    return arena, offsets, loss_pattern(lanes, ticks, seed=seed + 1), 2, 960
+
+
+@pytest.mark.parametrize("fs", [24000, 8000])
+@pytest.mark.parametrize("kind", ["celt", "silk"])
+def test_emul_concealment_below_48k(kind, fs):
+    from test_plc_parity import virtual_grid
+
+    lanes, ticks = 6, 14
+    arena, offsets, lost, ch, frame48 = _lossy_streams(kind, lanes, ticks, fs, 51)
+    n = frame48 * fs // 48000
+    va, vo, vf = virtual_grid(arena, offsets, lost, frame48)      # the host front end hands the device 48 kHz sample counts
+    lib = helpers.emul_lib()
+    for i16 in (False, True):
+        po, so, ro = _oracle_lossy(arena, offsets, lost, lanes, ticks, ch, n, fs, i16)
+        lib.emu_set_flags(helpers.ptr(vf))
+        try:
+            pe, se, re, _, _ = helpers.emul_decode_grid(va, vo, lanes, ticks, ch, n, i16=i16, fs=fs)
+        finally:
+            lib.emu_set_flags(None)
+        assert (so == n).all() and np.array_equal(so, se) and np.array_equal(ro, re)
+        assert np.array_equal(po, pe), (kind, fs, i16)
+    assert lost.sum() > 10
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fs", [24000, 16000, 8000])
+@pytest.mark.parametrize("kind", ["celt", "silk"])
+def test_gpu_concealment_below_48k(kind, fs):
+    """Through the host front end: flags[p] & 2 = decode(None); the packet's bytes are ignored."""
+    lanes, ticks = 48, 14
+    arena, offsets, lost, ch, frame48 = _lossy_streams(kind, lanes, ticks, fs, 61)
+    n = frame48 * fs // 48000
+    ids = np.tile(np.arange(lanes, dtype=np.uint32), ticks)
+    flags = (lost.astype(np.uint8) << 1)
+    for i16 in (False, True):
+        po, so, ro = _oracle_lossy(arena, offsets, lost, lanes, ticks, ch, n, fs, i16)
+        pg, sg, rg = _gpu(arena, offsets, ids, lanes, ch, n, fs, i16=i16, flags=flags, max_frames_per_pass=5 * lanes)
+        assert np.array_equal(so, sg) and np.array_equal(ro, rg), (kind, fs)
+        assert np.array_equal(po, pg), (kind, fs, i16)
