@@ -388,8 +388,14 @@ __global__ void __launch_bounds__(32 * DE_WARPS) k_deemph(TailParams P) {
           if (!o || cnt <= 0) continue;
           const float* tx = tile + r * PITCH;
           const int cr = CC == 2 ? (r & 1) : 0;     // (idx0 is a multiple of 32: row r is channel r % CC of its stream)
+          const bool hy = (hyb_mask >> r) & 1u, late = (late_mask >> r) & 1u;
           for (int j = l; j < cnt; j += 32)
-            if ((k0 + j) % ds == 0) o[(size_t)((k0 + j) / ds) * CC + cr] = tx[j];
+            if ((k0 + j) % ds == 0) {
+              float* q = o + (size_t)((k0 + j) / ds) * CC + cr;
+              float v = tx[j];
+              if (hy) { v = *q + v; if (P.apply_gain && !late) v *= P.gain; }   // hybrid: onto the SILK samples, then the gain on the sum
+              *q = v;
+            }
         }
       } else if (CC == 2) {
 #pragma unroll 2

@@ -249,11 +249,7 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
         if (lead) { meta[f] = m; samples_out[p] = audiosize / ds_out; final_range_out[p] = 0; }
         continue;
       }
-      if (ds_out > 1 && md == 1001) {   // (hybrid streams are not carried below 48 kHz)
-        if (lead) { meta[f] = m; samples_out[p] = MB_UNIMPLEMENTED; final_range_out[p] = st_range_final; }
-        pkt_failed = true;
-        continue;
-      }
+
       int lmq = -1;
       for (int q = 0; q <= MAX_LM; q++) if ((SHORT_MDCT << q) == audiosize) lmq = q;
       if (lmq < 0) {   // (the host front end only cuts whole frame sizes)
@@ -307,7 +303,11 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
     else reject = silk_only && st_prev_mode == 1001;
     // below 48 kHz a stream stays in one mode: plain SILK-only packets, or CELT-only ones (row F4; the fades, redundancy frames and
     // concealed transition frames of a mode switch are not built at those rates)
-    if (quirk_ds(Q.quirks) > 1 && ((silk_bit && (!silk_only || st_prev_mode == 1002)) || trans_to_celt)) reject = true;
+    if (quirk_ds(Q.quirks) > 1) {
+      const bool plain_hybrid = hybrid && !red && !fadeout && (st_prev_mode == 0 || st_prev_mode == 1001);
+      const bool plain_silk = silk_only && (st_prev_mode == 0 || st_prev_mode == 1000);
+      if ((silk_bit && !plain_hybrid && !plain_silk) || trans_to_celt) reject = true;
+    }
     if (reject) {
       if (lead) {
         meta[f] = m;

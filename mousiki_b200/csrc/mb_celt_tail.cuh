@@ -254,10 +254,12 @@ MB_DEV void celt_deemph_lane(uint32_t lane, int c, const TailParams& P) {
     const bool accum = (m.flags & 8u) != 0;
     // the decode gain applies once to the finished row: here, unless the row still waits for a cross-fade (k_fade applies it)
     d.apply_gain = (side || (m.flags & MB_FL_FADE_ROW)) ? 0 : P.apply_gain;
-    if (P.ds > 1) {
+    if (P.ds > 1) {   // (hybrid: the kept samples add onto the SILK samples already in the row, celt_decoder.rs:2281-2290)
       for (int j = 0; j < N; j++) {
-        const float v = d.step(x[j]);
-        if (out && j % P.ds == 0) out[(size_t)(j / P.ds) * CC] = v;
+        if (out && j % P.ds == 0) {
+          float* o = out + (size_t)(j / P.ds) * CC;
+          *o = d.step(x[j], accum ? *o : 0.f, accum);
+        } else d.step(x[j]);
       }
       continue;
     }

@@ -66,7 +66,7 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
     if (toc & 3u) code = MB_UNIMPLEMENTED;              // multi-frame packets (row F1)
     // (below 48 kHz a SILK-only packet decodes when its internal rate does not exceed the output rate: the resampler's copy, 2x and
     //  interpolating modes are built, its down-sampling FIRs are not; hybrid packets and concealment frames are refused)
-    else if (ola && ((q2_off && len - 1 <= 1) || (!(toc & 0x80u) && (q2_off || (toc & 0x60u) == 0x60u || 8 + 4 * (int)((toc >> 5) & 3u) > 48 / ds_out))))
+    else if (ola && ((q2_off && len - 1 <= 1) || (!(toc & 0x80u) && (q2_off || ((toc & 0x60u) == 0x60u ? 16 : 8 + 4 * (int)((toc >> 5) & 3u)) > 48 / ds_out))))
       code = MB_UNIMPLEMENTED;
     else if (len - 1 > 1275) code = MB_INVALID_PACKET;  // src/packet.rs:465: a frame is at most 1275 bytes
     else if (!(toc & 0x80u)) {

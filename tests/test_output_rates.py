@@ -6,7 +6,8 @@ denormalise_bands clears the bins from N / downsample on, src/celt/bands.rs:4198
 48 kHz sample and keeps every downsample-th one) for coded CELT-only frames, single and multi-frame packets, f32 / int16 / 24-bit;
 and SILK-only packets whose internal rate does not exceed the output rate — the resampler's copy, 2x and interpolating modes
 (src/silk/resampler.rs:87-176, 279-369) in the k_silk lane. Not built: the resampler's down-sampling FIRs (a WB packet in an
-8 / 12 kHz decoder), hybrid packets, mode switches and in-band FEC at those rates — reported per packet as -5 there. Lost packets
+8 / 12 kHz decoder, hybrid packets below 16 kHz), mode switches and in-band FEC at those rates — reported per packet as -5 there.
+Hybrid streams decode at 24 / 16 kHz (SILK WB through the resampler, the CELT bands down-sampled and added onto it). Lost packets
 of CELT-only and SILK-only streams are concealed at those rates like at 48 kHz (the concealment runs at the codec's own rate; only
 the sample accounting changes).
 
@@ -214,12 +215,15 @@ def _lossy_streams(kind, lanes, ticks, fs, seed):
     if kind == "celt":
         arena, offsets, lost = lossy_grid(lanes, ticks, 3, True, seed=seed)
         return arena, offsets, lost, 2, 960
+    if kind == "hybrid":     # FB 20 ms stereo: SILK WB at the output rate + CELT bands 17.. down-sampled, added in k_deemph
+        from test_hybrid_parity import hyb_toc
+        arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, (40, 200), lambda k, r: hyb_toc(1, 1, True), seed=seed, channels=2)
+        return arena, offsets, loss_pattern(lanes, ticks, seed=seed + 1), 2, 960
     arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, (15, 50), lambda k, r: helpers.silk_toc(0, 1, False), seed=seed, channels=2)
     return arena, offsets, loss_pattern(lanes, ticks, seed=seed + 1), 2, 960
 
 
-@pytest.mark.parametrize("fs", [24000, 8000])
-@pytest.mark.parametrize("kind", ["celt", "silk"])
+@pytest.mark.parametrize("kind,fs", [("celt", 24000), ("celt", 8000), ("silk", 24000), ("silk", 8000), ("hybrid", 24000), ("hybrid", 16000)])
 def test_emul_concealment_below_48k(kind, fs):
     from test_plc_parity import virtual_grid
 
@@ -241,8 +245,8 @@ def test_emul_concealment_below_48k(kind, fs):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("fs", [24000, 16000, 8000])
-@pytest.mark.parametrize("kind", ["celt", "silk"])
+@pytest.mark.parametrize("kind,fs", [("celt", 24000), ("celt", 16000), ("celt", 8000), ("silk", 24000), ("silk", 16000), ("silk", 8000),
+                                     ("hybrid", 24000), ("hybrid", 16000)])
 def test_gpu_concealment_below_48k(kind, fs):
     """Through the host front end: flags[p] & 2 = decode(None); the packet's bytes are ignored."""
     lanes, ticks = 48, 14
