@@ -488,8 +488,9 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
       st_celt_end = (int)MB_ST_END(status);
       celt_conceal(f, r, status, m, SHORT_MDCT << lmq, lmq, 17, 2u | 8u | (celt_reset ? 4u : 0u) | silk_reset | trans_flags);
       silk_side_seen = true; st_fold_serial = 1;
-      st_prev_mode = 1001; st_prev_redundancy = 0; st_range_final = silk_rng; st_last_duration = SHORT_MDCT << lmq;
-      if (lead) { meta[f] = m; samples_out[p] = SHORT_MDCT << lmq; final_range_out[p] = st_range_final; }
+      const int Nq = (SHORT_MDCT << lmq) / quirk_ds(Q.quirks);
+      st_prev_mode = 1001; st_prev_redundancy = 0; st_range_final = silk_rng; st_last_duration = Nq;
+      if (lead) { meta[f] = m; samples_out[p] = Nq; final_range_out[p] = st_range_final; }
       continue;
     }
     if (hybrid && red) {

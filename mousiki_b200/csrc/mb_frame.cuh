@@ -38,8 +38,8 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
   const bool q2_off = !(quirks & Q2_MDCT_ZERO_FILL);
   const int ds_out = quirk_ds(quirks);
   const bool ola = q2_off || ds_out > 1;
-  // (lost packets are concealed below 48 kHz too — the stream pass refuses the hybrid case; in-band FEC is not)
-  if ((q2_off && ((flags && (flags[pkt] & 3u)) || len == 0)) || (ds_out > 1 && flags && (flags[pkt] & 1u))) {
+  // (below 48 kHz lost packets are concealed and in-band FEC is decoded like at 48 kHz)
+  if (q2_off && ((flags && (flags[pkt] & 3u)) || len == 0)) {
     rec_base[S_STATUS * 32] = (uint32_t)(uint8_t)(int8_t)MB_UNIMPLEMENTED;
     return;
   }

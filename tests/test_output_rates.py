@@ -6,7 +6,7 @@ denormalise_bands clears the bins from N / downsample on, src/celt/bands.rs:4198
 48 kHz sample and keeps every downsample-th one) for coded CELT-only frames, single and multi-frame packets, f32 / int16 / 24-bit;
 and SILK-only packets whose internal rate does not exceed the output rate — the resampler's copy, 2x and interpolating modes
 (src/silk/resampler.rs:87-176, 279-369) in the k_silk lane. Not built: the resampler's down-sampling FIRs (a WB packet in an
-8 / 12 kHz decoder, hybrid packets below 16 kHz), mode switches and in-band FEC at those rates — reported per packet as -5 there.
+8 / 12 kHz decoder, hybrid packets below 16 kHz) and mode switches at those rates — reported per packet as -5 there; in-band FEC works as at 48 kHz.
 Hybrid streams decode at 24 / 16 kHz (SILK WB through the resampler, the CELT bands down-sampled and added onto it). Lost packets
 of CELT-only and SILK-only streams are concealed at those rates like at 48 kHz (the concealment runs at the codec's own rate; only
 the sample accounting changes).
@@ -257,5 +257,74 @@ def test_gpu_concealment_below_48k(kind, fs):
     for i16 in (False, True):
         po, so, ro = _oracle_lossy(arena, offsets, lost, lanes, ticks, ch, n, fs, i16)
         pg, sg, rg = _gpu(arena, offsets, ids, lanes, ch, n, fs, i16=i16, flags=flags, max_frames_per_pass=5 * lanes)
+        assert np.array_equal(so, sg) and np.array_equal(ro, rg), (kind, fs)
+        assert np.array_equal(po, pg), (kind, fs, i16)
+
+
+def _oracle_fec(arena, offsets, flags, lanes, ticks, ch, n, fs, i16):
+    lib = helpers.oracle_lib()
+    pcm = np.zeros((lanes * ticks, n * ch), dtype=np.int16 if i16 else np.float32)
+    samples = np.zeros(lanes * ticks, dtype=np.int32)
+    rng = np.zeros(lanes * ticks, dtype=np.uint32)
+    fn = lib.orc_decode_i16 if i16 else lib.orc_decode_float
+    for j in range(lanes):
+        h = lib.orc_create(fs, ch, helpers.QUIRKS_MOUSIKI)
+        for t in range(ticks):
+            p = t * lanes + j
+            if flags[p] & 2:
+                samples[p] = fn(h, None, 0, helpers.ptr(pcm[p]), n, 0)
+            else:
+                pkt = np.ascontiguousarray(arena[offsets[p]:offsets[p + 1]])
+                samples[p] = fn(h, helpers.ptr(pkt), len(pkt), helpers.ptr(pcm[p]), n, int(flags[p] & 1))
+            rng[p] = lib.orc_final_range(h)
+        lib.orc_destroy(h)
+    return pcm, samples, rng
+
+
+def _fec_streams(kind, lanes, ticks, seed):
+    """-> (arena, offsets, flags, ch, frame48): a lost packet is recovered from the NEXT packet's LBRR data (flag 1) when that one
+    arrived, else concealed (flag 2) — Decoder::decode(.., fec = true), src/opus_decoder.rs:1240-1316"""
+    from test_hybrid_parity import hyb_toc
+    from test_silk_plc_parity import fec_grid, loss_pattern
+
+    toc, payload = (helpers.silk_toc(2, 1, True), (40, 120)) if kind == "silk" else (hyb_toc(1, 1, True), (40, 200))
+    arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, payload, lambda k, r: toc, seed=seed, channels=2)
+    lost = loss_pattern(lanes, ticks, seed=seed + 1, rate=0.3, burst=2)
+    fa, fo, ff = fec_grid(arena, offsets, lost, lanes, ticks)
+    return fa, fo, ff, 2, 960
+
+
+@pytest.mark.parametrize("kind,fs", [("silk", 24000), ("silk", 16000), ("hybrid", 24000), ("hybrid", 16000)])
+def test_emul_fec_below_48k(kind, fs):
+    lanes, ticks = 6, 12
+    fa, fo, ff, ch, frame48 = _fec_streams(kind, lanes, ticks, 71)
+    n = frame48 * fs // 48000
+    pk = [np.array([frame48 & 255, frame48 >> 8], dtype=np.uint8) if ff[p] & 2 else fa[fo[p]:fo[p + 1]] for p in range(len(ff))]
+    vo = np.zeros(len(pk) + 1, dtype=np.uint32)
+    vo[1:] = np.cumsum([len(x) for x in pk])
+    va = np.concatenate(pk).astype(np.uint8)
+    lib = helpers.emul_lib()
+    for i16 in (False, True):
+        po, so, ro = _oracle_fec(fa, fo, ff, lanes, ticks, ch, n, fs, i16)
+        lib.emu_set_flags(helpers.ptr(ff))
+        try:
+            pe, se, re, _, _ = helpers.emul_decode_grid(va, vo, lanes, ticks, ch, n, i16=i16, fs=fs)
+        finally:
+            lib.emu_set_flags(None)
+        assert (so == n).all() and np.array_equal(so, se) and np.array_equal(ro, re)
+        assert np.array_equal(po, pe), (kind, fs, i16)
+    assert (ff == 1).sum() >= 6
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind,fs", [("silk", 24000), ("silk", 16000), ("hybrid", 24000), ("hybrid", 16000)])
+def test_gpu_fec_below_48k(kind, fs):
+    lanes, ticks = 32, 12
+    fa, fo, ff, ch, frame48 = _fec_streams(kind, lanes, ticks, 81)
+    n = frame48 * fs // 48000
+    ids = np.tile(np.arange(lanes, dtype=np.uint32), ticks)
+    for i16 in (False, True):
+        po, so, ro = _oracle_fec(fa, fo, ff, lanes, ticks, ch, n, fs, i16)
+        pg, sg, rg = _gpu(fa, fo, ids, lanes, ch, n, fs, i16=i16, flags=ff)
         assert np.array_equal(so, sg) and np.array_equal(ro, rg), (kind, fs)
         assert np.array_equal(po, pg), (kind, fs, i16)
