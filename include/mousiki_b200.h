@@ -52,8 +52,8 @@ typedef struct bd_config {
   uint32_t n_streams;                /* decoder states to allocate (stream ids are 0..n_streams-1) */
   int32_t sample_rate_hz;            /* Decoder::new(sample_rate, ..): 48000; 8/12/16/24 kHz: coded CELT-only frames (CELT's down-
                                       * sampling, celt_decoder.rs:2232-2297) and SILK-only packets whose internal rate does not exceed
-                                      * the output rate (resampler.rs:87-176) decode (hybrid at 24 / 16 kHz), lost packets are concealed, in-band FEC works; mode switches
-                                      * and SILK above the output rate report BD_OPUS_UNIMPLEMENTED per packet there; sample counts
+                                      * the output rate (resampler.rs:87-176) decode (hybrid at 24 / 16 kHz), mode switches, lost packets and in-band FEC work as at 48 kHz;
+                                      * SILK above the output rate reports BD_OPUS_UNIMPLEMENTED per packet there; sample counts
                                       * and pcm_stride are in output samples */
   int32_t channels;                  /* Channels::Mono = 1 / Channels::Stereo = 2 */
   int32_t gain_q8;                   /* DecoderBuilder::gain / OPUS_SET_GAIN, Q8 dB (src/codec.rs:411-463) */

@@ -303,11 +303,13 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
     else reject = silk_only && st_prev_mode == 1001;
     // below 48 kHz a stream stays in one mode: plain SILK-only packets, or CELT-only ones (row F4; the fades, redundancy frames and
     // concealed transition frames of a mode switch are not built at those rates)
+#ifdef MB_F4_ONE_MODE   // (kept for bisecting: below 48 kHz a stream stays in one mode)
     if (quirk_ds(Q.quirks) > 1) {
       const bool plain_hybrid = hybrid && !red && !fadeout && (st_prev_mode == 0 || st_prev_mode == 1001);
       const bool plain_silk = silk_only && (st_prev_mode == 0 || st_prev_mode == 1000);
       if ((silk_bit && !plain_hybrid && !plain_silk) || trans_to_celt) reject = true;
     }
+#endif
     if (reject) {
       if (lead) {
         meta[f] = m;
@@ -522,8 +524,8 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
       } else {
         st_prev_mode = 1001; st_prev_redundancy = !c2s;
         st_range_final = celt_rng ^ red_rng;
-        st_last_duration = N;
-        if (lead) { samples_out[p] = N; final_range_out[p] = st_range_final; }
+        st_last_duration = N / quirk_ds(Q.quirks);
+        if (lead) { samples_out[p] = N / quirk_ds(Q.quirks); final_range_out[p] = st_range_final; }
       }
       continue;
     }
@@ -541,8 +543,8 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
     if (fadeout && !red && sil_aux) {   // 40 / 60 ms SILK-only packet after a hybrid one
       silk_side_seen = true; st_fold_serial = 1;
       run_silence(2u | silk_reset);
-      st_prev_mode = 1000; st_prev_redundancy = 0; st_range_final = silk_rng; st_last_duration = silk_n;
-      if (lead) { samples_out[p] = silk_n; final_range_out[p] = st_range_final; }
+      st_prev_mode = 1000; st_prev_redundancy = 0; st_range_final = silk_rng; st_last_duration = silk_n / quirk_ds(Q.quirks);
+      if (lead) { samples_out[p] = silk_n / quirk_ds(Q.quirks); final_range_out[p] = st_range_final; }
       continue;
     }
     if (red_aux) {
@@ -573,8 +575,8 @@ MB_DEV void celt_energy_stream(Team tm, EnergySmem* sm, uint32_t lane, const Ene
       } else {
         st_prev_mode = 1000; st_prev_redundancy = !c2s;
         st_range_final = silk_rng ^ red_rng;
-        st_last_duration = silk_n;
-        if (lead) { samples_out[p] = silk_n; final_range_out[p] = st_range_final; }
+        st_last_duration = silk_n / quirk_ds(Q.quirks);
+        if (lead) { samples_out[p] = silk_n / quirk_ds(Q.quirks); final_range_out[p] = st_range_final; }
       }
       continue;
     }

@@ -286,17 +286,20 @@ MB_DEV void celt_fade_cell(uint32_t f, int c, const TailParams& P) {
   const uint32_t src = P.side_of[f];
   if (src == 0xffffffffu || !P.pcm_f32) return;
   const int CC = P.CC;
+  // Below 48 kHz (row F4) the rows hold every ds-th sample: 2.5 ms are F = 120 / ds samples and smooth_fade steps through the
+  // window by ds (opus_decoder.rs:100-135: inc = 48000 / Fs).
+  const int ds = P.ds, F = SHORT_MDCT / ds;
   const uint32_t p = P.pkt_map ? P.pkt_map[f] : f;
   float* row = P.pcm_f32 + pcm_elem_off(P.out_map, p, P.pcm_stride) + c;
   const float* red = side_row(P.xbuf, src) + c;
   if ((m.flags & 1u) && (m.flags & 512u) && (m.flags & MB_FL_TRANS_IN) && !(m.flags & (8u | 16u))) {
     // SILK-only / hybrid -> CELT-only without a redundancy frame (opus_decoder.rs:1083-1112): the audio concealed in the old mode
     // opens the frame and fades into it (frames of 5 ms and more), or fades into its first 2.5 ms (2.5 ms frames)
-    const int N = SHORT_MDCT << (int)MB_H0_LM(P.rec[rec_index(f, S_HDR0)]);
-    const int at = N >= 2 * SHORT_MDCT ? SHORT_MDCT : 0;
+    const int N = (SHORT_MDCT << (int)MB_H0_LM(P.rec[rec_index(f, S_HDR0)])) / ds;
+    const int at = N >= 2 * F ? F : 0;
     for (int i = 0; i < at; i++) row[(size_t)i * CC] = red[(size_t)i * CC];
-    for (int i = 0; i < SHORT_MDCT; i++) {
-      const float wv = bits2f(kWindow120Bits[i]), w = wv * wv;
+    for (int i = 0; i < F; i++) {
+      const float wv = bits2f(kWindow120Bits[i * ds]), w = wv * wv;
       float* o = row + (size_t)(at + i) * CC;
       *o = w * *o + (1.0f - w) * red[(size_t)(at + i) * CC];
     }
@@ -306,19 +309,19 @@ MB_DEV void celt_fade_cell(uint32_t f, int c, const TailParams& P) {
   }
   const uint32_t status = P.rec[rec_index(f, S_STATUS)];   // (SILK header: in the hybrid layout, or where 40 / 60 ms packets keep it)
   const uint32_t silk_h0 = P.rec[rec_index(f, ((status >> 17) & 3u) ? S_SILK_HYB : S_HDR0)];
-  const int N = (int)((silk_h0 >> 8) & 3u) * (int)((silk_h0 >> 5) & 7u) * 240;   // samples of the finished row (the SILK side's)
+  const int N = (int)((silk_h0 >> 8) & 3u) * (int)((silk_h0 >> 5) & 7u) * 240 / ds;   // samples of the finished row (the SILK side's)
   if (m.flags & 128u) {          // SILK -> CELT: the end of the row fades into the second half of the redundancy frame
-    for (int i = 0; i < SHORT_MDCT; i++) {
-      const float wv = bits2f(kWindow120Bits[i]), w = wv * wv;
-      float* o = row + (size_t)(N - SHORT_MDCT + i) * CC;
-      *o = w * red[(size_t)(SHORT_MDCT + i) * CC] + (1.0f - w) * *o;
+    for (int i = 0; i < F; i++) {
+      const float wv = bits2f(kWindow120Bits[i * ds]), w = wv * wv;
+      float* o = row + (size_t)(N - F + i) * CC;
+      *o = w * red[(size_t)(F + i) * CC] + (1.0f - w) * *o;
     }
   } else if (m.flags & 64u) {    // CELT -> SILK: the redundancy frame opens the row and fades into the SILK audio
-    for (int i = 0; i < SHORT_MDCT; i++) row[(size_t)i * CC] = red[(size_t)i * CC];
-    for (int i = 0; i < SHORT_MDCT; i++) {
-      const float wv = bits2f(kWindow120Bits[i]), w = wv * wv;
-      float* o = row + (size_t)(SHORT_MDCT + i) * CC;
-      *o = w * *o + (1.0f - w) * red[(size_t)(SHORT_MDCT + i) * CC];
+    for (int i = 0; i < F; i++) row[(size_t)i * CC] = red[(size_t)i * CC];
+    for (int i = 0; i < F; i++) {
+      const float wv = bits2f(kWindow120Bits[i * ds]), w = wv * wv;
+      float* o = row + (size_t)(F + i) * CC;
+      *o = w * *o + (1.0f - w) * red[(size_t)(F + i) * CC];
     }
   }
   if (P.apply_gain)

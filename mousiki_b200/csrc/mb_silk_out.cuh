@@ -462,7 +462,8 @@ MB_DEV void silk_lane(const SilkLaneParams& q, uint32_t lane, SilkWork& W, int32
       SilkPacketCtl ctl;
       ctl.mode = SILK_PKT_LOST;
       ctl.samples48 = imin(SHORT_MDCT << (int)MB_H0_LM(rb[S_HDR0 * 32]), 2 * SHORT_MDCT);
-      ctl.limit = ctl.samples48;
+      ctl.limit = ctl.samples48 / quirk_ds(q.quirks);
+      o.fs_out_khz = 48 / quirk_ds(q.quirks);
       silk_synth_packet(S, W, H, X, side_live, 0u, rb, q.quirks, o, stage, fir, ctl);
       continue;
     }
@@ -483,7 +484,7 @@ MB_DEV void silk_lane(const SilkLaneParams& q, uint32_t lane, SilkWork& W, int32
     // 120 samples, here for the rest; redundancy: k_fade for the whole row
     const bool fadeout = (fl & 8u) && !((status >> 17) & 1u) && !MB_ST_LOST(status);
     o.CC = q.CC; o.gain = q.gain; o.apply_gain = ((shared && !fadeout) || (fl & MB_FL_FADE_ROW)) ? 0 : q.apply_gain;
-    o.gain_from = fadeout ? SHORT_MDCT : 0;
+    o.gain_from = fadeout ? SHORT_MDCT / quirk_ds(q.quirks) : 0;
     o.fs_out_khz = 48 / quirk_ds(q.quirks);
     SilkPacketCtl ctl;
     ctl.mode = MB_ST_LOST(status) ? SILK_PKT_LOST : (MB_ST_FEC(status) ? SILK_PKT_FEC : SILK_PKT_NORMAL);

@@ -6,7 +6,8 @@ denormalise_bands clears the bins from N / downsample on, src/celt/bands.rs:4198
 48 kHz sample and keeps every downsample-th one) for coded CELT-only frames, single and multi-frame packets, f32 / int16 / 24-bit;
 and SILK-only packets whose internal rate does not exceed the output rate — the resampler's copy, 2x and interpolating modes
 (src/silk/resampler.rs:87-176, 279-369) in the k_silk lane. Not built: the resampler's down-sampling FIRs (a WB packet in an
-8 / 12 kHz decoder, hybrid packets below 16 kHz) and mode switches at those rates — reported per packet as -5 there; in-band FEC works as at 48 kHz.
+8 / 12 kHz decoder, hybrid packets below 16 kHz) — reported per packet as -5 there. Mode switches (redundancy frames, fades, concealed
+transition frames) and in-band FEC work as at 48 kHz.
 Hybrid streams decode at 24 / 16 kHz (SILK WB through the resampler, the CELT bands down-sampled and added onto it). Lost packets
 of CELT-only and SILK-only streams are concealed at those rates like at 48 kHz (the concealment runs at the codec's own rate; only
 the sample accounting changes).
@@ -88,24 +89,6 @@ def test_gpu_output_rate_packets_of_several_frames_and_mixed_sizes():
     assert np.array_equal(so, sg) and np.array_equal(ro, rg) and np.array_equal(po, pg)
 
 
-@pytest.mark.gpu
-def test_gpu_output_rate_refuses_what_it_does_not_carry():
-    lanes, fs = 8, 24000
-    arena, offsets = helpers.fuzz_grid(lanes, 3, 60, lambda t, j, r: helpers.celt_toc(3, True), seed=37)
-    flags = np.zeros(3 * lanes, dtype=np.uint8)
-    flags[lanes + 0] = flags[lanes + 1] = 1     # decode(fec=true) on a CELT-only packet: concealed like a loss (opus_decoder.rs:1247-1250)
-    arena[offsets[lanes + 2]] = arena[offsets[lanes + 3]] = helpers.silk_toc(2, 1, True)      # SILK-only
-    arena[offsets[lanes + 4]] = arena[offsets[lanes + 5]] = 0x7C                               # hybrid FB 20 ms stereo
-    ids = np.tile(np.arange(lanes, dtype=np.uint32), 3)
-    pg, sg, rg = _gpu(arena, offsets, ids, lanes, 2, 480, fs, flags=flags)
-    assert (sg[lanes + 2:lanes + 6] == -5).all(), sg[lanes:2 * lanes]
-    assert (sg[:lanes] == 480).all() and (sg[lanes:lanes + 2] == 480).all() and (sg[lanes + 6:2 * lanes] == 480).all()
-    po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, 3, 2, 480, fs=fs)
-    for j in (6, 7):
-        for t in range(3):
-            assert np.array_equal(pg[t * lanes + j], po[t * lanes + j]) and rg[t * lanes + j] == ro[t * lanes + j]
-
-
 SILK_SHAPES = [
     ("wb 20 ms mono", helpers.silk_toc(2, 1, False), 1, (20, 60), 960),
     ("wb 20 ms stereo", helpers.silk_toc(2, 1, True), 2, (25, 70), 960),
@@ -171,20 +154,60 @@ def test_gpu_silk_only_output_rates(fs):
 
 
 @pytest.mark.gpu
-def test_gpu_output_rate_refuses_silk_above_the_output_rate_and_mode_switches():
+def test_gpu_output_rate_refuses_silk_above_the_output_rate():
     lanes, fs = 8, 12000
     wb, wo = helpers.silk_fuzz_grid(lanes, 1, (20, 60), lambda k, r: helpers.silk_toc(2, 1, False), seed=41, channels=1)   # WB in a 12 kHz decoder
     ids = np.arange(lanes, dtype=np.uint32)
     pg, sg, rg = _gpu(wb, wo, ids, lanes, 1, 240, fs)
     assert (sg == -5).all()
-    # NB SILK, then a CELT-only packet: the switch (concealed transition frame + fade) is not built below 48 kHz
-    na, no = helpers.silk_fuzz_grid(lanes, 1, (10, 40), lambda k, r: helpers.silk_toc(0, 1, False), seed=43, channels=1)
-    ca, co = helpers.fuzz_grid(lanes, 1, 40, lambda t, j, r: helpers.celt_toc(3, False), seed=45)
-    arena = np.concatenate([na, ca])
-    offsets = np.concatenate([no, no[-1] + co[1:]]).astype(np.uint32)
-    ids = np.tile(np.arange(lanes, dtype=np.uint32), 2)
-    pg, sg, rg = _gpu(arena, offsets, ids, lanes, 1, 240, fs)
-    assert (sg[:lanes] == 240).all() and (sg[lanes:] == -5).all()
+    hy, ho = helpers.silk_fuzz_grid(lanes, 1, (40, 120), lambda k, r: 0x7C, seed=42, channels=2)                           # hybrid in a 12 kHz decoder
+    pg, sg, rg = _gpu(hy, ho, ids, lanes, 2, 240, fs)
+    assert (sg == -5).all()
+
+
+def _walk_toc(fs):
+    """CELT-only of every size and bandwidth, SILK-only up to the output rate, hybrid from 16 kHz on: a stream that switches mode freely"""
+    from test_hybrid_parity import hyb_toc
+    max_bw = 2 if fs >= 16000 else (1 if fs >= 12000 else 0)
+
+    def toc(k, r):
+        m = int(r.integers(0, 10))
+        if m < 4:
+            return helpers.celt_toc(int(r.integers(1, 4)), bool(r.integers(0, 2)), int(r.integers(0, 4)))
+        if m < 9 or fs < 16000:
+            return helpers.silk_toc(int(r.integers(0, max_bw + 1)), int(r.integers(0, 2)), bool(r.integers(0, 2)))
+        return hyb_toc(r.integers(0, 2), r.integers(0, 2), r.integers(0, 2))
+    return toc
+
+
+@pytest.mark.parametrize("fs", RATES)
+def test_emul_every_mode_switch_decodes_below_48k(fs):
+    """Random walks over the modes, with and without redundancy frames (src/opus_decoder.rs:575-640, 746-819, 868-1112): the fades
+    step through the window by 48000 / Fs (smooth_fade, :100-135), side rows and transition frames hold output-rate samples."""
+    lanes, ticks = 8, 14
+    cap = 960 * fs // 48000
+    for ch, seed in ((2, 91), (1, 92)):
+        arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, (10, 140), _walk_toc(fs), seed=seed, channels=ch, redundancy=True)
+        for i16 in (False, True):
+            po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, cap, i16=i16, fs=fs)
+            pe, se, re, _, _ = helpers.emul_decode_grid(arena, offsets, lanes, ticks, ch, cap, i16=i16, fs=fs)
+            assert (so > 0).all() and np.array_equal(so, se) and np.array_equal(ro, re)
+            assert np.array_equal(po, pe), (fs, ch, i16)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fs", RATES)
+def test_gpu_every_mode_switch_decodes_below_48k(fs):
+    lanes, ticks = 48, 14
+    cap = 960 * fs // 48000
+    ids = np.tile(np.arange(lanes, dtype=np.uint32), ticks)
+    for ch, seed in ((2, 97), (1, 98)):
+        arena, offsets = helpers.silk_fuzz_grid(lanes, ticks, (10, 140), _walk_toc(fs), seed=seed, channels=ch, redundancy=True)
+        for i16 in (False, True):
+            po, so, ro = helpers.oracle_decode_grid(arena, offsets, lanes, ticks, ch, cap, i16=i16, fs=fs)
+            pg, sg, rg = _gpu(arena, offsets, ids, lanes, ch, cap, fs, i16=i16, max_frames_per_pass=5 * lanes)
+            assert (so > 0).all() and np.array_equal(so, sg) and np.array_equal(ro, rg), (fs, ch)
+            assert np.array_equal(po, pg), (fs, ch, i16)
 
 
 def _oracle_lossy(arena, offsets, lost, lanes, ticks, ch, n, fs, i16):
