@@ -50,11 +50,9 @@ typedef struct bd_handle bd_handle;
 typedef struct bd_config {
   uint32_t struct_size;              /* sizeof(bd_config), for forward compatibility */
   uint32_t n_streams;                /* decoder states to allocate (stream ids are 0..n_streams-1) */
-  int32_t sample_rate_hz;            /* Decoder::new(sample_rate, ..): 48000; 8/12/16/24 kHz: coded CELT-only frames (CELT's down-
-                                      * sampling, celt_decoder.rs:2232-2297) and SILK-only packets whose internal rate does not exceed
-                                      * the output rate (resampler.rs:87-176) decode (hybrid at 24 / 16 kHz), mode switches, lost packets and in-band FEC work as at 48 kHz;
-                                      * SILK above the output rate reports BD_OPUS_UNIMPLEMENTED per packet there; sample counts
-                                      * and pcm_stride are in output samples */
+  int32_t sample_rate_hz;            /* Decoder::new(sample_rate, ..): 48000, 24000, 16000, 12000 or 8000 (CELT's down-sampling,
+                                      * celt_decoder.rs:2232-2297; every mode of the SILK resampler, resampler.rs:87-176); sample
+                                      * counts and pcm_stride are in output samples */
   int32_t channels;                  /* Channels::Mono = 1 / Channels::Stereo = 2 */
   int32_t gain_q8;                   /* DecoderBuilder::gain / OPUS_SET_GAIN, Q8 dB (src/codec.rs:411-463) */
   int32_t disable_phase_inversion;   /* <0: decoder default (mono decoders disable it), 0/1 explicit */

@@ -34,10 +34,7 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
   const uint8_t* data = arena + off;
   // The overlap-add form of the inverse MDCT (quirk Q2 cleared) is built for coded CELT-only frames: concealment, in-band FEC and
   // packets with a SILK part are refused per packet there.
-  // So are output rates below 48 kHz (row F4: the CELT down-sampling path is built, the SILK resampler's other ratios are not).
   const bool q2_off = !(quirks & Q2_MDCT_ZERO_FILL);
-  const int ds_out = quirk_ds(quirks);
-  const bool ola = q2_off || ds_out > 1;
   // (below 48 kHz lost packets are concealed and in-band FEC is decoded like at 48 kHz)
   if (q2_off && ((flags && (flags[pkt] & 3u)) || len == 0)) {
     rec_base[S_STATUS * 32] = (uint32_t)(uint8_t)(int8_t)MB_UNIMPLEMENTED;
@@ -64,10 +61,7 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
   if (code == MB_OK) {
     toc = data[0];
     if (toc & 3u) code = MB_UNIMPLEMENTED;              // multi-frame packets (row F1)
-    // (below 48 kHz a SILK-only packet decodes when its internal rate does not exceed the output rate: the resampler's copy, 2x and
-    //  interpolating modes are built, its down-sampling FIRs are not; hybrid packets and concealment frames are refused)
-    else if (ola && ((q2_off && len - 1 <= 1) || (!(toc & 0x80u) && (q2_off || ((toc & 0x60u) == 0x60u ? 16 : 8 + 4 * (int)((toc >> 5) & 3u)) > 48 / ds_out))))
-      code = MB_UNIMPLEMENTED;
+    else if (q2_off && (len - 1 <= 1 || !(toc & 0x80u))) code = MB_UNIMPLEMENTED;
     else if (len - 1 > 1275) code = MB_INVALID_PACKET;  // src/packet.rs:465: a frame is at most 1275 bytes
     else if (!(toc & 0x80u)) {
       if (len - 1 <= 1) {                                    // a frame of at most one byte is a concealed frame (src/opus_decoder.rs:491-496)

@@ -24,6 +24,7 @@ MB_DEV bool silk_set_fs(SilkChanState& c, int fs_khz, int nb_subfr) {
     for (int i = 0; i < 6; i++) c.res_iir[i] = 0;
     for (int i = 0; i < 8; i++) c.res_fir[i] = 0;
     for (int i = 0; i < 16; i++) c.res_delay[i] = 0;
+    for (int i = 0; i < 24; i++) c.res_down[i] = 0;
     c.res_ready = 1;
   }
   if (c.fs_khz != fs_khz) {
@@ -160,6 +161,60 @@ MB_DEV_NOINLINE int silk_resample48(SilkChanState& c, const SilkSrc& in, int n_i
         made += 2;
       }
       c.res_iir[0] = S0; c.res_iir[1] = S1; c.res_iir[2] = S2; c.res_iir[3] = S3; c.res_iir[4] = S4; c.res_iir[5] = S5;
+      int16_t keep[16];
+      for (int i = 0; i < delay; i++) keep[i] = (int16_t)in.at(n_in - delay + i);
+      for (int i = 0; i < delay; i++) c.res_delay[i] = keep[i];
+      return made;
+    }
+    if (fs_out < fs) {
+      // Output rate below the internal rate (resampler_private_down_fir.rs:139-284, resampler_private_ar2.rs:19-38): a second-order
+      // AR filter (Q8), then a polyphase FIR stepped by the ratio; batches of 1 ms (the delay buffer), then 10 ms, each with
+      // the previous batch's last `order` filtered samples in front. 16 -> 12 kHz and 12 -> 8 kHz: 18 taps, 3 / 2 phases; 16 -> 8: 24.
+      const int16_t* coefs = fs_out * 4 == fs * 3 ? silk_Resampler_3_4_COEFS : (fs_out * 3 == fs * 2 ? silk_Resampler_2_3_COEFS : silk_Resampler_1_2_COEFS);
+      const int fracs = fs_out * 4 == fs * 3 ? 3 : (fs_out * 3 == fs * 2 ? 2 : 1);
+      const int order = fs_out * 2 == fs ? 24 : 18, half = order / 2;
+      const int16_t* firc = coefs + 2;
+      const int32_t a0 = coefs[0], a1 = coefs[1];
+      int64_t invd = ((int64_t)fs << 16) / fs_out;                       // compute_inv_ratio_q16, no 2x stage
+      while (((invd * fs_out) >> 16) < (int64_t)fs) invd++;
+      const int32_t incd = (int32_t)invd;
+      int32_t buf[160 + 24];
+      for (int i = 0; i < order; i++) buf[i] = c.res_down[i];
+      int32_t A0 = c.res_iir[0], A1 = c.res_iir[1];
+      int made = 0, t = 0, n = fs;
+      while (t < n_in) {
+        if (n > n_in - t) n = n_in - t;
+        for (int k = 0; k < n; k++, t++) {
+          const int32_t x = t < delay ? (int32_t)c.res_delay[t] : in.at(t - delay);
+          int32_t o32 = s_add(A0, s_shl(x, 8));
+          buf[order + k] = o32;
+          o32 = s_shl(o32, 2);
+          A0 = s_mlawb(A1, o32, a0);
+          A1 = s_mulwb(o32, a1);
+        }
+        const int32_t max_idx = n << 16;
+        for (int32_t idx = 0; idx < max_idx; idx = s_add(idx, incd)) {
+          const int32_t* b = buf + (idx >> 16);
+          int32_t acc;
+          if (order == 18) {
+            const int ind = s_mulwb(idx & 0xFFFF, fracs);
+            const int16_t* f = firc + half * ind;
+            const int16_t* r = firc + half * (fracs - 1 - ind);
+            acc = s_mulwb(b[0], f[0]);
+            for (int k = 1; k < half; k++) acc = s_mlawb(acc, b[k], f[k]);
+            for (int k = 0; k < half; k++) acc = s_mlawb(acc, b[order - 1 - k], r[k]);
+          } else {
+            acc = s_mulwb(s_add(b[0], b[order - 1]), firc[0]);
+            for (int k = 1; k < half; k++) acc = s_mlawb(acc, s_add(b[k], b[order - 1 - k]), firc[k]);
+          }
+          silk_sink_put(sink, s_sat16(s_add(acc, 1 << 5) >> 6));
+          made++;
+        }
+        for (int i = 0; i < order; i++) buf[i] = buf[n + i];
+        n = 10 * fs;
+      }
+      for (int i = 0; i < order; i++) c.res_down[i] = buf[i];
+      c.res_iir[0] = A0; c.res_iir[1] = A1;
       int16_t keep[16];
       for (int i = 0; i < delay; i++) keep[i] = (int16_t)in.at(n_in - delay + i);
       for (int i = 0; i < delay; i++) c.res_delay[i] = keep[i];
@@ -314,6 +369,7 @@ MB_DEV_NOINLINE int silk_synth_packet(SilkState& S, SilkWork& W, const SilkHistR
       for (int k = 0; k < 6; k++) S.ch[1].res_iir[k] = S.ch[0].res_iir[k];
       for (int k = 0; k < 8; k++) S.ch[1].res_fir[k] = S.ch[0].res_fir[k];
       for (int k = 0; k < 16; k++) S.ch[1].res_delay[k] = S.ch[0].res_delay[k];
+      for (int k = 0; k < 24; k++) S.ch[1].res_down[k] = S.ch[0].res_down[k];
       S.ch[1].res_ready = 1;
     }
     S.n_channels_api = (int8_t)CC; S.n_channels_internal = (int8_t)nci;

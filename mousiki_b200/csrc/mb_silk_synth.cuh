@@ -81,6 +81,7 @@ struct SilkChanState {
   int32_t res_iir[6];            // up2_hq all-pass state of the API resampler
   int16_t res_fir[8];            // FIR interpolator tail
   int16_t res_delay[16];         // input delay line (fs_khz samples)
+  int32_t res_down[24];          // down-sampling kernel's FIR tail (output rate below the internal rate; AR2 state in res_iir[0..2))
   int32_t prev_gain_q16;
   int16_t fs_khz, nb_subfr, frame_length, lag_prev;
   int8_t first_frame_after_reset, last_gain_index, prev_signal_type, res_ready;
@@ -120,6 +121,7 @@ MB_DEV void silk_chan_reset(SilkChanState& c) {   // init_decoder.rs:14-26 + Dec
   for (int i = 0; i < 16; i++) { c.s_lpc_q14[i] = 0; c.prev_nlsf_q15[i] = 0; c.res_delay[i] = 0; }
   for (int i = 0; i < 6; i++) c.res_iir[i] = 0;
   for (int i = 0; i < 8; i++) c.res_fir[i] = 0;
+  for (int i = 0; i < 24; i++) c.res_down[i] = 0;
   c.prev_gain_q16 = 65536;
   c.fs_khz = 0; c.nb_subfr = 4; c.frame_length = 0; c.lag_prev = 0;
   c.first_frame_after_reset = 1; c.last_gain_index = 0; c.prev_signal_type = 0; c.res_ready = 0;

@@ -579,11 +579,16 @@ int SilkResampler::init(int fs_in, int fs_out) {
   for (int i = 0; i < 3; i++) if (in_rates[i] == fs_in) ii = i;
   for (int i = 0; i < 5; i++) if (out_rates[i] == fs_out) oi = i;
   if (ii < 0 || oi < 0) return -1;
-  if (fs_out < fs_in) return -2;  // down-FIR kernels (API rate below the internal rate) are not restated
   *this = SilkResampler();
   input_delay = silk_delay_matrix_dec[ii * 5 + oi];
   fs_in_khz = fs_in / 1000; fs_out_khz = fs_out / 1000; batch_size = fs_in_khz * 10;
-  mode = fs_out == fs_in ? 0 : (fs_out == 2 * fs_in ? 1 : 2);
+  mode = fs_out == fs_in ? 0 : (fs_out == 2 * fs_in ? 1 : (fs_out > fs_in ? 2 : 3));
+  if (mode == 3) {   // down_fir_config (resampler.rs:246-264); a decoder meets 3/4 (16 -> 12), 2/3 (12 -> 8) and 1/2 (16 -> 8)
+    if ((int64_t)fs_out * 4 == (int64_t)fs_in * 3) { down_fracs = 3; down_order = 18; down_coefs = silk_Resampler_3_4_COEFS; }
+    else if ((int64_t)fs_out * 3 == (int64_t)fs_in * 2) { down_fracs = 2; down_order = 18; down_coefs = silk_Resampler_2_3_COEFS; }
+    else if (fs_out * 2 == fs_in) { down_fracs = 1; down_order = 24; down_coefs = silk_Resampler_1_2_COEFS; }
+    else return -2;
+  }
   int up2x = mode == 2;
   int64_t inv = ((int64_t)fs_in << (16 + up2x)) / fs_out;
   while (((inv * fs_out) >> 16) < ((int64_t)fs_in << up2x)) inv++;
@@ -629,6 +634,47 @@ static int iir_fir(SilkResampler* R, int16_t* out, const int16_t* in, int in_len
   memcpy(R->s_fir, buf + 2 * n, sizeof(R->s_fir));
   return produced;
 }
+// resampler_private_ar2.rs:19-38 + resampler_private_down_fir.rs:139-284
+static int down_fir(SilkResampler* R, int16_t* out, const int16_t* in, int in_len) {
+  if (in_len <= 0) return 0;
+  const int order = R->down_order, half = order / 2, fracs = R->down_fracs;
+  const int16_t* fir = R->down_coefs + 2;
+  const int32_t a0 = R->down_coefs[0], a1 = R->down_coefs[1];
+  int32_t buf[160 + 36];
+  memcpy(buf, R->s_down, order * sizeof(int32_t));
+  int produced = 0, n = 0;
+  while (in_len > 0) {
+    n = in_len < R->batch_size ? in_len : R->batch_size;
+    for (int k = 0; k < n; k++) {   // second-order AR filter, Q8 out
+      int32_t o32 = w_add(R->s_iir[0], w_shl((int32_t)in[k], 8));
+      buf[order + k] = o32;
+      o32 = w_shl(o32, 2);
+      R->s_iir[0] = smlawb(R->s_iir[1], o32, a0);
+      R->s_iir[1] = smulwb(o32, a1);
+    }
+    const int32_t max_idx = n << 16;
+    for (int32_t idx = 0; idx < max_idx; idx = w_add(idx, R->inv_ratio_q16)) {
+      const int32_t* b = buf + (idx >> 16);
+      int32_t acc;
+      if (order == 18) {
+        const int ind = smulwb(idx & 0xFFFF, fracs);
+        const int16_t* f = fir + half * ind;
+        const int16_t* r = fir + half * (fracs - 1 - ind);
+        acc = smulwb(b[0], f[0]);
+        for (int k = 1; k < half; k++) acc = smlawb(acc, b[k], f[k]);
+        for (int k = 0; k < half; k++) acc = smlawb(acc, b[order - 1 - k], r[k]);
+      } else {
+        acc = smulwb(w_add(b[0], b[order - 1]), fir[0]);
+        for (int k = 1; k < half; k++) acc = smlawb(acc, w_add(b[k], b[order - 1 - k]), fir[k]);
+      }
+      out[produced++] = sat16(w_add(acc, 1 << 5) >> 6);
+    }
+    in += n; in_len -= n;
+    if (in_len > 0) memmove(buf, buf + n, order * sizeof(int32_t));
+  }
+  memcpy(R->s_down, buf + n, order * sizeof(int32_t));
+  return produced;
+}
 // resampler.rs:279-369
 int SilkResampler::run(int16_t* out, const int16_t* in, int in_len) {
   int ns = fs_in_khz - input_delay;
@@ -641,9 +687,12 @@ int SilkResampler::run(int16_t* out, const int16_t* in, int in_len) {
   } else if (mode == 1) {
     up2_hq(s_iir, out, delay_buf, fs_in_khz); produced = fs_out_khz;
     up2_hq(s_iir, out + produced, in2, len2); produced += 2 * len2;
-  } else {
+  } else if (mode == 2) {
     produced = iir_fir(this, out, delay_buf, fs_in_khz);
     produced += iir_fir(this, out + produced, in2, len2);
+  } else {
+    produced = down_fir(this, out, delay_buf, fs_in_khz);
+    produced += down_fir(this, out + produced, in2, len2);
   }
   if (input_delay > 0) memcpy(delay_buf, in + in_len - input_delay, input_delay * sizeof(int16_t));
   return produced;

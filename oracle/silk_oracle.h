@@ -46,10 +46,14 @@ struct SilkControl {  // decoder_control.rs
 };
 
 struct SilkResampler {  // resampler.rs:40-48
-  int fs_in_khz = 0, fs_out_khz = 0, batch_size = 0, input_delay = 0, inv_ratio_q16 = 0, mode = 0;  // 0 copy 1 up2 2 iir_fir
+  int fs_in_khz = 0, fs_out_khz = 0, batch_size = 0, input_delay = 0, inv_ratio_q16 = 0, mode = 0;  // 0 copy 1 up2 2 iir_fir 3 down_fir
   int16_t delay_buf[96] = {0};
   int32_t s_iir[6] = {0};
   int16_t s_fir[8] = {0};
+  // down-sampling kernel (resampler_private_down_fir.rs:20-80): AR2 state in s_iir[0..2), FIR tail, ratio configuration
+  int32_t s_down[36] = {0};
+  int down_order = 0, down_fracs = 0;
+  const int16_t* down_coefs = nullptr;
   int init(int fs_in_hz, int fs_out_hz);
   int run(int16_t* out, const int16_t* in, int in_len);
 };

@@ -4,11 +4,11 @@ src/opus_decoder.rs:1550-1556.
 Built: the CELT side — `downsample = 48000 / Fs` in synthesis and de-emphasis (src/celt/celt_decoder.rs:584-776, 2232-2297;
 denormalise_bands clears the bins from N / downsample on, src/celt/bands.rs:4198-4204; the de-emphasis filter runs over every
 48 kHz sample and keeps every downsample-th one) for coded CELT-only frames, single and multi-frame packets, f32 / int16 / 24-bit;
-and SILK-only packets whose internal rate does not exceed the output rate — the resampler's copy, 2x and interpolating modes
-(src/silk/resampler.rs:87-176, 279-369) in the k_silk lane. Not built: the resampler's down-sampling FIRs (a WB packet in an
-8 / 12 kHz decoder, hybrid packets below 16 kHz) — reported per packet as -5 there. Mode switches (redundancy frames, fades, concealed
-transition frames) and in-band FEC work as at 48 kHz.
-Hybrid streams decode at 24 / 16 kHz (SILK WB through the resampler, the CELT bands down-sampled and added onto it). Lost packets
+and the SILK side — every mode of the resampler in the k_silk lane (src/silk/resampler.rs:87-176, 279-369): copy, 2x, the
+interpolating up-sampler with the ratio's own step, and the down-sampling kernel where the output rate lies below the internal
+one (resampler_private_ar2.rs, resampler_private_down_fir.rs: a WB packet in a 12 / 8 kHz decoder). Mode switches (redundancy
+frames, fades, concealed transition frames) and in-band FEC work as at 48 kHz. Hybrid streams: SILK WB through the resampler, the
+CELT bands down-sampled and added onto it (nothing of them is left below 16 kHz). Lost packets
 of CELT-only and SILK-only streams are concealed at those rates like at 48 kHz (the concealment runs at the codec's own rate; only
 the sample accounting changes).
 
@@ -99,7 +99,9 @@ SILK_SHAPES = [
 
 
 def _silk_fits(toc, fs):
-    return 8 + 4 * ((toc >> 5) & 3) <= fs // 1000
+    """(every SILK bandwidth decodes at every output rate: below the internal rate the resampler's down-sampling kernel runs,
+    resampler_private_down_fir.rs — 16 -> 12 kHz, 12 -> 8 kHz, 16 -> 8 kHz)"""
+    return True
 
 
 @pytest.mark.parametrize("fs", RATES)
@@ -119,7 +121,7 @@ def test_emul_silk_only_output_rates(fs):
         ran += 1
     assert ran >= 2
     # a stream that changes its SILK bandwidth and frame size from packet to packet (the resampler is re-initialised on a rate change)
-    bws = [b for b in (0, 1, 2) if 8 + 4 * b <= fs // 1000]
+    bws = [0, 1, 2]
     arena, offsets = helpers.silk_fuzz_grid(lanes, 10, (20, 80), lambda k, r: helpers.silk_toc(int(r.choice(bws)), int(r.integers(0, 2)), True),
                                             seed=13, channels=2)
     cap = 960 * fs // 48000
@@ -143,7 +145,7 @@ def test_gpu_silk_only_output_rates(fs):
             pg, sg, rg = _gpu(arena, offsets, ids, lanes, ch, frame, fs, i16=i16, max_frames_per_pass=2 * lanes)
             assert np.array_equal(so, sg) and np.array_equal(ro, rg), (name, fs)
             assert np.array_equal(po, pg), (name, fs, i16)
-    bws = [b for b in (0, 1, 2) if 8 + 4 * b <= fs // 1000]
+    bws = [0, 1, 2]
     arena, offsets = helpers.silk_fuzz_grid(lanes, 8, (20, 80), lambda k, r: helpers.silk_toc(int(r.choice(bws)), int(r.integers(0, 2)), True),
                                             seed=19, channels=2)
     ids = np.tile(np.arange(lanes, dtype=np.uint32), 8)
@@ -153,28 +155,16 @@ def test_gpu_silk_only_output_rates(fs):
     assert np.array_equal(so, sg) and np.array_equal(ro, rg) and np.array_equal(po, pg)
 
 
-@pytest.mark.gpu
-def test_gpu_output_rate_refuses_silk_above_the_output_rate():
-    lanes, fs = 8, 12000
-    wb, wo = helpers.silk_fuzz_grid(lanes, 1, (20, 60), lambda k, r: helpers.silk_toc(2, 1, False), seed=41, channels=1)   # WB in a 12 kHz decoder
-    ids = np.arange(lanes, dtype=np.uint32)
-    pg, sg, rg = _gpu(wb, wo, ids, lanes, 1, 240, fs)
-    assert (sg == -5).all()
-    hy, ho = helpers.silk_fuzz_grid(lanes, 1, (40, 120), lambda k, r: 0x7C, seed=42, channels=2)                           # hybrid in a 12 kHz decoder
-    pg, sg, rg = _gpu(hy, ho, ids, lanes, 2, 240, fs)
-    assert (sg == -5).all()
-
-
 def _walk_toc(fs):
-    """CELT-only of every size and bandwidth, SILK-only up to the output rate, hybrid from 16 kHz on: a stream that switches mode freely"""
+    """CELT-only, SILK-only and hybrid packets of every size and bandwidth: a stream that switches mode freely"""
     from test_hybrid_parity import hyb_toc
-    max_bw = 2 if fs >= 16000 else (1 if fs >= 12000 else 0)
+    max_bw = 2
 
     def toc(k, r):
         m = int(r.integers(0, 10))
         if m < 4:
             return helpers.celt_toc(int(r.integers(1, 4)), bool(r.integers(0, 2)), int(r.integers(0, 4)))
-        if m < 9 or fs < 16000:
+        if m < 9:
             return helpers.silk_toc(int(r.integers(0, max_bw + 1)), int(r.integers(0, 2)), bool(r.integers(0, 2)))
         return hyb_toc(r.integers(0, 2), r.integers(0, 2), r.integers(0, 2))
     return toc
@@ -246,7 +236,8 @@ def _lossy_streams(kind, lanes, ticks, fs, seed):
     return arena, offsets, loss_pattern(lanes, ticks, seed=seed + 1), 2, 960
 
 
-@pytest.mark.parametrize("kind,fs", [("celt", 24000), ("celt", 8000), ("silk", 24000), ("silk", 8000), ("hybrid", 24000), ("hybrid", 16000)])
+@pytest.mark.parametrize("kind,fs", [("celt", 24000), ("celt", 8000), ("silk", 24000), ("silk", 8000), ("hybrid", 24000), ("hybrid", 16000),
+                                     ("hybrid", 8000)])
 def test_emul_concealment_below_48k(kind, fs):
     from test_plc_parity import virtual_grid
 
@@ -269,7 +260,7 @@ def test_emul_concealment_below_48k(kind, fs):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("kind,fs", [("celt", 24000), ("celt", 16000), ("celt", 8000), ("silk", 24000), ("silk", 16000), ("silk", 8000),
-                                     ("hybrid", 24000), ("hybrid", 16000)])
+                                     ("hybrid", 24000), ("hybrid", 16000), ("hybrid", 12000)])
 def test_gpu_concealment_below_48k(kind, fs):
     """Through the host front end: flags[p] & 2 = decode(None); the packet's bytes are ignored."""
     lanes, ticks = 48, 14
@@ -317,7 +308,7 @@ def _fec_streams(kind, lanes, ticks, seed):
     return fa, fo, ff, 2, 960
 
 
-@pytest.mark.parametrize("kind,fs", [("silk", 24000), ("silk", 16000), ("hybrid", 24000), ("hybrid", 16000)])
+@pytest.mark.parametrize("kind,fs", [("silk", 24000), ("silk", 16000), ("silk", 8000), ("hybrid", 24000), ("hybrid", 12000)])
 def test_emul_fec_below_48k(kind, fs):
     lanes, ticks = 6, 12
     fa, fo, ff, ch, frame48 = _fec_streams(kind, lanes, ticks, 71)
@@ -340,7 +331,7 @@ def test_emul_fec_below_48k(kind, fs):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("kind,fs", [("silk", 24000), ("silk", 16000), ("hybrid", 24000), ("hybrid", 16000)])
+@pytest.mark.parametrize("kind,fs", [("silk", 24000), ("silk", 12000), ("hybrid", 16000), ("hybrid", 8000)])
 def test_gpu_fec_below_48k(kind, fs):
     lanes, ticks = 32, 12
     fa, fo, ff, ch, frame48 = _fec_streams(kind, lanes, ticks, 81)
