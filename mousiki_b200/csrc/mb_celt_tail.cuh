@@ -276,7 +276,9 @@ MB_DEV void celt_deemph_lane(uint32_t lane, int c, const TailParams& P) {
 // gain is applied to the finished row. w = window[i]^2 over 120 samples (48 kHz).
 MB_DEV void celt_fade_cell(uint32_t f, int c, const TailParams& P) {
   const FrameMeta m = P.meta[f];
-  if ((m.flags & MB_FL_PLC) && !(m.flags & 1u) && P.pcm_f32) {   // a lost packet before anything was decoded: silence (opus_decoder.rs:527-540)
+  // a lost packet before anything was decoded: silence (opus_decoder.rs:527-540). (Neither CELT nor SILK part: a lost packet of a
+  // SILK-only stream carries bit 1 and whatever seed the stream's CELT history left — it is the k_silk lane's, not a zero fill.)
+  if ((m.flags & MB_FL_PLC) && !(m.flags & 3u) && P.pcm_f32) {
     const uint32_t p0 = P.pkt_map ? P.pkt_map[f] : f;
     float* row0 = P.pcm_f32 + pcm_elem_off(P.out_map, p0, P.pcm_stride) + c;
     for (int i = 0; i < (int)m.seed_in; i++) row0[(size_t)i * P.CC] = 0.f;

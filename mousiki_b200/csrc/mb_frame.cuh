@@ -122,7 +122,9 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
         }
       } else {
         bool after_hybrid = prev_mode && *prev_mode == 1001;
-        if (prev_pkt != 0xffffffffu && offsets[prev_pkt + 1] > offsets[prev_pkt]) {
+        if (prev_pkt != 0xffffffffu && flags && (flags[prev_pkt] & 2u) && !fec) after_hybrid = true;   // lost: the mode before it is the stream
+                                                                                            // pass's to know; make room for the frame
+        else if (prev_pkt != 0xffffffffu && offsets[prev_pkt + 1] > offsets[prev_pkt]) {
           const uint32_t ptoc = arena[offsets[prev_pkt]];
           after_hybrid = !(ptoc & 0x80u) && (ptoc & 0x60u) == 0x60u;
         }

@@ -142,6 +142,7 @@ static int packet_parse(const uint8_t* data, int len, int self_delimited, Parsed
 }
 
 struct OpusDecoder {
+  int self_delimited = 0, last_packet_offset = 0;   // set by the multistream wrapper below
   int fs = 48000, channels = 2;
   CeltDecoder celt;
   SilkDecoder silk;
@@ -383,8 +384,9 @@ struct OpusDecoder {
     int pmode = packet_mode(toc), pbw = packet_bandwidth(toc), pfs = packet_samples_per_frame(toc, fs);
     int pch = (toc & 4) ? 2 : 1;
     Parsed P;
-    int r = packet_parse(data, len, 0, &P);
+    int r = packet_parse(data, len, self_delimited, &P);   // (self-delimited framing: substreams of a multistream packet, :1139-1160)
     if (r < 0) return r;
+    last_packet_offset = P.packet_offset;
     if (decode_fec) {   // :1240-1316
       if (fsz < pfs || pmode == MODE_CELT_ONLY || mode == MODE_CELT_ONLY) return decode_native(nullptr, 0, pcm, fsz, 0, soft_clip);
       const int duration_copy = last_packet_duration;
@@ -628,6 +630,88 @@ int orc_decode_grid(int fs, int channels, uint32_t quirks, const uint8_t* arena,
   work(0);
   for (auto& t : th) t.join();
   return 0;
+}
+
+// ---- multistream decoder (row F4): opus_multistream_decode_native (src/opus_multistream.rs:717-950) — N substream decoders, the
+// first N-1 substream packets in self-delimited framing, channel mapping as in get_left/right/mono_channel (:60-140).
+struct MsDecoder {
+  int fs = 48000, channels = 0, streams = 0, coupled = 0;
+  uint8_t mapping[256];
+  std::vector<OpusDecoder> dec;
+};
+void* orc_ms_create(int fs, int channels, int streams, int coupled, const uint8_t* mapping, uint32_t quirks) {
+  if (channels < 1 || channels > 255 || streams < 1 || coupled < 0 || coupled > streams || streams + coupled > 255) return nullptr;
+  for (int c = 0; c < channels; c++) if (mapping[c] != 255 && mapping[c] >= streams + coupled) return nullptr;
+  MsDecoder* m = new MsDecoder;
+  m->fs = fs; m->channels = channels; m->streams = streams; m->coupled = coupled;
+  memcpy(m->mapping, mapping, channels);
+  m->dec.resize(streams);
+  for (int s = 0; s < streams; s++) {
+    if (m->dec[s].init(fs, s < coupled ? 2 : 1) != 0) { delete m; return nullptr; }
+    m->dec[s].celt.quirks = quirks; m->dec[s].silk.quirks = quirks;
+  }
+  return m;
+}
+void orc_ms_destroy(void* h) { delete (MsDecoder*)h; }
+// pcm (float) or pcm16 (int16: the substreams decode with the soft clipper on, then float2int16): [frame_size][channels]
+int orc_ms_decode(void* h, const uint8_t* data, int len, float* pcm, int16_t* pcm16, int frame_size, int fec) {
+  MsDecoder* m = (MsDecoder*)h;
+  if (frame_size <= 0) return OPUS_BAD_ARG;
+  const int nb = m->streams;
+  if (frame_size > m->fs / 25 * 3) frame_size = m->fs / 25 * 3;
+  const bool do_plc = len == 0 || data == nullptr;
+  if (!do_plc) {
+    if (len < 2 * nb - 1) return OPUS_INVALID_PACKET;
+    const uint8_t* cur = data; int remaining = len, samples = -1;     // opus_multistream_packet_validate (:717-752)
+    for (int s = 0; s < nb; s++) {
+      if (remaining == 0) return OPUS_INVALID_PACKET;
+      Parsed P;
+      const int r = packet_parse(cur, remaining, s + 1 != nb, &P);
+      if (r < 0) return r;
+      const int ns = P.count * packet_samples_per_frame(cur[0], m->fs);
+      if (ns * 25 > m->fs * 3) return OPUS_INVALID_PACKET;
+      if (samples >= 0 && samples != ns) return OPUS_INVALID_PACKET;
+      samples = ns;
+      cur += P.packet_offset; remaining -= P.packet_offset;
+    }
+    if (samples > frame_size) return OPUS_BUFFER_TOO_SMALL;
+  }
+  std::vector<float> scratch((size_t)2 * frame_size);
+  const uint8_t* cur = data; int remaining = len, decoded_fs = frame_size;
+  auto put = [&](int chan, const float* src, int stride, int n) {
+    for (int i = 0; i < n; i++) {
+      const float v = src ? src[(size_t)i * stride] : 0.f;
+      if (pcm16) pcm16[(size_t)i * m->channels + chan] = float2int16(v); else pcm[(size_t)i * m->channels + chan] = v;
+    }
+  };
+  for (int s = 0; s < nb; s++) {
+    OpusDecoder& d = m->dec[s];
+    d.self_delimited = s + 1 != nb;
+    int ret;
+    if (do_plc) ret = d.decode_native(nullptr, 0, scratch.data(), decoded_fs, fec, pcm16 != nullptr);
+    else {
+      if (remaining == 0) return OPUS_INTERNAL_ERROR;
+      ret = d.decode_native(cur, remaining, scratch.data(), decoded_fs, fec, pcm16 != nullptr);
+      if (ret >= 0) { cur += d.last_packet_offset; remaining -= d.last_packet_offset; }
+    }
+    d.self_delimited = 0;
+    if (ret < 0) return ret;
+    if (ret == 0) return OPUS_INTERNAL_ERROR;
+    decoded_fs = ret;
+    for (int c = 0; c < m->channels; c++) {
+      if (s < m->coupled) {
+        if (m->mapping[c] == 2 * s) put(c, scratch.data(), 2, decoded_fs);
+        else if (m->mapping[c] == 2 * s + 1) put(c, scratch.data() + 1, 2, decoded_fs);
+      } else if (m->mapping[c] == s + m->coupled) put(c, scratch.data(), 1, decoded_fs);
+    }
+  }
+  for (int c = 0; c < m->channels; c++) if (m->mapping[c] == 255) put(c, nullptr, 0, decoded_fs);   // muted channels
+  return decoded_fs;
+}
+uint32_t orc_ms_final_range(void* h) {   // OPUS_GET_FINAL_RANGE of a multistream decoder: xor over the substreams (:640-660)
+  MsDecoder* m = (MsDecoder*)h; uint32_t r = 0;
+  for (auto& d : m->dec) r ^= d.range_final;
+  return r;
 }
 
 }  // extern "C"
