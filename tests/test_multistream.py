@@ -238,3 +238,25 @@ def test_emul_streams_that_switch_mode_and_lose_packets(ch, seed):
         ol.orc_destroy(h)
     assert (so == 960).all() and np.array_equal(so, se) and np.array_equal(ro, re)
     assert np.array_equal(po, pe)
+
+
+def test_reference_multistream_known_answers():
+    """The vectors the reference holds for this path (src/opus_multistream.rs:2548-2578): a two-stream packet whose first stream is
+    self-delimited validates to 480 samples; a second stream of another duration is an invalid packet; a one-byte-payload SILK
+    packet decodes through a stereo multistream decoder. On the oracle and on the host-side framing."""
+    two = dict(channels=2, streams=2, coupled=0, mapping=[0, 1])
+    ok, bad = bytes([0x00, 0x01, 0xAA, 0x00, 0xBB]), bytes([0x00, 0x01, 0xAA, 0x18, 0xBB])
+    _, s, _ = _oracle_ms(two, [ok], 960, False)
+    assert s[0] == 480
+    _, s, _ = _oracle_ms(two, [bad], 2880, False)
+    assert s[0] == -4
+    toc, frames, off = parse_packet(ok, True)
+    assert (toc, frames, off) == (0x00, [b"\xaa"], 3) and parse_packet(ok[off:], False)[1] == [b"\xbb"]
+
+    from mousiki_b200.multistream import MultistreamBatchDecoder
+    ms = MultistreamBatchDecoder.__new__(MultistreamBatchDecoder)      # (framing only: no device behind it)
+    ms.fs, ms.streams = 48000, 2
+    assert ms._validate(ok, 960)[1] == 0 and ms._validate(bad, 2880)[1] == -4 and ms._validate(ok, 240)[1] == -2
+    stereo = dict(channels=2, streams=1, coupled=1, mapping=[0, 1])
+    _, s, _ = _oracle_ms(stereo, [bytes([0x00, 0xAA])], 960, True)
+    assert s[0] > 0
