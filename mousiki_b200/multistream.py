@@ -305,3 +305,73 @@ def pack_multistream(sub_packets):
                 body += _size_bytes(len(f))
             out += body + b"".join(frames)
     return out
+
+
+def matrix_out_float(matrix, x):
+    """mapping_matrix_multiply_channel_out_float (src/mapping_matrix.rs:188-217) over every input row in turn: matrix int16
+    [rows, cols] (Q15), x float32 [frames, n_in] -> float32 [frames, rows]; output += (cell / 32768) * sample, one input channel
+    after the other, every product and sum rounded to float32 like the reference's loop."""
+    rows = matrix.shape[0]
+    out = np.zeros((x.shape[0], rows), dtype=np.float32)
+    for c in range(x.shape[1]):
+        coeff = matrix[:, c].astype(np.float32) / np.float32(32768.0)
+        out += coeff[None, :] * x[:, c:c + 1].astype(np.float32)
+    return out
+
+
+def matrix_out_short(matrix, x16):
+    """mapping_matrix_multiply_channel_out_short (:251-283): x16 int16 [frames, n_in] -> int16 [frames, rows], each term
+    (cell * sample + 16384) >> 15, the int16 sum wrapping."""
+    rows = matrix.shape[0]
+    out = np.zeros((x16.shape[0], rows), dtype=np.int32)
+    for c in range(x16.shape[1]):
+        delta = (matrix[:, c].astype(np.int32)[None, :] * x16[:, c:c + 1].astype(np.int32) + 16384) >> 15
+        out = ((out + delta + 32768) & 0xFFFF) - 32768
+    return out.astype(np.int16)
+
+
+class ProjectionBatchDecoder:
+    """M independent `OpusProjectionDecoder`s (`opus_projection_decoder_create`, src/projection.rs:533-570): a multistream decoder
+    with the identity mapping, its decoded channels mixed into `channels` outputs by the demixing matrix (little-endian int16,
+    column-major, `channels` rows x `streams + coupled_streams` columns)."""
+
+    def __init__(self, n_decoders, sample_rate, channels, streams, coupled_streams, demixing_matrix, device=0, **kw):
+        n_in = streams + coupled_streams
+        raw = bytes(demixing_matrix)
+        if len(raw) != 2 * n_in * channels:
+            raise ValueError("demixing matrix size")                      # OPUS_BAD_ARG (:541-547)
+        self.matrix = np.frombuffer(raw, dtype="<i2").reshape(n_in, channels).T.copy()     # [rows = channels, cols = n_in]
+        self.channels, self.n_in = channels, n_in
+        self._ms = MultistreamBatchDecoder(n_decoders, sample_rate, channels, streams, coupled_streams, list(range(channels)), device=device, **kw)
+
+    def close(self):
+        self._ms.close()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def final_range(self):
+        return self._ms.final_range()
+
+    def _decode(self, packets, frame_size, i16, fec):
+        pcm, samples = self._ms._decode(packets, frame_size, i16, fec)
+        n_used = min(self.n_in, self.channels)     # decoded channel c reaches the mixer when an output channel maps to it
+        out = np.zeros_like(pcm)
+        for m in range(len(packets)):
+            if samples[m] <= 0:
+                continue
+            x = pcm[m].reshape(-1, self.channels)[:samples[m], :n_used]
+            y = matrix_out_short(self.matrix, x) if i16 else matrix_out_float(self.matrix, x)
+            out[m].reshape(-1, self.channels)[:samples[m]] = y
+        return out, samples
+
+    def decode_float(self, packets, frame_size, fec=False):
+        """opus_projection_decode_float (:661-706)"""
+        return self._decode(packets, frame_size, False, fec)
+
+    def decode(self, packets, frame_size, fec=False):
+        """opus_projection_decode (:614-659): int16, the substreams through the soft clipper, Q15 mixing with rounding"""
+        return self._decode(packets, frame_size, True, fec)

@@ -714,4 +714,84 @@ uint32_t orc_ms_final_range(void* h) {   // OPUS_GET_FINAL_RANGE of a multistrea
   return r;
 }
 
+// ---- projection decoder (row F4): opus_projection_decode / _decode_float (src/projection.rs:533-706) — a multistream decoder with
+// the identity mapping whose decoded channels are accumulated through the demixing matrix (column-major int16, Q15;
+// mapping_matrix_multiply_channel_out_float / _short, src/mapping_matrix.rs:188-283).
+// x: [frame_size][cols] decoded channels (float; for the int16 form already soft-clipped); out: [frame_size][rows], zeroed here.
+void orc_matrix_out_float(const int16_t* m, int rows, int cols, const float* x, int n_in, float* out, int frame_size) {
+  for (int i = 0; i < frame_size * rows; i++) out[i] = 0.f;
+  for (int c = 0; c < n_in; c++)
+    for (int f = 0; f < frame_size; f++) {
+      const float v = x[(size_t)f * cols + c];
+      for (int r = 0; r < rows; r++) {
+        const float coeff = (float)m[(size_t)rows * c + r] / 32768.0f;
+        out[(size_t)f * rows + r] += coeff * v;
+      }
+    }
+}
+void orc_matrix_out_short(const int16_t* m, int rows, int cols, const float* x, int n_in, int16_t* out, int frame_size) {
+  for (int i = 0; i < frame_size * rows; i++) out[i] = 0;
+  for (int c = 0; c < n_in; c++)
+    for (int f = 0; f < frame_size; f++) {
+      const int32_t v = float2int16(x[(size_t)f * cols + c]);
+      for (int r = 0; r < rows; r++) {
+        const int32_t delta = ((int32_t)m[(size_t)rows * c + r] * v + 16384) >> 15;
+        out[(size_t)f * rows + r] = (int16_t)((int32_t)out[(size_t)f * rows + r] + delta);
+      }
+    }
+}
+// h: a multistream decoder created with channels output channels and mapping[c] = c; matrix: rows = channels, cols = streams + coupled
+int orc_proj_decode(void* h, const int16_t* matrix, const uint8_t* data, int len, float* pcm, int16_t* pcm16, int frame_size, int fec) {
+  MsDecoder* m = (MsDecoder*)h;
+  const int rows = m->channels, cols = m->streams + m->coupled;
+  if (frame_size > m->fs / 25 * 3) frame_size = m->fs / 25 * 3;
+  std::vector<float> x((size_t)frame_size * rows, 0.f);
+  // (the substreams decode to float — with the soft clipper on for the int16 form — into the identity-mapped channels)
+  int ret;
+  {
+    // decode float with soft clip: run the int16 path's substream decode but keep floats
+    std::vector<float> scratch((size_t)2 * frame_size);
+    const int nb = m->streams;
+    const bool do_plc = len == 0 || data == nullptr;
+    if (!do_plc) {
+      if (len < 2 * nb - 1) return OPUS_INVALID_PACKET;
+      const uint8_t* cur = data; int remaining = len, samples = -1;
+      for (int s = 0; s < nb; s++) {
+        if (remaining == 0) return OPUS_INVALID_PACKET;
+        Parsed P;
+        const int r = packet_parse(cur, remaining, s + 1 != nb, &P);
+        if (r < 0) return r;
+        const int ns = P.count * packet_samples_per_frame(cur[0], m->fs);
+        if (ns * 25 > m->fs * 3) return OPUS_INVALID_PACKET;
+        if (samples >= 0 && samples != ns) return OPUS_INVALID_PACKET;
+        samples = ns;
+        cur += P.packet_offset; remaining -= P.packet_offset;
+      }
+      if (samples > frame_size) return OPUS_BUFFER_TOO_SMALL;
+    }
+    const uint8_t* cur = data; int remaining = len, dfs = frame_size;
+    for (int s = 0; s < nb; s++) {
+      OpusDecoder& d = m->dec[s];
+      d.self_delimited = s + 1 != nb;
+      int r = do_plc ? d.decode_native(nullptr, 0, scratch.data(), dfs, fec, pcm16 != nullptr)
+                     : d.decode_native(cur, remaining, scratch.data(), dfs, fec, pcm16 != nullptr);
+      if (!do_plc && r >= 0) { cur += d.last_packet_offset; remaining -= d.last_packet_offset; }
+      d.self_delimited = 0;
+      if (r < 0) return r;
+      if (r == 0) return OPUS_INTERNAL_ERROR;
+      dfs = r;
+      const int width = s < m->coupled ? 2 : 1, first = s < m->coupled ? 2 * s : s + m->coupled;
+      for (int k = 0; k < width; k++)
+        if (first + k < rows)
+          for (int i = 0; i < dfs; i++) x[(size_t)i * rows + first + k] = scratch[(size_t)i * width + k];
+    }
+    ret = dfs;
+  }
+  const int n_in = cols < rows ? cols : rows;   // decoded channel c reaches the handler only when an output channel maps to it (c < channels)
+  // x is laid out [frame][rows]; the matrix routines take the input stride as `cols`
+  if (pcm16) orc_matrix_out_short(matrix, rows, rows, x.data(), n_in, pcm16, ret);
+  else orc_matrix_out_float(matrix, rows, rows, x.data(), n_in, pcm, ret);
+  return ret;
+}
+
 }  // extern "C"

@@ -35,6 +35,8 @@ def oracle_lib():
         lib.orc_decode_i16.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int]
         lib.orc_trace_enable.argtypes = [C.c_void_p, C.c_int]
         lib.orc_last_redundancy.argtypes = [C.c_void_p]
+        lib.orc_matrix_out_float.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        lib.orc_matrix_out_short.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
         lib.orc_trace_info.argtypes = [C.c_void_p, C.c_void_p]
         lib.orc_trace_get.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
         lib.orc_decode_grid.argtypes = [C.c_int, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,

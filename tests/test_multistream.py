@@ -260,3 +260,69 @@ def test_reference_multistream_known_answers():
     stereo = dict(channels=2, streams=1, coupled=1, mapping=[0, 1])
     _, s, _ = _oracle_ms(stereo, [bytes([0x00, 0xAA])], 960, True)
     assert s[0] > 0
+
+
+# ---------------------------------------------------------------------------------------------- projection (demixing matrix)
+SIMPLE_MATRIX_DATA = [0, 32767, 0, 0, 32767, 0, 0, 0, 0, 0, 0, 32767]     # src/mapping_matrix.rs:370 (4 rows x 3 columns, column-major)
+SIMPLE_MATRIX_INPUT = [32767, 0, -32768, 29491, -3277, -29491, 26214, -6554, -26214, 22938, -9830, -22938, 19661, -13107, -19661,
+                       16384, -16384, -16384, 13107, -19661, -13107, 9830, -22938, -9830, 6554, -26214, -6554, 3277, -29491, -3277]
+SIMPLE_MATRIX_EXPECTED = [0, 32767, 0, -32768, -3277, 29491, 0, -29491, -6554, 26214, 0, -26214, -9830, 22938, 0, -22938, -13107,
+                          19661, 0, -19661, -16384, 16384, 0, -16384, -19661, 13107, 0, -13107, -22938, 9830, 0, -9830, -26214, 6554, 0,
+                          -6554, -29491, 3277, 0, -3277]
+
+
+def test_matrix_mixing_known_answer():
+    """simple_matrix_operations_follow_reference (src/mapping_matrix.rs:415-500): the _out_short and _out_float forms, within the
+    reference's own tolerance of 1 LSB — on the host-side mixer and on the oracle's."""
+    from mousiki_b200.multistream import matrix_out_float, matrix_out_short
+    m = np.array(SIMPLE_MATRIX_DATA, dtype=np.int16).reshape(3, 4).T.copy()
+    x16 = np.array(SIMPLE_MATRIX_INPUT, dtype=np.int16).reshape(10, 3)
+    want = np.array(SIMPLE_MATRIX_EXPECTED, dtype=np.int32).reshape(10, 4)
+    assert np.abs(matrix_out_short(m, x16).astype(np.int32) - want).max() <= 1
+    xf = x16.astype(np.float32) / np.float32(32768.0)
+    yf = matrix_out_float(m, xf)
+    y16 = np.clip(np.rint(yf * 32768.0), -32768, 32767).astype(np.int32)
+    assert np.abs(y16 - want).max() <= 1
+    lib = helpers.oracle_lib()
+    md = np.array(SIMPLE_MATRIX_DATA, dtype=np.int16)
+    of, o16 = np.zeros((10, 4), dtype=np.float32), np.zeros((10, 4), dtype=np.int16)
+    lib.orc_matrix_out_float(helpers.ptr(md), 4, 3, helpers.ptr(xf), 3, helpers.ptr(of), 10)
+    lib.orc_matrix_out_short(helpers.ptr(md), 4, 3, helpers.ptr(xf), 3, helpers.ptr(o16), 10)
+    assert np.array_equal(of, yf) and np.array_equal(o16, matrix_out_short(m, x16))
+
+
+def _oracle_proj(layout, matrix_i16, packets, frame_size, i16):
+    lib = _ms_lib()
+    lib.orc_proj_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+    mp = np.arange(layout["channels"], dtype=np.uint8)
+    h = lib.orc_ms_create(48000, layout["channels"], layout["streams"], layout["coupled"], helpers.ptr(mp), helpers.QUIRKS_MOUSIKI)
+    assert h
+    pcm = np.zeros((len(packets), frame_size * layout["channels"]), dtype=np.int16 if i16 else np.float32)
+    samples = np.zeros(len(packets), dtype=np.int32)
+    for t, pkt in enumerate(packets):
+        buf = np.frombuffer(pkt, dtype=np.uint8).copy() if pkt else None
+        samples[t] = lib.orc_proj_decode(h, helpers.ptr(matrix_i16), helpers.ptr(buf), len(pkt) if pkt else 0,
+                                         None if i16 else helpers.ptr(pcm[t]), helpers.ptr(pcm[t]) if i16 else None, frame_size, 0)
+    lib.orc_ms_destroy(h)
+    return pcm, samples
+
+
+@pytest.mark.gpu
+def test_gpu_projection_decode():
+    """First-order ambisonics shape: 4 output channels from 2 coupled streams (4 decoded channels), a dense random Q15 matrix."""
+    from mousiki_b200.multistream import ProjectionBatchDecoder
+
+    layout = dict(channels=4, streams=2, coupled=2)
+    rng = np.random.default_rng(5)
+    matrix = rng.integers(-20000, 20000, size=16).astype("<i2")     # column-major [rows = 4][cols = 4]
+    n_dec, ticks = 3, 5
+    subs = [_sub_packets(dict(streams=2, coupled=2), ticks, seed=71 + d) for d in range(n_dec)]
+    packets = [[None if (t == 3 and d == 1) else pack_multistream(subs[d][t]) for t in range(ticks)] for d in range(n_dec)]
+    for i16 in (False, True):
+        want = [_oracle_proj(layout, matrix, packets[d], 960, i16) for d in range(n_dec)]
+        with ProjectionBatchDecoder(n_dec, 48000, 4, 2, 2, matrix.tobytes()) as pd:
+            for t in range(ticks):
+                pcm, samples = (pd.decode if i16 else pd.decode_float)([packets[d][t] for d in range(n_dec)], 960)
+                for d in range(n_dec):
+                    assert samples[d] == want[d][1][t] == 960
+                    assert np.array_equal(pcm[d], want[d][0][t]), (i16, d, t)
