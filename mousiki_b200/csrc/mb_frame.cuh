@@ -122,7 +122,7 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
         }
       } else {
         bool after_hybrid = prev_mode && *prev_mode == 1001;
-        if (prev_pkt != 0xffffffffu && flags && (flags[prev_pkt] & 2u) && !fec) after_hybrid = true;   // lost: the mode before it is the stream
+        if (prev_pkt != 0xffffffffu && flags && (flags[prev_pkt] & 2u)) after_hybrid = true;   // lost: the mode before it is the stream
                                                                                             // pass's to know; make room for the frame
         else if (prev_pkt != 0xffffffffu && offsets[prev_pkt + 1] > offsets[prev_pkt]) {
           const uint32_t ptoc = arena[offsets[prev_pkt]];
@@ -137,7 +137,7 @@ MB_DEV void parse_cell_body(const uint8_t* arena, const uint32_t* offsets, uint3
         rec_base[S_AUXREF * 32] = 0u;
         if (st_silk & (1u << 14)) {
           const int C = (toc & 4u) ? 2 : 1, end = ((toc >> 5) & 3u) == 0 ? 13 : 17;   // NB 13, MB / WB 17 (opus_decoder.rs:861-866)
-          const uint32_t keep = (1u << 16) | (1u << 18);
+          const uint32_t keep = (1u << 16) | (1u << 18) | (st_silk & (1u << 30));   // SILK part, its layout, decoded from LBRR data
           const bool own_room = (st_silk & (1u << 18)) != 0;
           if (red.bytes > 0 && own_room && !after_hybrid)
             celt_parse_frame<0>(data + 1 + red.cutoff, red.bytes, 1, C, end, quirks, disable_inv, rec_base, nullptr,

@@ -326,3 +326,42 @@ def test_gpu_projection_decode():
                 for d in range(n_dec):
                     assert samples[d] == want[d][1][t] == 960
                     assert np.array_equal(pcm[d], want[d][0][t]), (i16, d, t)
+
+
+def test_emul_fec_on_a_silk_packet_right_after_a_hybrid_one():
+    """decode(.., fec = true) taken on the hybrid -> SILK-only switch: the cell holds the LBRR-decoded SILK record AND the 2.5 ms
+    CELT fade-out frame (opus_decoder.rs:868-893); the status word must keep saying "decoded from LBRR data" (stereo: the side
+    channel's presence and the mid-only flag follow the LBRR rules, dec_api.rs:240-290). Then the same packet decoded normally."""
+    lanes, ticks = 48, 4
+    ha, ho = helpers.silk_fuzz_grid(lanes, 1, (40, 160), lambda k, r: hyb_toc(1, 1, bool(k & 1)), seed=5, channels=2)
+    sa, so_ = helpers.silk_fuzz_grid(lanes, 2, (30, 90), lambda k, r: helpers.silk_toc(2, 1, True), seed=6, channels=2)
+    pk, fl = [], []
+    for j in range(lanes):
+        pk.append(ha[ho[j]:ho[j + 1]]); fl.append(0)
+    for j in range(lanes):
+        pk.append(sa[so_[j]:so_[j + 1]]); fl.append(1)
+    for j in range(lanes):
+        pk.append(sa[so_[j]:so_[j + 1]]); fl.append(0)
+    for j in range(lanes):
+        pk.append(sa[so_[lanes + j]:so_[lanes + j + 1]]); fl.append(0)
+    off = np.zeros(len(pk) + 1, dtype=np.uint32)
+    off[1:] = np.cumsum([len(x) for x in pk])
+    arena, ff = np.concatenate(pk).astype(np.uint8), np.array(fl, dtype=np.uint8)
+    lib = helpers.emul_lib()
+    lib.emu_set_flags(helpers.ptr(ff))
+    try:
+        pe, se, re, _, _ = helpers.emul_decode_grid(arena, off, lanes, ticks, 2, 960)
+    finally:
+        lib.emu_set_flags(None)
+    ol = helpers.oracle_lib()
+    po, so, ro = np.zeros_like(pe), np.zeros_like(se), np.zeros_like(re)
+    for j in range(lanes):
+        h = ol.orc_create(48000, 2, helpers.QUIRKS_MOUSIKI)
+        for t in range(ticks):
+            p = t * lanes + j
+            b = np.ascontiguousarray(arena[off[p]:off[p + 1]])
+            so[p] = ol.orc_decode_float(h, helpers.ptr(b), len(b), helpers.ptr(po[p]), 960, int(ff[p] & 1))
+            ro[p] = ol.orc_final_range(h)
+        ol.orc_destroy(h)
+    assert (so == 960).all() and np.array_equal(so, se) and np.array_equal(ro, re)
+    assert np.array_equal(po, pe)
