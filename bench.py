@@ -431,7 +431,10 @@ def run_gpu(args):
     traffic = None
     tf = ROOT / "profiles" / "roofline_traffic.json"
     if tf.exists():
-        traffic = json.loads(tf.read_text()).get(top_name)
+        table = json.loads(tf.read_text())
+        traffic = table.get(top_name)
+        if traffic is not None and table.get("_per_frame"):   # per-frame figures: scaled to the frames one launch processes
+            traffic = int(traffic * frames_per_launch)
     cpu_baseline = None
     if world == 1:
         cores = os.cpu_count() or 1
